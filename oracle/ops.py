@@ -1,0 +1,165 @@
+"""Oracle: floating-point ops of the hot path restated in torch-CPU fp32.
+
+Third-party arithmetic that is NOT vendored in the reference is restated from
+its published semantics and anchored on the reference's call sites:
+  * spconv-cu120==2.3.6 SubMConv3d  (uv_requirements.txt:152; call sites
+    point_transformer_v3m1_base.py:278-284, :499-506; structure.py:137-146)
+  * torch-scatter==2.1.2 segment_csr / scatter_mean (uv_requirements.txt:170;
+    call sites point_transformer_v3m1_base.py:416-421, keypoint_ptv3.py:44)
+  * flash-attn==2.6.3 varlen qkv-packed attention (uv_requirements.txt:36; call
+    site :208-215) -- the oracle follows the reference's own dense branch
+    :191-206 instead.
+Test infrastructure only (see oracle/__init__.py).
+"""
+import numpy as np
+import torch
+
+
+# ----------------------------------------------------------------------------
+# A3: padding / window layout (point_transformer_v3m1_base.py:115-170)
+# ----------------------------------------------------------------------------
+def padding_and_inverse(offset, K):
+    """Closed form of get_padding_and_inverse.  offset: int64 (B,) cumulative.
+    Returns pad (T,), unpad (N,), cu_seqlens int32."""
+    offset = np.asarray(offset, dtype=np.int64)
+    starts = np.concatenate([[0], offset[:-1]])
+    pad, unpad, cu = [], [], []
+    t0 = 0
+    for s, e in zip(starts, offset):
+        n = int(e - s)
+        n_pad = ((n + K - 1) // K) * K if n > K else n
+        p = np.arange(n_pad, dtype=np.int64)
+        if n_pad != n:
+            r = n % K
+            # the K-r empty slots of the last window repeat the last K-r slots of
+            # the previous window => last window == last K rows of the scene
+            p[n_pad - K + r:] = p[n_pad - 2 * K + r: n_pad - K]
+        pad.append(p + s)
+        unpad.append(np.arange(n, dtype=np.int64) + t0)
+        cu.append(np.arange(t0, t0 + n_pad, K, dtype=np.int32) if n_pad > 0 else np.zeros(0, np.int32))
+        t0 += n_pad
+    cu.append(np.array([t0], dtype=np.int32))
+    return np.concatenate(pad), np.concatenate(unpad), np.concatenate(cu)
+
+
+def windows_from_offset(offset, K):
+    """Equivalent window description used by the CUDA kernel: one record per
+    window (q_start, q_len, k_start, k_len) in serialized-row space.  Queries are
+    the window's own real rows; keys are the window's rows, except that the
+    ragged last window of a scene with n > K uses the last K rows of the scene."""
+    offset = np.asarray(offset, dtype=np.int64)
+    starts = np.concatenate([[0], offset[:-1]])
+    recs = []
+    for s, e in zip(starts, offset):
+        n = int(e - s)
+        if n <= K:
+            if n > 0:
+                recs.append((s, n, s, n))
+            continue
+        nw = (n + K - 1) // K
+        for w in range(nw):
+            q0 = s + w * K
+            ql = min(K, e - q0)
+            k0 = q0 if ql == K else e - K
+            recs.append((q0, ql, k0, K))
+    return np.asarray(recs, dtype=np.int64).reshape(-1, 4)
+
+
+def window_attention(qkv, order, inverse, offset, H, K, scale=None):
+    """SerializedAttention.forward dense branch (:172-222) for ONE order, flash
+    window semantics (K fixed; scenes with n<=K form one short window).
+    qkv: (N, 3C) fp32 in storage order; order/inverse: serialized order row
+    and its inverse (N,).  Returns (N, C) in storage order."""
+    N, C3 = qkv.shape
+    C = C3 // 3
+    d = C // H
+    scale = scale if scale is not None else d ** -0.5
+    pad, unpad, cu = padding_and_inverse(offset, K)
+    pad_t = torch.from_numpy(pad)
+    g = qkv[order[pad_t]]                       # (T, 3C) padded serialized layout
+    out = torch.empty(g.shape[0], C, dtype=qkv.dtype)
+    for i in range(len(cu) - 1):
+        a, b = int(cu[i]), int(cu[i + 1])
+        if b <= a:
+            continue
+        blk = g[a:b].reshape(b - a, 3, H, d).permute(1, 2, 0, 3)   # (3,H,L,d)
+        q, k, v = blk[0], blk[1], blk[2]
+        attn = torch.softmax((q * scale) @ k.transpose(-2, -1), dim=-1)
+        out[a:b] = (attn @ v).transpose(0, 1).reshape(b - a, C)
+    inv = torch.from_numpy(unpad)[inverse]
+    return out[inv]
+
+
+# ----------------------------------------------------------------------------
+# A5: submanifold convolution (spconv 2.x SubMConv3d semantics, restated)
+# ----------------------------------------------------------------------------
+def _pack_key(b, xyz, shift=21):
+    return (b.to(torch.int64) << (3 * shift)) | (xyz[:, 0].to(torch.int64) << (2 * shift)) | \
+           (xyz[:, 1].to(torch.int64) << shift) | xyz[:, 2].to(torch.int64)
+
+
+def subm_neighbor_table(indices, ksize):
+    """indices int (N,4)=[b,x,y,z] -> nbr int64 (N, k^3), -1 where the site
+    grid+delta (same batch element) is not active.  Kernel offset index is
+    ((dx+r)*k + (dy+r))*k + (dz+r), i.e. weight[:, kx, ky, kz, :] multiplies the
+    input at grid + (kx-r, ky-r, kz-r) (cross-correlation, as torch conv3d;
+    SubM index generation ignores `padding`, windows are centred)."""
+    idx = indices.to(torch.int64)
+    N = idx.shape[0]
+    r = ksize // 2
+    OFF = 1 << 10                                   # bias so shifted coords stay >= 0
+    key = _pack_key(idx[:, 0], idx[:, 1:] + OFF)
+    skey, sidx = torch.sort(key)
+    nbr = torch.full((N, ksize ** 3), -1, dtype=torch.int64)
+    kk = 0
+    for dx in range(-r, r + 1):
+        for dy in range(-r, r + 1):
+            for dz in range(-r, r + 1):
+                q = _pack_key(idx[:, 0], idx[:, 1:] + OFF + torch.tensor([dx, dy, dz]))
+                pos = torch.searchsorted(skey, q).clamp_(max=N - 1)
+                hit = skey[pos] == q
+                nbr[hit, kk] = sidx[pos[hit]]
+                kk += 1
+    return nbr
+
+
+def subm_conv(features, nbr, weight, bias=None):
+    """out[i] = bias + sum_k W[:,k,:] @ in[nbr[i,k]]  (absent neighbours skipped).
+    weight: spconv 2.x layout (out, kD, kH, kW, in)."""
+    Cout = weight.shape[0]
+    Cin = weight.shape[-1]
+    K3 = nbr.shape[1]
+    w = weight.reshape(Cout, K3, Cin)
+    out = torch.zeros(features.shape[0], Cout, dtype=features.dtype)
+    for k in range(K3):
+        rows = torch.nonzero(nbr[:, k] >= 0).squeeze(1)
+        if rows.numel() == 0:
+            continue
+        out.index_add_(0, rows, features[nbr[rows, k]] @ w[:, k, :].t())
+    if bias is not None:
+        out = out + bias
+    return out
+
+
+# ----------------------------------------------------------------------------
+# torch_scatter restatements
+# ----------------------------------------------------------------------------
+def segment_csr(src, indptr, reduce="sum"):
+    """torch_scatter.segment_csr along dim 0; empty segments give 0."""
+    lengths = (indptr[1:] - indptr[:-1]).to(torch.int64)
+    r = {"sum": "sum", "mean": "mean", "max": "max", "min": "min"}[reduce]
+    out = torch.segment_reduce(src, r, lengths=lengths, axis=0, unsafe=True)
+    if reduce in ("max", "min", "mean"):
+        empty = lengths == 0
+        if bool(empty.any()):
+            out[empty] = 0
+    return out
+
+
+def scatter_mean(src, index, dim=0, dim_size=None):
+    assert dim == 0
+    n = int(index.max()) + 1 if dim_size is None else dim_size
+    out = torch.zeros((n,) + tuple(src.shape[1:]), dtype=src.dtype)
+    out.index_add_(0, index, src)
+    cnt = torch.bincount(index, minlength=n).clamp_(min=1).to(src.dtype)
+    return out / cnt.view(-1, *([1] * (src.dim() - 1)))

@@ -1,0 +1,175 @@
+"""Freeze outputs of the UNMODIFIED reference (imported from /root/reference on
+CPU through ref_loader.py) into small .npz fixtures.  Run in the build
+container only:  python tests/golden/make_golden.py
+
+Fixtures (all inputs are seeded; the script is the provenance):
+  serialization.npz  reference `encode` for the 4 orders at depths 1..16 + KATs
+  gridsample.npz     reference GridSample (fnv + ravel, train + test mode) with
+                     np.argsort forced stable and np.random.randint recorded
+  padding.npz        reference SerializedAttention.get_padding_and_inverse
+  attention.npz      reference SerializedAttention.forward (dense branch)
+  forward.npz        reference OffsetKeypointPTv3 forward (PT-v3m1 base config,
+                     deterministic weights synth.make_weights(seed=0)), two
+                     scenes run one per forward, with intermediate features
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REPO = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, REPO)
+sys.path.insert(0, HERE)
+
+import ref_loader  # noqa: E402
+from ptv3_b200 import synth  # noqa: E402
+
+BASE_CFG = dict(
+    in_channels=4, order=["z", "z-trans", "hilbert", "hilbert-trans"], stride=(2, 2, 2, 2),
+    enc_depths=(2, 2, 2, 6, 2), enc_channels=(32, 64, 128, 256, 512), enc_num_head=(2, 4, 8, 16, 32),
+    enc_patch_size=(1024,) * 5, dec_depths=(2, 2, 2, 2), dec_channels=(64, 64, 128, 256),
+    dec_num_head=(4, 4, 8, 16), dec_patch_size=(1024,) * 4, shuffle_orders=True)
+
+
+def gold_serialization(R):
+    rng = np.random.default_rng(1)
+    out = {}
+    g = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [1, 2, 3], [5, 9, 14], [255, 256, 511], [1000, 77, 300]])
+    b = np.array([0, 0, 0, 0, 0, 1, 1, 2])
+    out["kat_grid"], out["kat_batch"] = g, b
+    for o in BASE_CFG["order"]:
+        out[f"kat_{o}"] = R.encode(torch.from_numpy(g), torch.from_numpy(b), 10, o).numpy()
+    for depth in range(1, 17):
+        gg = rng.integers(0, 1 << depth, size=(257, 3))
+        bb = np.sort(rng.integers(0, 7, size=257))
+        out[f"grid_d{depth}"], out[f"batch_d{depth}"] = gg, bb
+        for o in BASE_CFG["order"]:
+            out[f"code_d{depth}_{o}"] = R.encode(torch.from_numpy(gg), torch.from_numpy(bb), depth, o).numpy()
+    np.savez_compressed(os.path.join(HERE, "serialization.npz"), **out)
+
+
+def gold_gridsample(R):
+    coord, feat = synth.pig_scan(6000, scale=1.0, seed=3)
+    coord = coord - np.array([0.3, 0.1, 0.0], dtype=np.float32)        # negative coordinates too
+    out = dict(coord=coord, grid_size=np.float64(0.02))
+    real_argsort, real_randint = np.argsort, np.random.randint
+    rec = {}
+
+    def randint(lo, hi, size):
+        r = np.random.default_rng(7).integers(lo, hi, size)
+        rec["rand"] = r
+        return r
+
+    np.argsort = lambda a, *x, **k: real_argsort(a, kind="stable")
+    np.random.randint = randint
+    try:
+        for hash_type in ("fnv", "ravel"):
+            gs = R.GridSample(grid_size=0.02, hash_type=hash_type, mode="train", return_grid_coord=True,
+                              return_inverse=True, return_min_coord=True)
+            dd = dict(coord=coord.copy(), feat=feat.copy(), index_valid_keys=["coord", "feat"])
+            r = gs(dd)
+            out[f"{hash_type}_coord"], out[f"{hash_type}_feat"] = r["coord"], r["feat"]
+            out[f"{hash_type}_grid_coord"], out[f"{hash_type}_inverse"] = r["grid_coord"], r["inverse"]
+            out[f"{hash_type}_min_coord"], out[f"{hash_type}_rand"] = r["min_coord"], rec["rand"]
+            g = np.floor(coord / np.array(0.02)).astype(int)
+            g -= g.min(0)
+            out[f"{hash_type}_key"] = gs.hash(g)
+        gs = R.GridSample(grid_size=0.02, hash_type="fnv", mode="test", return_grid_coord=True)
+        parts = gs(dict(coord=coord.copy(), feat=feat.copy(), index_valid_keys=["coord", "feat"]))
+        out["test_num_parts"] = np.int64(len(parts))
+        for i, p in enumerate(parts):
+            out[f"test_index_{i}"] = p["index"]
+    finally:
+        np.argsort, np.random.randint = real_argsort, real_randint
+    np.savez_compressed(os.path.join(HERE, "gridsample.npz"), **out)
+
+
+def gold_padding(R):
+    out = {}
+    cases = [([5], 4), ([4], 4), ([3], 4), ([9, 12, 20], 4), ([1024], 1024), ([1025], 1024), ([2500, 3200, 5248], 1024),
+             ([100, 2148], 1024), ([7, 16, 17, 48], 8)]
+    for i, (off, K) in enumerate(cases):
+        att = R.SerializedAttention(channels=16, num_heads=1, patch_size=K, enable_flash=False)
+        att.patch_size = K
+        pt = R.Point(offset=torch.tensor(off, dtype=torch.int64), coord=torch.zeros(off[-1], 3))
+        pad, unpad, cu = att.get_padding_and_inverse(pt)
+        out[f"offset_{i}"], out[f"K_{i}"] = np.asarray(off), np.int64(K)
+        out[f"pad_{i}"], out[f"unpad_{i}"], out[f"cu_{i}"] = pad.numpy(), unpad.numpy(), cu.numpy()
+    out["n_cases"] = np.int64(len(cases))
+    np.savez_compressed(os.path.join(HERE, "padding.npz"), **out)
+
+
+def gold_attention(R):
+    torch.manual_seed(5)
+    n, C, H, K = 2300, 32, 2, 1024
+    att = R.SerializedAttention(channels=C, num_heads=H, patch_size=K, enable_flash=False,
+                                upcast_attention=False, upcast_softmax=False, order_index=0).eval()
+    feat = torch.randn(n, C)
+    order = torch.randperm(n)[None]
+    inverse = torch.zeros_like(order).scatter_(1, order, torch.arange(n)[None])
+    pt = R.Point(feat=feat.clone(), offset=torch.tensor([n]), serialized_order=order, serialized_inverse=inverse)
+    with torch.no_grad():
+        qkv = att.qkv(feat)
+        out = att(pt).feat
+    np.savez_compressed(os.path.join(HERE, "attention.npz"), qkv=qkv.numpy(), order=order[0].numpy(),
+                        inverse=inverse[0].numpy(), offset=np.array([n]), H=np.int64(H), K=np.int64(K),
+                        proj_w=att.proj.weight.detach().numpy(), proj_b=att.proj.bias.detach().numpy(), out=out.numpy())
+
+
+def gold_forward(R):
+    from oracle import gridsample as G
+    m = R.OffsetKeypointPTv3(backbone_conf=dict(type="PT-v3m1", enable_flash=False, upcast_attention=False,
+                                                upcast_softmax=False, **BASE_CFG)).eval()
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    m.load_state_dict(W, strict=False)
+    import json
+    with open(os.path.join(HERE, "param_shapes.json"), "w") as fh:       # reference state_dict names/shapes
+        json.dump({k: list(v) for k, v in shapes.items() if not k.endswith("num_batches_tracked")}, fh, indent=0)
+    feats = {}
+
+    def hook(name):
+        def h(mod, inp, o):
+            feats[name] = o.feat.detach().clone()
+        return h
+
+    bb = m.backbone
+    bb.embedding.register_forward_hook(hook("stem"))
+    bb.enc.enc0.register_forward_hook(hook("enc0"))
+    bb.enc.enc1.down.register_forward_hook(hook("pool1"))
+    bb.enc.enc4.register_forward_hook(hook("enc4"))
+    bb.dec.dec3.register_forward_hook(hook("dec3"))
+    out = {}
+    scenes = [(5000, 0.62, 11), (1500, 0.3, 12)]
+    for i, (R_, scale, seed) in enumerate(scenes):
+        coord, feat = synth.pig_scan(R_, scale=scale, seed=seed)
+        gs = G.grid_sample(coord, 0.02)
+        iu = gs["idx_unique"]
+        c, f, g = coord[iu], feat[iu], gs["grid_coord"][iu]
+        torch.manual_seed(100 + i)
+        perms = np.stack([torch.randperm(4).numpy() for _ in range(5)])
+        torch.manual_seed(100 + i)
+        with torch.no_grad():
+            r = m(dict(coord=torch.from_numpy(c), grid_coord=torch.from_numpy(g), feat=torch.from_numpy(f),
+                       offset=torch.tensor([len(iu)]), grid_size=0.02))
+        out[f"coord_{i}"], out[f"feat_{i}"], out[f"grid_coord_{i}"], out[f"perms_{i}"] = c, f, g, perms
+        out[f"pred_{i}"] = r["pred"].numpy()
+        for k in ("stem", "enc0", "pool1", "enc4", "dec3"):
+            out[f"{k}_{i}"] = feats[k].numpy()
+        print("scene", i, "N0", len(iu))
+    out["n_scenes"] = np.int64(len(scenes))
+    np.savez_compressed(os.path.join(HERE, "forward.npz"), **out)
+
+
+if __name__ == "__main__":
+    R = ref_loader.load()
+    gold_serialization(R)
+    gold_gridsample(R)
+    gold_padding(R)
+    gold_attention(R)
+    gold_forward(R)
+    for f in sorted(os.listdir(HERE)):
+        if f.endswith(".npz"):
+            print(f, os.path.getsize(os.path.join(HERE, f)))

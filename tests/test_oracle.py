@@ -1,0 +1,158 @@
+"""CPU: the oracle against the frozen outputs of the reference (tests/golden)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import gridsample as G
+from oracle import ops as O
+from oracle import ptv3 as P
+from oracle import serialization as S
+from ptv3_b200 import synth
+
+
+def test_encode_kat_and_all_depths(golden):
+    g = golden("serialization")
+    for o in S.ORDERS:
+        assert np.array_equal(S.encode(g["kat_grid"], g["kat_batch"], 10, o), g[f"kat_{o}"])
+    # SURVEY.md 8c known answers
+    assert S.encode(g["kat_grid"], g["kat_batch"], 10, "hilbert").tolist() == \
+        [0, 7, 3, 1, 36, 1073743272, 1174405120, 3094547079]
+    for depth in range(1, 17):
+        for o in S.ORDERS:
+            got = S.encode(g[f"grid_d{depth}"], g[f"batch_d{depth}"], depth, o)
+            assert np.array_equal(got, g[f"code_d{depth}_{o}"]), (depth, o)
+
+
+def test_code_prefix_property():
+    """code >> 3 partitions points exactly as (batch, grid >> 1): pooling relies on it."""
+    rng = np.random.default_rng(0)
+    g = rng.integers(0, 256, size=(20000, 3))
+    b = rng.integers(0, 3, size=20000)
+    ref = (b.astype(np.int64) << 40) | ((g[:, 0] >> 1) << 20) | ((g[:, 1] >> 1) << 10) | (g[:, 2] >> 1)
+    for o in S.ORDERS:
+        c = S.encode(g, b, 8, o) >> 3
+        _, inv_c = np.unique(c, return_inverse=True)
+        _, inv_r = np.unique(ref, return_inverse=True)
+        # same partition <=> bijection between labels
+        pairs = np.unique(np.stack([inv_c, inv_r]), axis=1)
+        assert pairs.shape[1] == inv_c.max() + 1 == inv_r.max() + 1
+
+
+def test_hash_kat():
+    a = np.array([[0, 0, 0], [1, 2, 3], [100, 50, 25]])
+    assert [hex(x) for x in G.fnv_hash_vec(a)] == ["0xd94d12186c0f2fb7", "0xd949aa186c0c492b", "0xd8d2ec186ba792f0"]
+    assert G.ravel_hash_vec(a).tolist() == [0, 1381, 133925]
+
+
+@pytest.mark.parametrize("hash_type", ["fnv", "ravel"])
+def test_gridsample_vs_reference(golden, hash_type):
+    g = golden("gridsample")
+    r = G.grid_sample(g["coord"], float(g["grid_size"]), hash_type, rand=g[f"{hash_type}_rand"])
+    assert np.array_equal(r["key"], g[f"{hash_type}_key"])
+    iu = r["idx_unique"]
+    assert np.array_equal(r["grid_coord"][iu], g[f"{hash_type}_grid_coord"])
+    assert np.array_equal(g["coord"][iu], g[f"{hash_type}_coord"])
+    assert np.array_equal(r["inverse"], g[f"{hash_type}_inverse"])
+    assert np.allclose(r["min_grid"] * float(g["grid_size"]), g[f"{hash_type}_min_coord"].ravel())
+
+
+def test_gridsample_test_mode(golden):
+    g = golden("gridsample")
+    r = G.grid_sample(g["coord"], float(g["grid_size"]), "fnv")
+    parts = G.grid_sample_test_parts(r["count"], r["idx_sort"])
+    assert len(parts) == int(g["test_num_parts"])
+    for i, p in enumerate(parts):
+        assert np.array_equal(p, g[f"test_index_{i}"])
+    covered = np.zeros(len(g["coord"]), bool)
+    for p in parts:
+        covered[p] = True
+    assert covered.all()
+
+
+def test_padding_vs_reference(golden):
+    g = golden("padding")
+    for i in range(int(g["n_cases"])):
+        pad, unpad, cu = O.padding_and_inverse(g[f"offset_{i}"], int(g[f"K_{i}"]))
+        assert np.array_equal(pad, g[f"pad_{i}"]), i
+        assert np.array_equal(unpad, g[f"unpad_{i}"]), i
+        assert np.array_equal(cu, g[f"cu_{i}"]), i
+
+
+def test_windows_equal_padding_semantics(golden):
+    """The (q,k) window records describe the same key sets as the padded layout."""
+    g = golden("padding")
+    for i in range(int(g["n_cases"])):
+        off, K = g[f"offset_{i}"], int(g[f"K_{i}"])
+        pad, unpad, cu = O.padding_and_inverse(off, K)
+        win = O.windows_from_offset(off, K)
+        seen = np.zeros(off[-1], int)
+        for q0, ql, k0, kl in win:
+            # padded slot of the first query of this window
+            slot = unpad[q0]
+            w = np.searchsorted(cu, slot, side="right") - 1
+            keys = np.sort(pad[cu[w]:cu[w + 1]])
+            assert np.array_equal(keys, np.arange(k0, k0 + kl)), (i, q0)
+            seen[q0:q0 + ql] += 1
+        assert (seen == 1).all()
+
+
+def test_attention_vs_reference(golden):
+    g = golden("attention")
+    out = O.window_attention(torch.from_numpy(g["qkv"]), torch.from_numpy(g["order"]), torch.from_numpy(g["inverse"]),
+                             g["offset"], int(g["H"]), int(g["K"]))
+    out = out @ torch.from_numpy(g["proj_w"]).t() + torch.from_numpy(g["proj_b"])
+    ref = torch.from_numpy(g["out"])
+    assert ((out - ref).norm() / ref.norm()).item() < 1e-5
+
+
+def test_subm_conv_vs_dense_conv3d():
+    """Pins the restated spconv semantics on torch's dense cross-correlation."""
+    torch.manual_seed(0)
+    for k in (3, 5):
+        B, S_, Cin, Cout = 2, 9, 5, 7
+        occ = torch.rand(B, S_, S_, S_) < 0.3
+        idx = torch.nonzero(occ).to(torch.int32)
+        feat = torch.randn(idx.shape[0], Cin)
+        w = torch.randn(Cout, k, k, k, Cin)
+        bias = torch.randn(Cout)
+        dense = torch.zeros(B, Cin, S_, S_, S_)
+        dense[idx[:, 0].long(), :, idx[:, 1].long(), idx[:, 2].long(), idx[:, 3].long()] = feat
+        ref = torch.nn.functional.conv3d(dense, w.permute(0, 4, 1, 2, 3), bias, padding=k // 2)
+        ref = ref[idx[:, 0].long(), :, idx[:, 1].long(), idx[:, 2].long(), idx[:, 3].long()]
+        got = O.subm_conv(feat, O.subm_neighbor_table(idx, k), w, bias)
+        assert torch.allclose(got, ref, atol=1e-4, rtol=1e-4)
+
+
+def test_segment_csr_and_scatter_mean():
+    torch.manual_seed(0)
+    src = torch.randn(10, 3)
+    ptr = torch.tensor([0, 3, 3, 4, 10])
+    mx = O.segment_csr(src, ptr, "max")
+    assert torch.equal(mx[0], src[0:3].max(0).values) and torch.equal(mx[1], torch.zeros(3))
+    assert torch.allclose(O.segment_csr(src, ptr, "mean")[3], src[4:10].mean(0))
+    idx = torch.tensor([0, 0, 2, 2, 2, 1, 0, 1, 1, 2])
+    sm = O.scatter_mean(src, idx)
+    assert torch.allclose(sm[2], src[idx == 2].mean(0))
+
+
+def _weights():
+    import json, os
+    from conftest import GOLDEN
+    with open(os.path.join(GOLDEN, "param_shapes.json")) as f:
+        shapes = json.load(f)
+    return {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+
+
+def test_forward_vs_reference(golden):
+    g = golden("forward")
+    W = _weights()
+    for i in range(int(g["n_scenes"])):
+        tr = {}
+        pt = P.backbone_forward(W, g[f"coord_{i}"], g[f"grid_coord_{i}"], g[f"feat_{i}"], [len(g[f"coord_{i}"])],
+                                perms=list(g[f"perms_{i}"]), trace=tr)
+        for k in ("stem", "enc0", "pool1", "enc4", "dec3"):
+            ref = torch.from_numpy(g[f"{k}_{i}"])
+            assert ((tr[k] - ref).norm() / ref.norm()).item() < 1e-5, (i, k)
+        pred = P.offset_head(W, pt.feat)
+        ref = torch.from_numpy(g[f"pred_{i}"])
+        assert ((pred - ref).norm() / ref.norm()).item() < 1e-5
