@@ -1,0 +1,200 @@
+/*
+ * ptv3_b200.h -- flat C ABI of libptv3_b200.so: the PTv3 backbone hot path as
+ * hand-written sm_100a CUDA.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in `_host`;
+ *   - the library never allocates or frees device memory, never synchronises
+ *     the device and never touches a stream other than the one passed in
+ *     (`stream` is a cudaStream_t passed as void*; 0 = legacy default stream);
+ *   - scratch memory comes from the caller: `ptv3_<op>_workspace()` returns the
+ *     bytes `ptv3_<op>()` needs for the same sizes (256-byte aligned pointer);
+ *   - return value: 0 on success, a negative PTV3_E* code otherwise
+ *     (`ptv3_error_string`).  The Python host raises RuntimeError on != 0,
+ *     mirroring the reference's assert/exception convention
+ *     (pointcept/models/utils/structure.py:59,76,81);
+ *   - integer index arrays use int64 where the reference's tensors are int64
+ *     (serialized_code/order/inverse, cluster, idx_ptr), int32 for the spconv
+ *     style indices / neighbour tables (spconv uses int32 indices).
+ * All reference citations are relative to /root/reference.
+ */
+#ifndef PTV3_B200_H
+#define PTV3_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTV3_OK 0
+#define PTV3_EINVAL (-1)     /* bad argument / unsupported shape */
+#define PTV3_EWORKSPACE (-2) /* workspace too small */
+#define PTV3_ELAUNCH (-3)    /* cudaGetLastError() != cudaSuccess after a launch */
+#define PTV3_EUNSUPPORTED (-4)
+
+/* element types of floating point feature buffers */
+#define PTV3_F32 0
+#define PTV3_BF16 1
+
+/* serialization orders, pointcept/models/utils/serialization/default.py:9-24 */
+#define PTV3_ORDER_Z 0
+#define PTV3_ORDER_Z_TRANS 1
+#define PTV3_ORDER_HILBERT 2
+#define PTV3_ORDER_HILBERT_TRANS 3
+
+int ptv3_abi_version(void);
+const char* ptv3_error_string(int code);
+/* number of kernels this library has launched since load (host counter; bench.py's gpu_launches) */
+int64_t ptv3_launch_count(void);
+
+/* ---------------------------------------------------------------------------
+ * A2  space-filling-curve codes.
+ * Replaces pointcept/models/utils/serialization/default.py:9-24 (encode),
+ * z_order.py:66-101 (xyz2key) and hilbert.py:91-198 (encode).
+ * grid_coord: (n,3) int32 or int64 (grid_is_i64); batch: (n) int64 or NULL.
+ * code[r*n + i] = (batch[i] << 3*depth) | curve(order_ids_host[r])(grid[i] & (2^depth-1)).
+ * 1 <= depth <= 16, 1 <= n_orders <= 8.
+ * ------------------------------------------------------------------------- */
+int ptv3_encode(const void* grid_coord, int grid_is_i64, const int64_t* batch, int64_t n, int depth,
+                const int* order_ids_host, int n_orders, int64_t* code, void* stream);
+
+/* per-axis max of an (n,3) grid (int64 x 3, device) -- feeds depth = bit_length(max+1),
+ * structure.py:73, and sparse_shape = max + 96, structure.py:131-134 */
+int ptv3_grid_max(const void* grid_coord, int grid_is_i64, int64_t n, int64_t* out_max3, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A2  row-wise argsort of (rows,n) int64 codes + inverse permutation.
+ * Replaces torch.argsort + scatter_ at structure.py:92-99.  LSD radix sort over
+ * the low `key_bits` bits only (codes must be >= 0 and < 2^key_bits), stable,
+ * so order is defined for duplicate codes as well (ascending index).
+ * order[r][j] = index of the j-th smallest code of row r; inverse[r][order[r][j]] = j.
+ * ------------------------------------------------------------------------- */
+size_t ptv3_argsort_rows_workspace(int64_t rows, int64_t n);
+int ptv3_argsort_rows(const int64_t* code, int64_t rows, int64_t n, int key_bits, int64_t* order,
+                      int64_t* inverse /* may be NULL */, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A0  GridSample voxel hashing / unique / representative selection.
+ * Replaces pointcept/datasets/transform.py:848-927 (+ fnv_hash_vec :949-963,
+ * ravel_hash_vec :930-946).  Contract: within a voxel points are
+ * ordered by ascending original index (stable sort); the per-voxel random draw
+ * is the input array `rand` (NULL = first point of every voxel).
+ *   coord      (r,3) float32
+ *   grid_coord (r,3) int64   floor(coord/grid_size) - min   (all points)
+ *   key        (r)   uint64  hash of grid_coord (hash_type 0 = fnv, 1 = ravel)
+ *   idx_sort   (r)   int64   stable argsort of key
+ *   inverse    (r)   int64   voxel id of every point (ids in ascending-key order)
+ *   count      (r)   int64   first *n_voxels entries valid: points per voxel
+ *   idx_unique (r)   int64   first *n_voxels entries valid: selected point per voxel
+ *   min_grid   (3)   int64   the subtracted minimum
+ *   n_voxels   (1)   int64
+ * ------------------------------------------------------------------------- */
+size_t ptv3_gridsample_workspace(int64_t r);
+int ptv3_gridsample(const float* coord, int64_t r, double grid_size, int hash_type, const int64_t* rand /* NULL ok */,
+                    int64_t* grid_coord, uint64_t* key, int64_t* idx_sort, int64_t* inverse, int64_t* count,
+                    int64_t* idx_unique, int64_t* min_grid, int64_t* n_voxels, void* workspace,
+                    size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A6  SerializedPooling integer front end.
+ * Replaces point_transformer_v3m1_base.py:385-412: code >> 3*pool_depth,
+ * torch.unique(code[0]) -> cluster/counts, torch.sort(cluster) -> indices,
+ * idx_ptr, head_indices, and the argsort of the pooled codes.  No sort is
+ * needed: the parent rows are already sorted by every order (prefix property,
+ * tests/test_oracle.py::test_code_prefix_property).
+ *   code, order (rows,n) int64 of the parent;   shift = 3*pool_depth
+ *   cluster (n)      pooled id of every parent point  (= torch.unique inverse)
+ *   indices (n)      parent points grouped by cluster (= order[0])
+ *   idx_ptr (n+1)    first *n_pooled+1 entries valid (CSR over `indices`)
+ *   head    (n)      first *n_pooled valid: indices[idx_ptr[k]]
+ *   new_code/new_order/new_inverse (rows, n) with row stride n; first *n_pooled
+ *                    entries of each row valid
+ *   n_pooled (1) int64
+ * ------------------------------------------------------------------------- */
+size_t ptv3_pool_front_workspace(int64_t rows, int64_t n);
+int ptv3_pool_front(const int64_t* code, const int64_t* order, int64_t rows, int64_t n, int shift, int64_t* cluster,
+                    int64_t* indices, int64_t* idx_ptr, int64_t* head, int64_t* new_code, int64_t* new_order,
+                    int64_t* new_inverse, int64_t* n_pooled, void* workspace, size_t workspace_bytes, void* stream);
+
+/* gather of the per-point integer attributes of the pooled point set (:426-433):
+ * new_grid[k] = grid[head[k]] >> pool_depth ; new_batch[k] = batch[head[k]];
+ * spconv indices (m,4) int32 = [batch, x, y, z] (structure.py:137-141). */
+int ptv3_pool_gather_ints(const int64_t* grid /* (n,3) */, const int64_t* batch, const int64_t* head, int64_t m,
+                          int pool_depth, int64_t* new_grid, int64_t* new_batch, int32_t* new_indices, void* stream);
+
+/* offset (cumulative scene sizes, int64 (n_scenes)) from a sorted batch vector */
+int ptv3_batch_to_offset(const int64_t* batch, int64_t n, int64_t n_scenes, int64_t* offset, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * torch_scatter.segment_csr / scatter_mean (call sites
+ * point_transformer_v3m1_base.py:416-421, keypoint_ptv3.py:44).
+ * out[k] = reduce_{j in [indptr[k], indptr[k+1])} src[gather ? gather[j] : j]
+ * reduce: 0 sum, 1 mean, 2 max, 3 min; empty segments give 0.
+ * src (n_src, c), out (m, c), dtype PTV3_F32 or PTV3_BF16 (fp32 accumulate).
+ * ------------------------------------------------------------------------- */
+int ptv3_segment_csr(const void* src, int dtype, const int64_t* gather /* NULL ok */, const int64_t* indptr, int64_t m,
+                     int64_t c, int reduce, void* out, void* stream);
+
+/* A7  SerializedUnpooling gather-add (:471-482) with the two GELUs fused:
+ * skip_act[i] = act(skip[i]); out[i] = skip_act[i] + act(up[inverse[i]]); act = GELU(erf) if gelu else identity.
+ * skip (n,c), up (m,c), skip_act (n,c) or NULL in `dtype`; out (n,c) is always fp32 (the residual stream). */
+int ptv3_unpool_add(const void* skip, const void* up, int dtype, const int64_t* inverse, int64_t n, int64_t c, int gelu,
+                    void* out, void* skip_act, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A5  submanifold convolution (spconv 2.3.6 SubMConv3d semantics restated,
+ * call sites point_transformer_v3m1_base.py:278-284,499-506).
+ * Neighbour map: indices (n,4) int32 [b,x,y,z]; nbr (n, ksize^3) int32, -1 =
+ * no active site at grid+delta; kernel offset index ((dx+r)*k+(dy+r))*k+(dz+r).
+ * The map is what the spconv indice_key cache holds (structure.py:137-146).
+ * ------------------------------------------------------------------------- */
+size_t ptv3_subm_map_workspace(int64_t n);
+int ptv3_subm_build_map(const int32_t* indices, int64_t n, int ksize, int32_t* nbr, void* workspace,
+                        size_t workspace_bytes, void* stream);
+
+/* out[i,:] = bias + sum_k W[k] in[nbr[i,k],:]
+ * weight layout (k^3, c_out, c_in) (= spconv's (out,kD,kH,kW,in) permuted once on the host side),
+ * dtype of in/weight/out given by `dtype`; bias fp32 or NULL; accumulation fp32.
+ * algo: 0 = auto, 1 = CUDA-core reference kernel, 2 = tcgen05 implicit GEMM (bf16 only). */
+size_t ptv3_subm_conv_workspace(int64_t n, int c_in, int c_out, int k3, int dtype, int algo);
+int ptv3_subm_conv(const void* in, const void* weight, const float* bias, const int32_t* nbr, int64_t n, int c_in,
+                   int c_out, int k3, int dtype, int algo, void* out, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A3/A4  serialized window attention.
+ * Window records replace get_padding_and_inverse (:115-170): int64 (w,4) =
+ * (q_start, q_len, k_start, k_len) in serialized-row space; the ragged last
+ * window of a scene with n > K attends to the last K rows of the scene.
+ * n_windows_max = sum_b max(1, ceil(n_b / K)) is what the caller allocates.
+ * ------------------------------------------------------------------------- */
+int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, int64_t* windows,
+                       int64_t n_windows_max, int64_t* n_windows, void* stream);
+
+/* out[row(p), h, :] = softmax_j(scale * q[row(p),h,:] . k[row(j),h,:]) v[row(j),h,:]
+ * for p in the window's queries, j in the window's keys, row(p) = order ? order[p] : p.
+ * qkv (n,3,h,d) packed rows (= Linear(C,3C) output, :184-190 / flash layout :208-215);
+ * out (n,h,d) in storage order (the reference's feat[inverse], :216-218). d == 16.
+ * algo: 0 auto, 1 CUDA-core fp32-math kernel, 2 tensor-core kernel (bf16 only). */
+int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order /* NULL = identity */, const int64_t* windows,
+                         const int64_t* n_windows /* device scalar */, int64_t n_windows_max,
+                         int64_t max_len /* upper bound of q_len and k_len */, int64_t n, int h, int d, float scale,
+                         int algo, void* out, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * Dense glue kernels of Block.forward (:318-338): fused residual + LayerNorm.
+ *   t = gamma ? LayerNorm(x; gamma, beta, eps) : x          (fp32 math)
+ *   r = residual ? residual + t : t ;  res_out = r  (fp32, optional)
+ *   out2 = gamma2 ? LayerNorm(r; gamma2, beta2, eps) : r    (dtype_out2, optional: pre-norm /
+ *          bf16 copy for the next GEMM).  x: dtype_x; residual, res_out: fp32.
+ * ------------------------------------------------------------------------- */
+int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float* beta, float eps,
+                     const float* residual, float* res_out, const float* gamma2, const float* beta2, void* out2,
+                     int dtype_out2, int64_t n, int c, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PTV3_B200_H */

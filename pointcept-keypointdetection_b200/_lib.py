@@ -1,0 +1,74 @@
+"""ctypes binding of libptv3_b200.so (the flat C ABI declared in include/ptv3_b200.h).
+
+There is no CPU fallback: if the shared library is missing or a call returns a
+non-zero code a RuntimeError is raised (the reference's convention is Python
+asserts/exceptions, pointcept/models/utils/structure.py:59,76,81).
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libptv3_b200.so")
+
+c_i64, c_int, c_vp, c_sz = ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
+c_f32, c_f64 = ctypes.c_float, ctypes.c_double
+
+# name -> (restype, argtypes); order mirrors include/ptv3_b200.h
+SIGNATURES = {
+    "ptv3_abi_version": (c_int, []),
+    "ptv3_error_string": (ctypes.c_char_p, [c_int]),
+    "ptv3_launch_count": (c_i64, []),
+    "ptv3_encode": (c_int, [c_vp, c_int, c_vp, c_i64, c_int, ctypes.POINTER(c_int), c_int, c_vp, c_vp]),
+    "ptv3_grid_max": (c_int, [c_vp, c_int, c_i64, c_vp, c_vp]),
+    "ptv3_argsort_rows_workspace": (c_sz, [c_i64, c_i64]),
+    "ptv3_argsort_rows": (c_int, [c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "ptv3_gridsample_workspace": (c_sz, [c_i64]),
+    "ptv3_gridsample": (c_int, [c_vp, c_i64, c_f64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                c_vp, c_sz, c_vp]),
+    "ptv3_pool_front_workspace": (c_sz, [c_i64, c_i64]),
+    "ptv3_pool_front": (c_int, [c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                c_vp, c_sz, c_vp]),
+    "ptv3_pool_gather_ints": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "ptv3_batch_to_offset": (c_int, [c_vp, c_i64, c_i64, c_vp, c_vp]),
+    "ptv3_segment_csr": (c_int, [c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp]),
+    "ptv3_unpool_add": (c_int, [c_vp, c_vp, c_int, c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp]),
+    "ptv3_subm_map_workspace": (c_sz, [c_i64]),
+    "ptv3_subm_build_map": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, c_sz, c_vp]),
+    "ptv3_subm_conv_workspace": (c_sz, [c_i64, c_int, c_int, c_int, c_int, c_int]),
+    "ptv3_subm_conv": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_sz,
+                               c_vp]),
+    "ptv3_build_windows": (c_int, [c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp]),
+    "ptv3_attn_window_fwd": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_f32, c_int,
+                                     c_vp, c_vp]),
+    "ptv3_ln_residual": (c_int, [c_vp, c_int, c_vp, c_vp, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_i64, c_int,
+                                 c_vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load (once) and return the ctypes handle.  Raises RuntimeError if the library has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc -gencode arch=compute_100a,code=sm_100a).  ptv3_b200 has no CPU or PyTorch fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError here = header / library mismatch
+        fn.restype, fn.argtypes = res, args
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().ptv3_error_string(int(rc)).decode()
+        raise RuntimeError(f"{what} failed: {msg} (code {rc})")
+
+
+def launch_count():
+    return int(load().ptv3_launch_count())

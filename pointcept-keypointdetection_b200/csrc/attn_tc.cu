@@ -1,0 +1,216 @@
+// A4: serialized window attention, bf16 tensor-core kernel (head_dim 16).
+//
+// One CTA per (window, head): the window's K and V rows (<= 1024 x 16 bf16 each)
+// are gathered ONCE into shared memory through the serialized order, then every
+// warp walks 16-query tiles over 64-key chunks: S = Q K^T on the tensor cores,
+// online softmax in registers (exp2 with the scale folded into one FFMA), P is
+// re-used from the S accumulator registers as the A operand of P V, and the row
+// sum comes from an extra MMA against a ones tile so it is the sum of exactly
+// the bf16 P that multiplies V.  The [order] gather and the [inverse] scatter of
+// the reference (point_transformer_v3m1_base.py:184-190, :216-218) are fused:
+// rows are read from / written to storage order directly.
+//
+// head_dim 16 makes this kernel exp/issue bound, not tensor bound (SURVEY.md
+// section 7): 64 tensor FLOPs per exp.
+#include "common.cuh"
+
+namespace ptv3 {
+
+constexpr int kD = 16;
+constexpr int kWarps = 8;
+constexpr int kThreads = kWarps * 32;
+constexpr int kChunk = 64;  // keys per softmax step
+
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+__device__ __forceinline__ void mma_bf16_16816(float c[4], const uint32_t a[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t r[4], uint32_t smem_addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_addr));
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t r[4], uint32_t smem_addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(smem_addr));
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr));
+}
+
+// smem: K [kpad][16] bf16 then V [kpad][16] bf16, kpad = keys rounded up to 64
+__global__ void __launch_bounds__(kThreads, 2) attn_window_mma_kernel(
+    const __nv_bfloat16* __restrict__ qkv, const int64_t* __restrict__ order, const int64_t* __restrict__ windows,
+    const int64_t* __restrict__ n_windows, int h, float scale_log2, int kpad_max, __nv_bfloat16* __restrict__ out) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int w = blockIdx.x, head = blockIdx.y;
+  if (w >= n_windows[0]) return;
+  const int64_t q0 = windows[4 * w + 0], ql = windows[4 * w + 1], k0 = windows[4 * w + 2], kl = windows[4 * w + 3];
+  if (ql <= 0 || kl <= 0) return;
+  const int kpad = (int)((kl + kChunk - 1) / kChunk) * kChunk;
+  if (kpad > kpad_max) return;  // caller guarantees max_len; never taken
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+  __nv_bfloat16* Vs = Ks + (size_t)kpad * kD;
+  const uint32_t ks_addr = (uint32_t)__cvta_generic_to_shared(Ks);
+  const uint32_t vs_addr = (uint32_t)__cvta_generic_to_shared(Vs);
+  const int64_t rs = (int64_t)3 * h * kD;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  // ---- gather K and V rows of this (window, head): 4 x 16 B per key ----
+  for (int idx = tid; idx < kpad * 4; idx += kThreads) {
+    int key = idx >> 2, part = idx & 3;
+    uint32_t dst = (part < 2 ? ks_addr : vs_addr) + (uint32_t)(key * 32 + (part & 1) * 16);
+    if (key < kl) {
+      int64_t row = order ? order[k0 + key] : k0 + key;
+      const __nv_bfloat16* src = qkv + row * rs + (int64_t)(part < 2 ? 1 : 2) * h * kD + head * kD + (part & 1) * 8;
+      cp_async16(dst, src);
+    } else {
+      asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(dst), "r"(0u));
+    }
+  }
+  asm volatile("cp.async.commit_group;");
+  asm volatile("cp.async.wait_group 0;");
+  __syncthreads();
+
+  const int g = lane >> 2, t = lane & 3;
+  const int n_qtiles = (int)((ql + 15) >> 4);
+  const int n_chunks = kpad / kChunk;
+  // ldmatrix lane addressing: lane supplies the row address of matrix (lane>>3), row (lane&7)
+  //  K (non-trans): matrices {keys 0-7 dims 0-7, keys 0-7 dims 8-15, keys 8-15 dims 0-7, keys 8-15 dims 8-15}
+  const uint32_t k_lane_off = (uint32_t)((((lane >> 4) << 3) + (lane & 7)) * 32 + ((lane >> 3) & 1) * 16);
+  //  V (trans): matrices {keys 0-7 dims 0-7, keys 8-15 dims 0-7, keys 0-7 dims 8-15, keys 8-15 dims 8-15}
+  const uint32_t v_lane_off = (uint32_t)(((((lane >> 3) & 1) << 3) + (lane & 7)) * 32 + (lane >> 4) * 16);
+  const uint32_t ones = 0x3f803f80u;  // bf16 (1.0, 1.0)
+
+  for (int qt = warp; qt < n_qtiles; qt += kWarps) {
+    // ---- Q fragment (A operand, 16 x 16) straight from global ----
+    const int64_t qi0 = (int64_t)qt * 16 + g, qi1 = qi0 + 8;
+    const bool v0 = qi0 < ql, v1 = qi1 < ql;
+    int64_t row0 = 0, row1 = 0;
+    uint32_t qa[4] = {0u, 0u, 0u, 0u};
+    if (v0) {
+      row0 = order ? order[q0 + qi0] : q0 + qi0;
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(qkv + row0 * rs + head * kD);
+      qa[0] = p[t];
+      qa[2] = p[t + 4];
+    }
+    if (v1) {
+      row1 = order ? order[q0 + qi1] : q0 + qi1;
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(qkv + row1 * rs + head * kD);
+      qa[1] = p[t];
+      qa[3] = p[t + 4];
+    }
+    float o[2][4], l[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) o[0][i] = o[1][i] = l[i] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY;  // running maxima (raw score units) of rows g and g+8
+
+    for (int c = 0; c < n_chunks; ++c) {
+      float s[8][4];
+#pragma unroll
+      for (int b = 0; b < 8; ++b) s[b][0] = s[b][1] = s[b][2] = s[b][3] = 0.f;
+      const uint32_t kc = ks_addr + (uint32_t)(c * kChunk * 32);
+#pragma unroll
+      for (int b2 = 0; b2 < 4; ++b2) {
+        uint32_t kb[4];
+        ldmatrix_x4(kb, kc + (uint32_t)(b2 * 16 * 32) + k_lane_off);
+        mma_bf16_16816(s[2 * b2], qa, kb[0], kb[1]);
+        mma_bf16_16816(s[2 * b2 + 1], qa, kb[2], kb[3]);
+      }
+      if (c == n_chunks - 1 && kl < kpad) {
+        const int base = c * kChunk + 2 * t;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          int key = base + b * 8;
+          if (key >= kl) s[b][0] = s[b][2] = -INFINITY;
+          if (key + 1 >= kl) s[b][1] = s[b][3] = -INFINITY;
+        }
+      }
+      float mx0 = m0, mx1 = m1;
+#pragma unroll
+      for (int b = 0; b < 8; ++b) {
+        mx0 = fmaxf(mx0, fmaxf(s[b][0], s[b][1]));
+        mx1 = fmaxf(mx1, fmaxf(s[b][2], s[b][3]));
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      const float a0 = ex2((m0 - mx0) * scale_log2), a1 = ex2((m1 - mx1) * scale_log2);
+      m0 = mx0;
+      m1 = mx1;
+      const float ms0 = mx0 * scale_log2, ms1 = mx1 * scale_log2;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        o[i][0] *= a0; o[i][1] *= a0; o[i][2] *= a1; o[i][3] *= a1;
+      }
+      l[0] *= a0; l[1] *= a0; l[2] *= a1; l[3] *= a1;
+      const uint32_t vc = vs_addr + (uint32_t)(c * kChunk * 32);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {  // 16 keys per step
+        uint32_t pa[4];
+        pa[0] = pack_bf16(ex2(fmaf(s[2 * j][0], scale_log2, -ms0)), ex2(fmaf(s[2 * j][1], scale_log2, -ms0)));
+        pa[1] = pack_bf16(ex2(fmaf(s[2 * j][2], scale_log2, -ms1)), ex2(fmaf(s[2 * j][3], scale_log2, -ms1)));
+        pa[2] = pack_bf16(ex2(fmaf(s[2 * j + 1][0], scale_log2, -ms0)), ex2(fmaf(s[2 * j + 1][1], scale_log2, -ms0)));
+        pa[3] = pack_bf16(ex2(fmaf(s[2 * j + 1][2], scale_log2, -ms1)), ex2(fmaf(s[2 * j + 1][3], scale_log2, -ms1)));
+        uint32_t vb[4];
+        ldmatrix_x4_trans(vb, vc + (uint32_t)(j * 16 * 32) + v_lane_off);
+        mma_bf16_16816(o[0], pa, vb[0], vb[1]);
+        mma_bf16_16816(o[1], pa, vb[2], vb[3]);
+        mma_bf16_16816(l, pa, ones, ones);
+      }
+    }
+    // ---- epilogue: normalise, write bf16 pairs to storage rows ----
+    if (v0) {
+      float inv = 1.f / l[0];
+      uint32_t* p = reinterpret_cast<uint32_t*>(out + row0 * (int64_t)h * kD + head * kD);
+      p[t] = pack_bf16(o[0][0] * inv, o[0][1] * inv);
+      p[t + 4] = pack_bf16(o[1][0] * inv, o[1][1] * inv);
+    }
+    if (v1) {
+      float inv = 1.f / l[2];
+      uint32_t* p = reinterpret_cast<uint32_t*>(out + row1 * (int64_t)h * kD + head * kD);
+      p[t] = pack_bf16(o[0][2] * inv, o[0][3] * inv);
+      p[t + 4] = pack_bf16(o[1][2] * inv, o[1][3] * inv);
+    }
+  }
+}
+
+int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
+                   int64_t n_windows_max, int64_t max_len, int64_t n, int h, float scale, __nv_bfloat16* out,
+                   cudaStream_t st) {
+  (void)n;
+  int kpad = (int)(cdiv(max_len, kChunk) * kChunk);
+  size_t smem = (size_t)kpad * kD * 2 * 2;
+  if (smem > 200 * 1024) return PTV3_EUNSUPPORTED;  // patch > 3200
+  static size_t configured = 0;
+  if (smem > configured) {
+    if (cudaFuncSetAttribute(attn_window_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+        cudaSuccess)
+      return PTV3_ELAUNCH;
+    configured = smem;
+  }
+  dim3 grid((unsigned)n_windows_max, (unsigned)h);
+  attn_window_mma_kernel<<<grid, kThreads, smem, st>>>(qkv, order, windows, n_windows, h,
+                                                       scale * 1.4426950408889634f, kpad, out);
+  return check_launch();
+}
+
+}  // namespace ptv3

@@ -1,0 +1,284 @@
+// A5: submanifold convolution -- hashed neighbour map + CUDA-core kernels
+// (fp32 parity path, small-C_in stem).  The bf16 tensor-core kernel lives in
+// subm_tc.cu.  Semantics: oracle/ops.py::subm_neighbor_table / subm_conv.
+#include "common.cuh"
+
+namespace ptv3 {
+
+// ------------------------------ neighbour map ----------------------------------
+constexpr uint64_t kEmptyKey = ~0ull;
+constexpr int kCoordBias = 8;  // keeps shifted coordinates non-negative for |delta| <= 8
+
+__device__ __forceinline__ uint64_t pack_site(int b, int x, int y, int z) {
+  // 10 bits batch | 3 x 18 bits coordinates
+  return ((uint64_t)(uint32_t)b << 54) | ((uint64_t)(uint32_t)(x + kCoordBias) << 36) |
+         ((uint64_t)(uint32_t)(y + kCoordBias) << 18) | (uint64_t)(uint32_t)(z + kCoordBias);
+}
+
+__device__ __forceinline__ uint32_t hash_site(uint64_t k) {
+  k ^= k >> 33;
+  k *= 0xff51afd7ed558ccdull;
+  k ^= k >> 33;
+  k *= 0xc4ceb9fe1a85ec53ull;
+  k ^= k >> 33;
+  return (uint32_t)k;
+}
+
+__global__ void __launch_bounds__(256) subm_insert_kernel(const int32_t* __restrict__ indices, int64_t n,
+                                                          unsigned long long* __restrict__ keys,
+                                                          int* __restrict__ vals, uint32_t mask) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int4 s = reinterpret_cast<const int4*>(indices)[i];
+    uint64_t key = pack_site(s.x, s.y, s.z, s.w);
+    uint32_t slot = hash_site(key) & mask;
+    while (true) {
+      unsigned long long prev = atomicCAS(&keys[slot], (unsigned long long)kEmptyKey, (unsigned long long)key);
+      if (prev == kEmptyKey || prev == key) {
+        atomicMin(&vals[slot], (int)i);  // duplicate sites: lowest row wins
+        break;
+      }
+      slot = (slot + 1) & mask;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) subm_lookup_kernel(const int32_t* __restrict__ indices, int64_t n, int ksize,
+                                                          const unsigned long long* __restrict__ keys,
+                                                          const int* __restrict__ vals, uint32_t mask,
+                                                          int32_t* __restrict__ nbr) {
+  const int k3 = ksize * ksize * ksize, r = ksize / 2;
+  const int64_t total = n * k3;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    int64_t i = t / k3;
+    int k = (int)(t - i * k3);
+    int dz = k % ksize - r, dy = (k / ksize) % ksize - r, dx = k / (ksize * ksize) - r;
+    int4 s = reinterpret_cast<const int4*>(indices)[i];
+    int x = s.y + dx, y = s.z + dy, z = s.w + dz;
+    int found = -1;
+    if (x >= -kCoordBias && y >= -kCoordBias && z >= -kCoordBias) {
+      uint64_t key = pack_site(s.x, x, y, z);
+      uint32_t slot = hash_site(key) & mask;
+      while (true) {
+        unsigned long long cur = keys[slot];
+        if (cur == key) {
+          found = vals[slot];
+          break;
+        }
+        if (cur == kEmptyKey) break;
+        slot = (slot + 1) & mask;
+      }
+    }
+    nbr[t] = found;
+  }
+}
+
+static uint32_t table_capacity(int64_t n) {
+  uint64_t cap = 1024;
+  while (cap < (uint64_t)(2 * n)) cap <<= 1;
+  return (uint32_t)cap;
+}
+
+// ------------------------------ tiled CUDA-core conv ---------------------------
+constexpr int BM = 64, BN = 64, BK = 16;
+
+template <typename T>
+__global__ void __launch_bounds__(256) subm_conv_tiled_kernel(const T* __restrict__ in, const T* __restrict__ w,
+                                                              const float* __restrict__ bias,
+                                                              const int32_t* __restrict__ nbr, int64_t n, int cin,
+                                                              int cout, int k3, T* __restrict__ out) {
+  __shared__ float As[BK][BM + 4];
+  __shared__ float Bs[BK][BN + 4];
+  __shared__ int nb[BM];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int64_t row0 = (int64_t)blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k = 0; k < k3; ++k) {
+    int has = 0;
+    if (tid < BM) {
+      int64_t r = row0 + tid;
+      int v = r < n ? nbr[r * k3 + k] : -1;
+      nb[tid] = v;
+      has = v >= 0;
+    }
+    if (!__syncthreads_or(has)) continue;
+    for (int c0 = 0; c0 < cin; c0 += BK) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        int idx = e * 256 + tid;  // 0..1023
+        int m = idx >> 4, kk = idx & 15;
+        int src = nb[m];
+        int ci = c0 + kk;
+        As[kk][m] = (src >= 0 && ci < cin) ? Elem<T>::load(in + (int64_t)src * cin + ci) : 0.f;
+        int co = n0 + m;
+        Bs[kk][m] = (co < cout && ci < cin) ? Elem<T>::load(w + ((int64_t)k * cout + co) * cin + ci) : 0.f;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < BK; ++kk) {
+        float a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int64_t r = row0 + ty * 4 + i;
+    if (r >= n) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int co = n0 + tx * 4 + j;
+      if (co < cout) Elem<T>::store(out + r * cout + co, acc[i][j] + (bias ? bias[co] : 0.f));
+    }
+  }
+}
+
+// ------------------------------ small-C_in "row per warp" conv (stem) -----------
+// lane = output channel (c_out <= 32*CPL), loops only over the occupied offsets.
+template <typename T, int CPL>
+__global__ void __launch_bounds__(256) subm_conv_rowwarp_kernel(const T* __restrict__ in, const T* __restrict__ w,
+                                                                const float* __restrict__ bias,
+                                                                const int32_t* __restrict__ nbr, int64_t n, int cin,
+                                                                int cout, int k3, T* __restrict__ out) {
+  extern __shared__ float ws[];  // [k3][cin][cout]
+  for (int idx = threadIdx.x; idx < k3 * cin * cout; idx += blockDim.x) {
+    int co = idx % cout, ci = (idx / cout) % cin, k = idx / (cout * cin);
+    ws[idx] = Elem<T>::load(w + ((int64_t)k * cout + co) * cin + ci);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (; row < n; row += stride) {
+    float acc[CPL];
+#pragma unroll
+    for (int q = 0; q < CPL; ++q) acc[q] = 0.f;
+    const int32_t* nb = nbr + row * k3;
+    for (int kb = 0; kb < k3; kb += 32) {
+      int mine = (kb + lane < k3) ? nb[kb + lane] : -1;
+      uint32_t present = __ballot_sync(0xffffffffu, mine >= 0);
+      while (present) {
+        int b = __ffs(present) - 1;
+        present &= present - 1;
+        int src = __shfl_sync(0xffffffffu, mine, b);
+        int k = kb + b;
+        for (int ci = 0; ci < cin; ++ci) {
+          float x = Elem<T>::load(in + (int64_t)src * cin + ci);
+#pragma unroll
+          for (int q = 0; q < CPL; ++q) {
+            int co = q * 32 + lane;
+            if (co < cout) acc[q] = fmaf(x, ws[(k * cin + ci) * cout + co], acc[q]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < CPL; ++q) {
+      int co = q * 32 + lane;
+      if (co < cout) Elem<T>::store(out + row * cout + co, acc[q] + (bias ? bias[co] : 0.f));
+    }
+  }
+}
+
+template <typename T>
+static int conv_cuda_core(const T* in, const T* w, const float* bias, const int32_t* nbr, int64_t n, int cin, int cout,
+                          int k3, T* out, cudaStream_t st) {
+  size_t smem = (size_t)k3 * cin * cout * sizeof(float);
+  if (cin <= 8 && cout <= 64 && smem <= 200 * 1024) {
+    int g = (int)cdiv(n, 8);
+    int cap = kNumSMs * 2 * 8;
+    if (g > cap) g = cap;
+    if (cout <= 32) {
+      cudaFuncSetAttribute(subm_conv_rowwarp_kernel<T, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      subm_conv_rowwarp_kernel<T, 1><<<g, 256, smem, st>>>(in, w, bias, nbr, n, cin, cout, k3, out);
+    } else {
+      cudaFuncSetAttribute(subm_conv_rowwarp_kernel<T, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      subm_conv_rowwarp_kernel<T, 2><<<g, 256, smem, st>>>(in, w, bias, nbr, n, cin, cout, k3, out);
+    }
+    return check_launch();
+  }
+  dim3 grid((unsigned)cdiv(n, BM), (unsigned)cdiv(cout, BN));
+  subm_conv_tiled_kernel<T><<<grid, 256, 0, st>>>(in, w, bias, nbr, n, cin, cout, k3, out);
+  return check_launch();
+}
+
+// implemented in subm_tc.cu
+size_t subm_conv_tc_workspace(int64_t n, int c_in, int c_out, int k3);
+int subm_conv_tc(const __nv_bfloat16* in, const __nv_bfloat16* w, const float* bias, const int32_t* nbr, int64_t n,
+                 int c_in, int c_out, int k3, __nv_bfloat16* out, void* ws, size_t ws_bytes, cudaStream_t st);
+bool subm_conv_tc_supported(int c_in, int c_out, int k3);
+
+}  // namespace ptv3
+
+using namespace ptv3;
+
+extern "C" {
+
+size_t ptv3_subm_map_workspace(int64_t n) {
+  uint32_t cap = table_capacity(n > 0 ? n : 1);
+  return align_up((size_t)cap * 8) + align_up((size_t)cap * 4) + 512;
+}
+
+int ptv3_subm_build_map(const int32_t* indices, int64_t n, int ksize, int32_t* nbr, void* workspace,
+                        size_t workspace_bytes, void* stream) {
+  if (n < 0 || ksize < 1 || ksize > 7 || (ksize & 1) == 0) return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!indices || !nbr || n >= (1ll << 30)) return PTV3_EINVAL;
+  uint32_t cap = table_capacity(n);
+  Workspace ws(workspace, workspace_bytes);
+  unsigned long long* keys = ws.take<unsigned long long>(cap);
+  int* vals = ws.take<int>(cap);
+  if (!ws.ok()) return PTV3_EWORKSPACE;
+  cudaStream_t st = as_stream(stream);
+  cudaMemsetAsync(keys, 0xff, (size_t)cap * 8, st);
+  cudaMemsetAsync(vals, 0x7f, (size_t)cap * 4, st);
+  subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1);
+  int64_t total = n * ksize * ksize * ksize;
+  subm_lookup_kernel<<<grid_for(total, 256, 16), 256, 0, st>>>(indices, n, ksize, keys, vals, cap - 1, nbr);
+  return check_launch(2);
+}
+
+size_t ptv3_subm_conv_workspace(int64_t n, int c_in, int c_out, int k3, int dtype, int algo) {
+  if (dtype == PTV3_BF16 && algo != 1 && subm_conv_tc_supported(c_in, c_out, k3))
+    return subm_conv_tc_workspace(n, c_in, c_out, k3);
+  return 0;
+}
+
+int ptv3_subm_conv(const void* in, const void* weight, const float* bias, const int32_t* nbr, int64_t n, int c_in,
+                   int c_out, int k3, int dtype, int algo, void* out, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+  if (n < 0 || c_in < 1 || c_out < 1 || k3 < 1 || algo < 0 || algo > 2) return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!in || !weight || !nbr || !out) return PTV3_EINVAL;
+  cudaStream_t st = as_stream(stream);
+  if (dtype == PTV3_BF16) {
+    bool tc_ok = subm_conv_tc_supported(c_in, c_out, k3);
+    if (algo == 2 && !tc_ok) return PTV3_EUNSUPPORTED;
+    if (algo != 1 && tc_ok)
+      return subm_conv_tc((const __nv_bfloat16*)in, (const __nv_bfloat16*)weight, bias, nbr, n, c_in, c_out, k3,
+                          (__nv_bfloat16*)out, workspace, workspace_bytes, st);
+    return conv_cuda_core<__nv_bfloat16>((const __nv_bfloat16*)in, (const __nv_bfloat16*)weight, bias, nbr, n, c_in,
+                                         c_out, k3, (__nv_bfloat16*)out, st);
+  }
+  if (dtype == PTV3_F32) {
+    if (algo == 2) return PTV3_EUNSUPPORTED;
+    return conv_cuda_core<float>((const float*)in, (const float*)weight, bias, nbr, n, c_in, c_out, k3, (float*)out,
+                                 st);
+  }
+  return PTV3_EINVAL;
+}
+
+}  // extern "C"

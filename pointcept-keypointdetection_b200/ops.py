@@ -1,0 +1,281 @@
+"""Torch-tensor wrappers over the C ABI (include/ptv3_b200.h).
+
+torch is plumbing here: it owns device memory and the current stream; every
+computation below is one of our sm_100a kernels.  All functions require CUDA
+tensors and raise RuntimeError otherwise (no CPU fallback).
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+
+ORDER_IDS = {"z": 0, "z-trans": 1, "hilbert": 2, "hilbert-trans": 3}
+REDUCE_IDS = {"sum": 0, "add": 0, "mean": 1, "max": 2, "min": 3}
+F32, BF16 = 0, 1
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("ptv3_b200 ops need CUDA tensors (no CPU fallback)")
+
+
+def _dt(t):
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise RuntimeError(f"unsupported dtype {t.dtype} (float32 / bfloat16 only)")
+
+
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+# ------------------------------------------------------------------ A2 serialization
+def encode_orders(grid_coord, batch, depth, orders):
+    """(len(orders), N) int64 codes.  serialization/default.py:9-24 for several orders in one pass."""
+    _need_cuda(grid_coord, batch)
+    lib = _lib.load()
+    if grid_coord.dtype not in (torch.int32, torch.int64):
+        grid_coord = grid_coord.long()
+    g = grid_coord.contiguous()
+    n = g.shape[0]
+    b = batch.contiguous().long() if batch is not None else None
+    ids = (ctypes.c_int * len(orders))(*[ORDER_IDS[o] for o in orders])
+    code = torch.empty((len(orders), n), dtype=torch.int64, device=g.device)
+    _lib.check(lib.ptv3_encode(_p(g), int(g.dtype == torch.int64), _p(b), n, int(depth), ids, len(orders), _p(code),
+                               _stream()), "ptv3_encode")
+    return code
+
+
+def encode(grid_coord, batch=None, depth=16, order="z"):
+    """Drop-in for pointcept.models.utils.serialization.encode (default.py:9-24)."""
+    if order not in ORDER_IDS:
+        raise AssertionError(order)
+    return encode_orders(grid_coord, batch, depth, [order])[0]
+
+
+def grid_max(grid_coord):
+    _need_cuda(grid_coord)
+    lib = _lib.load()
+    g = grid_coord.contiguous()
+    if g.dtype not in (torch.int32, torch.int64):
+        g = g.long()
+    out = torch.empty(1, dtype=torch.int64, device=g.device)
+    _lib.check(lib.ptv3_grid_max(_p(g), int(g.dtype == torch.int64), g.shape[0], _p(out), _stream()), "ptv3_grid_max")
+    return out
+
+
+def argsort_rows(code, key_bits=63, want_inverse=True):
+    """order, inverse of (rows, N) int64 codes (structure.py:92-99)."""
+    _need_cuda(code)
+    lib = _lib.load()
+    code = code.contiguous()
+    rows, n = code.shape
+    order = torch.empty_like(code)
+    inverse = torch.empty_like(code) if want_inverse else None
+    nbytes = lib.ptv3_argsort_rows_workspace(rows, n)
+    ws = _ws(nbytes, code.device)
+    _lib.check(lib.ptv3_argsort_rows(_p(code), rows, n, int(key_bits), _p(order), _p(inverse), _p(ws), ws.numel(),
+                                     _stream()), "ptv3_argsort_rows")
+    return order, inverse
+
+
+# ------------------------------------------------------------------ A0 GridSample
+def gridsample(coord, grid_size, hash_type="fnv", rand=None):
+    """Returns dict of device tensors (see include/ptv3_b200.h); one host sync to read the voxel count."""
+    _need_cuda(coord, rand)
+    lib = _lib.load()
+    coord = coord.contiguous().float()
+    r = coord.shape[0]
+    dev = coord.device
+    i64 = dict(dtype=torch.int64, device=dev)
+    grid = torch.empty((r, 3), **i64)
+    key = torch.empty(r, **i64)
+    idx_sort, inverse, count, idx_unique = (torch.empty(r, **i64) for _ in range(4))
+    min_grid = torch.empty(3, **i64)
+    n_vox = torch.zeros(1, **i64)
+    if rand is not None:
+        rand = rand.contiguous().long()
+        if rand.numel() < r:
+            rand = torch.cat([rand, rand.new_zeros(r - rand.numel())])
+    ws = _ws(lib.ptv3_gridsample_workspace(r), dev)
+    _lib.check(lib.ptv3_gridsample(_p(coord), r, float(grid_size), 0 if hash_type == "fnv" else 1, _p(rand), _p(grid),
+                                   _p(key), _p(idx_sort), _p(inverse), _p(count), _p(idx_unique), _p(min_grid),
+                                   _p(n_vox), _p(ws), ws.numel(), _stream()), "ptv3_gridsample")
+    m = int(n_vox.item())
+    return dict(grid_coord=grid, key=key, idx_sort=idx_sort, inverse=inverse, count=count[:m],
+                idx_unique=idx_unique[:m], min_grid=min_grid, n_voxels=m)
+
+
+# ------------------------------------------------------------------ A6 pooling front end
+def pool_front(code, order, pool_depth):
+    """SerializedPooling integer front end (:385-412).  One host sync (pooled count)."""
+    _need_cuda(code, order)
+    lib = _lib.load()
+    code, order = code.contiguous(), order.contiguous()
+    rows, n = code.shape
+    dev = code.device
+    i64 = dict(dtype=torch.int64, device=dev)
+    cluster, indices, head = (torch.empty(n, **i64) for _ in range(3))
+    idx_ptr = torch.empty(n + 1, **i64)
+    new_code, new_order, new_inverse = (torch.empty((rows, n), **i64) for _ in range(3))
+    n_pooled = torch.zeros(1, **i64)
+    ws = _ws(lib.ptv3_pool_front_workspace(rows, n), dev)
+    _lib.check(lib.ptv3_pool_front(_p(code), _p(order), rows, n, 3 * int(pool_depth), _p(cluster), _p(indices),
+                                   _p(idx_ptr), _p(head), _p(new_code), _p(new_order), _p(new_inverse), _p(n_pooled),
+                                   _p(ws), ws.numel(), _stream()), "ptv3_pool_front")
+    m = int(n_pooled.item())
+    return dict(cluster=cluster, indices=indices, idx_ptr=idx_ptr[:m + 1], head=head[:m],
+                code=new_code[:, :m].contiguous(), order=new_order[:, :m].contiguous(),
+                inverse=new_inverse[:, :m].contiguous(), n_pooled=m)
+
+
+def pool_gather_ints(grid, batch, head, pool_depth, m=None, want_grid=True, want_batch=True, want_indices=True):
+    _need_cuda(grid, batch, head)
+    lib = _lib.load()
+    grid, batch = grid.contiguous().long(), batch.contiguous().long()
+    m = int(head.shape[0]) if head is not None else int(grid.shape[0] if m is None else m)
+    dev = grid.device
+    ng = torch.empty((m, 3), dtype=torch.int64, device=dev) if want_grid else None
+    nb = torch.empty(m, dtype=torch.int64, device=dev) if want_batch else None
+    ni = torch.empty((m, 4), dtype=torch.int32, device=dev) if want_indices else None
+    _lib.check(lib.ptv3_pool_gather_ints(_p(grid), _p(batch), _p(head.contiguous() if head is not None else None), m,
+                                         int(pool_depth), _p(ng), _p(nb), _p(ni), _stream()), "ptv3_pool_gather_ints")
+    return ng, nb, ni
+
+
+def batch_to_offset(batch, n_scenes):
+    _need_cuda(batch)
+    lib = _lib.load()
+    batch = batch.contiguous().long()
+    off = torch.empty(int(n_scenes), dtype=torch.int64, device=batch.device)
+    _lib.check(lib.ptv3_batch_to_offset(_p(batch), batch.shape[0], int(n_scenes), _p(off), _stream()),
+               "ptv3_batch_to_offset")
+    return off
+
+
+# ------------------------------------------------------------------ segment reductions
+def segment_csr(src, indptr, reduce="sum", gather=None, long_segments=False):
+    """torch_scatter.segment_csr along dim 0 (optionally reading src rows through `gather`)."""
+    _need_cuda(src, indptr, gather)
+    lib = _lib.load()
+    shape = src.shape
+    src2 = src.contiguous().view(shape[0], -1) if src.dim() != 2 else src.contiguous()
+    c = src2.shape[1]
+    indptr = indptr.contiguous().long()
+    m = indptr.numel() - 1
+    out = torch.empty((m, c), dtype=src.dtype, device=src.device)
+    g = gather.contiguous().long() if gather is not None else None
+    _lib.check(lib.ptv3_segment_csr(_p(src2), _dt(src2), _p(g), _p(indptr), -m if long_segments else m, c,
+                                    REDUCE_IDS[reduce], _p(out), _stream()), "ptv3_segment_csr")
+    return out.view((m,) + tuple(shape[1:]))
+
+
+def unpool_add(skip, up, inverse, gelu=True, want_skip_act=True):
+    """out = act(skip) + act(up)[inverse]; also returns act(skip) (SerializedUnpooling :471-482)."""
+    _need_cuda(skip, up, inverse)
+    lib = _lib.load()
+    skip, up = skip.contiguous(), up.contiguous()
+    assert skip.dtype == up.dtype and skip.shape[1] == up.shape[1]
+    n, c = skip.shape
+    out = torch.empty_like(skip)
+    act = torch.empty_like(skip) if want_skip_act else None
+    _lib.check(lib.ptv3_unpool_add(_p(skip), _p(up), _dt(skip), _p(inverse.contiguous().long()), n, c, int(gelu),
+                                   _p(out), _p(act), _stream()), "ptv3_unpool_add")
+    return out, act
+
+
+def ln_residual(x, gamma=None, beta=None, eps=1e-5, residual=None, want_res=True, gamma2=None, beta2=None,
+                out2_dtype=None):
+    """t = LN(x) if gamma is given else x; r = residual + t (or t); returns (r fp32 or None, LN2(r) or None)."""
+    _need_cuda(x)
+    lib = _lib.load()
+    x = x.contiguous()
+    n, c = x.shape
+    res_out = torch.empty((n, c), dtype=torch.float32, device=x.device) if want_res else None
+    out2 = torch.empty((n, c), dtype=out2_dtype, device=x.device) if gamma2 is not None else None
+    if residual is not None:
+        residual = residual.contiguous()
+        assert residual.dtype == torch.float32
+    _lib.check(lib.ptv3_ln_residual(_p(x), _dt(x), _p(gamma), _p(beta), float(eps), _p(residual), _p(res_out),
+                                    _p(gamma2), _p(beta2), _p(out2), _dt(out2) if out2 is not None else 0, n, c,
+                                    _stream()), "ptv3_ln_residual")
+    return res_out, out2
+
+
+# ------------------------------------------------------------------ A5 submanifold conv
+def subm_build_map(indices, ksize):
+    """indices (N,4) int32 [b,x,y,z] -> nbr (N, ksize^3) int32 (-1 = absent)."""
+    _need_cuda(indices)
+    lib = _lib.load()
+    indices = indices.contiguous().int()
+    n = indices.shape[0]
+    nbr = torch.empty((n, ksize ** 3), dtype=torch.int32, device=indices.device)
+    ws = _ws(lib.ptv3_subm_map_workspace(n), indices.device)
+    _lib.check(lib.ptv3_subm_build_map(_p(indices), n, int(ksize), _p(nbr), _p(ws), ws.numel(), _stream()),
+               "ptv3_subm_build_map")
+    return nbr
+
+
+def subm_conv(feat, weight_koc, bias, nbr, algo=0):
+    """feat (N,Cin), weight (k^3, Cout, Cin) same dtype, bias fp32 (Cout) or None -> (N,Cout)."""
+    _need_cuda(feat, weight_koc, nbr)
+    lib = _lib.load()
+    feat, weight_koc = feat.contiguous(), weight_koc.contiguous()
+    assert feat.dtype == weight_koc.dtype
+    n, cin = feat.shape
+    k3, cout, cin2 = weight_koc.shape
+    assert cin2 == cin and nbr.shape == (n, k3) and nbr.dtype == torch.int32
+    out = torch.empty((n, cout), dtype=feat.dtype, device=feat.device)
+    dt = _dt(feat)
+    ws = _ws(lib.ptv3_subm_conv_workspace(n, cin, cout, k3, dt, algo), feat.device)
+    b = bias.contiguous().float() if bias is not None else None
+    _lib.check(lib.ptv3_subm_conv(_p(feat), _p(weight_koc), _p(b), _p(nbr.contiguous()), n, cin, cout, k3, dt,
+                                  int(algo), _p(out), _p(ws), ws.numel(), _stream()), "ptv3_subm_conv")
+    return out
+
+
+# ------------------------------------------------------------------ A3/A4 attention
+def build_windows(offset, patch, n_total):
+    """Window records (W_max,4) int64 + device count.  W_max = N // patch + n_scenes (upper bound, no sync)."""
+    _need_cuda(offset)
+    lib = _lib.load()
+    offset = offset.contiguous().long()
+    b = offset.numel()
+    wmax = int(n_total) // int(patch) + b
+    windows = torch.empty((wmax, 4), dtype=torch.int64, device=offset.device)
+    nwin = torch.empty(1, dtype=torch.int64, device=offset.device)
+    _lib.check(lib.ptv3_build_windows(_p(offset), b, int(patch), _p(windows), wmax, _p(nwin), _stream()),
+               "ptv3_build_windows")
+    return windows, nwin
+
+
+def attn_window(qkv, order, windows, n_windows, num_heads, max_len, scale=None, algo=0):
+    """qkv (N, 3*H*16) rows in storage order -> (N, H*16) in storage order."""
+    _need_cuda(qkv, order, windows, n_windows)
+    lib = _lib.load()
+    qkv = qkv.contiguous()
+    n = qkv.shape[0]
+    c = qkv.numel() // (3 * n) if n > 0 else 0
+    h = int(num_heads)
+    d = c // h if h else 0
+    out = torch.empty((n, c), dtype=qkv.dtype, device=qkv.device)
+    if n == 0:
+        return out
+    scale = float(scale) if scale is not None else d ** -0.5
+    o = order.contiguous().long() if order is not None else None
+    _lib.check(lib.ptv3_attn_window_fwd(_p(qkv), _dt(qkv), _p(o), _p(windows), _p(n_windows), windows.shape[0],
+                                        int(max_len), n, h, d, scale, int(algo), _p(out), _stream()),
+               "ptv3_attn_window_fwd")
+    return out
