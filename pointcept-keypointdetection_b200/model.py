@@ -1,0 +1,648 @@
+"""PT-v3m1 backbone + the fork's heads over the sm_100a kernels (inference).
+
+Same module tree, constructor arguments and state_dict names as the reference
+(pointcept/models/point_transformer_v3/point_transformer_v3m1_base.py,
+offset_keypoint_ptv3.py, keypoint_ptv3.py, default.py) so its checkpoints load
+unchanged; the forward of every module is re-designed around our fused ops:
+
+  * the residual stream (`point.feat`) is fp32; GEMM / conv / attention operands are
+    `compute_dtype` (bf16 by default, fp32 for the 1e-4 parity path) -- what the
+    reference gets from torch.autocast;
+  * eval-mode BatchNorm is folded into the adjacent Linear / conv weights;
+  * residual adds, LayerNorms and the casts between them are one kernel
+    (ops.ln_residual); the two GELUs + gather-add of unpooling are one kernel;
+  * attention reads / writes rows in storage order through the serialized order
+    (no [order] gather, no [inverse] scatter, no padding copies);
+  * pooling derives clusters and the pooled orders from the parent's orders
+    without sorting.
+Attention uses the flash window semantics of the reference (fixed patch size,
+short scenes form one short window, :208-215); its enable_flash=False branch
+only coincides with that for one scene per forward.
+Training (autograd through the kernels) is out of scope for this round.
+"""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+from .structure import Point, SparseConvTensor, offset2batch  # noqa: F401
+
+
+def _cached(module, slot, params, builder):
+    """Per-module cache of prepared (folded / re-laid / cast) weights keyed on parameter versions."""
+    key = tuple((p.data_ptr(), p._version, p.dtype, p.device) for p in params if p is not None)
+    store = module.__dict__.setdefault("_prep_cache", {})
+    hit = store.get(slot)
+    if hit is not None and hit[0] == key:
+        return hit[1]
+    with torch.no_grad():
+        val = builder()
+    store[slot] = (key, val)
+    return val
+
+
+def _bn_scale_shift(bn):
+    s = bn.weight.float() / torch.sqrt(bn.running_var.float() + bn.eps)
+    return s, bn.bias.float() - bn.running_mean.float() * s
+
+
+def _feat_cd(point, dtype):
+    """point.feat in the compute dtype (cached copy written by the producing kernel when there is one)."""
+    f = point.get("_feat_cd")
+    if f is not None and f.dtype == dtype and f.shape == point.feat.shape:
+        return f
+    return point.feat if point.feat.dtype == dtype else point.feat.to(dtype)
+
+
+class PointModule(nn.Module):
+    """modules.py:28-34."""
+
+
+class SparseModule(nn.Module):
+    """spconv.pytorch.modules.SparseModule stand-in (modules.py:84 tests isinstance)."""
+
+
+def is_spconv_module(m):
+    return isinstance(m, SparseModule)
+
+
+class PointSequential(PointModule):
+    """modules.py:37-111: named container that dispatches on the module kind."""
+
+    def __init__(self, *args, **kwargs):
+        super().__init__()
+        for i, m in enumerate(args):
+            self.add_module(str(i), m)
+        for k, m in kwargs.items():
+            self.add_module(k, m)
+
+    def __getitem__(self, idx):
+        return list(self._modules.values())[idx]
+
+    def __len__(self):
+        return len(self._modules)
+
+    def add(self, module, name=None):
+        self.add_module(str(len(self._modules)) if name is None else name, module)
+        return self
+
+    def forward(self, input):
+        for module in self._modules.values():
+            if isinstance(module, PointModule):
+                input = module(input)
+            elif is_spconv_module(module):
+                if isinstance(input, Point):
+                    input.sparse_conv_feat = module(input.sparse_conv_feat)
+                    input.feat = input.sparse_conv_feat.features
+                else:
+                    input = module(input)
+            else:
+                if isinstance(input, Point):
+                    input.feat = module(input.feat)
+                    input["_feat_cd"] = None
+                    if "sparse_conv_feat" in input:
+                        input.sparse_conv_feat = input.sparse_conv_feat.replace_feature(input.feat)
+                elif isinstance(input, SparseConvTensor):
+                    if input.indices.shape[0] != 0:
+                        input = input.replace_feature(module(input.features))
+                else:
+                    input = module(input)
+        return input
+
+
+class SubMConv3d(SparseModule):
+    """spconv.pytorch.SubMConv3d surface (call sites :278-284, :499-506): weight (out,kD,kH,kW,in), bias (out),
+    forward(SparseConvTensor) -> SparseConvTensor on the same sites; the neighbour map is cached in
+    x.indice_dict[(indice_key, k)] and shared through replace_feature.  `padding` is ignored like in spconv 2.x."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1, bias=True,
+                 indice_key=None):
+        super().__init__()
+        if stride != 1 or dilation != 1 or groups != 1:
+            raise NotImplementedError("SubMConv3d: stride/dilation/groups other than 1 are not on the PTv3 path")
+        if not isinstance(kernel_size, int):
+            assert len(set(kernel_size)) == 1
+            kernel_size = kernel_size[0]
+        self.in_channels, self.out_channels, self.kernel_size = in_channels, out_channels, kernel_size
+        self.indice_key = indice_key
+        k = kernel_size
+        self.weight = nn.Parameter(torch.empty(out_channels, k, k, k, in_channels))
+        self.bias = nn.Parameter(torch.empty(out_channels)) if bias else None
+        bound = 1.0 / math.sqrt(in_channels * k ** 3)
+        nn.init.uniform_(self.weight, -bound, bound)
+        if bias:
+            nn.init.uniform_(self.bias, -bound, bound)
+
+    def neighbor_map(self, x):
+        key = (self.indice_key, self.kernel_size)
+        nbr = x.indice_dict.get(key) if self.indice_key is not None else None
+        if nbr is None:
+            nbr = ops.subm_build_map(x.indices, self.kernel_size)
+            if self.indice_key is not None:
+                x.indice_dict[key] = nbr
+        return nbr
+
+    def _weights(self, dtype, scale=None, shift=None):
+        def build():
+            w = self.weight.float()
+            b = self.bias.float() if self.bias is not None else None
+            if scale is not None:      # fold an eval-mode BatchNorm that follows the conv
+                w = w * scale.view(-1, 1, 1, 1, 1)
+                b = shift if b is None else b * scale + shift
+            k3 = self.kernel_size ** 3
+            w = w.reshape(self.out_channels, k3, self.in_channels).permute(1, 0, 2).contiguous().to(dtype)
+            return w, (b.contiguous() if b is not None else None)
+        return _cached(self, ("w", dtype, scale is not None), [self.weight, self.bias, scale, shift], build)
+
+    def conv(self, features, x, scale=None, shift=None, algo=0):
+        w, b = self._weights(features.dtype, scale, shift)
+        return ops.subm_conv(features, w, b, self.neighbor_map(x), algo=algo)
+
+    def forward(self, x):
+        return x.replace_feature(self.conv(x.features, x))
+
+
+class SerializedAttention(PointModule):
+    """:51-222.  qkv Linear -> fused window attention kernel -> proj Linear."""
+
+    def __init__(self, channels, num_heads, patch_size, qkv_bias=True, qk_scale=None, attn_drop=0.0, proj_drop=0.0,
+                 order_index=0, enable_rpe=False, enable_flash=True, upcast_attention=True, upcast_softmax=True):
+        super().__init__()
+        assert channels % num_heads == 0
+        if enable_rpe:
+            raise NotImplementedError("enable_rpe=True is not used by any target config (SURVEY.md 8a A4)")
+        if channels // num_heads != 16:
+            raise NotImplementedError("head_dim must be 16 (true for every PTv3 config, SURVEY.md fact 1)")
+        self.channels, self.num_heads = channels, num_heads
+        self.scale = qk_scale or (channels // num_heads) ** -0.5
+        self.order_index = order_index
+        self.patch_size_max = patch_size
+        self.patch_size = patch_size
+        self.qkv = nn.Linear(channels, channels * 3, bias=qkv_bias)
+        self.proj = nn.Linear(channels, channels)
+        self.compute_dtype = torch.bfloat16
+        self.algo = 0
+
+    @torch.no_grad()
+    def get_windows(self, point):
+        """Replaces get_padding_and_inverse (:115-170): per-window (q_start,q_len,k_start,k_len) records, cached in
+        the Point like the reference caches pad/unpad/cu_seqlens."""
+        key = f"windows_{self.patch_size}"
+        if key not in point:
+            point[key] = ops.build_windows(point.offset, self.patch_size, point.feat.shape[0])
+        return point[key]
+
+    def attend(self, point, qkv):
+        windows, nwin = self.get_windows(point)
+        order = point.serialized_order[self.order_index]
+        return ops.attn_window(qkv, order, windows, nwin, self.num_heads, self.patch_size, self.scale, self.algo)
+
+    def _w(self, lin, dtype):
+        return _cached(self, (id(lin), dtype), [lin.weight, lin.bias],
+                       lambda: (lin.weight.to(dtype), lin.bias.to(dtype) if lin.bias is not None else None))
+
+    def forward(self, point):
+        cd = self.compute_dtype
+        wq, bq = self._w(self.qkv, cd)
+        wp, bp = self._w(self.proj, cd)
+        a = self.attend(point, F.linear(_feat_cd(point, cd), wq, bq))
+        point.feat = F.linear(a, wp, bp).float()
+        point["_feat_cd"] = None
+        return point
+
+
+class MLP(nn.Module):
+    """:225-248."""
+
+    def __init__(self, in_channels, hidden_channels=None, out_channels=None, act_layer=nn.GELU, drop=0.0):
+        super().__init__()
+        out_channels = out_channels or in_channels
+        hidden_channels = hidden_channels or in_channels
+        self.fc1 = nn.Linear(in_channels, hidden_channels)
+        self.act = act_layer()
+        self.fc2 = nn.Linear(hidden_channels, out_channels)
+        self.drop = nn.Dropout(drop)
+
+    def forward(self, x):
+        return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
+
+
+class Block(PointModule):
+    """:251-338.  xCPE (SubMConv3d -> Linear -> LN) + attention + MLP with pre-norm; three fused
+    residual/LayerNorm kernels replace the six elementwise passes of the reference."""
+
+    def __init__(self, channels, num_heads, patch_size=48, mlp_ratio=4.0, qkv_bias=True, qk_scale=None, attn_drop=0.0,
+                 proj_drop=0.0, drop_path=0.0, norm_layer=nn.LayerNorm, act_layer=nn.GELU, pre_norm=True,
+                 order_index=0, cpe_indice_key=None, enable_rpe=False, enable_flash=True, upcast_attention=True,
+                 upcast_softmax=True):
+        super().__init__()
+        if not pre_norm:
+            raise NotImplementedError("pre_norm=False is not used by any target config")
+        self.channels, self.pre_norm = channels, pre_norm
+        self.cpe = PointSequential(
+            SubMConv3d(channels, channels, kernel_size=3, bias=True, indice_key=cpe_indice_key),
+            nn.Linear(channels, channels), norm_layer(channels))
+        self.norm1 = PointSequential(norm_layer(channels))
+        self.attn = SerializedAttention(channels=channels, patch_size=patch_size, num_heads=num_heads,
+                                        qkv_bias=qkv_bias, qk_scale=qk_scale, attn_drop=attn_drop,
+                                        proj_drop=proj_drop, order_index=order_index, enable_rpe=enable_rpe,
+                                        enable_flash=enable_flash, upcast_attention=upcast_attention,
+                                        upcast_softmax=upcast_softmax)
+        self.norm2 = PointSequential(norm_layer(channels))
+        self.mlp = PointSequential(MLP(in_channels=channels, hidden_channels=int(channels * mlp_ratio),
+                                       out_channels=channels, act_layer=act_layer, drop=proj_drop))
+        self.drop_path = PointSequential(nn.Identity())   # DropPath is identity in eval (timm)
+        self.compute_dtype = torch.bfloat16
+        self.conv_algo = 0
+
+    def _lin(self, lin, dtype):
+        return _cached(self, (id(lin), dtype), [lin.weight, lin.bias],
+                       lambda: (lin.weight.to(dtype), lin.bias.to(dtype) if lin.bias is not None else None))
+
+    @staticmethod
+    def _ln(ln):
+        return ln.weight, ln.bias, ln.eps
+
+    @torch.no_grad()
+    def forward(self, point):
+        if self.training:
+            raise NotImplementedError("ptv3_b200 Block: inference only (call .eval())")
+        cd = self.compute_dtype
+        x = point.feat if point.feat.dtype == torch.float32 else point.feat.float()
+        sp = point.sparse_conv_feat
+        conv_in = sp.features if sp.features.dtype == cd else sp.features.to(cd)
+        # cpe: SubMConv3d -> Linear -> LayerNorm, + shortcut, then pre-norm of the attention
+        y = self.cpe[0].conv(conv_in, sp, algo=self.conv_algo)
+        y = F.linear(y, *self._lin(self.cpe[1], cd))
+        g1, b1, eps1 = self._ln(self.cpe[2])
+        gn1, bn1, _ = self._ln(self.norm1[0])
+        x, h = ops.ln_residual(y, g1, b1, eps1, residual=x, gamma2=gn1, beta2=bn1, out2_dtype=cd)
+        # attention
+        qkv = F.linear(h, *self.attn._w(self.attn.qkv, cd))
+        a = self.attn.attend(point, qkv)
+        p = F.linear(a, *self.attn._w(self.attn.proj, cd))
+        gn2, bn2, eps2 = self._ln(self.norm2[0])
+        x, h = ops.ln_residual(p, None, None, eps2, residual=x, gamma2=gn2, beta2=bn2, out2_dtype=cd)
+        # mlp
+        mlp = self.mlp[0]
+        f = F.gelu(F.linear(h, *self._lin(mlp.fc1, cd)))
+        f = F.linear(f, *self._lin(mlp.fc2, cd))
+        x, xcd = ops.ln_residual(f, None, None, 1e-5, residual=x, out2_dtype=None if cd == torch.float32 else cd)
+        point.feat = x
+        point["_feat_cd"] = xcd if xcd is not None else x
+        point.sparse_conv_feat = sp.replace_feature(point["_feat_cd"])
+        return point
+
+
+class SerializedPooling(PointModule):
+    """:341-444.  Integer front end without sorts (ops.pool_front), gather-fused segment max / mean."""
+
+    def __init__(self, in_channels, out_channels, stride=2, norm_layer=None, act_layer=None, reduce="max",
+                 shuffle_orders=True, traceable=True):
+        super().__init__()
+        assert stride == 2 ** (math.ceil(stride) - 1).bit_length()
+        assert reduce in ["sum", "mean", "min", "max"]
+        self.in_channels, self.out_channels, self.stride = in_channels, out_channels, stride
+        self.reduce, self.shuffle_orders, self.traceable = reduce, shuffle_orders, traceable
+        self.proj = nn.Linear(in_channels, out_channels)
+        if norm_layer is not None:
+            self.norm = PointSequential(norm_layer(out_channels))
+        if act_layer is not None:
+            self.act = PointSequential(act_layer())
+        self.compute_dtype = torch.bfloat16
+
+    @torch.no_grad()
+    def forward(self, point):
+        cd = self.compute_dtype
+        pooling_depth = (math.ceil(self.stride) - 1).bit_length()
+        if pooling_depth > point.serialized_depth:
+            pooling_depth = 0
+        assert {"serialized_code", "serialized_order", "serialized_inverse", "serialized_depth"}.issubset(
+            point.keys()), "Run point.serialization() point cloud before SerializedPooling"
+        pf = ops.pool_front(point.serialized_code, point.serialized_order, pooling_depth)
+        grid_coord, batch, indices4 = ops.pool_gather_ints(point.grid_coord, point.batch, pf["head"], pooling_depth)
+        code, order, inverse = pf["code"], pf["order"], pf["inverse"]
+        if self.shuffle_orders:
+            perm = torch.randperm(code.shape[0])
+            if not torch.equal(perm, torch.arange(code.shape[0])):
+                perm = perm.to(code.device)
+                code, order, inverse = code[perm], order[perm], inverse[perm]
+        w, b = _cached(self, ("proj", cd), [self.proj.weight, self.proj.bias],
+                       lambda: (self.proj.weight.to(cd), self.proj.bias.to(cd)))
+        y = F.linear(_feat_cd(point, cd), w, b)
+        feat = ops.segment_csr(y, pf["idx_ptr"], self.reduce, gather=pf["indices"]).float()
+        coord = ops.segment_csr(point.coord.float(), pf["idx_ptr"], "mean", gather=pf["indices"])
+        if hasattr(self, "norm"):
+            bn = self.norm[0]
+            if isinstance(bn, nn.BatchNorm1d):
+                s, t = _cached(self, "bn", [bn.weight, bn.bias, bn.running_mean, bn.running_var],
+                               lambda: _bn_scale_shift(bn))
+                feat = feat * s + t
+            else:
+                feat = bn(feat)
+        if hasattr(self, "act"):
+            feat = self.act[0](feat)
+        n_scenes = len(point.offset)
+        new = Point(feat=feat, coord=coord, grid_coord=grid_coord, serialized_code=code, serialized_order=order,
+                    serialized_inverse=inverse, serialized_depth=point.serialized_depth - pooling_depth, batch=batch,
+                    offset=ops.batch_to_offset(batch, n_scenes))
+        for k in ("condition", "context", "grid_size", "order"):
+            if k in point:
+                new[k] = point[k]
+        if self.traceable:
+            new["pooling_inverse"] = pf["cluster"]
+            new["pooling_parent"] = point
+        new["_feat_cd"] = feat if cd == torch.float32 else feat.to(cd)
+        new["sparse_shape"] = [(1 << max(int(new.serialized_depth), 0)) + 96] * 3
+        new["sparse_conv_feat"] = SparseConvTensor(new["_feat_cd"], indices4, new["sparse_shape"], n_scenes)
+        return new
+
+
+class SerializedUnpooling(PointModule):
+    """:447-482.  Both Linear+BN pairs folded; GELU, GELU and the gather-add are one kernel."""
+
+    def __init__(self, in_channels, skip_channels, out_channels, norm_layer=None, act_layer=None, traceable=False):
+        super().__init__()
+        self.proj = PointSequential(nn.Linear(in_channels, out_channels))
+        self.proj_skip = PointSequential(nn.Linear(skip_channels, out_channels))
+        if norm_layer is not None:
+            self.proj.add(norm_layer(out_channels))
+            self.proj_skip.add(norm_layer(out_channels))
+        self.gelu = act_layer is not None and issubclass(act_layer, nn.GELU)
+        if act_layer is not None:
+            if not self.gelu:
+                raise NotImplementedError("SerializedUnpooling: only GELU is fused")
+            self.proj.add(act_layer())
+            self.proj_skip.add(act_layer())
+        self.traceable = traceable
+        self.compute_dtype = torch.bfloat16
+
+    def _folded(self, seq, dtype):
+        lin = seq[0]
+        bn = seq[1] if len(seq) > 1 and isinstance(seq[1], nn.BatchNorm1d) else None
+        params = [lin.weight, lin.bias] + ([bn.weight, bn.bias, bn.running_mean, bn.running_var] if bn else [])
+
+        def build():
+            w, b = lin.weight.float(), lin.bias.float()
+            if bn is not None:
+                s, t = _bn_scale_shift(bn)
+                w, b = w * s[:, None], b * s + t
+            return w.to(dtype).contiguous(), b.to(dtype).contiguous()
+        return _cached(self, (id(seq), dtype), params, build)
+
+    @torch.no_grad()
+    def forward(self, point):
+        assert "pooling_parent" in point and "pooling_inverse" in point
+        cd = self.compute_dtype
+        parent = point.pop("pooling_parent")
+        inverse = point.pop("pooling_inverse")
+        up = F.linear(_feat_cd(point, cd), *self._folded(self.proj, cd))
+        skip = F.linear(_feat_cd(parent, cd), *self._folded(self.proj_skip, cd))
+        out, skip_act = ops.unpool_add(skip, up, inverse, gelu=self.gelu)
+        parent.feat = out
+        parent["_feat_cd"] = None
+        # the reference leaves the parent's sparse tensor holding the proj_skip branch only (PointSequential updates
+        # it before `parent.feat = parent.feat + point.feat[inverse]`, :476-477): the next conv reads that.
+        parent.sparse_conv_feat = parent.sparse_conv_feat.replace_feature(skip_act)
+        if self.traceable:
+            parent["unpooling_parent"] = point
+        return parent
+
+
+class Embedding(PointModule):
+    """:485-516.  Stem SubMConv3d(k5) with the eval BatchNorm folded, then GELU."""
+
+    def __init__(self, in_channels, embed_channels, norm_layer=None, act_layer=None):
+        super().__init__()
+        self.in_channels, self.embed_channels = in_channels, embed_channels
+        self.stem = PointSequential(conv=SubMConv3d(in_channels, embed_channels, kernel_size=5, padding=1, bias=False,
+                                                    indice_key="stem"))
+        if norm_layer is not None:
+            self.stem.add(norm_layer(embed_channels), name="norm")
+        if act_layer is not None:
+            self.stem.add(act_layer(), name="act")
+        self.compute_dtype = torch.bfloat16
+
+    @torch.no_grad()
+    def forward(self, point):
+        cd = self.compute_dtype
+        conv = self.stem.conv
+        sp = point.sparse_conv_feat
+        bn = getattr(self.stem, "norm", None)
+        feat_in = point.feat.float()
+        if isinstance(bn, nn.BatchNorm1d) and not bn.training:
+            s, t = _cached(self, "bn", [bn.weight, bn.bias, bn.running_mean, bn.running_var],
+                           lambda: _bn_scale_shift(bn))
+            y = conv.conv(feat_in, sp, scale=s, shift=t)
+        else:
+            y = conv.conv(feat_in, sp)
+            if bn is not None:
+                y = bn(y)
+        if hasattr(self.stem, "act"):
+            y = self.stem.act(y)
+        point.feat = y
+        point["_feat_cd"] = y if cd == torch.float32 else y.to(cd)
+        point.sparse_conv_feat = sp.replace_feature(point["_feat_cd"])
+        return point
+
+
+class PointTransformerV3(PointModule):
+    """:519-714 (PT-v3m1).  Same constructor and state_dict as the reference.
+    `compute_dtype`: torch.bfloat16 (default, = the reference under autocast) or torch.float32."""
+
+    def __init__(self, in_channels=6, order=("z", "z-trans"), stride=(2, 2, 2, 2), enc_depths=(2, 2, 2, 6, 2),
+                 enc_channels=(32, 64, 128, 256, 512), enc_num_head=(2, 4, 8, 16, 32),
+                 enc_patch_size=(48, 48, 48, 48, 48), dec_depths=(2, 2, 2, 2), dec_channels=(64, 64, 128, 256),
+                 dec_num_head=(4, 4, 8, 16), dec_patch_size=(48, 48, 48, 48), mlp_ratio=4, qkv_bias=True,
+                 qk_scale=None, attn_drop=0.0, proj_drop=0.0, drop_path=0.3, pre_norm=True, shuffle_orders=True,
+                 enable_rpe=False, enable_flash=True, upcast_attention=False, upcast_softmax=False, enc_mode=False,
+                 pdnorm_bn=False, pdnorm_ln=False, pdnorm_decouple=True, pdnorm_adaptive=False, pdnorm_affine=True,
+                 pdnorm_conditions=("ScanNet", "S3DIS", "Structured3D"), compute_dtype=torch.bfloat16):
+        super().__init__()
+        from functools import partial
+        self.num_stages = len(enc_depths)
+        self.order = [order] if isinstance(order, str) else list(order)
+        self.enc_mode = enc_mode
+        self.shuffle_orders = shuffle_orders
+        assert self.num_stages == len(stride) + 1
+        assert self.num_stages == len(enc_depths) == len(enc_channels) == len(enc_num_head) == len(enc_patch_size)
+        assert self.enc_mode or self.num_stages == len(dec_depths) + 1
+        assert self.enc_mode or self.num_stages == len(dec_channels) + 1
+        assert self.enc_mode or self.num_stages == len(dec_num_head) + 1
+        assert self.enc_mode or self.num_stages == len(dec_patch_size) + 1
+        if pdnorm_bn or pdnorm_ln:
+            raise NotImplementedError("PDNorm is disabled in every target config (SURVEY.md section 2 row 11)")
+        bn_layer = partial(nn.BatchNorm1d, eps=1e-3, momentum=0.01)
+        ln_layer = nn.LayerNorm
+        act_layer = nn.GELU
+
+        self.embedding = Embedding(in_channels=in_channels, embed_channels=enc_channels[0], norm_layer=bn_layer,
+                                   act_layer=act_layer)
+        common = dict(mlp_ratio=mlp_ratio, qkv_bias=qkv_bias, qk_scale=qk_scale, attn_drop=attn_drop,
+                      proj_drop=proj_drop, norm_layer=ln_layer, act_layer=act_layer, pre_norm=pre_norm,
+                      enable_rpe=enable_rpe, enable_flash=enable_flash, upcast_attention=upcast_attention,
+                      upcast_softmax=upcast_softmax)
+        self.enc = PointSequential()
+        for s in range(self.num_stages):
+            enc = PointSequential()
+            if s > 0:
+                enc.add(SerializedPooling(in_channels=enc_channels[s - 1], out_channels=enc_channels[s],
+                                          stride=stride[s - 1], norm_layer=bn_layer, act_layer=act_layer,
+                                          shuffle_orders=shuffle_orders), name="down")
+            for i in range(enc_depths[s]):
+                enc.add(Block(channels=enc_channels[s], num_heads=enc_num_head[s], patch_size=enc_patch_size[s],
+                              order_index=i % len(self.order), cpe_indice_key=f"stage{s}", **common), name=f"block{i}")
+            if len(enc) != 0:
+                self.enc.add(module=enc, name=f"enc{s}")
+        if not self.enc_mode:
+            self.dec = PointSequential()
+            dec_channels = list(dec_channels) + [enc_channels[-1]]
+            for s in reversed(range(self.num_stages - 1)):
+                dec = PointSequential()
+                dec.add(SerializedUnpooling(in_channels=dec_channels[s + 1], skip_channels=enc_channels[s],
+                                            out_channels=dec_channels[s], norm_layer=bn_layer, act_layer=act_layer),
+                        name="up")
+                for i in range(dec_depths[s]):
+                    dec.add(Block(channels=dec_channels[s], num_heads=dec_num_head[s], patch_size=dec_patch_size[s],
+                                  order_index=i % len(self.order), cpe_indice_key=f"stage{s}", **common),
+                            name=f"block{i}")
+                self.dec.add(module=dec, name=f"dec{s}")
+        self.set_compute_dtype(compute_dtype)
+
+    def set_compute_dtype(self, dtype):
+        assert dtype in (torch.bfloat16, torch.float32)
+        for m in self.modules():
+            if hasattr(m, "compute_dtype"):
+                m.compute_dtype = dtype
+        return self
+
+    def set_algos(self, conv=0, attn=0):
+        """Kernel selection for A/B tests: 0 auto, 1 CUDA-core reference kernels, 2 tensor-core kernels."""
+        for m in self.modules():
+            if isinstance(m, Block):
+                m.conv_algo = conv
+            if isinstance(m, SerializedAttention):
+                m.algo = attn
+        return self
+
+    @torch.no_grad()
+    def forward(self, data_dict):
+        point = Point(data_dict)
+        point.serialization(order=self.order, shuffle_orders=self.shuffle_orders)
+        point.sparsify()
+        point = self.embedding(point)
+        point = self.enc(point)
+        if not self.enc_mode:
+            point = self.dec(point)
+        return point
+
+
+class OffsetKeypointPTv3(nn.Module):
+    """offset_keypoint_ptv3.py:7-107 (inference branch): backbone -> Linear/BN/ReLU/Dropout/Linear -> (N,K,4),
+    sigmoid on the mask channel.  The head runs in fp32 (offsets need ~1e-3 absolute accuracy)."""
+
+    def __init__(self, backbone_conf, num_keypoints=6, hidden_dim=256, backbone=None):
+        super().__init__()
+        in_channels = backbone_conf["dec_channels"][0] if "dec_channels" in backbone_conf else 64
+        if backbone is None:
+            conf = dict(backbone_conf)
+            conf.pop("type", None)
+            backbone = PointTransformerV3(**conf)
+        self.backbone = backbone
+        self.num_keypoints = num_keypoints
+        self.head = nn.Sequential(nn.Linear(in_channels, hidden_dim), nn.BatchNorm1d(hidden_dim),
+                                  nn.ReLU(inplace=True), nn.Linear(hidden_dim, num_keypoints * 4))
+
+    @torch.no_grad()
+    def forward(self, data_dict):
+        if self.training:
+            raise NotImplementedError("ptv3_b200 OffsetKeypointPTv3: inference only (call .eval())")
+        point = self.backbone(data_dict)
+        feat = point.feat if isinstance(point, Point) else point
+        lin, bn = self.head[0], self.head[1]
+
+        def build():
+            s, t = _bn_scale_shift(bn)
+            return (lin.weight.float() * s[:, None]).contiguous(), (lin.bias.float() * s + t).contiguous()
+        w, b = _cached(self, "head0", [lin.weight, lin.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var],
+                       build)
+        h = F.relu(F.linear(feat.float(), w, b), inplace=True)
+        pred = F.linear(h, self.head[3].weight.float(), self.head[3].bias.float()).view(-1, self.num_keypoints, 4)
+        pred[..., 3] = torch.sigmoid(pred[..., 3])
+        return dict(pred=pred)
+
+
+class KeypointPTv3(nn.Module):
+    """keypoint_ptv3.py:8-98 (inference): per-scene mean pool (torch_scatter.scatter_mean, :44) -> 3-layer MLP."""
+
+    def __init__(self, backbone_conf, num_keypoints=6, hidden_dim=256, backbone=None):
+        super().__init__()
+        in_channels = backbone_conf["dec_channels"][0] if "dec_channels" in backbone_conf else 64
+        if backbone is None:
+            conf = dict(backbone_conf)
+            conf.pop("type", None)
+            backbone = PointTransformerV3(**conf)
+        self.backbone = backbone
+        self.num_keypoints = num_keypoints
+        self.reg_head = nn.Sequential(nn.Linear(in_channels, hidden_dim), nn.BatchNorm1d(hidden_dim),
+                                      nn.ReLU(inplace=True), nn.Dropout(0.3), nn.Linear(hidden_dim, hidden_dim),
+                                      nn.ReLU(inplace=True), nn.Linear(hidden_dim, num_keypoints * 3))
+
+    @torch.no_grad()
+    def forward(self, data_dict):
+        if self.training:
+            raise NotImplementedError("ptv3_b200 KeypointPTv3: inference only (call .eval())")
+        point = self.backbone(data_dict)
+        indptr = F.pad(point.offset, (1, 0))
+        g = ops.segment_csr(point.feat.float(), indptr, "mean", long_segments=True)
+        return dict(pred=self.reg_head(g).view(-1, self.num_keypoints, 3))
+
+
+class DefaultSegmentorV2(nn.Module):
+    """default.py:41-95 (inference): backbone -> Linear(backbone_out_channels, num_classes)."""
+
+    def __init__(self, num_classes, backbone_out_channels, backbone=None, criteria=None, freeze_backbone=False):
+        super().__init__()
+        if isinstance(backbone, dict):
+            conf = dict(backbone)
+            conf.pop("type", None)
+            backbone = PointTransformerV3(**conf)
+        self.backbone = backbone
+        self.seg_head = nn.Linear(backbone_out_channels, num_classes) if num_classes > 0 else nn.Identity()
+
+    @torch.no_grad()
+    def forward(self, input_dict, return_point=False):
+        point = self.backbone(Point(input_dict))
+        while isinstance(point, Point) and "pooling_parent" in point:     # enc_mode backbones (:74-82)
+            parent = point.pop("pooling_parent")
+            inverse = point.pop("pooling_inverse")
+            parent.feat = torch.cat([parent.feat, point.feat[inverse]], dim=-1)
+            point = parent
+        feat = point.feat if isinstance(point, Point) else point
+        out = dict(seg_logits=self.seg_head(feat.float()))
+        if return_point:
+            out["point"] = point
+        return out
+
+
+def aggregate_keypoints(coord, pred, offset, mode="argmax", mask_thresh=0.5):
+    """tools/infer_offset.py:366-399 per scene, on the device without per-keypoint host syncs:
+    kp[b,k] = coord[i*] + pred[i*,k,:3], i* = argmax_i pred[i,k,3] over the scene (votes in model units)."""
+    votes = coord[:, None, :] + pred[..., :3]
+    conf = pred[..., 3]
+    starts = F.pad(offset, (1, 0))[:-1].tolist()
+    ends = offset.tolist()
+    out = []
+    for s, e in zip(starts, ends):
+        c, v = conf[s:e], votes[s:e]
+        best = c.argmax(0)                                             # (K,)
+        kp = v[best, torch.arange(v.shape[1], device=v.device)]
+        if mode == "weighted":
+            w = torch.where(c > mask_thresh, c, torch.zeros_like(c))
+            tot = w.sum(0)
+            kpw = (v * w[..., None]).sum(0) / tot.clamp_min(1e-12)[:, None]
+            kp = torch.where((tot > 0)[:, None], kpw, kp)
+        out.append(kp)
+    return torch.stack(out)

@@ -71,7 +71,7 @@ def grid_max(grid_coord):
     g = grid_coord.contiguous()
     if g.dtype not in (torch.int32, torch.int64):
         g = g.long()
-    out = torch.empty(1, dtype=torch.int64, device=g.device)
+    out = torch.empty(3, dtype=torch.int64, device=g.device)
     _lib.check(lib.ptv3_grid_max(_p(g), int(g.dtype == torch.int64), g.shape[0], _p(out), _stream()), "ptv3_grid_max")
     return out
 
@@ -189,7 +189,7 @@ def unpool_add(skip, up, inverse, gelu=True, want_skip_act=True):
     skip, up = skip.contiguous(), up.contiguous()
     assert skip.dtype == up.dtype and skip.shape[1] == up.shape[1]
     n, c = skip.shape
-    out = torch.empty_like(skip)
+    out = torch.empty((n, c), dtype=torch.float32, device=skip.device)
     act = torch.empty_like(skip) if want_skip_act else None
     _lib.check(lib.ptv3_unpool_add(_p(skip), _p(up), _dt(skip), _p(inverse.contiguous().long()), n, c, int(gelu),
                                    _p(out), _p(act), _stream()), "ptv3_unpool_add")
@@ -198,13 +198,16 @@ def unpool_add(skip, up, inverse, gelu=True, want_skip_act=True):
 
 def ln_residual(x, gamma=None, beta=None, eps=1e-5, residual=None, want_res=True, gamma2=None, beta2=None,
                 out2_dtype=None):
-    """t = LN(x) if gamma is given else x; r = residual + t (or t); returns (r fp32 or None, LN2(r) or None)."""
+    """t = LN(x) if gamma is given else x; r = residual + t (or t).  Returns (r fp32 or None, out2 or None) with
+    out2 = LN2(r) if gamma2 is given, else r cast to out2_dtype (when out2_dtype is given)."""
     _need_cuda(x)
     lib = _lib.load()
     x = x.contiguous()
     n, c = x.shape
     res_out = torch.empty((n, c), dtype=torch.float32, device=x.device) if want_res else None
-    out2 = torch.empty((n, c), dtype=out2_dtype, device=x.device) if gamma2 is not None else None
+    if gamma2 is not None and out2_dtype is None:
+        out2_dtype = torch.float32
+    out2 = torch.empty((n, c), dtype=out2_dtype, device=x.device) if out2_dtype is not None else None
     if residual is not None:
         residual = residual.contiguous()
         assert residual.dtype == torch.float32

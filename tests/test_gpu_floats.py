@@ -1,0 +1,236 @@
+"""GPU parity, floating point kernels and the whole forward.
+Tolerances (BASELINE.json north_star): rel-L2 <= 1e-4 for fp32, <= 1e-2 for bf16 against the fp32 oracle /
+frozen reference outputs."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gridsample as G
+from oracle import ops as O
+from oracle import ptv3 as P
+from oracle import serialization as S
+
+pytestmark = pytest.mark.gpu
+
+TOL_F32, TOL_BF16 = 1e-4, 1e-2
+
+
+def rel_l2(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def _scene(seed, r=6000, scale=0.6):
+    from ptv3_b200 import synth
+    coord, feat = synth.pig_scan(r, scale=scale, seed=seed)
+    gs = G.grid_sample(coord, 0.02)
+    iu = gs["idx_unique"]
+    return coord[iu], feat[iu], gs["grid_coord"][iu]
+
+
+def test_segment_csr_and_scatter_mean():
+    from ptv3_b200 import ops, shims
+    torch.manual_seed(0)
+    n, c = 5000, 64
+    src = torch.randn(n, c)
+    cs = torch.cumsum(torch.randint(0, 9, (1500,)), 0).clamp(max=n)
+    ptr = torch.cat([torch.zeros(1, dtype=torch.long), cs, torch.tensor([n])])
+    perm = torch.randperm(n)
+    for red in ("max", "mean", "sum", "min"):
+        ref = O.segment_csr(src[perm], ptr, red)
+        got = ops.segment_csr(src.cuda(), ptr.cuda(), red, gather=perm.cuda())
+        assert rel_l2(got, ref) < 1e-6, red
+        got = shims.segment_csr(src[perm].cuda(), ptr.cuda(), reduce=red)
+        assert rel_l2(got, ref) < 1e-6, red
+    got = ops.segment_csr(src.bfloat16().cuda(), ptr.cuda(), "max", gather=perm.cuda())
+    assert torch.equal(got.float().cpu(), O.segment_csr(src.bfloat16().float()[perm], ptr, "max"))
+    # coordinates: c == 3 goes through the generic kernel
+    xyz = torch.randn(n, 3)
+    assert rel_l2(ops.segment_csr(xyz.cuda(), ptr.cuda(), "mean", gather=perm.cuda()),
+                  O.segment_csr(xyz[perm], ptr, "mean")) < 1e-6
+    # long segments (per-scene mean pool, keypoint_ptv3.py:44)
+    batch = torch.sort(torch.randint(0, 3, (n,)))[0]
+    assert rel_l2(shims.scatter_mean(src.cuda(), batch.cuda(), dim=0), O.scatter_mean(src, batch)) < 1e-5
+
+
+def test_unpool_add_and_ln_residual():
+    from ptv3_b200 import ops
+    import torch.nn.functional as F
+    torch.manual_seed(1)
+    n, m, c = 4000, 900, 64
+    skip, up = torch.randn(n, c), torch.randn(m, c)
+    inv = torch.randint(0, m, (n,))
+    out, act = ops.unpool_add(skip.cuda(), up.cuda(), inv.cuda(), gelu=True)
+    assert rel_l2(act, F.gelu(skip)) < 1e-6
+    assert rel_l2(out, F.gelu(skip) + F.gelu(up)[inv]) < 1e-6
+    out, act = ops.unpool_add(skip.bfloat16().cuda(), up.bfloat16().cuda(), inv.cuda(), gelu=True)
+    assert out.dtype == torch.float32 and act.dtype == torch.bfloat16
+    assert rel_l2(out, F.gelu(skip.bfloat16().float()) + F.gelu(up.bfloat16().float())[inv]) < 1e-5
+    for c in (32, 64, 128, 256, 512, 96):
+        x, res = torch.randn(777, c) * 3 + 1, torch.randn(777, c)
+        g1, b1, g2, b2 = (torch.randn(c) for _ in range(4))
+        r_ref = res + F.layer_norm(x, (c,), g1, b1, 1e-5)
+        o_ref = F.layer_norm(r_ref, (c,), g2, b2, 1e-5)
+        r, o = ops.ln_residual(x.cuda(), g1.cuda(), b1.cuda(), 1e-5, residual=res.cuda(), gamma2=g2.cuda(),
+                               beta2=b2.cuda(), out2_dtype=torch.float32)
+        assert rel_l2(r, r_ref) < 1e-5 and rel_l2(o, o_ref) < 1e-5, c
+        r, o = ops.ln_residual(x.cuda(), None, None, 1e-5, residual=res.cuda(), out2_dtype=torch.bfloat16)
+        assert rel_l2(r, res + x) < 1e-6 and rel_l2(o, (res + x).bfloat16()) < 1e-6, c
+        r, o = ops.ln_residual(x.bfloat16().cuda(), g1.cuda(), b1.cuda(), 1e-5, want_res=False, gamma2=None,
+                               out2_dtype=torch.bfloat16)
+        assert r is None and rel_l2(o, F.layer_norm(x.bfloat16().float(), (c,), g1, b1, 1e-5)) < 5e-3, c
+
+
+@pytest.mark.parametrize("k,cin,cout", [(3, 32, 32), (3, 64, 64), (3, 48, 80), (5, 4, 32), (5, 6, 48), (3, 128, 128)])
+def test_subm_conv_vs_oracle(k, cin, cout):
+    from ptv3_b200 import ops
+    torch.manual_seed(k * 100 + cin)
+    _, _, grid = _scene(21, r=4000, scale=0.5)
+    idx = torch.from_numpy(np.concatenate([np.zeros((len(grid), 1), np.int64), grid], 1).astype(np.int32))
+    n = idx.shape[0]
+    feat = torch.randn(n, cin)
+    w = torch.randn(cout, k, k, k, cin) / (cin * k ** 3) ** 0.5
+    bias = torch.randn(cout)
+    nbr_ref = O.subm_neighbor_table(idx, k)
+    ref = O.subm_conv(feat, nbr_ref, w, bias)
+    nbr = ops.subm_build_map(idx.cuda(), k)
+    wk = w.reshape(cout, k ** 3, cin).permute(1, 0, 2).contiguous()
+    got = ops.subm_conv(feat.cuda(), wk.cuda(), bias.cuda(), nbr, algo=1)
+    assert rel_l2(got, ref) < TOL_F32
+    got = ops.subm_conv(feat.bfloat16().cuda(), wk.bfloat16().cuda(), bias.cuda(), nbr, algo=1)
+    assert rel_l2(got, ref) < TOL_BF16
+    got = ops.subm_conv(feat.bfloat16().cuda(), wk.bfloat16().cuda(), bias.cuda(), nbr, algo=0)
+    assert rel_l2(got, ref) < TOL_BF16
+
+
+def test_attention_golden(golden):
+    """Reference SerializedAttention.forward (dense branch, one scene) frozen in tests/golden/attention.npz."""
+    from ptv3_b200 import ops
+    g = golden("attention")
+    qkv = torch.from_numpy(g["qkv"]).cuda()
+    order = torch.from_numpy(g["order"]).cuda()
+    off = torch.from_numpy(g["offset"]).cuda()
+    H, K = int(g["H"]), int(g["K"])
+    w, nw = ops.build_windows(off, K, qkv.shape[0])
+    ref = torch.from_numpy(g["out"])
+    pw, pb = torch.from_numpy(g["proj_w"]).cuda(), torch.from_numpy(g["proj_b"]).cuda()
+    a = ops.attn_window(qkv, order, w, nw, H, K, algo=1)
+    assert rel_l2(a @ pw.t() + pb, ref) < TOL_F32
+    a = ops.attn_window(qkv.bfloat16(), order, w, nw, H, K, algo=1)
+    assert rel_l2(a.float() @ pw.t() + pb, ref) < TOL_BF16
+    a = ops.attn_window(qkv.bfloat16(), order, w, nw, H, K, algo=2)
+    assert rel_l2(a.float() @ pw.t() + pb, ref) < TOL_BF16
+
+
+@pytest.mark.parametrize("counts,K,H", [([5], 16, 1), ([1024], 1024, 2), ([1025], 1024, 2), ([700, 2300, 64, 1100], 1024, 4),
+                                        ([300, 17, 129], 128, 32), ([3000], 1024, 3)])
+def test_attention_ragged_vs_oracle(counts, K, H):
+    """Ragged scenes: short windows, the overlapping last window, several heads; all three kernels."""
+    from ptv3_b200 import ops, shims
+    torch.manual_seed(sum(counts) + K)
+    n, C = sum(counts), H * 16
+    qkv = torch.randn(n, 3 * C) * 1.5
+    offset = np.cumsum(counts)
+    order = torch.cat([torch.randperm(c) + s for c, s in zip(counts, np.concatenate([[0], offset[:-1]]))])
+    inverse = torch.empty_like(order)
+    inverse[order] = torch.arange(n)
+    ref = O.window_attention(qkv, order, inverse, offset, H, K)
+    w, nw = ops.build_windows(torch.from_numpy(offset).cuda(), K, n)
+    got = ops.attn_window(qkv.cuda(), order.cuda(), w, nw, H, K, algo=1)
+    assert rel_l2(got, ref) < TOL_F32
+    qb = qkv.bfloat16()
+    refb = O.window_attention(qb.float(), order, inverse, offset, H, K)
+    for algo in (1, 2):
+        got = ops.attn_window(qb.cuda(), order.cuda(), w, nw, H, K, algo=algo)
+        assert rel_l2(got, refb) < 6e-3, algo       # bf16 P and bf16 output rounding
+    # flash_attn call surface (:208-215): padded layout + cu_seqlens, identity order
+    pad, unpad, cu = O.padding_and_inverse(offset, K)
+    g = qb[order[torch.from_numpy(pad)]].reshape(-1, 3, H, 16).cuda()
+    out = shims.flash_attn_varlen_qkvpacked_func(g, torch.from_numpy(cu).cuda(), max_seqlen=K, dropout_p=0.0,
+                                                 softmax_scale=16 ** -0.5)
+    out = out.reshape(-1, C)[torch.from_numpy(unpad).cuda()[inverse.cuda()]]
+    assert rel_l2(out, refb) < 6e-3
+
+
+def _weights():
+    from conftest import GOLDEN
+    from ptv3_b200 import synth
+    with open(os.path.join(GOLDEN, "param_shapes.json")) as f:
+        shapes = json.load(f)
+    return {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+
+
+def _model(dtype):
+    from ptv3_b200 import model as M
+    m = M.OffsetKeypointPTv3(backbone_conf=dict(P.BASE_CFG, compute_dtype=dtype)).eval()
+    missing, unexpected = m.load_state_dict(_weights(), strict=False)
+    assert not unexpected and all(k.endswith("num_batches_tracked") for k in missing)
+    return m.cuda()
+
+
+def _hooks(m, feats):
+    bb = m.backbone
+    for name, mod in (("stem", bb.embedding), ("enc0", bb.enc.enc0), ("pool1", bb.enc.enc1.down),
+                      ("enc4", bb.enc.enc4), ("dec3", bb.dec.dec3)):
+        mod.register_forward_hook(lambda _m, _i, o, name=name: feats.__setitem__(name, o.feat.detach().clone()))
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_forward_golden(golden, dtype, tol):
+    """Whole OffsetKeypointPTv3 forward against the UNMODIFIED reference's frozen outputs (tests/golden/forward.npz),
+    same weights, same torch.randperm draws (5 per forward, CPU generator)."""
+    g = golden("forward")
+    m = _model(dtype)
+    feats = {}
+    _hooks(m, feats)
+    for i in range(int(g["n_scenes"])):
+        n = len(g[f"coord_{i}"])
+        torch.manual_seed(100 + i)
+        out = m(dict(coord=torch.from_numpy(g[f"coord_{i}"]).cuda(), grid_coord=torch.from_numpy(g[f"grid_coord_{i}"]).cuda(),
+                     feat=torch.from_numpy(g[f"feat_{i}"]).cuda(), offset=torch.tensor([n]).cuda(), grid_size=0.02))
+        for k in ("stem", "enc0", "pool1", "enc4", "dec3"):
+            assert rel_l2(feats[k], torch.from_numpy(g[f"{k}_{i}"])) < tol, (i, k)
+        ref = torch.from_numpy(g[f"pred_{i}"])
+        assert rel_l2(out["pred"], ref) < tol, i
+        # keypoint positions (tools/infer_offset.py:366-399), 1 mm at the reference scale of 874 mm / unit
+        coord = torch.from_numpy(g[f"coord_{i}"])
+        kp_ref = P.aggregate_keypoints(coord, ref, mode="weighted")
+        kp = P.aggregate_keypoints(coord, out["pred"].float().cpu(), mode="weighted")
+        err_mm = (kp - kp_ref).norm(dim=1).max().item() * 873.69
+        assert err_mm < (1.0 if dtype == torch.float32 else 10.0), err_mm
+
+
+def test_forward_batched_equals_per_scene():
+    """Scenes are independent units: a batch of 3 equals 3 single-scene forwards."""
+    m = _model(torch.float32)
+    m.backbone.shuffle_orders = False
+    for mod in m.backbone.modules():
+        if hasattr(mod, "shuffle_orders"):
+            mod.shuffle_orders = False
+    scenes = [_scene(31, 7000, 0.7), _scene(32, 1500, 0.3), _scene(33, 4000, 0.5)]
+    singles = []
+    for c, f, gcoord in scenes:
+        singles.append(m(dict(coord=torch.from_numpy(c).cuda(), grid_coord=torch.from_numpy(gcoord).cuda(),
+                              feat=torch.from_numpy(f).cuda(), offset=torch.tensor([len(c)]).cuda()))["pred"])
+    cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
+    offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
+    batched = m(dict(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset))["pred"]
+    assert rel_l2(batched, torch.cat(singles)) < 1e-5
+
+
+def test_forward_vs_oracle_fresh_scene():
+    """A scene that is NOT in the golden set, against the oracle restatement run here on the CPU."""
+    m = _model(torch.float32)
+    W = _weights()
+    c, f, gcoord = _scene(41, 5000, 0.55)
+    torch.manual_seed(7)
+    perms = [torch.randperm(4).numpy() for _ in range(5)]
+    pt = P.backbone_forward(W, c, gcoord, f, [len(c)], perms=list(perms))
+    ref = P.offset_head(W, pt.feat)
+    torch.manual_seed(7)
+    out = m(dict(coord=torch.from_numpy(c).cuda(), grid_coord=torch.from_numpy(gcoord).cuda(),
+                 feat=torch.from_numpy(f).cuda(), offset=torch.tensor([len(c)]).cuda()))["pred"]
+    assert rel_l2(out, ref) < TOL_F32
