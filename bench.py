@@ -1,0 +1,355 @@
+"""bench.py -- PTv3 (PT-v3m1 + offset-keypoint head) forward throughput on B200.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (CUDA kernels through the C ABI)
+  python bench.py --impl reference --gpus N ...             the reference's CPU path (oracle port) on the host cores
+
+Workload (BASELINE.json configs[1]): 16 synthetic 100k-point pig scans per GPU (SURVEY.md 8d generator, scale 4.1,
+GridSample 0.02 m -> ~72.9k voxels per scene), bf16 inference, keypoint-offset head.  A "step" is one forward of
+the batch.  `value` = input voxels / s with inputs resident in HBM; `e2e` = the same through the public call with
+pinned HOST inputs (H2D inside the timed region) and a D2H read of the per-scene keypoints.  One JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+if REPO not in sys.path:
+    sys.path.insert(0, REPO)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+CFG = dict(in_channels=4, order=("z", "z-trans", "hilbert", "hilbert-trans"), stride=(2, 2, 2, 2),
+           enc_depths=(2, 2, 2, 6, 2), enc_channels=(32, 64, 128, 256, 512), enc_num_head=(2, 4, 8, 16, 32),
+           enc_patch_size=(1024,) * 5, dec_depths=(2, 2, 2, 2), dec_channels=(64, 64, 128, 256),
+           dec_num_head=(4, 4, 8, 16), dec_patch_size=(1024,) * 4, shuffle_orders=True)
+GRID = 0.02
+METRIC = "ptv3_forward_voxels_per_sec"
+UNIT = "voxels/s"
+
+
+def peaks():
+    try:
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=p["hbm_gbs"], tf_burst=p["bf16_tflops"], tf_sust=p["bf16_tflops_sustained"], src="measured")
+    except Exception:
+        return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def make_raw_scenes(n_scenes, points, scale, seed0, in_channels=4):
+    from ptv3_b200 import synth
+    return [synth.pig_scan(points, scale=scale, seed=seed0 + i, in_channels=in_channels) for i in range(n_scenes)]
+
+
+def build_model(dtype, device):
+    from ptv3_b200 import model as M, synth
+    m = M.OffsetKeypointPTv3(backbone_conf=dict(CFG, compute_dtype=dtype)).eval()
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    m.load_state_dict(W, strict=False)
+    return m.to(device), W
+
+
+def voxelize_on_device(raw, device):
+    """GridSample (our CUDA kernel, first point per voxel) per scene -> host numpy batch dict."""
+    from ptv3_b200 import ops
+    coords, feats, grids, counts = [], [], [], []
+    for coord, feat in raw:
+        c = torch.from_numpy(coord).to(device)
+        r = ops.gridsample(c, GRID, "fnv")
+        iu = r["idx_unique"]
+        coords.append(c[iu].cpu())
+        feats.append(torch.from_numpy(feat).to(device)[iu].cpu())
+        grids.append(r["grid_coord"][iu].cpu())
+        counts.append(int(iu.numel()))
+    return dict(coord=torch.cat(coords), feat=torch.cat(feats), grid_coord=torch.cat(grids),
+                offset=torch.tensor(np.cumsum(counts), dtype=torch.int64)), counts
+
+
+def attn_flops(rec_meta):
+    """Algorithmic FLOPs of one window-attention launch: 4 * C * sum_w q_len * k_len (QK^T + PV)."""
+    w = rec_meta["windows"][: int(rec_meta["n_windows"].item())].cpu().numpy()
+    pairs = float((w[:, 1] * w[:, 3]).sum())
+    return 4.0 * rec_meta["h"] * rec_meta["d"] * pairs, pairs * rec_meta["h"]
+
+
+def conv_flops(rec_meta):
+    """Algorithmic FLOPs of one submanifold conv launch: 2 * Cin * Cout * (number of present neighbours)."""
+    present = float((rec_meta["nbr"] >= 0).sum().item())
+    return 2.0 * rec_meta["cin"] * rec_meta["cout"] * present, present
+
+
+def run_ours(args):
+    from ptv3_b200 import _lib, ops
+    from ptv3_b200.model import aggregate_keypoints
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    model, _ = build_model(dtype, device)
+
+    raw = make_raw_scenes(args.scenes, args.points, args.scale, seed0=1000 * rank)
+    host, counts = voxelize_on_device(raw, device)
+    n_vox = int(sum(counts))
+    pinned = {k: v.pin_memory() for k, v in host.items()}
+    resident = {k: v.to(device) for k, v in host.items()}
+    h2d_bytes = int(sum(v.numel() * v.element_size() for v in pinned.values()))
+
+    def step_resident():
+        return model(dict(resident))["pred"]
+
+    def step_e2e():
+        d = {k: v.to(device, non_blocking=True) for k, v in pinned.items()}
+        pred = model(d)["pred"]
+        kp = aggregate_keypoints(d["coord"], pred, d["offset"])            # (scenes, 6, 3) on device
+        return kp.cpu()                                                   # D2H read of the step's result
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        a.record()
+        for _ in range(steps):
+            out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        barrier()
+        ms = max(a.elapsed_time(b), 0.0)
+        t = torch.tensor([ms, wall], device=device, dtype=torch.float64)
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1]), out
+
+    torch.manual_seed(0)
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = _lib.launch_count()
+    ms, _, _ = timed(step_resident, args.steps)
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop()
+    for _ in range(2):
+        step_e2e()
+    _, e2e_wall, kp = timed(step_e2e, args.steps)
+    d2h_bytes = int(kp.numel() * kp.element_size())
+
+    total_vox = torch.tensor([n_vox], device=device, dtype=torch.float64)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(total_vox)
+    total_vox = float(total_vox.item())
+    value = total_vox * args.steps / (ms * 1e-3)
+    e2e = total_vox * args.steps / (e2e_wall * 1e-3)
+
+    # ---- roofline leg: per-op CUDA events over instrumented steps (rank 0) -------------------------------
+    roof, ops_ms = None, {}
+    if rank == 0:
+        pk = peaks()
+        ops.profile_start()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step_resident()
+        b.record()
+        recs = ops.profile_stop()
+        step_ms = a.elapsed_time(b)
+        tot = {}
+        for name, t, meta in recs:
+            fl, units = attn_flops(meta) if name == "attn_window" else conv_flops(meta)
+            e = tot.setdefault(name, dict(ms=0.0, flops=0.0, units=0.0, launches=0))
+            e["ms"] += t
+            e["flops"] += fl
+            e["units"] += units
+            e["launches"] += 1
+        ops_ms = {k: round(v["ms"], 3) for k, v in tot.items()}
+        ops_ms["step_instrumented"] = round(step_ms, 3)
+        top = max(tot, key=lambda k: tot[k]["ms"])
+        e = tot[top]
+        ach = e["flops"] / (e["ms"] * 1e-3) / 1e12
+        roof = dict(kernel=top, bound="tensor", achieved=round(ach, 2), peak=pk["tf_sust"], unit="TFLOP/s",
+                    frac=round(ach / pk["tf_sust"], 4), traffic=None, peak_source=pk["src"] + " (sustained bf16 GEMM)",
+                    launches_per_step=e["launches"], ms_per_step=round(e["ms"], 3),
+                    share_of_step=round(e["ms"] / step_ms, 3))
+        if top == "attn_window":   # head_dim 16: the exp pipe, not the tensor pipe, bounds this kernel
+            roof["exp_per_s"] = round(e["units"] / (e["ms"] * 1e-3) / 1e12, 3)
+            roof["exp_peak_mufu_per_s"] = round(16 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 3)
+    cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(args, seconds=20.0)
+
+    if rank == 0:
+        line = dict(metric=METRIC, value=round(value, 1), unit=UNIT, n_gpus=world, steps=args.steps,
+                    warmup=max(args.warmup, 3), ms_per_step=round(ms / args.steps, 3), higher_is_better=True,
+                    scaling="weak", vs_baseline=None, dtype=args.dtype, data="synthetic",
+                    config=dict(workload=f"PTv3-v1m1 + offset-keypoint head forward, {args.scenes} scenes x "
+                                         f"{args.points} raw pts (scale {args.scale}, grid {GRID} m) per GPU",
+                                voxels_per_gpu=n_vox, scenes_per_gpu=args.scenes, raw_points_per_scene=args.points,
+                                patch=1024, parallelism=f"scene-sharded x{world} (no collective in forward)",
+                                l2="per-step working set (qkv 224 MB at stage 0) exceeds the 126 MB L2"),
+                    e2e=dict(value=round(e2e, 1), unit=UNIT, h2d_bytes_per_step=h2d_bytes,
+                             d2h_bytes_per_step=d2h_bytes, ms_per_step=round(e2e_wall / args.steps, 3),
+                             result="per-scene keypoints (scenes,6,3) fp32 after on-device aggregation"),
+                    gpu_launches=int(launches), clocks=clocks, roofline=roof, cpu_baseline=cpu, op_ms=ops_ms)
+        print(json.dumps(line))
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+def cpu_sample_scene(args, seconds, steps=1):
+    """One scene of the same workload, scaled so that `steps` oracle forwards take about `seconds` on this host."""
+    from oracle import gridsample as G
+    from ptv3_b200 import synth
+    cores = os.cpu_count() or 1
+    est_rate = 9000.0 * max(1.0, (cores / 8.0) ** 0.5)          # voxels/s, indicative
+    target = min(72900.0, max(4000.0, est_rate * seconds / steps))
+    scale = args.scale * (target / 72900.0) ** 0.5
+    coord, feat = synth.pig_scan(args.points, scale=scale, seed=0)
+    gs = G.grid_sample(coord, GRID)
+    iu = gs["idx_unique"]
+    return coord[iu], feat[iu], gs["grid_coord"][iu], scale
+
+
+def cpu_forward(W, scene):
+    from oracle import ptv3 as P
+    c, f, g, _ = scene
+    perms = [torch.randperm(4).numpy() for _ in range(5)]
+    pt = P.backbone_forward(W, c, g, f, [len(c)], cfg=dict(CFG), perms=perms)
+    return P.offset_head(W, pt.feat)
+
+
+def cpu_baseline(args, seconds=20.0):
+    """The oracle port of the reference forward (fp32, dense-branch attention, restated spconv) on the host cores."""
+    from ptv3_b200 import model as M, synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    m = M.OffsetKeypointPTv3(backbone_conf=dict(CFG))
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    scene = cpu_sample_scene(args, seconds)
+    t0 = time.perf_counter()
+    cpu_forward(W, scene)
+    dt = time.perf_counter() - t0
+    n = len(scene[0])
+    return dict(value=round(n / dt, 1), unit=UNIT, cores=cores, kind="port",
+                sample=f"1 scene of the workload at scale {scene[3]:.2f} -> {n} voxels, 1 forward, fp32, {dt:.1f} s")
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; the reference itself is Python that cannot travel to
+    the GPU box) timed on all host cores; each step = one bounded-sample scene forward."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from ptv3_b200 import model as M, synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    m = M.OffsetKeypointPTv3(backbone_conf=dict(CFG))
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    total = args.steps + args.warmup
+    scene = cpu_sample_scene(args, seconds=150.0, steps=total)
+    n = len(scene[0])
+    torch.manual_seed(0)
+    for _ in range(args.warmup):
+        cpu_forward(W, scene)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_forward(W, scene)
+    dt = time.perf_counter() - t0
+    v = n * args.steps / dt
+    sample = f"1 scene per step at scale {scene[3]:.2f} -> {n} voxels (of the {args.scenes}-scene batch), fp32"
+    line = dict(impl="reference", metric=METRIC, value=round(v, 1), unit=UNIT, n_gpus=int(os.environ.get("WORLD_SIZE", "1")),
+                steps=args.steps, warmup=args.warmup, ms_per_step=round(dt / args.steps * 1e3, 3),
+                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload=f"PTv3-v1m1 + offset-keypoint head forward on the host CPU (oracle port of the "
+                                     f"reference, enable_flash=False semantics, restated spconv), {sample}"),
+                cpu_baseline=dict(value=round(v, 1), unit=UNIT, cores=cores, kind="port", sample=sample),
+                e2e=dict(value=round(v, 1), unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                gpu_launches=0)
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--scenes", type=int, default=16)
+    ap.add_argument("--points", type=int, default=100000)
+    ap.add_argument("--scale", type=float, default=4.1)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

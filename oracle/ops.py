@@ -110,16 +110,13 @@ def subm_neighbor_table(indices, ksize):
     OFF = 1 << 10                                   # bias so shifted coords stay >= 0
     key = _pack_key(idx[:, 0], idx[:, 1:] + OFF)
     skey, sidx = torch.sort(key)
-    nbr = torch.full((N, ksize ** 3), -1, dtype=torch.int64)
-    kk = 0
-    for dx in range(-r, r + 1):
-        for dy in range(-r, r + 1):
-            for dz in range(-r, r + 1):
-                q = _pack_key(idx[:, 0], idx[:, 1:] + OFF + torch.tensor([dx, dy, dz]))
-                pos = torch.searchsorted(skey, q).clamp_(max=N - 1)
-                hit = skey[pos] == q
-                nbr[hit, kk] = sidx[pos[hit]]
-                kk += 1
+    rng = torch.arange(-r, r + 1)
+    delta = torch.stack(torch.meshgrid(rng, rng, rng, indexing="ij"), -1).reshape(-1, 3)      # (k^3, 3), dz fastest
+    dkey = (delta[:, 0].to(torch.int64) << (2 * 21)) + (delta[:, 1].to(torch.int64) << 21) + delta[:, 2].to(torch.int64)
+    q = (key[:, None] + dkey[None, :]).reshape(-1)          # packed keys add component-wise (bias keeps fields >= 0)
+    pos = torch.searchsorted(skey, q).clamp_(max=N - 1)
+    hit = skey[pos] == q
+    nbr = torch.where(hit, sidx[pos], torch.full_like(pos, -1)).reshape(N, ksize ** 3)
     return nbr
 
 

@@ -306,7 +306,9 @@ size_t ptv3_argsort_rows_workspace(int64_t rows, int64_t n) { return radix_argso
 
 int ptv3_argsort_rows(const int64_t* code, int64_t rows, int64_t n, int key_bits, int64_t* order, int64_t* inverse,
                       void* workspace, size_t workspace_bytes, void* stream) {
-  if (rows < 0 || n < 0 || !order) return PTV3_EINVAL;
+  if (rows < 0 || n < 0) return PTV3_EINVAL;
+  if (rows == 0 || n == 0) return PTV3_OK;
+  if (!order || !code) return PTV3_EINVAL;
   return radix_argsort_rows((const uint64_t*)code, rows, n, key_bits, order, inverse, nullptr, workspace,
                             workspace_bytes, as_stream(stream));
 }

@@ -37,6 +37,41 @@ def _dt(t):
     raise RuntimeError(f"unsupported dtype {t.dtype} (float32 / bfloat16 only)")
 
 
+# ---- optional per-op CUDA-event timing (bench.py's roofline leg); off by default -------------------------
+_PROF = None
+
+
+def profile_start():
+    global _PROF
+    _PROF = []
+
+
+def profile_stop():
+    """Returns [(name, ms, meta)] for every op launched since profile_start(); synchronises."""
+    global _PROF
+    rec, _PROF = _PROF or [], None
+    torch.cuda.synchronize()
+    return [(name, a.elapsed_time(b), meta) for name, a, b, meta in rec]
+
+
+class _timed:
+    def __init__(self, name, **meta):
+        self.name, self.meta = name, meta
+
+    def __enter__(self):
+        if _PROF is not None:
+            self.a = torch.cuda.Event(enable_timing=True)
+            self.a.record()
+        return self
+
+    def __exit__(self, *exc):
+        if _PROF is not None:
+            b = torch.cuda.Event(enable_timing=True)
+            b.record()
+            _PROF.append((self.name, self.a, b, self.meta))
+        return False
+
+
 def _ws(nbytes, device):
     return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
 
@@ -244,8 +279,9 @@ def subm_conv(feat, weight_koc, bias, nbr, algo=0):
     dt = _dt(feat)
     ws = _ws(lib.ptv3_subm_conv_workspace(n, cin, cout, k3, dt, algo), feat.device)
     b = bias.contiguous().float() if bias is not None else None
-    _lib.check(lib.ptv3_subm_conv(_p(feat), _p(weight_koc), _p(b), _p(nbr.contiguous()), n, cin, cout, k3, dt,
-                                  int(algo), _p(out), _p(ws), ws.numel(), _stream()), "ptv3_subm_conv")
+    with _timed("subm_conv", n=n, cin=cin, cout=cout, k3=k3, dtype=dt, nbr=nbr):
+        _lib.check(lib.ptv3_subm_conv(_p(feat), _p(weight_koc), _p(b), _p(nbr.contiguous()), n, cin, cout, k3, dt,
+                                      int(algo), _p(out), _p(ws), ws.numel(), _stream()), "ptv3_subm_conv")
     return out
 
 
@@ -278,7 +314,8 @@ def attn_window(qkv, order, windows, n_windows, num_heads, max_len, scale=None, 
         return out
     scale = float(scale) if scale is not None else d ** -0.5
     o = order.contiguous().long() if order is not None else None
-    _lib.check(lib.ptv3_attn_window_fwd(_p(qkv), _dt(qkv), _p(o), _p(windows), _p(n_windows), windows.shape[0],
-                                        int(max_len), n, h, d, scale, int(algo), _p(out), _stream()),
-               "ptv3_attn_window_fwd")
+    with _timed("attn_window", n=n, h=h, d=d, windows=windows, n_windows=n_windows, dtype=_dt(qkv)):
+        _lib.check(lib.ptv3_attn_window_fwd(_p(qkv), _dt(qkv), _p(o), _p(windows), _p(n_windows), windows.shape[0],
+                                            int(max_len), n, h, d, scale, int(algo), _p(out), _stream()),
+                   "ptv3_attn_window_fwd")
     return out
