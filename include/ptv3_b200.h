@@ -163,6 +163,16 @@ int ptv3_subm_conv(const void* in, const void* weight, const float* bias, const 
                    int c_out, int k3, int dtype, int algo, void* out, void* workspace, size_t workspace_bytes,
                    void* stream);
 
+/* bf16 tensor-core path with the weight packed once (eval: weights are constants).  `packed` is the
+ * shared-memory image of the K-blocked, 128-byte-swizzled weight (ptv3_subm_pack_weight_bytes() bytes, 1024-byte
+ * aligned); supported shapes: c_in == 32 or a multiple of 64 (<= 512), c_out in {32,64,128,256,512}, k3 <= 27. */
+int ptv3_subm_conv_tc_supported(int c_in, int c_out, int k3);
+size_t ptv3_subm_pack_weight_bytes(int c_in, int c_out, int k3);
+int ptv3_subm_pack_weight(const void* weight /* (k3,c_out,c_in) bf16 */, int c_in, int c_out, int k3, void* packed,
+                          void* stream);
+int ptv3_subm_conv_packed(const void* in, const void* packed, const float* bias, const int32_t* nbr, int64_t n,
+                          int c_in, int c_out, int k3, void* out, void* stream);
+
 /* ---------------------------------------------------------------------------
  * A3/A4  serialized window attention.
  * Window records replace get_padding_and_inverse (:115-170): int64 (w,4) =

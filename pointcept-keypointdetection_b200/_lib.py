@@ -37,6 +37,10 @@ SIGNATURES = {
     "ptv3_subm_conv_workspace": (c_sz, [c_i64, c_int, c_int, c_int, c_int, c_int]),
     "ptv3_subm_conv": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_sz,
                                c_vp]),
+    "ptv3_subm_conv_tc_supported": (c_int, [c_int, c_int, c_int]),
+    "ptv3_subm_pack_weight_bytes": (c_sz, [c_int, c_int, c_int]),
+    "ptv3_subm_pack_weight": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_vp]),
+    "ptv3_subm_conv_packed": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_build_windows": (c_int, [c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp]),
     "ptv3_attn_window_fwd": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_f32, c_int,
                                      c_vp, c_vp]),

@@ -220,6 +220,10 @@ size_t subm_conv_tc_workspace(int64_t n, int c_in, int c_out, int k3);
 int subm_conv_tc(const __nv_bfloat16* in, const __nv_bfloat16* w, const float* bias, const int32_t* nbr, int64_t n,
                  int c_in, int c_out, int k3, __nv_bfloat16* out, void* ws, size_t ws_bytes, cudaStream_t st);
 bool subm_conv_tc_supported(int c_in, int c_out, int k3);
+size_t subm_conv_tc_packed_bytes(int c_in, int c_out, int k3);
+int subm_pack_weight_tc(const __nv_bfloat16* w, int c_in, int c_out, int k3, __nv_bfloat16* packed, cudaStream_t st);
+int subm_conv_tc_packed(const __nv_bfloat16* in, const __nv_bfloat16* packed, const float* bias, const int32_t* nbr,
+                        int64_t n, int c_in, int c_out, int k3, __nv_bfloat16* out, cudaStream_t st);
 
 }  // namespace ptv3
 
@@ -279,6 +283,26 @@ int ptv3_subm_conv(const void* in, const void* weight, const float* bias, const 
                                  st);
   }
   return PTV3_EINVAL;
+}
+
+int ptv3_subm_conv_tc_supported(int c_in, int c_out, int k3) { return subm_conv_tc_supported(c_in, c_out, k3) ? 1 : 0; }
+
+size_t ptv3_subm_pack_weight_bytes(int c_in, int c_out, int k3) {
+  return subm_conv_tc_supported(c_in, c_out, k3) ? subm_conv_tc_packed_bytes(c_in, c_out, k3) : 0;
+}
+
+int ptv3_subm_pack_weight(const void* weight, int c_in, int c_out, int k3, void* packed, void* stream) {
+  if (!weight || !packed) return PTV3_EINVAL;
+  return subm_pack_weight_tc((const __nv_bfloat16*)weight, c_in, c_out, k3, (__nv_bfloat16*)packed, as_stream(stream));
+}
+
+int ptv3_subm_conv_packed(const void* in, const void* packed, const float* bias, const int32_t* nbr, int64_t n,
+                          int c_in, int c_out, int k3, void* out, void* stream) {
+  if (n < 0) return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!in || !packed || !nbr || !out) return PTV3_EINVAL;
+  return subm_conv_tc_packed((const __nv_bfloat16*)in, (const __nv_bfloat16*)packed, bias, nbr, n, c_in, c_out, k3,
+                             (__nv_bfloat16*)out, as_stream(stream));
 }
 
 }  // extern "C"

@@ -158,6 +158,13 @@ class SubMConv3d(SparseModule):
 
     def conv(self, features, x, scale=None, shift=None, algo=0):
         w, b = self._weights(features.dtype, scale, shift)
+        k3 = self.kernel_size ** 3
+        if (features.dtype == torch.bfloat16 and algo != 1
+                and ops.subm_conv_tc_supported(self.in_channels, self.out_channels, k3)):
+            # tcgen05 path: the K-blocked / swizzled weight image is built once per parameter version
+            packed = _cached(self, ("packed", scale is not None), [self.weight, self.bias, scale, shift],
+                             lambda: ops.subm_pack_weight(w))
+            return ops.subm_conv_packed(features, packed, b, self.neighbor_map(x), self.out_channels)
         return ops.subm_conv(features, w, b, self.neighbor_map(x), algo=algo)
 
     def forward(self, x):

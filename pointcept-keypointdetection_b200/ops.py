@@ -285,6 +285,41 @@ def subm_conv(feat, weight_koc, bias, nbr, algo=0):
     return out
 
 
+def subm_conv_tc_supported(cin, cout, k3):
+    return bool(_lib.load().ptv3_subm_conv_tc_supported(int(cin), int(cout), int(k3)))
+
+
+def subm_pack_weight(weight_koc):
+    """(k^3, Cout, Cin) bf16 -> the K-blocked, swizzled shared-memory image the tcgen05 conv kernel bulk-copies."""
+    _need_cuda(weight_koc)
+    lib = _lib.load()
+    w = weight_koc.contiguous()
+    assert w.dtype == torch.bfloat16
+    k3, cout, cin = w.shape
+    nbytes = lib.ptv3_subm_pack_weight_bytes(cin, cout, k3)
+    if nbytes == 0:
+        raise RuntimeError(f"subm_pack_weight: unsupported shape cin={cin} cout={cout} k3={k3}")
+    packed = torch.empty(nbytes // 2, dtype=torch.bfloat16, device=w.device)
+    _lib.check(lib.ptv3_subm_pack_weight(_p(w), cin, cout, k3, _p(packed), _stream()), "ptv3_subm_pack_weight")
+    return packed
+
+
+def subm_conv_packed(feat, packed, bias, nbr, cout):
+    """bf16 tcgen05 path with a pre-packed weight (subm_pack_weight)."""
+    _need_cuda(feat, packed, nbr)
+    lib = _lib.load()
+    feat = feat.contiguous()
+    assert feat.dtype == torch.bfloat16 and nbr.dtype == torch.int32
+    n, cin = feat.shape
+    k3 = nbr.shape[1]
+    out = torch.empty((n, cout), dtype=feat.dtype, device=feat.device)
+    b = bias.contiguous().float() if bias is not None else None
+    with _timed("subm_conv", n=n, cin=cin, cout=cout, k3=k3, dtype=BF16, nbr=nbr):
+        _lib.check(lib.ptv3_subm_conv_packed(_p(feat), _p(packed), _p(b), _p(nbr.contiguous()), n, cin, int(cout), k3,
+                                             _p(out), _stream()), "ptv3_subm_conv_packed")
+    return out
+
+
 # ------------------------------------------------------------------ A3/A4 attention
 def build_windows(offset, patch, n_total):
     """Window records (W_max,4) int64 + device count.  W_max = N // patch + n_scenes (upper bound, no sync)."""

@@ -106,6 +106,34 @@ def test_subm_conv_vs_oracle(k, cin, cout):
     assert rel_l2(got, ref) < TOL_BF16
 
 
+@pytest.mark.parametrize("cin,cout", [(32, 32), (64, 64), (128, 128), (256, 256), (512, 512), (32, 64), (64, 32),
+                                      (128, 256), (256, 128)])
+def test_subm_conv_tcgen05_vs_oracle(cin, cout):
+    """bf16 tcgen05 implicit-GEMM kernel (algo 2 and the packed-weight entry) against the fp32 oracle evaluated on
+    the bf16-rounded operands: only the final bf16 rounding of the output differs (rel-L2 <= 4e-3)."""
+    from ptv3_b200 import ops
+    torch.manual_seed(cin * 7 + cout)
+    _, _, grid = _scene(22, r=5000, scale=0.55)
+    idx = torch.from_numpy(np.concatenate([np.zeros((len(grid), 1), np.int64), grid], 1).astype(np.int32))
+    n = idx.shape[0]
+    assert n % 128 != 0          # ragged last tile
+    feat = torch.randn(n, cin).bfloat16()
+    w = (torch.randn(cout, 3, 3, 3, cin) / (cin * 14) ** 0.5).bfloat16()
+    bias = torch.randn(cout)
+    nbr_ref = O.subm_neighbor_table(idx, 3)
+    ref = O.subm_conv(feat.float(), nbr_ref, w.float(), bias)
+    nbr = ops.subm_build_map(idx.cuda(), 3)
+    wk = w.reshape(cout, 27, cin).permute(1, 0, 2).contiguous().cuda()
+    assert ops.subm_conv_tc_supported(cin, cout, 27)
+    got = ops.subm_conv(feat.cuda(), wk, bias.cuda(), nbr, algo=2)
+    assert rel_l2(got, ref) < 4e-3, rel_l2(got, ref)
+    packed = ops.subm_pack_weight(wk)
+    got2 = ops.subm_conv_packed(feat.cuda(), packed, bias.cuda(), nbr, cout)
+    assert torch.equal(got, got2)
+    got3 = ops.subm_conv_packed(feat.cuda(), packed, None, nbr, cout)
+    assert rel_l2(got3, ref - bias) < 4e-3
+
+
 def test_attention_golden(golden):
     """Reference SerializedAttention.forward (dense branch, one scene) frozen in tests/golden/attention.npz."""
     from ptv3_b200 import ops
