@@ -213,6 +213,134 @@ __global__ void __launch_bounds__(256) ln_residual_kernel(const TX* __restrict__
   }
 }
 
+
+// ---- vectorised variant: every thread owns 8 contiguous channels (16 B of bf16 / 32 B of fp32), a row is spread
+// over L = c/8 lanes (VPT = 2: 16 channels per thread for c = 512) and reduced with xor-shuffles inside the warp.
+template <typename T>
+__device__ __forceinline__ void ld8(const T* p, float (&v)[8]);
+template <>
+__device__ __forceinline__ void ld8<float>(const float* p, float (&v)[8]) {
+  float4 a = reinterpret_cast<const float4*>(p)[0], b = reinterpret_cast<const float4*>(p)[1];
+  v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
+template <>
+__device__ __forceinline__ void ld8<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[8]) {
+  uint4 u = *reinterpret_cast<const uint4*>(p);
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = __uint_as_float(w[i] << 16);
+    v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void st8(T* p, const float (&v)[8]);
+template <>
+__device__ __forceinline__ void st8<float>(float* p, const float (&v)[8]) {
+  reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+  reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+template <>
+__device__ __forceinline__ void st8<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[8]) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    w[i] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+template <typename TX, typename TO, int L, int VPT>
+__global__ void __launch_bounds__(256) ln_residual_vec_kernel(const TX* __restrict__ x, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, float eps,
+                                                              const float* __restrict__ residual,
+                                                              float* __restrict__ res_out,
+                                                              const float* __restrict__ gamma2,
+                                                              const float* __restrict__ beta2, TO* __restrict__ out2,
+                                                              int64_t n) {
+  constexpr int C = L * 8 * VPT;
+  constexpr int ROWS_PER_WARP = 32 / L;
+  const int lane = threadIdx.x & 31, sub = lane % L;
+  const int64_t warp_global = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const float inv_c = 1.f / (float)C;
+  for (int64_t row = warp_global * ROWS_PER_WARP + lane / L; row < n; row += warps_total * ROWS_PER_WARP) {
+    float v[VPT][8];
+    float s = 0.f;
+#pragma unroll
+    for (int p = 0; p < VPT; ++p) {
+      ld8<TX>(x + row * C + (p * L + sub) * 8, v[p]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += v[p][i];
+    }
+    if (gamma) {
+#pragma unroll
+      for (int d = L / 2; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+      const float mean = s * inv_c;
+      float q = 0.f;
+#pragma unroll
+      for (int p = 0; p < VPT; ++p)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float d0 = v[p][i] - mean;
+          q += d0 * d0;
+        }
+#pragma unroll
+      for (int d = L / 2; d > 0; d >>= 1) q += __shfl_xor_sync(0xffffffffu, q, d);
+      const float rstd = rsqrtf(q * inv_c + eps);
+#pragma unroll
+      for (int p = 0; p < VPT; ++p) {
+        float g[8], b[8];
+        ld8<float>(gamma + (p * L + sub) * 8, g);
+        ld8<float>(beta + (p * L + sub) * 8, b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[p][i] = (v[p][i] - mean) * rstd * g[i] + b[i];
+      }
+    }
+    float s2 = 0.f;
+#pragma unroll
+    for (int p = 0; p < VPT; ++p) {
+      if (residual) {
+        float r[8];
+        ld8<float>(residual + row * C + (p * L + sub) * 8, r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[p][i] += r[i];
+      }
+      if (res_out) st8<float>(res_out + row * C + (p * L + sub) * 8, v[p]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s2 += v[p][i];
+    }
+    if (out2 == nullptr) continue;
+    if (gamma2) {
+#pragma unroll
+      for (int d = L / 2; d > 0; d >>= 1) s2 += __shfl_xor_sync(0xffffffffu, s2, d);
+      const float mean2 = s2 * inv_c;
+      float q2 = 0.f;
+#pragma unroll
+      for (int p = 0; p < VPT; ++p)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float d0 = v[p][i] - mean2;
+          q2 += d0 * d0;
+        }
+#pragma unroll
+      for (int d = L / 2; d > 0; d >>= 1) q2 += __shfl_xor_sync(0xffffffffu, q2, d);
+      const float rstd2 = rsqrtf(q2 * inv_c + eps);
+#pragma unroll
+      for (int p = 0; p < VPT; ++p) {
+        float g[8], b[8];
+        ld8<float>(gamma2 + (p * L + sub) * 8, g);
+        ld8<float>(beta2 + (p * L + sub) * 8, b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[p][i] = (v[p][i] - mean2) * rstd2 * g[i] + b[i];
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < VPT; ++p) st8<TO>(out2 + row * C + (p * L + sub) * 8, v[p]);
+  }
+}
+
 template <typename T>
 static int seg_dispatch(const T* src, const int64_t* gather, const int64_t* indptr, int64_t m, int64_t c, int reduce,
                         T* out, int64_t hint_rows_per_seg, cudaStream_t st) {
@@ -291,6 +419,33 @@ int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float
   int cap = kNumSMs * 8 * 4;
   if (g > cap) g = cap;
   cudaStream_t st = as_stream(stream);
+  if (c == 32 || c == 64 || c == 128 || c == 256 || c == 512) {
+    // rows are spread over c/8 lanes; enough CTAs for ~8 resident warps of loads per SM sub-partition
+    const int l = c == 512 ? 32 : c / 8;
+    const int64_t rows_per_cta_v = 8 * (32 / l);
+    int gv = (int)cdiv(n, rows_per_cta_v);
+    const int capv = kNumSMs * 8 * 8;
+    if (gv > capv) gv = capv;
+#define LAUNCHVEC(TX, TO, L, VPT)                                                                                  \
+  ln_residual_vec_kernel<TX, TO, L, VPT><<<gv, 256, 0, st>>>((const TX*)x, gamma, beta, eps, residual, res_out, \
+                                                            gamma2, beta2, (TO*)out2, n)
+#define LAUNCHC(TX, TO)                          \
+  do {                                           \
+    if (c == 32) LAUNCHVEC(TX, TO, 4, 1);        \
+    else if (c == 64) LAUNCHVEC(TX, TO, 8, 1);   \
+    else if (c == 128) LAUNCHVEC(TX, TO, 16, 1); \
+    else if (c == 256) LAUNCHVEC(TX, TO, 32, 1); \
+    else LAUNCHVEC(TX, TO, 32, 2);               \
+  } while (0)
+    if (dtype_x == PTV3_F32 && dtype_out2 == PTV3_F32) LAUNCHC(float, float);
+    else if (dtype_x == PTV3_F32 && dtype_out2 == PTV3_BF16) LAUNCHC(float, __nv_bfloat16);
+    else if (dtype_x == PTV3_BF16 && dtype_out2 == PTV3_F32) LAUNCHC(__nv_bfloat16, float);
+    else if (dtype_x == PTV3_BF16 && dtype_out2 == PTV3_BF16) LAUNCHC(__nv_bfloat16, __nv_bfloat16);
+    else return PTV3_EINVAL;
+#undef LAUNCHC
+#undef LAUNCHVEC
+    return check_launch();
+  }
 #define LAUNCHV(TX, TO, V)                                                                                   \
   ln_residual_kernel<TX, TO, V><<<g, 256, 0, st>>>((const TX*)x, gamma, beta, eps, residual, res_out, gamma2, \
                                                    beta2, (TO*)out2, n, c)

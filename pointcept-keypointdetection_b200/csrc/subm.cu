@@ -170,17 +170,25 @@ __global__ void __launch_bounds__(256) subm_conv_rowwarp_kernel(const T* __restr
     for (int kb = 0; kb < k3; kb += 32) {
       int mine = (kb + lane < k3) ? nb[kb + lane] : -1;
       uint32_t present = __ballot_sync(0xffffffffu, mine >= 0);
+      // every lane gathers the features of ITS neighbour (cin <= 8) so the random loads of a row overlap ...
+      float xin[8];
+#pragma unroll
+      for (int ci = 0; ci < 8; ++ci)
+        xin[ci] = (mine >= 0 && ci < cin) ? Elem<T>::load(in + (int64_t)mine * cin + ci) : 0.f;
+      // ... then the occupied offsets are consumed one by one through shuffles
       while (present) {
         int b = __ffs(present) - 1;
         present &= present - 1;
-        int src = __shfl_sync(0xffffffffu, mine, b);
         int k = kb + b;
-        for (int ci = 0; ci < cin; ++ci) {
-          float x = Elem<T>::load(in + (int64_t)src * cin + ci);
 #pragma unroll
-          for (int q = 0; q < CPL; ++q) {
-            int co = q * 32 + lane;
-            if (co < cout) acc[q] = fmaf(x, ws[(k * cin + ci) * cout + co], acc[q]);
+        for (int ci = 0; ci < 8; ++ci) {
+          if (ci < cin) {
+            float x = __shfl_sync(0xffffffffu, xin[ci], b);
+#pragma unroll
+            for (int q = 0; q < CPL; ++q) {
+              int co = q * 32 + lane;
+              if (co < cout) acc[q] = fmaf(x, ws[(k * cin + ci) * cout + co], acc[q]);
+            }
           }
         }
       }

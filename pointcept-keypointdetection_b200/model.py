@@ -520,6 +520,7 @@ class PointTransformerV3(PointModule):
 
     def set_compute_dtype(self, dtype):
         assert dtype in (torch.bfloat16, torch.float32)
+        self.compute_dtype = dtype
         for m in self.modules():
             if hasattr(m, "compute_dtype"):
                 m.compute_dtype = dtype
@@ -575,8 +576,17 @@ class OffsetKeypointPTv3(nn.Module):
             return (lin.weight.float() * s[:, None]).contiguous(), (lin.bias.float() * s + t).contiguous()
         w, b = _cached(self, "head0", [lin.weight, lin.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var],
                        build)
-        h = F.relu(F.linear(feat.float(), w, b), inplace=True)
-        pred = F.linear(h, self.head[3].weight.float(), self.head[3].bias.float()).view(-1, self.num_keypoints, 4)
+        # fp32 parity mode keeps strict fp32 GEMMs; with a bf16 backbone the features already carry bf16 rounding,
+        # so the two head GEMMs use TF32 tensor-core math (fp32 in/out, 10-bit mantissa products, fp32 accumulate)
+        tf32 = getattr(self.backbone, "compute_dtype", torch.float32) != torch.float32
+        prev = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = bool(tf32)
+        try:
+            h = F.relu(F.linear(feat.float(), w, b), inplace=True)
+            pred = F.linear(h, self.head[3].weight.float(), self.head[3].bias.float())
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = prev
+        pred = pred.view(-1, self.num_keypoints, 4)
         pred[..., 3] = torch.sigmoid(pred[..., 3])
         return dict(pred=pred)
 
