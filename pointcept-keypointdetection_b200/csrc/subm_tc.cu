@@ -23,8 +23,7 @@ constexpr int TM = 128;          // output rows per CTA (UMMA M)
 constexpr int KBLK = 64;         // bf16 per K-block (one 128-byte swizzle row)
 constexpr int A_BYTES = TM * KBLK * 2;
 constexpr int MAX_K3 = 27;
-constexpr int PRODUCERS = 128;
-constexpr int LAG = 2;           // cp.async groups in flight per producer thread
+constexpr int PRODUCERS = 256;   // 8 gather warps
 
 static inline int n_kblocks(int c_in, int k3) { return (k3 * c_in + KBLK - 1) / KBLK; }
 static inline int pick_nt(int c_out) { return c_out >= 256 ? 256 : c_out; }
@@ -71,183 +70,253 @@ struct ConvSmem {
   static constexpr int B_BYTES = NT * KBLK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int NBR_OFF = STAGES * STAGE_BYTES;
-  static constexpr int NBR_BYTES = TM * MAX_K3 * 4;
-  static constexpr int LIST_OFF = NBR_OFF + NBR_BYTES;          // kb_list: up to 216 entries (uint16)
-  static constexpr int LIST_BYTES = 512;
-  static constexpr int BAR_OFF = LIST_OFF + LIST_BYTES;          // full[STAGES], empty[STAGES], accum, then misc
-  static constexpr int TOTAL = BAR_OFF + 256;
+  static constexpr int NBR_BYTES = TM * MAX_K3 * 4;              // one neighbour tile; two buffers
+  static constexpr int MISC_OFF = NBR_OFF + 2 * NBR_BYTES;       // stage flags, masks, tmem pointer
+  static constexpr int BAR_OFF = MISC_OFF + 256;                 // mbarriers
+  static constexpr int TOTAL = BAR_OFF + 8 * (2 * STAGES + 6);
   static constexpr int DYN_BYTES = TOTAL + 1024;                 // slack for the 1024-byte alignment
 };
 
-template <int NT, int STAGES>
-__global__ void __launch_bounds__(160) subm_conv_tc_kernel(const __nv_bfloat16* __restrict__ in,
-                                                           const __nv_bfloat16* __restrict__ packed,
-                                                           const float* __restrict__ bias,
-                                                           const int32_t* __restrict__ nbr, int64_t n, int c_in,
-                                                           int c_out, int k3, int n_kb_total,
-                                                           __nv_bfloat16* __restrict__ out) {
+constexpr int kConvThreads = 416;  // warps 0-7 producers, warp 8 MMA issuer, warps 9-12 epilogue
+constexpr int kMmaWarp = 8;
+
+__device__ __forceinline__ void producers_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// Persistent: CTA b handles row tiles b, b + gridDim.x, ...  The three roles run decoupled through mbarriers, so the
+// gather of tile i+1 (and the bulk prefetch of its neighbour rows) overlaps the MMAs of tile i and the epilogue of
+// tile i-1 (two accumulators in TMEM).
+template <int NT, int STAGES, int LAG>
+__global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __nv_bfloat16* __restrict__ in,
+                                                                       const __nv_bfloat16* __restrict__ packed,
+                                                                       const float* __restrict__ bias,
+                                                                       const int32_t* __restrict__ nbr, int64_t n,
+                                                                       int c_in, int c_out, int k3, int n_kb_total,
+                                                                       int n_tiles, __nv_bfloat16* __restrict__ out) {
   using L = ConvSmem<NT, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t s_base = smem_u32(smem);
-  int32_t* nbr_s = reinterpret_cast<int32_t*>(smem + L::NBR_OFF);
-  uint16_t* kb_list = reinterpret_cast<uint16_t*>(smem + L::LIST_OFF);
+  uint32_t* stage_flag = reinterpret_cast<uint32_t*>(smem + L::MISC_OFF);        // [STAGES] (<= 8)
+  uint32_t* masks = reinterpret_cast<uint32_t*>(smem + L::MISC_OFF + 64);        // [4]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::MISC_OFF + 128);
   const uint32_t bar_base = s_base + L::BAR_OFF;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
-  const uint32_t accum_bar = bar_base + 8u * (2 * STAGES);
-  volatile uint32_t* misc = reinterpret_cast<volatile uint32_t*>(smem + L::BAR_OFF + 8 * (2 * STAGES + 1));
-  // misc[0] = tmem base, misc[1] = number of K-blocks in this tile, misc[2..] = per-offset presence flags (27)
+  auto nbr_full = [&](int b) { return bar_base + 8u * (2 * STAGES + b); };
+  auto acc_full = [&](int b) { return bar_base + 8u * (2 * STAGES + 2 + b); };
+  auto acc_free = [&](int b) { return bar_base + 8u * (2 * STAGES + 4 + b); };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int64_t row0 = (int64_t)blockIdx.x * TM;
   const int nt_tile = blockIdx.y;
+  const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-  if (tid < 32) misc[2 + tid] = 0;
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar(s), PRODUCERS);
       mbar_init(empty_bar(s), 1);
     }
-    mbar_init(accum_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(nbr_full(b), 1);
+      mbar_init(acc_full(b), 1);
+      mbar_init(acc_free(b), 128);
+    }
     mbar_fence_init();
+    masks[0] = masks[1] = masks[2] = masks[3] = 0;
   }
-  if (warp == 4) tmem_alloc<NT>(smem_u32((const void*)&misc[0]));
-  __syncthreads();
-
-  // ---- neighbour rows of this tile -> shared memory, per-offset presence flags
-  for (int idx = tid; idx < TM * k3; idx += blockDim.x) {
-    int r = idx / k3, k = idx - r * k3;
-    int64_t row = row0 + r;
-    int v = row < n ? nbr[row * k3 + k] : -1;
-    nbr_s[idx] = v;
-    if (v >= 0) misc[2 + k] = 1;
-  }
+  if (warp == kMmaWarp) tmem_alloc<2 * NT>(smem_u32(tmem_slot));
   fence_before_sync();
   __syncthreads();
   fence_after_sync();
-  if (tid == 0) {
-    int cnt = 0;
-    if (c_in >= KBLK) {
-      const int per = c_in / KBLK;
-      for (int k = 0; k < k3; ++k)
-        if (misc[2 + k])
-          for (int cb = 0; cb < per; ++cb) kb_list[cnt++] = (uint16_t)(k * per + cb);
-    } else {  // c_in == 32: two offsets per K-block
-      for (int kb = 0; kb < n_kb_total; ++kb) {
-        int k0 = 2 * kb, k1 = 2 * kb + 1;
-        if (misc[2 + k0] || (k1 < k3 && misc[2 + k1])) kb_list[cnt++] = (uint16_t)kb;
-      }
-    }
-    misc[1] = (uint32_t)cnt;
-  }
-  __syncthreads();
-  const int n_kb = (int)misc[1];
-  const uint32_t tmem_base = misc[0];
+  const uint32_t tmem_base = *tmem_slot;
 
-  if (warp < 4) {
-    // =========================== producers: gather A, bulk-copy B ===========================
+  if (warp < kMmaWarp) {
+    // =========================== producers ===========================
     const int c = tid & 7, r0 = tid >> 3;
     const char* wtile = reinterpret_cast<const char*>(packed) + (int64_t)nt_tile * n_kb_total * L::B_BYTES;
-    for (int it = 0; it < n_kb; ++it) {
-      const int s = it % STAGES;
-      const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
-      mbar_wait(empty_bar(s), ph ^ 1u);
-      const int kb = kb_list[it];
-      const uint32_t a_s = s_base + s * L::STAGE_BYTES;
+    const uint32_t nbr_tile_bytes = (uint32_t)(TM * k3 * 4);
+    auto tile_full = [&](int i) { return ((int64_t)(blockIdx.x + (int64_t)i * gridDim.x) + 1) * TM <= n; };
+    auto prefetch_nbr = [&](int i) {   // thread 0 only: bulk copy of a full tile's neighbour rows
+      const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
+      mbar_arrive_expect_tx(nbr_full(i & 1), nbr_tile_bytes);
+      bulk_g2s(s_base + L::NBR_OFF + (i & 1) * L::NBR_BYTES, nbr + row0 * k3, nbr_tile_bytes, nbr_full(i & 1));
+    };
+    if (tid == 0 && my_tiles > 0 && tile_full(0)) prefetch_nbr(0);
+    uint32_t g = 0;  // global K-block counter of this CTA
+    for (int i = 0; i < my_tiles; ++i) {
+      const int tb = i & 1;
+      const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
+      int32_t* nbr_s = reinterpret_cast<int32_t*>(smem + L::NBR_OFF + tb * L::NBR_BYTES);
       if (tid == 0) {
-        mbar_expect_tx(full_bar(s), L::B_BYTES);
-        bulk_g2s(a_s + A_BYTES, wtile + (int64_t)kb * L::B_BYTES, L::B_BYTES, full_bar(s));
+        masks[(i + 2) & 3] = 0;
+        if (i + 1 < my_tiles && tile_full(i + 1)) prefetch_nbr(i + 1);   // buffer tb^1 was released by the
+      }                                                                  // producers_sync() that ended tile i-1
+      if (tile_full(i)) {
+        mbar_wait(nbr_full(tb), (uint32_t)(i >> 1) & 1u);
+      } else {  // ragged last tile: plain loads, -1 beyond n
+        for (int idx = tid; idx < TM * k3; idx += PRODUCERS) {
+          const int64_t row = row0 + idx / k3;
+          nbr_s[idx] = row < n ? nbr[row0 * k3 + idx] : -1;
+        }
+        producers_sync();
       }
-      int k, ch;
+      // per-offset presence over the 128 rows of the tile
+      const uint32_t nbr_sa = s_base + L::NBR_OFF + tb * L::NBR_BYTES;
+      if (tid < TM) {
+        uint32_t local = 0;
+        for (int k = 0; k < k3; ++k) local |= (ld_shared_s32(nbr_sa + (uint32_t)(tid * k3 + k) * 4u) >= 0 ? 1u : 0u) << k;
+        local = __reduce_or_sync(0xffffffffu, local);
+        if (lane == 0) atomicOr(&masks[i & 3], local);
+      }
+      producers_sync();
+      const uint32_t mask = masks[i & 3];
+      const int per = c_in >= KBLK ? c_in / KBLK : 1;
+      uint32_t blk_mask;  // bit j = K-block group j is needed (offset j for c_in >= 64, offset pair j for c_in == 32)
       if (c_in >= KBLK) {
-        const int per = c_in / KBLK;
-        k = kb / per;
-        ch = (kb - k * per) * KBLK + c * 8;
+        blk_mask = mask;
       } else {
-        k = 2 * kb + (c >> 2);
-        ch = (c & 3) * 8;
+        blk_mask = 0;
+        for (int kb = 0; kb < n_kb_total; ++kb) blk_mask |= (((mask >> (2 * kb)) & 3u) ? 1u : 0u) << kb;
       }
-      const bool k_ok = k < k3;
+      const int n_kb = __popc(blk_mask) * per;
+      int done = 0;
+      while (blk_mask) {
+        const int j = __ffs(blk_mask) - 1;
+        blk_mask &= blk_mask - 1;
+        for (int cb = 0; cb < per; ++cb, ++g, ++done) {
+          const int s = g % STAGES;
+          const uint32_t ph = (g / STAGES) & 1u;
+          mbar_wait(empty_bar(s), ph ^ 1u);
+          const int kb = j * per + cb;
+          const uint32_t a_s = s_base + s * L::STAGE_BYTES;
+          if (tid == 0) {
+            stage_flag[s] = (done == 0 ? 1u : 0u) | (done == n_kb - 1 ? 2u : 0u) |
+                            ((done == n_kb - 1 && i == my_tiles - 1) ? 4u : 0u);
+            mbar_expect_tx(full_bar(s), L::B_BYTES);
+            bulk_g2s(a_s + A_BYTES, wtile + (int64_t)kb * L::B_BYTES, L::B_BYTES, full_bar(s));
+          }
+          int k, ch;
+          if (c_in >= KBLK) {
+            k = j;
+            ch = cb * KBLK + c * 8;
+          } else {
+            k = 2 * j + (c >> 2);
+            ch = (c & 3) * 8;
+          }
+          const bool k_ok = k < k3;
+          int src[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int r = r0 + 16 * j;
-        const int src = k_ok ? nbr_s[r * k3 + k] : -1;
-        const __nv_bfloat16* g = in + (src >= 0 ? (int64_t)src * c_in + ch : 0);
-        const uint32_t dst = a_s + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4);
-        cp_async16(dst, g, src >= 0 ? 16u : 0u);
+          for (int q = 0; q < 4; ++q)   // four independent shared loads, then the (divergent) copies
+            src[q] = k_ok ? ld_shared_s32(nbr_sa + (uint32_t)((r0 + 32 * q) * k3 + k) * 4u) : -1;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int r = r0 + 32 * q;
+            const uint32_t dst = a_s + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4);
+            if (src[q] >= 0)   // absent neighbours are zeroed with a plain shared store: a zero-size cp.async would
+              cp_async16(dst, in + (int64_t)src[q] * c_in + ch, 16u);   // still send a request for one hot address
+            else
+              st_shared_zero16(dst);
+          }
+          cp_async_commit();
+          if (g >= (uint32_t)LAG) {
+            cp_async_wait<LAG>();
+            fence_proxy_async();
+            mbar_arrive(full_bar((g - LAG) % STAGES));
+          }
+        }
       }
-      cp_async_commit();
-      if (it >= LAG) {
-        cp_async_wait<LAG>();
-        fence_proxy_async();
-        mbar_arrive(full_bar((it - LAG) % STAGES));
-      }
+      producers_sync();   // everyone is done reading nbr_s[tb]: it may be refilled for tile i+2
     }
     cp_async_wait<0>();
     fence_proxy_async();
-    for (int it = (n_kb > LAG ? n_kb - LAG : 0); it < n_kb; ++it) mbar_arrive(full_bar(it % STAGES));
-
-    // =========================== epilogue: TMEM -> bf16 rows ===========================
-    mbar_wait(accum_bar, 0);
-    fence_after_sync();
-    const int r = warp * 32 + lane;
-    const int64_t row = row0 + r;
-#pragma unroll 1
-    for (int cb = 0; cb < NT; cb += 32) {
-      uint32_t v[32];
-      tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)cb, v);
-      tmem_ld_wait();
-      if (row < n) {
-        const int co0 = nt_tile * NT + cb;
-        uint32_t pk[16];
-#pragma unroll
-        for (int q = 0; q < 16; ++q) {
-          float a = __uint_as_float(v[2 * q]) + (bias ? bias[co0 + 2 * q] : 0.f);
-          float b = __uint_as_float(v[2 * q + 1]) + (bias ? bias[co0 + 2 * q + 1] : 0.f);
-          __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-          pk[q] = *reinterpret_cast<uint32_t*>(&h);
+    for (uint32_t q = (g > (uint32_t)LAG ? g - LAG : 0); q < g; ++q) mbar_arrive(full_bar(q % STAGES));
+  } else if (warp == kMmaWarp) {
+    // =========================== MMA issuer (one thread) ===========================
+    if (lane == 0 && my_tiles > 0) {
+      constexpr uint32_t idesc = idesc_bf16_f32(TM, NT);
+      uint32_t g = 0, t = 0;
+      while (true) {
+        const int s = g % STAGES;
+        mbar_wait(full_bar(s), (g / STAGES) & 1u);
+        fence_after_sync();
+        const uint32_t flag = stage_flag[s];
+        const uint32_t ab = t & 1u;
+        if (flag & 1u) {   // first K-block of a tile: its accumulator must have been drained by the epilogue
+          mbar_wait(acc_free(ab), ((t >> 1) & 1u) ^ 1u);
+          fence_after_sync();
         }
-        uint4* dst = reinterpret_cast<uint4*>(out + row * c_out + co0);
+        const uint32_t a_s = s_base + s * L::STAGE_BYTES;
+        const uint64_t a_desc = smem_desc_sw128(a_s);
+        const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) dst[q] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        for (int kk = 0; kk < KBLK / 16; ++kk)
+          mma_bf16_ss(tmem_base + ab * NT, a_desc + 2 * kk, b_desc + 2 * kk, idesc, ((flag & 1u) && kk == 0) ? 0u : 1u);
+        mma_commit(empty_bar(s));
+        if (flag & 2u) {
+          mma_commit(acc_full(ab));
+          ++t;
+        }
+        ++g;
+        if (flag & 4u) break;
       }
     }
-  } else if (lane == 0) {
-    // =========================== MMA issuer (one thread) ===========================
-    constexpr uint32_t idesc = idesc_bf16_f32(TM, NT);
-    for (int it = 0; it < n_kb; ++it) {
-      const int s = it % STAGES;
-      const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
-      mbar_wait(full_bar(s), ph);
+  } else {
+    // =========================== epilogue: TMEM -> +bias -> bf16 rows ===========================
+    const int q4 = warp & 3;   // TMEM lane quarter this warp may access
+    for (int i = 0; i < my_tiles; ++i) {
+      const uint32_t ab = (uint32_t)i & 1u;
+      mbar_wait(acc_full(ab), (uint32_t)(i >> 1) & 1u);
       fence_after_sync();
-      const uint32_t a_s = s_base + s * L::STAGE_BYTES;
-      const uint64_t a_desc = smem_desc_sw128(a_s);
-      const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
+      const int64_t row = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + q4 * 32 + lane;
+#pragma unroll 1
+      for (int cb = 0; cb < NT; cb += 32) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + ab * NT + (uint32_t)cb, v);
+        tmem_ld_wait();
+        if (cb + 32 >= NT) {   // last read of this accumulator: hand it back to the MMA warp
+          fence_before_sync();
+          mbar_arrive(acc_free(ab));
+        }
+        if (row < n) {
+          const int co0 = nt_tile * NT + cb;
+          uint32_t pk[16];
 #pragma unroll
-      for (int kk = 0; kk < KBLK / 16; ++kk)   // +32 bytes per K=16 step -> +2 in the (addr >> 4) field
-        mma_bf16_ss(tmem_base, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (it | kk) ? 1u : 0u);
-      mma_commit(empty_bar(s));
+          for (int q = 0; q < 16; ++q) {
+            float a = __uint_as_float(v[2 * q]) + (bias ? bias[co0 + 2 * q] : 0.f);
+            float b = __uint_as_float(v[2 * q + 1]) + (bias ? bias[co0 + 2 * q + 1] : 0.f);
+            __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+            pk[q] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          uint4* dst = reinterpret_cast<uint4*>(out + row * c_out + co0);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) dst[q] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        }
+      }
     }
-    mma_commit(accum_bar);
   }
   fence_before_sync();
   __syncthreads();
-  if (warp == 4) tmem_dealloc<NT>(tmem_base);
+  if (warp == kMmaWarp) tmem_dealloc<2 * NT>(tmem_base);
 }
 
-template <int NT, int STAGES>
+template <int NT, int STAGES, int LAG>
 static int launch_conv(const __nv_bfloat16* in, const __nv_bfloat16* packed, const float* bias, const int32_t* nbr,
                        int64_t n, int c_in, int c_out, int k3, __nv_bfloat16* out, cudaStream_t st) {
   using L = ConvSmem<NT, STAGES>;
+  static_assert(STAGES <= 8 && LAG < STAGES, "ring");
+  static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
   static bool configured = false;
   if (!configured) {
-    cudaFuncSetAttribute(subm_conv_tc_kernel<NT, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::DYN_BYTES);
+    cudaFuncSetAttribute(subm_conv_tc_kernel<NT, STAGES, LAG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         L::DYN_BYTES);
     configured = true;
   }
-  dim3 grid((unsigned)cdiv(n, TM), (unsigned)(c_out / NT));
-  subm_conv_tc_kernel<NT, STAGES><<<grid, 160, L::DYN_BYTES, st>>>(in, packed, bias, nbr, n, c_in, c_out, k3,
-                                                                    n_kblocks(c_in, k3), out);
+  const int n_tiles = (int)cdiv(n, TM);
+  const int ny = c_out / NT;
+  int gx = kNumSMs / ny;
+  if (gx > n_tiles) gx = n_tiles;
+  dim3 grid((unsigned)gx, (unsigned)ny);
+  subm_conv_tc_kernel<NT, STAGES, LAG><<<grid, kConvThreads, L::DYN_BYTES, st>>>(
+      in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out);
   return check_launch();
 }
 
@@ -263,10 +332,10 @@ int subm_conv_tc_packed(const __nv_bfloat16* in, const __nv_bfloat16* packed, co
                         int64_t n, int c_in, int c_out, int k3, __nv_bfloat16* out, cudaStream_t st) {
   if (!subm_conv_tc_supported(c_in, c_out, k3)) return PTV3_EUNSUPPORTED;
   switch (pick_nt(c_out)) {
-    case 32: return launch_conv<32, 4>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
-    case 64: return launch_conv<64, 4>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
-    case 128: return launch_conv<128, 3>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
-    default: return launch_conv<256, 4>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    case 32: return launch_conv<32, 8, 5>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    case 64: return launch_conv<64, 7, 4>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    case 128: return launch_conv<128, 5, 3>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    default: return launch_conv<256, 4, 2>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
   }
 }
 

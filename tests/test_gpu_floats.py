@@ -134,6 +134,31 @@ def test_subm_conv_tcgen05_vs_oracle(cin, cout):
     assert rel_l2(got3, ref - bias) < 4e-3
 
 
+@pytest.mark.parametrize("cin,cout", [(32, 32), (64, 64), (256, 256), (512, 512)])
+def test_subm_conv_tcgen05_many_tiles(cin, cout):
+    """Persistent path: several 128-row tiles per CTA (ring / accumulator phase wrap-around), ragged last tile, two
+    scenes; checked against the fp32 oracle on bf16-rounded operands."""
+    from ptv3_b200 import ops
+    torch.manual_seed(cin + 3 * cout)
+    g = torch.Generator().manual_seed(5)
+    n_target = 148 * 128 * 3 + 77 if cin <= 64 else 148 * 128 + 391
+    cells = torch.randint(0, 48, (n_target * 2, 3), generator=g)
+    b = torch.randint(0, 2, (n_target * 2, 1), generator=g)
+    idx = torch.unique(torch.cat([b, cells], 1), dim=0)[:n_target].int()
+    idx = idx[torch.randperm(idx.shape[0], generator=g)].contiguous()
+    n = idx.shape[0]
+    assert n > 148 * 128 and n % 128 != 0
+    feat = torch.randn(n, cin).bfloat16()
+    w = (torch.randn(cout, 3, 3, 3, cin) / (cin * 14) ** 0.5).bfloat16()
+    bias = torch.randn(cout)
+    ref = O.subm_conv(feat.float(), O.subm_neighbor_table(idx, 3), w.float(), bias)
+    nbr = ops.subm_build_map(idx.cuda(), 3)
+    wk = w.reshape(cout, 27, cin).permute(1, 0, 2).contiguous().cuda()
+    got = ops.subm_conv_packed(feat.cuda(), ops.subm_pack_weight(wk), bias.cuda(), nbr, cout)
+    assert rel_l2(got, ref) < 4e-3, rel_l2(got, ref)
+    assert torch.isfinite(got.float()).all()
+
+
 def test_attention_golden(golden):
     """Reference SerializedAttention.forward (dense branch, one scene) frozen in tests/golden/attention.npz."""
     from ptv3_b200 import ops
