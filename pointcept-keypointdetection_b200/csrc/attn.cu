@@ -113,6 +113,10 @@ __global__ void __launch_bounds__(kAttnThreads) attn_window_simt_kernel(
 }
 
 // implemented in attn_tc.cu
+int attn_window_tc05(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows,
+                     const int64_t* n_windows, int64_t n_windows_max, int64_t max_len, int h, float scale,
+                     __nv_bfloat16* out, cudaStream_t st);
+extern int g_attn_tc05_variant;
 int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                    int64_t n_windows_max, int64_t max_len, int64_t n, int h, float scale, __nv_bfloat16* out,
                    cudaStream_t st);
@@ -133,15 +137,20 @@ int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, i
 int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const int64_t* windows,
                          const int64_t* n_windows, int64_t n_windows_max, int64_t max_len, int64_t n, int h, int d,
                          float scale, int algo, void* out, void* stream) {
-  if (n < 0 || h < 1 || h > 65535 || d != kAttnD || n_windows_max < 0 || max_len < 1 || algo < 0 || algo > 2)
+  if (n < 0 || h < 1 || h > 65535 || d != kAttnD || n_windows_max < 0 || max_len < 1 || algo < 0 || algo > 3)
     return PTV3_EINVAL;
   if (n == 0 || n_windows_max == 0) return PTV3_OK;
   if (!qkv || !windows || !n_windows || !out) return PTV3_EINVAL;
   cudaStream_t st = as_stream(stream);
+  if (dtype == PTV3_BF16 && (algo == 3 || (algo == 0 && max_len <= 1024))) {
+    if (max_len > 1024) return PTV3_EUNSUPPORTED;
+    return attn_window_tc05((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
+                            (__nv_bfloat16*)out, st);
+  }
   if (dtype == PTV3_BF16 && algo != 1)
     return attn_window_tc((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, n, h, scale,
                           (__nv_bfloat16*)out, st);
-  if (algo == 2) return PTV3_EUNSUPPORTED;
+  if (algo >= 2) return PTV3_EUNSUPPORTED;
   int64_t qblocks = cdiv(max_len, kAttnThreads);
   if (qblocks > 65535) return PTV3_EINVAL;
   dim3 grid((unsigned)n_windows_max, (unsigned)h, (unsigned)qblocks);
@@ -154,6 +163,11 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const
   else
     return PTV3_EINVAL;
   return check_launch();
+}
+
+int ptv3_debug_set(int key, int value) {
+  if (key == 1) { g_attn_tc05_variant = value; return PTV3_OK; }
+  return PTV3_EINVAL;
 }
 
 }  // extern "C"

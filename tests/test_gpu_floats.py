@@ -174,8 +174,9 @@ def test_attention_golden(golden):
     assert rel_l2(a @ pw.t() + pb, ref) < TOL_F32
     a = ops.attn_window(qkv.bfloat16(), order, w, nw, H, K, algo=1)
     assert rel_l2(a.float() @ pw.t() + pb, ref) < TOL_BF16
-    a = ops.attn_window(qkv.bfloat16(), order, w, nw, H, K, algo=2)
-    assert rel_l2(a.float() @ pw.t() + pb, ref) < TOL_BF16
+    for algo in (2, 3):
+        a = ops.attn_window(qkv.bfloat16(), order, w, nw, H, K, algo=algo)
+        assert rel_l2(a.float() @ pw.t() + pb, ref) < TOL_BF16, algo
 
 
 @pytest.mark.parametrize("counts,K,H", [([5], 16, 1), ([1024], 1024, 2), ([1025], 1024, 2), ([700, 2300, 64, 1100], 1024, 4),
@@ -196,9 +197,9 @@ def test_attention_ragged_vs_oracle(counts, K, H):
     assert rel_l2(got, ref) < TOL_F32
     qb = qkv.bfloat16()
     refb = O.window_attention(qb.float(), order, inverse, offset, H, K)
-    for algo in (1, 2):
+    for algo in (1, 2, 3) if K <= 1024 else (1, 2):
         got = ops.attn_window(qb.cuda(), order.cuda(), w, nw, H, K, algo=algo)
-        assert rel_l2(got, refb) < 6e-3, algo       # bf16 P and bf16 output rounding
+        assert rel_l2(got, refb) < 6e-3, (algo, rel_l2(got, refb))       # bf16 P and bf16 output rounding
     # flash_attn call surface (:208-215): padded layout + cu_seqlens, identity order
     pad, unpad, cu = O.padding_and_inverse(offset, K)
     g = qb[order[torch.from_numpy(pad)]].reshape(-1, 3, H, 16).cuda()
