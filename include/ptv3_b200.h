@@ -187,8 +187,9 @@ int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, i
  * for p in the window's queries, j in the window's keys, row(p) = order ? order[p] : p.
  * qkv (n,3,h,d) packed rows (= Linear(C,3C) output, :184-190 / flash layout :208-215);
  * out (n,h,d) in storage order (the reference's feat[inverse], :216-218). d == 16.
- * algo: 0 auto, 1 CUDA-core fp32-math kernel, 2 mma.sync tensor-core kernel (bf16), 3 tcgen05/TMEM kernel (bf16,
- * windows <= 1024; what auto picks for bf16). */
+ * algo: 0 auto (bf16 -> 2, fp32 -> 1), 1 CUDA-core fp32-math kernel, 2 mma.sync tensor-core kernel (bf16),
+ * 3 tcgen05/TMEM kernel (bf16, windows <= 1024).  At head_dim 16 the tcgen05 kernel is bound by the TMEM read
+ * port (4 B per score at ~64 B/clk/SM = the same 16 scores/clk/SM as the exp unit), see DESIGN.md section 4. */
 int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order /* NULL = identity */, const int64_t* windows,
                          const int64_t* n_windows /* device scalar */, int64_t n_windows_max,
                          int64_t max_len /* upper bound of q_len and k_len */, int64_t n, int h, int d, float scale,

@@ -142,7 +142,7 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const
   if (n == 0 || n_windows_max == 0) return PTV3_OK;
   if (!qkv || !windows || !n_windows || !out) return PTV3_EINVAL;
   cudaStream_t st = as_stream(stream);
-  if (dtype == PTV3_BF16 && (algo == 3 || (algo == 0 && max_len <= 1024))) {
+  if (dtype == PTV3_BF16 && algo == 3) {
     if (max_len > 1024) return PTV3_EUNSUPPORTED;
     return attn_window_tc05((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
                             (__nv_bfloat16*)out, st);

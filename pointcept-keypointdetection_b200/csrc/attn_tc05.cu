@@ -7,8 +7,9 @@
 //     V    : MN-major, no swizzle  (8-key core matrices; N blocks = [d 0-7 | d 8-15 | ones column | zeros])
 // The ones column makes the P.V MMA also produce the softmax denominator (sum of exactly the bf16 P that multiplies V).
 //
-// Roles (288 threads): warps 0-3 and 4-7 are two softmax warpgroups, each owning one 128-query tile at a time
-// ("slot"); warp 8 lane 0 issues every tcgen05.mma.  Per query tile and 64-key chunk:
+// Roles (576 threads): two "slots" work on two 128-query tiles at a time; a slot has 8 softmax warps (thread = one
+// query row x 32 of the 64 keys of a chunk) and its own MMA-issuer warp (lane 0 issues tcgen05.mma), so the slots
+// run decoupled and one slot's exps overlap the other's waits.  Per query tile and 64-key chunk:
 //     S = Q K^T      tcgen05.mma M128 N64 K16  -> TMEM (two S buffers per slot)
 //     pass 1         tcgen05.ld S, thread = query row: running max with 3-input max, no shuffles
 //     pass 2         S again -> p = exp2(s*c - m*c) -> bf16 -> shared memory (128-byte swizzle, A operand)
@@ -30,13 +31,14 @@ constexpr int QT = 128;        // queries per tile (UMMA M)
 constexpr int KC = 64;         // keys per chunk (UMMA N of S, K extent of one P buffer)
 constexpr int MAXQT = 8;       // <= 1024 queries per window
 constexpr int MAXKC = 16;      // <= 1024 keys per window
-constexpr int THREADS = 288;
+constexpr int THREADS = 576;      // 16 softmax warps + 2 MMA-issuer warps
 constexpr int Q_OFF = 0;                              // 8 tiles x 4096 B
 constexpr int K_OFF = Q_OFF + MAXQT * QT * 32;        // 32768: 1024 keys x 32 B
 constexpr int V_OFF = K_OFF + MAXKC * KC * 32;        // 65536: 128 key groups x 512 B
 constexpr int P_OFF = V_OFF + MAXKC * KC * 64;        // 131072: [slot][buf] x 16384 B
 constexpr int BAR_OFF = P_OFF + 4 * 16384;            // 196608
-constexpr int SMEM_BYTES = BAR_OFF + 256 + 1024;      // + alignment slack
+constexpr int MX_OFF = BAR_OFF + 256;                 // partial row maxima [2][2][128] fp32
+constexpr int SMEM_BYTES = MX_OFF + 2048 + 1024;      // + alignment slack
 // TMEM columns of slot s: S buffer b at s*256 + b*64, O at s*256 + 128 (32 columns)
 constexpr int TMEM_COLS = 512;
 
@@ -87,14 +89,14 @@ __global__ void __launch_bounds__(a5::THREADS, 1) attn_window_tc05_kernel(
   if (tid == 0) {
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar(s, 0), 1); mbar_init(bar(s, 1), 1);
-      mbar_init(bar(s, 2), 128); mbar_init(bar(s, 3), 128);
-      mbar_init(bar(s, 4), 128); mbar_init(bar(s, 5), 128);
+      mbar_init(bar(s, 2), 256); mbar_init(bar(s, 3), 256);
+      mbar_init(bar(s, 4), 256); mbar_init(bar(s, 5), 256);
       mbar_init(bar(s, 6), 1); mbar_init(bar(s, 7), 1);
       mbar_init(bar(s, 8), 1); mbar_init(bar(s, 9), 128);
     }
     mbar_fence_init();
   }
-  if (warp == 8) tmem_alloc<TMEM_COLS>(smem_u32(tmem_slot));
+  if (warp == 16) tmem_alloc<TMEM_COLS>(smem_u32(tmem_slot));
 
   // ---------------- stage Q, K, V of this (window, head) ----------------
   const int64_t rs = (int64_t)3 * h * D;
@@ -136,26 +138,26 @@ __global__ void __launch_bounds__(a5::THREADS, 1) attn_window_tc05_kernel(
   fence_after_sync();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 8) {
-    // =========================== MMA issuer ===========================
+  if (warp >= 16) {
+    // =========================== MMA issuers: warp 16 -> slot 0, warp 17 -> slot 1 ===========================
     if (lane == 0) {
+      const int s = warp - 16;
       constexpr uint32_t idesc_s = idesc_bf16_f32(QT, KC);                    // S: M128 N64, A and B K-major
       constexpr uint32_t idesc_o = idesc_bf16_f32(QT, 32) | (1u << 16);       // O: M128 N32, B (V) MN-major
-      const uint32_t v_lbo = variant ? 128u : 512u, v_sbo = variant ? 512u : 128u;
-      uint32_t gs[2] = {0, 0}, gp[2] = {0, 0};
-      const int rounds = (n_qt + 1) / 2;
-      auto issue_qk = [&](int s, int t, int c) {
-        const uint32_t b = gs[s] & 1u;
-        mbar_wait(bar(s, 2 + b), ((gs[s] >> 1) & 1u) ^ 1u);
+      const uint32_t v_lbo = (variant & 1) ? 128u : 512u, v_sbo = (variant & 1) ? 512u : 128u;
+      uint32_t gs = 0, gp = 0;
+      auto issue_qk = [&](int t, int c) {
+        const uint32_t b = gs & 1u;
+        mbar_wait(bar(s, 2 + b), ((gs >> 1) & 1u) ^ 1u);
         fence_after_sync();
         mma_bf16_ss(tmem + s * 256 + b * 64, desc_plain(sb + Q_OFF + t * 4096, 128, 256),
                     desc_plain(sb + K_OFF + c * 2048, 128, 256), idesc_s, 0u);
         mma_commit(bar(s, b));
-        ++gs[s];
+        ++gs;
       };
-      auto issue_pv = [&](int s, int r, int c) {
-        const uint32_t b = gp[s] & 1u;
-        mbar_wait(bar(s, 4 + b), (gp[s] >> 1) & 1u);
+      auto issue_pv = [&](int r, int c) {
+        const uint32_t b = gp & 1u;
+        mbar_wait(bar(s, 4 + b), (gp >> 1) & 1u);
         if (c == 0) mbar_wait(bar(s, 9), ((uint32_t)r & 1u) ^ 1u);   // O of the previous tile has been read
         fence_after_sync();
         const uint32_t p_s = sb + P_OFF + (s * 2 + b) * 16384;
@@ -165,100 +167,118 @@ __global__ void __launch_bounds__(a5::THREADS, 1) attn_window_tc05_kernel(
                       desc_plain(sb + V_OFF + c * 4096 + kk * 1024, v_lbo, v_sbo), idesc_o, (c | kk) ? 1u : 0u);
         mma_commit(bar(s, 6 + b));
         if (c == nc - 1) mma_commit(bar(s, 8));
-        ++gp[s];
+        ++gp;
       };
-      for (int r = 0; r < rounds; ++r) {
-        const int ns = (2 * r + 1 < n_qt) ? 2 : 1;
-        for (int c = 0; c < nc; ++c)
-          for (int s = 0; s < ns; ++s) issue_qk(s, 2 * r + s, c);
+      for (int r = 0; 2 * r + s < n_qt; ++r) {
+        const int t = 2 * r + s;
+        if (!(variant & 2))
+          for (int c = 0; c < nc; ++c) issue_qk(t, c);
         for (int c = 0; c <= nc; ++c) {
-          if (c < nc)
-            for (int s = 0; s < ns; ++s) issue_qk(s, 2 * r + s, c);
-          if (c >= 1)
-            for (int s = 0; s < ns; ++s) issue_pv(s, r, c - 1);
+          if (c < nc) issue_qk(t, c);
+          if (c >= 1) issue_pv(r, c - 1);
         }
       }
     }
   } else {
-    // =========================== softmax warpgroups ===========================
-    const int s = warp >> 2;                 // slot
-    const int row = tid & 127;               // query row inside the tile = TMEM lane
+    // =========================== softmax: 8 warps per slot ===========================
+    // warp w: slot w>>3, column half (w>>2)&1 of every 64-key chunk, TMEM lane quarter w&3 (the hardware rule:
+    // a warp may only touch lanes 32*(warp%4)..+31); thread = one query row x 32 keys per chunk.
+    const int s = warp >> 3;
+    const int half = (warp >> 2) & 1;
+    const int row = (warp & 3) * 32 + lane;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    float* mx = reinterpret_cast<float*>(smem + MX_OFF);   // [slot][half][128] partial row maxima
     uint32_t gs = 0, gp = 0;
-    const int rem_last = kl - (nc - 1) * KC;   // valid keys of the last chunk (1..64)
+    const int rem_last = kl - (nc - 1) * KC - half * 32;   // valid keys of my half of the last chunk
     for (int r = 0; 2 * r + s < n_qt; ++r) {
       const int t = 2 * r + s;
       const int qi = t * QT + row;
       int64_t orow = -1;
-      if (qi < ql) orow = order ? order[q0 + qi] : q0 + qi;
-      uint32_t v[64];   // raw fp32 bits of one S row chunk
+      if (half == 0 && qi < ql) orow = order ? order[q0 + qi] : q0 + qi;
+      uint32_t v[32];   // raw fp32 bits of my 32 columns of one S chunk
       auto load_chunk = [&](int c) {
         const uint32_t b = gs & 1u;
         mbar_wait(bar(s, b), (gs >> 1) & 1u);
         fence_after_sync();
-        const uint32_t ta = tmem + lane_base + s * 256 + b * 64;
-        tmem_ld64(ta, v);
+        tmem_ld32(tmem + lane_base + s * 256 + b * 64 + half * 32, v);
         tmem_ld_wait();
         fence_before_sync();
         mbar_arrive(bar(s, 2 + b));
         ++gs;
-        if (c == nc - 1 && rem_last < KC) {
+        if (c == nc - 1 && rem_last < 32) {
 #pragma unroll
-          for (int j = 0; j < 64; ++j)
+          for (int j = 0; j < 32; ++j)
             if (j >= rem_last) v[j] = 0xff800000u;   // -inf
         }
       };
-      // ---- pass 1: row maximum ----
-      float m = -INFINITY;
-      for (int c = 0; c < nc; ++c) {
+      // ---- pass 1: row maximum (two independent chains per thread, halves combined through shared memory) ----
+      float m0 = -INFINITY, m1 = -INFINITY;
+      if (variant & 2) m0 = 30.f;
+      for (int c = 0; c < nc && !(variant & 2); ++c) {
         load_chunk(c);
 #pragma unroll
-        for (int j = 0; j < 64; j += 2) m = max3(m, __uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+        for (int j = 0; j < 32; j += 4) {
+          m0 = max3(m0, __uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+          m1 = max3(m1, __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+        }
       }
+      float m = fmaxf(m0, m1);
+      mx[(s * 2 + half) * 128 + row] = m;
+      asm volatile("bar.sync %0, 256;" ::"r"(1 + s) : "memory");
+      m = fmaxf(m, mx[(s * 2 + (half ^ 1)) * 128 + row]);
       const float msc = m * scale_log2;
       // ---- pass 2: P = exp2(s*c - m*c) as bf16 into the swizzled A-operand buffer ----
       for (int c = 0; c < nc; ++c) {
         load_chunk(c);
-        uint32_t pk[32];
+        uint32_t pk[16];
+        if (variant & 4) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          pk[j] = pack2(ex2f(fmaf(__uint_as_float(v[2 * j]), scale_log2, -msc)),
-                         ex2f(fmaf(__uint_as_float(v[2 * j + 1]), scale_log2, -msc)));
+          for (int j = 0; j < 16; ++j)
+            pk[j] = pack2(fmaf(__uint_as_float(v[2 * j]), scale_log2, -msc),
+                          fmaf(__uint_as_float(v[2 * j + 1]), scale_log2, -msc));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            pk[j] = pack2(ex2f(fmaf(__uint_as_float(v[2 * j]), scale_log2, -msc)),
+                          ex2f(fmaf(__uint_as_float(v[2 * j + 1]), scale_log2, -msc)));
+        }
         const uint32_t b = gp & 1u;
         mbar_wait(bar(s, 6 + b), ((gp >> 1) & 1u) ^ 1u);
         const uint32_t prow = sb + P_OFF + (s * 2 + b) * 16384 + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch)
-          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(prow + ((ch ^ (row & 7)) << 4)),
-                       "r"(pk[4 * ch]), "r"(pk[4 * ch + 1]), "r"(pk[4 * ch + 2]), "r"(pk[4 * ch + 3])
+        for (int i = 0; i < 4; ++i)
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (((half * 4 + i) ^ (row & 7)) << 4)),
+                       "r"(pk[4 * i]), "r"(pk[4 * i + 1]), "r"(pk[4 * i + 2]), "r"(pk[4 * i + 3])
                        : "memory");
         fence_proxy_async();
         mbar_arrive(bar(s, 4 + b));
         ++gp;
       }
-      // ---- epilogue: O / denominator -> storage row ----
-      mbar_wait(bar(s, 8), (uint32_t)r & 1u);
-      fence_after_sync();
-      uint32_t o[32];
-      tmem_ld32(tmem + lane_base + s * 256 + 128, o);
-      tmem_ld_wait();
-      fence_before_sync();
-      mbar_arrive(bar(s, 9));
-      if (orow >= 0) {
-        const float inv = 1.f / __uint_as_float(o[16]);
-        uint32_t pk[8];
+      // ---- epilogue (column-half 0 warps): O / denominator -> storage row ----
+      if (half == 0) {
+        mbar_wait(bar(s, 8), (uint32_t)r & 1u);
+        fence_after_sync();
+        uint32_t o[32];
+        tmem_ld32(tmem + lane_base + s * 256 + 128, o);
+        tmem_ld_wait();
+        fence_before_sync();
+        mbar_arrive(bar(s, 9));
+        if (orow >= 0) {
+          const float inv = 1.f / __uint_as_float(o[16]);
+          uint32_t pk[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          pk[j] = pack2(__uint_as_float(o[2 * j]) * inv, __uint_as_float(o[2 * j + 1]) * inv);
-        uint4* dst = reinterpret_cast<uint4*>(out + orow * (int64_t)h * D + head * D);
-        dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-        dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+          for (int j = 0; j < 8; ++j)
+            pk[j] = pack2(__uint_as_float(o[2 * j]) * inv, __uint_as_float(o[2 * j + 1]) * inv);
+          uint4* dst = reinterpret_cast<uint4*>(out + orow * (int64_t)h * D + head * D);
+          dst[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          dst[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+        }
       }
     }
   }
   fence_before_sync();
   __syncthreads();
-  if (warp == 8) tmem_dealloc<a5::TMEM_COLS>(tmem);
+  if (warp == 16) tmem_dealloc<a5::TMEM_COLS>(tmem);
 }
 
 int attn_window_tc05(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows,
