@@ -77,6 +77,28 @@ __global__ void __launch_bounds__(256) seg_short_vec4_kernel(const T* __restrict
   }
 }
 
+// short segments, any channel count (c = 3 for coordinates): one thread per (segment, channel).
+template <typename T>
+__global__ void __launch_bounds__(256) seg_short_scalar_kernel(const T* __restrict__ src,
+                                                               const int64_t* __restrict__ gather,
+                                                               const int64_t* __restrict__ indptr, int64_t m, int c,
+                                                               int reduce, T* __restrict__ out) {
+  const int64_t total = m * c;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t k = t / c;
+    const int ch = (int)(t - k * c);
+    const int64_t a = indptr[k], b = indptr[k + 1];
+    float acc = red_init(reduce);
+    for (int64_t j = a; j < b; ++j) {
+      const int64_t row = gather ? gather[j] : j;
+      acc = red_op(reduce, acc, Elem<T>::load(src + row * c + ch));
+    }
+    if (b <= a) acc = 0.f;
+    else if (reduce == RED_MEAN) acc *= 1.f / (float)(b - a);
+    Elem<T>::store(out + t, acc);
+  }
+}
+
 // generic (any c, any segment length): one CTA per segment; warp w strides the
 // rows, lanes stride the channels; cross-warp combine through shared memory.
 template <typename T>
@@ -347,6 +369,8 @@ static int seg_dispatch(const T* src, const int64_t* gather, const int64_t* indp
   if ((c % 4) == 0 && hint_rows_per_seg <= 64) {
     int c4 = (int)(c / 4);
     seg_short_vec4_kernel<T><<<grid_for(m * c4, 256), 256, 0, st>>>(src, gather, indptr, m, c4, reduce, out);
+  } else if (hint_rows_per_seg <= 64) {
+    seg_short_scalar_kernel<T><<<grid_for(m * c, 256), 256, 0, st>>>(src, gather, indptr, m, (int)c, reduce, out);
   } else {
     int g = (int)(m < (int64_t)kNumSMs * 16 ? m : (int64_t)kNumSMs * 16);
     seg_block_kernel<T><<<g, 256, 0, st>>>(src, gather, indptr, m, (int)c, reduce, out);

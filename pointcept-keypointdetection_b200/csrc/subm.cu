@@ -201,10 +201,77 @@ __global__ void __launch_bounds__(256) subm_conv_rowwarp_kernel(const T* __restr
   }
 }
 
+
+// ------------------------------ stem specialisation: C_in = 4, C_out = 32 -------------------
+// lane = output channel; weights as float4 [k][co] in shared memory (one LDS.128 per neighbour); the neighbour ids of
+// the whole row (<= 128 offsets) and the lanes' own neighbour features are loaded up front so their latencies overlap.
+template <typename T>
+__device__ __forceinline__ float4 load_feat4(const T* p);
+template <>
+__device__ __forceinline__ float4 load_feat4<float>(const float* p) { return *reinterpret_cast<const float4*>(p); }
+template <>
+__device__ __forceinline__ float4 load_feat4<__nv_bfloat16>(const __nv_bfloat16* p) {
+  uint2 u = *reinterpret_cast<const uint2*>(p);
+  return make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u), __uint_as_float(u.y << 16),
+                     __uint_as_float(u.y & 0xffff0000u));
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) subm_conv_stem4_kernel(const T* __restrict__ in, const T* __restrict__ w,
+                                                              const float* __restrict__ bias,
+                                                              const int32_t* __restrict__ nbr, int64_t n, int k3,
+                                                              T* __restrict__ out) {
+  extern __shared__ float4 ws4[];  // [k3][32]
+  for (int idx = threadIdx.x; idx < k3 * 32; idx += blockDim.x) {
+    const int co = idx & 31, k = idx >> 5;
+    const T* p = w + ((int64_t)k * 32 + co) * 4;
+    ws4[idx] = make_float4(Elem<T>::load(p), Elem<T>::load(p + 1), Elem<T>::load(p + 2), Elem<T>::load(p + 3));
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const float b = bias ? bias[lane] : 0.f;
+  for (; row < n; row += stride) {
+    const int32_t* nb = nbr + row * k3;
+    int mine[4];
+    float4 x[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) mine[q] = (q * 32 + lane < k3) ? nb[q * 32 + lane] : -1;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      x[q] = mine[q] >= 0 ? load_feat4<T>(in + (int64_t)mine[q] * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t present = __ballot_sync(0xffffffffu, mine[q] >= 0);
+      while (present) {
+        const int j = __ffs(present) - 1;
+        present &= present - 1;
+        const float4 wv = ws4[(q * 32 + j) * 32 + lane];
+        acc0 = fmaf(__shfl_sync(0xffffffffu, x[q].x, j), wv.x, acc0);
+        acc1 = fmaf(__shfl_sync(0xffffffffu, x[q].y, j), wv.y, acc1);
+        acc0 = fmaf(__shfl_sync(0xffffffffu, x[q].z, j), wv.z, acc0);
+        acc1 = fmaf(__shfl_sync(0xffffffffu, x[q].w, j), wv.w, acc1);
+      }
+    }
+    Elem<T>::store(out + row * 32 + lane, acc0 + acc1 + b);
+  }
+}
+
 template <typename T>
 static int conv_cuda_core(const T* in, const T* w, const float* bias, const int32_t* nbr, int64_t n, int cin, int cout,
                           int k3, T* out, cudaStream_t st) {
   size_t smem = (size_t)k3 * cin * cout * sizeof(float);
+  if (cin == 4 && cout == 32 && k3 <= 128) {
+    const size_t sm4 = (size_t)k3 * 32 * sizeof(float4);
+    int g = (int)cdiv(n, 8);
+    const int cap = kNumSMs * 3 * 4;
+    if (g > cap) g = cap;
+    cudaFuncSetAttribute(subm_conv_stem4_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm4);
+    subm_conv_stem4_kernel<T><<<g, 256, sm4, st>>>(in, w, bias, nbr, n, k3, out);
+    return check_launch();
+  }
   if (cin <= 8 && cout <= 64 && smem <= 200 * 1024) {
     int g = (int)cdiv(n, 8);
     int cap = kNumSMs * 2 * 8;
