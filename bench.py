@@ -218,7 +218,12 @@ def run_ours(args):
         step_ms = a.elapsed_time(b)
         tot = {}
         for name, t, meta in recs:
-            fl, units = attn_flops(meta) if name == "attn_window" else conv_flops(meta)
+            if name == "attn_window":
+                fl, units = attn_flops(meta)
+            elif name == "mlp_fused":      # fc1 + fc2: 2 * (2 * n * c * hidden)
+                fl, units = 4.0 * meta["n"] * meta["c"] * meta["hidden"], float(meta["n"])
+            else:
+                fl, units = conv_flops(meta)
             e = tot.setdefault(name, dict(ms=0.0, flops=0.0, units=0.0, launches=0))
             e["ms"] += t
             e["flops"] += fl

@@ -1,0 +1,336 @@
+// A8: the Block's MLP  fc1 -> GELU(erf) -> fc2 (+ residual add) as ONE persistent tcgen05 kernel (bf16, C = 32 / 64).
+// Reference: MLP.forward point_transformer_v3m1_base.py:225-248 and the residual wiring of Block.forward :330-337.
+//
+// The reference (and a cuBLAS chain) writes the (N, 4C) hidden activation to HBM, reads it for GELU, writes it again and
+// reads it for fc2: 4 x N x 4C x 2 B.  Here the hidden tile never leaves the SM:
+//   GEMM1  D1[128 x 128] = X[128 x C] . W1[hb]^T          tcgen05.mma, accumulator in TMEM (2 buffers)
+//   epi 1  tcgen05.ld D1 -> + b1 -> GELU(erf) -> bf16 -> shared memory in the 128-byte-swizzled A-operand layout
+//   GEMM2  D2[128 x C] += H[128 x 128] . W2[:, hb]^T      accumulator in TMEM (2 buffers, one per row tile in flight)
+//   epi 2  tcgen05.ld D2 -> + b2 (+ fp32 residual) -> fp32 residual stream and its bf16 copy
+// Both weight matrices (pre-packed into shared-memory images by pack_kmajor_kernel) stay resident in shared memory
+// for the CTA's lifetime (one bulk copy each); X tiles are double-buffered by two loader warps with 16-byte cp.async.
+// HBM traffic per row: read C x 2 B (+ C x 4 B residual), write C x (4 + 2) B  -- the hidden activation costs nothing.
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace ptv3 {
+
+using namespace tc05;
+
+namespace mlp {
+constexpr int TM = 128;
+constexpr int HB = 128;            // hidden columns per GEMM1 / K extent per GEMM2 step
+constexpr int THREADS = 640;       // warps 0-1 loaders, 2 MMA issuer (+TMEM alloc), 3 spare, 4-19 epilogue
+constexpr int LOADERS = 64;
+constexpr int EPI = 512;
+
+template <int C>
+struct Smem {
+  static constexpr int HID = 4 * C;
+  static constexpr int NHB = HID / HB;
+  static constexpr int W1_BYTES = NHB * HB * 128;            // [hb][128 rows][64 (C padded)] swizzled
+  static constexpr int W2_TILE = C * 128;                    // one K-block of W2: [C rows][64]
+  static constexpr int W2_BYTES = (HID / 64) * W2_TILE;
+  static constexpr int A1_BYTES = TM * 128;                  // [128 rows][64]
+  static constexpr int A2_BYTES = 2 * TM * 128;              // two K-blocks
+  static constexpr int W1_OFF = 0;
+  static constexpr int W2_OFF = W1_OFF + W1_BYTES;
+  static constexpr int A1_OFF = W2_OFF + W2_BYTES;
+  static constexpr int A2_OFF = A1_OFF + 2 * A1_BYTES;
+  static constexpr int BAR_OFF = A2_OFF + 2 * A2_BYTES;
+  static constexpr int DYN_BYTES = BAR_OFF + 256 + 1024;
+};
+
+// exact-erf GELU, 0.5 x (1 + erf(x / sqrt 2)), with erf from Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, far below
+// the bf16 rounding of the hidden activation): 13 FMA-pipe instructions + one rcp and one ex2 on the MUFU pipe
+// instead of the ~30 of erff().  gelu = 0.5 (x + |x|) - 0.5 |x| p(t) exp(-x^2 / 2),  t = 1 / (1 + 0.3275911 |x| / sqrt 2)
+__device__ __forceinline__ float gelu_erf(float x) {
+  const float ax = fabsf(x);
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(ax, 0.23164189f, 1.0f)));   // 0.3275911 / sqrt(2)
+  float p = fmaf(t, 1.061405429f, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  p *= t;
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752f));            // exp(-x^2/2) = 2^(-x^2 log2(e)/2)
+  return fmaf(-0.5f * ax, p * e, 0.5f * (x + ax));
+}
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+}  // namespace mlp
+
+// generic K-major packer: w (rows, k) bf16 row-major -> [tile][kb][tile_rows][64] with the 128-byte swizzle (zero
+// padded along K up to a multiple of 64)
+__global__ void __launch_bounds__(256) pack_kmajor_kernel(const __nv_bfloat16* __restrict__ w, int rows, int k,
+                                                          int tile_rows, int n_kb, __nv_bfloat16* __restrict__ packed) {
+  const int64_t chunks = (int64_t)n_kb * rows * 8;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < chunks; t += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(t & 7);
+    const int64_t rowid = t >> 3;
+    const int rl = (int)(rowid % tile_rows);
+    const int64_t r2 = rowid / tile_rows;
+    const int kb = (int)(r2 % n_kb);
+    const int tile = (int)(r2 / n_kb);
+    const int row = tile * tile_rows + rl;
+    const int kk = kb * 64 + c * 8;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (kk < k) v = *reinterpret_cast<const uint4*>(w + (int64_t)row * k + kk);
+    char* base = reinterpret_cast<char*>(packed) + ((int64_t)tile * n_kb + kb) * tile_rows * 128;
+    const int off = (rl >> 3) * 1024 + (rl & 7) * 128 + ((c ^ (rl & 7)) << 4);
+    *reinterpret_cast<uint4*>(base + off) = v;
+  }
+}
+
+template <int C>
+__global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w1p, const float* __restrict__ b1,
+    const __nv_bfloat16* __restrict__ w2p, const float* __restrict__ b2, const float* __restrict__ residual, int64_t n,
+    int n_tiles, float* __restrict__ res_out, __nv_bfloat16* __restrict__ out_bf16) {
+  using namespace mlp;
+  using L = Smem<C>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t sb = smem_u32(smem);
+  auto bar = [&](int id) { return sb + L::BAR_OFF + 8u * (uint32_t)id; };
+  // 0 w_full | 1,2 a1_full | 3,4 a1_free | 5,6 d1_full | 7,8 d1_free | 9,10 a2_full | 11,12 a2_free | 13,14 d2_full
+  // | 15,16 d2_free
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::BAR_OFF + 200);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (tid == 0) {
+    mbar_init(bar(0), 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(bar(1 + b), LOADERS); mbar_init(bar(3 + b), 1);
+      mbar_init(bar(5 + b), 1);       mbar_init(bar(7 + b), EPI);
+      mbar_init(bar(9 + b), EPI);     mbar_init(bar(11 + b), 1);
+      mbar_init(bar(13 + b), 1);      mbar_init(bar(15 + b), EPI);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 2) {
+    // =========================== loaders ===========================
+    if (tid == 0) {
+      mbar_arrive_expect_tx(bar(0), L::W1_BYTES + L::W2_BYTES);
+      bulk_g2s(sb + L::W1_OFF, w1p, L::W1_BYTES, bar(0));
+      bulk_g2s(sb + L::W2_OFF, w2p, L::W2_BYTES, bar(0));
+    }
+    if (C == 32) {   // K is padded to 64: the upper four 16-byte chunks of every row stay zero for the kernel's life
+      for (int idx = tid; idx < 2 * TM * 4; idx += LOADERS) {
+        const int buf = idx / (TM * 4), r = (idx / 4) % TM, c = 4 + (idx & 3);
+        st_shared_zero16(sb + L::A1_OFF + buf * L::A1_BYTES + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+      }
+    }
+    const int c = tid & 7, r0 = tid >> 3;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int ab = i & 1;
+      const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
+      mbar_wait(bar(3 + ab), ((uint32_t)(i >> 1) & 1u) ^ 1u);
+      if (c < C / 8) {
+        const uint32_t a1 = sb + L::A1_OFF + ab * L::A1_BYTES;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+          const int r = r0 + 8 * q;
+          const uint32_t dst = a1 + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4);
+          if (row0 + r < n) cp_async16(dst, x + (row0 + r) * C + c * 8, 16u);
+          else st_shared_zero16(dst);
+        }
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      fence_proxy_async();
+      mbar_arrive(bar(1 + ab));
+    }
+  } else if (warp == 2) {
+    // =========================== MMA issuer ===========================
+    if (lane == 0) {
+      constexpr uint32_t idesc1 = idesc_bf16_f32(TM, HB), idesc2 = idesc_bf16_f32(TM, C);
+      mbar_wait(bar(0), 0);
+      uint32_t c1 = 0, c2 = 0;
+      for (int i = 0; i < my_tiles; ++i) {
+        const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
+        mbar_wait(bar(1 + ab), tph);
+        fence_after_sync();
+        for (int hb = 0; hb <= L::NHB; ++hb) {
+          if (hb < L::NHB) {
+            const uint32_t bb = c1 & 1u;
+            mbar_wait(bar(7 + bb), ((c1 >> 1) & 1u) ^ 1u);
+            fence_after_sync();
+            const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + ab * L::A1_BYTES);
+            const uint64_t b_desc = smem_desc_sw128(sb + L::W1_OFF + hb * HB * 128);
+#pragma unroll
+            for (int kk = 0; kk < C / 16 && kk < 4; ++kk)
+              mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc1, kk ? 1u : 0u);
+            mma_commit(bar(5 + bb));
+            if (hb == L::NHB - 1) mma_commit(bar(3 + ab));   // X tile fully consumed
+            ++c1;
+          }
+          if (hb >= 1) {
+            const int h2 = hb - 1;
+            const uint32_t bb = c2 & 1u;
+            mbar_wait(bar(9 + bb), (c2 >> 1) & 1u);
+            if (h2 == 0) mbar_wait(bar(15 + ab), tph ^ 1u);   // D2[ab] drained by the epilogue of tile i-2
+            fence_after_sync();
+#pragma unroll
+            for (int kb = 0; kb < 2; ++kb) {
+              const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
+              const uint64_t b_desc = smem_desc_sw128(sb + L::W2_OFF + (2 * h2 + kb) * L::W2_TILE);
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)
+                mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc2, (h2 | kb | kk) ? 1u : 0u);
+            }
+            mma_commit(bar(11 + bb));
+            if (h2 == L::NHB - 1) mma_commit(bar(13 + ab));
+            ++c2;
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // =========================== epilogue warps ===========================
+    const int q4 = warp & 3, quarter = (warp - 4) >> 2;   // TMEM lane quarter, column quarter of the 128-wide block
+    const int row = q4 * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
+    uint32_t e1 = 0;
+    for (int i = 0; i < my_tiles; ++i) {
+      const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
+      for (int hb = 0; hb < L::NHB; ++hb, ++e1) {
+        const uint32_t bb = e1 & 1u;
+        mbar_wait(bar(5 + bb), (e1 >> 1) & 1u);
+        fence_after_sync();
+        uint32_t v[32], pk[16];
+        const int col0 = quarter * 32;
+        tmem_ld32(tmem + lane_base + bb * HB + col0, v);
+        tmem_ld_wait();
+        fence_before_sync();
+        mbar_arrive(bar(7 + bb));
+        const float4* bp = reinterpret_cast<const float4*>(b1 + hb * HB + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 bv = bp[j];
+          pk[2 * j] = pack2(gelu_erf(__uint_as_float(v[4 * j]) + bv.x), gelu_erf(__uint_as_float(v[4 * j + 1]) + bv.y));
+          pk[2 * j + 1] =
+              pack2(gelu_erf(__uint_as_float(v[4 * j + 2]) + bv.z), gelu_erf(__uint_as_float(v[4 * j + 3]) + bv.w));
+        }
+        mbar_wait(bar(11 + bb), ((e1 >> 1) & 1u) ^ 1u);
+        // my 32 hidden columns = four 16-byte chunks of K-block (quarter >> 1), chunks (quarter & 1) * 4 ..
+        const uint32_t prow = sb + L::A2_OFF + bb * L::A2_BYTES + (quarter >> 1) * 16384 + (row >> 3) * 1024 +
+                              (row & 7) * 128;
+#pragma unroll
+        for (int c4 = 0; c4 < 4; ++c4)
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(
+                           prow + ((((quarter & 1) * 4 + c4) ^ (row & 7)) << 4)),
+                       "r"(pk[4 * c4]), "r"(pk[4 * c4 + 1]), "r"(pk[4 * c4 + 2]), "r"(pk[4 * c4 + 3])
+                       : "memory");
+        fence_proxy_async();
+        mbar_arrive(bar(9 + bb));
+      }
+      // ---- epilogue 2: D2 -> + b2 (+ residual) -> fp32 stream and bf16 copy; this thread owns C/4 columns ----
+      mbar_wait(bar(13 + ab), tph);
+      fence_after_sync();
+      constexpr int NC = C / 4;
+      uint32_t v[NC];
+      const int col0 = quarter * NC;
+      if constexpr (NC == 16) tmem_ld16(tmem + lane_base + 256 + ab * C + col0, v);
+      else tmem_ld8(tmem + lane_base + 256 + ab * C + col0, v);
+      tmem_ld_wait();
+      fence_before_sync();
+      mbar_arrive(bar(15 + ab));
+      const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
+      if (grow < n) {
+        float f[NC];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]) + b2[col0 + j];
+        if (residual) {
+          const float4* rp = reinterpret_cast<const float4*>(residual + grow * C + col0);
+#pragma unroll
+          for (int j = 0; j < NC / 4; ++j) {
+            const float4 r = rp[j];
+            f[4 * j] += r.x; f[4 * j + 1] += r.y; f[4 * j + 2] += r.z; f[4 * j + 3] += r.w;
+          }
+        }
+        if (res_out) {
+          float4* op = reinterpret_cast<float4*>(res_out + grow * C + col0);
+#pragma unroll
+          for (int j = 0; j < NC / 4; ++j) op[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        }
+        if (out_bf16) {
+          uint4* op = reinterpret_cast<uint4*>(out_bf16 + grow * C + col0);
+#pragma unroll
+          for (int j = 0; j < NC / 8; ++j)
+            op[j] = make_uint4(pack2(f[8 * j], f[8 * j + 1]), pack2(f[8 * j + 2], f[8 * j + 3]),
+                               pack2(f[8 * j + 4], f[8 * j + 5]), pack2(f[8 * j + 6], f[8 * j + 7]));
+        }
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<512>(tmem);
+}
+
+bool mlp_fused_supported(int c, int hidden) { return (c == 32 || c == 64) && hidden == 4 * c; }
+
+template <int C>
+static int launch_mlp(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const float* b1, const __nv_bfloat16* w2p,
+                      const float* b2, const float* residual, int64_t n, float* res_out, __nv_bfloat16* out_bf16,
+                      cudaStream_t st) {
+  using L = mlp::Smem<C>;
+  static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(mlp_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::DYN_BYTES);
+    configured = true;
+  }
+  const int n_tiles = (int)cdiv(n, mlp::TM);
+  const int g = n_tiles < kNumSMs ? n_tiles : kNumSMs;
+  mlp_fused_kernel<C><<<g, mlp::THREADS, L::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, n, n_tiles, res_out,
+                                                              out_bf16);
+  return check_launch();
+}
+
+}  // namespace ptv3
+
+using namespace ptv3;
+
+extern "C" {
+
+size_t ptv3_pack_kmajor_bytes(int rows, int k) { return (size_t)rows * (size_t)((k + 63) / 64) * 128; }
+
+int ptv3_pack_kmajor(const void* w, int rows, int k, int tile_rows, void* packed, void* stream) {
+  if (!w || !packed || rows < 1 || k < 8 || (k % 8) != 0 || tile_rows < 8 || (tile_rows % 8) != 0 ||
+      (rows % tile_rows) != 0)
+    return PTV3_EINVAL;
+  const int n_kb = (k + 63) / 64;
+  pack_kmajor_kernel<<<grid_for((int64_t)n_kb * rows * 8, 256), 256, 0, as_stream(stream)>>>(
+      (const __nv_bfloat16*)w, rows, k, tile_rows, n_kb, (__nv_bfloat16*)packed);
+  return check_launch();
+}
+
+int ptv3_mlp_fused_supported(int c, int hidden) { return mlp_fused_supported(c, hidden) ? 1 : 0; }
+
+int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
+                   const float* residual, int64_t n, int c, int hidden, float* res_out, void* out_bf16, void* stream) {
+  if (n < 0 || !mlp_fused_supported(c, hidden)) return n < 0 ? PTV3_EINVAL : PTV3_EUNSUPPORTED;
+  if (n == 0) return PTV3_OK;
+  if (!x || !w1_packed || !b1 || !w2_packed || !b2 || (!res_out && !out_bf16)) return PTV3_EINVAL;
+  cudaStream_t st = as_stream(stream);
+  if (c == 32)
+    return launch_mlp<32>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed,
+                          b2, residual, n, res_out, (__nv_bfloat16*)out_bf16, st);
+  return launch_mlp<64>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed,
+                        b2, residual, n, res_out, (__nv_bfloat16*)out_bf16, st);
+}
+
+}  // extern "C"

@@ -294,9 +294,19 @@ class Block(PointModule):
         x, h = ops.ln_residual(p, None, None, eps2, residual=x, gamma2=gn2, beta2=bn2, out2_dtype=cd)
         # mlp
         mlp = self.mlp[0]
-        f = F.gelu(F.linear(h, *self._lin(mlp.fc1, cd)))
-        f = F.linear(f, *self._lin(mlp.fc2, cd))
-        x, xcd = ops.ln_residual(f, None, None, 1e-5, residual=x, out2_dtype=None if cd == torch.float32 else cd)
+        hidden = mlp.fc1.out_features
+        if (cd == torch.bfloat16 and isinstance(mlp.act, nn.GELU) and mlp.act.approximate == "none"
+                and ops.mlp_fused_supported(self.channels, hidden) and mlp.fc2.out_features == self.channels):
+            # fc1 -> GELU -> fc2 -> + residual in one tcgen05 kernel: the (N, 4C) hidden activation stays on the SM
+            w1p, b1, w2p, b2 = _cached(
+                self, "mlp_packed", [mlp.fc1.weight, mlp.fc1.bias, mlp.fc2.weight, mlp.fc2.bias],
+                lambda: (ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), mlp.fc1.bias.float().contiguous(),
+                         ops.pack_kmajor(mlp.fc2.weight.to(cd), self.channels), mlp.fc2.bias.float().contiguous()))
+            x, xcd = ops.mlp_fused(h, w1p, b1, w2p, b2, hidden, residual=x)
+        else:
+            f = F.gelu(F.linear(h, *self._lin(mlp.fc1, cd)))
+            f = F.linear(f, *self._lin(mlp.fc2, cd))
+            x, xcd = ops.ln_residual(f, None, None, 1e-5, residual=x, out2_dtype=None if cd == torch.float32 else cd)
         point.feat = x
         point["_feat_cd"] = xcd if xcd is not None else x
         point.sparse_conv_feat = sp.replace_feature(point["_feat_cd"])

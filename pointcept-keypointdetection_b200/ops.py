@@ -252,6 +252,41 @@ def ln_residual(x, gamma=None, beta=None, eps=1e-5, residual=None, want_res=True
     return res_out, out2
 
 
+# ------------------------------------------------------------------ A8 fused MLP (tcgen05)
+def pack_kmajor(w, tile_rows):
+    """(rows, k) bf16 row-major weight -> K-blocked, 128-byte-swizzled shared-memory image (tiles of tile_rows rows)."""
+    _need_cuda(w)
+    lib = _lib.load()
+    w = w.contiguous()
+    assert w.dtype == torch.bfloat16 and w.dim() == 2
+    rows, k = w.shape
+    packed = torch.empty(lib.ptv3_pack_kmajor_bytes(rows, k) // 2, dtype=torch.bfloat16, device=w.device)
+    _lib.check(lib.ptv3_pack_kmajor(_p(w), rows, k, int(tile_rows), _p(packed), _stream()), "ptv3_pack_kmajor")
+    return packed
+
+
+def mlp_fused_supported(c, hidden):
+    return bool(_lib.load().ptv3_mlp_fused_supported(int(c), int(hidden)))
+
+
+def mlp_fused(x, w1_packed, b1, w2_packed, b2, hidden, residual=None, want_res=True, want_bf16=True):
+    """r = (residual +) fc2(GELU(fc1(x))) in one kernel.  x (N,C) bf16.  Returns (r fp32 or None, r bf16 or None)."""
+    _need_cuda(x, w1_packed, w2_packed)
+    lib = _lib.load()
+    x = x.contiguous()
+    assert x.dtype == torch.bfloat16
+    n, c = x.shape
+    res_out = torch.empty((n, c), dtype=torch.float32, device=x.device) if want_res else None
+    out16 = torch.empty((n, c), dtype=torch.bfloat16, device=x.device) if want_bf16 else None
+    if residual is not None:
+        residual = residual.contiguous()
+        assert residual.dtype == torch.float32 and residual.shape == x.shape
+    with _timed("mlp_fused", n=n, c=c, hidden=int(hidden)):
+        _lib.check(lib.ptv3_mlp_fused(_p(x), _p(w1_packed), _p(b1), _p(w2_packed), _p(b2), _p(residual), n, c,
+                                      int(hidden), _p(res_out), _p(out16), _stream()), "ptv3_mlp_fused")
+    return res_out, out16
+
+
 # ------------------------------------------------------------------ A5 submanifold conv
 def subm_build_map(indices, ksize):
     """indices (N,4) int32 [b,x,y,z] -> nbr (N, ksize^3) int32 (-1 = absent)."""

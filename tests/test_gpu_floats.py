@@ -159,6 +159,30 @@ def test_subm_conv_tcgen05_many_tiles(cin, cout):
     assert torch.isfinite(got.float()).all()
 
 
+@pytest.mark.parametrize("c,n", [(32, 1000), (64, 777), (32, 148 * 128 * 2 + 5), (64, 148 * 128 * 3 + 129)])
+def test_mlp_fused_tcgen05(c, n):
+    """fc1 -> GELU(erf) -> fc2 (+ residual) in one tcgen05 kernel against the torch fp32 reference on the same
+    bf16-rounded operands (hidden activation rounded to bf16 like the reference under autocast): rel-L2 <= 4e-3."""
+    import torch.nn.functional as F
+    from ptv3_b200 import ops
+    torch.manual_seed(c + n)
+    h = 4 * c
+    x = torch.randn(n, c).bfloat16()
+    w1 = (torch.randn(h, c) / c ** 0.5).bfloat16()
+    w2 = (torch.randn(c, h) / h ** 0.5).bfloat16()
+    b1, b2 = torch.randn(h) * 0.5, torch.randn(c) * 0.5
+    res = torch.randn(n, c)
+    hid = F.gelu(x.float() @ w1.float().t() + b1).bfloat16().float()
+    ref = hid @ w2.float().t() + b2
+    assert ops.mlp_fused_supported(c, h) and not ops.mlp_fused_supported(128, 512)
+    w1p, w2p = ops.pack_kmajor(w1.cuda(), 128), ops.pack_kmajor(w2.cuda(), c)
+    r, r16 = ops.mlp_fused(x.cuda(), w1p, b1.cuda(), w2p, b2.cuda(), h, residual=res.cuda())
+    assert rel_l2(r - res.cuda(), ref) < 4e-3, rel_l2(r - res.cuda(), ref)
+    assert torch.equal(r16, r.bfloat16())
+    r2, r216 = ops.mlp_fused(x.cuda(), w1p, b1.cuda(), w2p, b2.cuda(), h, residual=None, want_res=False)
+    assert r2 is None and rel_l2(r216, ref) < 6e-3
+
+
 def test_attention_golden(golden):
     """Reference SerializedAttention.forward (dense branch, one scene) frozen in tests/golden/attention.npz."""
     from ptv3_b200 import ops
