@@ -56,7 +56,7 @@ __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr)
 }
 
 // smem: K [kpad][16] bf16 then V [kpad][16] bf16, kpad = keys rounded up to 64
-__global__ void __launch_bounds__(kThreads, 2) attn_window_mma_kernel(
+__global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
     const __nv_bfloat16* __restrict__ qkv, const int64_t* __restrict__ order, const int64_t* __restrict__ windows,
     const int64_t* __restrict__ n_windows, int h, float scale_log2, int kpad_max, __nv_bfloat16* __restrict__ out) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
