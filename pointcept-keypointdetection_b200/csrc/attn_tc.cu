@@ -99,7 +99,9 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
   const uint32_t v_lane_off = (uint32_t)(((((lane >> 3) & 1) << 3) + (lane & 7)) * 32 + (lane >> 4) * 16);
   const uint32_t ones = 0x3f803f80u;  // bf16 (1.0, 1.0)
 
-  for (int qt = warp; qt < n_qtiles; qt += kWarps) {
+  // blockIdx.z splits the query tiles of one (window, head) over gridDim.z CTAs (each stages K/V itself): finer
+  // granularity for launches whose CTA count is a small non-integer number of waves
+  for (int qt = warp * (int)gridDim.z + (int)blockIdx.z; qt < n_qtiles; qt += kWarps * (int)gridDim.z) {
     // ---- Q fragment (A operand, 16 x 16) straight from global ----
     const int64_t qi0 = (int64_t)qt * 16 + g, qi1 = qi0 + 8;
     const bool v0 = qi0 < ql, v1 = qi1 < ql;
@@ -193,6 +195,8 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
   }
 }
 
+int g_attn_qsplit = 0;   // 0 = auto; debug slot 2 forces 1 / 2 / 4
+
 int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                    int64_t n_windows_max, int64_t max_len, int64_t n, int h, float scale, __nv_bfloat16* out,
                    cudaStream_t st) {
@@ -207,7 +211,20 @@ int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
       return PTV3_ELAUNCH;
     configured = smem;
   }
-  dim3 grid((unsigned)n_windows_max, (unsigned)h);
+  // query split: pick s in {1,2,4} that minimises ceil(waves) / s-scaled work (3 CTAs per SM resident)
+  int split = g_attn_qsplit;
+  if (split <= 0) {
+    const double slots = 3.0 * kNumSMs;
+    double best = 1e30;
+    split = 1;
+    for (int s = 1; s <= 4; s *= 2) {
+      const double ctas = (double)n_windows_max * h * s;
+      // time ~ waves * (compute per CTA / s + K/V staging); staging is ~4 % of a full CTA's work
+      const double t = ceil(ctas / slots) * (1.0 / s + 0.04);
+      if (t < best - 1e-9) { best = t; split = s; }
+    }
+  }
+  dim3 grid((unsigned)n_windows_max, (unsigned)h, (unsigned)split);
   attn_window_mma_kernel<<<grid, kThreads, smem, st>>>(qkv, order, windows, n_windows, h,
                                                        scale * 1.4426950408889634f, kpad, out);
   return check_launch();

@@ -12,6 +12,7 @@
 //   MMA:          one elected thread issues 4 x tcgen05.mma (M128, N=NT, K16), accumulator in TMEM (NT columns).
 // K-blocks whose offsets have no present neighbour anywhere in the 128-row tile are skipped.
 // Epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> + bias -> bf16 -> 64-byte row segments to HBM.
+#include <cstdlib>
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -23,7 +24,6 @@ constexpr int TM = 128;          // output rows per CTA (UMMA M)
 constexpr int KBLK = 64;         // bf16 per K-block (one 128-byte swizzle row)
 constexpr int A_BYTES = TM * KBLK * 2;
 constexpr int MAX_K3 = 27;
-constexpr int PRODUCERS = 256;   // 8 gather warps
 
 static inline int n_kblocks(int c_in, int k3) { return (k3 * c_in + KBLK - 1) / KBLK; }
 static inline int pick_nt(int c_out) { return c_out >= 256 ? 256 : c_out; }
@@ -77,21 +77,34 @@ struct ConvSmem {
   static constexpr int DYN_BYTES = TOTAL + 1024;                 // slack for the 1024-byte alignment
 };
 
-constexpr int kConvThreads = 416;  // warps 0-7 producers, warp 8 MMA issuer, warps 9-12 epilogue
-constexpr int kMmaWarp = 8;
+int g_conv_async = 1;   // debug slot 3 / PTV3_CONV_ASYNC: bit 0 = gather copies arrive on the stage barrier themselves (default); 0 = wait + fence + arrive; bits 4.. = timing ablations
 
-__device__ __forceinline__ void producers_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+constexpr int kGatherWarps = 16;
+constexpr int kGatherGroups = 4;                       // K-block g is filled by the 4 warps of group g % 4
+constexpr int kWarpsPerGroup = kGatherWarps / kGatherGroups;
+constexpr int kRowsPerWarp = TM / kWarpsPerGroup;      // 32 rows of the A stage per warp
+constexpr int kSlots = kRowsPerWarp / 4;               // 16-byte slots per lane and K-block
+constexpr int PRODUCERS = kGatherWarps * 32;
+constexpr int kMmaWarp = kGatherWarps;                 // warp 16: MMA issuer; warps 17-20: epilogue
+constexpr int kConvThreads = (kGatherWarps + 5) * 32;  // 672
+
+__device__ __forceinline__ void producers_sync() { asm volatile("bar.sync 1, %0;" ::"n"(PRODUCERS) : "memory"); }
 
 // Persistent: CTA b handles row tiles b, b + gridDim.x, ...  The three roles run decoupled through mbarriers, so the
 // gather of tile i+1 (and the bulk prefetch of its neighbour rows) overlaps the MMAs of tile i and the epilogue of
 // tile i-1 (two accumulators in TMEM).
-template <int NT, int STAGES, int LAG>
+//
+// Gather warps: K-block number g (a CTA-wide running count over tiles) belongs to warp group g % 4; its four warps
+// fill 32 rows of the 128 x 64 A stage each (8 slots per lane), wait for their own copies and arrive.  Four K-blocks
+// are therefore in flight, and the per-K-block bookkeeping (stage acquire, fence, arrive) is paid by 4 warps, not 16.
+template <int NT, int STAGES, bool ASYNC>
 __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __nv_bfloat16* __restrict__ in,
                                                                        const __nv_bfloat16* __restrict__ packed,
                                                                        const float* __restrict__ bias,
                                                                        const int32_t* __restrict__ nbr, int64_t n,
                                                                        int c_in, int c_out, int k3, int n_kb_total,
-                                                                       int n_tiles, __nv_bfloat16* __restrict__ out) {
+                                                                       int n_tiles, __nv_bfloat16* __restrict__ out,
+                                                                       int dbg) {
   using L = ConvSmem<NT, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -106,13 +119,15 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
   auto acc_full = [&](int b) { return bar_base + 8u * (2 * STAGES + 2 + b); };
   auto acc_free = [&](int b) { return bar_base + 8u * (2 * STAGES + 4 + b); };
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform for nvcc (role branches)
   const int nt_tile = blockIdx.y;
   const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(full_bar(s), PRODUCERS);
+      // one arrive per warp of the owning group (per lane when the copies arrive themselves) + the weight tx bytes
+      mbar_init(full_bar(s), ASYNC ? kWarpsPerGroup * 32 : kWarpsPerGroup);
       mbar_init(empty_bar(s), 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -130,26 +145,39 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp < kMmaWarp) {
-    // =========================== producers ===========================
-    const int c = tid & 7, r0 = tid >> 3;
+    // =========================== gather warps ===========================
+    const int c = lane & 7, rr = lane >> 3;   // lane -> (16-byte chunk, row within a group of 4)
+    const int group = warp / kWarpsPerGroup, wg = warp % kWarpsPerGroup;
+    // byte offsets of this lane's slot inside an 8-row / 1024-byte swizzle group, for even and odd passes
+    const uint32_t off_even = (uint32_t)(rr * 128 + ((c ^ rr) << 4));
+    const uint32_t off_odd = (uint32_t)((4 + rr) * 128 + ((c ^ (4 + rr)) << 4));
     const char* wtile = reinterpret_cast<const char*>(packed) + (int64_t)nt_tile * n_kb_total * L::B_BYTES;
     const uint32_t nbr_tile_bytes = (uint32_t)(TM * k3 * 4);
+    const uint32_t nbr_step = (uint32_t)(16 * k3);   // 4 rows further in the neighbour tile
+    const uint32_t row_bytes = (uint32_t)c_in * 2u;
     auto tile_full = [&](int i) { return ((int64_t)(blockIdx.x + (int64_t)i * gridDim.x) + 1) * TM <= n; };
-    auto prefetch_nbr = [&](int i) {   // thread 0 only: bulk copy of a full tile's neighbour rows
+    auto prefetch_nbr = [&](int i) {   // one elected thread of warp 0: bulk copy of a full tile's neighbour rows
       const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
       mbar_arrive_expect_tx(nbr_full(i & 1), nbr_tile_bytes);
       bulk_g2s(s_base + L::NBR_OFF + (i & 1) * L::NBR_BYTES, nbr + row0 * k3, nbr_tile_bytes, nbr_full(i & 1));
     };
-    if (tid == 0 && my_tiles > 0 && tile_full(0)) prefetch_nbr(0);
-    uint32_t g = 0;  // global K-block counter of this CTA
+    const char* last_ptr = reinterpret_cast<const char*>(in);   // ASYNC: target of zero-byte copies
+    if (warp == 0 && my_tiles > 0 && tile_full(0)) {
+      if (elect_one_sync()) prefetch_nbr(0);
+      __syncwarp();
+    }
+    uint32_t g0 = 0;  // K-blocks issued by this CTA before the current tile (identical in every gather warp)
     for (int i = 0; i < my_tiles; ++i) {
       const int tb = i & 1;
       const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
       int32_t* nbr_s = reinterpret_cast<int32_t*>(smem + L::NBR_OFF + tb * L::NBR_BYTES);
-      if (tid == 0) {
-        masks[(i + 2) & 3] = 0;
-        if (i + 1 < my_tiles && tile_full(i + 1)) prefetch_nbr(i + 1);   // buffer tb^1 was released by the
-      }                                                                  // producers_sync() that ended tile i-1
+      if (warp == 0) {
+        if (elect_one_sync()) {
+          masks[(i + 2) & 3] = 0;
+          if (i + 1 < my_tiles && tile_full(i + 1)) prefetch_nbr(i + 1);   // buffer tb^1 was released by the
+        }                                                                  // producers_sync() that ended tile i-1
+        __syncwarp();
+      }
       if (tile_full(i)) {
         mbar_wait(nbr_full(tb), (uint32_t)(i >> 1) & 1u);
       } else {  // ragged last tile: plain loads, -1 beyond n
@@ -178,65 +206,88 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
         for (int kb = 0; kb < n_kb_total; ++kb) blk_mask |= (((mask >> (2 * kb)) & 3u) ? 1u : 0u) << kb;
       }
       const int n_kb = __popc(blk_mask) * per;
-      int done = 0;
-      while (blk_mask) {
+      // this group's K-blocks of the tile: done = first, first + 4, ...  (done counts K-blocks in mask-bit order)
+      int popped = 0;   // set bits of blk_mask already dropped
+      for (int done = (int)((uint32_t)(group + kGatherGroups - (int)(g0 % kGatherGroups)) % kGatherGroups); done < n_kb;
+           done += kGatherGroups) {
+        const int jidx = done / per, cb = done - jidx * per;
+        while (popped < jidx) {
+          blk_mask &= blk_mask - 1;
+          ++popped;
+        }
         const int j = __ffs(blk_mask) - 1;
-        blk_mask &= blk_mask - 1;
-        for (int cb = 0; cb < per; ++cb, ++g, ++done) {
-          const int s = g % STAGES;
-          const uint32_t ph = (g / STAGES) & 1u;
-          mbar_wait(empty_bar(s), ph ^ 1u);
-          const int kb = j * per + cb;
-          const uint32_t a_s = s_base + s * L::STAGE_BYTES;
-          if (tid == 0) {
-            stage_flag[s] = (done == 0 ? 1u : 0u) | (done == n_kb - 1 ? 2u : 0u) |
-                            ((done == n_kb - 1 && i == my_tiles - 1) ? 4u : 0u);
+        const uint32_t g = g0 + (uint32_t)done;
+        const int s = (int)(g % STAGES);
+        if (dbg & 16) mbar_wait_spin(empty_bar(s), ((g / STAGES) & 1u) ^ 1u);
+        else mbar_wait(empty_bar(s), ((g / STAGES) & 1u) ^ 1u);
+        const int kb = j * per + cb;
+        const uint32_t a_s = s_base + s * L::STAGE_BYTES;
+        if (wg == 0 && elect_one_sync()) {
+          stage_flag[s] = (done == 0 ? 1u : 0u) | (done == n_kb - 1 ? 2u : 0u) |
+                          ((done == n_kb - 1 && i == my_tiles - 1) ? 4u : 0u);
+          if (!(dbg & 1)) {
             mbar_expect_tx(full_bar(s), L::B_BYTES);
             bulk_g2s(a_s + A_BYTES, wtile + (int64_t)kb * L::B_BYTES, L::B_BYTES, full_bar(s));
           }
-          int k, ch;
-          if (c_in >= KBLK) {
-            k = j;
-            ch = cb * KBLK + c * 8;
-          } else {
-            k = 2 * j + (c >> 2);
-            ch = (c & 3) * 8;
+        }
+        int k, ch;
+        if (c_in >= KBLK) {
+          k = j;
+          ch = cb * KBLK + c * 8;
+        } else {
+          k = 2 * j + (c >> 2);
+          ch = (c & 3) * 8;
+        }
+        const bool k_ok = k < k3 && !(dbg & 2);
+        const char* in_ch = reinterpret_cast<const char*>(in) + ch * 2;
+        const uint32_t np = nbr_sa + (uint32_t)((wg * kRowsPerWarp + rr) * k3 + k) * 4u;
+        const uint32_t a_w = a_s + (uint32_t)(wg * (kRowsPerWarp / 8)) * 1024u;
+        int src[kSlots];
+#pragma unroll
+        for (int u = 0; u < kSlots; ++u) src[u] = k_ok ? ld_shared_s32(np + (uint32_t)u * nbr_step) : -1;
+        if constexpr (ASYNC) {
+          // every slot is a cp.async (absent neighbours: zero source bytes = zero fill, aimed at the last address
+          // this lane really read so the ignored requests do not pile up on one line); the mbarrier arrival is
+          // triggered by the copies themselves, so the warp moves on without waiting
+#pragma unroll
+          for (int u = 0; u < kSlots; ++u) {
+            const uint32_t dst = a_w + (uint32_t)(u >> 1) * 1024u + ((u & 1) ? off_odd : off_even);
+            const bool ok = src[u] >= 0;
+            if (ok) last_ptr = in_ch + (uint64_t)(uint32_t)src[u] * row_bytes;
+            cp_async16(dst, last_ptr, ok ? 16u : 0u);
           }
-          const bool k_ok = k < k3;
-          int src[4];
+          cp_async_mbar_arrive_noinc(full_bar(s));
+        } else {
 #pragma unroll
-          for (int q = 0; q < 4; ++q)   // four independent shared loads, then the (divergent) copies
-            src[q] = k_ok ? ld_shared_s32(nbr_sa + (uint32_t)((r0 + 32 * q) * k3 + k) * 4u) : -1;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int r = r0 + 32 * q;
-            const uint32_t dst = a_s + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4);
-            if (src[q] >= 0)   // absent neighbours are zeroed with a plain shared store: a zero-size cp.async would
-              cp_async16(dst, in + (int64_t)src[q] * c_in + ch, 16u);   // still send a request for one hot address
+          for (int u = 0; u < kSlots; ++u) {
+            const uint32_t dst = a_w + (uint32_t)(u >> 1) * 1024u + ((u & 1) ? off_odd : off_even);
+            if (src[u] >= 0)   // absent neighbours are zeroed with a plain shared store
+              cp_async16(dst, in_ch + (uint64_t)(uint32_t)src[u] * row_bytes, 16u);
             else
               st_shared_zero16(dst);
           }
           cp_async_commit();
-          if (g >= (uint32_t)LAG) {
-            cp_async_wait<LAG>();
-            fence_proxy_async();
-            mbar_arrive(full_bar((g - LAG) % STAGES));
-          }
+          // blocking hand-over: the other three groups keep their K-blocks in flight meanwhile, and a warp never
+          // holds an un-arrived stage at a barrier or while it waits for another stage
+          cp_async_wait<0>();
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full_bar(s));
         }
       }
+      g0 += (uint32_t)n_kb;
       producers_sync();   // everyone is done reading nbr_s[tb]: it may be refilled for tile i+2
     }
-    cp_async_wait<0>();
-    fence_proxy_async();
-    for (uint32_t q = (g > (uint32_t)LAG ? g - LAG : 0); q < g; ++q) mbar_arrive(full_bar(q % STAGES));
   } else if (warp == kMmaWarp) {
-    // =========================== MMA issuer (one thread) ===========================
-    if (lane == 0 && my_tiles > 0) {
+    // =========================== MMA issuer ===========================
+    // The whole warp runs the loop (uniform control flow, values in uniform registers); one elected lane issues.
+    // Issuing from inside `if (lane == 0)` instead makes nvcc wrap every tcgen05 instruction in an ELECT / R2UR /
+    // BRA.U.ANY loop: ~135 instructions per K-block on a single thread, which bounded the whole kernel.
+    if (my_tiles > 0) {
       constexpr uint32_t idesc = idesc_bf16_f32(TM, NT);
-      uint32_t g = 0, t = 0;
+      uint32_t s = 0, ph = 0, t = 0;
       while (true) {
-        const int s = g % STAGES;
-        mbar_wait(full_bar(s), (g / STAGES) & 1u);
+        mbar_wait(full_bar(s), ph);
         fence_after_sync();
         const uint32_t flag = stage_flag[s];
         const uint32_t ab = t & 1u;
@@ -244,18 +295,25 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
           mbar_wait(acc_free(ab), ((t >> 1) & 1u) ^ 1u);
           fence_after_sync();
         }
-        const uint32_t a_s = s_base + s * L::STAGE_BYTES;
-        const uint64_t a_desc = smem_desc_sw128(a_s);
-        const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
+        if (elect_one_sync()) {
+          const uint32_t a_s = s_base + s * L::STAGE_BYTES;
+          const uint64_t a_desc = smem_desc_sw128(a_s);
+          const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
+          const int n_mma = (dbg & 4) ? 1 : KBLK / 16;
 #pragma unroll
-        for (int kk = 0; kk < KBLK / 16; ++kk)
-          mma_bf16_ss(tmem_base + ab * NT, a_desc + 2 * kk, b_desc + 2 * kk, idesc, ((flag & 1u) && kk == 0) ? 0u : 1u);
-        mma_commit(empty_bar(s));
-        if (flag & 2u) {
-          mma_commit(acc_full(ab));
-          ++t;
+          for (int kk = 0; kk < KBLK / 16; ++kk)
+            if (kk < n_mma)
+              mma_bf16_ss(tmem_base + ab * NT, a_desc + 2 * kk, b_desc + 2 * kk, idesc,
+                          ((flag & 1u) && kk == 0) ? 0u : 1u);
+          mma_commit(empty_bar(s));
+          if (flag & 2u) mma_commit(acc_full(ab));
         }
-        ++g;
+        __syncwarp();
+        if (flag & 2u) ++t;
+        if (++s == STAGES) {
+          s = 0;
+          ph ^= 1u;
+        }
         if (flag & 4u) break;
       }
     }
@@ -276,7 +334,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
           fence_before_sync();
           mbar_arrive(acc_free(ab));
         }
-        if (row < n) {
+        if (row < n && !(dbg & 8)) {
           const int co0 = nt_tile * NT + cb;
           uint32_t pk[16];
 #pragma unroll
@@ -298,15 +356,18 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
   if (warp == kMmaWarp) tmem_dealloc<2 * NT>(tmem_base);
 }
 
-template <int NT, int STAGES, int LAG>
+template <int NT, int STAGES>
 static int launch_conv(const __nv_bfloat16* in, const __nv_bfloat16* packed, const float* bias, const int32_t* nbr,
                        int64_t n, int c_in, int c_out, int k3, __nv_bfloat16* out, cudaStream_t st) {
   using L = ConvSmem<NT, STAGES>;
-  static_assert(STAGES <= 8 && LAG < STAGES, "ring");
+  static_assert(STAGES <= 8, "ring");
   static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
   static bool configured = false;
   if (!configured) {
-    cudaFuncSetAttribute(subm_conv_tc_kernel<NT, STAGES, LAG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (const char* e = getenv("PTV3_CONV_ASYNC")) g_conv_async = atoi(e);
+    cudaFuncSetAttribute(subm_conv_tc_kernel<NT, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         L::DYN_BYTES);
+    cudaFuncSetAttribute(subm_conv_tc_kernel<NT, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          L::DYN_BYTES);
     configured = true;
   }
@@ -315,8 +376,12 @@ static int launch_conv(const __nv_bfloat16* in, const __nv_bfloat16* packed, con
   int gx = kNumSMs / ny;
   if (gx > n_tiles) gx = n_tiles;
   dim3 grid((unsigned)gx, (unsigned)ny);
-  subm_conv_tc_kernel<NT, STAGES, LAG><<<grid, kConvThreads, L::DYN_BYTES, st>>>(
-      in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out);
+  if (g_conv_async & 1)
+    subm_conv_tc_kernel<NT, STAGES, true><<<grid, kConvThreads, L::DYN_BYTES, st>>>(
+        in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out, g_conv_async >> 4);
+  else
+    subm_conv_tc_kernel<NT, STAGES, false><<<grid, kConvThreads, L::DYN_BYTES, st>>>(
+        in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out, g_conv_async >> 4);
   return check_launch();
 }
 
@@ -332,10 +397,10 @@ int subm_conv_tc_packed(const __nv_bfloat16* in, const __nv_bfloat16* packed, co
                         int64_t n, int c_in, int c_out, int k3, __nv_bfloat16* out, cudaStream_t st) {
   if (!subm_conv_tc_supported(c_in, c_out, k3)) return PTV3_EUNSUPPORTED;
   switch (pick_nt(c_out)) {
-    case 32: return launch_conv<32, 8, 5>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
-    case 64: return launch_conv<64, 7, 4>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
-    case 128: return launch_conv<128, 5, 3>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
-    default: return launch_conv<256, 4, 2>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    case 32: return launch_conv<32, 8>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    case 64: return launch_conv<64, 7>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    case 128: return launch_conv<128, 5>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
+    default: return launch_conv<256, 4>(in, packed, bias, nbr, n, c_in, c_out, k3, out, st);
   }
 }
 
