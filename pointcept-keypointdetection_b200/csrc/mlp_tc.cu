@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
   // 0 w_full | 1,2 a1_full | 3,4 a1_free | 5,6 d1_full | 7,8 d1_free | 9,10 a2_full | 11,12 a2_free | 13,14 d2_full
   // | 15,16 d2_free
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::BAR_OFF + 200);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);   // provably warp-uniform for nvcc (role branches)
   const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (tid == 0) {
@@ -154,7 +155,9 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
     }
   } else if (warp == 2) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
+    // The whole warp runs the (uniform) control flow and waits; one elected lane issues.  Issuing from inside
+    // `if (lane == 0)` makes nvcc wrap every tcgen05 instruction in an ELECT / R2UR / BRA.U.ANY loop.
+    {
       constexpr uint32_t idesc1 = idesc_bf16_f32(TM, HB), idesc2 = idesc_bf16_f32(TM, C);
       mbar_wait(bar(0), 0);
       uint32_t c1 = 0, c2 = 0;
@@ -167,13 +170,16 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
             const uint32_t bb = c1 & 1u;
             mbar_wait(bar(7 + bb), ((c1 >> 1) & 1u) ^ 1u);
             fence_after_sync();
-            const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + ab * L::A1_BYTES);
-            const uint64_t b_desc = smem_desc_sw128(sb + L::W1_OFF + hb * HB * 128);
+            if (elect_one_sync()) {
+              const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + ab * L::A1_BYTES);
+              const uint64_t b_desc = smem_desc_sw128(sb + L::W1_OFF + hb * HB * 128);
 #pragma unroll
-            for (int kk = 0; kk < C / 16 && kk < 4; ++kk)
-              mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc1, kk ? 1u : 0u);
-            mma_commit(bar(5 + bb));
-            if (hb == L::NHB - 1) mma_commit(bar(3 + ab));   // X tile fully consumed
+              for (int kk = 0; kk < C / 16 && kk < 4; ++kk)
+                mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc1, kk ? 1u : 0u);
+              mma_commit(bar(5 + bb));
+              if (hb == L::NHB - 1) mma_commit(bar(3 + ab));   // X tile fully consumed
+            }
+            __syncwarp();
             ++c1;
           }
           if (hb >= 1) {
@@ -182,16 +188,19 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
             mbar_wait(bar(9 + bb), (c2 >> 1) & 1u);
             if (h2 == 0) mbar_wait(bar(15 + ab), tph ^ 1u);   // D2[ab] drained by the epilogue of tile i-2
             fence_after_sync();
+            if (elect_one_sync()) {
 #pragma unroll
-            for (int kb = 0; kb < 2; ++kb) {
-              const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
-              const uint64_t b_desc = smem_desc_sw128(sb + L::W2_OFF + (2 * h2 + kb) * L::W2_TILE);
+              for (int kb = 0; kb < 2; ++kb) {
+                const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
+                const uint64_t b_desc = smem_desc_sw128(sb + L::W2_OFF + (2 * h2 + kb) * L::W2_TILE);
 #pragma unroll
-              for (int kk = 0; kk < 4; ++kk)
-                mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc2, (h2 | kb | kk) ? 1u : 0u);
+                for (int kk = 0; kk < 4; ++kk)
+                  mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc2, (h2 | kb | kk) ? 1u : 0u);
+              }
+              mma_commit(bar(11 + bb));
+              if (h2 == L::NHB - 1) mma_commit(bar(13 + ab));
             }
-            mma_commit(bar(11 + bb));
-            if (h2 == L::NHB - 1) mma_commit(bar(13 + ab));
+            __syncwarp();
             ++c2;
           }
         }

@@ -77,7 +77,7 @@ struct ConvSmem {
   static constexpr int DYN_BYTES = TOTAL + 1024;                 // slack for the 1024-byte alignment
 };
 
-int g_conv_async = 1;   // debug slot 3 / PTV3_CONV_ASYNC: bit 0 = gather copies arrive on the stage barrier themselves (default); 0 = wait + fence + arrive; bits 4.. = timing ablations
+int g_conv_async = 1;   // debug slot 3 / PTV3_CONV_ASYNC: 1 = gather copies arrive on the stage barrier themselves (default), 0 = wait + fence + arrive
 
 constexpr int kGatherWarps = 16;
 constexpr int kGatherGroups = 4;                       // K-block g is filled by the 4 warps of group g % 4
@@ -103,15 +103,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
                                                                        const float* __restrict__ bias,
                                                                        const int32_t* __restrict__ nbr, int64_t n,
                                                                        int c_in, int c_out, int k3, int n_kb_total,
-                                                                       int n_tiles, __nv_bfloat16* __restrict__ out,
-                                                                       int dbg) {
+                                                                       int n_tiles, __nv_bfloat16* __restrict__ out) {
   using L = ConvSmem<NT, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t s_base = smem_u32(smem);
-  uint32_t* stage_flag = reinterpret_cast<uint32_t*>(smem + L::MISC_OFF);        // [STAGES] (<= 8)
   uint32_t* masks = reinterpret_cast<uint32_t*>(smem + L::MISC_OFF + 64);        // [4]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::MISC_OFF + 128);
+  volatile uint32_t* tile_nkb = reinterpret_cast<volatile uint32_t*>(smem + L::MISC_OFF + 160);   // [16] K-blocks per tile
   const uint32_t bar_base = s_base + L::BAR_OFF;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
@@ -206,6 +205,10 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
         for (int kb = 0; kb < n_kb_total; ++kb) blk_mask |= (((mask >> (2 * kb)) & 3u) ? 1u : 0u) << kb;
       }
       const int n_kb = __popc(blk_mask) * per;
+      // every gather warp stores the same value before it issues (and arrives for) any K-block of this tile, so the
+      // MMA warp, which reads it after the tile's first full barrier, always sees it
+      if (lane == 0) tile_nkb[i & 15] = (uint32_t)n_kb;
+      __syncwarp();
       // this group's K-blocks of the tile: done = first, first + 4, ...  (done counts K-blocks in mask-bit order)
       int popped = 0;   // set bits of blk_mask already dropped
       for (int done = (int)((uint32_t)(group + kGatherGroups - (int)(g0 % kGatherGroups)) % kGatherGroups); done < n_kb;
@@ -218,17 +221,12 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
         const int j = __ffs(blk_mask) - 1;
         const uint32_t g = g0 + (uint32_t)done;
         const int s = (int)(g % STAGES);
-        if (dbg & 16) mbar_wait_spin(empty_bar(s), ((g / STAGES) & 1u) ^ 1u);
-        else mbar_wait(empty_bar(s), ((g / STAGES) & 1u) ^ 1u);
+        mbar_wait(empty_bar(s), ((g / STAGES) & 1u) ^ 1u);
         const int kb = j * per + cb;
         const uint32_t a_s = s_base + s * L::STAGE_BYTES;
         if (wg == 0 && elect_one_sync()) {
-          stage_flag[s] = (done == 0 ? 1u : 0u) | (done == n_kb - 1 ? 2u : 0u) |
-                          ((done == n_kb - 1 && i == my_tiles - 1) ? 4u : 0u);
-          if (!(dbg & 1)) {
-            mbar_expect_tx(full_bar(s), L::B_BYTES);
-            bulk_g2s(a_s + A_BYTES, wtile + (int64_t)kb * L::B_BYTES, L::B_BYTES, full_bar(s));
-          }
+          mbar_expect_tx(full_bar(s), L::B_BYTES);
+          bulk_g2s(a_s + A_BYTES, wtile + (int64_t)kb * L::B_BYTES, L::B_BYTES, full_bar(s));
         }
         int k, ch;
         if (c_in >= KBLK) {
@@ -238,7 +236,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
           k = 2 * j + (c >> 2);
           ch = (c & 3) * 8;
         }
-        const bool k_ok = k < k3 && !(dbg & 2);
+        const bool k_ok = k < k3;
         const char* in_ch = reinterpret_cast<const char*>(in) + ch * 2;
         const uint32_t np = nbr_sa + (uint32_t)((wg * kRowsPerWarp + rr) * k3 + k) * 4u;
         const uint32_t a_w = a_s + (uint32_t)(wg * (kRowsPerWarp / 8)) * 1024u;
@@ -285,36 +283,36 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
     // BRA.U.ANY loop: ~135 instructions per K-block on a single thread, which bounded the whole kernel.
     if (my_tiles > 0) {
       constexpr uint32_t idesc = idesc_bf16_f32(TM, NT);
-      uint32_t s = 0, ph = 0, t = 0;
-      while (true) {
-        mbar_wait(full_bar(s), ph);
-        fence_after_sync();
-        const uint32_t flag = stage_flag[s];
-        const uint32_t ab = t & 1u;
-        if (flag & 1u) {   // first K-block of a tile: its accumulator must have been drained by the epilogue
-          mbar_wait(acc_free(ab), ((t >> 1) & 1u) ^ 1u);
+      uint32_t s = 0, ph = 0;   // ring position: uniform loop counters, so descriptors stay in uniform registers
+      bool ready = false;               // full barrier of stage s already seen complete (peeked during the last K-block)
+      for (int i = 0; i < my_tiles; ++i) {
+        const uint32_t ab = (uint32_t)i & 1u;
+        int n_kb = 1;
+        for (int kbi = 0; kbi < n_kb; ++kbi) {
+          if (!ready) mbar_wait(full_bar(s), ph);
           fence_after_sync();
-        }
-        if (elect_one_sync()) {
-          const uint32_t a_s = s_base + s * L::STAGE_BYTES;
-          const uint64_t a_desc = smem_desc_sw128(a_s);
-          const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
-          const int n_mma = (dbg & 4) ? 1 : KBLK / 16;
+          if (kbi == 0) {   // first K-block of the tile: tile_nkb[i] was written before it was issued
+            n_kb = ld_shared_s32(s_base + L::MISC_OFF + 160 + 4u * ((uint32_t)i & 15u));
+            mbar_wait(acc_free(ab), (((uint32_t)i >> 1) & 1u) ^ 1u);   // accumulator drained by the epilogue (tile i-2)
+            fence_after_sync();
+          }
+          // peek at the next stage before issuing: the poll's latency hides behind the MMAs
+          const uint32_t s1 = (s + 1 == STAGES) ? 0u : s + 1;
+          const uint32_t ph1 = (s + 1 == STAGES) ? (ph ^ 1u) : ph;
+          ready = mbar_test_wait(full_bar(s1), ph1);
+          if (elect_one_sync()) {
+            const uint32_t a_s = s_base + s * L::STAGE_BYTES;
+            const uint64_t a_desc = smem_desc_sw128(a_s);
+            const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
 #pragma unroll
-          for (int kk = 0; kk < KBLK / 16; ++kk)
-            if (kk < n_mma)
-              mma_bf16_ss(tmem_base + ab * NT, a_desc + 2 * kk, b_desc + 2 * kk, idesc,
-                          ((flag & 1u) && kk == 0) ? 0u : 1u);
-          mma_commit(empty_bar(s));
-          if (flag & 2u) mma_commit(acc_full(ab));
+            for (int kk = 0; kk < KBLK / 16; ++kk)
+              mma_bf16_ss(tmem_base + ab * NT, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (kbi > 0 || kk > 0) ? 1u : 0u);
+            mma_commit(empty_bar(s));
+            if (kbi == n_kb - 1) mma_commit(acc_full(ab));
+          }
+          s = s1;
+          ph = ph1;
         }
-        __syncwarp();
-        if (flag & 2u) ++t;
-        if (++s == STAGES) {
-          s = 0;
-          ph ^= 1u;
-        }
-        if (flag & 4u) break;
       }
     }
   } else {
@@ -322,7 +320,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
     const int q4 = warp & 3;   // TMEM lane quarter this warp may access
     for (int i = 0; i < my_tiles; ++i) {
       const uint32_t ab = (uint32_t)i & 1u;
-      mbar_wait(acc_full(ab), (uint32_t)(i >> 1) & 1u);
+      mbar_wait_sleep(acc_full(ab), (uint32_t)(i >> 1) & 1u, 128);
       fence_after_sync();
       const int64_t row = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + q4 * 32 + lane;
 #pragma unroll 1
@@ -334,7 +332,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
           fence_before_sync();
           mbar_arrive(acc_free(ab));
         }
-        if (row < n && !(dbg & 8)) {
+        if (row < n) {
           const int co0 = nt_tile * NT + cb;
           uint32_t pk[16];
 #pragma unroll
@@ -378,10 +376,10 @@ static int launch_conv(const __nv_bfloat16* in, const __nv_bfloat16* packed, con
   dim3 grid((unsigned)gx, (unsigned)ny);
   if (g_conv_async & 1)
     subm_conv_tc_kernel<NT, STAGES, true><<<grid, kConvThreads, L::DYN_BYTES, st>>>(
-        in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out, g_conv_async >> 4);
+        in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out);
   else
     subm_conv_tc_kernel<NT, STAGES, false><<<grid, kConvThreads, L::DYN_BYTES, st>>>(
-        in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out, g_conv_async >> 4);
+        in, packed, bias, nbr, n, c_in, c_out, k3, n_kblocks(c_in, k3), n_tiles, out);
   return check_launch();
 }
 

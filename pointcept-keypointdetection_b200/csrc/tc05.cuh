@@ -47,6 +47,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// long waits off the critical path (an epilogue waiting for a whole tile): back off between polls so the spinning
+// warp does not take issue slots from the MMA / gather warps on its scheduler
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, unsigned ns) {
+  while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
 // non-suspending poll (mbarrier.test_wait): for waits on the critical path of a short ring
 __device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;

@@ -35,8 +35,7 @@ def run(label, steps=8):
           flush=True)
 
 
-cfgs = [a for a in sys.argv[1:]] or ["base", "curve0", "split1", "curve0+split1"]
+cfgs = [a for a in sys.argv[1:]] or ["base"]
 for c in cfgs:
-    model.backbone.curve_order = "curve0" not in c
     lib.ptv3_debug_set(2, 1 if "split1" in c else (2 if "split2" in c else (4 if "split4" in c else 0)))
     run(c)
