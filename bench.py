@@ -152,10 +152,28 @@ def run_ours(args):
     def step_resident():
         return model(dict(resident))["pred"]
 
+    # e2e: every step copies ITS inputs from pinned host memory and reads ITS keypoints back.  The copy of step i+1
+    # runs on a side stream while step i computes (double-buffered device inputs); all of it is inside the timed region.
+    copy_stream = torch.cuda.Stream(device=device)
+    staged = {}
+
+    def stage_inputs():
+        with torch.cuda.stream(copy_stream):
+            d = {k: v.to(device, non_blocking=True) for k, v in pinned.items()}
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        staged["next"] = (d, ev)
+
     def step_e2e():
-        d = {k: v.to(device, non_blocking=True) for k, v in pinned.items()}
+        if "next" not in staged:
+            stage_inputs()
+        d, ev = staged.pop("next")
+        torch.cuda.current_stream().wait_event(ev)
+        for v in d.values():
+            v.record_stream(torch.cuda.current_stream())
+        stage_inputs()                                                    # H2D of the next step overlaps this one
         pred = model(d)["pred"]
-        kp = aggregate_keypoints(d["coord"], pred, d["offset"])            # (scenes, 6, 3) on device
+        kp = aggregate_keypoints(d["coord"], pred, d["offset"])            # (scenes, 6, 3) on device, one kernel
         return kp.cpu()                                                   # D2H read of the step's result
 
     def barrier():
@@ -195,6 +213,7 @@ def run_ours(args):
     for _ in range(2):
         step_e2e()
     _, e2e_wall, kp = timed(step_e2e, args.steps)
+    staged.clear()
     d2h_bytes = int(kp.numel() * kp.element_size())
 
     total_vox = torch.tensor([n_vox], device=device, dtype=torch.float64)

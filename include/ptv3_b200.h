@@ -223,6 +223,17 @@ int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float
                      const float* residual, float* res_out, const float* gamma2, const float* beta2, void* out2,
                      int dtype_out2, int64_t n, int c, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * A9  keypoint aggregation of the offset head (tools/infer_offset.py:366-399, the evaluator's
+ * hooks/offset_keypoint_evaluator.py:46-91 uses the same rule): per scene b and keypoint k
+ *   votes[i,k] = coord[i] + pred[i,k,0:3],  conf[i,k] = pred[i,k,3]   (model units; the caller applies scale/centroid)
+ *   mode 0 (argmax):   out[b,k] = votes[i*,k], i* = first argmax_i conf[i,k] over the scene's rows
+ *   mode 1 (weighted): confidence-weighted mean of the votes with conf > mask_thresh; argmax vote if there is none.
+ * coord (n,3) fp32, pred (n,k_pts,4) fp32, offset int64 (n_scenes) cumulative, out (n_scenes,k_pts,3) fp32.
+ * ------------------------------------------------------------------------- */
+int ptv3_keypoint_aggregate(const float* coord, const float* pred, const int64_t* offset, int64_t n_scenes, int k_pts,
+                            int mode, float mask_thresh, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

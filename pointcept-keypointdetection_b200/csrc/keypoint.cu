@@ -1,0 +1,94 @@
+// A9: per-scene keypoint aggregation of the offset head (tools/infer_offset.py:366-399), on the device:
+//   votes[i,k] = coord[i] + pred[i,k,:3],  conf[i,k] = pred[i,k,3]
+//   argmax:   kp[b,k] = votes[i*,k],  i* = first index of max conf over the scene's rows
+//   weighted: kp[b,k] = sum_i votes[i,k] w_i / sum_i w_i with w_i = conf > thresh ? conf : 0, argmax vote if no w_i
+// One CTA per (scene, keypoint): coalesced 16-byte reads of the keypoint's (dx,dy,dz,conf), warp-shuffle + shared
+// memory reduction in a fixed order (deterministic).  Replaces a per-scene, per-keypoint host loop with .item() syncs.
+#include "common.cuh"
+
+namespace ptv3 {
+
+constexpr int kKpThreads = 512;
+
+__global__ void __launch_bounds__(kKpThreads) keypoint_aggregate_kernel(const float* __restrict__ coord,
+                                                                        const float* __restrict__ pred,
+                                                                        const int64_t* __restrict__ offset, int k_pts,
+                                                                        int weighted, float thresh,
+                                                                        float* __restrict__ out) {
+  const int b = blockIdx.x, k = blockIdx.y;
+  const int64_t start = b ? offset[b - 1] : 0, end = offset[b];
+  float best_v = -INFINITY;
+  int64_t best_i = INT64_MAX;
+  float sw = 0.f, sx = 0.f, sy = 0.f, sz = 0.f;
+  for (int64_t i = start + threadIdx.x; i < end; i += kKpThreads) {
+    const float4 p = *reinterpret_cast<const float4*>(pred + (i * k_pts + k) * 4);
+    if (p.w > best_v) {   // strided ascending i per thread: the first maximum wins
+      best_v = p.w;
+      best_i = i;
+    }
+    if (weighted && p.w > thresh) {
+      const float cx = coord[i * 3], cy = coord[i * 3 + 1], cz = coord[i * 3 + 2];
+      sw += p.w;
+      sx = fmaf(cx + p.x, p.w, sx);
+      sy = fmaf(cy + p.y, p.w, sy);
+      sz = fmaf(cz + p.z, p.w, sz);
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best_v, d);
+    const int64_t oi = __shfl_xor_sync(0xffffffffu, best_i, d);
+    if (ov > best_v || (ov == best_v && oi < best_i)) {
+      best_v = ov;
+      best_i = oi;
+    }
+    sw += __shfl_xor_sync(0xffffffffu, sw, d);
+    sx += __shfl_xor_sync(0xffffffffu, sx, d);
+    sy += __shfl_xor_sync(0xffffffffu, sy, d);
+    sz += __shfl_xor_sync(0xffffffffu, sz, d);
+  }
+  __shared__ float s_v[kKpThreads / 32], s_w[kKpThreads / 32][4];
+  __shared__ int64_t s_i[kKpThreads / 32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    s_v[warp] = best_v;
+    s_i[warp] = best_i;
+    s_w[warp][0] = sw; s_w[warp][1] = sx; s_w[warp][2] = sy; s_w[warp][3] = sz;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < kKpThreads / 32; ++w) {
+      if (s_v[w] > best_v || (s_v[w] == best_v && s_i[w] < best_i)) {
+        best_v = s_v[w];
+        best_i = s_i[w];
+      }
+      sw += s_w[w][0]; sx += s_w[w][1]; sy += s_w[w][2]; sz += s_w[w][3];
+    }
+    float* o = out + ((int64_t)b * k_pts + k) * 3;
+    if (end <= start) {
+      o[0] = o[1] = o[2] = 0.f;
+    } else if (weighted && sw > 0.f) {
+      o[0] = sx / sw; o[1] = sy / sw; o[2] = sz / sw;
+    } else {
+      const float* p = pred + (best_i * k_pts + k) * 4;
+      o[0] = coord[best_i * 3] + p[0];
+      o[1] = coord[best_i * 3 + 1] + p[1];
+      o[2] = coord[best_i * 3 + 2] + p[2];
+    }
+  }
+}
+
+}  // namespace ptv3
+
+using namespace ptv3;
+
+extern "C" int ptv3_keypoint_aggregate(const float* coord, const float* pred, const int64_t* offset, int64_t n_scenes,
+                                       int k_pts, int mode, float mask_thresh, float* out, void* stream) {
+  if (n_scenes < 0 || k_pts < 1 || k_pts > 65535 || mode < 0 || mode > 1) return PTV3_EINVAL;
+  if (n_scenes == 0) return PTV3_OK;
+  if (!coord || !pred || !offset || !out) return PTV3_EINVAL;
+  dim3 grid((unsigned)n_scenes, (unsigned)k_pts);
+  keypoint_aggregate_kernel<<<grid, kKpThreads, 0, as_stream(stream)>>>(coord, pred, offset, k_pts, mode, mask_thresh,
+                                                                        out);
+  return check_launch();
+}

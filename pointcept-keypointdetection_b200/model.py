@@ -655,21 +655,7 @@ class DefaultSegmentorV2(nn.Module):
 
 
 def aggregate_keypoints(coord, pred, offset, mode="argmax", mask_thresh=0.5):
-    """tools/infer_offset.py:366-399 per scene, on the device without per-keypoint host syncs:
-    kp[b,k] = coord[i*] + pred[i*,k,:3], i* = argmax_i pred[i,k,3] over the scene (votes in model units)."""
-    votes = coord[:, None, :] + pred[..., :3]
-    conf = pred[..., 3]
-    starts = F.pad(offset, (1, 0))[:-1].tolist()
-    ends = offset.tolist()
-    out = []
-    for s, e in zip(starts, ends):
-        c, v = conf[s:e], votes[s:e]
-        best = c.argmax(0)                                             # (K,)
-        kp = v[best, torch.arange(v.shape[1], device=v.device)]
-        if mode == "weighted":
-            w = torch.where(c > mask_thresh, c, torch.zeros_like(c))
-            tot = w.sum(0)
-            kpw = (v * w[..., None]).sum(0) / tot.clamp_min(1e-12)[:, None]
-            kp = torch.where((tot > 0)[:, None], kpw, kp)
-        out.append(kp)
-    return torch.stack(out)
+    """tools/infer_offset.py:366-399 per scene, one kernel, no host sync:
+    kp[b,k] = coord[i*] + pred[i*,k,:3], i* = argmax_i pred[i,k,3] over the scene (votes in model units);
+    mode "weighted" = confidence-weighted mean of the votes above mask_thresh (argmax vote if none)."""
+    return ops.keypoint_aggregate(coord, pred, offset, mode=mode, mask_thresh=mask_thresh)

@@ -389,3 +389,20 @@ def attn_window(qkv, order, windows, n_windows, num_heads, max_len, scale=None, 
                                             int(max_len), n, h, d, scale, int(algo), _p(out), _stream()),
                    "ptv3_attn_window_fwd")
     return out
+
+
+# ------------------------------------------------------------------ A9 keypoint aggregation (offset head)
+def keypoint_aggregate(coord, pred, offset, mode="argmax", mask_thresh=0.5):
+    """coord (N,3) fp32, pred (N,K,4) fp32 [dx,dy,dz,conf], offset int64 (B) -> (B,K,3) fp32 keypoints in model
+    units (tools/infer_offset.py:366-399 per scene; no host sync)."""
+    _need_cuda(coord, pred, offset)
+    lib = _lib.load()
+    coord, pred = coord.contiguous().float(), pred.contiguous().float()
+    offset = offset.contiguous().long()
+    n, k = pred.shape[0], pred.shape[1]
+    assert coord.shape == (n, 3) and pred.shape == (n, k, 4)
+    out = torch.empty((offset.numel(), k, 3), dtype=torch.float32, device=pred.device)
+    _lib.check(lib.ptv3_keypoint_aggregate(_p(coord), _p(pred), _p(offset), offset.numel(), int(k),
+                                           {"argmax": 0, "weighted": 1}[mode], float(mask_thresh), _p(out), _stream()),
+               "ptv3_keypoint_aggregate")
+    return out

@@ -325,3 +325,27 @@ def test_forward_vs_oracle_fresh_scene():
     out = m(dict(coord=torch.from_numpy(c).cuda(), grid_coord=torch.from_numpy(gcoord).cuda(),
                  feat=torch.from_numpy(f).cuda(), offset=torch.tensor([len(c)]).cuda()))["pred"]
     assert rel_l2(out, ref) < TOL_F32
+
+
+@pytest.mark.parametrize("mode", ["argmax", "weighted"])
+def test_keypoint_aggregate_matches_oracle(mode):
+    """A9: ptv3_keypoint_aggregate against oracle.ptv3.aggregate_keypoints (tools/infer_offset.py:366-399) per scene:
+    ragged scenes (1 row, no confident row, exact ties -> first index wins)."""
+    from ptv3_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    sizes = [1, 777, 5000, 33, 12345]
+    n, K = sum(sizes), 6
+    coord = torch.randn(n, 3, generator=g)
+    pred = torch.randn(n, K, 4, generator=g) * 0.2
+    pred[..., 3] = torch.sigmoid(torch.randn(n, K, generator=g) * 2)
+    s3 = sizes[0] + sizes[1] + sizes[2]
+    pred[s3:s3 + sizes[3], :, 3] = 0.1                       # scene 3: nothing above the threshold, all tied
+    pred[5:9, 2, 3] = 0.999                                   # exact ties inside scene 1: first index wins
+    offset = torch.tensor(sizes).cumsum(0)
+    out = ops.keypoint_aggregate(coord.cuda(), pred.cuda(), offset.cuda(), mode=mode).cpu()
+    assert out.shape == (len(sizes), K, 3)
+    start = 0
+    for b, sz in enumerate(sizes):
+        ref = P.aggregate_keypoints(coord[start:start + sz], pred[start:start + sz], mode=mode)
+        assert torch.allclose(out[b], ref, rtol=1e-5, atol=1e-5), (b, (out[b] - ref).abs().max())
+        start += sz
