@@ -41,6 +41,20 @@ def peaks():
         return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
 
 
+def ncu_traffic(kernel_substr):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed summary of
+    one `ncu --set full` capture (profiles/r01_ncu_full_summary.json); None if that kernel was not captured."""
+    try:
+        with open(os.path.join(REPO, "profiles", "r01_ncu_full_summary.json")) as f:
+            rows = [r for r in json.load(f) if kernel_substr in r["kernel"] and r.get("dram_read_MB") is not None]
+        if not rows:
+            return None, "kernel not in the committed ncu capture"
+        b = sum((r["dram_read_MB"] + r["dram_write_MB"]) * 1e6 for r in rows) / len(rows)
+        return round(b), f"bytes per launch, mean of {len(rows)} captured launches (profiles/r01_ncu_full_summary.json)"
+    except Exception as e:  # noqa: BLE001
+        return None, f"no ncu summary ({type(e).__name__})"
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -257,6 +271,8 @@ def run_ours(args):
                     frac=round(ach / pk["tf_sust"], 4), traffic=None, peak_source=pk["src"] + " (sustained bf16 GEMM)",
                     launches_per_step=e["launches"], ms_per_step=round(e["ms"], 3),
                     share_of_step=round(e["ms"] / step_ms, 3))
+        roof["traffic"], roof["traffic_note"] = ncu_traffic({"attn_window": "attn_window", "subm_conv": "subm_conv_tc",
+                                                             "mlp_fused": "mlp_fused"}.get(top, top))
         if top == "attn_window":   # head_dim 16: the exp pipe, not the tensor pipe, bounds this kernel
             roof["exp_per_s"] = round(e["units"] / (e["ms"] * 1e-3) / 1e12, 3)
             roof["exp_peak_mufu_per_s"] = round(16 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 3)

@@ -37,7 +37,8 @@ struct Smem {
   static constexpr int W2_OFF = W1_OFF + W1_BYTES;
   static constexpr int A1_OFF = W2_OFF + W2_BYTES;
   static constexpr int A2_OFF = A1_OFF + 2 * A1_BYTES;
-  static constexpr int BAR_OFF = A2_OFF + 2 * A2_BYTES;
+  static constexpr int BIAS_OFF = A2_OFF + 2 * A2_BYTES;      // b1 (HID floats) then b2 (C floats)
+  static constexpr int BAR_OFF = BIAS_OFF + (HID + C) * 4;
   static constexpr int DYN_BYTES = BAR_OFF + 256 + 1024;
 };
 
@@ -114,6 +115,8 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
     }
     mbar_fence_init();
   }
+  for (int j = tid; j < L::HID + C; j += THREADS)
+    reinterpret_cast<float*>(smem + L::BIAS_OFF)[j] = j < L::HID ? b1[j] : b2[j - L::HID];
   if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
   fence_before_sync();
   __syncthreads();
@@ -157,53 +160,56 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
     // =========================== MMA issuer ===========================
     // The whole warp runs the (uniform) control flow and waits; one elected lane issues.  Issuing from inside
     // `if (lane == 0)` makes nvcc wrap every tcgen05 instruction in an ELECT / R2UR / BRA.U.ANY loop.
+    // Flat schedule over hidden-block steps t = tile * NHB + hb with GEMM1 two steps ahead of GEMM2:
+    //   fc1(0) fc1(1) | fc1(t+2) fc2(t) | ...   so the epilogue of step t+1 never waits for a GEMM1 that was queued
+    // behind the GEMM2 of step t.
     {
       constexpr uint32_t idesc1 = idesc_bf16_f32(TM, HB), idesc2 = idesc_bf16_f32(TM, C);
+      constexpr int NHB = L::NHB;
       mbar_wait(bar(0), 0);
-      uint32_t c1 = 0, c2 = 0;
-      for (int i = 0; i < my_tiles; ++i) {
-        const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
-        mbar_wait(bar(1 + ab), tph);
+      const int T = my_tiles * NHB;
+      auto fc1 = [&](int t) {
+        const int it = t / NHB, hb = t - it * NHB;
+        const uint32_t ab = (uint32_t)it & 1u, bb = (uint32_t)t & 1u;
+        if (hb == 0) mbar_wait(bar(1 + ab), (uint32_t)(it >> 1) & 1u);   // X tile landed
+        mbar_wait(bar(7 + bb), (((uint32_t)t >> 1) & 1u) ^ 1u);           // D1[bb] drained by the epilogue of step t-2
         fence_after_sync();
-        for (int hb = 0; hb <= L::NHB; ++hb) {
-          if (hb < L::NHB) {
-            const uint32_t bb = c1 & 1u;
-            mbar_wait(bar(7 + bb), ((c1 >> 1) & 1u) ^ 1u);
-            fence_after_sync();
-            if (elect_one_sync()) {
-              const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + ab * L::A1_BYTES);
-              const uint64_t b_desc = smem_desc_sw128(sb + L::W1_OFF + hb * HB * 128);
+        if (elect_one_sync()) {
+          const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + ab * L::A1_BYTES);
+          const uint64_t b_desc = smem_desc_sw128(sb + L::W1_OFF + hb * HB * 128);
 #pragma unroll
-              for (int kk = 0; kk < C / 16 && kk < 4; ++kk)
-                mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc1, kk ? 1u : 0u);
-              mma_commit(bar(5 + bb));
-              if (hb == L::NHB - 1) mma_commit(bar(3 + ab));   // X tile fully consumed
-            }
-            __syncwarp();
-            ++c1;
-          }
-          if (hb >= 1) {
-            const int h2 = hb - 1;
-            const uint32_t bb = c2 & 1u;
-            mbar_wait(bar(9 + bb), (c2 >> 1) & 1u);
-            if (h2 == 0) mbar_wait(bar(15 + ab), tph ^ 1u);   // D2[ab] drained by the epilogue of tile i-2
-            fence_after_sync();
-            if (elect_one_sync()) {
-#pragma unroll
-              for (int kb = 0; kb < 2; ++kb) {
-                const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
-                const uint64_t b_desc = smem_desc_sw128(sb + L::W2_OFF + (2 * h2 + kb) * L::W2_TILE);
-#pragma unroll
-                for (int kk = 0; kk < 4; ++kk)
-                  mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc2, (h2 | kb | kk) ? 1u : 0u);
-              }
-              mma_commit(bar(11 + bb));
-              if (h2 == L::NHB - 1) mma_commit(bar(13 + ab));
-            }
-            __syncwarp();
-            ++c2;
-          }
+          for (int kk = 0; kk < C / 16 && kk < 4; ++kk)
+            mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc1, kk ? 1u : 0u);
+          mma_commit(bar(5 + bb));
+          if (hb == NHB - 1) mma_commit(bar(3 + ab));   // X tile fully consumed
         }
+        __syncwarp();
+      };
+      auto fc2 = [&](int t) {
+        const int it = t / NHB, h2 = t - it * NHB;
+        const uint32_t ab = (uint32_t)it & 1u, bb = (uint32_t)t & 1u;
+        mbar_wait(bar(9 + bb), ((uint32_t)t >> 1) & 1u);                  // GELU(h) block written by the epilogue
+        if (h2 == 0) mbar_wait(bar(15 + ab), ((uint32_t)(it >> 1) & 1u) ^ 1u);   // D2[ab] drained (tile it-2)
+        fence_after_sync();
+        if (elect_one_sync()) {
+#pragma unroll
+          for (int kb = 0; kb < 2; ++kb) {
+            const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
+            const uint64_t b_desc = smem_desc_sw128(sb + L::W2_OFF + (2 * h2 + kb) * L::W2_TILE);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc2, (h2 | kb | kk) ? 1u : 0u);
+          }
+          mma_commit(bar(11 + bb));
+          if (h2 == NHB - 1) mma_commit(bar(13 + ab));
+        }
+        __syncwarp();
+      };
+      if (T > 0) fc1(0);
+      if (T > 1) fc1(1);
+      for (int t = 0; t < T; ++t) {
+        if (t + 2 < T) fc1(t + 2);
+        fc2(t);
       }
     }
   } else if (warp >= 4) {
@@ -211,63 +217,68 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
     const int q4 = warp & 3, quarter = (warp - 4) >> 2;   // TMEM lane quarter, column quarter of the 128-wide block
     const int row = q4 * 32 + lane;
     const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
-    uint32_t e1 = 0;
-    for (int i = 0; i < my_tiles; ++i) {
-      const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
-      for (int hb = 0; hb < L::NHB; ++hb, ++e1) {
+    auto gelu_step = [&](int i, int hb, uint32_t e1) {   // D1 -> + b1 -> GELU -> bf16 A operand of GEMM2
         const uint32_t bb = e1 & 1u;
-        mbar_wait(bar(5 + bb), (e1 >> 1) & 1u);
-        fence_after_sync();
-        uint32_t v[32], pk[16];
-        const int col0 = quarter * 32;
-        tmem_ld32(tmem + lane_base + bb * HB + col0, v);
-        tmem_ld_wait();
-        fence_before_sync();
-        mbar_arrive(bar(7 + bb));
-        const float4* bp = reinterpret_cast<const float4*>(b1 + hb * HB + col0);
+      mbar_wait(bar(5 + bb), (e1 >> 1) & 1u);
+      fence_after_sync();
+      uint32_t v[32], pk[16];
+      const int col0 = quarter * 32;
+      tmem_ld32(tmem + lane_base + bb * HB + col0, v);
+      tmem_ld_wait();
+      fence_before_sync();
+      mbar_arrive(bar(7 + bb));
+      const float4* bp = reinterpret_cast<const float4*>(smem + L::BIAS_OFF) + (hb * HB + col0) / 4;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 bv = bp[j];
-          pk[2 * j] = pack2(gelu_erf(__uint_as_float(v[4 * j]) + bv.x), gelu_erf(__uint_as_float(v[4 * j + 1]) + bv.y));
-          pk[2 * j + 1] =
-              pack2(gelu_erf(__uint_as_float(v[4 * j + 2]) + bv.z), gelu_erf(__uint_as_float(v[4 * j + 3]) + bv.w));
-        }
-        mbar_wait(bar(11 + bb), ((e1 >> 1) & 1u) ^ 1u);
-        // my 32 hidden columns = four 16-byte chunks of K-block (quarter >> 1), chunks (quarter & 1) * 4 ..
-        const uint32_t prow = sb + L::A2_OFF + bb * L::A2_BYTES + (quarter >> 1) * 16384 + (row >> 3) * 1024 +
-                              (row & 7) * 128;
-#pragma unroll
-        for (int c4 = 0; c4 < 4; ++c4)
-          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(
-                           prow + ((((quarter & 1) * 4 + c4) ^ (row & 7)) << 4)),
-                       "r"(pk[4 * c4]), "r"(pk[4 * c4 + 1]), "r"(pk[4 * c4 + 2]), "r"(pk[4 * c4 + 3])
-                       : "memory");
-        fence_proxy_async();
-        mbar_arrive(bar(9 + bb));
+      for (int j = 0; j < 8; ++j) {
+        const float4 bv = bp[j];
+        pk[2 * j] = pack2(gelu_erf(__uint_as_float(v[4 * j]) + bv.x), gelu_erf(__uint_as_float(v[4 * j + 1]) + bv.y));
+        pk[2 * j + 1] =
+            pack2(gelu_erf(__uint_as_float(v[4 * j + 2]) + bv.z), gelu_erf(__uint_as_float(v[4 * j + 3]) + bv.w));
       }
+      mbar_wait(bar(11 + bb), ((e1 >> 1) & 1u) ^ 1u);
+      // my 32 hidden columns = four 16-byte chunks of K-block (quarter >> 1), chunks (quarter & 1) * 4 ..
+      const uint32_t prow = sb + L::A2_OFF + bb * L::A2_BYTES + (quarter >> 1) * 16384 + (row >> 3) * 1024 +
+                            (row & 7) * 128;
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4)
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(
+                         prow + ((((quarter & 1) * 4 + c4) ^ (row & 7)) << 4)),
+                     "r"(pk[4 * c4]), "r"(pk[4 * c4 + 1]), "r"(pk[4 * c4 + 2]), "r"(pk[4 * c4 + 3])
+                     : "memory");
+      fence_proxy_async();
+      mbar_arrive(bar(9 + bb));
+    };
+    auto epilogue2 = [&](int i) {
+      const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
       // ---- epilogue 2: D2 -> + b2 (+ residual) -> fp32 stream and bf16 copy; this thread owns C/4 columns ----
+      constexpr int NC = C / 4;
+      const int col0 = quarter * NC;
+      const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
+      // the residual row segment is requested BEFORE waiting for GEMM2: its HBM latency hides behind that wait
+      float4 rres[NC / 4];
+#pragma unroll
+      for (int j = 0; j < NC / 4; ++j) rres[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (residual && grow < n) {
+        const float4* rp = reinterpret_cast<const float4*>(residual + grow * C + col0);
+#pragma unroll
+        for (int j = 0; j < NC / 4; ++j) rres[j] = __ldcs(rp + j);
+      }
       mbar_wait(bar(13 + ab), tph);
       fence_after_sync();
-      constexpr int NC = C / 4;
       uint32_t v[NC];
-      const int col0 = quarter * NC;
       if constexpr (NC == 16) tmem_ld16(tmem + lane_base + 256 + ab * C + col0, v);
       else tmem_ld8(tmem + lane_base + 256 + ab * C + col0, v);
       tmem_ld_wait();
       fence_before_sync();
       mbar_arrive(bar(15 + ab));
-      const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
       if (grow < n) {
         float f[NC];
+        const float* b2s = reinterpret_cast<const float*>(smem + L::BIAS_OFF) + L::HID;
 #pragma unroll
-        for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]) + b2[col0 + j];
-        if (residual) {
-          const float4* rp = reinterpret_cast<const float4*>(residual + grow * C + col0);
+        for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]) + b2s[col0 + j];
 #pragma unroll
-          for (int j = 0; j < NC / 4; ++j) {
-            const float4 r = rp[j];
-            f[4 * j] += r.x; f[4 * j + 1] += r.y; f[4 * j + 2] += r.z; f[4 * j + 3] += r.w;
-          }
+        for (int j = 0; j < NC / 4; ++j) {
+          f[4 * j] += rres[j].x; f[4 * j + 1] += rres[j].y; f[4 * j + 2] += rres[j].z; f[4 * j + 3] += rres[j].w;
         }
         if (res_out) {
           float4* op = reinterpret_cast<float4*>(res_out + grow * C + col0);
@@ -282,6 +293,14 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
                                pack2(f[8 * j + 4], f[8 * j + 5]), pack2(f[8 * j + 6], f[8 * j + 7]));
         }
       }
+    };
+    // order: G(i,0) E2(i-1) G(i,1) ... : the wait for GEMM2 of tile i-1 hides behind the first GELU block of tile i
+    uint32_t e1 = 0;
+    for (int i = 0; i <= my_tiles; ++i) {
+      if (i < my_tiles) gelu_step(i, 0, e1++);
+      if (i >= 1) epilogue2(i - 1);
+      if (i < my_tiles)
+        for (int hb = 1; hb < L::NHB; ++hb) gelu_step(i, hb, e1++);
     }
   }
   fence_before_sync();
