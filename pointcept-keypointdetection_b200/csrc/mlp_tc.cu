@@ -297,6 +297,10 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
     // order: G(i,0) E2(i-1) G(i,1) ... : the wait for GEMM2 of tile i-1 hides behind the first GELU block of tile i
     uint32_t e1 = 0;
     for (int i = 0; i <= my_tiles; ++i) {
+      if (residual && i >= 1) {   // pull tile i-1's residual segment into L2 while the GELU block below runs
+        const int64_t grow = (int64_t)(blockIdx.x + (int64_t)(i - 1) * gridDim.x) * TM + row;
+        if (grow < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(residual + grow * C + quarter * (C / 4)));
+      }
       if (i < my_tiles) gelu_step(i, 0, e1++);
       if (i >= 1) epilogue2(i - 1);
       if (i < my_tiles)
