@@ -281,40 +281,41 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
     // The whole warp runs the loop (uniform control flow, values in uniform registers); one elected lane issues.
     // Issuing from inside `if (lane == 0)` instead makes nvcc wrap every tcgen05 instruction in an ELECT / R2UR /
     // BRA.U.ANY loop: ~135 instructions per K-block on a single thread, which bounded the whole kernel.
-    if (my_tiles > 0) {
+    // ONE elected thread runs the whole issue loop: inside `if (elect_one_sync())` nvcc knows a single lane is
+    // active, keeps the ring state and descriptors in uniform registers and emits the tcgen05 instructions without
+    // per-instruction ELECT / R2UR loops or per-K-block warp re-convergence.
+    if (my_tiles > 0 && elect_one_sync()) {
       constexpr uint32_t idesc = idesc_bf16_f32(TM, NT);
-      uint32_t s = 0, ph = 0;   // ring position: uniform loop counters, so descriptors stay in uniform registers
-      bool ready = false;               // full barrier of stage s already seen complete (peeked during the last K-block)
+      uint32_t s = 0, ph = 0;
       for (int i = 0; i < my_tiles; ++i) {
         const uint32_t ab = (uint32_t)i & 1u;
-        int n_kb = 1;
+        const uint32_t d_tmem = tmem_base + ab * NT;
+        mbar_wait(full_bar(s), ph);   // first K-block of the tile: tile_nkb[i] was written before it was issued
+        fence_after_sync();
+        const int n_kb = ld_shared_s32(s_base + L::MISC_OFF + 160 + 4u * ((uint32_t)i & 15u));
+        mbar_wait(acc_free(ab), (((uint32_t)i >> 1) & 1u) ^ 1u);   // accumulator drained by the epilogue (tile i-2)
+        fence_after_sync();
         for (int kbi = 0; kbi < n_kb; ++kbi) {
-          if (!ready) mbar_wait(full_bar(s), ph);
-          fence_after_sync();
-          if (kbi == 0) {   // first K-block of the tile: tile_nkb[i] was written before it was issued
-            n_kb = ld_shared_s32(s_base + L::MISC_OFF + 160 + 4u * ((uint32_t)i & 15u));
-            mbar_wait(acc_free(ab), (((uint32_t)i >> 1) & 1u) ^ 1u);   // accumulator drained by the epilogue (tile i-2)
+          if (kbi > 0) {
+            mbar_wait(full_bar(s), ph);
             fence_after_sync();
           }
-          // peek at the next stage before issuing: the poll's latency hides behind the MMAs
-          const uint32_t s1 = (s + 1 == STAGES) ? 0u : s + 1;
-          const uint32_t ph1 = (s + 1 == STAGES) ? (ph ^ 1u) : ph;
-          ready = mbar_test_wait(full_bar(s1), ph1);
-          if (elect_one_sync()) {
-            const uint32_t a_s = s_base + s * L::STAGE_BYTES;
-            const uint64_t a_desc = smem_desc_sw128(a_s);
-            const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
+          const uint32_t a_s = s_base + s * L::STAGE_BYTES;
+          const uint64_t a_desc = smem_desc_sw128(a_s);
+          const uint64_t b_desc = smem_desc_sw128(a_s + A_BYTES);
 #pragma unroll
-            for (int kk = 0; kk < KBLK / 16; ++kk)
-              mma_bf16_ss(tmem_base + ab * NT, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (kbi > 0 || kk > 0) ? 1u : 0u);
-            mma_commit(empty_bar(s));
-            if (kbi == n_kb - 1) mma_commit(acc_full(ab));
+          for (int kk = 0; kk < KBLK / 16; ++kk)
+            mma_bf16_ss(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (kbi > 0 || kk > 0) ? 1u : 0u);
+          mma_commit(empty_bar(s));
+          if (++s == STAGES) {
+            s = 0;
+            ph ^= 1u;
           }
-          s = s1;
-          ph = ph1;
         }
+        mma_commit(acc_full(ab));
       }
     }
+    __syncwarp();
   } else {
     // =========================== epilogue: TMEM -> +bias -> bf16 rows ===========================
     const int q4 = warp & 3;   // TMEM lane quarter this warp may access
