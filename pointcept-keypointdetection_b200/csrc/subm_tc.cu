@@ -160,7 +160,6 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
       mbar_arrive_expect_tx(nbr_full(i & 1), nbr_tile_bytes);
       bulk_g2s(s_base + L::NBR_OFF + (i & 1) * L::NBR_BYTES, nbr + row0 * k3, nbr_tile_bytes, nbr_full(i & 1));
     };
-    const char* last_ptr = reinterpret_cast<const char*>(in);   // ASYNC: target of zero-byte copies
     if (warp == 0 && my_tiles > 0 && tile_full(0)) {
       if (elect_one_sync()) prefetch_nbr(0);
       __syncwarp();
@@ -188,15 +187,20 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
       }
       // per-offset presence over the 128 rows of the tile
       const uint32_t nbr_sa = s_base + L::NBR_OFF + tb * L::NBR_BYTES;
-      if (tid < TM) {
+      const int64_t tile_row0 = row0 < n ? row0 : 0;
+      {   // thread -> (row, quarter of the offsets): 512 threads share the 128 x k3 presence test
+        const int row = tid & (TM - 1), kq = tid >> 7, kper = (k3 + 3) >> 2;
+        const int k_lo = kq * kper, k_hi = min(k3, k_lo + kper);
         uint32_t local = 0;
-        for (int k = 0; k < k3; ++k) local |= (ld_shared_s32(nbr_sa + (uint32_t)(tid * k3 + k) * 4u) >= 0 ? 1u : 0u) << k;
+        for (int k = k_lo; k < k_hi; ++k)
+          local |= (ld_shared_s32(nbr_sa + (uint32_t)(row * k3 + k) * 4u) >= 0 ? 1u : 0u) << k;
         local = __reduce_or_sync(0xffffffffu, local);
-        if (lane == 0) atomicOr(&masks[i & 3], local);
+        if (lane == 0 && local) atomicOr(&masks[i & 3], local);
       }
       producers_sync();
       const uint32_t mask = masks[i & 3];
-      const int per = c_in >= KBLK ? c_in / KBLK : 1;
+      const int per = c_in >= KBLK ? c_in / KBLK : 1;   // 1, 2, 4 or 8
+      const int per_shift = 31 - __clz(per);
       uint32_t blk_mask;  // bit j = K-block group j is needed (offset j for c_in >= 64, offset pair j for c_in == 32)
       if (c_in >= KBLK) {
         blk_mask = mask;
@@ -213,7 +217,7 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
       int popped = 0;   // set bits of blk_mask already dropped
       for (int done = (int)((uint32_t)(group + kGatherGroups - (int)(g0 % kGatherGroups)) % kGatherGroups); done < n_kb;
            done += kGatherGroups) {
-        const int jidx = done / per, cb = done - jidx * per;
+        const int jidx = done >> per_shift, cb = done & (per - 1);
         while (popped < jidx) {
           blk_mask &= blk_mask - 1;
           ++popped;
@@ -244,15 +248,14 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
 #pragma unroll
         for (int u = 0; u < kSlots; ++u) src[u] = k_ok ? ld_shared_s32(np + (uint32_t)u * nbr_step) : -1;
         if constexpr (ASYNC) {
-          // every slot is a cp.async (absent neighbours: zero source bytes = zero fill, aimed at the last address
-          // this lane really read so the ignored requests do not pile up on one line); the mbarrier arrival is
+          // every slot is a cp.async (absent neighbours: zero source bytes = zero fill); the mbarrier arrival is
           // triggered by the copies themselves, so the warp moves on without waiting
 #pragma unroll
           for (int u = 0; u < kSlots; ++u) {
             const uint32_t dst = a_w + (uint32_t)(u >> 1) * 1024u + ((u & 1) ? off_odd : off_even);
             const bool ok = src[u] >= 0;
-            if (ok) last_ptr = in_ch + (uint64_t)(uint32_t)src[u] * row_bytes;
-            cp_async16(dst, last_ptr, ok ? 16u : 0u);
+            const uint32_t r = ok ? (uint32_t)src[u] : (uint32_t)tile_row0;   // zero-byte copies aim at a row of this tile
+            cp_async16(dst, in_ch + (uint64_t)r * row_bytes, ok ? 16u : 0u);
           }
           cp_async_mbar_arrive_noinc(full_bar(s));
         } else {
