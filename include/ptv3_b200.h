@@ -224,6 +224,14 @@ int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float
                      int dtype_out2, int64_t n, int c, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * A6 glue: y = act(x * scale[c] + shift[c]) in one pass (eval BatchNorm + GELU after the pooled segment-max,
+ * point_transformer_v3m1_base.py:433-437).  act: 0 none, 1 GELU (erf), 2 ReLU.  x (n,c) fp32 / bf16, c % 4 == 0;
+ * scale / shift fp32 (c) or NULL; out32 fp32 (n,c) and / or out16 bf16 (n,c).
+ * ------------------------------------------------------------------------- */
+int ptv3_affine_act(const void* x, int dtype_x, const float* scale, const float* shift, int act, int64_t n, int c,
+                    float* out32, void* out16, void* stream);
+
+/* ---------------------------------------------------------------------------
  * A9  keypoint aggregation of the offset head (tools/infer_offset.py:366-399, the evaluator's
  * hooks/offset_keypoint_evaluator.py:46-91 uses the same rule): per scene b and keypoint k
  *   votes[i,k] = coord[i] + pred[i,k,0:3],  conf[i,k] = pred[i,k,3]   (model units; the caller applies scale/centroid)

@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
     }
   } else if (warp == 2) {
     // =========================== MMA issuer ===========================
-    // The whole warp runs the (uniform) control flow and waits; one elected lane issues.  Issuing from inside
-    // `if (lane == 0)` makes nvcc wrap every tcgen05 instruction in an ELECT / R2UR / BRA.U.ANY loop.
+    // One elected lane runs the issue schedule.  (Issuing from inside `if (lane == 0)` instead makes nvcc wrap every
+    // tcgen05 instruction in an ELECT / R2UR / BRA.U.ANY loop.)
     // Flat schedule over hidden-block steps t = tile * NHB + hb with GEMM1 two steps ahead of GEMM2:
     //   fc1(0) fc1(1) | fc1(t+2) fc2(t) | ...   so the epilogue of step t+1 never waits for a GEMM1 that was queued
     // behind the GEMM2 of step t.
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
         if (hb == 0) mbar_wait(bar(1 + ab), (uint32_t)(it >> 1) & 1u);   // X tile landed
         mbar_wait(bar(7 + bb), (((uint32_t)t >> 1) & 1u) ^ 1u);           // D1[bb] drained by the epilogue of step t-2
         fence_after_sync();
-        if (elect_one_sync()) {
+        {
           const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + ab * L::A1_BYTES);
           const uint64_t b_desc = smem_desc_sw128(sb + L::W1_OFF + hb * HB * 128);
 #pragma unroll
@@ -183,7 +183,6 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
           mma_commit(bar(5 + bb));
           if (hb == NHB - 1) mma_commit(bar(3 + ab));   // X tile fully consumed
         }
-        __syncwarp();
       };
       auto fc2 = [&](int t) {
         const int it = t / NHB, h2 = t - it * NHB;
@@ -191,7 +190,7 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
         mbar_wait(bar(9 + bb), ((uint32_t)t >> 1) & 1u);                  // GELU(h) block written by the epilogue
         if (h2 == 0) mbar_wait(bar(15 + ab), ((uint32_t)(it >> 1) & 1u) ^ 1u);   // D2[ab] drained (tile it-2)
         fence_after_sync();
-        if (elect_one_sync()) {
+        {
 #pragma unroll
           for (int kb = 0; kb < 2; ++kb) {
             const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
@@ -203,14 +202,16 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
           mma_commit(bar(11 + bb));
           if (h2 == NHB - 1) mma_commit(bar(13 + ab));
         }
-        __syncwarp();
       };
-      if (T > 0) fc1(0);
-      if (T > 1) fc1(1);
-      for (int t = 0; t < T; ++t) {
-        if (t + 2 < T) fc1(t + 2);
-        fc2(t);
+      if (elect_one_sync()) {   // one thread runs the whole issue schedule (state and descriptors in uniform registers)
+        if (T > 0) fc1(0);
+        if (T > 1) fc1(1);
+        for (int t = 0; t < T; ++t) {
+          if (t + 2 < T) fc1(t + 2);
+          fc2(t);
+        }
       }
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // =========================== epilogue warps ===========================

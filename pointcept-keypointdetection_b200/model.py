@@ -349,18 +349,25 @@ class SerializedPooling(PointModule):
         w, b = _cached(self, ("proj", cd), [self.proj.weight, self.proj.bias],
                        lambda: (self.proj.weight.to(cd), self.proj.bias.to(cd)))
         y = F.linear(_feat_cd(point, cd), w, b)
-        feat = ops.segment_csr(y, pf["idx_ptr"], self.reduce, gather=pf["indices"]).float()
+        pooled = ops.segment_csr(y, pf["idx_ptr"], self.reduce, gather=pf["indices"])
         coord = ops.segment_csr(point.coord.float(), pf["idx_ptr"], "mean", gather=pf["indices"])
-        if hasattr(self, "norm"):
-            bn = self.norm[0]
-            if isinstance(bn, nn.BatchNorm1d):
-                s, t = _cached(self, "bn", [bn.weight, bn.bias, bn.running_mean, bn.running_var],
-                               lambda: _bn_scale_shift(bn))
-                feat = feat * s + t
-            else:
+        bn = self.norm[0] if hasattr(self, "norm") else None
+        act = self.act[0] if hasattr(self, "act") else None
+        gelu = isinstance(act, nn.GELU) and act.approximate == "none"
+        feat_cd = None
+        if (bn is None or (isinstance(bn, nn.BatchNorm1d) and not bn.training)) and (act is None or gelu) \
+                and pooled.shape[1] % 4 == 0:
+            # eval BatchNorm + GELU + the bf16 copy for the next conv / GEMM in one pass over the pooled rows
+            s, t = (None, None) if bn is None else _cached(
+                self, "bn", [bn.weight, bn.bias, bn.running_mean, bn.running_var], lambda: _bn_scale_shift(bn))
+            feat, feat_cd = ops.affine_act(pooled, s, t, "gelu" if gelu else "none", want_f32=True,
+                                           want_bf16=cd == torch.bfloat16)
+        else:
+            feat = pooled.float()
+            if bn is not None:
                 feat = bn(feat)
-        if hasattr(self, "act"):
-            feat = self.act[0](feat)
+            if act is not None:
+                feat = act(feat)
         n_scenes = len(point.offset)
         new = Point(feat=feat, coord=coord, grid_coord=grid_coord, serialized_code=code, serialized_order=order,
                     serialized_inverse=inverse, serialized_depth=point.serialized_depth - pooling_depth, batch=batch,
@@ -371,7 +378,7 @@ class SerializedPooling(PointModule):
         if self.traceable:
             new["pooling_inverse"] = pf["cluster"]
             new["pooling_parent"] = point
-        new["_feat_cd"] = feat if cd == torch.float32 else feat.to(cd)
+        new["_feat_cd"] = feat_cd if feat_cd is not None else (feat if cd == torch.float32 else feat.to(cd))
         new["sparse_shape"] = [(1 << max(int(new.serialized_depth), 0)) + 96] * 3
         new["sparse_conv_feat"] = SparseConvTensor(new["_feat_cd"], indices4, new["sparse_shape"], n_scenes)
         return new
@@ -457,10 +464,14 @@ class Embedding(PointModule):
             y = conv.conv(feat_in, sp)
             if bn is not None:
                 y = bn(y)
-        if hasattr(self.stem, "act"):
-            y = self.stem.act(y)
+        ycd = None
+        act = getattr(self.stem, "act", None)
+        if isinstance(act, nn.GELU) and act.approximate == "none" and y.shape[1] % 4 == 0:
+            y, ycd = ops.affine_act(y, None, None, "gelu", want_f32=True, want_bf16=cd == torch.bfloat16)
+        elif act is not None:
+            y = act(y)
         point.feat = y
-        point["_feat_cd"] = y if cd == torch.float32 else y.to(cd)
+        point["_feat_cd"] = ycd if ycd is not None else (y if cd == torch.float32 else y.to(cd))
         point.sparse_conv_feat = sp.replace_feature(point["_feat_cd"])
         return point
 
@@ -592,7 +603,7 @@ class OffsetKeypointPTv3(nn.Module):
         prev = torch.backends.cuda.matmul.allow_tf32
         torch.backends.cuda.matmul.allow_tf32 = bool(tf32)
         try:
-            h = F.relu(F.linear(feat.float(), w, b), inplace=True)
+            h = torch._addmm_activation(b, feat.float(), w.t())      # GEMM + bias + ReLU epilogue (cuBLASLt), exact
             pred = F.linear(h, self.head[3].weight.float(), self.head[3].bias.float())
         finally:
             torch.backends.cuda.matmul.allow_tf32 = prev

@@ -406,3 +406,19 @@ def keypoint_aggregate(coord, pred, offset, mode="argmax", mask_thresh=0.5):
                                            {"argmax": 0, "weighted": 1}[mode], float(mask_thresh), _p(out), _stream()),
                "ptv3_keypoint_aggregate")
     return out
+
+
+# ------------------------------------------------------------------ A6 glue: per-channel affine + activation
+def affine_act(x, scale=None, shift=None, act="none", want_f32=True, want_bf16=False):
+    """act(x * scale + shift) per channel in one pass -> (fp32 or None, bf16 or None).  act: none | gelu | relu."""
+    _need_cuda(x)
+    lib = _lib.load()
+    x = x.contiguous()
+    n, c = x.shape
+    o32 = torch.empty((n, c), dtype=torch.float32, device=x.device) if want_f32 else None
+    o16 = torch.empty((n, c), dtype=torch.bfloat16, device=x.device) if want_bf16 else None
+    sc = scale.contiguous().float() if scale is not None else None
+    sh = shift.contiguous().float() if shift is not None else None
+    _lib.check(lib.ptv3_affine_act(_p(x), _dt(x), _p(sc), _p(sh), {"none": 0, "gelu": 1, "relu": 2}[act], n, c,
+                                   _p(o32), _p(o16), _stream()), "ptv3_affine_act")
+    return o32, o16

@@ -349,3 +349,18 @@ def test_keypoint_aggregate_matches_oracle(mode):
         ref = P.aggregate_keypoints(coord[start:start + sz], pred[start:start + sz], mode=mode)
         assert torch.allclose(out[b], ref, rtol=1e-5, atol=1e-5), (b, (out[b] - ref).abs().max())
         start += sz
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("act", ["none", "gelu", "relu"])
+def test_affine_act(dtype, act):
+    """ptv3_affine_act = act(x * s + t) (eval BatchNorm + GELU after pooling, :433-437) against torch fp32."""
+    from ptv3_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(1003, 64, generator=g).to(dtype)
+    s, t = torch.randn(64, generator=g), torch.randn(64, generator=g)
+    ref = x.float() * s + t
+    ref = {"none": ref, "gelu": torch.nn.functional.gelu(ref), "relu": torch.relu(ref)}[act]
+    o32, o16 = ops.affine_act(x.cuda(), s.cuda(), t.cuda(), act, want_f32=True, want_bf16=True)
+    assert torch.allclose(o32.cpu(), ref, rtol=1e-5, atol=1e-6)
+    assert torch.equal(o16.cpu(), o32.cpu().bfloat16())
