@@ -224,3 +224,11 @@ def test_subm_map_vs_oracle():
         ref = O.subm_neighbor_table(torch.from_numpy(idx), k).numpy()
         got = ops.subm_build_map(dev(idx), k).cpu().numpy()
         assert np.array_equal(got, ref)
+        # duplicate sites (not produced by GridSample, but allowed by the ABI): the lowest row of a site is the one
+        # every neighbour refers to, and a duplicate row gets the same neighbour row as its canonical row
+        dup = np.concatenate([idx, idx[:100]], 0)
+        got2 = ops.subm_build_map(dev(dup), k).cpu().numpy()
+        assert np.array_equal(got2[: len(idx)], ref)
+        assert np.array_equal(got2[len(idx):], ref[:100])
+    one = ops.subm_build_map(dev(idx), 1).cpu().numpy()
+    assert np.array_equal(one[:, 0], np.arange(len(idx)))
