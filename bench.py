@@ -277,7 +277,7 @@ def run_ours(args):
             roof["exp_per_s"] = round(e["units"] / (e["ms"] * 1e-3) / 1e12, 3)
             roof["exp_peak_mufu_per_s"] = round(16 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 3)
     cpu = None
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:      # reported at N = 1 only
         cpu = cpu_baseline(args, seconds=20.0)
 
     if rank == 0:

@@ -55,7 +55,8 @@ __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr)
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr));
 }
 
-// smem: K [kpad][16] bf16 then V [kpad][16] bf16, kpad = keys rounded up to 64
+// smem: K [kpad][16] bf16, V [kpad][16] bf16, then the window's storage rows order_s [kpad] int32 (the queries
+// of a window are a sub-range of its keys, so the Q gather and the output scatter index through it as well)
 __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
     const __nv_bfloat16* __restrict__ qkv, const int64_t* __restrict__ order, const int64_t* __restrict__ windows,
     const int64_t* __restrict__ n_windows, int h, float scale_log2, int kpad_max, __nv_bfloat16* __restrict__ out) {
@@ -68,6 +69,7 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
   if (kpad > kpad_max) return;  // caller guarantees max_len; never taken
   __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smem_raw);
   __nv_bfloat16* Vs = Ks + (size_t)kpad * kD;
+  int* order_s = reinterpret_cast<int*>(Vs + (size_t)kpad * kD);
   const uint32_t ks_addr = (uint32_t)__cvta_generic_to_shared(Ks);
   const uint32_t vs_addr = (uint32_t)__cvta_generic_to_shared(Vs);
   const int64_t rs = (int64_t)3 * h * kD;
@@ -79,6 +81,7 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
     uint32_t dst = (part < 2 ? ks_addr : vs_addr) + (uint32_t)(key * 32 + (part & 1) * 16);
     if (key < kl) {
       int64_t row = order ? order[k0 + key] : k0 + key;
+      if (part == 0) order_s[key] = (int)row;
       const __nv_bfloat16* src = qkv + row * rs + (int64_t)(part < 2 ? 1 : 2) * h * kD + head * kD + (part & 1) * 8;
       cp_async16(dst, src);
     } else {
@@ -101,24 +104,34 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
 
   // blockIdx.z splits the query tiles of one (window, head) over gridDim.z CTAs (each stages K/V itself): finer
   // granularity for launches whose CTA count is a small non-integer number of waves
-  for (int qt = warp * (int)gridDim.z + (int)blockIdx.z; qt < n_qtiles; qt += kWarps * (int)gridDim.z) {
-    // ---- Q fragment (A operand, 16 x 16) straight from global ----
-    const int64_t qi0 = (int64_t)qt * 16 + g, qi1 = qi0 + 8;
-    const bool v0 = qi0 < ql, v1 = qi1 < ql;
-    int64_t row0 = 0, row1 = 0;
-    uint32_t qa[4] = {0u, 0u, 0u, 0u};
-    if (v0) {
-      row0 = order ? order[q0 + qi0] : q0 + qi0;
-      const uint32_t* p = reinterpret_cast<const uint32_t*>(qkv + row0 * rs + head * kD);
+  // Q fragments (A operand, 16 x 16) come straight from global memory; the fragment of the warp's NEXT query tile is
+  // requested before the key loop of the current one, so its L2 / HBM latency hides behind ~64 k scores of work
+  const int q_rel = (int)(q0 - k0);   // queries are rows q_rel .. q_rel + ql - 1 of the staged key range
+  auto load_q = [&](int qt, uint32_t (&qa)[4]) {
+    qa[0] = qa[1] = qa[2] = qa[3] = 0u;
+    const int qi0 = qt * 16 + g, qi1 = qi0 + 8;
+    if (qi0 < ql) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(qkv + (int64_t)order_s[q_rel + qi0] * rs + head * kD);
       qa[0] = p[t];
       qa[2] = p[t + 4];
     }
-    if (v1) {
-      row1 = order ? order[q0 + qi1] : q0 + qi1;
-      const uint32_t* p = reinterpret_cast<const uint32_t*>(qkv + row1 * rs + head * kD);
+    if (qi1 < ql) {
+      const uint32_t* p = reinterpret_cast<const uint32_t*>(qkv + (int64_t)order_s[q_rel + qi1] * rs + head * kD);
       qa[1] = p[t];
       qa[3] = p[t + 4];
     }
+  };
+  const int qt_step = kWarps * (int)gridDim.z;
+  uint32_t qa_next[4];
+  {
+    const int qt_first = warp * (int)gridDim.z + (int)blockIdx.z;
+    if (qt_first < n_qtiles) load_q(qt_first, qa_next);
+  }
+  for (int qt = warp * (int)gridDim.z + (int)blockIdx.z; qt < n_qtiles; qt += qt_step) {
+    uint32_t qa[4] = {qa_next[0], qa_next[1], qa_next[2], qa_next[3]};
+    if (qt + qt_step < n_qtiles) load_q(qt + qt_step, qa_next);
+    const int qi0 = qt * 16 + g, qi1 = qi0 + 8;
+    const bool v0 = qi0 < ql, v1 = qi1 < ql;
     float o[2][4], l[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) o[0][i] = o[1][i] = l[i] = 0.f;
@@ -182,13 +195,13 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
     // ---- epilogue: normalise, write bf16 pairs to storage rows ----
     if (v0) {
       float inv = 1.f / l[0];
-      uint32_t* p = reinterpret_cast<uint32_t*>(out + row0 * (int64_t)h * kD + head * kD);
+      uint32_t* p = reinterpret_cast<uint32_t*>(out + (int64_t)order_s[q_rel + qi0] * h * kD + head * kD);
       p[t] = pack_bf16(o[0][0] * inv, o[0][1] * inv);
       p[t + 4] = pack_bf16(o[1][0] * inv, o[1][1] * inv);
     }
     if (v1) {
       float inv = 1.f / l[2];
-      uint32_t* p = reinterpret_cast<uint32_t*>(out + row1 * (int64_t)h * kD + head * kD);
+      uint32_t* p = reinterpret_cast<uint32_t*>(out + (int64_t)order_s[q_rel + qi1] * h * kD + head * kD);
       p[t] = pack_bf16(o[0][2] * inv, o[0][3] * inv);
       p[t + 4] = pack_bf16(o[1][2] * inv, o[1][3] * inv);
     }
@@ -202,7 +215,7 @@ int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
                    cudaStream_t st) {
   (void)n;
   int kpad = (int)(cdiv(max_len, kChunk) * kChunk);
-  size_t smem = (size_t)kpad * kD * 2 * 2;
+  size_t smem = (size_t)kpad * kD * 2 * 2 + (size_t)kpad * 4;
   if (smem > 200 * 1024) return PTV3_EUNSUPPORTED;  // patch > 3200
   static size_t configured = 0;
   if (smem > configured) {
