@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
   //  V (trans): matrices {keys 0-7 dims 0-7, keys 8-15 dims 0-7, keys 0-7 dims 8-15, keys 8-15 dims 8-15}
   const uint32_t v_lane_off = (uint32_t)(((((lane >> 3) & 1) << 3) + (lane & 7)) * 32 + (lane >> 4) * 16);
   const uint32_t ones = 0x3f803f80u;  // bf16 (1.0, 1.0)
+  const float lazy_thr = 8.0f / scale_log2;   // raw-score distance that corresponds to a factor 2^8
 
   // blockIdx.z splits the query tiles of one (window, head) over gridDim.z CTAs (each stages K/V itself): finer
   // granularity for launches whose CTA count is a small non-integer number of waves
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
     float o[2][4], l[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) o[0][i] = o[1][i] = l[i] = 0.f;
-    float m0 = -INFINITY, m1 = -INFINITY;  // running maxima (raw score units) of rows g and g+8
+    float m0 = -INFINITY, m1 = -INFINITY;  // reference maxima (raw score units) of rows g and g+8
 
     for (int c = 0; c < n_chunks; ++c) {
       float s[8][4];
@@ -158,25 +159,32 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
           if (key + 1 >= kl) s[b][1] = s[b][3] = -INFINITY;
         }
       }
-      float mx0 = m0, mx1 = m1;
+      // Lazy rescaling: the running maxima m0 / m1 are only a reference point of the exponent, so they are moved
+      // (quad shuffles, two exponentials, rescale of o and l) only when some row of the warp saw a score more than
+      // 2^8 above its reference; otherwise P = 2^(s - m) <= 256 is as exact as before and the chunk skips all of it.
+      float mx0 = s[0][0], mx1 = s[0][2];
 #pragma unroll
       for (int b = 0; b < 8; ++b) {
         mx0 = fmaxf(mx0, fmaxf(s[b][0], s[b][1]));
         mx1 = fmaxf(mx1, fmaxf(s[b][2], s[b][3]));
       }
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-      const float a0 = ex2((m0 - mx0) * scale_log2), a1 = ex2((m1 - mx1) * scale_log2);
-      m0 = mx0;
-      m1 = mx1;
-      const float ms0 = mx0 * scale_log2, ms1 = mx1 * scale_log2;
+      if (__any_sync(0xffffffffu, mx0 > m0 + lazy_thr || mx1 > m1 + lazy_thr)) {
+        mx0 = fmaxf(mx0, m0);
+        mx1 = fmaxf(mx1, m1);
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float a0 = ex2((m0 - mx0) * scale_log2), a1 = ex2((m1 - mx1) * scale_log2);
+        m0 = mx0;
+        m1 = mx1;
 #pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        o[i][0] *= a0; o[i][1] *= a0; o[i][2] *= a1; o[i][3] *= a1;
+        for (int i = 0; i < 2; ++i) {
+          o[i][0] *= a0; o[i][1] *= a0; o[i][2] *= a1; o[i][3] *= a1;
+        }
+        l[0] *= a0; l[1] *= a0; l[2] *= a1; l[3] *= a1;
       }
-      l[0] *= a0; l[1] *= a0; l[2] *= a1; l[3] *= a1;
+      const float ms0 = m0 * scale_log2, ms1 = m1 * scale_log2;
       const uint32_t vc = vs_addr + (uint32_t)(c * kChunk * 32);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {  // 16 keys per step
