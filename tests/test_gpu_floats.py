@@ -233,6 +233,29 @@ def test_attention_ragged_vs_oracle(counts, K, H):
     assert rel_l2(out, refb) < 6e-3
 
 
+@pytest.mark.parametrize("gain", [4.0, 12.0])
+def test_attention_moving_maximum(gain):
+    """Lazy rescaling of the tensor-core kernel: keys whose scores keep growing along the window (the reference maximum
+    moves in jumps both below and far above the 2^8 threshold) and peaked softmaxes, against the fp32 oracle."""
+    from ptv3_b200 import ops
+    torch.manual_seed(3)
+    counts, K, H = [2048, 900], 1024, 2
+    n, C = sum(counts), H * 16
+    qkv = torch.randn(n, 3, H, 16)
+    ramp = torch.linspace(0.0, 1.0, n)[:, None, None]
+    qkv[:, 0] = qkv[:, 0].abs() * gain                     # positive queries ...
+    qkv[:, 1] = qkv[:, 1].abs() * (0.2 + ramp * gain)      # ... and keys that grow with the row index
+    qkv = qkv.reshape(n, 3 * C)
+    offset = np.cumsum(counts)
+    order = torch.arange(n)
+    qb = qkv.bfloat16()
+    refb = O.window_attention(qb.float(), order, order.clone(), offset, H, K)
+    w, nw = ops.build_windows(torch.from_numpy(offset).cuda(), K, n)
+    got = ops.attn_window(qb.cuda(), order.cuda(), w, nw, H, K, algo=2)
+    assert torch.isfinite(got).all()
+    assert rel_l2(got, refb) < 6e-3, rel_l2(got, refb)
+
+
 def _weights():
     from conftest import GOLDEN
     from ptv3_b200 import synth
