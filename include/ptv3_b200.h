@@ -124,6 +124,10 @@ int ptv3_pool_front(const int64_t* code, const int64_t* order, int64_t rows, int
 int ptv3_pool_gather_ints(const int64_t* grid /* (n,3) */, const int64_t* batch, const int64_t* head, int64_t m,
                           int pool_depth, int64_t* new_grid, int64_t* new_batch, int32_t* new_indices, void* stream);
 
+/* batch id per row from the cumulative offsets (offset2batch, models/utils/misc.py:13-22); n = number of rows
+ * (known to the caller from feat / coord, so no host sync is needed) */
+int ptv3_offset_to_batch(const int64_t* offset, int64_t n_scenes, int64_t n, int64_t* batch, void* stream);
+
 /* offset (cumulative scene sizes, int64 (n_scenes)) from a sorted batch vector */
 int ptv3_batch_to_offset(const int64_t* batch, int64_t n, int64_t n_scenes, int64_t* offset, void* stream);
 

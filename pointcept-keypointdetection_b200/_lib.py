@@ -29,6 +29,7 @@ SIGNATURES = {
     "ptv3_pool_front": (c_int, [c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                 c_vp, c_sz, c_vp]),
     "ptv3_pool_gather_ints": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "ptv3_offset_to_batch": (c_int, [c_vp, c_i64, c_i64, c_vp, c_vp]),
     "ptv3_batch_to_offset": (c_int, [c_vp, c_i64, c_i64, c_vp, c_vp]),
     "ptv3_segment_csr": (c_int, [c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp]),
     "ptv3_unpool_add": (c_int, [c_vp, c_vp, c_int, c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp]),

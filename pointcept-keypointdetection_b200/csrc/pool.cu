@@ -111,6 +111,22 @@ __global__ void fill_i64_kernel(int64_t* p, int64_t v, int64_t n) {
   if (i < n) p[i] = v;
 }
 
+// offset2batch (utils/misc.py:13-22) without the host sync of repeat_interleave: row i belongs to the first scene
+// whose cumulative offset exceeds i (binary search over the few scene offsets); rows beyond offset[-1] get the
+// last scene
+__global__ void __launch_bounds__(256) offset_to_batch_kernel(const int64_t* __restrict__ offset, int64_t n_scenes,
+                                                              int64_t n, int64_t* __restrict__ batch) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t lo = 0, hi = n_scenes - 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (offset[mid] > i) hi = mid;
+      else lo = mid + 1;
+    }
+    batch[i] = lo;
+  }
+}
+
 }  // namespace ptv3
 
 using namespace ptv3;
@@ -156,6 +172,14 @@ int ptv3_pool_gather_ints(const int64_t* grid, const int64_t* batch, const int64
   if (m == 0) return PTV3_OK;
   pool_gather_ints_kernel<<<grid_for(m, 256), 256, 0, as_stream(stream)>>>(grid, batch, head, m, pool_depth, new_grid,
                                                                            new_batch, new_indices);
+  return check_launch();
+}
+
+int ptv3_offset_to_batch(const int64_t* offset, int64_t n_scenes, int64_t n, int64_t* batch, void* stream) {
+  if (n < 0 || n_scenes < 1 || !offset) return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!batch) return PTV3_EINVAL;
+  offset_to_batch_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(offset, n_scenes, n, batch);
   return check_launch();
 }
 

@@ -190,6 +190,17 @@ def pool_gather_ints(grid, batch, head, pool_depth, m=None, want_grid=True, want
     return ng, nb, ni
 
 
+def offset_to_batch(offset, n):
+    """offset2batch (utils/misc.py:13-22) for n rows, no host sync."""
+    _need_cuda(offset)
+    lib = _lib.load()
+    offset = offset.contiguous().long()
+    batch = torch.empty(int(n), dtype=torch.int64, device=offset.device)
+    _lib.check(lib.ptv3_offset_to_batch(_p(offset), offset.numel(), int(n), _p(batch), _stream()),
+               "ptv3_offset_to_batch")
+    return batch
+
+
 def batch_to_offset(batch, n_scenes):
     _need_cuda(batch)
     lib = _lib.load()

@@ -55,7 +55,11 @@ class Point(dict):
     def __init__(self, *args, **kwargs):
         super().__init__(*args, **kwargs)
         if "batch" not in self and "offset" in self:
-            self["batch"] = offset2batch(self["offset"])
+            rows = next((self[k] for k in ("feat", "coord", "grid_coord") if k in self), None)
+            if rows is not None and self["offset"].is_cuda:
+                self["batch"] = ops.offset_to_batch(self["offset"], rows.shape[0])   # row count known: no host sync
+            else:
+                self["batch"] = offset2batch(self["offset"])
         elif "offset" not in self and "batch" in self:
             self["offset"] = batch2offset(self["batch"])
 

@@ -200,6 +200,12 @@ def test_batch_to_offset_with_empty_scenes():
     batch = np.array([1, 1, 1, 4, 4, 6])
     off = ops.batch_to_offset(dev(batch), 8).cpu().numpy()
     assert np.array_equal(off, np.cumsum(np.bincount(batch, minlength=8)))
+    # and back: offset2batch (utils/misc.py:13-22) skips the empty scenes exactly like repeat_interleave
+    got = ops.offset_to_batch(dev(off), len(batch)).cpu().numpy()
+    assert np.array_equal(got, batch)
+    sizes = np.array([70001, 1, 0, 33333, 5])
+    ref = np.repeat(np.arange(len(sizes)), sizes)
+    assert np.array_equal(ops.offset_to_batch(dev(np.cumsum(sizes)), int(sizes.sum())).cpu().numpy(), ref)
 
 
 def test_windows_golden(golden):
