@@ -246,6 +246,33 @@ int ptv3_affine_act(const void* x, int dtype_x, const float* scale, const float*
 int ptv3_keypoint_aggregate(const float* coord, const float* pred, const int64_t* offset, int64_t n_scenes, int k_pts,
                             int mode, float mask_thresh, float* out, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * backward of the ops that carry gradients (training step, engines/train.py:184-245 drives
+ * loss.backward() through spconv / flash_attn / torch_scatter autograd functions in the reference).
+ * All gradients are fp32; forward operands are `dtype` (PTV3_F32 / PTV3_BF16).
+ *
+ * SubMConv3d weight gradient: dweight[k][o][c] += sum_i dout[i][o] * in[nbr[i,k]][c]  (accumulates; the caller
+ * zeroes it).  The data gradient is the forward conv of `dout` with weights W'[k] = W[k3-1-k]^T (the neighbour
+ * map is symmetric), i.e. ptv3_subm_conv / ptv3_subm_conv_packed again.
+ * ------------------------------------------------------------------------- */
+int ptv3_subm_wgrad(const void* in, const void* dout, const int32_t* nbr, int64_t n, int c_in, int c_out, int k3,
+                    int dtype, float* dweight /* (k3,c_out,c_in) */, void* stream);
+
+/* Window attention backward (flash_attn_varlen_qkvpacked_func's backward, point_transformer_v3m1_base.py:208-215).
+ * qkv (n,3,h,16), out / dout (n,h,16) in `dtype`; dqkv (n,3,h,16) fp32, ZEROED by the caller (the K / V parts are
+ * accumulated: the last window of a scene shares keys with the one before it). */
+size_t ptv3_attn_window_bwd_workspace(int64_t n, int h);
+int ptv3_attn_window_bwd(const void* qkv, const void* out, const void* dout, int dtype, const int64_t* order,
+                         const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max, int64_t max_len,
+                         int64_t n, int h, int d, float scale, float* dqkv, void* workspace, size_t workspace_bytes,
+                         void* stream);
+
+/* torch_scatter.segment_csr backward (:416-421): dsrc[gather[j]] for every j of segment k from dout[k];
+ * max / min give the gradient to the first row (CSR order) that equals the reduced value. */
+int ptv3_segment_csr_bwd(const float* dout, const void* src, const void* out, int dtype,
+                         const int64_t* gather /* NULL ok */, const int64_t* indptr, int64_t m, int64_t c, int reduce,
+                         float* dsrc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -148,8 +148,8 @@ def segment_csr(src, indptr, reduce="sum"):
     out = torch.segment_reduce(src, r, lengths=lengths, axis=0, unsafe=True)
     if reduce in ("max", "min", "mean"):
         empty = lengths == 0
-        if bool(empty.any()):
-            out[empty] = 0
+        if bool(empty.any()):       # out-of-place so that autograd through the oracle keeps working
+            out = torch.where(empty.view(-1, *([1] * (out.dim() - 1))), torch.zeros((), dtype=out.dtype), out)
     return out
 
 

@@ -41,7 +41,12 @@ BASE_CFG = dict(
 )
 
 
+BN_TRAIN = False     # tests of the training step set this: nn.BatchNorm1d in train() uses batch statistics
+
+
 def _bn(x, W, p, eps=1e-3):
+    if BN_TRAIN:
+        return F.batch_norm(x, None, None, W[p + ".weight"], W[p + ".bias"], True, 0.0, eps)
     return (x - W[p + ".running_mean"]) / torch.sqrt(W[p + ".running_var"] + eps) * W[p + ".weight"] + W[p + ".bias"]
 
 
@@ -192,6 +197,36 @@ def keypoint_head(W, feat, batch, num_keypoints=6):
 def seg_head(W, feat):
     """DefaultSegmentorV2 (default.py:63-95): PTv3 with decoder has no pooling_parent left."""
     return _lin(feat, W, "seg_head")
+
+
+def offset_keypoint_loss(W, feat, target, num_keypoints=6):
+    """OffsetKeypointPTv3 training branch (offset_keypoint_ptv3.py:44-86): BCE-with-logits on every point's mask
+    channel + 2 x masked L1 on the offsets.  Differentiable (call the un-decorated backbone_forward.__wrapped__
+    under torch.enable_grad() for gradients)."""
+    h = F.relu(_bn(_lin(feat, W, "head.0"), W, "head.1", eps=1e-5))
+    pred = _lin(h, W, "head.3").view(-1, num_keypoints, 4)
+    offset_gt, mask_gt = target[..., :3], target[..., 3]
+    cls_loss = F.binary_cross_entropy_with_logits(pred[..., 3], mask_gt, reduction="none").mean()
+    valid = (mask_gt > 0.5).float().unsqueeze(-1)
+    reg_loss = (F.l1_loss(pred[..., :3], offset_gt, reduction="none") * valid).sum() / (valid.sum() * 3 + 1e-6)
+    return cls_loss + reg_loss * 2.0
+
+
+def offset_keypoint_grads(W, coord, grid_coord, feat, offset, target, perms=None, cfg=BASE_CFG, bn_train=True):
+    """loss and d loss / d W for every floating weight (engines/train.py:184-245: forward in train(), loss.backward()).
+    DropPath is not modelled (tests build the reference with drop_path = 0)."""
+    global BN_TRAIN
+    Wg = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and "running_" not in k else v)
+          for k, v in W.items()}
+    prev, BN_TRAIN = BN_TRAIN, bool(bn_train)
+    try:
+        with torch.enable_grad():
+            pt = backbone_forward.__wrapped__(Wg, coord, grid_coord, feat, offset, cfg=cfg, perms=perms)
+            loss = offset_keypoint_loss(Wg, pt.feat, torch.as_tensor(target))
+            loss.backward()
+    finally:
+        BN_TRAIN = prev
+    return loss.detach(), {k: v.grad for k, v in Wg.items() if v.requires_grad and v.grad is not None}
 
 
 def aggregate_keypoints(coord, pred, mode="argmax", scale=1.0, centroid=0.0, mask_thresh=0.5):

@@ -1,0 +1,122 @@
+"""torch.autograd.Function wrappers of the custom kernels that carry gradients in the training step
+(the reference gets these from spconv / flash_attn / torch_scatter autograd functions behind
+engines/train.py:184-245).  Forward = the inference kernels; backward = csrc/backward.cu plus re-use of the forward
+kernels where the adjoint is the same operator:
+
+  SubMConv3d   dX = conv(dY; W'[k] = W[k3-1-k]^T) over the same (symmetric) neighbour map, dW = ptv3_subm_wgrad
+  attention    ptv3_attn_window_bwd (log-sum-exp recomputed per row, no stored probabilities)
+  segment_csr  ptv3_segment_csr_bwd (max: first row equal to the maximum, like torch_scatter's arg output)
+  x[inverse]   segment sum over the pooling CSR (deterministic; no atomics)
+
+No CPU fallback: every op raises on non-CUDA tensors (ops._need_cuda).
+"""
+import torch
+
+from . import ops
+
+
+def _conv(x, w_koc, bias, nbr):
+    """x (N,Cin), w (k3,Cout,Cin) in x.dtype -> (N,Cout); tcgen05 kernel when the shape allows it."""
+    k3, cout, cin = w_koc.shape
+    if x.dtype == torch.bfloat16 and ops.subm_conv_tc_supported(cin, cout, k3):
+        return ops.subm_conv_packed(x, ops.subm_pack_weight(w_koc), bias, nbr, cout)
+    return ops.subm_conv(x, w_koc, bias, nbr)
+
+
+class SubMConvFn(torch.autograd.Function):
+    """feat (N,Cin) any float dtype, weight (Cout,k,k,k,Cin) fp32 parameter, bias (Cout) or None, nbr (N,k^3) int32.
+    Operands are cast to `cd` (what torch.autocast does for the reference's spconv call); output is `cd`."""
+
+    @staticmethod
+    def forward(ctx, feat, weight, bias, nbr, cd):
+        cout, cin = weight.shape[0], weight.shape[-1]
+        k3 = nbr.shape[1]
+        x = feat.detach().to(cd).contiguous()
+        w = weight.detach().reshape(cout, k3, cin).permute(1, 0, 2).contiguous().to(cd)
+        y = _conv(x, w, bias.detach().float() if bias is not None else None, nbr)
+        ctx.save_for_backward(x, w, nbr)
+        ctx.meta = (feat.dtype, weight.shape, bias is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, nbr = ctx.saved_tensors
+        feat_dtype, wshape, has_bias = ctx.meta
+        k3, cout, cin = w.shape
+        dy = dy.contiguous().to(x.dtype)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            wd = w.flip(0).transpose(1, 2).contiguous()          # (k3, Cin, Cout): W'[k] = W[k3-1-k]^T
+            dx = _conv(dy, wd, None, nbr).to(feat_dtype)
+        if ctx.needs_input_grad[1]:
+            dw = ops.subm_wgrad(x, dy, nbr, k3).permute(1, 0, 2).reshape(wshape)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = dy.float().sum(0)
+        return dx, dw, db, None, None
+
+
+class WindowAttnFn(torch.autograd.Function):
+    """qkv (N, 3*H*16) rows in storage order -> (N, H*16); see ops.attn_window."""
+
+    @staticmethod
+    def forward(ctx, qkv, order, windows, n_windows, num_heads, max_len, scale, algo):
+        q = qkv.detach().contiguous()
+        out = ops.attn_window(q, order, windows, n_windows, num_heads, max_len, scale, algo)
+        ctx.save_for_backward(q, out, order, windows, n_windows)
+        ctx.meta = (num_heads, max_len, scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q, out, order, windows, n_windows = ctx.saved_tensors
+        num_heads, max_len, scale = ctx.meta
+        dqkv = ops.attn_window_bwd(q, out, dout, order, windows, n_windows, num_heads, max_len, scale)
+        return dqkv.to(q.dtype), None, None, None, None, None, None, None
+
+
+class SegmentCSRFn(torch.autograd.Function):
+    """torch_scatter.segment_csr(src[gather], indptr, reduce) along dim 0."""
+
+    @staticmethod
+    def forward(ctx, src, indptr, reduce, gather):
+        s = src.detach().contiguous()
+        out = ops.segment_csr(s, indptr, reduce, gather=gather)
+        ctx.save_for_backward(s, out, indptr, gather)
+        ctx.reduce = reduce
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        s, out, indptr, gather = ctx.saved_tensors
+        return ops.segment_csr_bwd(dout, s, out, indptr, ctx.reduce, gather).to(s.dtype), None, None, None
+
+
+class GatherRowsFn(torch.autograd.Function):
+    """y = x[inverse] where (indices, idx_ptr) is the CSR of `inverse` (pooling cluster -> member rows):
+    dx[c] = sum of dy over the rows of cluster c, read through the CSR."""
+
+    @staticmethod
+    def forward(ctx, x, inverse, indices, idx_ptr):
+        ctx.save_for_backward(indices, idx_ptr)
+        return x.detach().index_select(0, inverse)
+
+    @staticmethod
+    def backward(ctx, dy):
+        indices, idx_ptr = ctx.saved_tensors
+        return ops.segment_csr(dy.contiguous(), idx_ptr, "sum", gather=indices), None, None, None
+
+
+def subm_conv(feat, weight, bias, nbr, cd):
+    return SubMConvFn.apply(feat, weight, bias, nbr, cd)
+
+
+def attn_window(qkv, order, windows, n_windows, num_heads, max_len, scale=None, algo=0):
+    return WindowAttnFn.apply(qkv, order, windows, n_windows, num_heads, max_len, scale, algo)
+
+
+def segment_csr(src, indptr, reduce="sum", gather=None):
+    return SegmentCSRFn.apply(src, indptr, reduce, gather)
+
+
+def gather_rows(x, inverse, indices, idx_ptr):
+    return GatherRowsFn.apply(x, inverse, indices, idx_ptr)

@@ -18,7 +18,7 @@ unchanged; the forward of every module is re-designed around our fused ops:
 Attention uses the flash window semantics of the reference (fixed patch size,
 short scenes form one short window, :208-215); its enable_flash=False branch
 only coincides with that for one scene per forward.
-Training (autograd through the kernels) is out of scope for this round.
+Training: in train() mode every entry point dispatches to train.py (autograd through the kernels, autograd.py).
 """
 import math
 
@@ -260,7 +260,8 @@ class Block(PointModule):
         self.norm2 = PointSequential(norm_layer(channels))
         self.mlp = PointSequential(MLP(in_channels=channels, hidden_channels=int(channels * mlp_ratio),
                                        out_channels=channels, act_layer=act_layer, drop=proj_drop))
-        self.drop_path = PointSequential(nn.Identity())   # DropPath is identity in eval (timm)
+        self.drop_path = PointSequential(nn.Identity())   # DropPath is identity in eval (timm); no parameters
+        self.drop_path_rate = float(drop_path)            # used by the training forward (train.block_forward)
         self.compute_dtype = torch.bfloat16
         self.conv_algo = 0
 
@@ -512,8 +513,10 @@ class PointTransformerV3(PointModule):
                       proj_drop=proj_drop, norm_layer=ln_layer, act_layer=act_layer, pre_norm=pre_norm,
                       enable_rpe=enable_rpe, enable_flash=enable_flash, upcast_attention=upcast_attention,
                       upcast_softmax=upcast_softmax)
+        enc_dp = [x.item() for x in torch.linspace(0, drop_path, sum(enc_depths))]                  # :603-610
         self.enc = PointSequential()
         for s in range(self.num_stages):
+            enc_dp_ = enc_dp[sum(enc_depths[:s]):sum(enc_depths[:s + 1])]
             enc = PointSequential()
             if s > 0:
                 enc.add(SerializedPooling(in_channels=enc_channels[s - 1], out_channels=enc_channels[s],
@@ -521,21 +524,25 @@ class PointTransformerV3(PointModule):
                                           shuffle_orders=shuffle_orders), name="down")
             for i in range(enc_depths[s]):
                 enc.add(Block(channels=enc_channels[s], num_heads=enc_num_head[s], patch_size=enc_patch_size[s],
-                              order_index=i % len(self.order), cpe_indice_key=f"stage{s}", **common), name=f"block{i}")
+                              order_index=i % len(self.order), cpe_indice_key=f"stage{s}", drop_path=enc_dp_[i],
+                              **common), name=f"block{i}")
             if len(enc) != 0:
                 self.enc.add(module=enc, name=f"enc{s}")
         if not self.enc_mode:
             self.dec = PointSequential()
             dec_channels = list(dec_channels) + [enc_channels[-1]]
+            dec_dp = [x.item() for x in torch.linspace(0, drop_path, sum(dec_depths))]              # :652-661
             for s in reversed(range(self.num_stages - 1)):
+                dec_dp_ = dec_dp[sum(dec_depths[:s]):sum(dec_depths[:s + 1])]
+                dec_dp_.reverse()
                 dec = PointSequential()
                 dec.add(SerializedUnpooling(in_channels=dec_channels[s + 1], skip_channels=enc_channels[s],
                                             out_channels=dec_channels[s], norm_layer=bn_layer, act_layer=act_layer),
                         name="up")
                 for i in range(dec_depths[s]):
                     dec.add(Block(channels=dec_channels[s], num_heads=dec_num_head[s], patch_size=dec_patch_size[s],
-                                  order_index=i % len(self.order), cpe_indice_key=f"stage{s}", **common),
-                            name=f"block{i}")
+                                  order_index=i % len(self.order), cpe_indice_key=f"stage{s}",
+                                  drop_path=dec_dp_[i], **common), name=f"block{i}")
                 self.dec.add(module=dec, name=f"dec{s}")
         self.set_compute_dtype(compute_dtype)
 
@@ -556,8 +563,14 @@ class PointTransformerV3(PointModule):
                 m.algo = attn
         return self
 
-    @torch.no_grad()
     def forward(self, data_dict):
+        if self.training:                     # autograd path over the same modules
+            from . import train
+            return train.backbone_forward(self, data_dict)
+        return self._forward_eval(data_dict)
+
+    @torch.no_grad()
+    def _forward_eval(self, data_dict):
         point = Point(data_dict)
         point.serialization(order=self.order, shuffle_orders=self.shuffle_orders)
         point.sparsify()
@@ -584,10 +597,14 @@ class OffsetKeypointPTv3(nn.Module):
         self.head = nn.Sequential(nn.Linear(in_channels, hidden_dim), nn.BatchNorm1d(hidden_dim),
                                   nn.ReLU(inplace=True), nn.Linear(hidden_dim, num_keypoints * 4))
 
-    @torch.no_grad()
     def forward(self, data_dict):
         if self.training:
-            raise NotImplementedError("ptv3_b200 OffsetKeypointPTv3: inference only (call .eval())")
+            from . import train
+            return train.offset_keypoint_forward(self, data_dict)
+        return self._forward_eval(data_dict)
+
+    @torch.no_grad()
+    def _forward_eval(self, data_dict):
         point = self.backbone(data_dict)
         feat = point.feat if isinstance(point, Point) else point
         lin, bn = self.head[0], self.head[1]
@@ -628,10 +645,14 @@ class KeypointPTv3(nn.Module):
                                       nn.ReLU(inplace=True), nn.Dropout(0.3), nn.Linear(hidden_dim, hidden_dim),
                                       nn.ReLU(inplace=True), nn.Linear(hidden_dim, num_keypoints * 3))
 
-    @torch.no_grad()
     def forward(self, data_dict):
         if self.training:
-            raise NotImplementedError("ptv3_b200 KeypointPTv3: inference only (call .eval())")
+            from . import train
+            return train.keypoint_forward(self, data_dict)
+        return self._forward_eval(data_dict)
+
+    @torch.no_grad()
+    def _forward_eval(self, data_dict):
         point = self.backbone(data_dict)
         indptr = F.pad(point.offset, (1, 0))
         g = ops.segment_csr(point.feat.float(), indptr, "mean", long_segments=True)
@@ -650,8 +671,14 @@ class DefaultSegmentorV2(nn.Module):
         self.backbone = backbone
         self.seg_head = nn.Linear(backbone_out_channels, num_classes) if num_classes > 0 else nn.Identity()
 
-    @torch.no_grad()
     def forward(self, input_dict, return_point=False):
+        if self.training:
+            from . import train
+            return train.segmentor_forward(self, input_dict)
+        return self._forward_eval(input_dict, return_point)
+
+    @torch.no_grad()
+    def _forward_eval(self, input_dict, return_point=False):
         point = self.backbone(Point(input_dict))
         while isinstance(point, Point) and "pooling_parent" in point:     # enc_mode backbones (:74-82)
             parent = point.pop("pooling_parent")

@@ -433,3 +433,57 @@ def affine_act(x, scale=None, shift=None, act="none", want_f32=True, want_bf16=F
     _lib.check(lib.ptv3_affine_act(_p(x), _dt(x), _p(sc), _p(sh), {"none": 0, "gelu": 1, "relu": 2}[act], n, c,
                                    _p(o32), _p(o16), _stream()), "ptv3_affine_act")
     return o32, o16
+
+
+# ------------------------------------------------------------------ backward kernels
+def subm_wgrad(feat, dout, nbr, k3):
+    """dW (k3, Cout, Cin) fp32 = sum_i dout[i] (x) feat[nbr[i,k]]."""
+    _need_cuda(feat, dout, nbr)
+    lib = _lib.load()
+    feat, dout = feat.contiguous(), dout.contiguous()
+    assert feat.dtype == dout.dtype and nbr.dtype == torch.int32 and nbr.shape == (feat.shape[0], k3)
+    n, cin = feat.shape
+    cout = dout.shape[1]
+    dw = torch.zeros((k3, cout, cin), dtype=torch.float32, device=feat.device)
+    _lib.check(lib.ptv3_subm_wgrad(_p(feat), _p(dout), _p(nbr.contiguous()), n, cin, cout, int(k3), _dt(feat), _p(dw),
+                                   _stream()), "ptv3_subm_wgrad")
+    return dw
+
+
+def attn_window_bwd(qkv, out, dout, order, windows, n_windows, num_heads, max_len, scale=None):
+    """Gradient of attn_window w.r.t. qkv: (N, 3*H*16) fp32."""
+    _need_cuda(qkv, out, dout, order, windows, n_windows)
+    lib = _lib.load()
+    qkv, out = qkv.contiguous(), out.contiguous()
+    dout = dout.contiguous().to(qkv.dtype)
+    n = qkv.shape[0]
+    c = qkv.numel() // (3 * n) if n > 0 else 0
+    h = int(num_heads)
+    d = c // h if h else 0
+    dqkv = torch.zeros((n, 3 * c), dtype=torch.float32, device=qkv.device)
+    if n == 0:
+        return dqkv
+    scale = float(scale) if scale is not None else d ** -0.5
+    o = order.contiguous().long() if order is not None else None
+    ws = _ws(lib.ptv3_attn_window_bwd_workspace(n, h), qkv.device)
+    _lib.check(lib.ptv3_attn_window_bwd(_p(qkv), _p(out), _p(dout), _dt(qkv), _p(o), _p(windows), _p(n_windows),
+                                        windows.shape[0], int(max_len), n, h, d, scale, _p(dqkv), _p(ws), ws.numel(),
+                                        _stream()), "ptv3_attn_window_bwd")
+    return dqkv
+
+
+def segment_csr_bwd(dout, src, out, indptr, reduce="sum", gather=None):
+    """Gradient of segment_csr w.r.t. src: (n_src, c) fp32 (rows outside every segment get 0)."""
+    _need_cuda(dout, src, indptr, gather)
+    lib = _lib.load()
+    src2 = src.contiguous().view(src.shape[0], -1)
+    c = src2.shape[1]
+    indptr = indptr.contiguous().long()
+    m = indptr.numel() - 1
+    dout = dout.contiguous().float().view(m, c)
+    out2 = out.contiguous().view(m, c) if out is not None else None
+    g = gather.contiguous().long() if gather is not None else None
+    dsrc = torch.zeros(src2.shape, dtype=torch.float32, device=src.device)
+    _lib.check(lib.ptv3_segment_csr_bwd(_p(dout), _p(src2), _p(out2), _dt(src2), _p(g), _p(indptr), m, c,
+                                        REDUCE_IDS[reduce], _p(dsrc), _stream()), "ptv3_segment_csr_bwd")
+    return dsrc.view(src.shape)

@@ -1,0 +1,217 @@
+"""Training-mode forward of the same module tree (backward + AMP-style mixed precision + DDP).
+
+`model.py` is the fused inference path; this file walks the SAME nn.Modules (same parameters / state_dict) with
+autograd enabled: the custom kernels enter the graph through `autograd.py`, the dense glue (Linear = cuBLAS,
+LayerNorm, BatchNorm in batch-statistics mode, GELU) is torch, exactly the split the reference has between its
+third-party CUDA ops and torch.  Semantics follow the reference in train() mode:
+
+  * BatchNorm1d uses batch statistics and updates the running ones (:505 `momentum=0.01, eps=1e-3`);
+  * DropPath (timm) drops whole rows of the residual branch with the per-block rate of :603-661;
+  * `compute_dtype` plays the role of torch.autocast (engines/train.py:184): GEMM / conv / attention operands are
+    cast to it, the residual stream, the norms, the head and the loss stay fp32;
+  * the loss of OffsetKeypointPTv3 is offset_keypoint_ptv3.py:50-86, of KeypointPTv3 keypoint_ptv3.py:52-63, of
+    DefaultSegmentorV2 the caller's criterion on the logits (default.py:86-88).
+"""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import autograd as A
+from . import ops
+from .structure import Point, SparseConvTensor
+
+
+def _lin(x, lin, cd):
+    return F.linear(x.to(cd), lin.weight.to(cd), lin.bias.to(cd) if lin.bias is not None else None)
+
+
+def _ln(x, ln):
+    return F.layer_norm(x.float(), ln.normalized_shape, ln.weight, ln.bias, ln.eps)
+
+
+def _bn(x, bn):
+    return bn(x.float())            # nn.BatchNorm1d: batch statistics in train(), running ones in eval()
+
+
+def _drop_path(x, rate, training):
+    """timm.layers.DropPath on an (N, C) tensor: one Bernoulli draw per row, kept rows scaled by 1 / keep."""
+    if rate == 0.0 or not training:
+        return x
+    keep = 1.0 - rate
+    mask = x.new_empty((x.shape[0], 1)).bernoulli_(keep)
+    return x * (mask / keep)
+
+
+def embedding_forward(mod, point):
+    conv = mod.stem.conv
+    sp = point.sparse_conv_feat
+    y = A.subm_conv(point.feat.float(), conv.weight, conv.bias, conv.neighbor_map(sp), torch.float32)
+    if hasattr(mod.stem, "norm"):
+        y = _bn(y, mod.stem.norm)
+    if hasattr(mod.stem, "act"):
+        y = mod.stem.act(y)
+    point.feat = y
+    point.sparse_conv_feat = sp.replace_feature(y)
+    return point
+
+
+def block_forward(mod, point):
+    cd = mod.compute_dtype
+    sp = point.sparse_conv_feat
+    x = point.feat.float()
+    conv = mod.cpe[0]
+    y = A.subm_conv(sp.features, conv.weight, conv.bias, conv.neighbor_map(sp), cd)
+    y = _ln(_lin(y, mod.cpe[1], cd), mod.cpe[2])
+    x = x + y
+    att = mod.attn
+    qkv = _lin(_ln(x, mod.norm1[0]), att.qkv, cd)
+    windows, nwin = att.get_windows(point)
+    a = A.attn_window(qkv, point.serialized_order[att.order_index], windows, nwin, att.num_heads, att.patch_size,
+                      att.scale, att.algo)
+    x = x + _drop_path(_lin(a, att.proj, cd).float(), mod.drop_path_rate, mod.training)
+    mlp = mod.mlp[0]
+    f = _lin(mlp.act(_lin(_ln(x, mod.norm2[0]), mlp.fc1, cd)), mlp.fc2, cd)
+    x = x + _drop_path(f.float(), mod.drop_path_rate, mod.training)
+    point.feat = x
+    point["_feat_cd"] = None
+    point.sparse_conv_feat = sp.replace_feature(x)
+    return point
+
+
+def pooling_forward(mod, point):
+    cd = mod.compute_dtype
+    depth = (math.ceil(mod.stride) - 1).bit_length()
+    if depth > point.serialized_depth:
+        depth = 0
+    with torch.no_grad():
+        pf = ops.pool_front(point.serialized_code, point.serialized_order, depth)
+        grid_coord, batch, indices4 = ops.pool_gather_ints(point.grid_coord, point.batch, pf["head"], depth)
+        code, order, inverse = pf["code"], pf["order"], pf["inverse"]
+        if mod.shuffle_orders:
+            perm = torch.randperm(code.shape[0])
+            if not torch.equal(perm, torch.arange(code.shape[0])):
+                perm = perm.to(code.device)
+                code, order, inverse = code[perm], order[perm], inverse[perm]
+        coord = ops.segment_csr(point.coord.float(), pf["idx_ptr"], "mean", gather=pf["indices"])
+        n_scenes = len(point.offset)
+        offset = ops.batch_to_offset(batch, n_scenes)
+    feat = A.segment_csr(_lin(point.feat, mod.proj, cd), pf["idx_ptr"], mod.reduce, pf["indices"]).float()
+    if hasattr(mod, "norm"):
+        feat = _bn(feat, mod.norm[0])
+    if hasattr(mod, "act"):
+        feat = mod.act[0](feat)
+    new = Point(feat=feat, coord=coord, grid_coord=grid_coord, serialized_code=code, serialized_order=order,
+                serialized_inverse=inverse, serialized_depth=point.serialized_depth - depth, batch=batch, offset=offset)
+    for k in ("condition", "context", "grid_size", "order"):
+        if k in point:
+            new[k] = point[k]
+    new["pooling_inverse"] = pf["cluster"]
+    new["pooling_parent"] = point
+    new["_pooling_csr"] = (pf["indices"], pf["idx_ptr"])
+    new["sparse_shape"] = [(1 << max(int(new.serialized_depth), 0)) + 96] * 3
+    new["sparse_conv_feat"] = SparseConvTensor(feat, indices4, new["sparse_shape"], n_scenes)
+    return new
+
+
+def _proj_seq(seq, x, cd):
+    for m in seq:
+        if isinstance(m, nn.Linear):
+            x = _lin(x, m, cd)
+        elif isinstance(m, nn.BatchNorm1d):
+            x = _bn(x, m)
+        else:
+            x = m(x)
+    return x
+
+
+def unpooling_forward(mod, point):
+    cd = mod.compute_dtype
+    parent = point.pop("pooling_parent")
+    inverse = point.pop("pooling_inverse")
+    indices, idx_ptr = point.pop("_pooling_csr")
+    up = _proj_seq(mod.proj, point.feat, cd).float()
+    skip = _proj_seq(mod.proj_skip, parent.feat, cd).float()
+    parent.feat = skip + A.gather_rows(up, inverse, indices, idx_ptr)
+    parent["_feat_cd"] = None
+    # the parent's sparse tensor keeps the proj_skip branch only (reference :476-477, see model.SerializedUnpooling)
+    parent.sparse_conv_feat = parent.sparse_conv_feat.replace_feature(skip)
+    if mod.traceable:
+        parent["unpooling_parent"] = point
+    return parent
+
+
+def backbone_forward(bb, data_dict):
+    from . import model as M
+    point = Point(data_dict)
+    with torch.no_grad():
+        point.serialization(order=bb.order, shuffle_orders=bb.shuffle_orders)
+        point.sparsify()
+    point = embedding_forward(bb.embedding, point)
+    stages = [bb.enc] + ([] if bb.enc_mode else [bb.dec])
+    for seq in stages:
+        for stage in seq._modules.values():
+            for m in stage._modules.values():
+                if isinstance(m, M.Block):
+                    point = block_forward(m, point)
+                elif isinstance(m, M.SerializedPooling):
+                    point = pooling_forward(m, point)
+                elif isinstance(m, M.SerializedUnpooling):
+                    point = unpooling_forward(m, point)
+                else:
+                    raise NotImplementedError(type(m))
+    return point
+
+
+def offset_keypoint_forward(model, data_dict):
+    """offset_keypoint_ptv3.py:37-107: per-point (dx,dy,dz,mask logit); BCE on every point + L1 on the points whose
+    target mask is set (weight 2)."""
+    point = backbone_forward(model.backbone, data_dict)
+    pred = model.head(point.feat.float()).view(-1, model.num_keypoints, 4)
+    out = {}
+    if "target" in data_dict:
+        target = data_dict["target"]
+        offset_gt, mask_gt = target[..., :3], target[..., 3]
+        cls_loss = F.binary_cross_entropy_with_logits(pred[..., 3], mask_gt, reduction="none").mean()
+        valid = (mask_gt > 0.5).float().unsqueeze(-1)
+        reg_loss = (F.l1_loss(pred[..., :3], offset_gt, reduction="none") * valid).sum() / (valid.sum() * 3 + 1e-6)
+        out["loss"] = cls_loss + reg_loss * 2.0
+        out["train/cls_loss"] = cls_loss.detach()
+        out["train/reg_loss"] = reg_loss.detach()
+    if not model.training:
+        final = pred.clone()
+        final[..., 3] = torch.sigmoid(pred[..., 3])
+        out["pred"] = final
+    else:
+        out["pred_logits"] = pred
+    return out
+
+
+def keypoint_forward(model, data_dict):
+    """keypoint_ptv3.py:37-98: per-scene mean pool -> regression MLP; MSE on (B,K,3) targets."""
+    point = backbone_forward(model.backbone, data_dict)
+    feat = point.feat.float()                                        # torch_scatter.scatter_mean over a few long scenes
+    cnt = torch.diff(F.pad(point.offset, (1, 0))).clamp_min(1).to(feat.dtype)
+    g = feat.new_zeros((len(point.offset), feat.shape[1])).index_add_(0, point.batch, feat) / cnt[:, None]
+    pred = model.reg_head(g).view(-1, model.num_keypoints, 3)
+    out = {}
+    if "target" in data_dict:
+        target = data_dict["target"]
+        out["loss"] = F.mse_loss(pred if pred.shape == target.shape else pred.view(-1, 3), target)
+    if not model.training:
+        out["pred"] = pred
+    else:
+        out["pred_train"] = pred
+    return out
+
+
+def segmentor_forward(model, input_dict, criterion=None):
+    """default.py:63-95 with a decoder backbone: logits = seg_head(feat); loss = criterion(logits, segment)."""
+    point = backbone_forward(model.backbone, Point(input_dict))
+    logits = model.seg_head(point.feat.float())
+    out = dict(seg_logits=logits)
+    if "segment" in input_dict:
+        crit = criterion or getattr(model, "criteria", None) or nn.CrossEntropyLoss(ignore_index=-1)
+        out["loss"] = crit(logits, input_dict["segment"])
+    return out

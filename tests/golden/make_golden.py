@@ -11,6 +11,11 @@ Fixtures (all inputs are seeded; the script is the provenance):
   forward.npz        reference OffsetKeypointPTv3 forward (PT-v3m1 base config,
                      deterministic weights synth.make_weights(seed=0)), two
                      scenes run one per forward, with intermediate features
+  train.npz          reference OffsetKeypointPTv3 in train() mode (drop_path 0, BatchNorm batch statistics): loss and
+                     parameter gradients of one scene after loss.backward() (every gradient's norm + six full tensors)
+  heads.npz          reference KeypointPTv3 (scatter_mean + regression MLP, C_in = 4) and
+                     DefaultSegmentorV2 (20 classes, C_in = 6, BASELINE configs[2] shape)
+                     forwards, one scene each, same deterministic weights
 """
 import os
 import sys
@@ -22,6 +27,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, REPO)
 sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(HERE))
 
 import ref_loader  # noqa: E402
 from ptv3_b200 import synth  # noqa: E402
@@ -163,6 +169,79 @@ def gold_forward(R):
     np.savez_compressed(os.path.join(HERE, "forward.npz"), **out)
 
 
+def gold_heads(R):
+    """The two other heads of SURVEY 8a row A9 run through the UNMODIFIED reference classes."""
+    import json
+    from oracle import gridsample as G
+    out, shapes_all = {}, {}
+    coord, feat4 = synth.pig_scan(4000, scale=0.55, seed=21)
+    gs = G.grid_sample(coord, 0.02)
+    iu = gs["idx_unique"]
+    c, g = coord[iu], gs["grid_coord"][iu]
+    rng = np.random.default_rng(77)
+    feat6 = np.concatenate([feat4[iu], rng.normal(size=(len(iu), 2)).astype(np.float32)], 1)
+    out["coord"], out["grid_coord"], out["feat4"], out["feat6"] = c, g, feat4[iu], feat6
+    bb = dict(type="PT-v3m1", enable_flash=False, upcast_attention=False, upcast_softmax=False, **BASE_CFG)
+
+    def run(m, feat, key, tag):
+        shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+        W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+        m.load_state_dict(W, strict=False)
+        shapes_all[tag] = {k: list(v) for k, v in shapes.items() if not k.endswith("num_batches_tracked")}
+        torch.manual_seed(300)
+        out[f"perms_{tag}"] = np.stack([torch.randperm(4).numpy() for _ in range(5)])
+        torch.manual_seed(300)
+        with torch.no_grad():
+            r = m(dict(coord=torch.from_numpy(c), grid_coord=torch.from_numpy(g), feat=torch.from_numpy(feat),
+                       offset=torch.tensor([len(iu)]), grid_size=0.02))
+        out[f"out_{tag}"] = r[key].numpy()
+        print(tag, "N0", len(iu), key, r[key].shape)
+
+    run(R.KeypointPTv3(backbone_conf=dict(bb)).eval(), feat4[iu], "pred", "keypoint")
+    run(R.DefaultSegmentorV2(num_classes=20, backbone_out_channels=64, backbone=dict(bb, in_channels=6)).eval(),
+        feat6, "seg_logits", "segmentor")
+    with open(os.path.join(HERE, "param_shapes_heads.json"), "w") as fh:
+        json.dump(shapes_all, fh, indent=0)
+    np.savez_compressed(os.path.join(HERE, "heads.npz"), **out)
+
+
+from make_golden_names import TRAIN_GRADS, make_target  # noqa: E402  (tests/make_golden_names.py)
+
+
+def gold_train(R):
+    from oracle import gridsample as G
+    m = R.OffsetKeypointPTv3(backbone_conf=dict(type="PT-v3m1", enable_flash=False, upcast_attention=False,
+                                                upcast_softmax=False, drop_path=0.0, **BASE_CFG))
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    m.load_state_dict(W, strict=False)
+    m.train()
+    coord, feat = synth.pig_scan(3000, scale=0.5, seed=61)
+    gs = G.grid_sample(coord, 0.02)
+    iu = gs["idx_unique"]
+    c, f, g = coord[iu], feat[iu], gs["grid_coord"][iu]
+    target = make_target(len(iu), 62)
+    torch.manual_seed(400)
+    perms = np.stack([torch.randperm(4).numpy() for _ in range(5)])
+    torch.manual_seed(400)
+    r = m(dict(coord=torch.from_numpy(c), grid_coord=torch.from_numpy(g), feat=torch.from_numpy(f),
+               offset=torch.tensor([len(iu)]), grid_size=0.02, target=torch.from_numpy(target)))
+    r["loss"].backward()
+    out = dict(coord=c, feat=f, grid_coord=g, target=target, perms=perms, loss=np.float64(r["loss"].item()))
+    names, norms = [], []
+    for k, p in m.named_parameters():
+        if p.grad is not None:
+            names.append(k)
+            norms.append(p.grad.norm().item())
+    out["grad_names"] = np.array(names)
+    out["grad_norms"] = np.array(norms, dtype=np.float64)
+    for i, k in enumerate(TRAIN_GRADS):
+        out[f"grad_{i}"] = dict(m.named_parameters())[k].grad.numpy()
+    out["running_mean_stem"] = m.backbone.embedding.stem.norm.running_mean.numpy()
+    print("train: N0", len(iu), "loss", r["loss"].item(), "params with grad", len(names))
+    np.savez_compressed(os.path.join(HERE, "train.npz"), **out)
+
+
 if __name__ == "__main__":
     R = ref_loader.load()
     gold_serialization(R)
@@ -170,6 +249,8 @@ if __name__ == "__main__":
     gold_padding(R)
     gold_attention(R)
     gold_forward(R)
+    gold_heads(R)
+    gold_train(R)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

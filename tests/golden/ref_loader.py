@@ -171,6 +171,18 @@ def load():
     ptv3 = importlib.import_module("pointcept.models.point_transformer_v3.point_transformer_v3m1_base")
     okp = importlib.import_module("pointcept.models.offset_keypoint_ptv3")
     kp = importlib.import_module("pointcept.models.keypoint_ptv3")
+    # default.py (DefaultSegmentorV2) imports torch_cluster and peft at module level without using them on this path
+    for absent, names in (("torch_cluster", ()), ("peft", ("LoraConfig", "get_peft_model"))):
+        if absent not in sys.modules:
+            stub = types.ModuleType(absent)
+            for nm in names:
+                setattr(stub, nm, None)
+            sys.modules[absent] = stub
+    try:
+        seg = importlib.import_module("pointcept.models.default")
+    except Exception as e:                                 # noqa: BLE001 -- report, the other fixtures do not need it
+        print("pointcept.models.default not importable:", repr(e))
+        seg = None
     structure = importlib.import_module("pointcept.models.utils.structure")
     ser = importlib.import_module("pointcept.models.utils.serialization")
     builder = importlib.import_module("pointcept.models.builder")
@@ -182,5 +194,6 @@ def load():
     spec.loader.exec_module(tr)
     _loaded.update(ptv3=ptv3, PointTransformerV3=ptv3.PointTransformerV3, SerializedAttention=ptv3.SerializedAttention,
                    OffsetKeypointPTv3=okp.OffsetKeypointPTv3, KeypointPTv3=kp.KeypointPTv3,
+                   DefaultSegmentorV2=getattr(seg, "DefaultSegmentorV2", None),
                    Point=structure.Point, encode=ser.encode, GridSample=tr.GridSample, builder=builder)
     return types.SimpleNamespace(**_loaded)

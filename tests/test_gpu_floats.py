@@ -387,3 +387,68 @@ def test_affine_act(dtype, act):
     o32, o16 = ops.affine_act(x.cuda(), s.cuda(), t.cuda(), act, want_f32=True, want_bf16=True)
     assert torch.allclose(o32.cpu(), ref, rtol=1e-5, atol=1e-6)
     assert torch.equal(o16.cpu(), o32.cpu().bfloat16())
+
+
+def _head_weights(tag):
+    from conftest import GOLDEN
+    from ptv3_b200 import synth
+    with open(os.path.join(GOLDEN, "param_shapes_heads.json")) as f:
+        shapes = json.load(f)[tag]
+    return {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+
+
+def _load(m, W):
+    missing, unexpected = m.load_state_dict(W, strict=False)
+    assert not unexpected and all(k.endswith("num_batches_tracked") for k in missing), (missing, unexpected)
+    return m.eval().cuda()
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_keypoint_head_golden(golden, dtype, tol):
+    """A9: KeypointPTv3 (per-scene mean pool -> regression MLP) against the unmodified reference's frozen output, and
+    a 3-scene batch against per-scene oracle runs (ragged scenes through scatter_mean)."""
+    from ptv3_b200 import model as M
+    g = golden("heads")
+    n = len(g["coord"])
+    W = _head_weights("keypoint")
+    m = _load(M.KeypointPTv3(backbone_conf=dict(P.BASE_CFG, compute_dtype=dtype)), W)
+    torch.manual_seed(300)
+    out = m(dict(coord=torch.from_numpy(g["coord"]).cuda(), grid_coord=torch.from_numpy(g["grid_coord"]).cuda(),
+                 feat=torch.from_numpy(g["feat4"]).cuda(), offset=torch.tensor([n]).cuda(), grid_size=0.02))["pred"]
+    ref = torch.from_numpy(g["out_keypoint"])
+    assert out.shape == (1, 6, 3) and rel_l2(out, ref) < tol, rel_l2(out, ref)
+    if dtype == torch.float32:
+        for mod in m.backbone.modules():
+            if hasattr(mod, "shuffle_orders"):
+                mod.shuffle_orders = False
+        scenes = [_scene(51, 3000, 0.45), _scene(52, 900, 0.25), _scene(53, 2000, 0.4)]
+        refs = []
+        for c, f, gc in scenes:
+            pt = P.backbone_forward(W, c, gc, f, [len(c)], perms=None)
+            refs.append(P.keypoint_head(W, pt.feat, pt.batch))
+        cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
+        offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
+        out = m(dict(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset))["pred"]
+        assert out.shape == (3, 6, 3) and rel_l2(out, torch.cat(refs)) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_segmentor_head_golden(golden, dtype, tol):
+    """A9 / BASELINE configs[2] shape: DefaultSegmentorV2 over PT-v3m1 with C_in = 6 and 20 classes against the
+    unmodified reference's frozen logits; predicted classes agree wherever the reference's margin exceeds the
+    tolerance."""
+    from ptv3_b200 import model as M
+    g = golden("heads")
+    n = len(g["coord"])
+    W = _head_weights("segmentor")
+    m = _load(M.DefaultSegmentorV2(num_classes=20, backbone_out_channels=64,
+                                   backbone=dict(P.BASE_CFG, in_channels=6, compute_dtype=dtype)), W)
+    torch.manual_seed(300)
+    out = m(dict(coord=torch.from_numpy(g["coord"]).cuda(), grid_coord=torch.from_numpy(g["grid_coord"]).cuda(),
+                 feat=torch.from_numpy(g["feat6"]).cuda(), offset=torch.tensor([n]).cuda(), grid_size=0.02))
+    logits = out["seg_logits"].float().cpu()
+    ref = torch.from_numpy(g["out_segmentor"])
+    assert logits.shape == (n, 20) and rel_l2(logits, ref) < tol, rel_l2(logits, ref)
+    top2 = ref.topk(2, dim=1).values
+    clear = (top2[:, 0] - top2[:, 1]) > 4 * tol * ref.abs().max()
+    assert clear.any() and torch.equal(logits.argmax(1)[clear], ref.argmax(1)[clear])

@@ -1,0 +1,230 @@
+"""GPU parity of the backward path: every custom autograd op against torch.autograd through
+the CPU oracle on the same seeded inputs, then the whole OffsetKeypointPTv3 training step against the UNMODIFIED
+reference's loss.backward() frozen in tests/golden/train.npz.
+Tolerances: fp32 operands rel-L2 <= 1e-4 per op (<= 1e-3 for gradients that went through the whole network),
+bf16 operands <= 1e-2 per op."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gridsample as G
+from oracle import ops as O
+from oracle import ptv3 as P
+
+pytestmark = pytest.mark.gpu
+
+TOL = {torch.float32: 1e-4, torch.bfloat16: 1e-2}
+
+
+def rel_l2(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def _sites(seed, n_scenes=2, r=2500, scale=0.4):
+    from ptv3_b200 import synth
+    idx = []
+    for b in range(n_scenes):
+        coord, _ = synth.pig_scan(r, scale=scale, seed=seed + b)
+        gs = G.grid_sample(coord, 0.02)
+        g = gs["grid_coord"][gs["idx_unique"]]
+        idx.append(np.concatenate([np.full((len(g), 1), b), g], 1))
+    return torch.from_numpy(np.concatenate(idx)).int()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("k,cin,cout", [(3, 32, 32), (3, 64, 64), (5, 4, 32), (3, 48, 80)])
+def test_subm_conv_grads(dtype, k, cin, cout):
+    from ptv3_b200 import autograd as A, ops
+    idx = _sites(3)
+    n = idx.shape[0]
+    g = torch.Generator().manual_seed(k * 1000 + cin)
+    x = torch.randn(n, cin, generator=g)
+    w = torch.randn(cout, k, k, k, cin, generator=g) / (k ** 3 * cin) ** 0.5
+    b = torch.randn(cout, generator=g) * 0.1
+    dy = torch.randn(n, cout, generator=g)
+    if dtype == torch.bfloat16:      # the oracle sees the same rounded operands
+        x, w, dy = x.bfloat16().float(), w.bfloat16().float(), dy.bfloat16().float()
+    xr, wr, br = x.clone().requires_grad_(), w.clone().requires_grad_(), b.clone().requires_grad_()
+    nbr_ref = O.subm_neighbor_table(idx, k)
+    O.subm_conv(xr, nbr_ref, wr, br).backward(dy)
+    xg, wg, bg = x.cuda().requires_grad_(), w.cuda().requires_grad_(), b.cuda().requires_grad_()
+    nbr = ops.subm_build_map(idx.cuda(), k)
+    y = A.subm_conv(xg, wg, bg, nbr, dtype)
+    y.backward(dy.cuda().to(y.dtype))
+    tol = TOL[dtype]
+    assert rel_l2(xg.grad, xr.grad) < tol, rel_l2(xg.grad, xr.grad)
+    assert rel_l2(wg.grad, wr.grad) < tol, rel_l2(wg.grad, wr.grad)
+    assert rel_l2(bg.grad, br.grad) < tol, rel_l2(bg.grad, br.grad)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("sizes,K", [([700, 2300, 1024, 1], 1024), ([300, 130], 128), ([5000], 1024)])
+def test_attention_grads(dtype, sizes, K):
+    """Ragged scenes: a short scene (one short window), a scene whose last window re-uses the previous window's tail
+    (keys shared by two windows -> accumulated dK / dV), an exact multiple of K, and a one-row scene."""
+    from ptv3_b200 import autograd as A, ops
+    n, H, d = sum(sizes), 4, 16
+    g = torch.Generator().manual_seed(n)
+    qkv = torch.randn(n, 3 * H * d, generator=g)
+    dout = torch.randn(n, H * d, generator=g)
+    offset = torch.tensor(np.cumsum(sizes))
+    order = torch.cat([torch.randperm(s, generator=g) + (int(offset[i]) - s) for i, s in enumerate(sizes)])
+    inverse = torch.empty_like(order)
+    inverse[order] = torch.arange(n)
+    if dtype == torch.bfloat16:
+        qkv, dout = qkv.bfloat16().float(), dout.bfloat16().float()
+    qr = qkv.clone().requires_grad_()
+    ref = O.window_attention(qr, order, inverse, offset.numpy(), H, K)
+    ref.backward(dout)
+    windows, nwin = ops.build_windows(offset.cuda(), K, n)
+    qg = qkv.cuda().to(dtype).requires_grad_()
+    out = A.attn_window(qg, order.cuda(), windows, nwin, H, K)
+    out.backward(dout.cuda().to(dtype))
+    assert rel_l2(out, ref) < TOL[dtype]
+    grad, gref = qg.grad.float().cpu().view(n, 3, -1), qr.grad.view(n, 3, -1)
+    for part, name in enumerate("qkv"):
+        err = rel_l2(grad[:, part], gref[:, part])
+        assert err < TOL[dtype], (name, err)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("reduce", ["max", "mean", "sum", "min"])
+def test_segment_csr_grads(dtype, reduce):
+    from ptv3_b200 import autograd as A
+    g = torch.Generator().manual_seed(11)
+    n, c = 4000, 48
+    lens = torch.randint(0, 9, (1200,), generator=g)
+    lens = lens[torch.cumsum(lens, 0) <= n]
+    ptr = torch.cat([torch.zeros(1, dtype=torch.long), torch.cumsum(lens, 0)])
+    m = ptr.numel() - 1
+    perm = torch.randperm(n, generator=g)
+    src = torch.randn(n, c, generator=g)
+    dout = torch.randn(m, c, generator=g)
+    if dtype == torch.bfloat16:
+        src = src.bfloat16().float()
+        if reduce in ("max", "min"):     # make ties certain in some segments: the FIRST row in CSR order wins
+            src[perm[1]] = src[perm[0]]
+    sr = src.clone().requires_grad_()
+    gathered = sr[perm][: int(ptr[-1])]
+    if reduce in ("max", "min"):
+        # torch_scatter's arg semantics restated: first row of the segment (CSR order) that attains the extremum
+        ref_out = O.segment_csr(gathered.detach(), ptr, reduce)
+        seg = torch.repeat_interleave(torch.arange(m), lens)
+        hit = gathered.detach() == ref_out[seg]
+        pos = torch.arange(gathered.shape[0])[:, None].expand_as(hit)
+        big = torch.full((m, c), gathered.shape[0], dtype=torch.long)
+        firstpos = big.scatter_reduce(0, seg[:, None].expand_as(hit), torch.where(hit, pos, big[seg]), "amin")
+        first = pos == firstpos[seg]
+        gref_g = torch.where(first, dout[seg], torch.zeros(()))
+        gref = torch.zeros(n, c)
+        gref[perm[: int(ptr[-1])]] = gref_g
+    else:
+        O.segment_csr(gathered, ptr, reduce).backward(dout)
+        gref = sr.grad
+    sg = src.cuda().to(dtype).requires_grad_()
+    out = A.segment_csr(sg, ptr.cuda(), reduce, perm.cuda())
+    out.backward(dout.cuda().to(dtype))
+    assert rel_l2(sg.grad, gref) < (1e-6 if dtype == torch.float32 else 1e-2)
+
+
+def test_gather_rows_grad():
+    from ptv3_b200 import autograd as A, ops
+    g = torch.Generator().manual_seed(2)
+    m, n, c = 700, 3000, 64
+    inverse = torch.randint(0, m, (n,), generator=g)
+    inverse[:m] = torch.arange(m)                        # every cluster has a member, like pooling
+    indices = torch.sort(inverse, stable=True)[1]
+    idx_ptr = torch.cat([torch.zeros(1, dtype=torch.long), torch.cumsum(torch.bincount(inverse, minlength=m), 0)])
+    x = torch.randn(m, c, generator=g)
+    dy = torch.randn(n, c, generator=g)
+    xr = x.clone().requires_grad_()
+    xr[inverse].backward(dy)
+    xg = x.cuda().requires_grad_()
+    A.gather_rows(xg, inverse.cuda(), indices.cuda(), idx_ptr.cuda()).backward(dy.cuda())
+    assert rel_l2(xg.grad, xr.grad) < 1e-6
+
+
+def _weights():
+    from conftest import GOLDEN
+    from ptv3_b200 import synth
+    with open(os.path.join(GOLDEN, "param_shapes.json")) as f:
+        shapes = json.load(f)
+    return {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+
+
+def _train_model(dtype):
+    from ptv3_b200 import model as M
+    m = M.OffsetKeypointPTv3(backbone_conf=dict(P.BASE_CFG, drop_path=0.0, compute_dtype=dtype))
+    missing, unexpected = m.load_state_dict(_weights(), strict=False)
+    assert not unexpected and all(k.endswith("num_batches_tracked") for k in missing)
+    return m.cuda().train()
+
+
+# bf16: the per-op gradient tests above hold 1e-2; through the whole network the 0.6 % forward noise of bf16 operands
+# flips a fraction f of the non-smooth selections (sign() of the L1 loss, ReLU masks, segment-max winners), which moves
+# gradient mass by ~sqrt(2 f) -- measured 1.4 % at the head, 9 % at the last block, 18-22 % in the encoder with these
+# random weights (tools/grad_probe.py: keeping any one module kind in fp32 does not remove it, all-fp32 gives 1e-4).
+# The whole-step bf16 check is therefore direction (rel-L2 < 0.3 <=> cosine > 0.95) + loss, not 1e-2.
+@pytest.mark.parametrize("dtype,tol_loss,tol_grad", [(torch.float32, 1e-5, 1e-3), (torch.bfloat16, 1e-2, 0.3)])
+def test_training_step_golden(golden, dtype, tol_loss, tol_grad):
+    """Whole training step (train() mode: BatchNorm batch statistics, 5 randperm draws, loss of
+    offset_keypoint_ptv3.py:50-86, backward through every kernel) against the unmodified reference."""
+    from make_golden_names import TRAIN_GRADS
+    g = golden("train")
+    m = _train_model(dtype)
+    n = len(g["coord"])
+    torch.manual_seed(400)
+    out = m(dict(coord=torch.from_numpy(g["coord"]).cuda(), grid_coord=torch.from_numpy(g["grid_coord"]).cuda(),
+                 feat=torch.from_numpy(g["feat"]).cuda(), offset=torch.tensor([n]).cuda(), grid_size=0.02,
+                 target=torch.from_numpy(g["target"]).cuda()))
+    out["loss"].backward()
+    ref_loss = float(g["loss"])
+    assert abs(out["loss"].item() - ref_loss) < tol_loss * abs(ref_loss), (out["loss"].item(), ref_loss)
+    params = dict(m.named_parameters())
+    errs = {k: rel_l2(params[k].grad, torch.from_numpy(g[f"grad_{i}"])) for i, k in enumerate(TRAIN_GRADS)}
+    print({k: f"{v:.2e}" for k, v in errs.items()})
+    worst = max(errs.values())
+    assert worst < tol_grad, errs
+    names = [str(s) for s in g["grad_names"]]
+    assert all(params[k].grad is not None for k in names)
+    got = torch.tensor([params[k].grad.norm().item() for k in names], dtype=torch.float64)
+    ref = torch.from_numpy(g["grad_norms"])
+    # parameters whose gradient is analytically zero (a bias in front of a batch-statistics BatchNorm) hold rounding
+    # noise on both sides: measure the error relative to max(own norm, 1e-5 x the largest norm)
+    rel = (got - ref).abs() / ref.clamp_min(1e-5 * ref.max().item())
+    print(f"{dtype}: loss {out['loss'].item():.6f} vs {ref_loss:.6f}; worst full-tensor grad rel-L2 {worst:.2e}; "
+          f"grad-norm rel err max {rel.max().item():.2e} median {rel.median().item():.2e}")
+    assert rel.max().item() < (1e-2 if dtype == torch.float32 else 0.5)
+    # BatchNorm running statistics were updated like nn.BatchNorm1d(momentum=0.01) does
+    assert rel_l2(m.backbone.embedding.stem.norm.running_mean, torch.from_numpy(g["running_mean_stem"])) < 1e-3
+
+
+def test_training_loss_decreases():
+    """Five AdamW steps on a fixed two-scene batch (bf16 operands, drop_path on): the loss goes down and stays
+    finite -- optimizer + autograd plumbing end to end."""
+    from make_golden_names import make_target
+    from ptv3_b200 import model as M, synth
+    torch.manual_seed(0)
+    m = M.OffsetKeypointPTv3(backbone_conf=dict(P.BASE_CFG, drop_path=0.1)).cuda().train()
+    opt = torch.optim.AdamW(m.parameters(), lr=2e-3)
+    scenes = []
+    for s in (71, 72):
+        coord, feat = synth.pig_scan(3000, scale=0.5, seed=s)
+        gs = G.grid_sample(coord, 0.02)
+        iu = gs["idx_unique"]
+        scenes.append((coord[iu], feat[iu], gs["grid_coord"][iu]))
+    cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
+    offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
+    target = torch.from_numpy(make_target(int(offset[-1]), 5)).cuda()
+    losses = []
+    for _ in range(6):
+        opt.zero_grad(set_to_none=True)
+        out = m(dict(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset, target=target))
+        out["loss"].backward()
+        opt.step()
+        losses.append(out["loss"].item())
+    assert all(np.isfinite(losses)) and losses[-1] < losses[0], losses

@@ -156,3 +156,50 @@ def test_forward_vs_reference(golden):
         pred = P.offset_head(W, pt.feat)
         ref = torch.from_numpy(g[f"pred_{i}"])
         assert ((pred - ref).norm() / ref.norm()).item() < 1e-5
+
+
+def _head_weights(tag):
+    import json, os
+    from conftest import GOLDEN
+    with open(os.path.join(GOLDEN, "param_shapes_heads.json")) as f:
+        shapes = json.load(f)[tag]
+    return {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+
+
+def test_keypoint_and_segmentor_heads_vs_reference(golden):
+    """KeypointPTv3 (scatter_mean + MLP) and DefaultSegmentorV2 (C_in = 6, 20 classes), frozen from
+    the unmodified reference classes (tests/golden/make_golden.py::gold_heads)."""
+    g = golden("heads")
+    n = len(g["coord"])
+    W = _head_weights("keypoint")
+    pt = P.backbone_forward(W, g["coord"], g["grid_coord"], g["feat4"], [n], perms=list(g["perms_keypoint"]))
+    pred = P.keypoint_head(W, pt.feat, pt.batch)
+    ref = torch.from_numpy(g["out_keypoint"])
+    assert pred.shape == ref.shape == (1, 6, 3)
+    assert ((pred - ref).norm() / ref.norm()).item() < 1e-5
+    W = _head_weights("segmentor")
+    pt = P.backbone_forward(W, g["coord"], g["grid_coord"], g["feat6"], [n], cfg=dict(P.BASE_CFG, in_channels=6),
+                            perms=list(g["perms_segmentor"]))
+    logits = P.seg_head(W, pt.feat)
+    ref = torch.from_numpy(g["out_segmentor"])
+    assert logits.shape == ref.shape == (n, 20)
+    assert ((logits - ref).norm() / ref.norm()).item() < 1e-5
+
+
+def test_training_grads_vs_reference(golden):
+    """oracle autograd (train() mode: BatchNorm batch statistics, drop_path 0) against the unmodified
+    reference's loss.backward() frozen in tests/golden/train.npz."""
+    g = golden("train")
+    W = _weights()
+    loss, grads = P.offset_keypoint_grads(W, g["coord"], g["grid_coord"], g["feat"], [len(g["coord"])], g["target"],
+                                          perms=list(g["perms"]))
+    assert abs(loss.item() - float(g["loss"])) < 1e-5 * abs(float(g["loss"]))
+    names = [str(n) for n in g["grad_names"]]
+    assert set(names) == set(grads)
+    from make_golden_names import TRAIN_GRADS
+    for i, k in enumerate(TRAIN_GRADS):
+        ref = torch.from_numpy(g[f"grad_{i}"])
+        assert ((grads[k] - ref).norm() / ref.norm()).item() < 1e-4, k
+    got = torch.tensor([grads[n].norm().item() for n in names], dtype=torch.float64)
+    ref = torch.from_numpy(g["grad_norms"])
+    assert ((got - ref).abs() / ref.clamp_min(1e-12)).max().item() < 1e-3
