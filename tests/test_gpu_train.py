@@ -195,7 +195,8 @@ def test_training_step_golden(golden, dtype, tol_loss, tol_grad):
     ref = torch.from_numpy(g["grad_norms"])
     # parameters whose gradient is analytically zero (a bias in front of a batch-statistics BatchNorm) hold rounding
     # noise on both sides: measure the error relative to max(own norm, 1e-5 x the largest norm)
-    rel = (got - ref).abs() / ref.clamp_min(1e-5 * ref.max().item())
+    floor = (1e-5 if dtype == torch.float32 else 1e-3) * ref.max().item()
+    rel = (got - ref).abs() / ref.clamp_min(floor)
     print(f"{dtype}: loss {out['loss'].item():.6f} vs {ref_loss:.6f}; worst full-tensor grad rel-L2 {worst:.2e}; "
           f"grad-norm rel err max {rel.max().item():.2e} median {rel.median().item():.2e}")
     assert rel.max().item() < (1e-2 if dtype == torch.float32 else 0.5)
