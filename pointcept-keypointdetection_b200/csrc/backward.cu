@@ -268,6 +268,12 @@ __global__ void segment_csr_bwd_kernel(const float* __restrict__ dout, const T* 
   }
 }
 
+// csrc/attn_bwd_tc.cu
+int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const __nv_bfloat16* dout,
+                       const int64_t* order, const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max,
+                       int64_t max_len, int h, float scale, float* dqkv, cudaStream_t st);
+int g_attn_bwd_simt = 0;   // debug slot 4: 1 forces the CUDA-core kernels for bf16 too
+
 }  // namespace ptv3
 
 using namespace ptv3;
@@ -310,6 +316,11 @@ int ptv3_attn_window_bwd(const void* qkv, const void* out, const void* dout, int
   if (n < 0 || h < 1 || h > 65535 || d != kBD || n_windows_max < 0 || max_len < 1) return PTV3_EINVAL;
   if (n == 0 || n_windows_max == 0) return PTV3_OK;
   if (!qkv || !out || !dout || !windows || !n_windows || !dqkv) return PTV3_EINVAL;
+  if (dtype == PTV3_BF16 && !g_attn_bwd_simt) {
+    int rc = attn_window_bwd_tc((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, order,
+                                windows, n_windows, n_windows_max, max_len, h, scale, dqkv, as_stream(stream));
+    if (rc != PTV3_EUNSUPPORTED) return rc;
+  }
   Workspace ws(workspace, workspace_bytes);
   float* lse = ws.take<float>((size_t)n * h);
   float* dvec = ws.take<float>((size_t)n * h);

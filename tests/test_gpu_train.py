@@ -61,9 +61,9 @@ def test_subm_conv_grads(dtype, k, cin, cout):
     assert rel_l2(bg.grad, br.grad) < tol, rel_l2(bg.grad, br.grad)
 
 
-@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("sizes,K", [([700, 2300, 1024, 1], 1024), ([300, 130], 128), ([5000], 1024)])
-def test_attention_grads(dtype, sizes, K):
+@pytest.mark.parametrize("dtype,simt", [(torch.float32, True), (torch.bfloat16, False), (torch.bfloat16, True)])
+@pytest.mark.parametrize("sizes,K", [([700, 2300, 1024, 1], 1024), ([300, 130], 128), ([5000], 1024), ([1500, 40], 1000)])
+def test_attention_grads(dtype, simt, sizes, K):
     """Ragged scenes: a short scene (one short window), a scene whose last window re-uses the previous window's tail
     (keys shared by two windows -> accumulated dK / dV), an exact multiple of K, and a one-row scene."""
     from ptv3_b200 import autograd as A, ops
@@ -83,7 +83,12 @@ def test_attention_grads(dtype, sizes, K):
     windows, nwin = ops.build_windows(offset.cuda(), K, n)
     qg = qkv.cuda().to(dtype).requires_grad_()
     out = A.attn_window(qg, order.cuda(), windows, nwin, H, K)
-    out.backward(dout.cuda().to(dtype))
+    from ptv3_b200 import _lib
+    _lib.load().ptv3_debug_set(4, int(simt))       # bf16: tensor-core kernel (default) or the CUDA-core one
+    try:
+        out.backward(dout.cuda().to(dtype))
+    finally:
+        _lib.load().ptv3_debug_set(4, 0)
     assert rel_l2(out, ref) < TOL[dtype]
     grad, gref = qg.grad.float().cpu().view(n, 3, -1), qr.grad.view(n, 3, -1)
     for part, name in enumerate("qkv"):
