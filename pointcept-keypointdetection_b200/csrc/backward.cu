@@ -273,6 +273,10 @@ int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const
                        const int64_t* order, const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max,
                        int64_t max_len, int h, float scale, float* dqkv, cudaStream_t st);
 int g_attn_bwd_simt = 0;   // debug slot 4: 1 forces the CUDA-core kernels for bf16 too
+// csrc/wgrad_tc.cu
+int subm_wgrad_fast(const void* in, const void* dout, const int32_t* nbr, int64_t n, int c_in, int c_out, int k3, int dtype,
+                    float* dweight, cudaStream_t st);
+int g_wgrad_simt = 0;      // debug slot 5: 1 forces the generic CUDA-core kernel
 
 }  // namespace ptv3
 
@@ -285,6 +289,10 @@ int ptv3_subm_wgrad(const void* in, const void* dout, const int32_t* nbr, int64_
   if (n < 0 || c_in < 1 || c_out < 1 || k3 < 1 || k3 > 65535) return PTV3_EINVAL;
   if (n == 0) return PTV3_OK;
   if (!in || !dout || !nbr || !dweight) return PTV3_EINVAL;
+  if (!g_wgrad_simt) {
+    int rc = subm_wgrad_fast(in, dout, nbr, n, c_in, c_out, k3, dtype, dweight, as_stream(stream));
+    if (rc != PTV3_EUNSUPPORTED) return rc;
+  }
   const int64_t tiles = cdiv(c_out, kWgTO) * cdiv(c_in, kWgTC);
   if (tiles > 65535) return PTV3_EINVAL;
   // enough row chunks to fill the machine a few times, at least 1024 rows per CTA to amortise the atomics

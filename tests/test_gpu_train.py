@@ -35,9 +35,13 @@ def _sites(seed, n_scenes=2, r=2500, scale=0.4):
     return torch.from_numpy(np.concatenate(idx)).int()
 
 
-@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("k,cin,cout", [(3, 32, 32), (3, 64, 64), (5, 4, 32), (3, 48, 80)])
-def test_subm_conv_grads(dtype, k, cin, cout):
+@pytest.mark.parametrize("dtype,simt", [(torch.float32, False), (torch.float32, True), (torch.bfloat16, False),
+                                        (torch.bfloat16, True)])
+@pytest.mark.parametrize("k,cin,cout", [(3, 32, 32), (3, 64, 64), (5, 4, 32), (5, 6, 32), (3, 48, 80), (3, 128, 64),
+                                        (3, 64, 128), (3, 32, 64)])
+def test_subm_conv_grads(dtype, simt, k, cin, cout):
+    """simt = the generic CUDA-core weight-gradient kernel; otherwise the tensor-core (bf16, channels % 32 == 0) or
+    the stem (fp32, C_out 32, C_in <= 8) fast path when the shape has one."""
     from ptv3_b200 import autograd as A, ops
     idx = _sites(3)
     n = idx.shape[0]
@@ -54,7 +58,12 @@ def test_subm_conv_grads(dtype, k, cin, cout):
     xg, wg, bg = x.cuda().requires_grad_(), w.cuda().requires_grad_(), b.cuda().requires_grad_()
     nbr = ops.subm_build_map(idx.cuda(), k)
     y = A.subm_conv(xg, wg, bg, nbr, dtype)
-    y.backward(dy.cuda().to(y.dtype))
+    from ptv3_b200 import _lib
+    _lib.load().ptv3_debug_set(5, int(simt))
+    try:
+        y.backward(dy.cuda().to(y.dtype))
+    finally:
+        _lib.load().ptv3_debug_set(5, 0)
     tol = TOL[dtype]
     assert rel_l2(xg.grad, xr.grad) < tol, rel_l2(xg.grad, xr.grad)
     assert rel_l2(wg.grad, wr.grad) < tol, rel_l2(wg.grad, wr.grad)
