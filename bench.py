@@ -373,6 +373,108 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def run_train(args):
+    """SURVEY 8f rank 1 / BASELINE configs[4] shape of work: one training step = forward in train() mode (BatchNorm
+    batch statistics, DropPath), the offset-keypoint loss, backward through every kernel, gradient all-reduce over
+    NCCL when N > 1 (ptv3_b200/ddp.py, overlapped with backward), fused AdamW.  Same scenes per GPU as the forward
+    bench; not the headline line (run with --mode train)."""
+    from ptv3_b200 import _lib
+    from ptv3_b200.ddp import GradSync
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    from make_golden_names import make_target
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    model, _ = build_model(dtype, device)
+    model.train()
+    raw = make_raw_scenes(args.scenes, args.points, args.scale, seed0=1000 * rank)
+    host, counts = voxelize_on_device(raw, device)
+    n_vox = int(sum(counts))
+    host["target"] = torch.from_numpy(make_target(n_vox, 7 + rank))
+    pinned = {k: v.pin_memory() for k, v in host.items()}
+    resident = {k: v.to(device) for k, v in host.items()}
+    h2d_bytes = int(sum(v.numel() * v.element_size() for v in pinned.values()))
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.05, fused=True)
+    sync = GradSync(model.parameters()) if world > 1 else None
+
+    def step(batch):
+        if sync is not None:
+            sync.zero_grad()
+        else:
+            opt.zero_grad(set_to_none=True)
+        out = model(dict(batch))
+        out["loss"].backward()
+        if sync is not None:
+            sync.finish()
+        opt.step()
+        return out["loss"]
+
+    def step_e2e():
+        d = {k: v.to(device, non_blocking=True) for k, v in pinned.items()}
+        return float(step(d).item())                                  # D2H read of the step's loss
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        a.record()
+        for _ in range(steps):
+            out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        barrier()
+        t = torch.tensor([a.elapsed_time(b), wall], device=device, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1]), out
+
+    torch.manual_seed(rank)
+    for _ in range(max(args.warmup, 3)):
+        step(resident)
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = _lib.launch_count()
+    ms, _, loss = timed(lambda: step(resident), args.steps)
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop()
+    step_e2e()
+    _, e2e_wall, loss_e2e = timed(step_e2e, args.steps)
+    total_vox = torch.tensor([n_vox], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(total_vox)
+    total_vox = float(total_vox.item())
+    n_params = sum(p.numel() for p in model.parameters())
+    if rank == 0:
+        print(json.dumps(dict(
+            metric="ptv3_train_step_voxels_per_sec", value=round(total_vox * args.steps / (ms * 1e-3), 1), unit=UNIT,
+            n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=round(ms / args.steps, 3),
+            higher_is_better=True, scaling="weak", vs_baseline=None, dtype=args.dtype, data="synthetic", mode="train",
+            config=dict(workload=f"PTv3-v1m1 + offset-keypoint head TRAINING step (fwd + loss + bwd + AdamW), "
+                                 f"{args.scenes} scenes x {args.points} raw pts (scale {args.scale}, grid {GRID} m) "
+                                 f"per GPU", voxels_per_gpu=n_vox, params=n_params,
+                        parallelism=f"replicas x{world}, scenes sharded per rank, bucketed gradient all-reduce "
+                                    f"({'NCCL AVG, overlapped with backward' if world > 1 else 'none at N=1'})"),
+            e2e=dict(value=round(total_vox * args.steps / (e2e_wall * 1e-3), 1), unit=UNIT, h2d_bytes_per_step=h2d_bytes,
+                     d2h_bytes_per_step=4, ms_per_step=round(e2e_wall / args.steps, 3), result="loss (fp32 scalar)"),
+            gpu_launches=int(launches), clocks=clocks, loss=round(float(loss.item()), 5),
+            peak_mem_gib=round(torch.cuda.max_memory_allocated() / 2 ** 30, 2))))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -384,9 +486,13 @@ def main():
     ap.add_argument("--points", type=int, default=100000)
     ap.add_argument("--scale", type=float, default=4.1)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="forward", choices=["forward", "train"],
+                    help="forward = the headline metric (default); train = training step (SURVEY 8f rank 1)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.mode == "train":
+        run_train(args)
     else:
         run_ours(args)
 

@@ -109,3 +109,60 @@ def test_scene_sharding_world_size_2_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert sorted(res) == [(0, True, True), (1, True, True)]
+
+
+def _grad_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from ptv3_b200.ddp import GradSync
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)                       # replicas start from identical parameters
+        net = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.GELU(), torch.nn.Linear(16, 16), torch.nn.GELU(),
+                                  torch.nn.Linear(16, 4))
+        unused = torch.nn.Parameter(torch.ones(3))             # a parameter that gets no gradient
+        sync = GradSync(list(net.parameters()) + [unused], bucket_bytes=300)      # three small buckets
+        assert len(sync.buckets) >= 3
+        g = torch.Generator().manual_seed(1)
+        data = torch.randn(world, 5, 8, generator=g)
+        out = []
+        for step in range(2):                      # second step checks zero_grad() re-attaches the bucket views
+            sync.zero_grad()
+            net(data[rank] * (step + 1)).square().mean().backward()
+            sync.finish()
+            out.append([p.grad.clone() for p in net.parameters()])
+        q.put((rank, out, unused.grad.clone()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_grad_sync_world_size_2_gloo():
+    """Training config: replicas + one bucketed gradient all-reduce per step; the averaged gradients must
+    equal the mean of the per-rank gradients computed in one process."""
+    import torch.multiprocessing as mp
+    world, port = 2, 29500 + (os.getpid() % 2000) + 7
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_grad_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.GELU(), torch.nn.Linear(16, 16), torch.nn.GELU(),
+                              torch.nn.Linear(16, 4))
+    g = torch.Generator().manual_seed(1)
+    data = torch.randn(world, 5, 8, generator=g)
+    for step in range(2):
+        want = None
+        for r in range(world):
+            net.zero_grad()
+            net(data[r] * (step + 1)).square().mean().backward()
+            gr = [p.grad.clone() / world for p in net.parameters()]
+            want = gr if want is None else [a + b for a, b in zip(want, gr)]
+        for r in range(world):
+            for a, b in zip(res[r][1][step], want):
+                assert torch.allclose(a, b, atol=1e-6)
+    assert all(torch.equal(r[2], torch.zeros(3)) for r in res)
