@@ -273,6 +273,12 @@ int ptv3_segment_csr_bwd(const float* dout, const void* src, const void* out, in
                          const int64_t* gather /* NULL ok */, const int64_t* indptr, int64_t m, int64_t c, int reduce,
                          float* dsrc, void* stream);
 
+/* LayerNorm backward (Block.forward :318-338): x (n,c) in dtype_x, dy (n,c) in dtype_dy, gamma fp32 (c);
+ * dx fp32 (n,c); dgamma / dbeta fp32 (c) are ACCUMULATED (the caller zeroes them).  c in {32,64,128,256,512},
+ * otherwise PTV3_EUNSUPPORTED (the host falls back to torch's LayerNorm for that module). */
+int ptv3_layer_norm_bwd(const void* x, int dtype_x, const void* dy, int dtype_dy, const float* gamma, float eps,
+                        int64_t n, int c, float* dx, float* dgamma, float* dbeta, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,6 +58,7 @@ SIGNATURES = {
     "ptv3_attn_window_bwd": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_f32,
                                      c_vp, c_vp, c_sz, c_vp]),
     "ptv3_segment_csr_bwd": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp]),
+    "ptv3_layer_norm_bwd": (c_int, [c_vp, c_int, c_vp, c_int, c_vp, c_f32, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
     "ptv3_keypoint_aggregate": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_f32, c_vp, c_vp]),
 }
 

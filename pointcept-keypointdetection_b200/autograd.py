@@ -106,6 +106,37 @@ class GatherRowsFn(torch.autograd.Function):
         return ops.segment_csr(dy.contiguous(), idx_ptr, "sum", gather=indices), None, None, None
 
 
+class LayerNormFn(torch.autograd.Function):
+    """y = LayerNorm(x) over the last dim of an (N, C) tensor, written directly in `out_dtype` (the dtype of the GEMM
+    that consumes it): forward = ops.ln_residual, backward = ptv3_layer_norm_bwd (mean / rstd recomputed)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps, out_dtype):
+        xd = x.detach().contiguous()
+        _, y = ops.ln_residual(xd, weight.detach().float(), bias.detach().float(), eps, want_res=False,
+                               out2_dtype=out_dtype)
+        ctx.save_for_backward(xd, weight)
+        ctx.eps = eps
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        if dy.dtype not in (torch.float32, torch.bfloat16):
+            dy = dy.float()
+        dx, dg, db = ops.layer_norm_bwd(x, dy, weight.detach(), ctx.eps)
+        return dx.to(x.dtype), dg.to(weight.dtype), db.to(weight.dtype), None, None
+
+
+def layer_norm(x, ln, out_dtype=torch.float32):
+    """nn.LayerNorm `ln` applied to (N, C) rows; custom kernels for the PTv3 channel counts, torch otherwise."""
+    c = x.shape[-1]
+    if (x.dim() == 2 and c in ops.LN_BWD_CHANNELS and ln.elementwise_affine and ln.bias is not None
+            and x.dtype in (torch.float32, torch.bfloat16)):
+        return LayerNormFn.apply(x, ln.weight, ln.bias, ln.eps, out_dtype)
+    return torch.nn.functional.layer_norm(x.float(), ln.normalized_shape, ln.weight, ln.bias, ln.eps).to(out_dtype)
+
+
 def subm_conv(feat, weight, bias, nbr, cd):
     return SubMConvFn.apply(feat, weight, bias, nbr, cd)
 

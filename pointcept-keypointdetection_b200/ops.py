@@ -487,3 +487,19 @@ def segment_csr_bwd(dout, src, out, indptr, reduce="sum", gather=None):
     _lib.check(lib.ptv3_segment_csr_bwd(_p(dout), _p(src2), _p(out2), _dt(src2), _p(g), _p(indptr), m, c,
                                         REDUCE_IDS[reduce], _p(dsrc), _stream()), "ptv3_segment_csr_bwd")
     return dsrc.view(src.shape)
+
+
+LN_BWD_CHANNELS = (32, 64, 128, 256, 512)
+
+
+def layer_norm_bwd(x, dy, gamma, eps):
+    """(dx fp32 (n,c), dgamma fp32 (c), dbeta fp32 (c)) of y = LayerNorm(x; gamma, beta, eps)."""
+    _need_cuda(x, dy, gamma)
+    lib = _lib.load()
+    x, dy = x.contiguous(), dy.contiguous()
+    n, c = x.shape
+    dx = torch.empty((n, c), dtype=torch.float32, device=x.device)
+    dgb = torch.zeros((2, c), dtype=torch.float32, device=x.device)
+    _lib.check(lib.ptv3_layer_norm_bwd(_p(x), _dt(x), _p(dy), _dt(dy), _p(gamma.contiguous().float()), float(eps), n, c,
+                                       _p(dx), _p(dgb[0]), _p(dgb[1]), _stream()), "ptv3_layer_norm_bwd")
+    return dx, dgb[0], dgb[1]

@@ -27,8 +27,8 @@ def _lin(x, lin, cd):
     return F.linear(x.to(cd), lin.weight.to(cd), lin.bias.to(cd) if lin.bias is not None else None)
 
 
-def _ln(x, ln):
-    return F.layer_norm(x.float(), ln.normalized_shape, ln.weight, ln.bias, ln.eps)
+def _ln(x, ln, out_dtype=torch.float32):
+    return A.layer_norm(x, ln, out_dtype)
 
 
 def _bn(x, bn):
@@ -66,13 +66,13 @@ def block_forward(mod, point):
     y = _ln(_lin(y, mod.cpe[1], cd), mod.cpe[2])
     x = x + y
     att = mod.attn
-    qkv = _lin(_ln(x, mod.norm1[0]), att.qkv, cd)
+    qkv = _lin(_ln(x, mod.norm1[0], cd), att.qkv, cd)
     windows, nwin = att.get_windows(point)
     a = A.attn_window(qkv, point.serialized_order[att.order_index], windows, nwin, att.num_heads, att.patch_size,
                       att.scale, att.algo)
     x = x + _drop_path(_lin(a, att.proj, cd).float(), mod.drop_path_rate, mod.training)
     mlp = mod.mlp[0]
-    f = _lin(mlp.act(_lin(_ln(x, mod.norm2[0]), mlp.fc1, cd)), mlp.fc2, cd)
+    f = _lin(mlp.act(_lin(_ln(x, mod.norm2[0], cd), mlp.fc1, cd)), mlp.fc2, cd)
     x = x + _drop_path(f.float(), mod.drop_path_rate, mod.training)
     point.feat = x
     point["_feat_cd"] = None

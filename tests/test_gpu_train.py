@@ -162,6 +162,41 @@ def test_gather_rows_grad():
     assert rel_l2(xg.grad, xr.grad) < 1e-6
 
 
+@pytest.mark.parametrize("c", [32, 64, 128, 256, 512, 48])
+@pytest.mark.parametrize("xdt,odt", [(torch.float32, torch.float32), (torch.float32, torch.bfloat16),
+                                     (torch.bfloat16, torch.float32)])
+def test_layer_norm_grads(c, xdt, odt):
+    """LayerNorm forward (ln_residual kernel) + ptv3_layer_norm_bwd against torch autograd in fp32 on the CPU; c = 48
+    takes the torch fallback.  n is not a multiple of the rows per warp / CTA."""
+    from ptv3_b200 import autograd as A
+    g = torch.Generator().manual_seed(c)
+    n = 3001
+    x = torch.randn(n, c, generator=g) * 2.0 + 0.5
+    dy = torch.randn(n, c, generator=g)
+    if xdt == torch.bfloat16:
+        x = x.bfloat16().float()
+    if odt == torch.bfloat16:
+        dy = dy.bfloat16().float()
+    ln = torch.nn.LayerNorm(c)
+    with torch.no_grad():
+        ln.weight.copy_(torch.rand(c, generator=g) + 0.5)
+        ln.bias.copy_(torch.randn(c, generator=g) * 0.1)
+    xr = x.clone().requires_grad_()
+    ref = ln(xr)
+    ref.backward(dy)
+    gw, gb = ln.weight.grad.clone(), ln.bias.grad.clone()
+    lng = torch.nn.LayerNorm(c).cuda()
+    lng.load_state_dict(ln.state_dict())
+    xg = x.cuda().to(xdt).requires_grad_()
+    out = A.layer_norm(xg, lng, odt)
+    assert out.dtype == odt
+    out.backward(dy.cuda().to(odt))
+    tol = 1e-5 if odt == torch.float32 else 4e-3
+    assert rel_l2(out, ref) < tol
+    assert rel_l2(xg.grad, xr.grad) < (1e-5 if xdt == torch.float32 else 4e-3)
+    assert rel_l2(lng.weight.grad, gw) < 1e-4 and rel_l2(lng.bias.grad, gb) < 1e-4
+
+
 def _weights():
     from conftest import GOLDEN
     from ptv3_b200 import synth
