@@ -83,7 +83,9 @@ int ptv3_argsort_rows(const int64_t* code, int64_t rows, int64_t n, int key_bits
  * is the input array `rand` (NULL = first point of every voxel).
  *   coord      (r,3) float32
  *   grid_coord (r,3) int64   floor(coord/grid_size) - min   (all points)
- *   key        (r)   uint64  hash of grid_coord (hash_type 0 = fnv, 1 = ravel)
+ *   key        (r)   uint64  hash of grid_coord (hash_type 0 = fnv, 1 = ravel, 2 = ravel with the quotient
+ *                            coord / grid_size rounded in float32: the A0' inference voxelisers,
+ *                            tools/OffsetKeyPointPrediction_Qt.py:276-296, tools/pigseg_shared.py:132-146)
  *   idx_sort   (r)   int64   stable argsort of key
  *   inverse    (r)   int64   voxel id of every point (ids in ascending-key order)
  *   count      (r)   int64   first *n_voxels entries valid: points per voxel

@@ -71,3 +71,17 @@ def grid_sample_test_parts(count, idx_sort):
     point (i % count) of every voxel."""
     seg_start = np.cumsum(np.insert(count, 0, 0)[:-1])
     return [idx_sort[seg_start + i % count] for i in range(int(count.max()))]
+
+
+def voxelize_first(coord, grid_size, keep_order=True):
+    """Inference-time voxelisers (SURVEY 8a row A0'): tools/OffsetKeyPointPrediction_Qt.py:276-296 (keep_order=True:
+    first point per voxel, indices sorted back to scan order) and tools/pigseg_shared.py:132-146 (keep_order=False:
+    lexicographic voxel order).  `coord / grid_size` with a Python float stays float32 in numpy.
+    Returns (indices, grid_coord shifted to start at 0)."""
+    coord = np.asarray(coord, dtype=np.float32)
+    discrete = np.floor(coord / grid_size).astype(np.int32)
+    discrete -= discrete.min(axis=0, keepdims=True)
+    _, idx = np.unique(discrete, axis=0, return_index=True)
+    if keep_order:
+        idx = np.sort(idx)
+    return idx, discrete[idx].astype(np.int64)

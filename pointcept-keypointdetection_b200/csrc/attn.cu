@@ -121,6 +121,7 @@ extern int g_attn_qsplit;
 extern int g_conv_async;
 extern int g_attn_bwd_simt;
 extern int g_wgrad_simt;
+extern int g_attn_bwd_warps;
 int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                    int64_t n_windows_max, int64_t max_len, int64_t n, int h, float scale, __nv_bfloat16* out,
                    cudaStream_t st);
@@ -175,6 +176,7 @@ int ptv3_debug_set(int key, int value) {
   if (key == 3) { g_conv_async = value; return PTV3_OK; }
   if (key == 4) { g_attn_bwd_simt = value; return PTV3_OK; }
   if (key == 5) { g_wgrad_simt = value; return PTV3_OK; }
+  if (key == 6) { g_attn_bwd_warps = value; return PTV3_OK; }
   return PTV3_EINVAL;
 }
 

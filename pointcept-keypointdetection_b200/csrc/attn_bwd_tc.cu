@@ -15,8 +15,6 @@ namespace ptv3 {
 namespace {
 
 constexpr int kD = 16;
-constexpr int kWarps = 8;
-constexpr int kThreads = kWarps * 32;
 
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -54,10 +52,12 @@ __device__ __forceinline__ void zero16(uint32_t dst) {
 }  // namespace
 
 // smem: K, V, Q, dO [kpad][16] bf16 each; lse_s, d_s [kpad] fp32; order_s [kpad] int32
-__global__ void __launch_bounds__(kThreads, 1) attn_bwd_mma_kernel(
+template <int kWarps>
+__global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
     const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
     const int64_t* __restrict__ order, const int64_t* __restrict__ windows, const int64_t* __restrict__ n_windows, int h,
     float scale, float sl2, int kpad_max, float* __restrict__ dqkv) {
+  constexpr int kThreads = kWarps * 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int w = blockIdx.x, head = blockIdx.y;
   if (w >= n_windows[0]) return;
@@ -319,6 +319,8 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_mma_kernel(
   }
 }
 
+int g_attn_bwd_warps = 16;   // debug slot 6
+
 // returns PTV3_EUNSUPPORTED when the window does not fit in shared memory (caller falls back to the CUDA-core path)
 int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const __nv_bfloat16* dout,
                        const int64_t* order, const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max,
@@ -328,13 +330,21 @@ int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const
   if (smem > 220 * 1024) return PTV3_EUNSUPPORTED;
   static size_t configured = 0;
   if (smem > configured) {
-    if (cudaFuncSetAttribute(attn_bwd_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    if (cudaFuncSetAttribute(attn_bwd_mma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+            cudaSuccess ||
+        cudaFuncSetAttribute(attn_bwd_mma_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+            cudaSuccess)
       return PTV3_ELAUNCH;
     configured = smem;
   }
   dim3 grid((unsigned)n_windows_max, (unsigned)h);
-  attn_bwd_mma_kernel<<<grid, kThreads, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
+  // one CTA per SM (140 KB of staged operands): 16 warps hide the ldmatrix / MUFU latency better than 8
+  if (g_attn_bwd_warps == 8)
+    attn_bwd_mma_kernel<8><<<grid, 256, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
                                                     scale * 1.4426950408889634f, kpad, dqkv);
+  else
+    attn_bwd_mma_kernel<16><<<grid, 512, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
+                                                     scale * 1.4426950408889634f, kpad, dqkv);
   return check_launch();
 }
 

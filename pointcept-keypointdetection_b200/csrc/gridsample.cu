@@ -16,13 +16,18 @@ __global__ void gs_init_minmax(long long* mm) {
 }
 
 // numpy>=2: float32 array / 0-d float64 array promotes to float64 (transform.py:850-853)
+// f32div: the inference-time voxelisers (tools/OffsetKeyPointPrediction_Qt.py:284, tools/pigseg_shared.py:133) divide
+// the float32 array by a Python float, which numpy keeps in float32 -- a different floor near cell borders
 __global__ void __launch_bounds__(256) gs_floor_kernel(const float* __restrict__ coord, int64_t r, double grid_size,
-                                                       int64_t* __restrict__ grid, long long* __restrict__ mm) {
+                                                       int f32div, int64_t* __restrict__ grid,
+                                                       long long* __restrict__ mm) {
+  const float gs32 = (float)grid_size;
   long long mn[3] = {INT64_MAX, INT64_MAX, INT64_MAX}, mx[3] = {INT64_MIN, INT64_MIN, INT64_MIN};
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < r; i += (int64_t)gridDim.x * blockDim.x) {
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
-      double q = (double)coord[3 * i + a] / grid_size;  // IEEE div.rn.f64
+      double q = f32div ? (double)__fdiv_rn(coord[3 * i + a], gs32)
+                        : (double)coord[3 * i + a] / grid_size;  // IEEE div.rn.f64
       long long g = (long long)floor(q);
       grid[3 * i + a] = g;
       mn[a] = g < mn[a] ? g : mn[a];
@@ -134,7 +139,9 @@ int ptv3_gridsample(const float* coord, int64_t r, double grid_size, int hash_ty
                     int64_t* grid_coord, uint64_t* key, int64_t* idx_sort, int64_t* inverse, int64_t* count,
                     int64_t* idx_unique, int64_t* min_grid, int64_t* n_voxels, void* workspace,
                     size_t workspace_bytes, void* stream) {
-  if (r < 0 || !(grid_size > 0.0) || hash_type < 0 || hash_type > 1 || !n_voxels) return PTV3_EINVAL;
+  if (r < 0 || !(grid_size > 0.0) || hash_type < 0 || hash_type > 2 || !n_voxels) return PTV3_EINVAL;
+  const int f32div = hash_type == 2;
+  if (f32div) hash_type = 1;
   cudaStream_t st = as_stream(stream);
   if (r == 0) {
     cudaMemsetAsync(n_voxels, 0, 8, st);
@@ -154,7 +161,7 @@ int ptv3_gridsample(const float* coord, int64_t r, double grid_size, int hash_ty
   if (!ws.ok()) return PTV3_EWORKSPACE;
   int g = grid_for(r, 256);
   gs_init_minmax<<<1, 32, 0, st>>>(mm);
-  gs_floor_kernel<<<g, 256, 0, st>>>(coord, r, grid_size, grid_coord, mm);
+  gs_floor_kernel<<<g, 256, 0, st>>>(coord, r, grid_size, f32div, grid_coord, mm);
   gs_hash_kernel<<<g, 256, 0, st>>>(grid_coord, r, mm, hash_type, key, min_grid);
   g_launch_count += 3;
   int rc = radix_argsort_rows(key, 1, r, 64, idx_sort, nullptr, skey, rs_ws, rs_bytes, st);

@@ -145,7 +145,7 @@ def gridsample(coord, grid_size, hash_type="fnv", rand=None):
         if rand.numel() < r:
             rand = torch.cat([rand, rand.new_zeros(r - rand.numel())])
     ws = _ws(lib.ptv3_gridsample_workspace(r), dev)
-    _lib.check(lib.ptv3_gridsample(_p(coord), r, float(grid_size), 0 if hash_type == "fnv" else 1, _p(rand), _p(grid),
+    _lib.check(lib.ptv3_gridsample(_p(coord), r, float(grid_size), {"fnv": 0, "ravel": 1, "ravel_f32": 2}[hash_type], _p(rand), _p(grid),
                                    _p(key), _p(idx_sort), _p(inverse), _p(count), _p(idx_unique), _p(min_grid),
                                    _p(n_vox), _p(ws), ws.numel(), _stream()), "ptv3_gridsample")
     m = int(n_vox.item())

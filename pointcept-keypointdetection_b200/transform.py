@@ -103,3 +103,27 @@ class GridSample(object):
             self._extras(part, full, r, idx_part)
             parts.append(part)
         return parts
+
+
+def normalize_unit_sphere(coord):
+    """tools/OffsetKeyPointPrediction_Qt.py:262-273 (and offset_keypoint_dataset.py:166-177): centre on the centroid,
+    divide by the largest distance to it.  Returns (normalised coord fp32, centroid (3,), scale ())."""
+    c = coord.float()
+    centroid = c.mean(0)
+    centered = c - centroid
+    scale = centered.norm(dim=1).max()
+    scale = torch.where(scale < 1e-6, torch.ones_like(scale), scale)
+    return centered / scale, centroid, scale
+
+
+def voxelize_first(coord, grid_size, keep_order=True):
+    """The reference's inference-time voxelisers (SURVEY 8a row A0'): `np.unique(floor(coord / grid), axis=0,
+    return_index=True)` keeps the FIRST point of every voxel; the Qt server then sorts the indices back to scan order
+    (tools/OffsetKeyPointPrediction_Qt.py:288-289, keep_order=True), pig-seg keeps lexicographic voxel order
+    (tools/pigseg_shared.py:133-134, keep_order=False).  Returns (indices int64 (M,), grid_coord int64 (M,3) already
+    shifted to start at 0).  One kernel chain (float32 quotient like numpy, ravel key, stable radix sort, run heads)."""
+    r = ops.gridsample(coord, grid_size, "ravel_f32", rand=None)
+    idx = r["idx_unique"]
+    if keep_order:
+        idx = torch.sort(idx)[0]
+    return idx, r["grid_coord"][idx]

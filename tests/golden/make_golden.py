@@ -13,6 +13,10 @@ Fixtures (all inputs are seeded; the script is the provenance):
                      scenes run one per forward, with intermediate features
   train.npz          reference OffsetKeypointPTv3 in train() mode (drop_path 0, BatchNorm batch statistics): loss and
                      parameter gradients of one scene after loss.backward() (every gradient's norm + six full tensors)
+  voxelize.npz       the inference-time voxeliser `voxelize_points` (tools/OffsetKeyPointPrediction_Qt.py:276-296,
+                     extracted from the file by ast -- the module itself imports Qt) on a scan with points placed on
+                     and next to cell borders; pig-seg's variant (tools/pigseg_shared.py:132-134) is the same
+                     np.unique without the final index sort
   heads.npz          reference KeypointPTv3 (scatter_mean + regression MLP, C_in = 4) and
                      DefaultSegmentorV2 (20 classes, C_in = 6, BASELINE configs[2] shape)
                      forwards, one scene each, same deterministic weights
@@ -242,6 +246,38 @@ def gold_train(R):
     np.savez_compressed(os.path.join(HERE, "train.npz"), **out)
 
 
+def _extract_function(path, name):
+    import ast
+    import typing
+    src = open(path, encoding="utf-8").read()
+    node = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == name)
+    ns = {"np": np, "Tuple": typing.Tuple}
+    exec(compile(ast.Module(body=[node], type_ignores=[]), path, "exec"), ns)
+    return ns[name]
+
+
+def gold_voxelize(R):
+    fn = _extract_function(os.path.join(ref_loader.REF, "tools", "OffsetKeyPointPrediction_Qt.py"), "voxelize_points")
+    coord, feat = synth.pig_scan(20000, scale=1.0, seed=81)
+    rng = np.random.default_rng(82)
+    g = np.float32(0.02)
+    # points exactly on multiples of the cell size and one float32 ulp to either side: float32 vs float64 quotients differ
+    cells = rng.integers(-40, 40, size=(3000, 3)).astype(np.float32)
+    border = cells * g
+    border = np.concatenate([border, np.nextafter(border, np.float32(np.inf)), np.nextafter(border, np.float32(-np.inf))])
+    coord = np.concatenate([coord, border.astype(np.float32)])
+    coord = coord[rng.permutation(len(coord))]
+    feat = rng.normal(size=(len(coord), 4)).astype(np.float32)
+    sc, sf, sg = fn(coord, feat, 0.02)
+    # recover the kept indices (rows are unique as (coord, feat) pairs)
+    discrete = np.floor(coord / 0.02).astype(np.int32)
+    discrete -= discrete.min(axis=0, keepdims=True)
+    _, ui = np.unique(discrete, axis=0, return_index=True)
+    assert np.array_equal(coord[np.sort(ui)], sc) and np.array_equal(feat[np.sort(ui)], sf)
+    np.savez_compressed(os.path.join(HERE, "voxelize.npz"), coord=coord, idx_lex=ui, idx_sorted=np.sort(ui), grid=sg)
+    print("voxelize: R", len(coord), "M", len(ui))
+
+
 if __name__ == "__main__":
     R = ref_loader.load()
     gold_serialization(R)
@@ -251,6 +287,7 @@ if __name__ == "__main__":
     gold_forward(R)
     gold_heads(R)
     gold_train(R)
+    gold_voxelize(R)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -238,3 +238,27 @@ def test_subm_map_vs_oracle():
         assert np.array_equal(got2[len(idx):], ref[:100])
     one = ops.subm_build_map(dev(idx), 1).cpu().numpy()
     assert np.array_equal(one[:, 0], np.arange(len(idx)))
+
+
+def test_voxelize_first_matches_reference(golden):
+    """A0': first point per voxel with numpy's float32 quotient, both index orders, bit-exact against the reference's
+    `voxelize_points` (frozen) and the oracle on a fresh scan; normalisation to the unit sphere."""
+    from oracle import gridsample as G
+    from ptv3_b200 import synth, transform
+    g = golden("voxelize")
+    coord = torch.from_numpy(g["coord"]).cuda()
+    idx, grid = transform.voxelize_first(coord, 0.02, keep_order=True)
+    assert torch.equal(idx.cpu(), torch.from_numpy(g["idx_sorted"]))
+    assert torch.equal(grid.cpu(), torch.from_numpy(g["grid"]).long())
+    idx, _ = transform.voxelize_first(coord, 0.02, keep_order=False)
+    assert torch.equal(idx.cpu(), torch.from_numpy(g["idx_lex"]))
+    c, _ = synth.pig_scan(50000, scale=2.0, seed=91)
+    for keep in (True, False):
+        ri, rg = G.voxelize_first(c, 0.03, keep_order=keep)
+        idx, grid = transform.voxelize_first(torch.from_numpy(c).cuda(), 0.03, keep_order=keep)
+        assert torch.equal(idx.cpu(), torch.from_numpy(ri)) and torch.equal(grid.cpu(), torch.from_numpy(rg))
+    n, cen, sc = transform.normalize_unit_sphere(torch.from_numpy(c).cuda())
+    centered = c - c.mean(0)
+    ref = centered / np.linalg.norm(centered, axis=1).max()
+    # floating point: the fp32 centroid depends on the summation order (numpy pairwise vs a device tree)
+    assert np.allclose(n.cpu().numpy(), ref, atol=1e-5) and abs(float(n.norm(dim=1).max()) - 1.0) < 1e-6

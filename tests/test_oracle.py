@@ -203,3 +203,14 @@ def test_training_grads_vs_reference(golden):
     got = torch.tensor([grads[n].norm().item() for n in names], dtype=torch.float64)
     ref = torch.from_numpy(g["grad_norms"])
     assert ((got - ref).abs() / ref.clamp_min(1e-12)).max().item() < 1e-3
+
+
+def test_voxelize_first_vs_reference(golden):
+    """A0' (inference voxelisers): oracle restatement against the reference's own `voxelize_points` output, on a scan
+    with points on / one ulp off the cell borders (float32 quotient)."""
+    from oracle import gridsample as G
+    g = golden("voxelize")
+    idx, grid = G.voxelize_first(g["coord"], 0.02, keep_order=True)
+    assert np.array_equal(idx, g["idx_sorted"]) and np.array_equal(grid, g["grid"])
+    idx, _ = G.voxelize_first(g["coord"], 0.02, keep_order=False)
+    assert np.array_equal(idx, g["idx_lex"])
