@@ -281,6 +281,11 @@ int ptv3_segment_csr_bwd(const float* dout, const void* src, const void* out, in
 int ptv3_layer_norm_bwd(const void* x, int dtype_x, const void* dy, int dtype_dy, const float* gamma, float eps,
                         int64_t n, int c, float* dx, float* dgamma, float* dbeta, void* stream);
 
+/* Column sums out[j] = sum_i x[i][j] (fp32 accumulate; the bias gradient of a Linear).  x (n,c) fp32 / bf16 with
+ * 16-byte rows pieces: c % 8 == 0 (bf16) or c % 4 == 0 (fp32) and at most 256 vectors per row, else PTV3_EUNSUPPORTED.
+ * `out` (c) fp32 is overwritten. */
+int ptv3_column_sum(const void* x, int dtype, int64_t n, int c, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

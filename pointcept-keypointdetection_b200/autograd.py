@@ -51,7 +51,7 @@ class SubMConvFn(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             dw = ops.subm_wgrad(x, dy, nbr, k3).permute(1, 0, 2).reshape(wshape)
         if has_bias and ctx.needs_input_grad[2]:
-            db = dy.float().sum(0)
+            db = ops.column_sum(dy)
         return dx, dw, db, None, None
 
 
@@ -126,6 +126,38 @@ class LayerNormFn(torch.autograd.Function):
             dy = dy.float()
         dx, dg, db = ops.layer_norm_bwd(x, dy, weight.detach(), ctx.eps)
         return dx.to(x.dtype), dg.to(weight.dtype), db.to(weight.dtype), None, None
+
+
+class LinearFn(torch.autograd.Function):
+    """y = x W^T + b with operands cast to `cd` (torch.autocast's Linear): cuBLAS GEMMs both ways, the bias gradient
+    by ptv3_column_sum instead of torch's generic dim-0 reduction."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, cd):
+        xc = x.detach().to(cd)
+        wc = weight.detach().to(cd)
+        y = torch.nn.functional.linear(xc, wc, bias.detach().to(cd) if bias is not None else None)
+        ctx.save_for_backward(xc, wc)
+        ctx.meta = (x.dtype, weight.dtype, bias is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xc, wc = ctx.saved_tensors
+        xdt, wdt, has_bias = ctx.meta
+        dy = dy.contiguous().to(xc.dtype)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = (dy @ wc).to(xdt)
+        if ctx.needs_input_grad[1]:
+            dw = (dy.t() @ xc).to(wdt)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = ops.column_sum(dy).to(wdt)
+        return dx, dw, db, None
+
+
+def linear(x, lin, cd):
+    return LinearFn.apply(x, lin.weight, lin.bias, cd)
 
 
 def layer_norm(x, ln, out_dtype=torch.float32):

@@ -503,3 +503,16 @@ def layer_norm_bwd(x, dy, gamma, eps):
     _lib.check(lib.ptv3_layer_norm_bwd(_p(x), _dt(x), _p(dy), _dt(dy), _p(gamma.contiguous().float()), float(eps), n, c,
                                        _p(dx), _p(dgb[0]), _p(dgb[1]), _stream()), "ptv3_layer_norm_bwd")
     return dx, dgb[0], dgb[1]
+
+
+def column_sum(x):
+    """sum over dim 0 of an (n, c) fp32 / bf16 matrix -> fp32 (c); torch for shapes the kernel does not take."""
+    _need_cuda(x)
+    n, c = x.shape
+    e = 8 if x.dtype == torch.bfloat16 else 4
+    if x.dtype not in (torch.bfloat16, torch.float32) or c % e != 0 or c // e > 256:
+        return x.float().sum(0)
+    x = x.contiguous()
+    out = torch.empty(c, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().ptv3_column_sum(_p(x), _dt(x), n, c, _p(out), _stream()), "ptv3_column_sum")
+    return out

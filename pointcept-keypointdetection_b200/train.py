@@ -24,7 +24,7 @@ from .structure import Point, SparseConvTensor
 
 
 def _lin(x, lin, cd):
-    return F.linear(x.to(cd), lin.weight.to(cd), lin.bias.to(cd) if lin.bias is not None else None)
+    return A.linear(x, lin, cd)
 
 
 def _ln(x, ln, out_dtype=torch.float32):

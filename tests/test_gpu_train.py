@@ -197,6 +197,40 @@ def test_layer_norm_grads(c, xdt, odt):
     assert rel_l2(lng.weight.grad, gw) < 1e-4 and rel_l2(lng.bias.grad, gb) < 1e-4
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("cin,cout", [(64, 192), (32, 96), (512, 2048), (64, 24), (20, 36)])
+def test_linear_grads(dtype, cin, cout):
+    """autograd.LinearFn (cuBLAS GEMMs + ptv3_column_sum for the bias gradient; (20, 36) takes torch's sum)."""
+    from ptv3_b200 import autograd as A
+    g = torch.Generator().manual_seed(cin + cout)
+    n = 4099
+    x = torch.randn(n, cin, generator=g)
+    dy = torch.randn(n, cout, generator=g)
+    lin = torch.nn.Linear(cin, cout)
+    if dtype == torch.bfloat16:
+        x, dy = x.bfloat16().float(), dy.bfloat16().float()
+        with torch.no_grad():
+            lin.weight.copy_(lin.weight.bfloat16().float())
+            lin.bias.copy_(lin.bias.bfloat16().float())
+    xr = x.clone().requires_grad_()
+    ref = lin(xr)
+    ref.backward(dy)
+    ling = torch.nn.Linear(cin, cout).cuda()
+    ling.load_state_dict(lin.state_dict())
+    xg = x.cuda().requires_grad_()
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        out = A.linear(xg, ling, dtype)
+        out.backward(dy.cuda().to(dtype))
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    tol = TOL[dtype]
+    assert rel_l2(out, ref) < tol and rel_l2(xg.grad, xr.grad) < tol
+    assert rel_l2(ling.weight.grad, lin.weight.grad) < tol
+    assert rel_l2(ling.bias.grad, lin.bias.grad) < 1e-5
+
+
 def _weights():
     from conftest import GOLDEN
     from ptv3_b200 import synth
