@@ -262,12 +262,17 @@ int ptv3_subm_wgrad(const void* in, const void* dout, const int32_t* nbr, int64_
 
 /* Window attention backward (flash_attn_varlen_qkvpacked_func's backward, point_transformer_v3m1_base.py:208-215).
  * qkv (n,3,h,16), out / dout (n,h,16) in `dtype`; dqkv (n,3,h,16) fp32, ZEROED by the caller (the K / V parts are
- * accumulated: the last window of a scene shares keys with the one before it). */
+ * accumulated: the last window of a scene shares keys with the one before it).
+ * `lse` (n,h) fp32 or NULL: the rows' log-sum-exp in log2 units of the scaled scores as written by
+ * ptv3_attn_window_fwd_lse (bf16 only; PTV3_EUNSUPPORTED otherwise); NULL = recomputed inside the backward. */
+int ptv3_attn_window_fwd_lse(const void* qkv, int dtype, const int64_t* order, const int64_t* windows,
+                             const int64_t* n_windows, int64_t n_windows_max, int64_t max_len, int64_t n, int h, int d,
+                             float scale, void* out, float* lse, void* stream);
 size_t ptv3_attn_window_bwd_workspace(int64_t n, int h);
 int ptv3_attn_window_bwd(const void* qkv, const void* out, const void* dout, int dtype, const int64_t* order,
                          const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max, int64_t max_len,
-                         int64_t n, int h, int d, float scale, float* dqkv, void* workspace, size_t workspace_bytes,
-                         void* stream);
+                         int64_t n, int h, int d, float scale, const float* lse /* NULL ok */, float* dqkv,
+                         void* workspace, size_t workspace_bytes, void* stream);
 
 /* torch_scatter.segment_csr backward (:416-421): dsrc[gather[j]] for every j of segment k from dout[k];
  * max / min give the gradient to the first row (CSR order) that equals the reduced value. */

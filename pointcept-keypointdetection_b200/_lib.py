@@ -55,8 +55,10 @@ SIGNATURES = {
     "ptv3_affine_act": (c_int, [c_vp, c_int, c_vp, c_vp, c_int, c_i64, c_int, c_vp, c_vp, c_vp]),
     "ptv3_subm_wgrad": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_attn_window_bwd_workspace": (c_sz, [c_i64, c_int]),
+    "ptv3_attn_window_fwd_lse": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_f32, c_vp,
+                                         c_vp, c_vp]),
     "ptv3_attn_window_bwd": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_f32,
-                                     c_vp, c_vp, c_sz, c_vp]),
+                                     c_vp, c_vp, c_vp, c_sz, c_vp]),
     "ptv3_segment_csr_bwd": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp]),
     "ptv3_layer_norm_bwd": (c_int, [c_vp, c_int, c_vp, c_int, c_vp, c_f32, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
     "ptv3_column_sum": (c_int, [c_vp, c_int, c_i64, c_int, c_vp, c_vp]),

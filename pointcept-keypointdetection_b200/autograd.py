@@ -61,16 +61,20 @@ class WindowAttnFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, qkv, order, windows, n_windows, num_heads, max_len, scale, algo):
         q = qkv.detach().contiguous()
-        out = ops.attn_window(q, order, windows, n_windows, num_heads, max_len, scale, algo)
-        ctx.save_for_backward(q, out, order, windows, n_windows)
+        lse = None
+        if q.dtype == torch.bfloat16 and algo in (0, 2) and max_len <= 1024:
+            out, lse = ops.attn_window_lse(q, order, windows, n_windows, num_heads, max_len, scale)
+        else:
+            out = ops.attn_window(q, order, windows, n_windows, num_heads, max_len, scale, algo)
+        ctx.save_for_backward(q, out, order, windows, n_windows, lse)
         ctx.meta = (num_heads, max_len, scale)
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        q, out, order, windows, n_windows = ctx.saved_tensors
+        q, out, order, windows, n_windows, lse = ctx.saved_tensors
         num_heads, max_len, scale = ctx.meta
-        dqkv = ops.attn_window_bwd(q, out, dout, order, windows, n_windows, num_heads, max_len, scale)
+        dqkv = ops.attn_window_bwd(q, out, dout, order, windows, n_windows, num_heads, max_len, scale, lse=lse)
         return dqkv.to(q.dtype), None, None, None, None, None, None, None
 
 

@@ -124,7 +124,7 @@ extern int g_wgrad_simt;
 extern int g_attn_bwd_warps;
 int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                    int64_t n_windows_max, int64_t max_len, int64_t n, int h, float scale, __nv_bfloat16* out,
-                   cudaStream_t st);
+                   cudaStream_t st, float* lse = nullptr);
 
 }  // namespace ptv3
 
@@ -168,6 +168,17 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const
   else
     return PTV3_EINVAL;
   return check_launch();
+}
+
+int ptv3_attn_window_fwd_lse(const void* qkv, int dtype, const int64_t* order, const int64_t* windows,
+                             const int64_t* n_windows, int64_t n_windows_max, int64_t max_len, int64_t n, int h, int d,
+                             float scale, void* out, float* lse, void* stream) {
+  if (n < 0 || h < 1 || h > 65535 || d != kAttnD || n_windows_max < 0 || max_len < 1) return PTV3_EINVAL;
+  if (dtype != PTV3_BF16) return PTV3_EUNSUPPORTED;
+  if (n == 0 || n_windows_max == 0) return PTV3_OK;
+  if (!qkv || !windows || !n_windows || !out || !lse) return PTV3_EINVAL;
+  return attn_window_tc((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, n, h, scale,
+                        (__nv_bfloat16*)out, as_stream(stream), lse);
 }
 
 int ptv3_debug_set(int key, int value) {

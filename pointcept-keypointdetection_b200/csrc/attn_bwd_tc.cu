@@ -52,11 +52,12 @@ __device__ __forceinline__ void zero16(uint32_t dst) {
 }  // namespace
 
 // smem: K, V, Q, dO [kpad][16] bf16 each; lse_s, d_s [kpad] fp32; order_s [kpad] int32
+// lse_g (optional): the forward's log-sum-exp per (row, head), log2 units of the scaled scores -> sweep 1 is skipped
 template <int kWarps>
 __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
     const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
     const int64_t* __restrict__ order, const int64_t* __restrict__ windows, const int64_t* __restrict__ n_windows, int h,
-    float scale, float sl2, int kpad_max, float* __restrict__ dqkv) {
+    float scale, float sl2, int kpad_max, float* __restrict__ dqkv, const float* __restrict__ lse_g) {
   constexpr int kThreads = kWarps * 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int w = blockIdx.x, head = blockIdx.y;
@@ -125,6 +126,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
       }
     }
     d_s[qi] = acc;
+    if (lse_g) lse_s[qi] = lse_g[row * h + head];
   }
   __syncthreads();
 
@@ -147,7 +149,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
     const int qi0 = qt * 16 + g, qi1 = qi0 + 8;
     // sweep 1: log-sum-exp in log2 units of the scaled scores
     float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-    for (int c = 0; c < kpad / 64; ++c) {
+    for (int c = 0; c < (lse_g ? 0 : kpad / 64); ++c) {
       float s[8][4];
 #pragma unroll
       for (int b2 = 0; b2 < 4; ++b2) {
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
     l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float lse0 = m0 + __log2f(l0), lse1 = m1 + __log2f(l1);
+    const float lse0 = lse_g ? lse_s[qi0] : m0 + __log2f(l0), lse1 = lse_g ? lse_s[qi1] : m1 + __log2f(l1);
     const float D0 = d_s[qi0], D1 = d_s[qi1];
     // sweep 2: dQ
     float dq[2][4];
@@ -235,13 +237,13 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
       float* o = dqkv + (int64_t)order_s[q_rel + qi0] * rs + head * kD;
       *reinterpret_cast<float2*>(o + 2 * t) = make_float2(dq[0][0] * scale, dq[0][1] * scale);
       *reinterpret_cast<float2*>(o + 8 + 2 * t) = make_float2(dq[1][0] * scale, dq[1][1] * scale);
-      if (t == 0) lse_s[qi0] = lse0;
+      if (t == 0 && !lse_g) lse_s[qi0] = lse0;
     }
     if (qi1 < ql) {
       float* o = dqkv + (int64_t)order_s[q_rel + qi1] * rs + head * kD;
       *reinterpret_cast<float2*>(o + 2 * t) = make_float2(dq[0][2] * scale, dq[0][3] * scale);
       *reinterpret_cast<float2*>(o + 8 + 2 * t) = make_float2(dq[1][2] * scale, dq[1][3] * scale);
-      if (t == 0) lse_s[qi1] = lse1;
+      if (t == 0 && !lse_g) lse_s[qi1] = lse1;
     }
   }
   __syncthreads();
@@ -324,7 +326,7 @@ int g_attn_bwd_warps = 16;   // debug slot 6
 // returns PTV3_EUNSUPPORTED when the window does not fit in shared memory (caller falls back to the CUDA-core path)
 int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const __nv_bfloat16* dout,
                        const int64_t* order, const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max,
-                       int64_t max_len, int h, float scale, float* dqkv, cudaStream_t st) {
+                       int64_t max_len, int h, float scale, float* dqkv, cudaStream_t st, const float* lse) {
   int kpad = (int)(cdiv(max_len, 64) * 64);
   size_t smem = (size_t)kpad * 128 + (size_t)kpad * 12;
   if (smem > 220 * 1024) return PTV3_EUNSUPPORTED;
@@ -341,10 +343,10 @@ int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const
   // one CTA per SM (140 KB of staged operands): 16 warps hide the ldmatrix / MUFU latency better than 8
   if (g_attn_bwd_warps == 8)
     attn_bwd_mma_kernel<8><<<grid, 256, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
-                                                    scale * 1.4426950408889634f, kpad, dqkv);
+                                                    scale * 1.4426950408889634f, kpad, dqkv, lse);
   else
     attn_bwd_mma_kernel<16><<<grid, 512, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
-                                                     scale * 1.4426950408889634f, kpad, dqkv);
+                                                     scale * 1.4426950408889634f, kpad, dqkv, lse);
   return check_launch();
 }
 

@@ -57,9 +57,12 @@ __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr)
 
 // smem: K [kpad][16] bf16, V [kpad][16] bf16, then the window's storage rows order_s [kpad] int32 (the queries
 // of a window are a sub-range of its keys, so the Q gather and the output scatter index through it as well)
+// kLse (training forward): also writes the rows' log-sum-exp, in log2 units of the scaled scores, for the backward
+template <bool kLse>
 __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
     const __nv_bfloat16* __restrict__ qkv, const int64_t* __restrict__ order, const int64_t* __restrict__ windows,
-    const int64_t* __restrict__ n_windows, int h, float scale_log2, int kpad_max, __nv_bfloat16* __restrict__ out) {
+    const int64_t* __restrict__ n_windows, int h, float scale_log2, int kpad_max, __nv_bfloat16* __restrict__ out,
+    float* __restrict__ lse) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int w = blockIdx.x, head = blockIdx.y;
   if (w >= n_windows[0]) return;
@@ -206,12 +209,14 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
       uint32_t* p = reinterpret_cast<uint32_t*>(out + (int64_t)order_s[q_rel + qi0] * h * kD + head * kD);
       p[t] = pack_bf16(o[0][0] * inv, o[0][1] * inv);
       p[t + 4] = pack_bf16(o[1][0] * inv, o[1][1] * inv);
+      if (kLse && t == 0) lse[(int64_t)order_s[q_rel + qi0] * h + head] = m0 * scale_log2 + __log2f(l[0]);
     }
     if (v1) {
       float inv = 1.f / l[2];
       uint32_t* p = reinterpret_cast<uint32_t*>(out + (int64_t)order_s[q_rel + qi1] * h * kD + head * kD);
       p[t] = pack_bf16(o[0][2] * inv, o[0][3] * inv);
       p[t + 4] = pack_bf16(o[1][2] * inv, o[1][3] * inv);
+      if (kLse && t == 0) lse[(int64_t)order_s[q_rel + qi1] * h + head] = m1 * scale_log2 + __log2f(l[2]);
     }
   }
 }
@@ -220,15 +225,17 @@ int g_attn_qsplit = 0;   // 0 = auto; debug slot 2 forces 1 / 2 / 4
 
 int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                    int64_t n_windows_max, int64_t max_len, int64_t n, int h, float scale, __nv_bfloat16* out,
-                   cudaStream_t st) {
+                   cudaStream_t st, float* lse) {
   (void)n;
   int kpad = (int)(cdiv(max_len, kChunk) * kChunk);
   size_t smem = (size_t)kpad * kD * 2 * 2 + (size_t)kpad * 4;
   if (smem > 200 * 1024) return PTV3_EUNSUPPORTED;  // patch > 3200
   static size_t configured = 0;
   if (smem > configured) {
-    if (cudaFuncSetAttribute(attn_window_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
-        cudaSuccess)
+    if (cudaFuncSetAttribute(attn_window_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+            cudaSuccess ||
+        cudaFuncSetAttribute(attn_window_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+            cudaSuccess)
       return PTV3_ELAUNCH;
     configured = smem;
   }
@@ -246,8 +253,12 @@ int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
     }
   }
   dim3 grid((unsigned)n_windows_max, (unsigned)h, (unsigned)split);
-  attn_window_mma_kernel<<<grid, kThreads, smem, st>>>(qkv, order, windows, n_windows, h,
-                                                       scale * 1.4426950408889634f, kpad, out);
+  if (lse)
+    attn_window_mma_kernel<true><<<grid, kThreads, smem, st>>>(qkv, order, windows, n_windows, h,
+                                                               scale * 1.4426950408889634f, kpad, out, lse);
+  else
+    attn_window_mma_kernel<false><<<grid, kThreads, smem, st>>>(qkv, order, windows, n_windows, h,
+                                                                scale * 1.4426950408889634f, kpad, out, nullptr);
   return check_launch();
 }
 

@@ -271,7 +271,7 @@ __global__ void segment_csr_bwd_kernel(const float* __restrict__ dout, const T* 
 // csrc/attn_bwd_tc.cu
 int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const __nv_bfloat16* dout,
                        const int64_t* order, const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max,
-                       int64_t max_len, int h, float scale, float* dqkv, cudaStream_t st);
+                       int64_t max_len, int h, float scale, float* dqkv, cudaStream_t st, const float* lse);
 int g_attn_bwd_simt = 0;   // debug slot 4: 1 forces the CUDA-core kernels for bf16 too
 // csrc/wgrad_tc.cu
 int subm_wgrad_fast(const void* in, const void* dout, const int32_t* nbr, int64_t n, int c_in, int c_out, int k3, int dtype,
@@ -319,18 +319,18 @@ size_t ptv3_attn_window_bwd_workspace(int64_t n, int h) { return align_up((size_
 
 int ptv3_attn_window_bwd(const void* qkv, const void* out, const void* dout, int dtype, const int64_t* order,
                          const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max, int64_t max_len,
-                         int64_t n, int h, int d, float scale, float* dqkv, void* workspace, size_t workspace_bytes,
-                         void* stream) {
+                         int64_t n, int h, int d, float scale, const float* lse, float* dqkv, void* workspace,
+                         size_t workspace_bytes, void* stream) {
   if (n < 0 || h < 1 || h > 65535 || d != kBD || n_windows_max < 0 || max_len < 1) return PTV3_EINVAL;
   if (n == 0 || n_windows_max == 0) return PTV3_OK;
   if (!qkv || !out || !dout || !windows || !n_windows || !dqkv) return PTV3_EINVAL;
   if (dtype == PTV3_BF16 && !g_attn_bwd_simt) {
     int rc = attn_window_bwd_tc((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, order,
-                                windows, n_windows, n_windows_max, max_len, h, scale, dqkv, as_stream(stream));
+                                windows, n_windows, n_windows_max, max_len, h, scale, dqkv, as_stream(stream), lse);
     if (rc != PTV3_EUNSUPPORTED) return rc;
   }
   Workspace ws(workspace, workspace_bytes);
-  float* lse = ws.take<float>((size_t)n * h);
+  float* lse_ws = ws.take<float>((size_t)n * h);
   float* dvec = ws.take<float>((size_t)n * h);
   if (!ws.ok()) return PTV3_EWORKSPACE;
   int64_t blocks = cdiv(max_len, kBThreads);
@@ -339,15 +339,15 @@ int ptv3_attn_window_bwd(const void* qkv, const void* out, const void* dout, int
   cudaStream_t st = as_stream(stream);
   if (dtype == PTV3_F32) {
     attn_bwd_dq_kernel<float><<<grid, kBThreads, 0, st>>>((const float*)qkv, (const float*)out, (const float*)dout, order,
-                                                          windows, n_windows, h, scale, dqkv, lse, dvec);
+                                                          windows, n_windows, h, scale, dqkv, lse_ws, dvec);
     attn_bwd_dkv_kernel<float><<<grid, kBThreads, 0, st>>>((const float*)qkv, (const float*)dout, order, windows,
-                                                           n_windows, h, scale, lse, dvec, dqkv);
+                                                           n_windows, h, scale, lse_ws, dvec, dqkv);
   } else if (dtype == PTV3_BF16) {
     attn_bwd_dq_kernel<__nv_bfloat16><<<grid, kBThreads, 0, st>>>(
         (const __nv_bfloat16*)qkv, (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, order, windows, n_windows, h,
-        scale, dqkv, lse, dvec);
+        scale, dqkv, lse_ws, dvec);
     attn_bwd_dkv_kernel<__nv_bfloat16><<<grid, kBThreads, 0, st>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dout,
-                                                                   order, windows, n_windows, h, scale, lse, dvec, dqkv);
+                                                                   order, windows, n_windows, h, scale, lse_ws, dvec, dqkv);
   } else {
     return PTV3_EINVAL;
   }

@@ -450,7 +450,29 @@ def subm_wgrad(feat, dout, nbr, k3):
     return dw
 
 
-def attn_window_bwd(qkv, out, dout, order, windows, n_windows, num_heads, max_len, scale=None):
+def attn_window_lse(qkv, order, windows, n_windows, num_heads, max_len, scale=None):
+    """bf16 attn_window that also returns the rows' log-sum-exp (N, H) fp32 (log2 units) for attn_window_bwd."""
+    _need_cuda(qkv, order, windows, n_windows)
+    lib = _lib.load()
+    qkv = qkv.contiguous()
+    assert qkv.dtype == torch.bfloat16
+    n = qkv.shape[0]
+    c = qkv.numel() // (3 * n) if n > 0 else 0
+    h = int(num_heads)
+    d = c // h if h else 0
+    out = torch.empty((n, c), dtype=qkv.dtype, device=qkv.device)
+    lse = torch.empty((n, h), dtype=torch.float32, device=qkv.device)
+    if n == 0:
+        return out, lse
+    scale = float(scale) if scale is not None else d ** -0.5
+    o = order.contiguous().long() if order is not None else None
+    _lib.check(lib.ptv3_attn_window_fwd_lse(_p(qkv), _dt(qkv), _p(o), _p(windows), _p(n_windows), windows.shape[0],
+                                            int(max_len), n, h, d, scale, _p(out), _p(lse), _stream()),
+               "ptv3_attn_window_fwd_lse")
+    return out, lse
+
+
+def attn_window_bwd(qkv, out, dout, order, windows, n_windows, num_heads, max_len, scale=None, lse=None):
     """Gradient of attn_window w.r.t. qkv: (N, 3*H*16) fp32."""
     _need_cuda(qkv, out, dout, order, windows, n_windows)
     lib = _lib.load()
@@ -467,8 +489,8 @@ def attn_window_bwd(qkv, out, dout, order, windows, n_windows, num_heads, max_le
     o = order.contiguous().long() if order is not None else None
     ws = _ws(lib.ptv3_attn_window_bwd_workspace(n, h), qkv.device)
     _lib.check(lib.ptv3_attn_window_bwd(_p(qkv), _p(out), _p(dout), _dt(qkv), _p(o), _p(windows), _p(n_windows),
-                                        windows.shape[0], int(max_len), n, h, d, scale, _p(dqkv), _p(ws), ws.numel(),
-                                        _stream()), "ptv3_attn_window_bwd")
+                                        windows.shape[0], int(max_len), n, h, d, scale, _p(lse), _p(dqkv), _p(ws),
+                                        ws.numel(), _stream()), "ptv3_attn_window_bwd")
     return dqkv
 
 

@@ -130,8 +130,8 @@ def _grad_worker(rank, world, port, q):
             sync.zero_grad()
             net(data[rank] * (step + 1)).square().mean().backward()
             sync.finish()
-            out.append([p.grad.clone() for p in net.parameters()])
-        q.put((rank, out, unused.grad.clone()))
+            out.append([p.grad.numpy().copy() for p in net.parameters()])   # numpy pickles by value (a tensor would
+        q.put((rank, out, unused.grad.numpy().copy()))                      # travel as an fd of a process that exits)
     finally:
         dist.destroy_process_group()
 
@@ -164,5 +164,5 @@ def test_grad_sync_world_size_2_gloo():
             want = gr if want is None else [a + b for a, b in zip(want, gr)]
         for r in range(world):
             for a, b in zip(res[r][1][step], want):
-                assert torch.allclose(a, b, atol=1e-6)
-    assert all(torch.equal(r[2], torch.zeros(3)) for r in res)
+                assert torch.allclose(torch.from_numpy(a), b, atol=1e-6)
+    assert all((r[2] == 0).all() for r in res)

@@ -15,16 +15,20 @@ def main():
     windows, nwin = ops.build_windows(offset, K, n)
     out = ops.attn_window(qkv, order, windows, nwin, H, K)
     lib = _lib.load()
-    for warps in (8, 16):
+    out2, lse = ops.attn_window_lse(qkv, order, windows, nwin, H, K)
+    assert torch.equal(out, out2)
+    for warps, use_lse in ((8, False), (16, False), (16, True)):
         lib.ptv3_debug_set(6, warps)
+        kw = dict(lse=lse) if use_lse else {}
         for _ in range(2):
-            ops.attn_window_bwd(qkv, out, dout, order, windows, nwin, H, K)
+            ops.attn_window_bwd(qkv, out, dout, order, windows, nwin, H, K, **kw)
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for _ in range(5):
-            ops.attn_window_bwd(qkv, out, dout, order, windows, nwin, H, K)
+            ops.attn_window_bwd(qkv, out, dout, order, windows, nwin, H, K, **kw)
         b.record(); torch.cuda.synchronize()
-        print(f"warps={warps}: bwd {a.elapsed_time(b) / 5:.3f} ms (incl. the zero-fill of dqkv)")
+        print(f"warps={warps} lse={use_lse}: bwd {a.elapsed_time(b) / 5:.3f} ms (incl. the zero-fill of dqkv)")
+    lib.ptv3_debug_set(6, 16)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(5):
