@@ -286,6 +286,18 @@ int ptv3_segment_csr_bwd(const float* dout, const void* src, const void* out, in
 int ptv3_layer_norm_bwd(const void* x, int dtype_x, const void* dy, int dtype_dy, const float* gamma, float eps,
                         int64_t n, int c, float* dx, float* dgamma, float* dbeta, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * SURVEY 8f rank 2 (SpUNet-v1m1, sparse_unet/spconv_unet_v1m1_base.py:137-213): index pairs of
+ * spconv.SparseConv3d(kernel 2, stride 2) and of the SparseInverseConv3d that shares its indice_key.
+ * The coarse sites come from ptv3_pool_front on a z-order code (code >> 3 partitions like (batch, grid >> 1));
+ * this call turns `cluster` (fine row -> coarse row) into the two gather tables the conv kernels consume:
+ *   nbr_fwd (m,8): nbr_fwd[c][k] = fine row of coarse site c at kernel offset k = ((x&1)*2 + (y&1))*2 + (z&1), -1 absent
+ *   nbr_inv (n,8): nbr_inv[i][k(i)] = cluster[i], the other seven entries -1
+ * grid (n,3) int64 fine grid coordinates, cluster (n) int64.
+ * ------------------------------------------------------------------------- */
+int ptv3_sparse_pair_maps(const int64_t* grid, const int64_t* cluster, int64_t n, int64_t m, int32_t* nbr_fwd,
+                          int32_t* nbr_inv, void* stream);
+
 /* Column sums out[j] = sum_i x[i][j] (fp32 accumulate; the bias gradient of a Linear).  x (n,c) fp32 / bf16 with
  * 16-byte rows pieces: c % 8 == 0 (bf16) or c % 4 == 0 (fp32) and at most 256 vectors per row, else PTV3_EUNSUPPORTED.
  * `out` (c) fp32 is overwritten. */

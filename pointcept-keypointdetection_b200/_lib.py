@@ -61,6 +61,7 @@ SIGNATURES = {
                                      c_vp, c_vp, c_vp, c_sz, c_vp]),
     "ptv3_segment_csr_bwd": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp]),
     "ptv3_layer_norm_bwd": (c_int, [c_vp, c_int, c_vp, c_int, c_vp, c_f32, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "ptv3_sparse_pair_maps": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "ptv3_column_sum": (c_int, [c_vp, c_int, c_i64, c_int, c_vp, c_vp]),
     "ptv3_keypoint_aggregate": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_f32, c_vp, c_vp]),
 }

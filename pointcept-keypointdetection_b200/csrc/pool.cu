@@ -127,6 +127,18 @@ __global__ void __launch_bounds__(256) offset_to_batch_kernel(const int64_t* __r
   }
 }
 
+__global__ void __launch_bounds__(256) sparse_pair_maps_kernel(const int64_t* __restrict__ grid,
+                                                               const int64_t* __restrict__ cluster, int64_t n,
+                                                               int32_t* __restrict__ nbr_fwd,
+                                                               int32_t* __restrict__ nbr_inv) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(((grid[3 * i] & 1) * 2 + (grid[3 * i + 1] & 1)) * 2 + (grid[3 * i + 2] & 1));
+    const int64_t c = cluster[i];
+    nbr_fwd[c * 8 + k] = (int32_t)i;
+    nbr_inv[i * 8 + k] = (int32_t)c;
+  }
+}
+
 }  // namespace ptv3
 
 using namespace ptv3;
@@ -180,6 +192,18 @@ int ptv3_offset_to_batch(const int64_t* offset, int64_t n_scenes, int64_t n, int
   if (n == 0) return PTV3_OK;
   if (!batch) return PTV3_EINVAL;
   offset_to_batch_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(offset, n_scenes, n, batch);
+  return check_launch();
+}
+
+int ptv3_sparse_pair_maps(const int64_t* grid, const int64_t* cluster, int64_t n, int64_t m, int32_t* nbr_fwd,
+                          int32_t* nbr_inv, void* stream) {
+  if (n < 0 || m < 0) return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!grid || !cluster || !nbr_fwd || !nbr_inv) return PTV3_EINVAL;
+  cudaStream_t st = as_stream(stream);
+  cudaMemsetAsync(nbr_fwd, 0xff, (size_t)m * 8 * 4, st);
+  cudaMemsetAsync(nbr_inv, 0xff, (size_t)n * 8 * 4, st);
+  sparse_pair_maps_kernel<<<grid_for(n, 256), 256, 0, st>>>(grid, cluster, n, nbr_fwd, nbr_inv);
   return check_launch();
 }
 

@@ -199,8 +199,9 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
       }
       producers_sync();
       const uint32_t mask = masks[i & 3];
-      const int per = c_in >= KBLK ? c_in / KBLK : 1;   // 1, 2, 4 or 8
+      const int per = c_in >= KBLK ? c_in / KBLK : 1;   // 1, 2, 4, 8 on the PTv3 path; 3 / 6 in SpUNet's decoder
       const int per_shift = 31 - __clz(per);
+      const bool per_pow2 = (per & (per - 1)) == 0;
       uint32_t blk_mask;  // bit j = K-block group j is needed (offset j for c_in >= 64, offset pair j for c_in == 32)
       if (c_in >= KBLK) {
         blk_mask = mask;
@@ -217,7 +218,8 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
       int popped = 0;   // set bits of blk_mask already dropped
       for (int done = (int)((uint32_t)(group + kGatherGroups - (int)(g0 % kGatherGroups)) % kGatherGroups); done < n_kb;
            done += kGatherGroups) {
-        const int jidx = done >> per_shift, cb = done & (per - 1);
+        const int jidx = per_pow2 ? done >> per_shift : done / per;
+        const int cb = done - jidx * per;
         while (popped < jidx) {
           blk_mask &= blk_mask - 1;
           ++popped;

@@ -136,6 +136,9 @@ class SubMConv3d(SparseModule):
             nn.init.uniform_(self.bias, -bound, bound)
 
     def neighbor_map(self, x):
+        if self.kernel_size == 1:          # a 1x1x1 SubM conv is a per-site Linear: the table is the identity
+            n = x.indices.shape[0]
+            return torch.arange(n, dtype=torch.int32, device=x.indices.device).view(n, 1)
         key = (self.indice_key, self.kernel_size)
         nbr = x.indice_dict.get(key) if self.indice_key is not None else None
         if nbr is None:
@@ -159,6 +162,8 @@ class SubMConv3d(SparseModule):
     def conv(self, features, x, scale=None, shift=None, algo=0):
         w, b = self._weights(features.dtype, scale, shift)
         k3 = self.kernel_size ** 3
+        if k3 == 1:      # 1x1x1 SubM conv = a plain per-site GEMM: library call (cuBLAS), no gather
+            return F.linear(features, w[0], b.to(features.dtype) if b is not None else None)
         if (features.dtype == torch.bfloat16 and algo != 1
                 and ops.subm_conv_tc_supported(self.in_channels, self.out_channels, k3)):
             # tcgen05 path: the K-blocked / swizzled weight image is built once per parameter version

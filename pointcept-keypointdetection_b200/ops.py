@@ -318,8 +318,9 @@ def subm_conv(feat, weight_koc, bias, nbr, algo=0):
     lib = _lib.load()
     feat, weight_koc = feat.contiguous(), weight_koc.contiguous()
     assert feat.dtype == weight_koc.dtype
-    n, cin = feat.shape
+    cin = feat.shape[1]
     k3, cout, cin2 = weight_koc.shape
+    n = nbr.shape[0]          # output rows; SubM convs have n == feat.shape[0], strided / inverse convs do not
     assert cin2 == cin and nbr.shape == (n, k3) and nbr.dtype == torch.int32
     out = torch.empty((n, cout), dtype=feat.dtype, device=feat.device)
     dt = _dt(feat)
@@ -356,8 +357,8 @@ def subm_conv_packed(feat, packed, bias, nbr, cout):
     lib = _lib.load()
     feat = feat.contiguous()
     assert feat.dtype == torch.bfloat16 and nbr.dtype == torch.int32
-    n, cin = feat.shape
-    k3 = nbr.shape[1]
+    cin = feat.shape[1]
+    n, k3 = nbr.shape         # output rows (== feat rows for SubM convs)
     out = torch.empty((n, cout), dtype=feat.dtype, device=feat.device)
     b = bias.contiguous().float() if bias is not None else None
     with _timed("subm_conv", n=n, cin=cin, cout=cout, k3=k3, dtype=BF16, nbr=nbr):
@@ -538,3 +539,15 @@ def column_sum(x):
     out = torch.empty(c, dtype=torch.float32, device=x.device)
     _lib.check(_lib.load().ptv3_column_sum(_p(x), _dt(x), n, c, _p(out), _stream()), "ptv3_column_sum")
     return out
+
+
+def sparse_pair_maps(grid_coord, cluster, n_coarse):
+    """(nbr_fwd (M,8), nbr_inv (N,8)) int32 gather tables of SparseConv3d(k2,s2) / its SparseInverseConv3d."""
+    _need_cuda(grid_coord, cluster)
+    g, c = grid_coord.contiguous().long(), cluster.contiguous().long()
+    n = g.shape[0]
+    fwd = torch.empty((int(n_coarse), 8), dtype=torch.int32, device=g.device)
+    inv = torch.empty((n, 8), dtype=torch.int32, device=g.device)
+    _lib.check(_lib.load().ptv3_sparse_pair_maps(_p(g), _p(c), n, int(n_coarse), _p(fwd), _p(inv), _stream()),
+               "ptv3_sparse_pair_maps")
+    return fwd, inv

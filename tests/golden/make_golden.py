@@ -17,6 +17,8 @@ Fixtures (all inputs are seeded; the script is the provenance):
                      extracted from the file by ast -- the module itself imports Qt) on a scan with points placed on
                      and next to cell borders; pig-seg's variant (tools/pigseg_shared.py:132-134) is the same
                      np.unique without the final index sort
+  spunet.npz         reference SpUNetBase ("SpUNet-v1m1", 13 classes, C_in = 4) forward on a two-scene batch: the wiring of
+                     BasicBlock / down / up / skip concatenation over the restated spconv ops (oracle/spunet.py)
   heads.npz          reference KeypointPTv3 (scatter_mean + regression MLP, C_in = 4) and
                      DefaultSegmentorV2 (20 classes, C_in = 6, BASELINE configs[2] shape)
                      forwards, one scene each, same deterministic weights
@@ -278,6 +280,31 @@ def gold_voxelize(R):
     print("voxelize: R", len(coord), "M", len(ui))
 
 
+def gold_spunet(R):
+    import json
+    from oracle import gridsample as G
+    m = R.SpUNetBase(in_channels=4, num_classes=13).eval()
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    m.load_state_dict(W, strict=False)
+    with open(os.path.join(HERE, "param_shapes_spunet.json"), "w") as fh:
+        json.dump({k: list(v) for k, v in shapes.items() if not k.endswith("num_batches_tracked")}, fh, indent=0)
+    cs, fs, gs_, counts = [], [], [], []
+    for seed, scale in ((91, 0.8), (92, 0.5)):
+        coord, feat = synth.pig_scan(6000, scale=scale, seed=seed)
+        r = G.grid_sample(coord, 0.02)
+        iu = r["idx_unique"]
+        cs.append(coord[iu]); fs.append(feat[iu]); gs_.append(r["grid_coord"][iu]); counts.append(len(iu))
+    coord, feat, grid = np.concatenate(cs), np.concatenate(fs), np.concatenate(gs_)
+    offset = np.cumsum(counts)
+    with torch.no_grad():
+        out = m(dict(coord=torch.from_numpy(coord), grid_coord=torch.from_numpy(grid), feat=torch.from_numpy(feat),
+                     offset=torch.from_numpy(offset)))
+    print("spunet: N", len(coord), "logits", tuple(out.shape), "abs mean", out.abs().mean().item())
+    np.savez_compressed(os.path.join(HERE, "spunet.npz"), coord=coord, feat=feat, grid_coord=grid, offset=offset,
+                        logits=out.numpy())
+
+
 if __name__ == "__main__":
     R = ref_loader.load()
     gold_serialization(R)
@@ -288,6 +315,7 @@ if __name__ == "__main__":
     gold_heads(R)
     gold_train(R)
     gold_voxelize(R)
+    gold_spunet(R)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -130,6 +130,74 @@ def _install_third_party_standins():
                     nbr = x.indice_dict[key]
                 return x.replace_feature(O.subm_conv(x.features, nbr, self.weight, self.bias))
 
+        class SparseConv3d(SparseModule):
+            """k = 2, s = 2 only (SpUNet's down-sampling, spconv_unet_v1m1_base.py:137-151) over oracle/spunet.py."""
+
+            def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1,
+                         bias=True, indice_key=None, **kw):
+                super().__init__()
+                assert kernel_size == 2 and stride == 2 and padding == 0
+                self.indice_key = indice_key
+                self.weight = nn.Parameter(torch.empty(out_channels, 2, 2, 2, in_channels))
+                self.bias = nn.Parameter(torch.zeros(out_channels)) if bias else None
+                nn.init.kaiming_uniform_(self.weight, a=5 ** 0.5)
+
+            def forward(self, x):
+                from oracle import spunet as U
+                out_idx, cluster, koff = U.down_map(x.indices)
+                x.indice_dict[("pairs", self.indice_key)] = (x.indices, cluster, koff, x.spatial_shape)
+                f = U.sparse_conv_k2s2(x.features, cluster, koff, out_idx.shape[0], self.weight)
+                if self.bias is not None:
+                    f = f + self.bias
+                # same indice_dict object: the inverse conv finds the pairs under its indice_key like in spconv
+                return SparseConvTensor(f, out_idx, [(d + 1) // 2 for d in x.spatial_shape], x.batch_size,
+                                        x.indice_dict)
+
+        class SparseInverseConv3d(SparseModule):
+            def __init__(self, in_channels, out_channels, kernel_size, indice_key=None, bias=True, **kw):
+                super().__init__()
+                assert kernel_size == 2
+                self.indice_key = indice_key
+                self.weight = nn.Parameter(torch.empty(out_channels, 2, 2, 2, in_channels))
+                self.bias = nn.Parameter(torch.zeros(out_channels)) if bias else None
+                nn.init.kaiming_uniform_(self.weight, a=5 ** 0.5)
+
+            def forward(self, x):
+                from oracle import spunet as U
+                fine_idx, cluster, koff, shape = x.indice_dict[("pairs", self.indice_key)]
+                f = U.sparse_inverse_conv_k2(x.features, cluster, koff, self.weight)
+                if self.bias is not None:
+                    f = f + self.bias
+                return SparseConvTensor(f, fine_idx, shape, x.batch_size, x.indice_dict)
+
+        class SparseSequential(SparseModule):
+            def __init__(self, *args, **kwargs):
+                super().__init__()
+                if len(args) == 1 and isinstance(args[0], dict):
+                    for k, m in args[0].items():
+                        self.add_module(k, m)
+                else:
+                    for i, m in enumerate(args):
+                        self.add_module(str(i), m)
+                for k, m in kwargs.items():
+                    self.add_module(k, m)
+
+            def forward(self, x):
+                for m in self._modules.values():
+                    if isinstance(m, SparseModule):
+                        x = m(x)
+                    elif isinstance(x, SparseConvTensor):
+                        if x.indices.shape[0] != 0:
+                            x = x.replace_feature(m(x.features))
+                    else:
+                        x = m(x)
+                return x
+
+        class Identity(nn.Identity):
+            pass
+
+        spt.SparseConv3d, spt.SparseInverseConv3d = SparseConv3d, SparseInverseConv3d
+        spt.SparseSequential, spt.Identity = SparseSequential, Identity
         spm.is_spconv_module = lambda m: isinstance(m, SparseModule)
         spm.SparseModule = SparseModule
         spt.SparseModule, spt.SparseConvTensor, spt.SubMConv3d, spt.modules = SparseModule, SparseConvTensor, SubMConv3d, spm
@@ -178,6 +246,20 @@ def load():
             for nm in names:
                 setattr(stub, nm, None)
             sys.modules[absent] = stub
+    # SpUNet-v1m1 imports torch_geometric.utils.scatter (enc_mode only) and timm's trunc_normal_
+    if "torch_geometric" not in sys.modules:
+        tg, tgu = types.ModuleType("torch_geometric"), types.ModuleType("torch_geometric.utils")
+        tgu.scatter = None
+        tg.utils = tgu
+        sys.modules["torch_geometric"], sys.modules["torch_geometric.utils"] = tg, tgu
+    if not hasattr(sys.modules["timm.layers"], "trunc_normal_"):
+        sys.modules["timm.layers"].trunc_normal_ = torch.nn.init.trunc_normal_
+    try:
+        _stub_package("pointcept.models.sparse_unet", os.path.join(pc, "models", "sparse_unet"))
+        spunet = importlib.import_module("pointcept.models.sparse_unet.spconv_unet_v1m1_base")
+    except Exception as e:                                 # noqa: BLE001
+        print("SpUNet-v1m1 not importable:", repr(e))
+        spunet = None
     try:
         seg = importlib.import_module("pointcept.models.default")
     except Exception as e:                                 # noqa: BLE001 -- report, the other fixtures do not need it
@@ -195,5 +277,6 @@ def load():
     _loaded.update(ptv3=ptv3, PointTransformerV3=ptv3.PointTransformerV3, SerializedAttention=ptv3.SerializedAttention,
                    OffsetKeypointPTv3=okp.OffsetKeypointPTv3, KeypointPTv3=kp.KeypointPTv3,
                    DefaultSegmentorV2=getattr(seg, "DefaultSegmentorV2", None),
+                   SpUNetBase=getattr(spunet, "SpUNetBase", None),
                    Point=structure.Point, encode=ser.encode, GridSample=tr.GridSample, builder=builder)
     return types.SimpleNamespace(**_loaded)

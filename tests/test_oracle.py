@@ -214,3 +214,26 @@ def test_voxelize_first_vs_reference(golden):
     assert np.array_equal(idx, g["idx_sorted"]) and np.array_equal(grid, g["grid"])
     idx, _ = G.voxelize_first(g["coord"], 0.02, keep_order=False)
     assert np.array_equal(idx, g["idx_lex"])
+
+
+def test_spunet_forward_vs_reference(golden):
+    """oracle/spunet.py (functional) against the reference SpUNetBase class run over the restated
+    spconv ops (tests/golden/make_golden.py::gold_spunet): module wiring, state_dict names, skip order."""
+    import json, os
+    from conftest import GOLDEN
+    from oracle import spunet as U
+    g = golden("spunet")
+    with open(os.path.join(GOLDEN, "param_shapes_spunet.json")) as f:
+        shapes = json.load(f)
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    out = U.spunet_forward(W, g["grid_coord"], g["feat"], g["offset"])
+    ref = torch.from_numpy(g["logits"])
+    assert out.shape == ref.shape and ((out - ref).norm() / ref.norm()).item() < 1e-5
+    # strided conv map: every input site belongs to exactly one output site, offsets in 0..7, inverse conv of a
+    # one-hot weight returns the coarse feature
+    off = torch.from_numpy(g["offset"])
+    batch = torch.repeat_interleave(torch.arange(len(off)), torch.diff(off, prepend=torch.zeros(1, dtype=off.dtype)))
+    idx = torch.cat([batch[:, None], torch.from_numpy(g["grid_coord"])], 1)
+    out_idx, cluster, koff = U.down_map(idx)
+    assert torch.equal(out_idx[cluster].long()[:, 1:], idx[:, 1:] >> 1) and int(koff.min()) >= 0 and int(koff.max()) <= 7
+    assert torch.unique(torch.stack([cluster, koff], 1), dim=0).shape[0] == idx.shape[0]
