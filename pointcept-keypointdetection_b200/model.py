@@ -64,6 +64,14 @@ class SparseModule(nn.Module):
     """spconv.pytorch.modules.SparseModule stand-in (modules.py:84 tests isinstance)."""
 
 
+def pad_out_channels(c):
+    """Smallest output width the tcgen05 conv kernel tiles (32 ... 512) that holds c channels."""
+    for p in (32, 64, 128, 256, 512):
+        if c <= p:
+            return p
+    return c
+
+
 def is_spconv_module(m):
     return isinstance(m, SparseModule)
 
@@ -147,7 +155,9 @@ class SubMConv3d(SparseModule):
                 x.indice_dict[key] = nbr
         return nbr
 
-    def _weights(self, dtype, scale=None, shift=None):
+    def _weights(self, dtype, scale=None, shift=None, cin_p=None, cout_p=None):
+        cin_p, cout_p = cin_p or self.in_channels, cout_p or self.out_channels
+
         def build():
             w = self.weight.float()
             b = self.bias.float() if self.bias is not None else None
@@ -155,21 +165,30 @@ class SubMConv3d(SparseModule):
                 w = w * scale.view(-1, 1, 1, 1, 1)
                 b = shift if b is None else b * scale + shift
             k3 = self.kernel_size ** 3
-            w = w.reshape(self.out_channels, k3, self.in_channels).permute(1, 0, 2).contiguous().to(dtype)
-            return w, (b.contiguous() if b is not None else None)
-        return _cached(self, ("w", dtype, scale is not None), [self.weight, self.bias, scale, shift], build)
+            w = w.reshape(self.out_channels, k3, self.in_channels).permute(1, 0, 2)
+            if (cin_p, cout_p) != (self.in_channels, self.out_channels):     # zero rows / columns (pad_channels)
+                w = F.pad(w, (0, cin_p - self.in_channels, 0, cout_p - self.out_channels))
+                if b is not None:
+                    b = F.pad(b, (0, cout_p - self.out_channels))
+            return w.contiguous().to(dtype), (b.contiguous() if b is not None else None)
+        return _cached(self, ("w", dtype, scale is not None, cin_p, cout_p), [self.weight, self.bias, scale, shift],
+                       build)
+
+    pad_channels = False     # SpUNet sets this: 96-channel levels run as 128-wide tensors whose last columns are zero
 
     def conv(self, features, x, scale=None, shift=None, algo=0):
-        w, b = self._weights(features.dtype, scale, shift)
         k3 = self.kernel_size ** 3
+        cin_p, cout_p = self.in_channels, self.out_channels
+        if self.pad_channels and features.dtype == torch.bfloat16:
+            cin_p, cout_p = features.shape[1], pad_out_channels(self.out_channels)
+        w, b = self._weights(features.dtype, scale, shift, cin_p, cout_p)
         if k3 == 1:      # 1x1x1 SubM conv = a plain per-site GEMM: library call (cuBLAS), no gather
             return F.linear(features, w[0], b.to(features.dtype) if b is not None else None)
-        if (features.dtype == torch.bfloat16 and algo != 1
-                and ops.subm_conv_tc_supported(self.in_channels, self.out_channels, k3)):
+        if features.dtype == torch.bfloat16 and algo != 1 and ops.subm_conv_tc_supported(cin_p, cout_p, k3):
             # tcgen05 path: the K-blocked / swizzled weight image is built once per parameter version
-            packed = _cached(self, ("packed", scale is not None), [self.weight, self.bias, scale, shift],
-                             lambda: ops.subm_pack_weight(w))
-            return ops.subm_conv_packed(features, packed, b, self.neighbor_map(x), self.out_channels)
+            packed = _cached(self, ("packed", scale is not None, cin_p, cout_p),
+                             [self.weight, self.bias, scale, shift], lambda: ops.subm_pack_weight(w))
+            return ops.subm_conv_packed(features, packed, b, self.neighbor_map(x), cout_p)
         return ops.subm_conv(features, w, b, self.neighbor_map(x), algo=algo)
 
     def forward(self, x):

@@ -19,7 +19,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .model import SparseModule, SubMConv3d, _bn_scale_shift, _cached
+from .model import SparseModule, SubMConv3d, _bn_scale_shift, _cached, pad_out_channels
 from .structure import SparseConvTensor
 
 
@@ -66,23 +66,32 @@ class _PairConv(SparseModule):
         self.bias = nn.Parameter(torch.zeros(out_channels)) if bias else None
         nn.init.kaiming_uniform_(self.weight, a=5 ** 0.5)
 
-    def _weights(self, dtype, scale, shift):
+    def _weights(self, dtype, scale, shift, cin_p, cout_p):
         def build():
             w = self.weight.float()
             b = self.bias.float() if self.bias is not None else None
             if scale is not None:
                 w = w * scale.view(-1, 1, 1, 1, 1)
                 b = shift if b is None else b * scale + shift
-            w = w.reshape(self.out_channels, 8, self.in_channels).permute(1, 0, 2).contiguous().to(dtype)
-            return w, (b.contiguous() if b is not None else None)
-        return _cached(self, ("w", dtype, scale is not None), [self.weight, self.bias, scale, shift], build)
+            w = w.reshape(self.out_channels, 8, self.in_channels).permute(1, 0, 2)
+            if (cin_p, cout_p) != (self.in_channels, self.out_channels):
+                w = torch.nn.functional.pad(w, (0, cin_p - self.in_channels, 0, cout_p - self.out_channels))
+                if b is not None:
+                    b = torch.nn.functional.pad(b, (0, cout_p - self.out_channels))
+            return w.contiguous().to(dtype), (b.contiguous() if b is not None else None)
+        return _cached(self, ("w", dtype, scale is not None, cin_p, cout_p), [self.weight, self.bias, scale, shift],
+                       build)
 
     def gemm(self, feat, nbr, scale=None, shift=None):
-        w, b = self._weights(feat.dtype, scale, shift)
-        if feat.dtype == torch.bfloat16 and ops.subm_conv_tc_supported(self.in_channels, self.out_channels, 8):
-            packed = _cached(self, ("packed", scale is not None), [self.weight, self.bias, scale, shift],
-                             lambda: ops.subm_pack_weight(w))
-            return ops.subm_conv_packed(feat, packed, b, nbr, self.out_channels)
+        """bf16: channel counts the tcgen05 kernel does not tile (96) run zero-padded to the next width it does."""
+        cin_p, cout_p = self.in_channels, self.out_channels
+        if feat.dtype == torch.bfloat16:
+            cin_p, cout_p = feat.shape[1], pad_out_channels(self.out_channels)
+        w, b = self._weights(feat.dtype, scale, shift, cin_p, cout_p)
+        if feat.dtype == torch.bfloat16 and ops.subm_conv_tc_supported(cin_p, cout_p, 8):
+            packed = _cached(self, ("packed", scale is not None, cin_p, cout_p),
+                             [self.weight, self.bias, scale, shift], lambda: ops.subm_pack_weight(w))
+            return ops.subm_conv_packed(feat, packed, b, nbr, cout_p)
         return ops.subm_conv(feat, w, b, nbr)
 
 
@@ -199,6 +208,9 @@ class SpUNetBase(nn.Module):
             dec_channels = channels[len(channels) - s - 2]
         self.final = SubMConv3d(channels[-1], num_classes, kernel_size=1, padding=1, bias=True) \
             if num_classes > 0 else nn.Identity()
+        for mod in self.modules():
+            if isinstance(mod, SubMConv3d):
+                mod.pad_channels = True
 
     @torch.no_grad()
     def forward(self, input_dict):
@@ -224,8 +236,9 @@ class SpUNetBase(nn.Module):
         for s in reversed(range(self.num_stages)):
             x = self.up[s][0].conv(x, *_fold(self.up[s][1]))
             skip = skips.pop(-1)
-            x = x.replace_feature(torch.cat((torch.relu_(x.features), skip.features), dim=1))
+            c_up, c_skip = self.up[s][0].out_channels, self.down[s][0].in_channels     # logical widths (no padding)
+            x = x.replace_feature(torch.cat((torch.relu_(x.features)[:, :c_up], skip.features[:, :c_skip]), dim=1))
             x = self.dec[s](x)
         if isinstance(self.final, nn.Identity):
-            return x.features
-        return self.final.conv(x.features, x).float()
+            return x.features[:, :self.channels[-1]]
+        return self.final.conv(x.features, x)[:, :self.num_classes].float()
