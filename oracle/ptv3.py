@@ -11,7 +11,8 @@ checkpoint (or the deterministic test weights) drives both sides:
   OffsetKeypointPTv3.forward   offset_keypoint_ptv3.py:37-107
   KeypointPTv3.forward         keypoint_ptv3.py:37-98
   DefaultSegmentorV2.forward   default.py:63-95
-Eval mode only (BatchNorm running stats, no dropout / drop-path).  Attention
+Eval mode by default (BatchNorm running stats, no dropout / drop-path); BN_TRAIN / offset_keypoint_grads switch to
+batch statistics and run torch.autograd through the same functions for the training-step tests.  Attention
 uses flash window semantics (fixed K, short scenes = one short window), which
 equals the reference's enable_flash=False branch when run one scene per
 forward.  Test infrastructure only (see oracle/__init__.py).
