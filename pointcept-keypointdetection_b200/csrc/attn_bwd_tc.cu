@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
     float scale, float sl2, int kpad_max, float* __restrict__ dqkv, const float* __restrict__ lse_g) {
   constexpr int kThreads = kWarps * 32;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int w = blockIdx.x, head = blockIdx.y;
+  const int head = (int)(blockIdx.x % (unsigned)h), w = (int)(blockIdx.x / (unsigned)h);   // heads adjacent: L2 line reuse
   if (w >= n_windows[0]) return;
   const int64_t q0 = windows[4 * w + 0], ql = windows[4 * w + 1], k0 = windows[4 * w + 2], kl = windows[4 * w + 3];
   if (ql <= 0 || kl <= 0) return;
@@ -339,7 +339,8 @@ int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const
       return PTV3_ELAUNCH;
     configured = smem;
   }
-  dim3 grid((unsigned)n_windows_max, (unsigned)h);
+  if ((int64_t)n_windows_max * h > 2147483647LL) return PTV3_EINVAL;
+  dim3 grid((unsigned)(n_windows_max * h));
   // one CTA per SM (140 KB of staged operands): 16 warps hide the ldmatrix / MUFU latency better than 8
   if (g_attn_bwd_warps == 8)
     attn_bwd_mma_kernel<8><<<grid, 256, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,

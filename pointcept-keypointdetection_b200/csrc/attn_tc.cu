@@ -64,7 +64,9 @@ __global__ void __launch_bounds__(kThreads, 3) attn_window_mma_kernel(
     const int64_t* __restrict__ n_windows, int h, float scale_log2, int kpad_max, __nv_bfloat16* __restrict__ out,
     float* __restrict__ lse) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int w = blockIdx.x, head = blockIdx.y;
+  // heads of one window are neighbours in launch order: their 32-byte K / V / Q slices of the same 128-byte line
+  // are fetched while the line is still in L2 (with the window index fastest, ncu showed 3.4 x the algorithmic bytes)
+  const int head = (int)(blockIdx.x % (unsigned)h), w = (int)(blockIdx.x / (unsigned)h);
   if (w >= n_windows[0]) return;
   const int64_t q0 = windows[4 * w + 0], ql = windows[4 * w + 1], k0 = windows[4 * w + 2], kl = windows[4 * w + 3];
   if (ql <= 0 || kl <= 0) return;
@@ -252,7 +254,8 @@ int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
       if (t < best - 1e-9) { best = t; split = s; }
     }
   }
-  dim3 grid((unsigned)n_windows_max, (unsigned)h, (unsigned)split);
+  if ((int64_t)n_windows_max * h > 2147483647LL) return PTV3_EINVAL;
+  dim3 grid((unsigned)(n_windows_max * h), 1u, (unsigned)split);
   if (lse)
     attn_window_mma_kernel<true><<<grid, kThreads, smem, st>>>(qkv, order, windows, n_windows, h,
                                                                scale * 1.4426950408889634f, kpad, out, lse);
