@@ -276,6 +276,24 @@ def run_ours(args):
         if top == "attn_window":   # head_dim 16: the exp pipe, not the tensor pipe, bounds this kernel
             roof["exp_per_s"] = round(e["units"] / (e["ms"] * 1e-3) / 1e12, 3)
             roof["exp_peak_mufu_per_s"] = round(16 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 3)
+    # ---- GridSample leg (BASELINE metric: "GridSample reported separately in raw points/s"), raw scans resident ----
+    gs_leg = None
+    if rank == 0:
+        raw_dev = [torch.from_numpy(c).to(device) for c, _ in raw]
+        for c in raw_dev[:2]:
+            ops.gridsample(c, GRID, "fnv")
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for c in raw_dev:
+            ops.gridsample(c, GRID, "fnv")
+        b.record()
+        torch.cuda.synchronize()
+        gs_ms = a.elapsed_time(b)
+        n_raw = int(sum(c.shape[0] for c in raw_dev))
+        gs_leg = dict(raw_points_per_s=round(n_raw / (gs_ms * 1e-3), 1), ms_per_batch=round(gs_ms, 3), raw_points=n_raw,
+                      note="ptv3_gridsample (floor, FNV key, radix sort, unique, count, inverse, select) per scene, "
+                           "one host read of the voxel count per scene")
+        del raw_dev
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:      # reported at N = 1 only
         cpu = cpu_baseline(args, seconds=20.0)
@@ -292,7 +310,8 @@ def run_ours(args):
                     e2e=dict(value=round(e2e, 1), unit=UNIT, h2d_bytes_per_step=h2d_bytes,
                              d2h_bytes_per_step=d2h_bytes, ms_per_step=round(e2e_wall / args.steps, 3),
                              result="per-scene keypoints (scenes,6,3) fp32 after on-device aggregation"),
-                    gpu_launches=int(launches), clocks=clocks, roofline=roof, cpu_baseline=cpu, op_ms=ops_ms)
+                    gpu_launches=int(launches), clocks=clocks, roofline=roof, cpu_baseline=cpu, op_ms=ops_ms,
+                    gridsample=gs_leg)
         print(json.dumps(line))
     if world > 1:
         import torch.distributed as dist

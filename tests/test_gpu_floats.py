@@ -452,3 +452,49 @@ def test_segmentor_head_golden(golden, dtype, tol):
     top2 = ref.topk(2, dim=1).values
     clear = (top2[:, 0] - top2[:, 1]) > 4 * tol * ref.abs().max()
     assert clear.any() and torch.equal(logits.argmax(1)[clear], ref.argmax(1)[clear])
+
+
+def test_serving_paths_on_device(golden):
+    """collate, the Qt server's detect path (normalise -> first point per voxel -> model -> vote ->
+    de-normalise) and test-mode fragment voting, each against the same steps done with the oracle pieces."""
+    from ptv3_b200 import infer, model as M, synth, ops
+    m = _model(torch.float32)
+    for mod in m.modules():
+        if hasattr(mod, "shuffle_orders"):
+            mod.shuffle_orders = False
+    coord, feat = synth.pig_scan(20000, scale=350.0, seed=77)          # a scan in millimetres
+    coord = coord + np.array([1200.0, -300.0, 80.0], dtype=np.float32)
+    kp = infer.detect_keypoints(m, torch.from_numpy(coord).cuda(), torch.from_numpy(feat).cuda(), 0.02, mode="argmax")
+    # the same steps with the oracle's voxeliser / aggregation around OUR model's prediction.  The normalised
+    # coordinates are taken from the device function (a 1e-7 difference in the fp32 centroid would move points across
+    # voxel borders and, with random weights, the arg-max vote to another point)
+    from ptv3_b200 import transform
+    cn_t, cen_t, scale_t = transform.normalize_unit_sphere(torch.from_numpy(coord).cuda())
+    cn = cn_t.cpu().numpy()
+    idx, grid = G.voxelize_first(cn, 0.02, keep_order=True)
+    pred = m(dict(coord=torch.from_numpy(cn[idx]).cuda(), grid_coord=torch.from_numpy(grid).cuda(),
+                  feat=torch.from_numpy(feat[idx]).cuda(), offset=torch.tensor([len(idx)]).cuda()))["pred"].cpu()
+    ref = P.aggregate_keypoints(torch.from_numpy(cn[idx]), pred, mode="argmax") * float(scale_t) + cen_t.cpu()
+    assert abs(float(scale_t) - np.linalg.norm(coord - coord.mean(0), axis=1).max()) < 0.05
+    assert kp.shape == (6, 3) and (kp.cpu() - ref).abs().max().item() < 0.05      # millimetres
+    # collate: two scenes -> offsets, concatenation
+    a = dict(coord=torch.randn(5, 3).cuda(), feat=torch.randn(5, 4).cuda(), grid_size=0.02)
+    b = dict(coord=torch.randn(7, 3).cuda(), feat=torch.randn(7, 4).cuda(), grid_size=0.02)
+    c = infer.collate([a, b])
+    assert c["offset"].tolist() == [5, 12] and c["coord"].shape == (12, 3) and c["grid_size"] == 0.02
+    # fragment voting with a segmentor: every raw point gets exactly one vote per fragment it belongs to
+    seg = M.DefaultSegmentorV2(num_classes=5, backbone_out_channels=64,
+                               backbone=dict(P.BASE_CFG, in_channels=4, compute_dtype=torch.float32,
+                                             shuffle_orders=False)).eval().cuda()
+    c2, f2 = synth.pig_scan(12000, scale=0.5, seed=78)
+    data = dict(coord=torch.from_numpy(c2).cuda(), feat=torch.from_numpy(f2).cuda())
+    pred, prob = infer.segment_with_fragments(seg, data, 0.02, 5)
+    assert pred.shape == (12000,) and prob.shape == (12000, 5)
+    gs = ops.gridsample(data["coord"], 0.02, "fnv")
+    votes = prob.sum(1)                                           # = number of fragments that contained the point
+    cnt = gs["count"][gs["inverse"]]                              # population of the point's voxel
+    kmax = int(gs["count"].max())
+    # fragment i takes point (i % count) of every voxel: a point at position p of a voxel with c points is picked
+    # by the fragments i with i % c == p -> floor((kmax - 1 - p) / c) + 1 votes; summed over a voxel that is kmax
+    assert torch.allclose(votes.sum(), torch.tensor(float(kmax * gs["n_voxels"]), device=votes.device), rtol=1e-5)
+    assert float(votes.min()) >= 1.0 - 1e-4 and bool((votes <= torch.ceil(kmax / cnt.float()) + 1e-4).all())
