@@ -312,3 +312,85 @@ def test_training_loss_decreases():
         opt.step()
         losses.append(out["loss"].item())
     assert all(np.isfinite(losses)) and losses[-1] < losses[0], losses
+
+
+def test_training_other_heads_vs_oracle(golden):
+    """KeypointPTv3 (MSE on per-scene keypoints, keypoint_ptv3.py:52-63) and DefaultSegmentorV2 (cross entropy on
+    per-point logits, default.py:86-88) in train() mode, fp32: loss and gradients against torch autograd through
+    the oracle (BatchNorm batch statistics, dropout off, drop_path 0)."""
+    import torch.nn.functional as F
+    from ptv3_b200 import model as M, synth
+    g = golden("heads")
+    n = len(g["coord"])
+    from conftest import GOLDEN
+    with open(os.path.join(GOLDEN, "param_shapes_heads.json")) as f:
+        shapes = json.load(f)
+    torch.manual_seed(300)
+    perms = [torch.randperm(4).numpy() for _ in range(5)]
+    batch = lambda feat: dict(coord=torch.from_numpy(g["coord"]).cuda(), grid_coord=torch.from_numpy(g["grid_coord"]).cuda(),
+                              feat=torch.from_numpy(feat).cuda(), offset=torch.tensor([n]).cuda(), grid_size=0.02)
+
+    def oracle(W, feat, cfg, loss_fn):
+        Wg = {k: (v.clone().requires_grad_(True) if "running_" not in k else v) for k, v in W.items()}
+        P.BN_TRAIN = True
+        try:
+            with torch.enable_grad():
+                pt = P.backbone_forward.__wrapped__(Wg, g["coord"], g["grid_coord"], feat, [n], cfg=cfg, perms=list(perms))
+                loss = loss_fn(Wg, pt)
+                loss.backward()
+        finally:
+            P.BN_TRAIN = False
+        return loss.detach(), {k: v.grad for k, v in Wg.items() if torch.is_tensor(v) and v.requires_grad}
+
+    # ---- KeypointPTv3 ----
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes["keypoint"], seed=0).items()}
+    # two scenes (the head's BatchNorm1d needs more than one row in train()): the golden scene and a copy with
+    # negated features
+    target = torch.randn(2, 6, 3, generator=torch.Generator().manual_seed(1)) * 0.3
+    m = M.KeypointPTv3(backbone_conf=dict(P.BASE_CFG, drop_path=0.0, compute_dtype=torch.float32))
+    m.load_state_dict(W, strict=False)
+    m = m.cuda().train()
+    m.reg_head[3].p = 0.0                                               # nn.Dropout(0.3) is random: off for parity
+    c2, g2 = np.concatenate([g["coord"]] * 2), np.concatenate([g["grid_coord"]] * 2)
+    f2 = np.concatenate([g["feat4"], -g["feat4"]])
+    torch.manual_seed(300)
+    out = m(dict(coord=torch.from_numpy(c2).cuda(), grid_coord=torch.from_numpy(g2).cuda(),
+                 feat=torch.from_numpy(f2).cuda(), offset=torch.tensor([n, 2 * n]).cuda(), grid_size=0.02,
+                 target=target.cuda()))
+    out["loss"].backward()
+
+    def kp_oracle():
+        Wg = {k: (v.clone().requires_grad_(True) if "running_" not in k else v) for k, v in W.items()}
+        P.BN_TRAIN = True
+        try:
+            with torch.enable_grad():
+                pt = P.backbone_forward.__wrapped__(Wg, c2, g2, f2, [n, 2 * n], perms=list(perms))
+                loss = F.mse_loss(P.keypoint_head.__wrapped__(Wg, pt.feat, pt.batch), target)
+                loss.backward()
+        finally:
+            P.BN_TRAIN = False
+        return loss.detach(), {k: v.grad for k, v in Wg.items() if torch.is_tensor(v) and v.requires_grad}
+    ref_loss, ref = kp_oracle()
+    # BatchNorm over the TWO pooled rows of this batch turns 1e-6 feature differences into 1e-5 ones: fp32 bound 1e-4
+    assert abs(out["loss"].item() - ref_loss.item()) < 1e-4 * abs(ref_loss.item())
+    params = dict(m.named_parameters())
+    for k in ("reg_head.6.weight", "reg_head.0.weight", "backbone.dec.dec0.block1.attn.qkv.weight",
+              "backbone.enc.enc0.block0.cpe.0.weight"):
+        assert rel_l2(params[k].grad, ref[k]) < 1e-3, k
+    # ---- DefaultSegmentorV2 (C_in = 6, 20 classes) ----
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes["segmentor"], seed=0).items()}
+    labels = torch.randint(0, 20, (n,), generator=torch.Generator().manual_seed(2))
+    cfg6 = dict(P.BASE_CFG, in_channels=6)
+    m = M.DefaultSegmentorV2(num_classes=20, backbone_out_channels=64,
+                             backbone=dict(cfg6, drop_path=0.0, compute_dtype=torch.float32))
+    m.load_state_dict(W, strict=False)
+    m = m.cuda().train()
+    torch.manual_seed(300)
+    out = m(dict(batch(g["feat6"]), segment=labels.cuda()))
+    out["loss"].backward()
+    ref_loss, ref = oracle(W, g["feat6"], cfg6, lambda Wg, pt: F.cross_entropy(P.seg_head.__wrapped__(Wg, pt.feat),
+                                                                               labels, ignore_index=-1))
+    assert abs(out["loss"].item() - ref_loss.item()) < 1e-5 * abs(ref_loss.item())
+    params = dict(m.named_parameters())
+    for k in ("seg_head.weight", "backbone.embedding.stem.conv.weight", "backbone.enc.enc3.block2.mlp.0.fc1.weight"):
+        assert rel_l2(params[k].grad, ref[k]) < 1e-3, k
