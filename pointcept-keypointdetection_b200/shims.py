@@ -3,7 +3,8 @@
 `install()` registers, under the names the reference imports, thin modules whose
 bodies are our kernels:
 
-    spconv.pytorch            SubMConv3d, SparseConvTensor, SparseModule, SparseSequential
+    spconv.pytorch            SubMConv3d, SparseConv3d (k2,s2), SparseInverseConv3d (k2), SparseConvTensor,
+                              SparseModule, SparseSequential, Identity
     spconv.pytorch.modules    is_spconv_module
     torch_scatter             segment_csr, scatter_mean
     flash_attn                flash_attn_varlen_qkvpacked_func
@@ -107,10 +108,13 @@ def install(force=False):
     """Register the stand-in modules.  Returns the list of names that were installed."""
     done = []
     if force or _absent("spconv"):
+        from . import spunet        # strided / inverse convs of SpUNet-v1m1 (sparse_unet/spconv_unet_v1m1_base.py:23)
         mods = _module("spconv.pytorch.modules", is_spconv_module=is_spconv_module, SparseModule=SparseModule,
                        SparseSequential=SparseSequential)
         pt = _module("spconv.pytorch", SubMConv3d=SubMConv3d, SparseConvTensor=SparseConvTensor,
-                     SparseModule=SparseModule, SparseSequential=SparseSequential, modules=mods)
+                     SparseModule=SparseModule, SparseSequential=spunet.SparseSequential, modules=mods,
+                     SparseConv3d=spunet.SparseConv3d, SparseInverseConv3d=spunet.SparseInverseConv3d,
+                     Identity=nn.Identity)
         root = _module("spconv", pytorch=pt, __path__=[])
         pt.__path__ = []
         sys.modules.update({"spconv": root, "spconv.pytorch": pt, "spconv.pytorch.modules": mods})

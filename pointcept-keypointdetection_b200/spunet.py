@@ -95,6 +95,18 @@ class _PairConv(SparseModule):
         return ops.subm_conv(feat, w, b, nbr)
 
 
+def serialize_sites(indices):
+    """z-order code + order of the sites of a SparseConvTensor built by somebody else (the unmodified reference's
+    SpUNetBase.forward, :240-255): what SparseConv3d needs to find its coarse sites without a hash table."""
+    batch = indices[:, 0].long().contiguous()
+    grid = indices[:, 1:].long().contiguous()
+    depth = max(int(int(ops.grid_max(grid).max().item()) + 1).bit_length(), 1)
+    n_scenes = int(batch[-1].item()) + 1 if batch.numel() else 1
+    code = ops.encode_orders(grid, batch, depth, ["z"])
+    order, _ = ops.argsort_rows(code, key_bits=depth * 3 + max(1, (n_scenes - 1).bit_length()), want_inverse=False)
+    return code, order, grid, batch
+
+
 class SparseConv3d(_PairConv):
     def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1, bias=True,
                  indice_key=None):
@@ -104,6 +116,8 @@ class SparseConv3d(_PairConv):
 
     def conv(self, x, scale=None, shift=None):
         """x must carry the z-order serialization of its sites in x.indice_dict['_serial'] (SpUNetBase.forward)."""
+        if "_serial" not in x.indice_dict:
+            x.indice_dict["_serial"] = serialize_sites(x.indices)
         code, order, grid, batch = x.indice_dict["_serial"]
         pf = ops.pool_front(code, order, 1)
         new_grid, new_batch, indices4 = ops.pool_gather_ints(grid, batch, pf["head"], 1)

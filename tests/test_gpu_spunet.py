@@ -55,6 +55,10 @@ def test_strided_and_inverse_conv_vs_oracle(golden):
     x.indice_dict["_serial"] = (p.serialized_code, p.serialized_order, p.grid_coord.long(), p.batch)
     c = down(x)
     u = up(c)
+    # a tensor built by somebody else (no serialization attached, like the reference's SpUNetBase.forward builds it)
+    from ptv3_b200.structure import SparseConvTensor
+    c2 = down(SparseConvTensor(feat.cuda(), x.indices, x.spatial_shape, x.batch_size))
+    assert torch.equal(c2.indices, c.indices) and torch.equal(c2.features, c.features)
     # coarse rows come in z-order, the oracle's in (b,x,y,z) order: compare through the site keys
     key = lambda t: (t[:, 0].long() << 48) | (t[:, 1].long() << 32) | (t[:, 2].long() << 16) | t[:, 3].long()
     ko, kr = key(c.indices.cpu()), key(out_idx)
