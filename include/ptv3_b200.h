@@ -169,6 +169,14 @@ int ptv3_subm_conv(const void* in, const void* weight, const float* bias, const 
                    int c_out, int k3, int dtype, int algo, void* out, void* workspace, size_t workspace_bytes,
                    void* stream);
 
+/* Stem SubMConv3d (:499-511: k = 5, C_in = 4 -> 32, followed by BatchNorm + GELU) with the neighbour search fused
+ * into the convolution: no (n, k^3) table is materialised.  in (n,4) fp32, weight (k^3, 32, 4) fp32 (eval BatchNorm
+ * already folded in), bias fp32 (32) or NULL, act 0 none / 1 GELU (erf); out32 fp32 (n,32) and / or out16 bf16 (n,32).
+ * workspace: ptv3_subm_map_workspace(n) bytes (the hash table). */
+int ptv3_subm_stem_fused(const int32_t* indices, int64_t n, int ksize, const float* in, const float* weight,
+                         const float* bias, int act, float* out32, void* out16, void* workspace, size_t workspace_bytes,
+                         void* stream);
+
 /* bf16 tensor-core path with the weight packed once (eval: weights are constants).  `packed` is the
  * shared-memory image of the K-blocked, 128-byte-swizzled weight (ptv3_subm_pack_weight_bytes() bytes, 1024-byte
  * aligned); supported shapes: c_in == 32 or a multiple of 64 (<= 512), c_out in {32,64,128,256,512}, k3 <= 27. */

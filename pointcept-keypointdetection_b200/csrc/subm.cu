@@ -259,6 +259,89 @@ __global__ void __launch_bounds__(256) subm_conv_stem4_kernel(const T* __restric
   }
 }
 
+// Stem (k = 5, C_in = 4, C_out = 32, fp32) with the neighbour search inside: the 125-column table of the stem is used
+// by nothing else in inference, so writing it (583 MB at 1.17 M voxels) and reading it back is pure overhead.  A warp
+// owns a row: lanes probe the hash table for 4 offsets each, gather their 16-byte input rows, then the present
+// offsets are walked in the same order as subm_conv_stem4_kernel (bit-identical sums); lane = output channel.
+// Epilogue: + bias (folded BatchNorm), optional exact GELU, fp32 and / or bf16 copies.
+__global__ void __launch_bounds__(512, 2) subm_stem_fused_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                                              const float* __restrict__ bias,
+                                                              const int32_t* __restrict__ indices,
+                                                              const unsigned long long* __restrict__ keys,
+                                                              const int* __restrict__ vals, uint32_t mask, int64_t n,
+                                                              int ksize, int act, float* __restrict__ out32,
+                                                              __nv_bfloat16* __restrict__ out16) {
+  extern __shared__ float4 ws4[];  // [k3][32]
+  const int k3 = ksize * ksize * ksize, r = ksize / 2;
+  for (int idx = threadIdx.x; idx < k3 * 32; idx += blockDim.x) {
+    const int co = idx & 31, k = idx >> 5;
+    const float* p = w + ((int64_t)k * 32 + co) * 4;
+    ws4[idx] = make_float4(p[0], p[1], p[2], p[3]);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const float b = bias ? bias[lane] : 0.f;
+  // this lane's four kernel offsets
+  int dxs[4], dys[4], dzs[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int k = q * 32 + lane;
+    dzs[q] = k % ksize - r;
+    dys[q] = (k / ksize) % ksize - r;
+    dxs[q] = k / (ksize * ksize) - r;
+  }
+  for (; row < n; row += stride) {
+    const int4 s = reinterpret_cast<const int4*>(indices)[row];
+    // the four first probes are issued together (independent loads), collisions are resolved afterwards
+    int mine[4];
+    uint64_t key[4];
+    uint32_t slot[4];
+    unsigned long long cur[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int x = s.y + dxs[q], y = s.z + dys[q], z = s.w + dzs[q];
+      const bool ok = q * 32 + lane < k3 && x >= -kCoordBias && y >= -kCoordBias && z >= -kCoordBias;
+      key[q] = ok ? pack_site(s.x, x, y, z) : kEmptyKey;
+      slot[q] = hash_site(key[q]) & mask;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) cur[q] = key[q] != kEmptyKey ? keys[slot[q]] : (unsigned long long)kEmptyKey;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      while (cur[q] != key[q] && cur[q] != kEmptyKey) {
+        slot[q] = (slot[q] + 1) & mask;
+        cur[q] = keys[slot[q]];
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) mine[q] = (key[q] != kEmptyKey && cur[q] == key[q]) ? vals[slot[q]] : -1;
+    float4 x[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      x[q] = mine[q] >= 0 ? *reinterpret_cast<const float4*>(in + (int64_t)mine[q] * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t present = __ballot_sync(0xffffffffu, mine[q] >= 0);
+      while (present) {
+        const int j = __ffs(present) - 1;
+        present &= present - 1;
+        const float4 wv = ws4[(q * 32 + j) * 32 + lane];
+        acc0 = fmaf(__shfl_sync(0xffffffffu, x[q].x, j), wv.x, acc0);
+        acc1 = fmaf(__shfl_sync(0xffffffffu, x[q].y, j), wv.y, acc1);
+        acc0 = fmaf(__shfl_sync(0xffffffffu, x[q].z, j), wv.z, acc0);
+        acc1 = fmaf(__shfl_sync(0xffffffffu, x[q].w, j), wv.w, acc1);
+      }
+    }
+    float y = acc0 + acc1 + b;
+    if (act == 1) y = 0.5f * y * (1.f + erff(y * 0.70710678118654752f));
+    if (out32) out32[row * 32 + lane] = y;
+    if (out16) out16[row * 32 + lane] = __float2bfloat16_rn(y);
+  }
+}
+
 template <typename T>
 static int conv_cuda_core(const T* in, const T* w, const float* bias, const int32_t* nbr, int64_t n, int cin, int cout,
                           int k3, T* out, cudaStream_t st) {
@@ -327,6 +410,37 @@ int ptv3_subm_build_map(const int32_t* indices, int64_t n, int ksize, int32_t* n
   subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1);
   int64_t total = n * ksize * ksize * ksize;
   subm_lookup_kernel<<<grid_for(total, 256, 16), 256, 0, st>>>(indices, n, ksize, keys, vals, cap - 1, nbr);
+  return check_launch(2);
+}
+
+int ptv3_subm_stem_fused(const int32_t* indices, int64_t n, int ksize, const float* in, const float* weight,
+                         const float* bias, int act, float* out32, void* out16, void* workspace, size_t workspace_bytes,
+                         void* stream) {
+  if (n < 0 || ksize < 1 || ksize > 5 || (ksize & 1) == 0 || act < 0 || act > 1) return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!indices || !in || !weight || (!out32 && !out16) || n >= (1ll << 30)) return PTV3_EINVAL;
+  const int k3 = ksize * ksize * ksize;
+  uint32_t cap = table_capacity(n);
+  Workspace ws(workspace, workspace_bytes);
+  unsigned long long* keys = ws.take<unsigned long long>(cap);
+  int* vals = ws.take<int>(cap);
+  if (!ws.ok()) return PTV3_EWORKSPACE;
+  cudaStream_t st = as_stream(stream);
+  cudaMemsetAsync(keys, 0xff, (size_t)cap * 8, st);
+  cudaMemsetAsync(vals, 0x7f, (size_t)cap * 4, st);
+  subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1);
+  const size_t smem = (size_t)k3 * 32 * sizeof(float4);
+  static bool configured = false;
+  if (!configured) {
+    if (cudaFuncSetAttribute(subm_stem_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 125 * 32 * 16) !=
+        cudaSuccess)
+      return PTV3_ELAUNCH;
+    configured = true;
+  }
+  int64_t blocks = cdiv(n, 16);
+  if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
+  subm_stem_fused_kernel<<<(unsigned)blocks, 512, smem, st>>>(in, weight, bias, indices, keys, vals, cap - 1, n, ksize,
+                                                               act, out32, (__nv_bfloat16*)out16);
   return check_launch(2);
 }
 

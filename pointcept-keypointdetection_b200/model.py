@@ -473,6 +473,7 @@ class Embedding(PointModule):
         if act_layer is not None:
             self.stem.add(act_layer(), name="act")
         self.compute_dtype = torch.bfloat16
+        self.fuse_lookup = True        # A/B switch for the fused stem kernel (tests compare both paths)
 
     @torch.no_grad()
     def forward(self, point):
@@ -481,6 +482,20 @@ class Embedding(PointModule):
         sp = point.sparse_conv_feat
         bn = getattr(self.stem, "norm", None)
         feat_in = point.feat.float()
+        act = getattr(self.stem, "act", None)
+        gelu = isinstance(act, nn.GELU) and act.approximate == "none"
+        if (self.fuse_lookup and conv.in_channels == 4 and conv.out_channels == 32 and conv.kernel_size in (3, 5)
+                and (bn is None or (isinstance(bn, nn.BatchNorm1d) and not bn.training)) and (act is None or gelu)):
+            # neighbour search inside the conv (no (N, 125) table), folded BatchNorm, GELU and the bf16 copy in one kernel
+            s, t = (None, None) if bn is None else _cached(
+                self, "bn", [bn.weight, bn.bias, bn.running_mean, bn.running_var], lambda: _bn_scale_shift(bn))
+            w, b = conv._weights(torch.float32, s, t)
+            y, ycd = ops.subm_stem_fused(sp.indices, feat_in, w, b, conv.kernel_size, gelu=gelu, want_f32=True,
+                                         want_bf16=cd == torch.bfloat16)
+            point.feat = y
+            point["_feat_cd"] = ycd if ycd is not None else y
+            point.sparse_conv_feat = sp.replace_feature(point["_feat_cd"])
+            return point
         if isinstance(bn, nn.BatchNorm1d) and not bn.training:
             s, t = _cached(self, "bn", [bn.weight, bn.bias, bn.running_mean, bn.running_var],
                            lambda: _bn_scale_shift(bn))
@@ -490,8 +505,7 @@ class Embedding(PointModule):
             if bn is not None:
                 y = bn(y)
         ycd = None
-        act = getattr(self.stem, "act", None)
-        if isinstance(act, nn.GELU) and act.approximate == "none" and y.shape[1] % 4 == 0:
+        if gelu and y.shape[1] % 4 == 0:
             y, ycd = ops.affine_act(y, None, None, "gelu", want_f32=True, want_bf16=cd == torch.bfloat16)
         elif act is not None:
             y = act(y)

@@ -312,6 +312,22 @@ def subm_build_map(indices, ksize):
     return nbr
 
 
+def subm_stem_fused(indices, feat, weight_koc, bias, ksize, gelu=True, want_f32=True, want_bf16=True):
+    """Stem conv (C_in 4 -> 32, fp32) with the neighbour search inside + bias + GELU: returns (fp32, bf16) outputs."""
+    _need_cuda(indices, feat, weight_koc)
+    lib = _lib.load()
+    indices, feat, w = indices.contiguous().int(), feat.contiguous().float(), weight_koc.contiguous().float()
+    n = feat.shape[0]
+    assert feat.shape[1] == 4 and w.shape == (ksize ** 3, 32, 4)
+    o32 = torch.empty((n, 32), dtype=torch.float32, device=feat.device) if want_f32 else None
+    o16 = torch.empty((n, 32), dtype=torch.bfloat16, device=feat.device) if want_bf16 else None
+    b = bias.contiguous().float() if bias is not None else None
+    ws = _ws(lib.ptv3_subm_map_workspace(n), feat.device)
+    _lib.check(lib.ptv3_subm_stem_fused(_p(indices), n, int(ksize), _p(feat), _p(w), _p(b), 1 if gelu else 0, _p(o32),
+                                        _p(o16), _p(ws), ws.numel(), _stream()), "ptv3_subm_stem_fused")
+    return o32, o16
+
+
 def subm_conv(feat, weight_koc, bias, nbr, algo=0):
     """feat (N,Cin), weight (k^3, Cout, Cin) same dtype, bias fp32 (Cout) or None -> (N,Cout)."""
     _need_cuda(feat, weight_koc, nbr)

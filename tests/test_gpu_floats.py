@@ -498,3 +498,31 @@ def test_serving_paths_on_device(golden):
     # by the fragments i with i % c == p -> floor((kmax - 1 - p) / c) + 1 votes; summed over a voxel that is kmax
     assert torch.allclose(votes.sum(), torch.tensor(float(kmax * gs["n_voxels"]), device=votes.device), rtol=1e-5)
     assert float(votes.min()) >= 1.0 - 1e-4 and bool((votes <= torch.ceil(kmax / cnt.float()) + 1e-4).all())
+
+
+def test_fused_stem_equals_table_path():
+    """Embedding with the neighbour search fused into the stem conv (no (N,125) table) against the table path:
+    same present offsets in the same order, so the fp32 outputs are bit-identical; plus the oracle."""
+    m = _model(torch.bfloat16)
+    emb = m.backbone.embedding
+    from ptv3_b200.structure import Point
+    scenes = [_scene(61, 6000, 0.6), _scene(62, 2500, 0.35)]
+    cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
+    offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
+    outs = []
+    for fuse in (True, False):
+        emb.fuse_lookup = fuse
+        p = Point(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset)
+        p.serialization(order="z")
+        p.sparsify()
+        p = emb(p)
+        outs.append((p.feat.clone(), p["_feat_cd"].clone()))
+    emb.fuse_lookup = True
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert outs[0][1].dtype == torch.bfloat16 and outs[0][0].dtype == torch.float32
+    W = {k[len("backbone."):]: v for k, v in _weights().items() if k.startswith("backbone.")}
+    idx = torch.cat([torch.repeat_interleave(torch.arange(2), torch.tensor([len(s[0]) for s in scenes]))[:, None],
+                     cat(2).cpu()], 1).int()
+    ref = torch.nn.functional.gelu(P._bn(O.subm_conv(cat(1).cpu(), O.subm_neighbor_table(idx, 5),
+                                                     W["embedding.stem.conv.weight"], None), W, "embedding.stem.norm"))
+    assert rel_l2(outs[0][0], ref) < 1e-5
