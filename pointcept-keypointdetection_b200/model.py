@@ -355,22 +355,38 @@ class SerializedPooling(PointModule):
             self.act = PointSequential(act_layer())
         self.compute_dtype = torch.bfloat16
 
+    def pooling_depth(self, serialized_depth):
+        d = (math.ceil(self.stride) - 1).bit_length()
+        return 0 if d > serialized_depth else d
+
+    @torch.no_grad()
+    def plan(self, code, order, grid_coord, batch, pooling_depth, n_scenes):
+        """The integer half of the pooling (:385-412, :426-433): clusters, CSR, heads, pooled codes / orders / grid /
+        batch / offset.  It depends on the serialization only, so PointTransformerV3.forward runs it for ALL levels
+        before the first feature kernel: the one host read per level (pooled row count) then waits for a few tiny
+        integer kernels instead of draining the whole previous stage, and the feature pipeline has no sync at all."""
+        pf = ops.pool_front(code, order, pooling_depth)
+        g, b, indices4 = ops.pool_gather_ints(grid_coord, batch, pf["head"], pooling_depth)
+        c, o, inv = pf["code"], pf["order"], pf["inverse"]
+        if self.shuffle_orders:
+            perm = torch.randperm(c.shape[0])
+            if not torch.equal(perm, torch.arange(c.shape[0])):
+                perm = perm.to(c.device)
+                c, o, inv = c[perm], o[perm], inv[perm]
+        return dict(pf=pf, grid_coord=g, batch=b, indices4=indices4, code=c, order=o, inverse=inv,
+                    offset=ops.batch_to_offset(b, n_scenes))
+
     @torch.no_grad()
     def forward(self, point):
         cd = self.compute_dtype
-        pooling_depth = (math.ceil(self.stride) - 1).bit_length()
-        if pooling_depth > point.serialized_depth:
-            pooling_depth = 0
+        pooling_depth = self.pooling_depth(point.serialized_depth)
         assert {"serialized_code", "serialized_order", "serialized_inverse", "serialized_depth"}.issubset(
             point.keys()), "Run point.serialization() point cloud before SerializedPooling"
-        pf = ops.pool_front(point.serialized_code, point.serialized_order, pooling_depth)
-        grid_coord, batch, indices4 = ops.pool_gather_ints(point.grid_coord, point.batch, pf["head"], pooling_depth)
-        code, order, inverse = pf["code"], pf["order"], pf["inverse"]
-        if self.shuffle_orders:
-            perm = torch.randperm(code.shape[0])
-            if not torch.equal(perm, torch.arange(code.shape[0])):
-                perm = perm.to(code.device)
-                code, order, inverse = code[perm], order[perm], inverse[perm]
+        plans = point.pop("_pool_plans", None)
+        plan = plans.pop(0) if plans else self.plan(point.serialized_code, point.serialized_order, point.grid_coord,
+                                                    point.batch, pooling_depth, len(point.offset))
+        pf, grid_coord, batch, indices4 = plan["pf"], plan["grid_coord"], plan["batch"], plan["indices4"]
+        code, order, inverse = plan["code"], plan["order"], plan["inverse"]
         w, b = _cached(self, ("proj", cd), [self.proj.weight, self.proj.bias],
                        lambda: (self.proj.weight.to(cd), self.proj.bias.to(cd)))
         y = F.linear(_feat_cd(point, cd), w, b)
@@ -396,7 +412,9 @@ class SerializedPooling(PointModule):
         n_scenes = len(point.offset)
         new = Point(feat=feat, coord=coord, grid_coord=grid_coord, serialized_code=code, serialized_order=order,
                     serialized_inverse=inverse, serialized_depth=point.serialized_depth - pooling_depth, batch=batch,
-                    offset=ops.batch_to_offset(batch, n_scenes))
+                    offset=plan["offset"])
+        if plans:
+            new["_pool_plans"] = plans
         for k in ("condition", "context", "grid_size", "order"):
             if k in point:
                 new[k] = point[k]
@@ -582,6 +600,7 @@ class PointTransformerV3(PointModule):
                                   order_index=i % len(self.order), cpe_indice_key=f"stage{s}",
                                   drop_path=dec_dp_[i], **common), name=f"block{i}")
                 self.dec.add(module=dec, name=f"dec{s}")
+        self.plan_ahead = True
         self.set_compute_dtype(compute_dtype)
 
     def set_compute_dtype(self, dtype):
@@ -612,6 +631,20 @@ class PointTransformerV3(PointModule):
         point = Point(data_dict)
         point.serialization(order=self.order, shuffle_orders=self.shuffle_orders)
         point.sparsify()
+        if self.plan_ahead:
+            # integer front ends of every pooling level now (same order of torch.randperm draws as the reference:
+            # serialization, then pooling 1, 2, ...); see SerializedPooling.plan
+            plans, code, order = [], point.serialized_code, point.serialized_order
+            grid, batch, depth = point.grid_coord, point.batch, point.serialized_depth
+            for stage in self.enc._modules.values():
+                down = stage._modules.get("down")
+                if down is None:
+                    continue
+                pd = down.pooling_depth(depth)
+                plans.append(down.plan(code, order, grid, batch, pd, len(point.offset)))
+                code, order, grid, batch = plans[-1]["code"], plans[-1]["order"], plans[-1]["grid_coord"], plans[-1]["batch"]
+                depth -= pd
+            point["_pool_plans"] = plans
         point = self.embedding(point)
         point = self.enc(point)
         if not self.enc_mode:

@@ -82,21 +82,15 @@ def block_forward(mod, point):
 
 def pooling_forward(mod, point):
     cd = mod.compute_dtype
-    depth = (math.ceil(mod.stride) - 1).bit_length()
-    if depth > point.serialized_depth:
-        depth = 0
+    depth = mod.pooling_depth(point.serialized_depth)
+    n_scenes = len(point.offset)
     with torch.no_grad():
-        pf = ops.pool_front(point.serialized_code, point.serialized_order, depth)
-        grid_coord, batch, indices4 = ops.pool_gather_ints(point.grid_coord, point.batch, pf["head"], depth)
-        code, order, inverse = pf["code"], pf["order"], pf["inverse"]
-        if mod.shuffle_orders:
-            perm = torch.randperm(code.shape[0])
-            if not torch.equal(perm, torch.arange(code.shape[0])):
-                perm = perm.to(code.device)
-                code, order, inverse = code[perm], order[perm], inverse[perm]
+        plans = point.pop("_pool_plans", None)
+        plan = plans.pop(0) if plans else mod.plan(point.serialized_code, point.serialized_order, point.grid_coord,
+                                                   point.batch, depth, n_scenes)
+        pf, grid_coord, batch, indices4 = plan["pf"], plan["grid_coord"], plan["batch"], plan["indices4"]
+        code, order, inverse, offset = plan["code"], plan["order"], plan["inverse"], plan["offset"]
         coord = ops.segment_csr(point.coord.float(), pf["idx_ptr"], "mean", gather=pf["indices"])
-        n_scenes = len(point.offset)
-        offset = ops.batch_to_offset(batch, n_scenes)
     feat = A.segment_csr(_lin(point.feat, mod.proj, cd), pf["idx_ptr"], mod.reduce, pf["indices"]).float()
     if hasattr(mod, "norm"):
         feat = _bn(feat, mod.norm[0])
@@ -107,6 +101,8 @@ def pooling_forward(mod, point):
     for k in ("condition", "context", "grid_size", "order"):
         if k in point:
             new[k] = point[k]
+    if plans:
+        new["_pool_plans"] = plans
     new["pooling_inverse"] = pf["cluster"]
     new["pooling_parent"] = point
     new["_pooling_csr"] = (pf["indices"], pf["idx_ptr"])
@@ -148,6 +144,18 @@ def backbone_forward(bb, data_dict):
     with torch.no_grad():
         point.serialization(order=bb.order, shuffle_orders=bb.shuffle_orders)
         point.sparsify()
+        if bb.plan_ahead:        # integer front ends of all pooling levels first (see model.SerializedPooling.plan)
+            plans, code, order = [], point.serialized_code, point.serialized_order
+            grid, batch, depth = point.grid_coord, point.batch, point.serialized_depth
+            for stage in bb.enc._modules.values():
+                down = stage._modules.get("down")
+                if down is None:
+                    continue
+                pd = down.pooling_depth(depth)
+                plans.append(down.plan(code, order, grid, batch, pd, len(point.offset)))
+                code, order, grid, batch = plans[-1]["code"], plans[-1]["order"], plans[-1]["grid_coord"], plans[-1]["batch"]
+                depth -= pd
+            point["_pool_plans"] = plans
     point = embedding_forward(bb.embedding, point)
     stages = [bb.enc] + ([] if bb.enc_mode else [bb.dec])
     for seq in stages:
