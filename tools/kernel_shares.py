@@ -35,6 +35,16 @@ def main():
     print(f"voxels={sum(counts)} device total {tot/1e3:.3f} ms over {sum(e.count for e in ev)} launches")
     for e in sorted(ev, key=lambda e: -e.device_time_total)[: a.top]:
         print(f"{e.device_time_total/1e3:9.3f} ms {100*e.device_time_total/tot:5.1f}% n={e.count:4d} {e.key[:100]}")
+    # idle intervals of the device inside the step: where the host does not keep the queue full
+    ks = sorted([e for e in prof.events() if e.device_type.name == "CUDA" and e.time_range.end > e.time_range.start],
+                key=lambda e: e.time_range.start)
+    if ks:
+        span = ks[-1].time_range.end - ks[0].time_range.start
+        gaps = [(b.time_range.start - a.time_range.end, a.name, b.name) for a, b in zip(ks[:-1], ks[1:])]
+        idle = sum(g[0] for g in gaps if g[0] > 0)
+        print(f"first-to-last kernel span {span/1e3:.3f} ms, idle inside {idle/1e3:.3f} ms in {sum(g[0] > 2 for g in gaps)} gaps > 2 us")
+        for g, an, bn in sorted(gaps, key=lambda g: -g[0])[:14]:
+            print(f"  gap {g:8.1f} us after {an[:60]:60s} before {bn[:50]}")
 
 
 if __name__ == "__main__":
