@@ -601,6 +601,7 @@ class PointTransformerV3(PointModule):
                                   drop_path=dec_dp_[i], **common), name=f"block{i}")
                 self.dec.add(module=dec, name=f"dec{s}")
         self.plan_ahead = True
+        self.plan_overlap = True       # A/B switch: stem + first stage enqueued before the plan phase
         self.set_compute_dtype(compute_dtype)
 
     def set_compute_dtype(self, dtype):
@@ -631,22 +632,45 @@ class PointTransformerV3(PointModule):
         point = Point(data_dict)
         point.serialization(order=self.order, shuffle_orders=self.shuffle_orders)
         point.sparsify()
+        stages = list(self.enc._modules.values())
+        first_done = False
         if self.plan_ahead:
-            # integer front ends of every pooling level now (same order of torch.randperm draws as the reference:
-            # serialization, then pooling 1, 2, ...); see SerializedPooling.plan
-            plans, code, order = [], point.serialized_code, point.serialized_order
-            grid, batch, depth = point.grid_coord, point.batch, point.serialized_depth
-            for stage in self.enc._modules.values():
-                down = stage._modules.get("down")
-                if down is None:
-                    continue
-                pd = down.pooling_depth(depth)
-                plans.append(down.plan(code, order, grid, batch, pd, len(point.offset)))
-                code, order, grid, batch = plans[-1]["code"], plans[-1]["order"], plans[-1]["grid_coord"], plans[-1]["batch"]
-                depth -= pd
+            # Integer front ends of every pooling level (same order of torch.randperm draws as the reference:
+            # serialization, then pooling 1, 2, ...; see SerializedPooling.plan).  They run on a side stream while the
+            # main stream already works on the stem and the first encoder stage (which need no plan): the four host
+            # reads of the pooled row counts synchronise the side stream only.
+            main = torch.cuda.current_stream()
+            side = self.__dict__.get("_plan_stream")
+            if side is None or side.device != main.device:
+                side = self.__dict__["_plan_stream"] = torch.cuda.Stream(device=main.device)
+            ready = torch.cuda.Event()
+            ready.record(main)                                   # codes / orders / grid / batch are final here
+            code, order = point.serialized_code, point.serialized_order
+            grid, batch, depth, n_scenes = point.grid_coord, point.batch, point.serialized_depth, len(point.offset)
+            if self.plan_overlap and "down" not in stages[0]._modules:
+                point = stages[0](self.embedding(point))
+                first_done = True
+            side.wait_event(ready)
+            plans = []
+            with torch.cuda.stream(side):
+                for stage in stages:
+                    down = stage._modules.get("down")
+                    if down is None:
+                        continue
+                    pd = down.pooling_depth(depth)
+                    plans.append(down.plan(code, order, grid, batch, pd, n_scenes))
+                    code, order, grid, batch = (plans[-1][k] for k in ("code", "order", "grid_coord", "batch"))
+                    depth -= pd
+            main.wait_stream(side)
+            for plan in plans:                                   # allocated on the side stream, consumed on the main one
+                for v in list(plan.values()) + list(plan["pf"].values()):
+                    if torch.is_tensor(v):
+                        v.record_stream(main)
             point["_pool_plans"] = plans
-        point = self.embedding(point)
-        point = self.enc(point)
+        if not first_done:
+            point = stages[0](self.embedding(point))
+        for stage in stages[1:]:
+            point = stage(point)
         if not self.enc_mode:
             point = self.dec(point)
         return point
