@@ -132,15 +132,56 @@ class LayerNormFn(torch.autograd.Function):
         return dx.to(x.dtype), dg.to(weight.dtype), db.to(weight.dtype), None, None
 
 
+class ParamCast:
+    """Compute-dtype copies of a module tree's Linear parameters, refreshed by ONE multi-tensor copy per optimizer step
+    (torch.autocast re-casts every weight at every use: 2 small kernels per Linear per step here before this cache).
+    Copies are keyed by parameter identity and re-made when a parameter's version counter, storage or device moved."""
+
+    def __init__(self):
+        self.params, self.copies, self.stamp, self.index, self.cd = [], [], None, {}, None
+
+    def refresh(self, module, cd):
+        params = [p for m in module.modules() if isinstance(m, torch.nn.Linear)
+                  for p in (m.weight, m.bias) if p is not None and p.dtype != cd]
+        stamp = [(id(p), p._version, p.data_ptr()) for p in params]
+        if stamp == self.stamp and cd == self.cd:
+            return self
+        if ([s[0] for s in stamp] != [s[0] for s in (self.stamp or [])] or cd != self.cd
+                or any(c.device != p.device for c, p in zip(self.copies, params))):
+            self.copies = [torch.empty_like(p, dtype=cd) for p in params]
+            self.index = {id(p): c for p, c in zip(params, self.copies)}
+        with torch.no_grad():
+            if params:
+                torch._foreach_copy_(self.copies, [p.detach() for p in params])
+        self.params, self.stamp, self.cd = params, stamp, cd
+        return self
+
+    def get(self, p, cd):
+        c = self.index.get(id(p))
+        return c if c is not None and c.dtype == cd else None
+
+
+_param_cast = None            # the ParamCast of the forward in flight (set by train.backbone_forward)
+
+
+def set_param_cast(cache):
+    global _param_cast
+    _param_cast = cache
+
+
 class LinearFn(torch.autograd.Function):
-    """y = x W^T + b with operands cast to `cd` (torch.autocast's Linear): cuBLAS GEMMs both ways, the bias gradient
-    by ptv3_column_sum instead of torch's generic dim-0 reduction."""
+    """y = x W^T + b with operands cast to `cd` (torch.autocast's Linear): cuBLAS GEMMs both ways (the weight
+    gradient accumulated and written in fp32 by the GEMM itself), the bias gradient by ptv3_column_sum instead of
+    torch's generic dim-0 reduction.  `wc` / `bc`: compute-dtype copies from ParamCast, or None."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, cd):
+    def forward(ctx, x, weight, bias, cd, wc, bc):
         xc = x.detach().to(cd)
-        wc = weight.detach().to(cd)
-        y = torch.nn.functional.linear(xc, wc, bias.detach().to(cd) if bias is not None else None)
+        if wc is None:
+            wc = weight.detach().to(cd)
+        if bias is not None and bc is None:
+            bc = bias.detach().to(cd)
+        y = torch.nn.functional.linear(xc, wc, bc)
         ctx.save_for_backward(xc, wc)
         ctx.meta = (x.dtype, weight.dtype, bias is not None)
         return y
@@ -154,14 +195,20 @@ class LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = (dy @ wc).to(xdt)
         if ctx.needs_input_grad[1]:
-            dw = (dy.t() @ xc).to(wdt)
+            if wdt == torch.float32 and xc.dtype != torch.float32:
+                dw = torch.mm(dy.t(), xc, out_dtype=torch.float32)
+            else:
+                dw = (dy.t() @ xc).to(wdt)
         if has_bias and ctx.needs_input_grad[2]:
             db = ops.column_sum(dy).to(wdt)
-        return dx, dw, db, None
+        return dx, dw, db, None, None, None
 
 
 def linear(x, lin, cd):
-    return LinearFn.apply(x, lin.weight, lin.bias, cd)
+    c = _param_cast
+    wc = c.get(lin.weight, cd) if c is not None else None
+    bc = c.get(lin.bias, cd) if c is not None and lin.bias is not None else None
+    return LinearFn.apply(x, lin.weight, lin.bias, cd, wc, bc)
 
 
 def layer_norm(x, ln, out_dtype=torch.float32):

@@ -35,13 +35,14 @@ def _bn(x, bn):
     return bn(x.float())            # nn.BatchNorm1d: batch statistics in train(), running ones in eval()
 
 
-def _drop_path(x, rate, training):
-    """timm.layers.DropPath on an (N, C) tensor: one Bernoulli draw per row, kept rows scaled by 1 / keep."""
+def _residual(x, y, rate, training):
+    """x + DropPath(y) (timm.layers.DropPath: one Bernoulli draw per row, kept rows scaled by 1 / keep) in ONE
+    elementwise kernel: x fp32, y in the compute dtype, promoted inside the kernel instead of y.float() first."""
     if rate == 0.0 or not training:
-        return x
+        return x + y
     keep = 1.0 - rate
-    mask = x.new_empty((x.shape[0], 1)).bernoulli_(keep)
-    return x * (mask / keep)
+    mask = x.new_empty((x.shape[0], 1)).bernoulli_(keep).div_(keep)
+    return torch.addcmul(x, y, mask)
 
 
 def embedding_forward(mod, point):
@@ -70,10 +71,10 @@ def block_forward(mod, point):
     windows, nwin = att.get_windows(point)
     a = A.attn_window(qkv, point.serialized_order[att.order_index], windows, nwin, att.num_heads, att.patch_size,
                       att.scale, att.algo)
-    x = x + _drop_path(_lin(a, att.proj, cd).float(), mod.drop_path_rate, mod.training)
+    x = _residual(x, _lin(a, att.proj, cd), mod.drop_path_rate, mod.training)
     mlp = mod.mlp[0]
     f = _lin(mlp.act(_lin(_ln(x, mod.norm2[0], cd), mlp.fc1, cd)), mlp.fc2, cd)
-    x = x + _drop_path(f.float(), mod.drop_path_rate, mod.training)
+    x = _residual(x, f, mod.drop_path_rate, mod.training)
     point.feat = x
     point["_feat_cd"] = None
     point.sparse_conv_feat = sp.replace_feature(x)
@@ -141,6 +142,9 @@ def unpooling_forward(mod, point):
 def backbone_forward(bb, data_dict):
     from . import model as M
     point = Point(data_dict)
+    if not hasattr(bb, "_param_cast"):
+        bb._param_cast = A.ParamCast()
+    A.set_param_cast(bb._param_cast.refresh(bb, bb.compute_dtype))
     with torch.no_grad():
         point.serialization(order=bb.order, shuffle_orders=bb.shuffle_orders)
         point.sparsify()

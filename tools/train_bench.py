@@ -51,7 +51,7 @@ def main():
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
         step()
         torch.cuda.synchronize()
-    rows = sorted(prof.key_averages(), key=lambda r: -r.device_time_total)[:18]
+    rows = sorted(prof.key_averages(), key=lambda r: -r.device_time_total)[:40]
     tot = sum(r.device_time_total for r in prof.key_averages())
     print(f"device total {tot / 1e3:.1f} ms")
     for r in rows:
