@@ -53,7 +53,7 @@ __device__ __forceinline__ void zero16(uint32_t dst) {
 
 // smem: K, V, Q, dO [kpad][16] bf16 each; lse_s, d_s [kpad] fp32; order_s [kpad] int32
 // lse_g (optional): the forward's log-sum-exp per (row, head), log2 units of the scaled scores -> sweep 1 is skipped
-template <int kWarps>
+template <int kWarps, int kT>
 __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
     const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ dout,
     const int64_t* __restrict__ order, const int64_t* __restrict__ windows, const int64_t* __restrict__ n_windows, int h,
@@ -142,181 +142,197 @@ __global__ void __launch_bounds__(kWarps * 32, 1) attn_bwd_mma_kernel(
   const uint32_t a_off = (uint32_t)(((((lane >> 3) & 1) << 3) + (lane & 7)) * 32 + (lane >> 4) * 16);
 
   // =========================== phase A: dQ (and the rows' log-sum-exp) ===========================
-  for (int qt = warp; qt < n_qtiles; qt += kWarps) {
-    uint32_t qa[4], da[4];
-    ldsm4(qa, qs + (uint32_t)(qt * 512) + a_off);
-    ldsm4(da, dos + (uint32_t)(qt * 512) + a_off);
-    const int qi0 = qt * 16 + g, qi1 = qi0 + 8;
-    // sweep 1: log-sum-exp in log2 units of the scaled scores
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-    for (int c = 0; c < (lse_g ? 0 : kpad / 64); ++c) {
-      float s[8][4];
+  // kT query tiles per warp and pass: the K, V and K^T fragments of a key tile serve all of them.  Q / dO rows are zero up
+  // to kpad, and padded queries have lse = 1e30 (P = 0).
+  for (int qt = warp * kT; qt < n_qtiles; qt += kWarps * kT) {
+    uint32_t qa[kT][4], da[kT][4];
+    float lse[kT][2], D[kT][2];
 #pragma unroll
-      for (int b2 = 0; b2 < 4; ++b2) {
-        uint32_t kb[4];
-        ldsm4(kb, ks + (uint32_t)((c * 4 + b2) * 512) + b_off);
+    for (int j = 0; j < kT; ++j) {
+      ldsm4(qa[j], qs + (uint32_t)((qt + j) * 512) + a_off);
+      ldsm4(da[j], dos + (uint32_t)((qt + j) * 512) + a_off);
+      const int qi0 = (qt + j) * 16 + g, qi1 = qi0 + 8;
+      // sweep 1 (only without the forward's log-sum-exp): log2 units of the scaled scores
+      float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+      for (int c = 0; c < (lse_g ? 0 : kpad / 64); ++c) {
+        float s[8][4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) s[2 * b2][i] = s[2 * b2 + 1][i] = 0.f;
-        mma16816(s[2 * b2], qa, kb[0], kb[1]);
-        mma16816(s[2 * b2 + 1], qa, kb[2], kb[3]);
-      }
-      if ((c + 1) * 64 > kl) {
-        const int base = c * 64 + 2 * t;
+        for (int b2 = 0; b2 < 4; ++b2) {
+          uint32_t kb[4];
+          ldsm4(kb, ks + (uint32_t)((c * 4 + b2) * 512) + b_off);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) s[2 * b2][i] = s[2 * b2 + 1][i] = 0.f;
+          mma16816(s[2 * b2], qa[j], kb[0], kb[1]);
+          mma16816(s[2 * b2 + 1], qa[j], kb[2], kb[3]);
+        }
+        if ((c + 1) * 64 > kl) {
+          const int base = c * 64 + 2 * t;
+#pragma unroll
+          for (int b = 0; b < 8; ++b) {
+            int key = base + b * 8;
+            if (key >= kl) s[b][0] = s[b][2] = -INFINITY;
+            if (key + 1 >= kl) s[b][1] = s[b][3] = -INFINITY;
+          }
+        }
+        float mx0 = m0, mx1 = m1;
 #pragma unroll
         for (int b = 0; b < 8; ++b) {
-          int key = base + b * 8;
-          if (key >= kl) s[b][0] = s[b][2] = -INFINITY;
-          if (key + 1 >= kl) s[b][1] = s[b][3] = -INFINITY;
+          mx0 = fmaxf(mx0, fmaxf(s[b][0], s[b][1]) * sl2);
+          mx1 = fmaxf(mx1, fmaxf(s[b][2], s[b][3]) * sl2);
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        l0 *= ex2(m0 - mx0);
+        l1 *= ex2(m1 - mx1);
+        m0 = mx0;
+        m1 = mx1;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          l0 += ex2(fmaf(s[b][0], sl2, -m0)) + ex2(fmaf(s[b][1], sl2, -m0));
+          l1 += ex2(fmaf(s[b][2], sl2, -m1)) + ex2(fmaf(s[b][3], sl2, -m1));
         }
       }
-      float mx0 = m0, mx1 = m1;
-#pragma unroll
-      for (int b = 0; b < 8; ++b) {
-        mx0 = fmaxf(mx0, fmaxf(s[b][0], s[b][1]) * sl2);
-        mx1 = fmaxf(mx1, fmaxf(s[b][2], s[b][3]) * sl2);
-      }
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-      l0 *= ex2(m0 - mx0);
-      l1 *= ex2(m1 - mx1);
-      m0 = mx0;
-      m1 = mx1;
-#pragma unroll
-      for (int b = 0; b < 8; ++b) {
-        l0 += ex2(fmaf(s[b][0], sl2, -m0)) + ex2(fmaf(s[b][1], sl2, -m0));
-        l1 += ex2(fmaf(s[b][2], sl2, -m1)) + ex2(fmaf(s[b][3], sl2, -m1));
-      }
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      lse[j][0] = lse_g ? lse_s[qi0] : (qi0 < ql ? m0 + __log2f(l0) : 1e30f);
+      lse[j][1] = lse_g ? lse_s[qi1] : (qi1 < ql ? m1 + __log2f(l1) : 1e30f);
+      D[j][0] = d_s[qi0];
+      D[j][1] = d_s[qi1];
     }
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float lse0 = lse_g ? lse_s[qi0] : m0 + __log2f(l0), lse1 = lse_g ? lse_s[qi1] : m1 + __log2f(l1);
-    const float D0 = d_s[qi0], D1 = d_s[qi1];
     // sweep 2: dQ
-    float dq[2][4];
+    float dq[kT][2][4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) dq[0][i] = dq[1][i] = 0.f;
+    for (int j = 0; j < kT; ++j)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dq[j][0][i] = dq[j][1][i] = 0.f;
     for (int kt = 0; kt < n_ktiles; ++kt) {
       const uint32_t kb_addr = ks + (uint32_t)(kt * 512), vb_addr = vs + (uint32_t)(kt * 512);
-      uint32_t kb[4], vb[4];
-      float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
-      float p0[4] = {0.f, 0.f, 0.f, 0.f}, p1[4] = {0.f, 0.f, 0.f, 0.f};
+      uint32_t kb[4], vb[4], kt_[4];
       ldsm4(kb, kb_addr + b_off);
-      mma16816(s0, qa, kb[0], kb[1]);
-      mma16816(s1, qa, kb[2], kb[3]);
       ldsm4(vb, vb_addr + b_off);
-      mma16816(p0, da, vb[0], vb[1]);   // dP
-      mma16816(p1, da, vb[2], vb[3]);
-      float ds0[4], ds1[4];
-      ds0[0] = ex2(fmaf(s0[0], sl2, -lse0)) * (p0[0] - D0);
-      ds0[1] = ex2(fmaf(s0[1], sl2, -lse0)) * (p0[1] - D0);
-      ds0[2] = ex2(fmaf(s0[2], sl2, -lse1)) * (p0[2] - D1);
-      ds0[3] = ex2(fmaf(s0[3], sl2, -lse1)) * (p0[3] - D1);
-      ds1[0] = ex2(fmaf(s1[0], sl2, -lse0)) * (p1[0] - D0);
-      ds1[1] = ex2(fmaf(s1[1], sl2, -lse0)) * (p1[1] - D0);
-      ds1[2] = ex2(fmaf(s1[2], sl2, -lse1)) * (p1[2] - D1);
-      ds1[3] = ex2(fmaf(s1[3], sl2, -lse1)) * (p1[3] - D1);
-      if ((kt + 1) * 16 > kl) {   // keys past the window end
-        const int key = kt * 16 + 2 * t;
-        if (key >= kl) ds0[0] = ds0[2] = 0.f;
-        if (key + 1 >= kl) ds0[1] = ds0[3] = 0.f;
-        if (key + 8 >= kl) ds1[0] = ds1[2] = 0.f;
-        if (key + 9 >= kl) ds1[1] = ds1[3] = 0.f;
-      }
-      uint32_t pa[4] = {pack_bf16(ds0[0], ds0[1]), pack_bf16(ds0[2], ds0[3]), pack_bf16(ds1[0], ds1[1]),
-                        pack_bf16(ds1[2], ds1[3])};
-      uint32_t kt_[4];
       ldsm4t(kt_, kb_addr + a_off);
-      mma16816(dq[0], pa, kt_[0], kt_[1]);
-      mma16816(dq[1], pa, kt_[2], kt_[3]);
+      const bool edge = (kt + 1) * 16 > kl;   // keys past the window end
+      const int key = kt * 16 + 2 * t;
+#pragma unroll
+      for (int j = 0; j < kT; ++j) {
+        float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+        float p0[4] = {0.f, 0.f, 0.f, 0.f}, p1[4] = {0.f, 0.f, 0.f, 0.f};
+        mma16816(s0, qa[j], kb[0], kb[1]);
+        mma16816(s1, qa[j], kb[2], kb[3]);
+        mma16816(p0, da[j], vb[0], vb[1]);   // dP
+        mma16816(p1, da[j], vb[2], vb[3]);
+        float ds0[4], ds1[4];
+        ds0[0] = ex2(fmaf(s0[0], sl2, -lse[j][0])) * (p0[0] - D[j][0]);
+        ds0[1] = ex2(fmaf(s0[1], sl2, -lse[j][0])) * (p0[1] - D[j][0]);
+        ds0[2] = ex2(fmaf(s0[2], sl2, -lse[j][1])) * (p0[2] - D[j][1]);
+        ds0[3] = ex2(fmaf(s0[3], sl2, -lse[j][1])) * (p0[3] - D[j][1]);
+        ds1[0] = ex2(fmaf(s1[0], sl2, -lse[j][0])) * (p1[0] - D[j][0]);
+        ds1[1] = ex2(fmaf(s1[1], sl2, -lse[j][0])) * (p1[1] - D[j][0]);
+        ds1[2] = ex2(fmaf(s1[2], sl2, -lse[j][1])) * (p1[2] - D[j][1]);
+        ds1[3] = ex2(fmaf(s1[3], sl2, -lse[j][1])) * (p1[3] - D[j][1]);
+        if (edge) {
+          if (key >= kl) ds0[0] = ds0[2] = 0.f;
+          if (key + 1 >= kl) ds0[1] = ds0[3] = 0.f;
+          if (key + 8 >= kl) ds1[0] = ds1[2] = 0.f;
+          if (key + 9 >= kl) ds1[1] = ds1[3] = 0.f;
+        }
+        uint32_t pa[4] = {pack_bf16(ds0[0], ds0[1]), pack_bf16(ds0[2], ds0[3]), pack_bf16(ds1[0], ds1[1]),
+                          pack_bf16(ds1[2], ds1[3])};
+        mma16816(dq[j][0], pa, kt_[0], kt_[1]);
+        mma16816(dq[j][1], pa, kt_[2], kt_[3]);
+      }
     }
-    if (qi0 < ql) {
-      float* o = dqkv + (int64_t)order_s[q_rel + qi0] * rs + head * kD;
-      *reinterpret_cast<float2*>(o + 2 * t) = make_float2(dq[0][0] * scale, dq[0][1] * scale);
-      *reinterpret_cast<float2*>(o + 8 + 2 * t) = make_float2(dq[1][0] * scale, dq[1][1] * scale);
-      if (t == 0 && !lse_g) lse_s[qi0] = lse0;
-    }
-    if (qi1 < ql) {
-      float* o = dqkv + (int64_t)order_s[q_rel + qi1] * rs + head * kD;
-      *reinterpret_cast<float2*>(o + 2 * t) = make_float2(dq[0][2] * scale, dq[0][3] * scale);
-      *reinterpret_cast<float2*>(o + 8 + 2 * t) = make_float2(dq[1][2] * scale, dq[1][3] * scale);
-      if (t == 0 && !lse_g) lse_s[qi1] = lse1;
+#pragma unroll
+    for (int j = 0; j < kT; ++j) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int qi = (qt + j) * 16 + g + 8 * r;
+        if (qi < ql) {
+          float* o = dqkv + (int64_t)order_s[q_rel + qi] * rs + head * kD;
+          *reinterpret_cast<float2*>(o + 2 * t) = make_float2(dq[j][0][2 * r] * scale, dq[j][0][2 * r + 1] * scale);
+          *reinterpret_cast<float2*>(o + 8 + 2 * t) = make_float2(dq[j][1][2 * r] * scale, dq[j][1][2 * r + 1] * scale);
+          if (t == 0 && !lse_g) lse_s[qi] = lse[j][r];
+        }
+      }
     }
   }
   __syncthreads();
 
   // =========================== phase B: dK, dV on the transposed problem ===========================
-  for (int kt = warp; kt < n_ktiles; kt += kWarps) {
-    uint32_t ka[4], va[4];
-    ldsm4(ka, ks + (uint32_t)(kt * 512) + a_off);
-    ldsm4(va, vs + (uint32_t)(kt * 512) + a_off);
-    float dk[2][4], dv[2][4];
+  // kT key tiles per warp and pass: the four Q / dO fragment loads and the lse / D reads of a query tile serve all of them
+  // (shared-memory bandwidth, not MUFU, bounded this phase with one tile per warp: 4 ldmatrix.x4 + 4 LDS.64 per
+  // 8 exp2 per lane).  K / V rows are zero up to kpad (a multiple of 64), so tiles kt .. kt+kT-1 (kT <= 4) are always readable.
+  for (int kt = warp * kT; kt < n_ktiles; kt += kWarps * kT) {
+    uint32_t ka[kT][4], va[kT][4];
+    float dk[kT][2][4], dv[kT][2][4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) dk[0][i] = dk[1][i] = dv[0][i] = dv[1][i] = 0.f;
+    for (int j = 0; j < kT; ++j) {
+      ldsm4(ka[j], ks + (uint32_t)((kt + j) * 512) + a_off);
+      ldsm4(va[j], vs + (uint32_t)((kt + j) * 512) + a_off);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dk[j][0][i] = dk[j][1][i] = dv[j][0][i] = dv[j][1][i] = 0.f;
+    }
     for (int qt = 0; qt < n_qtiles; ++qt) {
       const uint32_t q_addr = qs + (uint32_t)(qt * 512), d_addr = dos + (uint32_t)(qt * 512);
-      uint32_t qb[4], db[4];
-      float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
-      float p0[4] = {0.f, 0.f, 0.f, 0.f}, p1[4] = {0.f, 0.f, 0.f, 0.f};
+      uint32_t qb[4], db[4], dt[4], qt_[4];
       ldsm4(qb, q_addr + b_off);
-      mma16816(s0, ka, qb[0], qb[1]);   // S^T: rows = keys, cols = queries qt*16 + (0..7 | 8..15)
-      mma16816(s1, ka, qb[2], qb[3]);
       ldsm4(db, d_addr + b_off);
-      mma16816(p0, va, db[0], db[1]);   // dP^T
-      mma16816(p1, va, db[2], db[3]);
+      ldsm4t(dt, d_addr + a_off);
+      ldsm4t(qt_, q_addr + a_off);
       const int qc = qt * 16 + 2 * t;
       const float2 ls0 = *reinterpret_cast<const float2*>(lse_s + qc), ls1 = *reinterpret_cast<const float2*>(lse_s + qc + 8);
       const float2 dd0 = *reinterpret_cast<const float2*>(d_s + qc), dd1 = *reinterpret_cast<const float2*>(d_s + qc + 8);
-      float pt0[4], pt1[4];
-      pt0[0] = ex2(fmaf(s0[0], sl2, -ls0.x));
-      pt0[1] = ex2(fmaf(s0[1], sl2, -ls0.y));
-      pt0[2] = ex2(fmaf(s0[2], sl2, -ls0.x));
-      pt0[3] = ex2(fmaf(s0[3], sl2, -ls0.y));
-      pt1[0] = ex2(fmaf(s1[0], sl2, -ls1.x));
-      pt1[1] = ex2(fmaf(s1[1], sl2, -ls1.y));
-      pt1[2] = ex2(fmaf(s1[2], sl2, -ls1.x));
-      pt1[3] = ex2(fmaf(s1[3], sl2, -ls1.y));
-      uint32_t pa[4] = {pack_bf16(pt0[0], pt0[1]), pack_bf16(pt0[2], pt0[3]), pack_bf16(pt1[0], pt1[1]),
-                        pack_bf16(pt1[2], pt1[3])};
-      uint32_t sa[4] = {pack_bf16(pt0[0] * (p0[0] - dd0.x), pt0[1] * (p0[1] - dd0.y)),
-                        pack_bf16(pt0[2] * (p0[2] - dd0.x), pt0[3] * (p0[3] - dd0.y)),
-                        pack_bf16(pt1[0] * (p1[0] - dd1.x), pt1[1] * (p1[1] - dd1.y)),
-                        pack_bf16(pt1[2] * (p1[2] - dd1.x), pt1[3] * (p1[3] - dd1.y))};
-      uint32_t dt[4], qt_[4];
-      ldsm4t(dt, d_addr + a_off);
-      mma16816(dv[0], pa, dt[0], dt[1]);
-      mma16816(dv[1], pa, dt[2], dt[3]);
-      ldsm4t(qt_, q_addr + a_off);
-      mma16816(dk[0], sa, qt_[0], qt_[1]);
-      mma16816(dk[1], sa, qt_[2], qt_[3]);
+#pragma unroll
+      for (int j = 0; j < kT; ++j) {
+        float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+        float p0[4] = {0.f, 0.f, 0.f, 0.f}, p1[4] = {0.f, 0.f, 0.f, 0.f};
+        mma16816(s0, ka[j], qb[0], qb[1]);   // S^T: rows = keys, cols = queries qt*16 + (0..7 | 8..15)
+        mma16816(s1, ka[j], qb[2], qb[3]);
+        mma16816(p0, va[j], db[0], db[1]);   // dP^T
+        mma16816(p1, va[j], db[2], db[3]);
+        float pt0[4], pt1[4];
+        pt0[0] = ex2(fmaf(s0[0], sl2, -ls0.x));
+        pt0[1] = ex2(fmaf(s0[1], sl2, -ls0.y));
+        pt0[2] = ex2(fmaf(s0[2], sl2, -ls0.x));
+        pt0[3] = ex2(fmaf(s0[3], sl2, -ls0.y));
+        pt1[0] = ex2(fmaf(s1[0], sl2, -ls1.x));
+        pt1[1] = ex2(fmaf(s1[1], sl2, -ls1.y));
+        pt1[2] = ex2(fmaf(s1[2], sl2, -ls1.x));
+        pt1[3] = ex2(fmaf(s1[3], sl2, -ls1.y));
+        uint32_t pa[4] = {pack_bf16(pt0[0], pt0[1]), pack_bf16(pt0[2], pt0[3]), pack_bf16(pt1[0], pt1[1]),
+                          pack_bf16(pt1[2], pt1[3])};
+        uint32_t sa[4] = {pack_bf16(pt0[0] * (p0[0] - dd0.x), pt0[1] * (p0[1] - dd0.y)),
+                          pack_bf16(pt0[2] * (p0[2] - dd0.x), pt0[3] * (p0[3] - dd0.y)),
+                          pack_bf16(pt1[0] * (p1[0] - dd1.x), pt1[1] * (p1[1] - dd1.y)),
+                          pack_bf16(pt1[2] * (p1[2] - dd1.x), pt1[3] * (p1[3] - dd1.y))};
+        mma16816(dv[j][0], pa, dt[0], dt[1]);
+        mma16816(dv[j][1], pa, dt[2], dt[3]);
+        mma16816(dk[j][0], sa, qt_[0], qt_[1]);
+        mma16816(dk[j][1], sa, qt_[2], qt_[3]);
+      }
     }
-    const int kj0 = kt * 16 + g, kj1 = kj0 + 8;
-    if (kj0 < kl) {
-      float* o = dqkv + (int64_t)order_s[kj0] * rs + (int64_t)h * kD + head * kD;
-      atomicAdd(o + 2 * t, dk[0][0] * scale);
-      atomicAdd(o + 2 * t + 1, dk[0][1] * scale);
-      atomicAdd(o + 8 + 2 * t, dk[1][0] * scale);
-      atomicAdd(o + 9 + 2 * t, dk[1][1] * scale);
-      o += (int64_t)h * kD;
-      atomicAdd(o + 2 * t, dv[0][0]);
-      atomicAdd(o + 2 * t + 1, dv[0][1]);
-      atomicAdd(o + 8 + 2 * t, dv[1][0]);
-      atomicAdd(o + 9 + 2 * t, dv[1][1]);
-    }
-    if (kj1 < kl) {
-      float* o = dqkv + (int64_t)order_s[kj1] * rs + (int64_t)h * kD + head * kD;
-      atomicAdd(o + 2 * t, dk[0][2] * scale);
-      atomicAdd(o + 2 * t + 1, dk[0][3] * scale);
-      atomicAdd(o + 8 + 2 * t, dk[1][2] * scale);
-      atomicAdd(o + 9 + 2 * t, dk[1][3] * scale);
-      o += (int64_t)h * kD;
-      atomicAdd(o + 2 * t, dv[0][2]);
-      atomicAdd(o + 2 * t + 1, dv[0][3]);
-      atomicAdd(o + 8 + 2 * t, dv[1][2]);
-      atomicAdd(o + 9 + 2 * t, dv[1][3]);
+#pragma unroll
+    for (int j = 0; j < kT; ++j) {
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int kj = (kt + j) * 16 + g + 8 * r;
+        if (kj < kl) {
+          float* o = dqkv + (int64_t)order_s[kj] * rs + (int64_t)h * kD + head * kD;
+          atomicAdd(o + 2 * t, dk[j][0][2 * r] * scale);
+          atomicAdd(o + 2 * t + 1, dk[j][0][2 * r + 1] * scale);
+          atomicAdd(o + 8 + 2 * t, dk[j][1][2 * r] * scale);
+          atomicAdd(o + 9 + 2 * t, dk[j][1][2 * r + 1] * scale);
+          o += (int64_t)h * kD;
+          atomicAdd(o + 2 * t, dv[j][0][2 * r]);
+          atomicAdd(o + 2 * t + 1, dv[j][0][2 * r + 1]);
+          atomicAdd(o + 8 + 2 * t, dv[j][1][2 * r]);
+          atomicAdd(o + 9 + 2 * t, dv[j][1][2 * r + 1]);
+        }
+      }
     }
   }
 }
@@ -332,9 +348,9 @@ int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const
   if (smem > 220 * 1024) return PTV3_EUNSUPPORTED;
   static size_t configured = 0;
   if (smem > configured) {
-    if (cudaFuncSetAttribute(attn_bwd_mma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+    if (cudaFuncSetAttribute(attn_bwd_mma_kernel<8, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
             cudaSuccess ||
-        cudaFuncSetAttribute(attn_bwd_mma_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
+        cudaFuncSetAttribute(attn_bwd_mma_kernel<16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
             cudaSuccess)
       return PTV3_ELAUNCH;
     configured = smem;
@@ -343,10 +359,10 @@ int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const
   dim3 grid((unsigned)(n_windows_max * h));
   // one CTA per SM (140 KB of staged operands): 16 warps hide the ldmatrix / MUFU latency better than 8
   if (g_attn_bwd_warps == 8)
-    attn_bwd_mma_kernel<8><<<grid, 256, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
+    attn_bwd_mma_kernel<8, 4><<<grid, 256, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
                                                     scale * 1.4426950408889634f, kpad, dqkv, lse);
   else
-    attn_bwd_mma_kernel<16><<<grid, 512, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
+    attn_bwd_mma_kernel<16, 2><<<grid, 512, smem, st>>>(qkv, out, dout, order, windows, n_windows, h, scale,
                                                      scale * 1.4426950408889634f, kpad, dqkv, lse);
   return check_launch();
 }
