@@ -257,6 +257,22 @@ int ptv3_keypoint_aggregate(const float* coord, const float* pred, const int64_t
                             int mode, float mask_thresh, float* out, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * A10  validation metric of the offset head (hooks/offset_keypoint_evaluator.py:46-91): per scene b
+ * and keypoint k
+ *   gt[b,k]    = mean over the scene's rows with target[i,k,3] > 0 of coord[i] + target[i,k,0:3]
+ *   kp[b,k]    = coord[i*] + pred[i*,k,0:3], i* = first argmax_i pred[i,k,3]
+ *   dist[b,k]  = |kp - gt|_2 * scale[b]   (scale NULL = 1),  valid[b,k] = 1;  no masked row: dist = 0, valid = 0 (skipped).
+ * coord (n,3), pred / target (n,k_pts,4) fp32, offset int64 (n_scenes) cumulative, scale fp32 (n_scenes) or NULL,
+ * dist fp32 / valid int32 (n_scenes,k_pts).
+ * acc: NULL, or (2 + 2*k_pts) doubles [total_dist, total_samples, dist_per_kp[k_pts], samples_per_kp[k_pts]] that the
+ * call UPDATES in the evaluator's own order (scene-major; per scene total_dist += mean of its valid distances) -- the
+ * running sums of a validation epoch stay on the device (the reference reads every distance with .item()).
+ * ------------------------------------------------------------------------- */
+int ptv3_keypoint_eval(const float* coord, const float* pred, const float* target, const int64_t* offset,
+                       const float* scale, int64_t n_scenes, int k_pts, float* dist, int32_t* valid, double* acc,
+                       void* stream);
+
+/* ---------------------------------------------------------------------------
  * backward of the ops that carry gradients (training step, engines/train.py:184-245 drives
  * loss.backward() through spconv / flash_attn / torch_scatter autograd functions in the reference).
  * All gradients are fp32; forward operands are `dtype` (PTV3_F32 / PTV3_BF16).

@@ -246,3 +246,44 @@ def aggregate_keypoints(coord, pred, mode="argmax", scale=1.0, centroid=0.0, mas
         else:
             out[k] = votes[conf[:, k].argmax(), k]
     return out
+
+
+def offset_keypoint_eval(coord, pred, target, offset, scale=None, acc=None):
+    """hooks/offset_keypoint_evaluator.py:46-91 for one batch (test infrastructure, CPU): per scene b / keypoint k the
+    ground truth is the mean of coord + target[:, k, :3] over the rows with target[:, k, 3] > 0 (keypoint skipped when
+    there are none), the prediction is the vote of the row with the highest predicted mask, the distance is their
+    L2 norm times scale[b].  Returns dist (B,K) fp32, valid (B,K) bool and `acc`, the evaluator's running sums
+    [total_dist, total_samples, dist_per_kp[K], samples_per_kp[K]] as Python floats, updated like lines 83-91."""
+    coord, pred, target = torch.as_tensor(coord), torch.as_tensor(pred), torch.as_tensor(target)
+    offset = [int(o) for o in offset]
+    K = pred.shape[1]
+    acc = [0.0] * (2 + 2 * K) if acc is None else list(acc)
+    dist = torch.zeros(len(offset), K, dtype=torch.float32)
+    valid = torch.zeros(len(offset), K, dtype=torch.bool)
+    for b, end in enumerate(offset):
+        start = offset[b - 1] if b else 0
+        c, p, t = coord[start:end], pred[start:end], target[start:end]
+        s = float(scale[b]) if scale is not None else 1.0
+        b_sum, b_n = 0.0, 0
+        for k in range(K):
+            idx = torch.nonzero(t[:, k, 3] > 0).squeeze(-1)
+            if len(idx) == 0:
+                continue
+            gt = (c[idx] + t[idx, k, :3]).mean(dim=0)
+            best = torch.argmax(p[:, k, 3])
+            d = torch.norm(c[best] + p[best, k, :3] - gt, p=2) * s
+            dist[b, k], valid[b, k] = d, True
+            acc[2 + k] += d.item()
+            acc[2 + K + k] += 1
+            b_sum += d.item()
+            b_n += 1
+        if b_n > 0:
+            acc[0] += b_sum / b_n
+            acc[1] += 1
+    return dist, valid, acc
+
+
+def offset_keypoint_eval_summary(acc, num_keypoints):
+    """mean_dist and the per-keypoint means the evaluator logs (offset_keypoint_evaluator.py:105-109)."""
+    K = num_keypoints
+    return acc[0] / (acc[1] + 1e-6), [acc[2 + k] / (acc[2 + K + k] + 1e-6) for k in range(K)]

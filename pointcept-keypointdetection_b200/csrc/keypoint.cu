@@ -92,3 +92,129 @@ extern "C" int ptv3_keypoint_aggregate(const float* coord, const float* pred, co
                                                                         out);
   return check_launch();
 }
+
+// A10: validation metric of the offset head (hooks/offset_keypoint_evaluator.py:46-91) on the device.
+//   gt[b,k]   = mean over the scene's rows with target[i,k,3] > 0 of coord[i] + target[i,k,:3]   (skipped if there are none)
+//   pred[b,k] = coord[i*] + pred[i*,k,:3], i* = first argmax_i pred[i,k,3]
+//   dist[b,k] = |pred - gt|_2 * scale[b]
+// One CTA per (scene, keypoint) streams the keypoint's 16-byte (dx,dy,dz,mask) records of `pred` and `target` once
+// (32 B / row algorithmic, coord rows only where the mask is set); fixed-order reduction.  keypoint_eval_accumulate then
+// folds (scenes, K) distances into the running sums in the reference's order (scene-major, double precision), so a
+// validation epoch needs one device->host read at its end instead of one .item() per scene and keypoint.
+namespace ptv3 {
+
+__global__ void __launch_bounds__(kKpThreads) keypoint_eval_kernel(const float* __restrict__ coord,
+                                                                   const float* __restrict__ pred,
+                                                                   const float* __restrict__ target,
+                                                                   const int64_t* __restrict__ offset,
+                                                                   const float* __restrict__ scale, int k_pts,
+                                                                   float* __restrict__ dist, int32_t* __restrict__ valid) {
+  const int b = blockIdx.x, k = blockIdx.y;
+  const int64_t start = b ? offset[b - 1] : 0, end = offset[b];
+  float best_v = -INFINITY;
+  int64_t best_i = INT64_MAX;
+  float gx = 0.f, gy = 0.f, gz = 0.f;
+  int cnt = 0;
+  for (int64_t i = start + threadIdx.x; i < end; i += kKpThreads) {
+    const float4 p = *reinterpret_cast<const float4*>(pred + (i * k_pts + k) * 4);
+    const float4 t = *reinterpret_cast<const float4*>(target + (i * k_pts + k) * 4);
+    if (p.w > best_v) {
+      best_v = p.w;
+      best_i = i;
+    }
+    if (t.w > 0.f) {
+      gx += coord[i * 3] + t.x;
+      gy += coord[i * 3 + 1] + t.y;
+      gz += coord[i * 3 + 2] + t.z;
+      ++cnt;
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best_v, d);
+    const int64_t oi = __shfl_xor_sync(0xffffffffu, best_i, d);
+    if (ov > best_v || (ov == best_v && oi < best_i)) {
+      best_v = ov;
+      best_i = oi;
+    }
+    gx += __shfl_xor_sync(0xffffffffu, gx, d);
+    gy += __shfl_xor_sync(0xffffffffu, gy, d);
+    gz += __shfl_xor_sync(0xffffffffu, gz, d);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, d);
+  }
+  __shared__ float s_v[kKpThreads / 32], s_g[kKpThreads / 32][3];
+  __shared__ int64_t s_i[kKpThreads / 32];
+  __shared__ int s_c[kKpThreads / 32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    s_v[warp] = best_v;
+    s_i[warp] = best_i;
+    s_g[warp][0] = gx; s_g[warp][1] = gy; s_g[warp][2] = gz;
+    s_c[warp] = cnt;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < kKpThreads / 32; ++w) {
+      if (s_v[w] > best_v || (s_v[w] == best_v && s_i[w] < best_i)) {
+        best_v = s_v[w];
+        best_i = s_i[w];
+      }
+      gx += s_g[w][0]; gy += s_g[w][1]; gz += s_g[w][2];
+      cnt += s_c[w];
+    }
+    const int64_t o = (int64_t)b * k_pts + k;
+    if (cnt == 0 || best_i == INT64_MAX) {
+      dist[o] = 0.f;
+      valid[o] = 0;
+    } else {
+      const float* p = pred + (best_i * k_pts + k) * 4;
+      const float dx = coord[best_i * 3] + p[0] - gx / (float)cnt;
+      const float dy = coord[best_i * 3 + 1] + p[1] - gy / (float)cnt;
+      const float dz = coord[best_i * 3 + 2] + p[2] - gz / (float)cnt;
+      const float nrm = sqrtf(dx * dx + dy * dy + dz * dz);
+      dist[o] = scale ? nrm * scale[b] : nrm;
+      valid[o] = 1;
+    }
+  }
+}
+
+// acc (2 + 2K) doubles: [total_dist, total_samples, dist_per_kp[K], samples_per_kp[K]] -- the evaluator's running sums,
+// updated in its own loop order (offset_keypoint_evaluator.py:47-91) by one thread: (scenes x K) is a few hundred values.
+__global__ void keypoint_eval_accumulate_kernel(const float* __restrict__ dist, const int32_t* __restrict__ valid,
+                                                int64_t n_scenes, int k_pts, double* __restrict__ acc) {
+  if (threadIdx.x || blockIdx.x) return;
+  double total = acc[0], samples = acc[1];
+  for (int64_t b = 0; b < n_scenes; ++b) {
+    double sum = 0.0;
+    int nv = 0;
+    for (int k = 0; k < k_pts; ++k) {
+      if (!valid[b * k_pts + k]) continue;
+      const double d = (double)dist[b * k_pts + k];
+      acc[2 + k] += d;
+      acc[2 + k_pts + k] += 1.0;
+      sum += d;
+      ++nv;
+    }
+    if (nv > 0) {
+      total += sum / nv;
+      samples += 1.0;
+    }
+  }
+  acc[0] = total;
+  acc[1] = samples;
+}
+
+}  // namespace ptv3
+
+extern "C" int ptv3_keypoint_eval(const float* coord, const float* pred, const float* target, const int64_t* offset,
+                                  const float* scale, int64_t n_scenes, int k_pts, float* dist, int32_t* valid,
+                                  double* acc, void* stream) {
+  if (n_scenes < 0 || k_pts < 1 || k_pts > 65535) return PTV3_EINVAL;
+  if (n_scenes == 0) return PTV3_OK;
+  if (!coord || !pred || !target || !offset || !dist || !valid) return PTV3_EINVAL;
+  dim3 grid((unsigned)n_scenes, (unsigned)k_pts);
+  keypoint_eval_kernel<<<grid, kKpThreads, 0, as_stream(stream)>>>(coord, pred, target, offset, scale, k_pts, dist,
+                                                                   valid);
+  if (acc) keypoint_eval_accumulate_kernel<<<1, 32, 0, as_stream(stream)>>>(dist, valid, n_scenes, k_pts, acc);
+  return check_launch();
+}

@@ -443,6 +443,31 @@ def keypoint_aggregate(coord, pred, offset, mode="argmax", mask_thresh=0.5):
     return out
 
 
+# ------------------------------------------------------------------ A10 offset-keypoint validation metric
+def keypoint_eval(coord, pred, target, offset, scale=None, acc=None):
+    """hooks/offset_keypoint_evaluator.py:46-91 for one batch: coord (N,3), pred / target (N,K,4) fp32, offset int64 (B),
+    scale fp32 (B) or None -> dist (B,K) fp32, valid (B,K) int32.  `acc`: float64 (2+2K) device tensor of the running sums
+    [total_dist, total_samples, dist_per_kp, samples_per_kp], updated in place (no host sync)."""
+    _need_cuda(coord, pred, target, offset)
+    lib = _lib.load()
+    coord, pred, target = coord.contiguous().float(), pred.contiguous().float(), target.contiguous().float()
+    offset = offset.contiguous().long()
+    n, k = pred.shape[0], pred.shape[1]
+    assert coord.shape == (n, 3) and pred.shape == (n, k, 4) and target.shape == (n, k, 4)
+    b = offset.numel()
+    if scale is not None:
+        scale = scale.contiguous().float()
+        assert scale.numel() == b and scale.is_cuda
+    if acc is not None:
+        assert acc.is_cuda and acc.dtype == torch.float64 and acc.is_contiguous() and acc.numel() == 2 + 2 * k
+    dist = torch.empty((b, k), dtype=torch.float32, device=pred.device)
+    valid = torch.empty((b, k), dtype=torch.int32, device=pred.device)
+    _lib.check(lib.ptv3_keypoint_eval(_p(coord), _p(pred), _p(target), _p(offset), _p(scale),
+                                      b, int(k), _p(dist), _p(valid), _p(acc), _stream()),
+               "ptv3_keypoint_eval")
+    return dist, valid
+
+
 # ------------------------------------------------------------------ A6 glue: per-channel affine + activation
 def affine_act(x, scale=None, shift=None, act="none", want_f32=True, want_bf16=False):
     """act(x * scale + shift) per channel in one pass -> (fp32 or None, bf16 or None).  act: none | gelu | relu."""

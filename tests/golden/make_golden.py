@@ -19,6 +19,9 @@ Fixtures (all inputs are seeded; the script is the provenance):
                      np.unique without the final index sort
   spunet.npz         reference SpUNetBase ("SpUNet-v1m1", 13 classes, C_in = 4) forward on a two-scene batch: the wiring of
                      BasicBlock / down / up / skip concatenation over the restated spconv ops (oracle/spunet.py)
+  eval.npz           reference OffsetKeypointEvaluator.eval() (hooks/offset_keypoint_evaluator.py) driven by a stub trainer
+                     over two validation batches (with / without `scale`, a keypoint without masked rows, a scene
+                     without any, a tied maximum of the predicted mask): the logged means and comm_info metric
   heads.npz          reference KeypointPTv3 (scatter_mean + regression MLP, C_in = 4) and
                      DefaultSegmentorV2 (20 classes, C_in = 6, BASELINE configs[2] shape)
                      forwards, one scene each, same deterministic weights
@@ -305,8 +308,44 @@ def gold_spunet(R):
                         logits=out.numpy())
 
 
+def gold_eval(R):
+    import importlib
+    import types
+    mod = importlib.import_module("pointcept.engines.hooks.offset_keypoint_evaluator")
+    from make_golden_names import eval_batches
+    batches = eval_batches()
+    logs, scalars = [], {}
+    loader = [{k: torch.from_numpy(v) for k, v in b.items()} for b in batches]
+
+    class Model(torch.nn.Module):
+        def forward(self, data_dict):
+            return dict(pred=data_dict["pred"])
+
+    trainer = types.SimpleNamespace(
+        model=Model(), val_loader=loader, epoch=0, comm_info={},
+        logger=types.SimpleNamespace(info=logs.append),
+        writer=types.SimpleNamespace(add_scalar=lambda name, v, step: scalars.__setitem__(name, (float(v), int(step)))))
+    hook = mod.OffsetKeypointEvaluator(num_keypoints=6)
+    hook.trainer = trainer
+    orig_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self         # the container has no GPU; the hook's arithmetic is untouched
+    try:
+        hook.after_epoch()
+    finally:
+        torch.Tensor.cuda = orig_cuda
+    print("eval:", logs[1], "|", trainer.comm_info)
+    out = {}                                               # inputs: make_golden_names.eval_batches() (seeded)
+    out["mean_dist"] = np.float64(-trainer.comm_info["current_metric_value"])
+    out["per_kp"] = np.array([scalars[f"val/KP_{k}_MeanDist"][0] for k in range(6)], dtype=np.float64)
+    out["logs"] = np.array(logs)
+    np.savez_compressed(os.path.join(HERE, "eval.npz"), **out)
+
+
 if __name__ == "__main__":
     R = ref_loader.load()
+    if sys.argv[1:] == ["eval"]:
+        gold_eval(R)
+        sys.exit(0)
     gold_serialization(R)
     gold_gridsample(R)
     gold_padding(R)
@@ -316,6 +355,7 @@ if __name__ == "__main__":
     gold_train(R)
     gold_voxelize(R)
     gold_spunet(R)
+    gold_eval(R)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -526,3 +526,62 @@ def test_fused_stem_equals_table_path():
     ref = torch.nn.functional.gelu(P._bn(O.subm_conv(cat(1).cpu(), O.subm_neighbor_table(idx, 5),
                                                      W["embedding.stem.conv.weight"], None), W, "embedding.stem.norm"))
     assert rel_l2(outs[0][0], ref) < 1e-5
+
+
+def test_keypoint_eval_matches_oracle_and_reference(golden):
+    """A10: ptv3_keypoint_eval (per-(scene, keypoint) distances + device-resident running sums) against
+    oracle.ptv3.offset_keypoint_eval and the unmodified evaluator's logged means (tests/golden/eval.npz): skipped
+    keypoints, a scene without valid keypoints, a tied predicted mask, batches with and without `scale`."""
+    from make_golden_names import eval_batches
+    from ptv3_b200 import ops
+    from ptv3_b200.evaluator import summarize
+    g = golden("eval")
+    acc = torch.zeros(2 + 2 * 6, dtype=torch.float64, device="cuda")
+    ref_acc = None
+    for b in eval_batches():
+        t = {k: torch.from_numpy(v).cuda() for k, v in b.items()}
+        dist, valid = ops.keypoint_eval(t["coord"], t["pred"], t["target"], t["offset"], t.get("scale"), acc=acc)
+        rd, rv, ref_acc = P.offset_keypoint_eval(b["coord"], b["pred"], b["target"], b["offset"], b.get("scale"), ref_acc)
+        assert torch.equal(valid.cpu().bool(), rv)
+        assert torch.allclose(dist.cpu(), rd, rtol=1e-5, atol=1e-5), (dist.cpu() - rd).abs().max()   # fp32 sum order
+    mean_dist, per_kp, counts = summarize(acc, 6)
+    assert abs(mean_dist - float(g["mean_dist"])) <= 1e-5 * float(g["mean_dist"])
+    assert np.allclose(per_kp, g["per_kp"], rtol=1e-5)
+    assert counts == [int(ref_acc[2 + 6 + k]) for k in range(6)] and acc[1].item() == ref_acc[1]
+    # ragged edge cases: an empty scene in the middle, a one-row scene, no accumulator
+    sizes = [1, 0, 4097]
+    gen = torch.Generator().manual_seed(3)
+    n = sum(sizes)
+    coord, pred = torch.randn(n, 3, generator=gen), torch.randn(n, 6, 4, generator=gen)
+    target = torch.randn(n, 6, 4, generator=gen)
+    offset = torch.tensor(sizes).cumsum(0)
+    dist, valid = ops.keypoint_eval(coord.cuda(), pred.cuda(), target.cuda(), offset.cuda())
+    rd, rv, _ = P.offset_keypoint_eval(coord, pred, target, offset)
+    assert torch.equal(valid.cpu().bool(), rv) and not valid[1].any()
+    assert torch.allclose(dist.cpu(), rd, rtol=1e-5, atol=1e-5)
+
+
+def test_offset_keypoint_evaluator_hook(golden):
+    """The drop-in hook (ptv3_b200.evaluator.OffsetKeypointEvaluator) driven like the reference's by a trainer object:
+    same log lines, writer scalars and comm_info metric as hooks/offset_keypoint_evaluator.py produced for eval.npz."""
+    import types
+    from make_golden_names import eval_batches
+    from ptv3_b200.evaluator import OffsetKeypointEvaluator
+    g = golden("eval")
+    logs, scalars = [], {}
+
+    class Model(torch.nn.Module):
+        def forward(self, data_dict):
+            return dict(pred=data_dict["pred"])
+
+    loader = [{k: torch.from_numpy(v) for k, v in b.items()} for b in eval_batches()]        # host tensors, as a DataLoader yields
+    trainer = types.SimpleNamespace(
+        model=Model(), val_loader=loader, epoch=0, comm_info={}, logger=types.SimpleNamespace(info=logs.append),
+        writer=types.SimpleNamespace(add_scalar=lambda name, v, step: scalars.__setitem__(name, (float(v), int(step)))))
+    hook = OffsetKeypointEvaluator(num_keypoints=6)
+    hook.trainer = trainer
+    hook.after_epoch()
+    assert logs == [str(s) for s in g["logs"]]                        # 4-decimal log lines identical to the reference's
+    assert trainer.comm_info["current_metric_name"] == "mean_dist"
+    assert abs(-trainer.comm_info["current_metric_value"] - float(g["mean_dist"])) <= 1e-5 * float(g["mean_dist"])
+    assert scalars["val/MeanDist"][1] == 1 and len(scalars) == 7

@@ -166,3 +166,35 @@ def test_grad_sync_world_size_2_gloo():
             for a, b in zip(res[r][1][step], want):
                 assert torch.allclose(torch.from_numpy(a), b, atol=1e-6)
     assert all((r[2] == 0).all() for r in res)
+
+
+def _eval_reduce_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from ptv3_b200.evaluator import reduce_sums, summarize
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        k = 3          # per-rank running sums [total_dist, total_samples, dist_per_kp[k], samples_per_kp[k]]
+        acc = torch.tensor([[4.0, 2, 1.5, 2.5, 0.0, 2, 2, 0], [9.0, 3, 3.0, 3.0, 3.0, 3, 3, 1]][rank], dtype=torch.float64)
+        q.put((rank,) + summarize(reduce_sums(acc), k))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_evaluator_sums_world_size_2_gloo():
+    """Validation metric across ranks (offset_keypoint_evaluator.py:94-103): the (2 + 2K) sums are all-reduced, then every
+    rank derives the same means."""
+    import torch.multiprocessing as mp
+    world, port = 2, 29500 + (os.getpid() % 2000) + 11
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_eval_reduce_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, mean_dist, per_kp, counts in res:
+        assert mean_dist == 13.0 / (5 + 1e-6)
+        assert per_kp == [4.5 / (5 + 1e-6), 5.5 / (5 + 1e-6), 3.0 / (1 + 1e-6)] and counts == [5, 5, 1]

@@ -237,3 +237,17 @@ def test_spunet_forward_vs_reference(golden):
     out_idx, cluster, koff = U.down_map(idx)
     assert torch.equal(out_idx[cluster].long()[:, 1:], idx[:, 1:] >> 1) and int(koff.min()) >= 0 and int(koff.max()) <= 7
     assert torch.unique(torch.stack([cluster, koff], 1), dim=0).shape[0] == idx.shape[0]
+
+
+def test_offset_keypoint_eval_vs_reference(golden):
+    """oracle.ptv3.offset_keypoint_eval pinned to the unmodified OffsetKeypointEvaluator.eval() (tests/golden/eval.npz,
+    make_golden.py::gold_eval): the logged mean distance and the per-keypoint means over two validation batches."""
+    from make_golden_names import eval_batches
+    g = golden("eval")
+    acc = None
+    for b in eval_batches():
+        dist, valid, acc = P.offset_keypoint_eval(b["coord"], b["pred"], b["target"], b["offset"], b.get("scale"), acc)
+    mean_dist, per_kp = P.offset_keypoint_eval_summary(acc, 6)
+    assert mean_dist == float(g["mean_dist"])                         # same arithmetic in the same order: exact
+    assert np.array_equal(np.array(per_kp), g["per_kp"])
+    assert acc[1] == 4 and acc[2 + 6 + 2] == 3                        # scene 1 of batch 0 not a sample; keypoint 2 skipped once
