@@ -267,10 +267,14 @@ int ptv3_keypoint_aggregate(const float* coord, const float* pred, const int64_t
  * acc: NULL, or (2 + 2*k_pts) doubles [total_dist, total_samples, dist_per_kp[k_pts], samples_per_kp[k_pts]] that the
  * call UPDATES in the evaluator's own order (scene-major; per scene total_dist += mean of its valid distances) -- the
  * running sums of a validation epoch stay on the device (the reference reads every distance with .item()).
+ * workspace: NULL (one CTA per scene and keypoint) or ptv3_keypoint_eval_workspace(n_rows, n_scenes, k_pts) bytes: each
+ * scene is then split over enough CTAs to fill the 148 SMs (contiguous whole-row reads, partials combined in a fixed order;
+ * the query returns 0 when the batch is too small to split).  Both forms give the same argmax row and valid flags.
  * ------------------------------------------------------------------------- */
+size_t ptv3_keypoint_eval_workspace(int64_t n_rows, int64_t n_scenes, int k_pts);
 int ptv3_keypoint_eval(const float* coord, const float* pred, const float* target, const int64_t* offset,
-                       const float* scale, int64_t n_scenes, int k_pts, float* dist, int32_t* valid, double* acc,
-                       void* stream);
+                       const float* scale, int64_t n_rows, int64_t n_scenes, int k_pts, float* dist, int32_t* valid,
+                       double* acc, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------
  * backward of the ops that carry gradients (training step, engines/train.py:184-245 drives

@@ -65,7 +65,8 @@ SIGNATURES = {
     "ptv3_sparse_pair_maps": (c_int, [c_vp, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "ptv3_column_sum": (c_int, [c_vp, c_int, c_i64, c_int, c_vp, c_vp]),
     "ptv3_keypoint_aggregate": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_f32, c_vp, c_vp]),
-    "ptv3_keypoint_eval": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "ptv3_keypoint_eval_workspace": (c_sz, [c_i64, c_i64, c_int]),
+    "ptv3_keypoint_eval": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
 }
 
 _lib = None

@@ -179,42 +179,167 @@ __global__ void __launch_bounds__(kKpThreads) keypoint_eval_kernel(const float* 
 }
 
 // acc (2 + 2K) doubles: [total_dist, total_samples, dist_per_kp[K], samples_per_kp[K]] -- the evaluator's running sums,
-// updated in its own loop order (offset_keypoint_evaluator.py:47-91) by one thread: (scenes x K) is a few hundred values.
+// updated in its own loop order (offset_keypoint_evaluator.py:47-91): warp 0 owns the per-keypoint sums (a lane per
+// keypoint, scenes in order, sums in registers), one lane of warp 1 the per-scene means; (scenes x K) is a few hundred values.
 __global__ void keypoint_eval_accumulate_kernel(const float* __restrict__ dist, const int32_t* __restrict__ valid,
                                                 int64_t n_scenes, int k_pts, double* __restrict__ acc) {
-  if (threadIdx.x || blockIdx.x) return;
-  double total = acc[0], samples = acc[1];
-  for (int64_t b = 0; b < n_scenes; ++b) {
-    double sum = 0.0;
-    int nv = 0;
-    for (int k = 0; k < k_pts; ++k) {
-      if (!valid[b * k_pts + k]) continue;
-      const double d = (double)dist[b * k_pts + k];
-      acc[2 + k] += d;
-      acc[2 + k_pts + k] += 1.0;
-      sum += d;
-      ++nv;
+  if (threadIdx.x < 32) {
+    for (int k = threadIdx.x; k < k_pts; k += 32) {
+      double sum = acc[2 + k], cnt = acc[2 + k_pts + k];
+      for (int64_t b = 0; b < n_scenes; ++b) {
+        if (!valid[b * k_pts + k]) continue;
+        sum += (double)dist[b * k_pts + k];
+        cnt += 1.0;
+      }
+      acc[2 + k] = sum;
+      acc[2 + k_pts + k] = cnt;
     }
-    if (nv > 0) {
-      total += sum / nv;
-      samples += 1.0;
+  } else if (threadIdx.x == 32) {
+    double total = acc[0], samples = acc[1];
+    for (int64_t b = 0; b < n_scenes; ++b) {
+      double sum = 0.0;
+      int nv = 0;
+      for (int k = 0; k < k_pts; ++k) {
+        if (!valid[b * k_pts + k]) continue;
+        sum += (double)dist[b * k_pts + k];
+        ++nv;
+      }
+      if (nv > 0) {
+        total += sum / nv;
+        samples += 1.0;
+      }
     }
+    acc[0] = total;
+    acc[1] = samples;
   }
-  acc[0] = total;
-  acc[1] = samples;
 }
 
 }  // namespace ptv3
 
+// Split form of keypoint_eval_kernel for grids that fill the 148 SMs: CTA (scene, split) streams a contiguous slice of the
+// scene's rows -- whole (K x 16 B) records of `pred` and `target`, consecutive threads on consecutive 16-byte records --
+// and keeps one partial per keypoint; thread t always sees keypoint t % K because the block size is a multiple of K.
+// Partials are combined in a fixed order (shared-memory tree inside the CTA, ascending splits in keypoint_eval_finish).
+namespace ptv3 {
+
+struct __align__(16) EvalPartial {
+  float best_v, gx, gy, gz;
+  int64_t best_i;
+  int cnt, pad;
+};
+
+__device__ __forceinline__ void eval_merge(EvalPartial& a, const EvalPartial& o) {
+  if (o.best_v > a.best_v || (o.best_v == a.best_v && o.best_i < a.best_i)) {
+    a.best_v = o.best_v;
+    a.best_i = o.best_i;
+  }
+  a.gx += o.gx; a.gy += o.gy; a.gz += o.gz;
+  a.cnt += o.cnt;
+}
+
+__global__ void __launch_bounds__(kKpThreads) keypoint_eval_split_kernel(const float* __restrict__ coord,
+                                                                         const float* __restrict__ pred,
+                                                                         const float* __restrict__ target,
+                                                                         const int64_t* __restrict__ offset, int k_pts,
+                                                                         EvalPartial* __restrict__ partials) {
+  __shared__ EvalPartial s_p[kKpThreads];
+  const int b = blockIdx.x, split = blockIdx.y, n_split = gridDim.y;
+  const int64_t start = b ? offset[b - 1] : 0, end = offset[b], len = end > start ? end - start : 0;
+  const int64_t r0 = start + len * split / n_split, r1 = start + len * (split + 1) / n_split;
+  const int t = threadIdx.x, T = blockDim.x, k = t % k_pts;
+  EvalPartial me{-INFINITY, 0.f, 0.f, 0.f, INT64_MAX, 0, 0};
+  const float4* p4 = reinterpret_cast<const float4*>(pred) + r0 * k_pts;
+  const float4* t4 = reinterpret_cast<const float4*>(target) + r0 * k_pts;
+  const int64_t n_rec = (r1 - r0) * k_pts;
+  for (int64_t r = t; r < n_rec; r += T) {
+    const float4 p = p4[r];
+    const float4 g = t4[r];
+    const int64_t i = r0 + r / k_pts;
+    if (p.w > me.best_v) {   // ascending rows per thread: the first maximum wins
+      me.best_v = p.w;
+      me.best_i = i;
+    }
+    if (g.w > 0.f) {
+      me.gx += coord[i * 3] + g.x;
+      me.gy += coord[i * 3 + 1] + g.y;
+      me.gz += coord[i * 3 + 2] + g.z;
+      ++me.cnt;
+    }
+  }
+  s_p[t] = me;
+  __syncthreads();
+  const int G = T / k_pts, g = t / k_pts;   // G threads per keypoint, tree over them
+  for (int h = 256; h > 0; h >>= 1) {
+    if (g < h && g + h < G) {
+      eval_merge(me, s_p[t + h * k_pts]);
+      s_p[t] = me;
+    }
+    __syncthreads();
+  }
+  if (t < k_pts) partials[((int64_t)b * n_split + split) * k_pts + t] = me;
+}
+
+__global__ void keypoint_eval_finish_kernel(const float* __restrict__ coord, const float* __restrict__ pred,
+                                            const float* __restrict__ scale, const EvalPartial* __restrict__ partials,
+                                            int n_split, int k_pts, float* __restrict__ dist,
+                                            int32_t* __restrict__ valid) {
+  const int b = blockIdx.x;
+  for (int k = threadIdx.x; k < k_pts; k += blockDim.x) {
+    EvalPartial a = partials[(int64_t)b * n_split * k_pts + k];
+    for (int s = 1; s < n_split; ++s) eval_merge(a, partials[((int64_t)b * n_split + s) * k_pts + k]);
+    const int64_t o = (int64_t)b * k_pts + k;
+    if (a.cnt == 0 || a.best_i == INT64_MAX) {
+      dist[o] = 0.f;
+      valid[o] = 0;
+    } else {
+      const float* p = pred + (a.best_i * k_pts + k) * 4;
+      const float dx = coord[a.best_i * 3] + p[0] - a.gx / (float)a.cnt;
+      const float dy = coord[a.best_i * 3 + 1] + p[1] - a.gy / (float)a.cnt;
+      const float dz = coord[a.best_i * 3 + 2] + p[2] - a.gz / (float)a.cnt;
+      const float nrm = sqrtf(dx * dx + dy * dy + dz * dz);
+      dist[o] = scale ? nrm * scale[b] : nrm;
+      valid[o] = 1;
+    }
+  }
+}
+
+// splits per scene: ~4 CTAs per SM over the whole grid, at least ~1024 rows per CTA; 1 = single-pass kernel
+static int eval_splits(int64_t n_rows, int64_t n_scenes, int k_pts) {
+  if (n_scenes <= 0 || k_pts > kKpThreads) return 1;
+  int64_t s = (4 * kNumSMs + n_scenes - 1) / n_scenes;
+  const int64_t by_rows = n_rows / (n_scenes * 1024);
+  if (s > by_rows) s = by_rows;
+  if (s > 256) s = 256;
+  return s < 2 ? 1 : (int)s;
+}
+
+}  // namespace ptv3
+
+extern "C" size_t ptv3_keypoint_eval_workspace(int64_t n_rows, int64_t n_scenes, int k_pts) {
+  const int s = eval_splits(n_rows, n_scenes, k_pts);
+  return s > 1 ? (size_t)n_scenes * s * k_pts * sizeof(EvalPartial) : 0;
+}
+
 extern "C" int ptv3_keypoint_eval(const float* coord, const float* pred, const float* target, const int64_t* offset,
-                                  const float* scale, int64_t n_scenes, int k_pts, float* dist, int32_t* valid,
-                                  double* acc, void* stream) {
-  if (n_scenes < 0 || k_pts < 1 || k_pts > 65535) return PTV3_EINVAL;
+                                  const float* scale, int64_t n_rows, int64_t n_scenes, int k_pts, float* dist,
+                                  int32_t* valid, double* acc, void* workspace, size_t workspace_bytes, void* stream) {
+  if (n_scenes < 0 || n_rows < 0 || k_pts < 1 || k_pts > 65535) return PTV3_EINVAL;
   if (n_scenes == 0) return PTV3_OK;
   if (!coord || !pred || !target || !offset || !dist || !valid) return PTV3_EINVAL;
-  dim3 grid((unsigned)n_scenes, (unsigned)k_pts);
-  keypoint_eval_kernel<<<grid, kKpThreads, 0, as_stream(stream)>>>(coord, pred, target, offset, scale, k_pts, dist,
-                                                                   valid);
-  if (acc) keypoint_eval_accumulate_kernel<<<1, 32, 0, as_stream(stream)>>>(dist, valid, n_scenes, k_pts, acc);
+  const int splits = workspace ? eval_splits(n_rows, n_scenes, k_pts) : 1;
+  if (splits > 1) {
+    if (workspace_bytes < (size_t)n_scenes * splits * k_pts * sizeof(EvalPartial)) return PTV3_EWORKSPACE;
+    EvalPartial* partials = static_cast<EvalPartial*>(workspace);
+    dim3 grid((unsigned)n_scenes, (unsigned)splits);
+    const int threads = k_pts * (kKpThreads / k_pts);
+    keypoint_eval_split_kernel<<<grid, threads, 0, as_stream(stream)>>>(coord, pred, target, offset, k_pts, partials);
+    keypoint_eval_finish_kernel<<<(unsigned)n_scenes, 32, 0, as_stream(stream)>>>(coord, pred, scale, partials, splits,
+                                                                                  k_pts, dist, valid);
+  } else {
+    dim3 grid((unsigned)n_scenes, (unsigned)k_pts);
+    keypoint_eval_kernel<<<grid, kKpThreads, 0, as_stream(stream)>>>(coord, pred, target, offset, scale, k_pts, dist,
+                                                                     valid);
+  }
+  if (acc) keypoint_eval_accumulate_kernel<<<1, 64, 0, as_stream(stream)>>>(dist, valid, n_scenes, k_pts, acc);
   return check_launch();
 }

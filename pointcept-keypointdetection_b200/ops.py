@@ -444,10 +444,11 @@ def keypoint_aggregate(coord, pred, offset, mode="argmax", mask_thresh=0.5):
 
 
 # ------------------------------------------------------------------ A10 offset-keypoint validation metric
-def keypoint_eval(coord, pred, target, offset, scale=None, acc=None):
+def keypoint_eval(coord, pred, target, offset, scale=None, acc=None, split=True):
     """hooks/offset_keypoint_evaluator.py:46-91 for one batch: coord (N,3), pred / target (N,K,4) fp32, offset int64 (B),
     scale fp32 (B) or None -> dist (B,K) fp32, valid (B,K) int32.  `acc`: float64 (2+2K) device tensor of the running sums
-    [total_dist, total_samples, dist_per_kp, samples_per_kp], updated in place (no host sync)."""
+    [total_dist, total_samples, dist_per_kp, samples_per_kp], updated in place (no host sync).  split=False keeps the
+    one-CTA-per-(scene, keypoint) kernel (no workspace)."""
     _need_cuda(coord, pred, target, offset)
     lib = _lib.load()
     coord, pred, target = coord.contiguous().float(), pred.contiguous().float(), target.contiguous().float()
@@ -462,8 +463,10 @@ def keypoint_eval(coord, pred, target, offset, scale=None, acc=None):
         assert acc.is_cuda and acc.dtype == torch.float64 and acc.is_contiguous() and acc.numel() == 2 + 2 * k
     dist = torch.empty((b, k), dtype=torch.float32, device=pred.device)
     valid = torch.empty((b, k), dtype=torch.int32, device=pred.device)
-    _lib.check(lib.ptv3_keypoint_eval(_p(coord), _p(pred), _p(target), _p(offset), _p(scale),
-                                      b, int(k), _p(dist), _p(valid), _p(acc), _stream()),
+    ws_bytes = lib.ptv3_keypoint_eval_workspace(n, b, int(k)) if split else 0
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=pred.device) if ws_bytes else None
+    _lib.check(lib.ptv3_keypoint_eval(_p(coord), _p(pred), _p(target), _p(offset), _p(scale), n, b, int(k), _p(dist),
+                                      _p(valid), _p(acc), _p(ws), ws_bytes, _stream()),
                "ptv3_keypoint_eval")
     return dist, valid
 

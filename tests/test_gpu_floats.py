@@ -548,17 +548,32 @@ def test_keypoint_eval_matches_oracle_and_reference(golden):
     assert abs(mean_dist - float(g["mean_dist"])) <= 1e-5 * float(g["mean_dist"])
     assert np.allclose(per_kp, g["per_kp"], rtol=1e-5)
     assert counts == [int(ref_acc[2 + 6 + k]) for k in range(6)] and acc[1].item() == ref_acc[1]
-    # ragged edge cases: an empty scene in the middle, a one-row scene, no accumulator
-    sizes = [1, 0, 4097]
+
+
+@pytest.mark.parametrize("split", [False, True])
+@pytest.mark.parametrize("K", [6, 5])
+def test_keypoint_eval_ragged(split, K):
+    """A10 on ragged scenes large enough for the split form (several CTAs per scene, whole-row reads): an empty scene in
+    the middle, a one-row scene, a sparse mask, tied maxima across split borders (the first row wins), no accumulator;
+    K = 5 makes the block size (510 / 5 = 102 threads per keypoint) and the tree reduction uneven."""
+    from ptv3_b200 import _lib, ops
+    sizes = [1, 0, 40001, 3000]
     gen = torch.Generator().manual_seed(3)
     n = sum(sizes)
-    coord, pred = torch.randn(n, 3, generator=gen), torch.randn(n, 6, 4, generator=gen)
-    target = torch.randn(n, 6, 4, generator=gen)
+    coord, pred = torch.randn(n, 3, generator=gen), torch.randn(n, K, 4, generator=gen)
+    target = torch.randn(n, K, 4, generator=gen) * 0.1
+    target[..., 3] = (torch.rand(n, K, generator=gen) < 0.02).float()
+    target[1:, 1, 3] = 0.0                                            # keypoint 1 masked nowhere in the big scenes
+    pred[[500, 20000, 39000], 2, 3] = 9.0                             # ties in different splits of scene 2
     offset = torch.tensor(sizes).cumsum(0)
-    dist, valid = ops.keypoint_eval(coord.cuda(), pred.cuda(), target.cuda(), offset.cuda())
+    assert (_lib.load().ptv3_keypoint_eval_workspace(n, len(sizes), K) > 0)
+    dist, valid = ops.keypoint_eval(coord.cuda(), pred.cuda(), target.cuda(), offset.cuda(), split=split)
     rd, rv, _ = P.offset_keypoint_eval(coord, pred, target, offset)
-    assert torch.equal(valid.cpu().bool(), rv) and not valid[1].any()
-    assert torch.allclose(dist.cpu(), rd, rtol=1e-5, atol=1e-5)
+    assert torch.equal(valid.cpu().bool(), rv) and not valid[1].any() and not valid[2:, 1].any()
+    assert torch.allclose(dist.cpu(), rd, rtol=2e-5, atol=2e-5), (dist.cpu() - rd).abs().max()
+    # the tied maximum resolves to row 500 of scene 2 in both forms: identical prediction vote -> same distance
+    other = ops.keypoint_eval(coord.cuda(), pred.cuda(), target.cuda(), offset.cuda(), split=not split)[0]
+    assert torch.allclose(dist, other, rtol=2e-5, atol=2e-5)
 
 
 def test_offset_keypoint_evaluator_hook(golden):
