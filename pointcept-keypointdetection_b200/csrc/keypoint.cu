@@ -237,7 +237,7 @@ __device__ __forceinline__ void eval_merge(EvalPartial& a, const EvalPartial& o)
   a.cnt += o.cnt;
 }
 
-__global__ void __launch_bounds__(kKpThreads) keypoint_eval_split_kernel(const float* __restrict__ coord,
+__global__ void __launch_bounds__(kKpThreads, 2) keypoint_eval_split_kernel(const float* __restrict__ coord,
                                                                          const float* __restrict__ pred,
                                                                          const float* __restrict__ target,
                                                                          const int64_t* __restrict__ offset, int k_pts,
@@ -246,15 +246,12 @@ __global__ void __launch_bounds__(kKpThreads) keypoint_eval_split_kernel(const f
   const int b = blockIdx.x, split = blockIdx.y, n_split = gridDim.y;
   const int64_t start = b ? offset[b - 1] : 0, end = offset[b], len = end > start ? end - start : 0;
   const int64_t r0 = start + len * split / n_split, r1 = start + len * (split + 1) / n_split;
-  const int t = threadIdx.x, T = blockDim.x, k = t % k_pts;
+  const int t = threadIdx.x, T = blockDim.x, G = T / k_pts;   // thread t: keypoint t % K, rows t / K + j * G
   EvalPartial me{-INFINITY, 0.f, 0.f, 0.f, INT64_MAX, 0, 0};
   const float4* p4 = reinterpret_cast<const float4*>(pred) + r0 * k_pts;
   const float4* t4 = reinterpret_cast<const float4*>(target) + r0 * k_pts;
   const int64_t n_rec = (r1 - r0) * k_pts;
-  for (int64_t r = t; r < n_rec; r += T) {
-    const float4 p = p4[r];
-    const float4 g = t4[r];
-    const int64_t i = r0 + r / k_pts;
+  auto consume = [&](const float4& p, const float4& g, int64_t i) {
     if (p.w > me.best_v) {   // ascending rows per thread: the first maximum wins
       me.best_v = p.w;
       me.best_i = i;
@@ -265,10 +262,22 @@ __global__ void __launch_bounds__(kKpThreads) keypoint_eval_split_kernel(const f
       me.gz += coord[i * 3 + 2] + g.z;
       ++me.cnt;
     }
+  };
+  int64_t r = t, row = r0 + t / k_pts;
+  for (; r + 3 * (int64_t)T < n_rec; r += 4 * T, row += 4 * G) {   // 8 independent 16-byte loads in flight per thread
+    float4 p[4], g[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      p[u] = __ldcs(p4 + r + u * T);
+      g[u] = __ldcs(t4 + r + u * T);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) consume(p[u], g[u], row + u * G);
   }
+  for (; r < n_rec; r += T, row += G) consume(__ldcs(p4 + r), __ldcs(t4 + r), row);
   s_p[t] = me;
   __syncthreads();
-  const int G = T / k_pts, g = t / k_pts;   // G threads per keypoint, tree over them
+  const int g = t / k_pts;   // G threads per keypoint, tree over them
   for (int h = 256; h > 0; h >>= 1) {
     if (g < h && g + h < G) {
       eval_merge(me, s_p[t + h * k_pts]);
@@ -279,37 +288,78 @@ __global__ void __launch_bounds__(kKpThreads) keypoint_eval_split_kernel(const f
   if (t < k_pts) partials[((int64_t)b * n_split + split) * k_pts + t] = me;
 }
 
-__global__ void keypoint_eval_finish_kernel(const float* __restrict__ coord, const float* __restrict__ pred,
-                                            const float* __restrict__ scale, const EvalPartial* __restrict__ partials,
-                                            int n_split, int k_pts, float* __restrict__ dist,
-                                            int32_t* __restrict__ valid) {
-  const int b = blockIdx.x;
-  for (int k = threadIdx.x; k < k_pts; k += blockDim.x) {
-    EvalPartial a = partials[(int64_t)b * n_split * k_pts + k];
-    for (int s = 1; s < n_split; ++s) eval_merge(a, partials[((int64_t)b * n_split + s) * k_pts + k]);
-    const int64_t o = (int64_t)b * k_pts + k;
-    if (a.cnt == 0 || a.best_i == INT64_MAX) {
-      dist[o] = 0.f;
-      valid[o] = 0;
-    } else {
+constexpr int kEvalStage = 4096;   // (scene, keypoint) pairs staged in shared memory by the finish kernel
+
+// One CTA: merges the splits of every (scene, keypoint) in ascending order, writes dist / valid and, when `acc` is given,
+// folds them into the running sums from shared memory (see keypoint_eval_accumulate_kernel for the order).
+__global__ void __launch_bounds__(256) keypoint_eval_finish_kernel(const float* __restrict__ coord,
+                                                                   const float* __restrict__ pred,
+                                                                   const float* __restrict__ scale,
+                                                                   const EvalPartial* __restrict__ partials, int n_split,
+                                                                   int64_t n_scenes, int k_pts, float* __restrict__ dist,
+                                                                   int32_t* __restrict__ valid, double* __restrict__ acc) {
+  __shared__ float s_d[kEvalStage];   // distance, < 0 = skipped keypoint
+  const int64_t n_pairs = n_scenes * k_pts;
+  for (int64_t o = threadIdx.x; o < n_pairs; o += blockDim.x) {
+    const int64_t b = o / k_pts;
+    const int k = (int)(o - b * k_pts);
+    EvalPartial a = partials[b * n_split * k_pts + k];
+    for (int s = 1; s < n_split; ++s) eval_merge(a, partials[(b * n_split + s) * k_pts + k]);
+    float d = -1.f;
+    if (a.cnt != 0 && a.best_i != INT64_MAX) {
       const float* p = pred + (a.best_i * k_pts + k) * 4;
       const float dx = coord[a.best_i * 3] + p[0] - a.gx / (float)a.cnt;
       const float dy = coord[a.best_i * 3 + 1] + p[1] - a.gy / (float)a.cnt;
       const float dz = coord[a.best_i * 3 + 2] + p[2] - a.gz / (float)a.cnt;
       const float nrm = sqrtf(dx * dx + dy * dy + dz * dz);
-      dist[o] = scale ? nrm * scale[b] : nrm;
-      valid[o] = 1;
+      d = scale ? nrm * scale[b] : nrm;
     }
+    dist[o] = d < 0.f ? 0.f : d;
+    valid[o] = d < 0.f ? 0 : 1;
+    if (o < kEvalStage) s_d[o] = d;
+  }
+  if (!acc) return;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    for (int k = threadIdx.x; k < k_pts; k += 32) {
+      double sum = acc[2 + k], cnt = acc[2 + k_pts + k];
+      for (int64_t b = 0; b < n_scenes; ++b) {
+        const float d = s_d[b * k_pts + k];
+        if (d < 0.f) continue;
+        sum += (double)d;
+        cnt += 1.0;
+      }
+      acc[2 + k] = sum;
+      acc[2 + k_pts + k] = cnt;
+    }
+  } else if (threadIdx.x == 32) {
+    double total = acc[0], samples = acc[1];
+    for (int64_t b = 0; b < n_scenes; ++b) {
+      double sum = 0.0;
+      int nv = 0;
+      for (int k = 0; k < k_pts; ++k) {
+        const float d = s_d[b * k_pts + k];
+        if (d < 0.f) continue;
+        sum += (double)d;
+        ++nv;
+      }
+      if (nv > 0) {
+        total += sum / nv;
+        samples += 1.0;
+      }
+    }
+    acc[0] = total;
+    acc[1] = samples;
   }
 }
 
-// splits per scene: ~4 CTAs per SM over the whole grid, at least ~1024 rows per CTA; 1 = single-pass kernel
+// splits per scene: one wave of 2 resident CTAs per SM over the whole grid (all CTAs run concurrently, no tail wave), at
+// least ~1024 rows per CTA; 1 = single-pass kernel
 static int eval_splits(int64_t n_rows, int64_t n_scenes, int k_pts) {
   if (n_scenes <= 0 || k_pts > kKpThreads) return 1;
-  int64_t s = (4 * kNumSMs + n_scenes - 1) / n_scenes;
+  int64_t s = 2 * kNumSMs / n_scenes;
   const int64_t by_rows = n_rows / (n_scenes * 1024);
   if (s > by_rows) s = by_rows;
-  if (s > 256) s = 256;
   return s < 2 ? 1 : (int)s;
 }
 
@@ -333,8 +383,10 @@ extern "C" int ptv3_keypoint_eval(const float* coord, const float* pred, const f
     dim3 grid((unsigned)n_scenes, (unsigned)splits);
     const int threads = k_pts * (kKpThreads / k_pts);
     keypoint_eval_split_kernel<<<grid, threads, 0, as_stream(stream)>>>(coord, pred, target, offset, k_pts, partials);
-    keypoint_eval_finish_kernel<<<(unsigned)n_scenes, 32, 0, as_stream(stream)>>>(coord, pred, scale, partials, splits,
-                                                                                  k_pts, dist, valid);
+    const bool fold = acc && n_scenes * k_pts <= kEvalStage;
+    keypoint_eval_finish_kernel<<<1, 256, 0, as_stream(stream)>>>(coord, pred, scale, partials, splits, n_scenes, k_pts,
+                                                                  dist, valid, fold ? acc : nullptr);
+    if (fold) acc = nullptr;
   } else {
     dim3 grid((unsigned)n_scenes, (unsigned)k_pts);
     keypoint_eval_kernel<<<grid, kKpThreads, 0, as_stream(stream)>>>(coord, pred, target, offset, scale, k_pts, dist,
