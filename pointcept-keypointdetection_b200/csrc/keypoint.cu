@@ -290,9 +290,9 @@ __global__ void __launch_bounds__(kKpThreads, 2) keypoint_eval_split_kernel(cons
 
 constexpr int kEvalStage = 4096;   // (scene, keypoint) pairs staged in shared memory by the finish kernel
 
-// One CTA: merges the splits of every (scene, keypoint) in ascending order, writes dist / valid and, when `acc` is given,
+// One CTA of 32 warps: merges the splits of every (scene, keypoint) in a fixed order, writes dist / valid and, when `acc` is given,
 // folds them into the running sums from shared memory (see keypoint_eval_accumulate_kernel for the order).
-__global__ void __launch_bounds__(256) keypoint_eval_finish_kernel(const float* __restrict__ coord,
+__global__ void __launch_bounds__(1024) keypoint_eval_finish_kernel(const float* __restrict__ coord,
                                                                    const float* __restrict__ pred,
                                                                    const float* __restrict__ scale,
                                                                    const EvalPartial* __restrict__ partials, int n_split,
@@ -300,11 +300,24 @@ __global__ void __launch_bounds__(256) keypoint_eval_finish_kernel(const float* 
                                                                    int32_t* __restrict__ valid, double* __restrict__ acc) {
   __shared__ float s_d[kEvalStage];   // distance, < 0 = skipped keypoint
   const int64_t n_pairs = n_scenes * k_pts;
-  for (int64_t o = threadIdx.x; o < n_pairs; o += blockDim.x) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, n_warps = blockDim.x >> 5;
+  for (int64_t o = warp; o < n_pairs; o += n_warps) {   // a warp per (scene, keypoint), a lane per split: one load latency
     const int64_t b = o / k_pts;
     const int k = (int)(o - b * k_pts);
-    EvalPartial a = partials[b * n_split * k_pts + k];
-    for (int s = 1; s < n_split; ++s) eval_merge(a, partials[(b * n_split + s) * k_pts + k]);
+    EvalPartial a{-INFINITY, 0.f, 0.f, 0.f, INT64_MAX, 0, 0};
+    for (int s = lane; s < n_split; s += 32) eval_merge(a, partials[(b * n_split + s) * k_pts + k]);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {   // butterfly: every lane ends with the same merged partial, fixed order
+      EvalPartial q;
+      q.best_v = __shfl_xor_sync(0xffffffffu, a.best_v, d);
+      q.best_i = __shfl_xor_sync(0xffffffffu, a.best_i, d);
+      q.gx = __shfl_xor_sync(0xffffffffu, a.gx, d);
+      q.gy = __shfl_xor_sync(0xffffffffu, a.gy, d);
+      q.gz = __shfl_xor_sync(0xffffffffu, a.gz, d);
+      q.cnt = __shfl_xor_sync(0xffffffffu, a.cnt, d);
+      eval_merge(a, q);
+    }
+    if (lane) continue;
     float d = -1.f;
     if (a.cnt != 0 && a.best_i != INT64_MAX) {
       const float* p = pred + (a.best_i * k_pts + k) * 4;
@@ -384,7 +397,7 @@ extern "C" int ptv3_keypoint_eval(const float* coord, const float* pred, const f
     const int threads = k_pts * (kKpThreads / k_pts);
     keypoint_eval_split_kernel<<<grid, threads, 0, as_stream(stream)>>>(coord, pred, target, offset, k_pts, partials);
     const bool fold = acc && n_scenes * k_pts <= kEvalStage;
-    keypoint_eval_finish_kernel<<<1, 256, 0, as_stream(stream)>>>(coord, pred, scale, partials, splits, n_scenes, k_pts,
+    keypoint_eval_finish_kernel<<<1, 1024, 0, as_stream(stream)>>>(coord, pred, scale, partials, splits, n_scenes, k_pts,
                                                                   dist, valid, fold ? acc : nullptr);
     if (fold) acc = nullptr;
   } else {
