@@ -1,5 +1,6 @@
 """Full-size checks (BASELINE.json configs[1]: 16 scenes x 100 000 raw points -> ~1.17 M voxels) through
-size-independent properties: the oracle cannot run these sizes in seconds, the invariants can be checked exactly.
+size-independent properties that can be checked exactly on the whole batch.  The floating-point comparison with the
+oracle at these sizes (one scene = ~1.5 s of oracle time) lives in tests/test_gpu_parity_fullsize.py.
 
   GridSample     keys strictly increasing, counts sum to R, inverse consistent, idempotent on its own output
   serialization  code[order] non-decreasing per row, inverse o order = identity, scenes stay contiguous
