@@ -201,9 +201,11 @@ int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, i
  * for p in the window's queries, j in the window's keys, row(p) = order ? order[p] : p.
  * qkv (n,3,h,d) packed rows (= Linear(C,3C) output, :184-190 / flash layout :208-215);
  * out (n,h,d) in storage order (the reference's feat[inverse], :216-218). d == 16.
- * algo: 0 auto (bf16 -> 2, fp32 -> 1), 1 CUDA-core fp32-math kernel, 2 mma.sync tensor-core kernel (bf16),
- * 3 tcgen05/TMEM kernel (bf16, windows <= 1024).  At head_dim 16 the tcgen05 kernel is bound by the TMEM read
- * port (4 B per score at ~64 B/clk/SM = the same 16 scores/clk/SM as the exp unit), see DESIGN.md section 4. */
+ * algo: 0 auto (bf16 -> 4, fp32 -> 1), 1 CUDA-core fp32-math kernel, 2 first-generation mma.sync kernel (bf16 P),
+ * 3 tcgen05/TMEM kernel (bf16, windows <= 1024), 4 the default bf16 kernel (operands staged as f16 with the 32-byte
+ * swizzle, reference maximum folded into the accumulator, two query tiles per warp).
+ * A window record that breaks the contract of ptv3_build_windows (k_len > max_len, or queries outside the key range)
+ * makes its CTA return without writing and raises the sticky flag read by ptv3_device_error(). */
 int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order /* NULL = identity */, const int64_t* windows,
                          const int64_t* n_windows /* device scalar */, int64_t n_windows_max,
                          int64_t max_len /* upper bound of q_len and k_len */, int64_t n, int h, int d, float scale,
@@ -223,8 +225,13 @@ int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const 
                    const float* residual /* NULL ok */, int64_t n, int c, int hidden, float* res_out /* NULL ok */,
                    void* out_bf16 /* NULL ok */, void* stream);
 
-/* development knob (tests only): key 1 = operand-descriptor variant of the tcgen05 attention kernel */
+/* development knob (tests only): key 1 = operand-descriptor variant of the tcgen05 attention kernel, 7 = chunk /
+ * occupancy variant of the default attention kernel, 8 = kernel of the training forward */
 int ptv3_debug_set(int key, int value);
+
+/* Reads AND clears the library's sticky device-side error flag (0 = none, 1 = attention window contract violated).
+ * Synchronises the device (one 4-byte copy): meant for tests and for shims that forward caller-built records. */
+int ptv3_device_error(void);
 
 /* ---------------------------------------------------------------------------
  * Dense glue kernels of Block.forward (:318-338): fused residual + LayerNorm.

@@ -51,6 +51,7 @@ SIGNATURES = {
     "ptv3_mlp_fused_supported": (c_int, [c_int, c_int]),
     "ptv3_mlp_fused": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
     "ptv3_debug_set": (c_int, [c_int, c_int]),
+    "ptv3_device_error": (c_int, []),
     "ptv3_ln_residual": (c_int, [c_vp, c_int, c_vp, c_vp, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_i64, c_int,
                                  c_vp]),
     "ptv3_affine_act": (c_int, [c_vp, c_int, c_vp, c_vp, c_int, c_i64, c_int, c_vp, c_vp, c_vp]),

@@ -125,6 +125,14 @@ extern int g_attn_bwd_warps;
 int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                    int64_t n_windows_max, int64_t max_len, int64_t n, int h, float scale, __nv_bfloat16* out,
                    cudaStream_t st, float* lse = nullptr);
+// implemented in attn_f16.cu (the default bf16 kernel)
+int attn_window_f16(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
+                    int64_t n_windows_max, int64_t max_len, int h, float scale, __nv_bfloat16* out, cudaStream_t st,
+                    float* lse, int* err);
+int* attn_error_flag();
+int attn_error_fetch_and_clear();
+extern int g_attn_f16_variant;
+extern int g_attn_lse_algo;
 
 }  // namespace ptv3
 
@@ -142,7 +150,7 @@ int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, i
 int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const int64_t* windows,
                          const int64_t* n_windows, int64_t n_windows_max, int64_t max_len, int64_t n, int h, int d,
                          float scale, int algo, void* out, void* stream) {
-  if (n < 0 || h < 1 || h > 65535 || d != kAttnD || n_windows_max < 0 || max_len < 1 || algo < 0 || algo > 3)
+  if (n < 0 || h < 1 || h > 65535 || d != kAttnD || n_windows_max < 0 || max_len < 1 || algo < 0 || algo > 4)
     return PTV3_EINVAL;
   if (n == 0 || n_windows_max == 0) return PTV3_OK;
   if (!qkv || !windows || !n_windows || !out) return PTV3_EINVAL;
@@ -152,9 +160,12 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const
     return attn_window_tc05((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
                             (__nv_bfloat16*)out, st);
   }
-  if (dtype == PTV3_BF16 && algo != 1)
+  if (dtype == PTV3_BF16 && algo == 2)      // first-generation kernel (bf16 P, unswizzled K / V), kept for the ablation
     return attn_window_tc((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, n, h, scale,
                           (__nv_bfloat16*)out, st);
+  if (dtype == PTV3_BF16 && algo != 1)      // 0 (auto) / 4: the f16-staged register kernel
+    return attn_window_f16((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
+                           (__nv_bfloat16*)out, st, nullptr, attn_error_flag());
   if (algo >= 2) return PTV3_EUNSUPPORTED;
   int64_t qblocks = cdiv(max_len, kAttnThreads);
   if (qblocks > 65535) return PTV3_EINVAL;
@@ -177,6 +188,9 @@ int ptv3_attn_window_fwd_lse(const void* qkv, int dtype, const int64_t* order, c
   if (dtype != PTV3_BF16) return PTV3_EUNSUPPORTED;
   if (n == 0 || n_windows_max == 0) return PTV3_OK;
   if (!qkv || !windows || !n_windows || !out || !lse) return PTV3_EINVAL;
+  if (g_attn_lse_algo != 2)
+    return attn_window_f16((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
+                           (__nv_bfloat16*)out, as_stream(stream), lse, attn_error_flag());
   return attn_window_tc((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, n, h, scale,
                         (__nv_bfloat16*)out, as_stream(stream), lse);
 }
@@ -188,7 +202,11 @@ int ptv3_debug_set(int key, int value) {
   if (key == 4) { g_attn_bwd_simt = value; return PTV3_OK; }
   if (key == 5) { g_wgrad_simt = value; return PTV3_OK; }
   if (key == 6) { g_attn_bwd_warps = value; return PTV3_OK; }
+  if (key == 7) { g_attn_f16_variant = value; return PTV3_OK; }
+  if (key == 8) { g_attn_lse_algo = value; return PTV3_OK; }
   return PTV3_EINVAL;
 }
+
+int ptv3_device_error(void) { return attn_error_fetch_and_clear(); }
 
 }  // extern "C"

@@ -426,6 +426,16 @@ def attn_window(qkv, order, windows, n_windows, num_heads, max_len, scale=None, 
     return out
 
 
+def device_error():
+    """Reads and clears the library's sticky device-side error flag (synchronises): 0 = none, 1 = an attention window
+    record violated the build_windows contract (k_len > max_len or queries outside the key range)."""
+    return int(_lib.load().ptv3_device_error())
+
+
+def debug_set(key, value):
+    _lib.check(_lib.load().ptv3_debug_set(int(key), int(value)), "ptv3_debug_set")
+
+
 # ------------------------------------------------------------------ A9 keypoint aggregation (offset head)
 def keypoint_aggregate(coord, pred, offset, mode="argmax", mask_thresh=0.5):
     """coord (N,3) fp32, pred (N,K,4) fp32 [dx,dy,dz,conf], offset int64 (B) -> (B,K,3) fp32 keypoints in model

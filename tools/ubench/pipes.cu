@@ -1,0 +1,179 @@
+// Pipe-rate micro-benchmarks behind profiles/r02_attention.md: what bounds a head_dim-16 softmax on one B200 SM.
+// Each kernel runs ONE CTA per SM (148 CTAs) and times its own loop with clock64(), so the result is in
+// operations per SM clock and does not depend on the clock the box happens to run at.
+//   mufu_f32      ex2.approx.ftz.f32                      (MUFU.EX2)
+//   mufu_f16x2    ex2.approx.f16x2  -> 2 exps per PTX op  (SASS: two MUFU.EX2.F16 + PRMT)
+//   hmma          mma.sync.m16n8k16 f16 -> fp32           (legacy tensor path, HMMA)
+//   ldsm          ldmatrix.x4 (conflict-free)             (shared-memory pipe)
+//   ldtm          tcgen05.ld.32x32b.x32                   (TMEM read path), 4 / 8 / 16 warps
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/ubench/pipes tools/ubench/pipes.cu
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#define CHECK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e), __LINE__); return 1; } } while (0)
+
+constexpr int ITERS = 4096;
+
+__global__ void mufu_f32(float* out, long long* cyc, float seed) {
+  float v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = seed * (threadIdx.x + i) * 1e-6f;
+  __syncthreads();
+  long long t0 = clock64();
+  for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(v[i]));
+  }
+  long long t1 = clock64();
+  float s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+  if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+
+__global__ void mufu_f16x2(uint32_t* out, long long* cyc, uint32_t seed) {
+  uint32_t v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = seed + threadIdx.x + i;
+  __syncthreads();
+  long long t0 = clock64();
+  for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) asm volatile("ex2.approx.f16x2 %0, %0;" : "+r"(v[i]));
+  }
+  long long t1 = clock64();
+  uint32_t s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s ^= v[i];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+  if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+
+__global__ void hmma(float* out, long long* cyc, uint32_t seed) {
+  float c[4][4];
+  uint32_t a[4] = {seed, seed + 1, seed + 2, seed + 3}, b0 = seed + 4, b1 = seed + 5;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f;
+  __syncthreads();
+  long long t0 = clock64();
+  for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                   : "+f"(c[i][0]), "+f"(c[i][1]), "+f"(c[i][2]), "+f"(c[i][3])
+                   : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+  long long t1 = clock64();
+  float s = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) s += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+  if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+
+__global__ void ldsm(uint32_t* out, long long* cyc, int conflict) {
+  __shared__ __align__(128) unsigned char sm[32768];
+  for (int i = threadIdx.x; i < 8192; i += blockDim.x) reinterpret_cast<uint32_t*>(sm)[i] = i;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // conflict = 0: 32-byte rows with the 32-byte swizzle (attn_f16.cu); 1: plain 32-byte rows (the round-1 layout)
+  const uint32_t rsw = conflict ? 0u : (uint32_t)((lane >> 2) & 1);
+  uint32_t addr = (uint32_t)__cvta_generic_to_shared(sm) + (warp & 15) * 1024 +
+                  (uint32_t)((((lane >> 4) << 3) + (lane & 7)) * 32) + ((((uint32_t)(lane >> 3) & 1) ^ rsw) << 4);
+  uint32_t acc = 0;
+  long long t0 = clock64();
+  for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint32_t r0, r1, r2, r3;
+      asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr + ((i & 1) << 9)));
+      acc ^= r0 ^ r1 ^ r2 ^ r3;
+    }
+  }
+  long long t1 = clock64();
+  out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+  if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+
+__global__ void ldtm(uint32_t* out, long long* cyc) {
+  __shared__ uint32_t slot;
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((uint32_t)__cvta_generic_to_shared(&slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = slot + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) & 3) * 64;
+  uint32_t acc = 0;
+  long long t0 = clock64();
+  for (int it = 0; it < ITERS / 4; ++it) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      uint32_t v[32];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+            "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+            "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+            "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          : "r"(tmem + i * 32)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc ^= v[j];
+    }
+  }
+  long long t1 = clock64();
+  out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+  if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(slot) : "memory");
+}
+
+static double mean_cycles(long long* d_cyc, int n) {
+  static long long h[256];
+  cudaMemcpy(h, d_cyc, n * sizeof(long long), cudaMemcpyDeviceToHost);
+  double s = 0;
+  for (int i = 0; i < n; ++i) s += (double)h[i];
+  return s / n;
+}
+
+int main() {
+  const int G = 148;
+  void* out;
+  long long* cyc;
+  CHECK(cudaMalloc(&out, G * 1024 * 4));
+  CHECK(cudaMalloc(&cyc, G * sizeof(long long)));
+  for (int threads : {256, 512, 1024}) {
+    for (int rep = 0; rep < 2; ++rep) mufu_f32<<<G, threads>>>((float*)out, cyc, 1.f);
+    CHECK(cudaDeviceSynchronize());
+    printf("mufu_f32    %4d threads/SM: %6.2f exp/clk/SM\n", threads, (double)threads * ITERS * 8 / mean_cycles(cyc, G));
+    for (int rep = 0; rep < 2; ++rep) mufu_f16x2<<<G, threads>>>((uint32_t*)out, cyc, 7u);
+    CHECK(cudaDeviceSynchronize());
+    printf("mufu_f16x2  %4d threads/SM: %6.2f exp/clk/SM (2 per PTX op)\n", threads, (double)threads * ITERS * 16 / mean_cycles(cyc, G));
+    for (int rep = 0; rep < 2; ++rep) hmma<<<G, threads>>>((float*)out, cyc, 3u);
+    CHECK(cudaDeviceSynchronize());
+    double mm = (double)(threads / 32) * ITERS * 4 / mean_cycles(cyc, G);
+    printf("hmma        %4d threads/SM: %6.3f m16n8k16/clk/SM = %7.1f dense FLOP/clk/SM\n", threads, mm, mm * 4096);
+    for (int conflict = 0; conflict < 2; ++conflict) {
+      for (int rep = 0; rep < 2; ++rep) ldsm<<<G, threads>>>((uint32_t*)out, cyc, conflict);
+      CHECK(cudaDeviceSynchronize());
+      printf("ldsm.x4 %s %4d threads/SM: %6.1f B/clk/SM\n", conflict ? "plain 32B rows " : "32B-swizzled   ", threads,
+             (double)(threads / 32) * ITERS * 4 * 512 / mean_cycles(cyc, G));
+    }
+  }
+  for (int threads : {128, 256, 512}) {
+    for (int rep = 0; rep < 2; ++rep) ldtm<<<G, threads>>>((uint32_t*)out, cyc);
+    CHECK(cudaDeviceSynchronize());
+    printf("ldtm.x32    %4d threads/SM: %6.1f B/clk/SM (%5.1f fp32 scores/clk/SM)\n", threads,
+           (double)threads * (ITERS / 4) * 2 * 128 / mean_cycles(cyc, G), (double)threads * (ITERS / 4) * 2 * 32 / mean_cycles(cyc, G));
+  }
+  return 0;
+}
