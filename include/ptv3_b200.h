@@ -83,9 +83,12 @@ int ptv3_argsort_rows(const int64_t* code, int64_t rows, int64_t n, int key_bits
  * is the input array `rand` (NULL = first point of every voxel).
  *   coord      (r,3) float32
  *   grid_coord (r,3) int64   floor(coord/grid_size) - min   (all points)
- *   key        (r)   uint64  hash of grid_coord (hash_type 0 = fnv, 1 = ravel, 2 = ravel with the quotient
- *                            coord / grid_size rounded in float32: the A0' inference voxelisers,
- *                            tools/OffsetKeyPointPrediction_Qt.py:276-296, tools/pigseg_shared.py:132-146)
+ *   key        (r)   uint64  hash of grid_coord.  hash_type selects the hash AND the precision of the quotient
+ *                            coord / grid_size (transform.py:850): 0 = fnv, float64 quotient (numpy >= 2);
+ *                            1 = ravel, float64; 2 = ravel, float32; 3 = fnv, float32.  float32 is what the
+ *                            reference's pinned numpy 1.26.4 computes for float32 coordinates
+ *                            (uv_requirements.txt:84) and what the A0' inference voxelisers compute under any numpy
+ *                            (tools/OffsetKeyPointPrediction_Qt.py:276-296, tools/pigseg_shared.py:132-146)
  *   idx_sort   (r)   int64   stable argsort of key
  *   inverse    (r)   int64   voxel id of every point (ids in ascending-key order)
  *   count      (r)   int64   first *n_voxels entries valid: points per voxel
@@ -202,14 +205,18 @@ int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, i
  * qkv (n,3,h,d) packed rows (= Linear(C,3C) output, :184-190 / flash layout :208-215);
  * out (n,h,d) in storage order (the reference's feat[inverse], :216-218). d == 16.
  * algo: 0 auto (bf16 -> 4, fp32 -> 1), 1 CUDA-core fp32-math kernel, 2 first-generation mma.sync kernel (bf16 P),
- * 3 tcgen05/TMEM kernel (bf16, windows <= 1024), 4 the default bf16 kernel (operands staged as f16 with the 32-byte
- * swizzle, reference maximum folded into the accumulator, two query tiles per warp).
+ * 3 round-1 tcgen05/TMEM kernel (bf16, windows <= 1024, two-pass), 4 the register kernel (operands staged as f16 with
+ * the 32-byte swizzle, reference maximum folded into the accumulator, two query tiles per warp),
+ * 5 the single-pass tcgen05/TMEM kernel (bf16, windows <= 1024; needs ptv3_attn_window_workspace bytes; units it
+ * cannot finish safely are recomputed by kernel 4 inside the same call).
  * A window record that breaks the contract of ptv3_build_windows (k_len > max_len, or queries outside the key range)
  * makes its CTA return without writing and raises the sticky flag read by ptv3_device_error(). */
+size_t ptv3_attn_window_workspace(int64_t n_windows_max, int h);
 int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order /* NULL = identity */, const int64_t* windows,
                          const int64_t* n_windows /* device scalar */, int64_t n_windows_max,
                          int64_t max_len /* upper bound of q_len and k_len */, int64_t n, int h, int d, float scale,
-                         int algo, void* out, void* stream);
+                         int algo, void* out, void* workspace /* algo 5 only, else NULL ok */, size_t workspace_bytes,
+                         void* stream);
 
 /* ---------------------------------------------------------------------------
  * A8  fused MLP of Block.forward (MLP.forward :225-248 + the residual add :337): one tcgen05 kernel for

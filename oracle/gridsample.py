@@ -38,19 +38,25 @@ def ravel_hash_vec(arr):
     return keys
 
 
-def voxelize(coord, grid_size):
-    """transform.py:850-855.  numpy>=2 promotes f32 / f64-0d-array to f64."""
-    scaled = np.asarray(coord).astype(np.float64) / np.float64(grid_size)
+def voxelize(coord, grid_size, quotient="f32"):
+    """transform.py:850-855: `coord / np.array(grid_size)`.  For float32 coordinates the reference's pinned numpy
+    1.26.4 (uv_requirements.txt:84) keeps the division in float32 (value-based casting treats the 0-d float64 array
+    like a scalar): quotient="f32", the default.  numpy >= 2 (NEP 50) promotes to float64: quotient="f64".  Both are
+    frozen from the unmodified reference class in tests/golden/gridsample.npz (keys *_q32 / plain)."""
+    if quotient == "f32":
+        scaled = np.asarray(coord).astype(np.float32) / np.float32(grid_size)
+    else:
+        scaled = np.asarray(coord).astype(np.float64) / np.float64(grid_size)
     grid = np.floor(scaled).astype(np.int64)
     gmin = grid.min(0)
     return grid - gmin, gmin
 
 
-def grid_sample(coord, grid_size, hash_type="fnv", rand=None):
+def grid_sample(coord, grid_size, hash_type="fnv", rand=None, quotient="f32"):
     """Returns dict(grid_coord (R,3) shifted, min_grid, key, idx_sort, count,
     inverse (R,), idx_unique (M,), seg_start (M,)).  rand=None picks the first
     point of every voxel (rand == 0)."""
-    grid, gmin = voxelize(coord, grid_size)
+    grid, gmin = voxelize(coord, grid_size, quotient)
     key = fnv_hash_vec(grid) if hash_type == "fnv" else ravel_hash_vec(grid)
     idx_sort = np.argsort(key, kind="stable")
     key_sort = key[idx_sort]

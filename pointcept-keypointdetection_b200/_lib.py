@@ -44,8 +44,9 @@ SIGNATURES = {
     "ptv3_subm_pack_weight": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_subm_conv_packed": (c_int, [c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_build_windows": (c_int, [c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_vp]),
+    "ptv3_attn_window_workspace": (c_sz, [c_i64, c_int]),
     "ptv3_attn_window_fwd": (c_int, [c_vp, c_int, c_vp, c_vp, c_vp, c_i64, c_i64, c_i64, c_int, c_int, c_f32, c_int,
-                                     c_vp, c_vp]),
+                                     c_vp, c_vp, c_sz, c_vp]),
     "ptv3_pack_kmajor_bytes": (c_sz, [c_int, c_int]),
     "ptv3_pack_kmajor": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_mlp_fused_supported": (c_int, [c_int, c_int]),

@@ -128,10 +128,15 @@ int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
 // implemented in attn_f16.cu (the default bf16 kernel)
 int attn_window_f16(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                     int64_t n_windows_max, int64_t max_len, int h, float scale, __nv_bfloat16* out, cudaStream_t st,
-                    float* lse, int* err);
+                    float* lse, int* err, const int* only_if = nullptr);
+// implemented in attn_tm.cu (tcgen05 / TMEM, single pass); redo = (n_windows_max * h) int flags, zeroed by the caller
+int attn_window_tm(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
+                   int64_t n_windows_max, int64_t max_len, int h, float scale, __nv_bfloat16* out, int* redo,
+                   cudaStream_t st);
 int* attn_error_flag();
 int attn_error_fetch_and_clear();
 extern int g_attn_f16_variant;
+extern int g_attn_tm_poly;
 extern int g_attn_lse_algo;
 
 }  // namespace ptv3
@@ -147,14 +152,32 @@ int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, i
   return check_launch();
 }
 
+size_t ptv3_attn_window_workspace(int64_t n_windows_max, int h) {
+  return align_up((size_t)(n_windows_max > 0 ? n_windows_max : 1) * (size_t)(h > 0 ? h : 1) * sizeof(int));
+}
+
 int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const int64_t* windows,
                          const int64_t* n_windows, int64_t n_windows_max, int64_t max_len, int64_t n, int h, int d,
-                         float scale, int algo, void* out, void* stream) {
-  if (n < 0 || h < 1 || h > 65535 || d != kAttnD || n_windows_max < 0 || max_len < 1 || algo < 0 || algo > 4)
+                         float scale, int algo, void* out, void* workspace, size_t workspace_bytes, void* stream) {
+  if (n < 0 || h < 1 || h > 65535 || d != kAttnD || n_windows_max < 0 || max_len < 1 || algo < 0 || algo > 5)
     return PTV3_EINVAL;
   if (n == 0 || n_windows_max == 0) return PTV3_OK;
   if (!qkv || !windows || !n_windows || !out) return PTV3_EINVAL;
   cudaStream_t st = as_stream(stream);
+  if (dtype == PTV3_BF16 && algo == 5) {
+    // tcgen05 / TMEM kernel; (window, head) units it flags (records outside its contract, rows whose scores spread over
+    // more than ~100 octaves) are recomputed by the register kernel in a second, normally empty, launch
+    if (max_len > 1024) return PTV3_EUNSUPPORTED;
+    const size_t need = ptv3_attn_window_workspace(n_windows_max, h);
+    if (!workspace || workspace_bytes < need) return PTV3_EWORKSPACE;
+    int* redo = static_cast<int*>(workspace);
+    if (cudaMemsetAsync(redo, 0, need, st) != cudaSuccess) return PTV3_ELAUNCH;
+    int rc = attn_window_tm((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
+                            (__nv_bfloat16*)out, redo, st);
+    if (rc != PTV3_OK) return rc;
+    return attn_window_f16((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
+                           (__nv_bfloat16*)out, st, nullptr, attn_error_flag(), redo);
+  }
   if (dtype == PTV3_BF16 && algo == 3) {
     if (max_len > 1024) return PTV3_EUNSUPPORTED;
     return attn_window_tc05((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
@@ -204,6 +227,7 @@ int ptv3_debug_set(int key, int value) {
   if (key == 6) { g_attn_bwd_warps = value; return PTV3_OK; }
   if (key == 7) { g_attn_f16_variant = value; return PTV3_OK; }
   if (key == 8) { g_attn_lse_algo = value; return PTV3_OK; }
+  if (key == 9) { g_attn_tm_poly = value; return PTV3_OK; }
   return PTV3_EINVAL;
 }
 

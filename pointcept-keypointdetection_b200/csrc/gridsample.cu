@@ -15,9 +15,12 @@ __global__ void gs_init_minmax(long long* mm) {
   else if (i < 6) mm[i] = INT64_MIN;   // max
 }
 
-// numpy>=2: float32 array / 0-d float64 array promotes to float64 (transform.py:850-853)
-// f32div: the inference-time voxelisers (tools/OffsetKeyPointPrediction_Qt.py:284, tools/pigseg_shared.py:133) divide
-// the float32 array by a Python float, which numpy keeps in float32 -- a different floor near cell borders
+// The quotient `coord / np.array(grid_size)` of transform.py:850 is a float32 division in the reference's pinned
+// numpy 1.26.4 (uv_requirements.txt:84: value-based casting treats the 0-d float64 array like a scalar) and a float64
+// division under numpy >= 2 (NEP 50).  Points within ~1e-6 cells of a voxel face land in different voxels, so the
+// precision is selectable (f32div): hash_type 0 / 1 = fnv / ravel with the float64 quotient, 3 / 2 = fnv / ravel with
+// the float32 quotient.  The inference-time voxelisers (tools/OffsetKeyPointPrediction_Qt.py:284,
+// tools/pigseg_shared.py:133) divide by a Python float, which every numpy keeps in float32.
 __global__ void __launch_bounds__(256) gs_floor_kernel(const float* __restrict__ coord, int64_t r, double grid_size,
                                                        int f32div, int64_t* __restrict__ grid,
                                                        long long* __restrict__ mm) {
@@ -139,9 +142,9 @@ int ptv3_gridsample(const float* coord, int64_t r, double grid_size, int hash_ty
                     int64_t* grid_coord, uint64_t* key, int64_t* idx_sort, int64_t* inverse, int64_t* count,
                     int64_t* idx_unique, int64_t* min_grid, int64_t* n_voxels, void* workspace,
                     size_t workspace_bytes, void* stream) {
-  if (r < 0 || !(grid_size > 0.0) || hash_type < 0 || hash_type > 2 || !n_voxels) return PTV3_EINVAL;
-  const int f32div = hash_type == 2;
-  if (f32div) hash_type = 1;
+  if (r < 0 || !(grid_size > 0.0) || hash_type < 0 || hash_type > 3 || !n_voxels) return PTV3_EINVAL;
+  const int f32div = hash_type >= 2;
+  if (f32div) hash_type = 3 - hash_type;      // 2 -> ravel (1), 3 -> fnv (0)
   cudaStream_t st = as_stream(stream);
   if (r == 0) {
     cudaMemsetAsync(n_voxels, 0, 8, st);

@@ -134,8 +134,15 @@ def argsort_rows(code, key_bits=63, want_inverse=True):
 
 
 # ------------------------------------------------------------------ A0 GridSample
-def gridsample(coord, grid_size, hash_type="fnv", rand=None):
-    """Returns dict of device tensors (see include/ptv3_b200.h); one host sync to read the voxel count."""
+HASH_IDS = {("fnv", "f64"): 0, ("ravel", "f64"): 1, ("ravel", "f32"): 2, ("fnv", "f32"): 3}
+
+
+def gridsample(coord, grid_size, hash_type="fnv", rand=None, quotient="f32"):
+    """Returns dict of device tensors (see include/ptv3_b200.h); one host sync to read the voxel count.
+    quotient: precision of `coord / grid_size` before the floor (transform.py:850): "f32" = the reference's pinned
+    numpy 1.26.4 (float32 array / 0-d float64 array stays float32), "f64" = numpy >= 2 (NEP 50 promotes to float64)."""
+    if hash_type == "ravel_f32":
+        hash_type, quotient = "ravel", "f32"
     _need_cuda(coord, rand)
     lib = _lib.load()
     coord = coord.contiguous().float()
@@ -152,7 +159,7 @@ def gridsample(coord, grid_size, hash_type="fnv", rand=None):
         if rand.numel() < r:
             rand = torch.cat([rand, rand.new_zeros(r - rand.numel())])
     ws = _ws(lib.ptv3_gridsample_workspace(r), dev)
-    _lib.check(lib.ptv3_gridsample(_p(coord), r, float(grid_size), {"fnv": 0, "ravel": 1, "ravel_f32": 2}[hash_type], _p(rand), _p(grid),
+    _lib.check(lib.ptv3_gridsample(_p(coord), r, float(grid_size), HASH_IDS[(hash_type, quotient)], _p(rand), _p(grid),
                                    _p(key), _p(idx_sort), _p(inverse), _p(count), _p(idx_unique), _p(min_grid),
                                    _p(n_vox), _p(ws), ws.numel(), _stream()), "ptv3_gridsample")
     m = int(n_vox.item())
@@ -419,9 +426,14 @@ def attn_window(qkv, order, windows, n_windows, num_heads, max_len, scale=None, 
         return out
     scale = float(scale) if scale is not None else d ** -0.5
     o = order.contiguous().long() if order is not None else None
+    ws, ws_bytes = None, 0
+    if int(algo) == 5:
+        ws_bytes = lib.ptv3_attn_window_workspace(windows.shape[0], h)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=qkv.device)
     with _timed("attn_window", n=n, h=h, d=d, windows=windows, n_windows=n_windows, dtype=_dt(qkv)):
         _lib.check(lib.ptv3_attn_window_fwd(_p(qkv), _dt(qkv), _p(o), _p(windows), _p(n_windows), windows.shape[0],
-                                            int(max_len), n, h, d, scale, int(algo), _p(out), _stream()),
+                                            int(max_len), n, h, d, scale, int(algo), _p(out), _p(ws), ws_bytes,
+                                            _stream()),
                    "ptv3_attn_window_fwd")
     return out
 

@@ -8,7 +8,9 @@ within a voxel points are ordered by ascending original index (the reference's
 np.argsort is unstable); the per-voxel random draw comes from `generator` (a
 torch CPU generator; the reference uses np.random) or can be passed in as
 data_dict["gridsample_rand"]; "sampled_index" (ScanNet data-efficient) is not
-supported.
+supported.  `quotient` selects the precision of `coord / np.array(grid_size)`
+(transform.py:850): "f32" (default) is what the reference's pinned numpy 1.26.4
+computes for float32 coordinates, "f64" what numpy >= 2 computes.
 """
 import copy
 
@@ -40,9 +42,12 @@ def index_operator(data_dict, index, duplicate=False):
 
 class GridSample(object):
     def __init__(self, grid_size=0.05, hash_type="fnv", mode="train", return_inverse=False, return_grid_coord=False,
-                 return_min_coord=False, return_displacement=False, project_displacement=False, generator=None):
+                 return_min_coord=False, return_displacement=False, project_displacement=False, generator=None,
+                 quotient="f32"):
         assert mode in ["train", "test"]
         assert hash_type in ["fnv", "ravel"]
+        assert quotient in ["f32", "f64"]
+        self.quotient = quotient
         self.grid_size = grid_size
         self.hash_type = hash_type
         self.mode = mode
@@ -84,7 +89,7 @@ class GridSample(object):
                 # the reference draws randint(0, count.max(), count.size) % count; any non-negative draw modulo the
                 # voxel population is an equally valid pick
                 rand = torch.randint(0, 1 << 30, (n,), generator=self.generator).to(coord.device, non_blocking=True)
-        r = ops.gridsample(coord, self.grid_size, self.hash_type, rand=rand)
+        r = ops.gridsample(coord, self.grid_size, self.hash_type, rand=rand, quotient=self.quotient)
         r["_coord"] = coord
         full = dict(data_dict)
         if self.mode == "train":
@@ -122,7 +127,7 @@ def voxelize_first(coord, grid_size, keep_order=True):
     (tools/OffsetKeyPointPrediction_Qt.py:288-289, keep_order=True), pig-seg keeps lexicographic voxel order
     (tools/pigseg_shared.py:133-134, keep_order=False).  Returns (indices int64 (M,), grid_coord int64 (M,3) already
     shifted to start at 0).  One kernel chain (float32 quotient like numpy, ravel key, stable radix sort, run heads)."""
-    r = ops.gridsample(coord, grid_size, "ravel_f32", rand=None)
+    r = ops.gridsample(coord, grid_size, "ravel", rand=None, quotient="f32")
     idx = r["idx_unique"]
     if keep_order:
         idx = torch.sort(idx)[0]

@@ -5,7 +5,9 @@ container only:  python tests/golden/make_golden.py
 Fixtures (all inputs are seeded; the script is the provenance):
   serialization.npz  reference `encode` for the 4 orders at depths 1..16 + KATs
   gridsample.npz     reference GridSample (fnv + ravel, train + test mode) with
-                     np.argsort forced stable and np.random.randint recorded
+                     np.argsort forced stable and np.random.randint recorded; keys *_q32_* / *_q64_*: the same class
+                     with the float32 quotient of its pinned numpy 1.26.4 and the float64 quotient of numpy >= 2 on a
+                     scan with points on voxel faces
   padding.npz        reference SerializedAttention.get_padding_and_inverse
   attention.npz      reference SerializedAttention.forward (dense branch)
   forward.npz        reference OffsetKeypointPTv3 forward (PT-v3m1 base config,
@@ -96,6 +98,23 @@ def gold_gridsample(R):
         out["test_num_parts"] = np.int64(len(parts))
         for i, p in enumerate(parts):
             out[f"test_index_{i}"] = p["index"]
+        # ---- quotient precision.  transform.py:850 divides by np.array(grid_size): the
+        # reference's pinned numpy 1.26.4 keeps float32 / 0-d float64 in float32, numpy >= 2 (this container)
+        # promotes to float64.  The float32 behaviour is reproduced WITH THE UNMODIFIED CLASS by handing it a float32
+        # grid size (np.array(np.float32(g)) is a 0-d float32 array -> a float32 division under every numpy).
+        # coord_q adds points that sit on voxel faces in float32 so that the two quotients really differ.
+        k = np.arange(-40, 60)
+        lattice = np.stack([np.float32(k * 0.02), np.float32((k + 3) * 0.02), np.float32((7 - k) * 0.02)], 1)
+        coord_q = np.concatenate([coord, lattice.astype(np.float32)])
+        out["coord_q"] = coord_q
+        for tag, gsz in (("q32", np.float32(0.02)), ("q64", 0.02)):
+            for hash_type in ("fnv", "ravel"):
+                gs = R.GridSample(grid_size=gsz, hash_type=hash_type, mode="train", return_grid_coord=True,
+                                  return_inverse=True)
+                r = gs(dict(coord=coord_q.copy(), index_valid_keys=["coord"]))
+                out[f"{hash_type}_{tag}_coord"], out[f"{hash_type}_{tag}_grid_coord"] = r["coord"], r["grid_coord"]
+                out[f"{hash_type}_{tag}_inverse"], out[f"{hash_type}_{tag}_rand"] = r["inverse"], rec["rand"]
+        assert not np.array_equal(out["fnv_q32_inverse"], out["fnv_q64_inverse"]), "quotients agree: fixture is blind"
     finally:
         np.argsort, np.random.randint = real_argsort, real_randint
     np.savez_compressed(os.path.join(HERE, "gridsample.npz"), **out)
@@ -345,6 +364,9 @@ if __name__ == "__main__":
     R = ref_loader.load()
     if sys.argv[1:] == ["eval"]:
         gold_eval(R)
+        sys.exit(0)
+    if sys.argv[1:] == ["gridsample"]:
+        gold_gridsample(R)
         sys.exit(0)
     gold_serialization(R)
     gold_gridsample(R)

@@ -99,13 +99,37 @@ def test_point_serialization_vs_oracle():
 def test_gridsample_golden(golden, hash_type):
     ops = _ops()
     g = golden("gridsample")
-    r = ops.gridsample(dev(g["coord"]), float(g["grid_size"]), hash_type, rand=dev(g[f"{hash_type}_rand"]))
+    r = ops.gridsample(dev(g["coord"]), float(g["grid_size"]), hash_type, rand=dev(g[f"{hash_type}_rand"]),
+                       quotient="f64")
     assert np.array_equal(r["key"].cpu().numpy().view(np.uint64), g[f"{hash_type}_key"])
     iu = r["idx_unique"].cpu().numpy()
     assert np.array_equal(r["grid_coord"].cpu().numpy()[iu], g[f"{hash_type}_grid_coord"])
     assert np.array_equal(g["coord"][iu], g[f"{hash_type}_coord"])
     assert np.array_equal(r["inverse"].cpu().numpy(), g[f"{hash_type}_inverse"])
     assert np.allclose(r["min_grid"].cpu().numpy() * float(g["grid_size"]), g[f"{hash_type}_min_coord"].ravel())
+
+
+@pytest.mark.parametrize("hash_type", ["fnv", "ravel"])
+@pytest.mark.parametrize("quotient", ["f32", "f64"])
+def test_gridsample_quotient_golden(golden, hash_type, quotient):
+    """Both quotient precisions of transform.py:850 (numpy 1.26.4 = float32, numpy >= 2 = float64), bit-exact against
+    the unmodified reference class on a scan with points on voxel faces (tests/golden/gridsample.npz *_q32 / *_q64)."""
+    ops = _ops()
+    from ptv3_b200.transform import GridSample
+    g = golden("gridsample")
+    tag = "q32" if quotient == "f32" else "q64"
+    r = ops.gridsample(dev(g["coord_q"]), float(g["grid_size"]), hash_type, rand=dev(g[f"{hash_type}_{tag}_rand"]),
+                       quotient=quotient)
+    iu = r["idx_unique"].cpu().numpy()
+    assert np.array_equal(r["grid_coord"].cpu().numpy()[iu], g[f"{hash_type}_{tag}_grid_coord"])
+    assert np.array_equal(g["coord_q"][iu], g[f"{hash_type}_{tag}_coord"])
+    assert np.array_equal(r["inverse"].cpu().numpy(), g[f"{hash_type}_{tag}_inverse"])
+    gs = GridSample(grid_size=float(g["grid_size"]), hash_type=hash_type, mode="train", return_grid_coord=True,
+                    return_inverse=True, quotient=quotient)
+    out = gs(dict(coord=dev(g["coord_q"]), index_valid_keys=["coord"], gridsample_rand=dev(g[f"{hash_type}_{tag}_rand"])))
+    assert np.array_equal(out["coord"].cpu().numpy(), g[f"{hash_type}_{tag}_coord"])
+    assert np.array_equal(out["inverse"].cpu().numpy(), g[f"{hash_type}_{tag}_inverse"])
+    assert GridSample().quotient == "f32"          # default = the reference's own environment
 
 
 def test_gridsample_transform_modes(golden):
@@ -115,7 +139,7 @@ def test_gridsample_transform_modes(golden):
     feat = torch.arange(len(g["coord"]), device="cuda", dtype=torch.float32)[:, None]
     # train mode, recorded draw
     gs = GridSample(grid_size=float(g["grid_size"]), hash_type="fnv", mode="train", return_grid_coord=True,
-                    return_inverse=True, return_min_coord=True)
+                    return_inverse=True, return_min_coord=True, quotient="f64")
     out = gs(dict(coord=coord.clone(), feat=feat.clone(), index_valid_keys=["coord", "feat"],
                   gridsample_rand=dev(g["fnv_rand"])))
     assert np.array_equal(out["coord"].cpu().numpy(), g["fnv_coord"])
@@ -123,7 +147,8 @@ def test_gridsample_transform_modes(golden):
     assert np.array_equal(out["inverse"].cpu().numpy(), g["fnv_inverse"])
     assert np.allclose(out["min_coord"].cpu().numpy(), g["fnv_min_coord"])
     # test mode: every raw point is covered, parts equal the reference's
-    gs = GridSample(grid_size=float(g["grid_size"]), hash_type="fnv", mode="test", return_grid_coord=True)
+    gs = GridSample(grid_size=float(g["grid_size"]), hash_type="fnv", mode="test", return_grid_coord=True,
+                    quotient="f64")
     parts = gs(dict(coord=coord.clone(), feat=feat.clone(), index_valid_keys=["coord", "feat"]))
     assert len(parts) == int(g["test_num_parts"])
     for i, p in enumerate(parts):
@@ -138,10 +163,10 @@ def test_gridsample_random_vs_oracle(r, scale):
     coord = coord - 1.7
     rng = np.random.default_rng(0)
     rand = rng.integers(0, 1000, size=r)
-    for hash_type in ("fnv", "ravel"):
-        m = len(G.grid_sample(coord, 0.02, hash_type)["count"])
-        ref = G.grid_sample(coord, 0.02, hash_type, rand=rand[:m])
-        got = ops.gridsample(dev(coord), 0.02, hash_type, rand=dev(rand))
+    for hash_type, q in (("fnv", "f32"), ("ravel", "f32"), ("fnv", "f64"), ("ravel", "f64")):
+        m = len(G.grid_sample(coord, 0.02, hash_type, quotient=q)["count"])
+        ref = G.grid_sample(coord, 0.02, hash_type, rand=rand[:m], quotient=q)
+        got = ops.gridsample(dev(coord), 0.02, hash_type, rand=dev(rand), quotient=q)
         assert got["n_voxels"] == m
         assert np.array_equal(got["grid_coord"].cpu().numpy(), ref["grid_coord"])
         assert np.array_equal(got["key"].cpu().numpy().view(np.uint64), ref["key"])

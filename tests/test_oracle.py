@@ -47,7 +47,7 @@ def test_hash_kat():
 @pytest.mark.parametrize("hash_type", ["fnv", "ravel"])
 def test_gridsample_vs_reference(golden, hash_type):
     g = golden("gridsample")
-    r = G.grid_sample(g["coord"], float(g["grid_size"]), hash_type, rand=g[f"{hash_type}_rand"])
+    r = G.grid_sample(g["coord"], float(g["grid_size"]), hash_type, rand=g[f"{hash_type}_rand"], quotient="f64")
     assert np.array_equal(r["key"], g[f"{hash_type}_key"])
     iu = r["idx_unique"]
     assert np.array_equal(r["grid_coord"][iu], g[f"{hash_type}_grid_coord"])
@@ -56,9 +56,25 @@ def test_gridsample_vs_reference(golden, hash_type):
     assert np.allclose(r["min_grid"] * float(g["grid_size"]), g[f"{hash_type}_min_coord"].ravel())
 
 
+@pytest.mark.parametrize("hash_type", ["fnv", "ravel"])
+@pytest.mark.parametrize("quotient", ["f32", "f64"])
+def test_gridsample_quotient_vs_reference(golden, hash_type, quotient):
+    """transform.py:850 under the reference's pinned numpy 1.26.4 (float32 quotient) and under numpy >= 2 (float64),
+    both frozen from the unmodified class on a scan with points on voxel faces; the two really differ there."""
+    g = golden("gridsample")
+    tag = "q32" if quotient == "f32" else "q64"
+    r = G.grid_sample(g["coord_q"], float(g["grid_size"]), hash_type, rand=g[f"{hash_type}_{tag}_rand"], quotient=quotient)
+    iu = r["idx_unique"]
+    assert np.array_equal(r["grid_coord"][iu], g[f"{hash_type}_{tag}_grid_coord"])
+    assert np.array_equal(g["coord_q"][iu], g[f"{hash_type}_{tag}_coord"])
+    assert np.array_equal(r["inverse"], g[f"{hash_type}_{tag}_inverse"])
+    other = G.grid_sample(g["coord_q"], float(g["grid_size"]), hash_type, quotient="f64" if quotient == "f32" else "f32")
+    assert len(other["count"]) != len(r["count"])
+
+
 def test_gridsample_test_mode(golden):
     g = golden("gridsample")
-    r = G.grid_sample(g["coord"], float(g["grid_size"]), "fnv")
+    r = G.grid_sample(g["coord"], float(g["grid_size"]), "fnv", quotient="f64")
     parts = G.grid_sample_test_parts(r["count"], r["idx_sort"])
     assert len(parts) == int(g["test_num_parts"])
     for i, p in enumerate(parts):

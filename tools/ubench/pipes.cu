@@ -137,6 +137,43 @@ __global__ void ldtm(uint32_t* out, long long* cyc) {
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(slot) : "memory");
 }
 
+// Independent streams of the instruction kinds of one softmax chunk, in selectable proportions, to see which
+// companion steals MUFU issue: per loop trip NM ex2, NC cvt.rn.f16x2.f32, NX 3-input max, NH mma.m16n8k16.
+template <int NM, int NC, int NX, int NH>
+__global__ void mix(float* out, long long* cyc, float seed) {
+  float v[8], mx[4];
+  uint32_t pk[4] = {0u, 0u, 0u, 0u};
+  float c[4][4];
+  uint32_t a[4] = {1u, 2u, 3u, 4u}, b0 = 5u, b1 = 6u;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = seed * (threadIdx.x + i) * 1e-6f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { mx[i] = seed * i; c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f; }
+  __syncthreads();
+  long long t0 = clock64();
+  for (int it = 0; it < ITERS / 4; ++it) {
+#pragma unroll
+    for (int i = 0; i < NM; ++i) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(v[i & 7]));
+#pragma unroll
+    for (int i = 0; i < NC; ++i) asm volatile("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(pk[i & 3]) : "f"(mx[i & 3]), "f"(mx[(i + 1) & 3]));
+#pragma unroll
+    for (int i = 0; i < NX; ++i) asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(mx[i & 3]) : "f"(seed), "f"(mx[(i + 2) & 3]));
+#pragma unroll
+    for (int i = 0; i < NH; ++i)
+      asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                   : "+f"(c[i & 3][0]), "+f"(c[i & 3][1]), "+f"(c[i & 3][2]), "+f"(c[i & 3][3])
+                   : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+  long long t1 = clock64();
+  float s = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += v[i];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) s += mx[i] + __uint_as_float(pk[i]) + c[i][0] + c[i][1] + c[i][2] + c[i][3];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+  if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
+}
+
 static double mean_cycles(long long* d_cyc, int n) {
   static long long h[256];
   cudaMemcpy(h, d_cyc, n * sizeof(long long), cudaMemcpyDeviceToHost);
@@ -169,6 +206,20 @@ int main() {
              (double)(threads / 32) * ITERS * 4 * 512 / mean_cycles(cyc, G));
     }
   }
+#define MIX(NM, NC, NX, NH, label)                                                                                  \
+  for (int threads : {512, 768}) {                                                                                  \
+    for (int rep = 0; rep < 2; ++rep) mix<NM, NC, NX, NH><<<G, threads>>>((float*)out, cyc, 1.f);                   \
+    CHECK(cudaDeviceSynchronize());                                                                                 \
+    printf("mix %-44s %4d threads/SM: %6.2f exp/clk/SM\n", label, threads,                                          \
+           (double)threads * (ITERS / 4) * NM / mean_cycles(cyc, G));                                               \
+  }
+  MIX(16, 0, 0, 0, "16 ex2")
+  MIX(16, 8, 0, 0, "16 ex2 + 8 cvt.f16x2")
+  MIX(16, 0, 8, 0, "16 ex2 + 8 max3")
+  MIX(16, 0, 0, 10, "16 ex2 + 10 hmma")
+  MIX(16, 8, 8, 0, "16 ex2 + 8 cvt + 8 max3")
+  MIX(16, 8, 8, 10, "16 ex2 + 8 cvt + 8 max3 + 10 hmma (softmax mix)")
+  MIX(16, 8, 8, 6, "16 ex2 + 8 cvt + 8 max3 + 6 hmma")
   for (int threads : {128, 256, 512}) {
     for (int rep = 0; rep < 2; ++rep) ldtm<<<G, threads>>>((uint32_t*)out, cyc);
     CHECK(cudaDeviceSynchronize());
