@@ -31,6 +31,16 @@ GRID = 0.02
 METRIC = "ptv3_forward_voxels_per_sec"
 UNIT = "voxels/s"
 
+# BASELINE.json configs[0..2] as bench workloads (--config 1 | 2 | 3; 2 is the headline the metric is quoted on)
+WORKLOADS = {
+    1: dict(scenes=1, points=40000, scale=1.0, in_channels=4, head="offset",
+            name="configs[0]: one 40k-pt pig scan, batch 1, keypoint-offset head"),
+    2: dict(scenes=16, points=100000, scale=4.1, in_channels=4, head="offset",
+            name="configs[1]: 16 x 100k-pt pig scans, keypoint-offset head"),
+    3: dict(scenes=8, points=150000, scale=5.0, in_channels=6, head="segmentor",
+            name="configs[2]: semseg-pt-v3m1-0-base shape, 8 ScanNet-sized scenes (150k pts, C_in 6, 20 classes)"),
+}
+
 
 def peaks():
     try:
@@ -43,14 +53,20 @@ def peaks():
 
 def ncu_traffic(kernel_substr):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed summary of
-    one `ncu --set full` capture (profiles/r01_ncu_full_summary.json); None if that kernel was not captured."""
+    one `ncu --set full` capture (profiles/r02_ncu_attention_summary.json for the attention kernel of this round, else
+    profiles/r01_ncu_full_summary.json); None if that kernel was not captured."""
     try:
-        with open(os.path.join(REPO, "profiles", "r01_ncu_full_summary.json")) as f:
-            rows = [r for r in json.load(f) if kernel_substr in r["kernel"] and r.get("dram_read_MB") is not None]
+        for name in ("r02_ncu_attention_summary.json", "r01_ncu_full_summary.json"):
+            with open(os.path.join(REPO, "profiles", name)) as f:
+                rows = [r for r in json.load(f) if kernel_substr in r["kernel"] and r.get("dram_read_MB") is not None]
+            if rows:
+                break
         if not rows:
             return None, "kernel not in the committed ncu capture"
+        if name.startswith("r02"):
+            rows = rows[:1]          # the default kernel's own capture (the other rows are ablations / other designs)
         b = sum((r["dram_read_MB"] + r["dram_write_MB"]) * 1e6 for r in rows) / len(rows)
-        return round(b), f"bytes per launch, mean of {len(rows)} captured launches (profiles/r01_ncu_full_summary.json)"
+        return round(b), f"bytes per launch, mean of {len(rows)} captured launch(es) (profiles/{name})"
     except Exception as e:  # noqa: BLE001
         return None, f"no ncu summary ({type(e).__name__})"
 
@@ -104,13 +120,25 @@ def make_raw_scenes(n_scenes, points, scale, seed0, in_channels=4):
     return [synth.pig_scan(points, scale=scale, seed=seed0 + i, in_channels=in_channels) for i in range(n_scenes)]
 
 
-def build_model(dtype, device):
+def build_model(dtype, device, in_channels=4, head="offset"):
     from ptv3_b200 import model as M, synth
-    m = M.OffsetKeypointPTv3(backbone_conf=dict(CFG, compute_dtype=dtype)).eval()
+    conf = dict(CFG, in_channels=in_channels, compute_dtype=dtype)
+    if head == "segmentor":      # configs/scannet/semseg-pt-v3m1-0-base.py: DefaultSegmentorV2, 20 classes
+        m = M.DefaultSegmentorV2(num_classes=20, backbone_out_channels=64, backbone=conf).eval()
+    else:
+        m = M.OffsetKeypointPTv3(backbone_conf=conf).eval()
     shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
     W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
     m.load_state_dict(W, strict=False)
     return m.to(device), W
+
+
+def shard_scenes(n_scenes, rank, world, scaling):
+    """Scene ids of this rank.  weak: every rank owns n_scenes scenes of its own; strong: the n_scenes of the job are
+    dealt round-robin (BASELINE configs[2]: batch 8 at 1 / 2 / 4 / 8 GPUs = 8 ... 1 scene per GPU)."""
+    if scaling == "strong":
+        return [i for i in range(n_scenes) if i % world == rank]
+    return [1000 * rank + i for i in range(n_scenes)]
 
 
 def voxelize_on_device(raw, device):
@@ -154,17 +182,22 @@ def run_ours(args):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
-    model, _ = build_model(dtype, device)
-
-    raw = make_raw_scenes(args.scenes, args.points, args.scale, seed0=1000 * rank)
+    model, _ = build_model(dtype, device, args.in_channels, args.head)
+    from ptv3_b200 import synth
+    ids = shard_scenes(args.scenes, rank, world, args.scaling)
+    if not ids:
+        raise SystemExit(f"--scaling strong needs at least one scene per rank ({args.scenes} scenes, {world} ranks)")
+    raw = [synth.pig_scan(args.points, scale=args.scale, seed=i, in_channels=args.in_channels) for i in ids]
     host, counts = voxelize_on_device(raw, device)
     n_vox = int(sum(counts))
     pinned = {k: v.pin_memory() for k, v in host.items()}
     resident = {k: v.to(device) for k, v in host.items()}
     h2d_bytes = int(sum(v.numel() * v.element_size() for v in pinned.values()))
 
+    out_key = "seg_logits" if args.head == "segmentor" else "pred"
+
     def step_resident():
-        return model(dict(resident))["pred"]
+        return model(dict(resident))[out_key]
 
     # e2e: every step copies ITS inputs from pinned host memory and reads ITS keypoints back.  The copy of step i+1
     # runs on a side stream while step i computes (double-buffered device inputs); all of it is inside the timed region.
@@ -186,7 +219,9 @@ def run_ours(args):
         for v in d.values():
             v.record_stream(torch.cuda.current_stream())
         stage_inputs()                                                    # H2D of the next step overlaps this one
-        pred = model(d)["pred"]
+        pred = model(d)[out_key]
+        if args.head == "segmentor":
+            return pred.argmax(1).to(torch.uint8).cpu()                   # D2H read: predicted class of every voxel
         kp = aggregate_keypoints(d["coord"], pred, d["offset"])            # (scenes, 6, 3) on device, one kernel
         return kp.cpu()                                                   # D2H read of the step's result
 
@@ -242,12 +277,18 @@ def run_ours(args):
     roof, ops_ms = None, {}
     if rank == 0:
         pk = peaks()
+        # per-op CUDA events need the op-by-op path: same kernels on the same stream, without the one-call-per-Block
+        # wrapper (ops.block_fwd) that hides them from the host
+        ops.NATIVE_BLOCK = False
+        step_resident()
+        torch.cuda.synchronize()
         ops.profile_start()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         step_resident()
         b.record()
         recs = ops.profile_stop()
+        ops.NATIVE_BLOCK = True
         step_ms = a.elapsed_time(b)
         tot = {}
         for name, t, meta in recs:
@@ -271,11 +312,14 @@ def run_ours(args):
                     frac=round(ach / pk["tf_sust"], 4), traffic=None, peak_source=pk["src"] + " (sustained bf16 GEMM)",
                     launches_per_step=e["launches"], ms_per_step=round(e["ms"], 3),
                     share_of_step=round(e["ms"] / step_ms, 3))
-        roof["traffic"], roof["traffic_note"] = ncu_traffic({"attn_window": "attn_window", "subm_conv": "subm_conv_tc",
+        roof["traffic"], roof["traffic_note"] = ncu_traffic({"attn_window": "attn_window_f16", "subm_conv": "subm_conv_tc",
                                                              "mlp_fused": "mlp_fused"}.get(top, top))
         if top == "attn_window":   # head_dim 16: the exp pipe, not the tensor pipe, bounds this kernel
             roof["exp_per_s"] = round(e["units"] / (e["ms"] * 1e-3) / 1e12, 3)
             roof["exp_peak_mufu_per_s"] = round(16 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 3)
+            roof["limiter"] = ("mufu: 16 ex2 / clk / SM measured (tools/ubench/pipes.cu; the packed f16x2 / bf16x2 forms "
+                               "are two MUFU ops each); frac_of_limiter = exp_per_s / exp_peak_mufu_per_s")
+            roof["frac_of_limiter"] = round(roof["exp_per_s"] / roof["exp_peak_mufu_per_s"], 4)
     # ---- GridSample leg (BASELINE metric: "GridSample reported separately in raw points/s"), raw scans resident ----
     gs_leg = None
     if rank == 0:
@@ -325,36 +369,50 @@ def cpu_sample_scene(args, seconds, steps=1):
     cores = os.cpu_count() or 1
     est_rate = 9000.0 * max(1.0, (cores / 8.0) ** 0.5)          # voxels/s, indicative
     target = min(72900.0, max(4000.0, est_rate * seconds / steps))
-    scale = args.scale * (target / 72900.0) ** 0.5
-    coord, feat = synth.pig_scan(args.points, scale=scale, seed=0)
+    full = 72900.0 * (args.scale / 4.1) ** 2 * min(1.0, args.points / 100000.0) ** 0.5     # voxels of one full scene
+    target = min(full, target)
+    scale = args.scale * (target / full) ** 0.5
+    coord, feat = synth.pig_scan(args.points, scale=scale, seed=0, in_channels=getattr(args, "in_channels", 4))
     gs = G.grid_sample(coord, GRID)
     iu = gs["idx_unique"]
     return coord[iu], feat[iu], gs["grid_coord"][iu], scale
 
 
-def cpu_forward(W, scene):
+def cpu_forward(W, scene, head="offset"):
     from oracle import ptv3 as P
     c, f, g, _ = scene
     perms = [torch.randperm(4).numpy() for _ in range(5)]
-    pt = P.backbone_forward(W, c, g, f, [len(c)], cfg=dict(CFG), perms=perms)
-    return P.offset_head(W, pt.feat)
+    pt = P.backbone_forward(W, c, g, f, [len(c)], cfg=dict(CFG, in_channels=f.shape[1]), perms=perms)
+    return P.seg_head(W, pt.feat) if head == "segmentor" else P.offset_head(W, pt.feat)
+
+
+def cpu_weights(args):
+    from ptv3_b200 import model as M, synth
+    conf = dict(CFG, in_channels=args.in_channels)
+    m = (M.DefaultSegmentorV2(num_classes=20, backbone_out_channels=64, backbone=conf) if args.head == "segmentor"
+         else M.OffsetKeypointPTv3(backbone_conf=conf))
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
+    return {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
 
 
 def cpu_baseline(args, seconds=20.0):
     """The oracle port of the reference forward (fp32, dense-branch attention, restated spconv) on the host cores."""
-    from ptv3_b200 import model as M, synth
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    m = M.OffsetKeypointPTv3(backbone_conf=dict(CFG))
-    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
-    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
-    scene = cpu_sample_scene(args, seconds)
-    t0 = time.perf_counter()
-    cpu_forward(W, scene)
-    dt = time.perf_counter() - t0
+    W = cpu_weights(args)
+    scene = cpu_sample_scene(args, seconds / 4.0)                 # 1 warm-up + 3 timed forwards inside the budget
+    cpu_forward(W, scene, args.head)                              # warm-up (first-call allocations, thread pool)
+    ts = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        cpu_forward(W, scene, args.head)
+        ts.append(time.perf_counter() - t0)
+    dt = float(np.median(ts))
     n = len(scene[0])
-    return dict(value=round(n / dt, 1), unit=UNIT, cores=cores, kind="port",
-                sample=f"1 scene of the workload at scale {scene[3]:.2f} -> {n} voxels, 1 forward, fp32, {dt:.1f} s")
+    return dict(value=round(n / dt, 1), unit=UNIT, cores=cores, kind="port", dtype="f32",
+                sample=f"1 scene of the workload at scale {scene[3]:.2f} -> {n} voxels, median of 3 forwards after a "
+                       f"warm-up, fp32 (the GPU arm computes in {args.dtype}), {dt:.2f} s each; the oracle PORT of the "
+                       f"reference forward, not the reference's own Python (which cannot travel to the GPU box)")
 
 
 def run_reference(args):
@@ -363,29 +421,27 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from ptv3_b200 import model as M, synth
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    m = M.OffsetKeypointPTv3(backbone_conf=dict(CFG))
-    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
-    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+    W = cpu_weights(args)
     total = args.steps + args.warmup
     scene = cpu_sample_scene(args, seconds=150.0, steps=total)
     n = len(scene[0])
     torch.manual_seed(0)
     for _ in range(args.warmup):
-        cpu_forward(W, scene)
+        cpu_forward(W, scene, args.head)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        cpu_forward(W, scene)
+        cpu_forward(W, scene, args.head)
     dt = time.perf_counter() - t0
     v = n * args.steps / dt
     sample = f"1 scene per step at scale {scene[3]:.2f} -> {n} voxels (of the {args.scenes}-scene batch), fp32"
     line = dict(impl="reference", metric=METRIC, value=round(v, 1), unit=UNIT, n_gpus=int(os.environ.get("WORLD_SIZE", "1")),
                 steps=args.steps, warmup=args.warmup, ms_per_step=round(dt / args.steps * 1e3, 3),
-                higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=f"PTv3-v1m1 + offset-keypoint head forward on the host CPU (oracle port of the "
-                                     f"reference, enable_flash=False semantics, restated spconv), {sample}"),
+                higher_is_better=True, scaling=args.scaling, vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload=f"PTv3-v1m1 + {'20-class segmentor' if args.head == 'segmentor' else 'offset-keypoint'} "
+                                     f"head forward on the host CPU ({args.workload_name}; oracle port of the "
+                                     f"reference, enable_flash=False semantics one scene per forward, restated spconv), {sample}"),
                 cpu_baseline=dict(value=round(v, 1), unit=UNIT, cores=cores, kind="port", sample=sample),
                 e2e=dict(value=round(v, 1), unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
@@ -501,13 +557,23 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
-    ap.add_argument("--scenes", type=int, default=16)
-    ap.add_argument("--points", type=int, default=100000)
-    ap.add_argument("--scale", type=float, default=4.1)
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3],
+                    help="BASELINE.json workload: 1 = configs[0] (one 40k-pt scan), 2 = configs[1] (16 x 100k-pt scans, the "
+                         "headline), 3 = configs[2] (8 ScanNet-sized scenes, C_in 6, 20-class segmentor)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --scenes per GPU (default); strong: --scenes in total, dealt over the ranks")
+    ap.add_argument("--scenes", type=int, default=None)
+    ap.add_argument("--points", type=int, default=None)
+    ap.add_argument("--scale", type=float, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--mode", default="forward", choices=["forward", "train"],
                     help="forward = the headline metric (default); train = training step (SURVEY 8f rank 1)")
     args = ap.parse_args()
+    wl = WORKLOADS[args.config]
+    for k in ("scenes", "points", "scale"):
+        if getattr(args, k) is None:
+            setattr(args, k, wl[k])
+    args.in_channels, args.head, args.workload_name = wl["in_channels"], wl["head"], wl["name"]
     if args.impl == "reference":
         run_reference(args)
     elif args.mode == "train":

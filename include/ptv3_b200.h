@@ -232,12 +232,42 @@ int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const 
                    const float* residual /* NULL ok */, int64_t n, int c, int hidden, float* res_out /* NULL ok */,
                    void* out_bf16 /* NULL ok */, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * A8  one call per Block (inference, bf16 operands): the whole launch chain of Block.forward
+ * (point_transformer_v3m1_base.py:318-338) issued natively -- xCPE SubMConv3d (tcgen05 kernel) -> Linear -> LayerNorm ->
+ * + shortcut -> LayerNorm -> qkv Linear -> window attention -> proj Linear -> + shortcut -> LayerNorm -> MLP -> + shortcut.
+ * The Linears are plain library GEMMs (cuBLASLt, bias epilogue, resolved with dlopen at first use); everything else is
+ * this library's kernels.  Replaces ~15 host round trips per Block by one (a single scan was host-bound).
+ *   x          (n,c) fp32   residual stream entering the Block
+ *   conv_in    (n,c) bf16   what the xCPE conv reads (the sparse tensor's features: equals bf16(x) except right after
+ *                           an unpooling, where the reference leaves the skip branch there, :476-477)
+ *   x_out      (n,c) fp32, x_out_bf16 (n,c) bf16   residual stream leaving the Block and its bf16 copy
+ * Weights: bf16 row-major (out, in) with bf16 biases for the Linears; LayerNorm parameters fp32; conv_w_packed from
+ * ptv3_subm_pack_weight; with mlp_fused = 1 (c <= 64) fc1_w / fc2_w are ptv3_pack_kmajor images and fc1_b / fc2_b fp32.
+ * ------------------------------------------------------------------------- */
+typedef struct ptv3_block_params {
+  int c, heads, hidden, k3, patch, mlp_fused, attn_algo;
+  float scale, eps_cpe, eps_norm2;
+  const void* conv_w_packed;
+  const float* conv_bias;
+  const void *cpe_lin_w, *cpe_lin_b;
+  const float *cpe_ln_g, *cpe_ln_b, *norm1_g, *norm1_b, *norm2_g, *norm2_b;
+  const void *qkv_w, *qkv_b, *proj_w, *proj_b;
+  const void *fc1_w, *fc1_b, *fc2_w, *fc2_b;
+} ptv3_block_params;
+size_t ptv3_block_workspace(const ptv3_block_params* p, int64_t n, int64_t n_windows_max);
+int ptv3_block_fwd(const ptv3_block_params* p, const float* x, const void* conv_in, const int32_t* nbr,
+                   const int64_t* order, const int64_t* windows, const int64_t* n_windows, int64_t n_windows_max,
+                   int64_t n, float* x_out, void* x_out_bf16, void* workspace, size_t workspace_bytes, void* stream);
+
 /* development knob (tests only): key 1 = operand-descriptor variant of the tcgen05 attention kernel, 7 = chunk /
  * occupancy variant of the default attention kernel, 8 = kernel of the training forward */
 int ptv3_debug_set(int key, int value);
 
-/* Reads AND clears the library's sticky device-side error flag (0 = none, 1 = attention window contract violated).
- * Synchronises the device (one 4-byte copy): meant for tests and for shims that forward caller-built records. */
+/* Reads AND clears the library's sticky device-side error word, a bit mask (0 = none): 1 = an attention window record
+ * violated the ptv3_build_windows contract (its CTA wrote nothing); 2 = a sparse-conv site lies outside the packed
+ * key range (batch id >= 1024 or a coordinate outside [0, 262128)) and was left out of the neighbour map.
+ * Synchronises the device (one 4-byte copy): meant for tests and for shims that forward caller-built inputs. */
 int ptv3_device_error(void);
 
 /* ---------------------------------------------------------------------------

@@ -13,9 +13,10 @@ checkpoint (or the deterministic test weights) drives both sides:
   DefaultSegmentorV2.forward   default.py:63-95
 Eval mode by default (BatchNorm running stats, no dropout / drop-path); BN_TRAIN / offset_keypoint_grads switch to
 batch statistics and run torch.autograd through the same functions for the training-step tests.  Attention
-uses flash window semantics (fixed K, short scenes = one short window), which
+uses flash window semantics (fixed K, short scenes = one short window) by default, which
 equals the reference's enable_flash=False branch when run one scene per
-forward.  Test infrastructure only (see oracle/__init__.py).
+forward; cfg["enable_flash"] = False switches to the dense branch's batch-wide
+K = min(smallest scene, patch) (:173-176), pinned on a two-scene run of the reference (dense_batch.npz).  Test infrastructure only (see oracle/__init__.py).
 """
 import math
 
@@ -72,7 +73,7 @@ def _sparse_indices(pt):
     return torch.cat([pt.batch[:, None].to(torch.int32), pt.grid_coord.to(torch.int32)], 1)
 
 
-def _block(pt, W, p, H, K, order_index, nbr):
+def _block(pt, W, p, H, K, order_index, nbr, enable_flash=True):
     x = pt.feat
     # The conv reads point.sparse_conv_feat.features (modules.py:84-87), which
     # SerializedUnpooling leaves stale: right after an unpool it still holds the
@@ -85,6 +86,8 @@ def _block(pt, W, p, H, K, order_index, nbr):
     x = x + y
     y = _ln(x, W, p + ".norm1.0")
     qkv = _lin(y, W, p + ".attn.qkv")
+    if not enable_flash:      # dense branch :173-176: one patch size for the whole batch
+        K = min(int(torch.diff(pt.offset, prepend=pt.offset.new_zeros(1)).min()), K)
     y = O.window_attention(qkv, pt.order[order_index], pt.inverse[order_index], pt.offset.numpy(), H, K)
     x = x + _lin(y, W, p + ".attn.proj")
     y = _ln(x, W, p + ".norm2.0")
@@ -162,7 +165,7 @@ def backbone_forward(W, coord, grid_coord, feat, offset, cfg=BASE_CFG, perms=Non
         pt.nbr = nbrs[s]
         for i in range(cfg["enc_depths"][s]):
             pt = _block(pt, W, f"enc.enc{s}.block{i}", cfg["enc_num_head"][s], cfg["enc_patch_size"][s],
-                        i % len(orders), pt.nbr)
+                        i % len(orders), pt.nbr, cfg.get("enable_flash", True))
         if trace is not None:
             trace[f"enc{s}"] = pt.feat.clone()
     if not cfg.get("enc_mode", False):
@@ -170,7 +173,7 @@ def backbone_forward(W, coord, grid_coord, feat, offset, cfg=BASE_CFG, perms=Non
             pt = _unpool(pt, W, f"dec.dec{s}.up")
             for i in range(cfg["dec_depths"][s]):
                 pt = _block(pt, W, f"dec.dec{s}.block{i}", cfg["dec_num_head"][s], cfg["dec_patch_size"][s],
-                            i % len(orders), pt.nbr)
+                            i % len(orders), pt.nbr, cfg.get("enable_flash", True))
             if trace is not None:
                 trace[f"dec{s}"] = pt.feat.clone()
     return pt

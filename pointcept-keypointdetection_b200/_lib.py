@@ -13,6 +13,15 @@ LIB_PATH = os.path.join(_HERE, "libptv3_b200.so")
 c_i64, c_int, c_vp, c_sz = ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t
 c_f32, c_f64 = ctypes.c_float, ctypes.c_double
 
+class BlockParams(ctypes.Structure):
+    """ptv3_block_params (include/ptv3_b200.h)."""
+    _fields_ = [(k, ctypes.c_int) for k in ("c", "heads", "hidden", "k3", "patch", "mlp_fused", "attn_algo")] + \
+               [(k, ctypes.c_float) for k in ("scale", "eps_cpe", "eps_norm2")] + \
+               [(k, ctypes.c_void_p) for k in ("conv_w_packed", "conv_bias", "cpe_lin_w", "cpe_lin_b", "cpe_ln_g",
+                                               "cpe_ln_b", "norm1_g", "norm1_b", "norm2_g", "norm2_b", "qkv_w", "qkv_b",
+                                               "proj_w", "proj_b", "fc1_w", "fc1_b", "fc2_w", "fc2_b")]
+
+
 # name -> (restype, argtypes); order mirrors include/ptv3_b200.h
 SIGNATURES = {
     "ptv3_abi_version": (c_int, []),
@@ -51,6 +60,9 @@ SIGNATURES = {
     "ptv3_pack_kmajor": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_mlp_fused_supported": (c_int, [c_int, c_int]),
     "ptv3_mlp_fused": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
+    "ptv3_block_workspace": (c_sz, [ctypes.POINTER(BlockParams), c_i64, c_i64]),
+    "ptv3_block_fwd": (c_int, [ctypes.POINTER(BlockParams), c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
+                               c_vp, c_sz, c_vp]),
     "ptv3_debug_set": (c_int, [c_int, c_int]),
     "ptv3_device_error": (c_int, []),
     "ptv3_ln_residual": (c_int, [c_vp, c_int, c_vp, c_vp, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_i64, c_int,

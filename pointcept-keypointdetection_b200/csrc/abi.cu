@@ -5,6 +5,22 @@ namespace ptv3 {
 
 int64_t g_launch_count = 0;
 
+// Sticky device-side error word (bit mask): a kernel that meets input outside its contract ORs a bit in and skips the
+// offending work instead of producing silent garbage; ptv3_device_error() reads and clears it (one synchronising copy).
+//   1 = attention window record violates the ptv3_build_windows contract (k_len > max_len, queries outside the keys)
+//   2 = sparse-conv site outside the packed key range (batch id >= 1024 or a coordinate outside [0, 262128))
+__device__ int g_device_error_flag = 0;
+int* device_error_flag() {
+  int* p = nullptr;
+  return cudaGetSymbolAddress((void**)&p, g_device_error_flag) == cudaSuccess ? p : nullptr;
+}
+int device_error_fetch_and_clear() {
+  int v = 0, zero = 0;
+  if (cudaMemcpyFromSymbol(&v, g_device_error_flag, sizeof(int)) != cudaSuccess) return PTV3_ELAUNCH;
+  if (v != 0) cudaMemcpyToSymbol(g_device_error_flag, &zero, sizeof(int));
+  return v;
+}
+
 // ---- phase 1: per-chunk sums ------------------------------------------------
 __global__ void __launch_bounds__(kScanThreads) scan_chunk_sums(const uint32_t* __restrict__ in, int64_t n,
                                                                 uint32_t* __restrict__ partials, int chunks) {
@@ -101,5 +117,7 @@ const char* ptv3_error_string(int code) {
 }
 
 int64_t ptv3_launch_count(void) { return ptv3::g_launch_count; }
+
+int ptv3_device_error(void) { return ptv3::device_error_fetch_and_clear(); }
 
 }  // extern "C"

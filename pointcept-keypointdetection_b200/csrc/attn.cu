@@ -133,8 +133,6 @@ int attn_window_f16(const __nv_bfloat16* qkv, const int64_t* order, const int64_
 int attn_window_tm(const __nv_bfloat16* qkv, const int64_t* order, const int64_t* windows, const int64_t* n_windows,
                    int64_t n_windows_max, int64_t max_len, int h, float scale, __nv_bfloat16* out, int* redo,
                    cudaStream_t st);
-int* attn_error_flag();
-int attn_error_fetch_and_clear();
 extern int g_attn_f16_variant;
 extern int g_attn_tm_poly;
 extern int g_attn_lse_algo;
@@ -176,7 +174,7 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const
                             (__nv_bfloat16*)out, redo, st);
     if (rc != PTV3_OK) return rc;
     return attn_window_f16((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
-                           (__nv_bfloat16*)out, st, nullptr, attn_error_flag(), redo);
+                           (__nv_bfloat16*)out, st, nullptr, device_error_flag(), redo);
   }
   if (dtype == PTV3_BF16 && algo == 3) {
     if (max_len > 1024) return PTV3_EUNSUPPORTED;
@@ -188,7 +186,7 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const
                           (__nv_bfloat16*)out, st);
   if (dtype == PTV3_BF16 && algo != 1)      // 0 (auto) / 4: the f16-staged register kernel
     return attn_window_f16((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
-                           (__nv_bfloat16*)out, st, nullptr, attn_error_flag());
+                           (__nv_bfloat16*)out, st, nullptr, device_error_flag());
   if (algo >= 2) return PTV3_EUNSUPPORTED;
   int64_t qblocks = cdiv(max_len, kAttnThreads);
   if (qblocks > 65535) return PTV3_EINVAL;
@@ -213,7 +211,7 @@ int ptv3_attn_window_fwd_lse(const void* qkv, int dtype, const int64_t* order, c
   if (!qkv || !windows || !n_windows || !out || !lse) return PTV3_EINVAL;
   if (g_attn_lse_algo != 2)
     return attn_window_f16((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
-                           (__nv_bfloat16*)out, as_stream(stream), lse, attn_error_flag());
+                           (__nv_bfloat16*)out, as_stream(stream), lse, device_error_flag());
   return attn_window_tc((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, n, h, scale,
                         (__nv_bfloat16*)out, as_stream(stream), lse);
 }
@@ -231,6 +229,5 @@ int ptv3_debug_set(int key, int value) {
   return PTV3_EINVAL;
 }
 
-int ptv3_device_error(void) { return attn_error_fetch_and_clear(); }
 
 }  // extern "C"

@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(af::kThreads, kMinCtas) attn_window_f16_kernel
   const int kpad = (int)((kl + 63) >> 6) << 6;
   // contract of the window records (ptv3_build_windows): keys fit the launch's shared memory and contain the queries
   if (kpad > kpad_max || q0 < k0 || q0 + ql > k0 + kl) {
-    if (threadIdx.x == 0 && err) atomicExch(err, 1);
+    if (threadIdx.x == 0 && err) atomicOr(err, 1);
     return;
   }
   const uint32_t ks_addr = (uint32_t)__cvta_generic_to_shared(smem_raw);
@@ -389,20 +389,6 @@ __global__ void __launch_bounds__(af::kThreads, kMinCtas) attn_window_f16_kernel
         }
       }
   }
-}
-
-// sticky device-side error flag: a window record that violates the contract makes its CTA return without writing;
-// ptv3_device_error() reads and clears it (one synchronising copy; tests and the flash_attn shim call it)
-__device__ int g_attn_error_flag = 0;
-int* attn_error_flag() {
-  int* p = nullptr;
-  return cudaGetSymbolAddress((void**)&p, g_attn_error_flag) == cudaSuccess ? p : nullptr;
-}
-int attn_error_fetch_and_clear() {
-  int v = 0, zero = 0;
-  if (cudaMemcpyFromSymbol(&v, g_attn_error_flag, sizeof(int)) != cudaSuccess) return PTV3_ELAUNCH;
-  if (v != 0) cudaMemcpyToSymbol(g_attn_error_flag, &zero, sizeof(int));
-  return v;
 }
 
 int g_attn_lse_algo = 0;      // debug slot 8: 2 = training forward on the first-generation kernel

@@ -11,6 +11,8 @@ namespace ptv3 {
 
 extern int64_t g_launch_count;  // host-side count of kernel launches (abi.cu)
 
+int* device_error_flag();   // abi.cu: device address of the sticky error word (bit mask, see ptv3_device_error)
+
 inline int check_launch(int n_kernels = 1) {
   g_launch_count += n_kernels;
   return cudaGetLastError() == cudaSuccess ? PTV3_OK : PTV3_ELAUNCH;

@@ -9,6 +9,14 @@ namespace ptv3 {
 constexpr uint64_t kEmptyKey = ~0ull;
 constexpr int kCoordBias = 8;  // keeps shifted coordinates non-negative for |delta| <= 8
 
+// sites the 64-bit key can hold: batch id in [0, 1024), coordinates in [0, 2^18 - 2 * kCoordBias) (the bias keeps
+// neighbour offsets |delta| <= 8 non-negative and inside the field).  PRECONDITION of the backward (dX through the
+// mirrored weights relies on j = nbr[i,k] <=> i = nbr[j,k^3-1-k]): sites are unique, which GridSample / pooling
+// guarantee; duplicates are tolerated by the forward (the lowest row wins) but not by that symmetry.
+__device__ __forceinline__ bool site_in_range(int b, int x, int y, int z) {
+  constexpr unsigned kMax = (1u << 18) - 2u * kCoordBias;
+  return (unsigned)b < 1024u && (unsigned)x < kMax && (unsigned)y < kMax && (unsigned)z < kMax;
+}
 __device__ __forceinline__ uint64_t pack_site(int b, int x, int y, int z) {
   // 10 bits batch | 3 x 18 bits coordinates
   return ((uint64_t)(uint32_t)b << 54) | ((uint64_t)(uint32_t)(x + kCoordBias) << 36) |
@@ -26,9 +34,14 @@ __device__ __forceinline__ uint32_t hash_site(uint64_t k) {
 
 __global__ void __launch_bounds__(256) subm_insert_kernel(const int32_t* __restrict__ indices, int64_t n,
                                                           unsigned long long* __restrict__ keys,
-                                                          int* __restrict__ vals, uint32_t mask) {
+                                                          int* __restrict__ vals, uint32_t mask,
+                                                          int* __restrict__ err) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     int4 s = reinterpret_cast<const int4*>(indices)[i];
+    if (!site_in_range(s.x, s.y, s.z, s.w)) {   // would alias another site's key: leave it out and say so
+      if (err) atomicOr(err, 2);
+      continue;
+    }
     uint64_t key = pack_site(s.x, s.y, s.z, s.w);
     uint32_t slot = hash_site(key) & mask;
     while (true) {
@@ -407,7 +420,7 @@ int ptv3_subm_build_map(const int32_t* indices, int64_t n, int ksize, int32_t* n
   cudaStream_t st = as_stream(stream);
   cudaMemsetAsync(keys, 0xff, (size_t)cap * 8, st);
   cudaMemsetAsync(vals, 0x7f, (size_t)cap * 4, st);
-  subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1);
+  subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1, device_error_flag());
   int64_t total = n * ksize * ksize * ksize;
   subm_lookup_kernel<<<grid_for(total, 256, 16), 256, 0, st>>>(indices, n, ksize, keys, vals, cap - 1, nbr);
   return check_launch(2);
@@ -428,7 +441,7 @@ int ptv3_subm_stem_fused(const int32_t* indices, int64_t n, int ksize, const flo
   cudaStream_t st = as_stream(stream);
   cudaMemsetAsync(keys, 0xff, (size_t)cap * 8, st);
   cudaMemsetAsync(vals, 0x7f, (size_t)cap * 4, st);
-  subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1);
+  subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1, device_error_flag());
   const size_t smem = (size_t)k3 * 32 * sizeof(float4);
   static bool configured = false;
   if (!configured) {

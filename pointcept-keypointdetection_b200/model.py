@@ -15,9 +15,11 @@ unchanged; the forward of every module is re-designed around our fused ops:
     (no [order] gather, no [inverse] scatter, no padding copies);
   * pooling derives clusters and the pooled orders from the parent's orders
     without sorting.
-Attention uses the flash window semantics of the reference (fixed patch size,
-short scenes form one short window, :208-215); its enable_flash=False branch
-only coincides with that for one scene per forward.
+Attention follows BOTH window semantics of the reference: enable_flash=True keeps the
+fixed patch size (short scenes form one short window, :208-215); enable_flash=False
+(the setting of both fork configs) uses K = min(smallest scene of the batch, patch)
+for every scene (:173-176), which differs from the flash windows as soon as a batch
+holds a scene shorter than the patch.
 Training: in train() mode every entry point dispatches to train.py (autograd through the kernels, autograd.py).
 """
 import math
@@ -206,9 +208,12 @@ class SerializedAttention(PointModule):
             raise NotImplementedError("enable_rpe=True is not used by any target config (SURVEY.md 8a A4)")
         if channels // num_heads != 16:
             raise NotImplementedError("head_dim must be 16 (true for every PTv3 config, SURVEY.md fact 1)")
+        if attn_drop != 0.0 or proj_drop != 0.0:
+            raise NotImplementedError("attn_drop / proj_drop are 0 in every target config; the kernels have no dropout")
         self.channels, self.num_heads = channels, num_heads
         self.scale = qk_scale or (channels // num_heads) ** -0.5
         self.order_index = order_index
+        self.enable_flash = bool(enable_flash)
         self.patch_size_max = patch_size
         self.patch_size = patch_size
         self.qkv = nn.Linear(channels, channels * 3, bias=qkv_bias)
@@ -220,6 +225,14 @@ class SerializedAttention(PointModule):
     def get_windows(self, point):
         """Replaces get_padding_and_inverse (:115-170): per-window (q_start,q_len,k_start,k_len) records, cached in
         the Point like the reference caches pad/unpad/cu_seqlens."""
+        if not self.enable_flash:
+            # dense branch (:173-176): ONE patch size for the whole batch, min(smallest scene, patch_size_max).  Like
+            # the reference this reads the scene sizes on the host (once per Point: every block of a stage shares it)
+            if "attn_patch_dense" not in point:
+                off = point.offset
+                counts = torch.diff(off, prepend=off.new_zeros(1))
+                point["attn_patch_dense"] = int(counts.min().item())
+            self.patch_size = max(1, min(point["attn_patch_dense"], self.patch_size_max))
         key = f"windows_{self.patch_size}"
         if key not in point:
             point[key] = ops.build_windows(point.offset, self.patch_size, point.feat.shape[0])
@@ -297,6 +310,51 @@ class Block(PointModule):
     def _ln(ln):
         return ln.weight, ln.bias, ln.eps
 
+    native = True      # one C-ABI call per Block (ops.block_fwd) when the shapes allow; False = the op-by-op path
+
+    def _native_params(self):
+        """ptv3_block_params of this Block (bf16 inference), rebuilt when a parameter changes."""
+        attn, mlp, conv = self.attn, self.mlp[0], self.cpe[0]
+        c, hidden = self.channels, mlp.fc1.out_features
+        cd = torch.bfloat16
+        lins = [self.cpe[1], attn.qkv, attn.proj, mlp.fc1, mlp.fc2]
+        lns = [self.cpe[2], self.norm1[0], self.norm2[0]]
+        params = [conv.weight, conv.bias] + [q for l in lins for q in (l.weight, l.bias)] + \
+                 [q for l in lns for q in (l.weight, l.bias)]
+
+        def build():
+            fused = ops.mlp_fused_supported(c, hidden) and mlp.fc2.out_features == c
+            dev = conv.weight.device
+            zeros = lambda n, dt: torch.zeros(n, dtype=dt, device=dev)
+            lw = lambda l: l.weight.to(cd).contiguous()
+            lb = lambda l: l.bias.to(cd).contiguous() if l.bias is not None else zeros(l.out_features, cd)
+            w, b = conv._weights(cd)
+            t = dict(conv_w_packed=ops.subm_pack_weight(w), conv_bias=b if b is not None else zeros(c, torch.float32),
+                     cpe_lin_w=lw(self.cpe[1]), cpe_lin_b=lb(self.cpe[1]),
+                     cpe_ln_g=self.cpe[2].weight.float().contiguous(), cpe_ln_b=self.cpe[2].bias.float().contiguous(),
+                     norm1_g=self.norm1[0].weight.float().contiguous(), norm1_b=self.norm1[0].bias.float().contiguous(),
+                     norm2_g=self.norm2[0].weight.float().contiguous(), norm2_b=self.norm2[0].bias.float().contiguous(),
+                     qkv_w=lw(attn.qkv), qkv_b=lb(attn.qkv), proj_w=lw(attn.proj), proj_b=lb(attn.proj))
+            if fused:
+                t.update(fc1_w=ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), fc1_b=mlp.fc1.bias.float().contiguous(),
+                         fc2_w=ops.pack_kmajor(mlp.fc2.weight.to(cd), c), fc2_b=mlp.fc2.bias.float().contiguous())
+            else:
+                t.update(fc1_w=lw(mlp.fc1), fc1_b=lb(mlp.fc1), fc2_w=lw(mlp.fc2), fc2_b=lb(mlp.fc2))
+            return ops.block_params(c=c, heads=attn.num_heads, hidden=hidden, k3=conv.kernel_size ** 3,
+                                    patch=attn.patch_size, mlp_fused=int(fused), attn_algo=attn.algo,
+                                    scale=float(attn.scale), eps_cpe=float(self.cpe[2].eps),
+                                    eps_norm2=float(self.norm2[0].eps), **t)
+        return _cached(self, "native", params, build)
+
+    def _native_ok(self, cd):
+        mlp = self.mlp[0]
+        return (self.native and ops.NATIVE_BLOCK and cd == torch.bfloat16 and self.conv_algo != 1
+                and isinstance(mlp.act, nn.GELU) and mlp.act.approximate == "none"
+                and all(isinstance(m, nn.LayerNorm) for m in (self.cpe[2], self.norm1[0], self.norm2[0]))
+                and float(self.cpe[2].eps) == float(self.norm1[0].eps)
+                and ops.subm_conv_tc_supported(self.channels, self.channels, self.cpe[0].kernel_size ** 3)
+                and mlp.fc1.out_features % 4 == 0)
+
     @torch.no_grad()
     def forward(self, point):
         if self.training:
@@ -305,6 +363,16 @@ class Block(PointModule):
         x = point.feat if point.feat.dtype == torch.float32 else point.feat.float()
         sp = point.sparse_conv_feat
         conv_in = sp.features if sp.features.dtype == cd else sp.features.to(cd)
+        if self._native_ok(cd):
+            bp, _keep = self._native_params()
+            windows, nwin = self.attn.get_windows(point)
+            bp.patch, bp.attn_algo = int(self.attn.patch_size), int(self.attn.algo)
+            x, xcd = ops.block_fwd(bp, x.contiguous(), conv_in.contiguous(), self.cpe[0].neighbor_map(sp),
+                                   point.serialized_order[self.attn.order_index], windows, nwin)
+            point.feat = x
+            point["_feat_cd"] = xcd
+            point.sparse_conv_feat = sp.replace_feature(xcd)
+            return point
         # cpe: SubMConv3d -> Linear -> LayerNorm, + shortcut, then pre-norm of the attention
         y = self.cpe[0].conv(conv_in, sp, algo=self.conv_algo)
         y = F.linear(y, *self._lin(self.cpe[1], cd))

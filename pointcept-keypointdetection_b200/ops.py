@@ -312,6 +312,53 @@ def mlp_fused(x, w1_packed, b1, w2_packed, b2, hidden, residual=None, want_res=T
     return res_out, out16
 
 
+# ------------------------------------------------------------------ A8 one native call per Block
+NATIVE_BLOCK = True      # bench.py's per-op timing leg and A/B tests switch this off (op-by-op path, same kernels)
+
+
+def block_params(**kw):
+    """ptv3_block_params from keyword arguments: ints / floats by value, tensors by device pointer.  Returns (struct,
+    keepalive list) -- the caller caches both next to the prepared weights."""
+    bp = _lib.BlockParams()
+    keep = []
+    for k, v in kw.items():
+        if torch.is_tensor(v):
+            _need_cuda(v)
+            assert v.is_contiguous()
+            keep.append(v)
+            setattr(bp, k, v.data_ptr())
+        else:
+            setattr(bp, k, v)
+    return bp, keep
+
+
+_BLOCK_WS = {}
+
+
+def block_fwd(bp, x, conv_in, nbr, order, windows, n_windows):
+    """Block.forward (:318-338) in ONE library call.  x (n,c) fp32, conv_in (n,c) bf16 -> (x_out fp32, x_out bf16).
+    The workspace is a per-device buffer that only grows (stream-ordered reuse: every Block of a forward runs on the
+    same stream)."""
+    _need_cuda(x, conv_in, nbr, order, windows, n_windows)
+    lib = _lib.load()
+    assert x.dtype == torch.float32 and conv_in.dtype == torch.bfloat16 and x.is_contiguous() and conv_in.is_contiguous()
+    n, c = x.shape
+    x_out = torch.empty((n, c), dtype=torch.float32, device=x.device)
+    x_cd = torch.empty((n, c), dtype=torch.bfloat16, device=x.device)
+    if n == 0:
+        return x_out, x_cd
+    need = lib.ptv3_block_workspace(ctypes.byref(bp), n, windows.shape[0])
+    key = (x.device.index, _stream())
+    ws = _BLOCK_WS.get(key)
+    if ws is None or ws.numel() < need:
+        ws = _BLOCK_WS[key] = torch.empty(int(need * 1.25), dtype=torch.uint8, device=x.device)
+    with _timed("block_fwd", n=n, c=c):
+        _lib.check(lib.ptv3_block_fwd(ctypes.byref(bp), _p(x), _p(conv_in), _p(nbr), _p(order), _p(windows), _p(n_windows),
+                                      windows.shape[0], n, _p(x_out), _p(x_cd), _p(ws), ws.numel(), _stream()),
+                   "ptv3_block_fwd")
+    return x_out, x_cd
+
+
 # ------------------------------------------------------------------ A5 submanifold conv
 def subm_build_map(indices, ksize):
     """indices (N,4) int32 [b,x,y,z] -> nbr (N, ksize^3) int32 (-1 = absent)."""
@@ -439,8 +486,9 @@ def attn_window(qkv, order, windows, n_windows, num_heads, max_len, scale=None, 
 
 
 def device_error():
-    """Reads and clears the library's sticky device-side error flag (synchronises): 0 = none, 1 = an attention window
-    record violated the build_windows contract (k_len > max_len or queries outside the key range)."""
+    """Reads and clears the library's sticky device-side error word (synchronises), a bit mask: 1 = an attention window
+    record violated the build_windows contract (k_len > max_len or queries outside the key range); 2 = a sparse-conv
+    site outside the packed key range (batch id >= 1024 or a coordinate outside [0, 262128))."""
     return int(_lib.load().ptv3_device_error())
 
 

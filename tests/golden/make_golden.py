@@ -24,6 +24,9 @@ Fixtures (all inputs are seeded; the script is the provenance):
   eval.npz           reference OffsetKeypointEvaluator.eval() (hooks/offset_keypoint_evaluator.py) driven by a stub trainer
                      over two validation batches (with / without `scale`, a keypoint without masked rows, a scene
                      without any, a tied maximum of the predicted mask): the logged means and comm_info metric
+  dense_batch.npz    reference OffsetKeypointPTv3 with enable_flash=False on a TWO-scene batch of unequal sizes (the dense
+                     branch's batch-wide patch size K = min(smallest scene, patch), :173-176): eval prediction and a
+                     training step (loss, gradient norms, six gradient tensors)
   heads.npz          reference KeypointPTv3 (scatter_mean + regression MLP, C_in = 4) and
                      DefaultSegmentorV2 (20 classes, C_in = 6, BASELINE configs[2] shape)
                      forwards, one scene each, same deterministic weights
@@ -270,6 +273,54 @@ def gold_train(R):
     np.savez_compressed(os.path.join(HERE, "train.npz"), **out)
 
 
+def gold_dense_batch(R):
+    """ADVICE round 1 / VERDICT item 4: both fork configs ship enable_flash=False with batch 4 / 8, where the reference
+    uses ONE patch size K = min(smallest scene of the batch, patch) for every scene (point_transformer_v3m1_base.py:
+    173-176).  A two-scene batch of unequal sizes through the unmodified class: eval forward and a training step."""
+    from oracle import gridsample as G
+    scenes = []
+    for (R_, scale, seed) in [(5000, 0.62, 21), (1500, 0.3, 22)]:
+        coord, feat = synth.pig_scan(R_, scale=scale, seed=seed)
+        gs = G.grid_sample(coord, 0.02)
+        iu = gs["idx_unique"]
+        scenes.append((coord[iu], feat[iu], gs["grid_coord"][iu]))
+    cat = lambda j: np.concatenate([s_[j] for s_ in scenes])
+    offset = np.cumsum([len(s_[0]) for s_ in scenes])
+    out = dict(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset)
+    data = lambda: dict(coord=torch.from_numpy(cat(0)), grid_coord=torch.from_numpy(cat(2)), feat=torch.from_numpy(cat(1)),
+                        offset=torch.from_numpy(offset), grid_size=0.02)
+    for mode in ("eval", "train"):
+        m = R.OffsetKeypointPTv3(backbone_conf=dict(type="PT-v3m1", enable_flash=False, upcast_attention=False,
+                                                    upcast_softmax=False, drop_path=0.0, **BASE_CFG))
+        shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+        m.load_state_dict({k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}, strict=False)
+        torch.manual_seed(500)
+        out["perms"] = np.stack([torch.randperm(4).numpy() for _ in range(5)])
+        torch.manual_seed(500)
+        if mode == "eval":
+            m.eval()
+            with torch.no_grad():
+                out["pred"] = m(data())["pred"].numpy()
+        else:
+            m.train()
+            target = make_target(int(offset[-1]), 63)
+            d = data()
+            d["target"] = torch.from_numpy(target)
+            r = m(d)
+            r["loss"].backward()
+            out["target"], out["loss"] = target, np.float64(r["loss"].item())
+            names, norms = [], []
+            for k, p_ in m.named_parameters():
+                if p_.grad is not None:
+                    names.append(k)
+                    norms.append(p_.grad.norm().item())
+            out["grad_names"], out["grad_norms"] = np.array(names), np.array(norms, dtype=np.float64)
+            for i, k in enumerate(TRAIN_GRADS):
+                out[f"grad_{i}"] = dict(m.named_parameters())[k].grad.numpy()
+    print("dense batch: offsets", offset.tolist(), "loss", out["loss"])
+    np.savez_compressed(os.path.join(HERE, "dense_batch.npz"), **out)
+
+
 def _extract_function(path, name):
     import ast
     import typing
@@ -368,6 +419,9 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["gridsample"]:
         gold_gridsample(R)
         sys.exit(0)
+    if sys.argv[1:] == ["dense_batch"]:
+        gold_dense_batch(R)
+        sys.exit(0)
     gold_serialization(R)
     gold_gridsample(R)
     gold_padding(R)
@@ -378,6 +432,7 @@ if __name__ == "__main__":
     gold_voxelize(R)
     gold_spunet(R)
     gold_eval(R)
+    gold_dense_batch(R)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -310,6 +310,48 @@ def test_attention_window_contract_flag():
     assert ops.device_error() == 0                          # cleared by the read
 
 
+def test_block_native_call_equals_op_by_op():
+    """ptv3_block_fwd (one C-ABI call per Block: conv -> cuBLASLt Linear -> LN ... -> MLP) against the op-by-op path over
+    the same kernels, for a fused-MLP width (C = 32 / 64) and a cuBLAS-MLP width (C = 128), on a two-scene batch."""
+    from ptv3_b200 import ops
+    m = _model(torch.bfloat16)
+    scenes = [_scene(71, 6000, 0.6), _scene(72, 2500, 0.35)]
+    cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
+    offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
+    feats = {}
+    for native in (True, False):
+        ops.NATIVE_BLOCK = native
+        try:
+            hooks = []
+            for name, mod in (("enc0", m.backbone.enc.enc0), ("enc2", m.backbone.enc.enc2)):
+                hooks.append(mod.register_forward_hook(
+                    lambda _m, _i, o, name=name, native=native: feats.__setitem__((name, native), o.feat.clone())))
+            torch.manual_seed(9)
+            pred = m(dict(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset))["pred"]
+            feats[("pred", native)] = pred.clone()
+            for h in hooks:
+                h.remove()
+        finally:
+            ops.NATIVE_BLOCK = True
+    for k in ("enc0", "enc2", "pred"):
+        e = rel_l2(feats[(k, True)], feats[(k, False)])
+        assert e < 2e-3, (k, e)       # same kernels; the GEMMs may pick another cuBLASLt algorithm (bf16 rounding)
+
+
+def test_subm_map_site_range_flag():
+    """the 64-bit site key holds 10 bits of batch id and 18-bit coordinates; sites outside that range
+    used to alias silently.  They are now left out of the map and reported through ptv3_device_error()."""
+    from ptv3_b200 import ops
+    idx = torch.tensor([[0, 1, 2, 3], [0, 1, 2, 4], [3, 5, 5, 5]], dtype=torch.int32).cuda()
+    nbr = ops.subm_build_map(idx, 3)
+    assert ops.device_error() == 0 and int(nbr[0, 14]) == 1 and int(nbr[1, 12]) == 0
+    bad = torch.tensor([[0, 1, 2, 3], [1024, 1, 2, 3], [0, 1, 2, 1 << 18]], dtype=torch.int32).cuda()
+    nbr = ops.subm_build_map(bad, 3)
+    assert ops.device_error() == 2
+    assert int(nbr[0, 13]) == 0 and (nbr[0] >= 0).sum().item() == 1     # the valid site sees only itself
+    assert ops.device_error() == 0
+
+
 def _weights():
     from conftest import GOLDEN
     from ptv3_b200 import synth

@@ -287,6 +287,44 @@ def test_training_step_golden(golden, dtype, tol_loss, tol_grad):
     assert rel_l2(m.backbone.embedding.stem.norm.running_mean, torch.from_numpy(g["running_mean_stem"])) < 1e-3
 
 
+@pytest.mark.parametrize("dtype,tol,tol_grad", [(torch.float32, 1e-4, 1e-3), (torch.bfloat16, 1e-2, 0.3)])
+def test_dense_branch_two_scene_batch_golden(golden, dtype, tol, tol_grad):
+    """enable_flash=False with a batch (the setting of both fork configs, configs/my_dataset/offset_keypoint_ptv3.py:36,
+    configs/pigseg/semseg-ptv3-v1m1-0-base.py:61): one patch size K = min(smallest scene, patch) for every scene
+    (point_transformer_v3m1_base.py:173-176).  Eval prediction and one training step of the CUDA model against the
+    unmodified reference on a two-scene batch of unequal sizes (tests/golden/dense_batch.npz)."""
+    from make_golden_names import TRAIN_GRADS
+    from ptv3_b200 import model as M
+    g = golden("dense_batch")
+    W = _weights()
+    m = M.OffsetKeypointPTv3(backbone_conf=dict(P.BASE_CFG, drop_path=0.0, enable_flash=False, compute_dtype=dtype))
+    m.load_state_dict(W, strict=False)
+    m = m.cuda().eval()
+    data = lambda: dict(coord=torch.from_numpy(g["coord"]).cuda(), grid_coord=torch.from_numpy(g["grid_coord"]).cuda(),
+                        feat=torch.from_numpy(g["feat"]).cuda(), offset=torch.from_numpy(g["offset"]).cuda(), grid_size=0.02)
+    torch.manual_seed(500)
+    pred = m(data())["pred"]
+    e = rel_l2(pred, torch.from_numpy(g["pred"]))
+    assert e < tol, e
+    flash = M.OffsetKeypointPTv3(backbone_conf=dict(P.BASE_CFG, drop_path=0.0, compute_dtype=torch.float32))
+    flash.load_state_dict(W, strict=False)
+    torch.manual_seed(500)
+    assert rel_l2(flash.cuda().eval()(data())["pred"], torch.from_numpy(g["pred"])) > 1e-3     # really another function
+    m.train()
+    d = data()
+    d["target"] = torch.from_numpy(g["target"]).cuda()
+    torch.manual_seed(500)
+    out = m(d)
+    out["loss"].backward()
+    ref_loss = float(g["loss"])
+    assert abs(out["loss"].item() - ref_loss) < (1e-5 if dtype == torch.float32 else 1e-2) * abs(ref_loss)
+    params = dict(m.named_parameters())
+    errs = {k: rel_l2(params[k].grad, torch.from_numpy(g[f"grad_{i}"])) for i, k in enumerate(TRAIN_GRADS)}
+    print(f"dense-branch batch {dtype}: pred rel-L2 {e:.2e}, loss {out['loss'].item():.6f} vs {ref_loss:.6f}, "
+          f"worst grad rel-L2 {max(errs.values()):.2e}")
+    assert max(errs.values()) < tol_grad, errs
+
+
 def test_training_loss_decreases():
     """Five AdamW steps on a fixed two-scene batch (bf16 operands, drop_path on): the loss goes down and stays
     finite -- optimizer + autograd plumbing end to end."""

@@ -221,6 +221,29 @@ def test_training_grads_vs_reference(golden):
     assert ((got - ref).abs() / ref.clamp_min(1e-12)).max().item() < 1e-3
 
 
+def test_dense_branch_two_scene_batch_vs_reference(golden):
+    """enable_flash=False (both fork configs): the reference uses ONE patch size K = min(smallest scene, patch) for
+    the whole batch (point_transformer_v3m1_base.py:173-176).  Oracle with cfg enable_flash=False against the unmodified
+    reference on a two-scene batch of unequal sizes: eval prediction, training loss and gradients; and the flash
+    window semantics really differ on this batch."""
+    from make_golden_names import TRAIN_GRADS
+    g = golden("dense_batch")
+    W = _weights()
+    cfg = dict(P.BASE_CFG, enable_flash=False)
+    pt = P.backbone_forward(W, g["coord"], g["grid_coord"], g["feat"], g["offset"], cfg=cfg, perms=list(g["perms"]))
+    pred = P.offset_head(W, pt.feat)
+    ref = torch.from_numpy(g["pred"])
+    assert ((pred - ref).norm() / ref.norm()).item() < 1e-5
+    pt = P.backbone_forward(W, g["coord"], g["grid_coord"], g["feat"], g["offset"], perms=list(g["perms"]))
+    assert ((P.offset_head(W, pt.feat) - ref).norm() / ref.norm()).item() > 1e-3      # flash windows: another function
+    loss, grads = P.offset_keypoint_grads(W, g["coord"], g["grid_coord"], g["feat"], g["offset"], g["target"],
+                                          perms=list(g["perms"]), cfg=cfg)
+    assert abs(loss.item() - float(g["loss"])) < 1e-5 * abs(float(g["loss"]))
+    for i, k in enumerate(TRAIN_GRADS):
+        r = torch.from_numpy(g[f"grad_{i}"])
+        assert ((grads[k] - r).norm() / r.norm()).item() < 1e-4, k
+
+
 def test_voxelize_first_vs_reference(golden):
     """A0' (inference voxelisers): oracle restatement against the reference's own `voxelize_points` output, on a scan
     with points on / one ulp off the cell borders (float32 quotient)."""
