@@ -204,7 +204,7 @@ int ptv3_build_windows(const int64_t* offset, int64_t n_scenes, int64_t patch, i
  * for p in the window's queries, j in the window's keys, row(p) = order ? order[p] : p.
  * qkv (n,3,h,d) packed rows (= Linear(C,3C) output, :184-190 / flash layout :208-215);
  * out (n,h,d) in storage order (the reference's feat[inverse], :216-218). d == 16.
- * algo: 0 auto (bf16 -> 4, fp32 -> 1), 1 CUDA-core fp32-math kernel, 2 first-generation mma.sync kernel (bf16 P),
+ * algo: 0 auto (bf16 -> 2, fp32 -> 1), 1 CUDA-core fp32-math kernel, 2 first-generation mma.sync kernel (bf16 P),
  * 3 round-1 tcgen05/TMEM kernel (bf16, windows <= 1024, two-pass), 4 the register kernel (operands staged as f16 with
  * the 32-byte swizzle, reference maximum folded into the accumulator, two query tiles per warp),
  * 5 the single-pass tcgen05/TMEM kernel (bf16, windows <= 1024; needs ptv3_attn_window_workspace bytes; units it

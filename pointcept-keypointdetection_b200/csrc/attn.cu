@@ -181,10 +181,12 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order, const
     return attn_window_tc05((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
                             (__nv_bfloat16*)out, st);
   }
-  if (dtype == PTV3_BF16 && algo == 2)      // first-generation kernel (bf16 P, unswizzled K / V), kept for the ablation
+  // 0 (auto) / 2: the first-generation mma.sync kernel -- inside the model it is still the fastest one (bench step:
+  // attention 11.5 ms vs 12.3 ms with kernel 4, profiles/r02_attention.md)
+  if (dtype == PTV3_BF16 && (algo == 2 || algo == 0))
     return attn_window_tc((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, n, h, scale,
                           (__nv_bfloat16*)out, st);
-  if (dtype == PTV3_BF16 && algo != 1)      // 0 (auto) / 4: the f16-staged register kernel
+  if (dtype == PTV3_BF16 && algo != 1)      // 4: the f16-staged register kernel (the most accurate bf16 path)
     return attn_window_f16((const __nv_bfloat16*)qkv, order, windows, n_windows, n_windows_max, max_len, h, scale,
                            (__nv_bfloat16*)out, st, nullptr, device_error_flag());
   if (algo >= 2) return PTV3_EUNSUPPORTED;

@@ -28,6 +28,19 @@ def batch2offset(batch):
     return torch.cumsum(batch.bincount(), dim=0).long()
 
 
+_PERM_CACHE = {}
+
+
+def device_perm(perm, device):
+    """Row permutation drawn on the host (torch.randperm, CPU generator, like the reference) as a device index tensor.
+    There are only k! of them: cached, so that a forward does not issue a synchronous pageable H2D copy per draw."""
+    key = (device, tuple(perm.tolist()))
+    t = _PERM_CACHE.get(key)
+    if t is None:
+        t = _PERM_CACHE[key] = perm.to(device)
+    return t
+
+
 class SparseConvTensor:
     """features (N,C), indices (N,4) int32 [b,x,y,z]; `indice_dict` is the spconv-style cache shared by every
     tensor derived through replace_feature (holds the neighbour maps keyed by (indice_key, ksize))."""
@@ -98,7 +111,7 @@ class Point(dict):
         if shuffle_orders:
             perm = torch.randperm(code.shape[0])
             if not torch.equal(perm, torch.arange(code.shape[0])):
-                perm = perm.to(code.device)
+                perm = device_perm(perm, code.device)
                 code, order_, inverse = code[perm], order_[perm], inverse[perm]
         self["serialized_code"] = code
         self["serialized_order"] = order_
