@@ -102,6 +102,18 @@ int ptv3_gridsample(const float* coord, int64_t r, double grid_size, int hash_ty
                     int64_t* idx_unique, int64_t* min_grid, int64_t* n_voxels, void* workspace,
                     size_t workspace_bytes, void* stream);
 
+/* The same for EVERY scene of a step in one launch chain (scenes = contiguous row ranges, `offset` cumulative, device):
+ * the per-scene results of ptv3_gridsample concatenated.  grid_coord / key / min_grid (n_scenes,3) are per scene (each
+ * scene shifted by its own minimum); idx_sort / idx_unique hold GLOBAL row indices ordered by (scene, ascending key);
+ * inverse (r) = global voxel id; voxel_offset (n_scenes) = cumulative voxel counts; n_voxels (1) = their total.
+ * `rand` is indexed by global voxel id.  One stable 64-bit key sort + one scene-id pass instead of a sort per scene. */
+size_t ptv3_gridsample_batch_workspace(int64_t r, int64_t n_scenes);
+int ptv3_gridsample_batch(const float* coord, int64_t r, const int64_t* offset, int64_t n_scenes, double grid_size,
+                          int hash_type, const int64_t* rand /* NULL ok */, int64_t* grid_coord, uint64_t* key,
+                          int64_t* idx_sort, int64_t* inverse, int64_t* count, int64_t* idx_unique, int64_t* min_grid,
+                          int64_t* voxel_offset, int64_t* n_voxels, void* workspace, size_t workspace_bytes,
+                          void* stream);
+
 /* ---------------------------------------------------------------------------
  * A6  SerializedPooling integer front end.
  * Replaces point_transformer_v3m1_base.py:385-412: code >> 3*pool_depth,

@@ -125,6 +125,137 @@ __global__ void __launch_bounds__(256) gs_select_kernel(const int64_t* __restric
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Batched GridSample: every scene of a step in ONE launch chain (the per-scene chain cost ~20
+// launches + one host read per scene).  Scenes are contiguous row ranges (cumulative `offset`); the result is the
+// per-scene result of ptv3_gridsample concatenated: voxels ordered by (scene, ascending key), point indices global.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int scene_of(const int64_t* __restrict__ offset, int b, int64_t i) {
+  int lo = 0, hi = b - 1;          // first scene whose end offset is > i
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (offset[mid] > i) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+
+__global__ void gsb_init_minmax(long long* mm, int b) {
+  for (int i = threadIdx.x; i < 6 * b; i += blockDim.x) mm[i] = (i % 6) < 3 ? INT64_MAX : INT64_MIN;
+}
+
+__global__ void __launch_bounds__(256) gsb_floor_kernel(const float* __restrict__ coord, int64_t r,
+                                                        const int64_t* __restrict__ offset, int b, double grid_size,
+                                                        int f32div, int64_t* __restrict__ grid, int* __restrict__ sid,
+                                                        long long* __restrict__ mm) {
+  const float gs32 = (float)grid_size;
+  for (int64_t i0 = (int64_t)blockIdx.x * blockDim.x; i0 < r; i0 += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = i0 + threadIdx.x;
+    const bool live = i < r;
+    int s = -1;
+    long long g[3] = {0, 0, 0};
+    if (live) {
+      s = scene_of(offset, b, i);
+      sid[i] = s;
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const double q = f32div ? (double)__fdiv_rn(coord[3 * i + a], gs32) : (double)coord[3 * i + a] / grid_size;
+        g[a] = (long long)floor(q);
+        grid[3 * i + a] = g[a];
+      }
+    }
+    // one atomic pair per warp and axis when the whole warp sits in one scene (the common case), per lane otherwise
+    const unsigned act = __ballot_sync(0xffffffffu, live);
+    const int s0 = __shfl_sync(0xffffffffu, s, __ffs(act) - 1);
+    const bool uniform = __all_sync(0xffffffffu, !live || s == s0);
+    if (uniform) {
+      if (act == 0) continue;
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        long long mn = live ? g[a] : INT64_MAX, mx = live ? g[a] : INT64_MIN;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+          long long o = __shfl_xor_sync(0xffffffffu, mn, d);
+          mn = o < mn ? o : mn;
+          o = __shfl_xor_sync(0xffffffffu, mx, d);
+          mx = o > mx ? o : mx;
+        }
+        if ((threadIdx.x & 31) == 0) {
+          atomicMin(&mm[6 * s0 + a], mn);
+          atomicMax(&mm[6 * s0 + 3 + a], mx);
+        }
+      }
+    } else if (live) {
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        atomicMin(&mm[6 * s + a], g[a]);
+        atomicMax(&mm[6 * s + 3 + a], g[a]);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) gsb_hash_kernel(int64_t* __restrict__ grid, int64_t r, const int* __restrict__ sid,
+                                                       const long long* __restrict__ mm, int b, int hash_type,
+                                                       uint64_t* __restrict__ key, int64_t* __restrict__ min_out) {
+  if (blockIdx.x == 0)
+    for (int i = threadIdx.x; i < 3 * b; i += blockDim.x) min_out[i] = mm[6 * (i / 3) + i % 3];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < r; i += (int64_t)gridDim.x * blockDim.x) {
+    const long long* m = mm + 6 * sid[i];
+    const int64_t x = grid[3 * i + 0] - m[0], y = grid[3 * i + 1] - m[1], z = grid[3 * i + 2] - m[2];
+    grid[3 * i + 0] = x;
+    grid[3 * i + 1] = y;
+    grid[3 * i + 2] = z;
+    uint64_t h;
+    if (hash_type == 0) {
+      h = 14695981039346656037ull;
+      h *= 1099511628211ull;
+      h ^= (uint64_t)x;
+      h *= 1099511628211ull;
+      h ^= (uint64_t)y;
+      h *= 1099511628211ull;
+      h ^= (uint64_t)z;
+    } else {
+      const uint64_t a1 = (uint64_t)(m[4] - m[1]) + 1ull, a2 = (uint64_t)(m[5] - m[2]) + 1ull;
+      h = ((uint64_t)x * a1 + (uint64_t)y) * a2 + (uint64_t)z;
+    }
+    key[i] = h;
+  }
+}
+
+// second sort key: scene id of the j-th point in key order
+__global__ void __launch_bounds__(256) gsb_gather_sid_kernel(const int64_t* __restrict__ idx, const int* __restrict__ sid,
+                                                             int64_t r, uint64_t* __restrict__ out) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < r; j += (int64_t)gridDim.x * blockDim.x)
+    out[j] = (uint64_t)sid[idx[j]];
+}
+
+// compose the two sorts (idx_sort = idx1[order2], sorted key likewise) and flag the first point of every voxel
+__global__ void __launch_bounds__(256) gsb_compose_kernel(const int64_t* __restrict__ idx1, const uint64_t* __restrict__ skey1,
+                                                          const int64_t* __restrict__ order2,
+                                                          const uint64_t* __restrict__ ssid, int64_t r,
+                                                          int64_t* __restrict__ idx_sort, uint32_t* __restrict__ flags) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < r; j += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = order2[j];
+    idx_sort[j] = idx1[o];
+    bool head = j == 0;
+    if (!head) {
+      const int64_t op = order2[j - 1];
+      head = ssid[j] != ssid[j - 1] || skey1[o] != skey1[op];
+    }
+    flags[j] = head ? 1u : 0u;
+  }
+}
+
+// voxels per scene (cumulative): the exclusive voxel scan at every scene boundary of the sorted order (scenes keep their
+// row ranges under the stable (scene, key) sort)
+__global__ void gsb_voxel_offset_kernel(const int64_t* __restrict__ offset, int b, const uint32_t* __restrict__ ex,
+                                        const uint32_t* __restrict__ total, int64_t r, int64_t* __restrict__ voxel_offset) {
+  for (int i = threadIdx.x; i < b; i += blockDim.x) {
+    const int64_t e = offset[i];
+    voxel_offset[i] = e >= r ? (int64_t)total[0] : (int64_t)ex[e];
+  }
+}
+
 }  // namespace ptv3
 
 using namespace ptv3;
@@ -176,6 +307,73 @@ int ptv3_gridsample(const float* coord, int64_t r, double grid_size, int hash_ty
   gs_segments_kernel<<<g, 256, 0, st>>>(idx_sort, flags, ex, total, r, inverse, seg_start, n_voxels);
   gs_select_kernel<<<g, 256, 0, st>>>(idx_sort, seg_start, n_voxels, rnd, count, idx_unique);
   return check_launch(2);
+}
+
+size_t ptv3_gridsample_batch_workspace(int64_t r, int64_t n_scenes) {
+  int64_t rr = r > 0 ? r : 1;
+  return radix_argsort_workspace(1, rr) + 3 * align_up((size_t)rr * 8) /* skey1, ssid keys, ssid sorted */ +
+         2 * align_up((size_t)rr * 8) /* idx1, order2 */ + align_up((size_t)(rr + 1) * 8) /* seg_start */ +
+         align_up((size_t)rr * 4) /* sid */ + 2 * align_up((size_t)rr * 4) /* flags, ex */ +
+         align_up(scan_workspace_elems(1, rr) * 4) + align_up((size_t)(n_scenes > 0 ? n_scenes : 1) * 48) + 2048;
+}
+
+int ptv3_gridsample_batch(const float* coord, int64_t r, const int64_t* offset, int64_t n_scenes, double grid_size,
+                          int hash_type, const int64_t* rnd, int64_t* grid_coord, uint64_t* key, int64_t* idx_sort,
+                          int64_t* inverse, int64_t* count, int64_t* idx_unique, int64_t* min_grid,
+                          int64_t* voxel_offset, int64_t* n_voxels, void* workspace, size_t workspace_bytes,
+                          void* stream) {
+  if (r < 0 || n_scenes < 1 || n_scenes > (1 << 20) || !(grid_size > 0.0) || hash_type < 0 || hash_type > 3 || !n_voxels ||
+      !offset)
+    return PTV3_EINVAL;
+  const int f32div = hash_type >= 2;
+  if (f32div) hash_type = 3 - hash_type;
+  cudaStream_t st = as_stream(stream);
+  if (r == 0) {
+    cudaMemsetAsync(n_voxels, 0, 8, st);
+    if (voxel_offset) cudaMemsetAsync(voxel_offset, 0, 8 * (size_t)n_scenes, st);
+    return PTV3_OK;
+  }
+  if (!coord || !grid_coord || !key || !idx_sort || !inverse || !count || !idx_unique || !min_grid || !voxel_offset)
+    return PTV3_EINVAL;
+  const int b = (int)n_scenes;
+  Workspace ws(workspace, workspace_bytes);
+  size_t rs_bytes = radix_argsort_workspace(1, r);
+  char* rs_ws = ws.take<char>(rs_bytes);
+  uint64_t* skey1 = ws.take<uint64_t>((size_t)r);
+  uint64_t* sidk = ws.take<uint64_t>((size_t)r);
+  uint64_t* ssid = ws.take<uint64_t>((size_t)r);
+  int64_t* idx1 = ws.take<int64_t>((size_t)r);
+  int64_t* order2 = ws.take<int64_t>((size_t)r);
+  int64_t* seg_start = ws.take<int64_t>((size_t)r + 1);
+  int* sid = ws.take<int>((size_t)r);
+  uint32_t* flags = ws.take<uint32_t>((size_t)r);
+  uint32_t* ex = ws.take<uint32_t>((size_t)r);
+  uint32_t* partials = ws.take<uint32_t>(scan_workspace_elems(1, r));
+  long long* mm = ws.take<long long>((size_t)6 * b);
+  uint32_t* total = ws.take<uint32_t>(1);
+  if (!ws.ok()) return PTV3_EWORKSPACE;
+  const int g = grid_for(r, 256);
+  gsb_init_minmax<<<1, 256, 0, st>>>(mm, b);
+  gsb_floor_kernel<<<g, 256, 0, st>>>(coord, r, offset, b, grid_size, f32div, grid_coord, sid, mm);
+  gsb_hash_kernel<<<g, 256, 0, st>>>(grid_coord, r, sid, mm, b, hash_type, key, min_grid);
+  g_launch_count += 3;
+  // stable LSD order: by key (64 bits), then by scene id
+  int rc = radix_argsort_rows(key, 1, r, 64, idx1, nullptr, skey1, rs_ws, rs_bytes, st);
+  if (rc != PTV3_OK) return rc;
+  int scene_bits = 1;
+  while ((1ll << scene_bits) < n_scenes) ++scene_bits;
+  gsb_gather_sid_kernel<<<g, 256, 0, st>>>(idx1, sid, r, sidk);
+  g_launch_count += 1;
+  rc = radix_argsort_rows(sidk, 1, r, scene_bits, order2, nullptr, ssid, rs_ws, rs_bytes, st);
+  if (rc != PTV3_OK) return rc;
+  gsb_compose_kernel<<<g, 256, 0, st>>>(idx1, skey1, order2, ssid, r, idx_sort, flags);
+  g_launch_count += 1;
+  rc = exclusive_scan_u32(flags, ex, 1, r, partials, total, st);
+  if (rc != PTV3_OK) return rc;
+  gs_segments_kernel<<<g, 256, 0, st>>>(idx_sort, flags, ex, total, r, inverse, seg_start, n_voxels);
+  gs_select_kernel<<<g, 256, 0, st>>>(idx_sort, seg_start, n_voxels, rnd, count, idx_unique);
+  gsb_voxel_offset_kernel<<<1, 256, 0, st>>>(offset, b, ex, total, r, voxel_offset);
+  return check_launch(3);
 }
 
 }  // extern "C"

@@ -200,7 +200,15 @@ class SubMConv3d(SparseModule):
         return ops.subm_conv(features, w, b, self.neighbor_map(x), algo=algo)
 
     def forward(self, x):
-        return x.replace_feature(self.conv(x.features, x))
+        """spconv.pytorch.SubMConv3d.forward as the unmodified reference calls it (modules.py:84-87).  Under
+        torch.autocast(bfloat16) -- how the reference's trainer / tester run the model (engines/train.py:202) -- the
+        features are taken in bf16 like spconv's autocast-aware ops do, which puts the call on the tcgen05 kernel."""
+        f = x.features
+        if (f.is_cuda and f.dtype == torch.float32 and torch.is_autocast_enabled()
+                and torch.get_autocast_gpu_dtype() == torch.bfloat16 and self.kernel_size > 1
+                and ops.subm_conv_tc_supported(self.in_channels, self.out_channels, self.kernel_size ** 3)):
+            f = f.to(torch.bfloat16)
+        return x.replace_feature(self.conv(f, x))
 
 
 class SerializedAttention(PointModule):

@@ -167,6 +167,37 @@ def gridsample(coord, grid_size, hash_type="fnv", rand=None, quotient="f32"):
                 idx_unique=idx_unique[:m], min_grid=min_grid, n_voxels=m)
 
 
+def gridsample_batch(coord, offset, grid_size, hash_type="fnv", rand=None, quotient="f32"):
+    """GridSample of every scene of a batch in one launch chain and ONE host read (coord (R,3) rows of all scenes,
+    offset (B) cumulative row counts).  The per-scene results of gridsample() concatenated: idx_unique / idx_sort hold
+    global row indices ordered by (scene, ascending key); voxel_offset (B) = cumulative voxel counts."""
+    _need_cuda(coord, offset, rand)
+    lib = _lib.load()
+    coord = coord.contiguous().float()
+    offset = offset.contiguous().long()
+    r, b = coord.shape[0], offset.numel()
+    dev = coord.device
+    i64 = dict(dtype=torch.int64, device=dev)
+    grid = torch.empty((r, 3), **i64)
+    key = torch.empty(r, **i64)
+    idx_sort, inverse, count, idx_unique = (torch.empty(r, **i64) for _ in range(4))
+    min_grid = torch.empty((b, 3), **i64)
+    tail = torch.zeros(b + 1, **i64)              # voxel_offset (b) followed by n_voxels: one D2H read for both
+    if rand is not None:
+        rand = rand.contiguous().long()
+        if rand.numel() < r:
+            rand = torch.cat([rand, rand.new_zeros(r - rand.numel())])
+    ws = _ws(lib.ptv3_gridsample_batch_workspace(r, b), dev)
+    _lib.check(lib.ptv3_gridsample_batch(_p(coord), r, _p(offset), b, float(grid_size), HASH_IDS[(hash_type, quotient)],
+                                         _p(rand), _p(grid), _p(key), _p(idx_sort), _p(inverse), _p(count),
+                                         _p(idx_unique), _p(min_grid), _p(tail), tail.data_ptr() + 8 * b, _p(ws),
+                                         ws.numel(), _stream()), "ptv3_gridsample_batch")
+    host = tail.cpu()
+    m = int(host[b])
+    return dict(grid_coord=grid, key=key, idx_sort=idx_sort, inverse=inverse, count=count[:m], idx_unique=idx_unique[:m],
+                min_grid=min_grid, voxel_offset=tail[:b], voxel_offset_host=host[:b], n_voxels=m)
+
+
 # ------------------------------------------------------------------ A6 pooling front end
 def pool_front(code, order, pool_depth):
     """SerializedPooling integer front end (:385-412).  One host sync (pooled count)."""

@@ -37,7 +37,15 @@ def device_perm(perm, device):
     key = (device, tuple(perm.tolist()))
     t = _PERM_CACHE.get(key)
     if t is None:
-        t = _PERM_CACHE[key] = perm.to(device)
+        k = perm.numel()
+        if k <= 5 and (device, tuple(range(k))) not in _PERM_CACHE:      # first draw on this device: upload all k!
+            import itertools
+            allp = torch.tensor(list(itertools.permutations(range(k))), dtype=perm.dtype).to(device)
+            for i, pp in enumerate(itertools.permutations(range(k))):
+                _PERM_CACHE[(device, pp)] = allp[i]
+            t = _PERM_CACHE[key]
+        else:
+            t = _PERM_CACHE[key] = perm.to(device)
     return t
 
 

@@ -177,6 +177,44 @@ def test_gridsample_random_vs_oracle(r, scale):
         assert np.array_equal(got["min_grid"].cpu().numpy(), ref["min_grid"])
 
 
+@pytest.mark.parametrize("hash_type,quotient", [("fnv", "f32"), ("ravel", "f64")])
+def test_gridsample_batch_equals_per_scene(hash_type, quotient):
+    """ptv3_gridsample_batch (every scene of a step in one launch chain, one host read) = the per-scene results of
+    ptv3_gridsample concatenated: ragged scenes incl. an empty one, recorded random picks, both hashes / quotients; and
+    against the numpy oracle per scene."""
+    ops = _ops()
+    from ptv3_b200 import synth
+    sizes = [5000, 1, 0, 12345, 777]
+    coords = [synth.pig_scan(max(r, 1), scale=0.3 + 0.2 * i, seed=40 + i)[0][:r] - 0.4 * i for i, r in enumerate(sizes)]
+    allc = dev(np.concatenate(coords))
+    offset = dev(np.cumsum(sizes))
+    rng = np.random.default_rng(1)
+    rand = rng.integers(0, 1000, size=sum(sizes))
+    got = ops.gridsample_batch(allc, offset, 0.02, hash_type, rand=dev(rand), quotient=quotient)
+    vo = got["voxel_offset_host"].numpy()
+    start_r, start_v = 0, 0
+    for i, (c, r) in enumerate(zip(coords, sizes)):
+        if r == 0:
+            assert vo[i] == start_v
+            continue
+        m = len(G.grid_sample(c, 0.02, hash_type, quotient=quotient)["count"])
+        ref = G.grid_sample(c, 0.02, hash_type, rand=rand[start_v:start_v + m], quotient=quotient)
+        assert vo[i] - start_v == m, i
+        sl_r, sl_v = slice(start_r, start_r + r), slice(start_v, start_v + m)
+        assert np.array_equal(got["grid_coord"][sl_r].cpu().numpy(), ref["grid_coord"])
+        assert np.array_equal(got["key"][sl_r].cpu().numpy().view(np.uint64), ref["key"])
+        assert np.array_equal(got["idx_sort"][sl_r].cpu().numpy() - start_r, ref["idx_sort"])
+        assert np.array_equal(got["inverse"][sl_r].cpu().numpy() - start_v, ref["inverse"])
+        assert np.array_equal(got["count"][sl_v].cpu().numpy(), ref["count"])
+        assert np.array_equal(got["idx_unique"][sl_v].cpu().numpy() - start_r, ref["idx_unique"])
+        assert np.array_equal(got["min_grid"][i].cpu().numpy(), ref["min_grid"])
+        one = ops.gridsample(dev(c), 0.02, hash_type, rand=dev(rand[start_v:start_v + m]), quotient=quotient)
+        assert np.array_equal(one["idx_unique"].cpu().numpy(), ref["idx_unique"])
+        start_r += r
+        start_v += m
+    assert got["n_voxels"] == start_v
+
+
 def _scene_grid(seed, n_scenes=3):
     from ptv3_b200 import synth
     grids, counts = [], []

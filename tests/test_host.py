@@ -198,3 +198,41 @@ def test_evaluator_sums_world_size_2_gloo():
     for rank, mean_dist, per_kp, counts in res:
         assert mean_dist == 13.0 / (5 + 1e-6)
         assert per_kp == [4.5 / (5 + 1e-6), 5.5 / (5 + 1e-6), 3.0 / (1 + 1e-6)] and counts == [5, 5, 1]
+
+
+def test_reference_builds_over_shims():
+    """VERDICT r01 weak #4 / north star "the reference runs unchanged": in a fresh interpreter ptv3_b200.shims.install(
+    force=True) registers OUR spconv / torch_scatter / flash_attn modules, the UNMODIFIED reference files
+    point_transformer_v3m1_base.py + offset_keypoint_ptv3.py are imported over them, the model is built and its state_dict
+    names / shapes equal the frozen reference ones (tests/golden/param_shapes.json).  Needs /root/reference: build
+    container only; the GPU-side half is tests/test_gpu_shims.py (replay of the frozen call trace)."""
+    import json
+    import subprocess
+    import sys
+    sys.path.insert(0, os.path.join(REPO, "tests", "golden"))
+    import ref_loader
+    if not ref_loader.available():
+        pytest.skip("reference tree not present (GPU box)")
+    out = subprocess.run([sys.executable, os.path.join(REPO, "tests", "golden", "make_shim_trace.py"), "structure"],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    got = json.loads(out.stdout.strip().splitlines()[-1])
+    with open(os.path.join(REPO, "tests", "golden", "param_shapes.json")) as f:
+        ref = json.load(f)
+    assert got == ref
+
+
+def test_shim_trace_covers_every_third_party_call_site():
+    """The frozen call sequence of one reference forward (tests/golden/shim_trace.json): 4 encodes, 23 SubMConv3d
+    forwards (stem + 22 Blocks), 22 flash-attention calls, 8 segment_csr calls (max + mean per pooling) -- exactly the
+    call sites SURVEY.md 8b lists; shims.py exposes an entry point for each."""
+    import json
+    from ptv3_b200 import shims
+    with open(os.path.join(REPO, "tests", "golden", "shim_trace.json")) as f:
+        tr = json.load(f)
+    kinds = {}
+    for c in tr["calls"]:
+        kinds[c["op"]] = kinds.get(c["op"], 0) + 1
+    assert kinds == {"encode": 4, "SubMConv3d.forward": 23, "flash_attn_varlen_qkvpacked_func": 22, "segment_csr": 8}
+    assert callable(shims.segment_csr) and callable(shims.flash_attn_varlen_qkvpacked_func)
+    assert hasattr(shims.SubMConv3d, "forward")
