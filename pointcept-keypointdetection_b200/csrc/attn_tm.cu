@@ -1,27 +1,32 @@
-// A4: serialized window attention on the 5th-generation tensor cores, second design (tcgen05 + TMEM), head_dim 16.
+// A4: serialized window attention on the 5th-generation tensor cores (tcgen05 + TMEM), head_dim 16.
 //
 // Reference: SerializedAttention.forward, point_transformer_v3m1_base.py:172-222 (flash branch :208-215).
 //
-// What round 1's tcgen05 kernel (attn_tc05.cu) got wrong and this one changes (profiles/r02_attention.md):
-//   * S was read out of TMEM TWICE (exact two-pass softmax) in 32-column sips with an mbarrier round trip per 64 keys.
-//     Here S is read ONCE.  The exponent reference of a row is the maximum over its FIRST 128 keys and never moves:
-//     P = 2^(s - m) is stored as bf16 (8 exponent bits) and accumulated in fp32, so a later score above the reference
-//     needs no rescaling of O -- nothing overflows until a score exceeds the reference by ~2^100, nothing of weight is
-//     lost unless the reference overshoots the true maximum (it cannot: it is a lower bound).  The epilogue checks
-//     every denominator (finite, > 0); a (window, head) that fails is flagged and recomputed by the register kernel
-//     (attn_f16.cu) -- scores that spread over more than 100 octaves inside one row.
-//   * S tiles are 128 queries x 64 keys (one tcgen05.mma M128 N64 K16), FOUR of them in flight.  The 16 exponential
-//     warps are 4 per TMEM lane quarter (= per scheduler); warp (q, i) owns the rows of quarter q in every step
-//     g = i (mod 4), all 64 columns: one barrier round trip per 2048 scores, and the four warps of a scheduler are by
-//     construction at DIFFERENT steps, so the control / TMEM phase of one overlaps the exponential phase of the others
-//     (the first version gave every warp a 32 x 32 corner of every tile: all sixteen marched in lockstep and the
-//     exponential unit idled during the common control phase: ncu XU 54 %).
-//   * per step and thread: tcgen05.ld of 64 fp32 scores -> one FFMA + one MUFU per score -> bf16x2 -> tcgen05.st: P goes
-//     back to TENSOR MEMORY and is the A operand of P V from there (tcgen05.mma with A in TMEM): no shared-memory round
-//     trip, no generic->async proxy fence.  No HMMA, no ldmatrix, no shuffles, no row-maximum tracking on the
-//     schedulers.  The denominator comes out of the P V MMA through a ones column in V.
-//   * the issuer thread refills an S tile as soon as its owner has read it (Q K^T runs four steps ahead) and issues
-//     P V when the owner has written P; both across query-tile boundaries.
+// Design (the measurements behind every choice: profiles/r02_attention.md):
+//   * S is read out of tensor memory ONCE.  The exponent reference of a row is the maximum over its FIRST chunk of keys
+//     and never moves: P = 2^(s - m) is stored as bf16 (8 exponent bits) and accumulated in fp32, so a later score
+//     above the reference needs no rescaling of O -- nothing overflows until a score exceeds the reference by ~2^100,
+//     nothing of weight is lost because the reference is a lower bound of the true maximum.  The epilogue checks every
+//     denominator (finite, > 0); a (window, head) that fails is flagged and recomputed by the register kernel
+//     (attn_f16.cu) inside the same C-ABI call -- scores that spread over more than 100 octaves inside one row.
+//   * per step: S = Q K^T for 128 queries x 32 keys (tcgen05.mma M128 N32 K16) -> tcgen05.ld, one FFMA + one MUFU (or
+//     an FMA-pipe polynomial) per score, bf16x2 -> tcgen05.st: P goes back to TENSOR MEMORY and is the A operand of
+//     P V from there (tcgen05.mma with A in TMEM): no shared-memory round trip, no generic->async proxy fence.  The
+//     denominator comes out of the same P V MMA through a ones column in V (N = 32: 16 dims | ones | zeros).
+//   * MMA count is a resource: a tcgen05.mma M128 x N x K16 costs >= 45.6 clk for every N <= 64 (tools/ubench/pipes.cu),
+//     so a step issues exactly three (Q K^T + two K = 16 slices of P V = 137 clk per 4 096 scores, a 30 scores / clk /
+//     SM ceiling); a variant with a separate ones MMA (5 per step) was capped at 14 scores / clk / SM by the issue rate.
+//   * one CTA per SM with 20 exponential warps = 5 step classes x 4 TMEM lane quarters; warp (q, i) owns rows
+//     32q..32q+31 of every step g = i (mod 5), so the five exponential warps of a scheduler sit at different steps and
+//     the control / TMEM phase of one overlaps the exponential phase of the others (a first version gave every warp a
+//     corner of every tile: all warps marched in lockstep and the exponential unit idled, ncu XU 54 %; four classes
+//     reached 58 - 70 %).
+//   * ONE ISSUER THREAD PER STEP CLASS: wait -> tcgen05.mma -> tcgen05.commit costs a single thread ~400 clk per
+//     round trip whatever the tile size, so one (or two) issuer threads for all classes capped the kernel at one step
+//     per ~420 clk (ncu: 57 % of the stall samples = exponential warps waiting for their S tile).  Each class's issuer
+//     refills the class's S tile as soon as its owner has read it (Q K^T of step g + 5 runs during the exponentials of
+//     step g) and fires P V when the owner has written P.  O is zeroed by the epilogue and only ever accumulated,
+//     because the issuers of one query tile are not ordered among themselves.
 // Output rows are written straight to storage order (the reference's [inverse] scatter, :216-218).
 #include "common.cuh"
 #include "tc05.cuh"
@@ -33,20 +38,21 @@ using namespace tc05;
 namespace tm {
 constexpr int D = 16;
 constexpr int QT = 128;          // queries per tile (UMMA M)
-constexpr int KC = 64;           // keys per S tile (UMMA N)
+constexpr int KC = 32;           // keys per step (UMMA N of S, two K = 16 slices of P V)
 constexpr int MAXK = 1024;       // keys / queries per window
-constexpr int N_EXP = 16;        // exponential warps
-constexpr int THREADS = (N_EXP + 2) * 32;   // warps 0..15 exponentials, warp 16 = Q K^T issuer (and TMEM allocation), 17 = P V issuer
-constexpr int NSB = 4;           // S tiles in flight (64 fp32 columns each); also P tiles (64 keys x bf16 = 32 columns)
+constexpr int NCLS = 3;          // step classes = S / P tiles in flight (per CTA; two CTAs per SM)
+constexpr int N_EXP = 4 * NCLS;  // exponential warps
+constexpr int THREADS = (N_EXP + NCLS) * 32;   // + one MMA-issuer warp per step class
 constexpr int Q_OFF = 0;                          // 8 tiles x 4096 B   (K-major, no swizzle, 8-row core matrices)
 constexpr int K_OFF = Q_OFF + MAXK * 32;          // 32768
-constexpr int V_OFF = K_OFF + MAXK * 32;          // 65536: 128 key groups x 512 B (MN-major: d0-7 | d8-15 | ones | 0)
-constexpr int BAR_OFF = V_OFF + MAXK * 64;        // 131072
+constexpr int V_OFF = K_OFF + MAXK * 32;          // 65536: 128 key groups x 256 B (MN-major: d0-7 | d8-15)
+constexpr int ONES_OFF = V_OFF + MAXK * 32;       // 98304: 2 key groups x 256 B, column 0 = 1 (the denominator)
+constexpr int BAR_OFF = ONES_OFF + 512;           // 98816
 constexpr int MX_OFF = BAR_OFF + 256;             // exponent references of 4 query tiles in flight: [4][128 rows] fp32
-constexpr int SMEM_BYTES = MX_OFF + 2048 + 1024;  // + alignment slack
-constexpr int TMEM_COLS = 512;                    // S: 4 x 64 | P: 4 x 32 at 256 | O: 2 x 32 at 384
-constexpr int P_COL = NSB * KC;
-constexpr int O_COL = P_COL + NSB * 32;
+constexpr int SMEM_BYTES = MX_OFF + 2048 + 64 + 1024;  // + the TMEM address slot + alignment slack
+constexpr int TMEM_COLS = 256;                    // S: 3 x 32 | P: 3 x 16 at 96 | O: 2 x 32 at 144
+constexpr int P_COL = NCLS * KC;
+constexpr int O_COL = P_COL + NCLS * 16;
 
 __device__ __forceinline__ float ex2f(float x) {
   float y;
@@ -101,7 +107,7 @@ __device__ __forceinline__ uint64_t desc_plain(uint32_t saddr, uint32_t lbo, uin
 
 // POLYN: every 8 consecutive keys, POLYN exponentials go to the FMA-pipe polynomial instead of the MUFU unit
 template <int POLYN>
-__global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
+__global__ void __launch_bounds__(tm::THREADS, 2) attn_window_tm_kernel(
     const __nv_bfloat16* __restrict__ qkv, const int64_t* __restrict__ order, const int64_t* __restrict__ windows,
     const int64_t* __restrict__ n_windows, int h, float scale_log2, __nv_bfloat16* __restrict__ out,
     int* __restrict__ redo /* (n_windows_max * h) flags: 1 = recompute with the register kernel */) {
@@ -121,25 +127,26 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t sb = smem_u32(smem);
-  // barriers: s_full[4] s_free[4] p_full[4] p_free[4] m_full[4] o_full[2] o_free[2]
+  // barriers: s_full[NCLS] s_free[NCLS] p_full[NCLS] p_free[NCLS] m_full[4] o_full[2] o_free[2]
   const uint32_t bar0 = sb + BAR_OFF;
   auto s_full = [&](uint32_t b) { return bar0 + 8u * b; };
-  auto s_free = [&](uint32_t b) { return bar0 + 8u * (4u + b); };
-  auto p_full = [&](uint32_t b) { return bar0 + 8u * (8u + b); };
-  auto p_free = [&](uint32_t b) { return bar0 + 8u * (12u + b); };
-  auto m_full = [&](uint32_t b) { return bar0 + 8u * (16u + b); };
-  auto o_full = [&](uint32_t b) { return bar0 + 8u * (20u + b); };
-  auto o_free = [&](uint32_t b) { return bar0 + 8u * (22u + b); };
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_OFF + 240);
+  auto s_free = [&](uint32_t b) { return bar0 + 8u * (NCLS + b); };
+  auto p_full = [&](uint32_t b) { return bar0 + 8u * (2 * NCLS + b); };
+  auto p_free = [&](uint32_t b) { return bar0 + 8u * (3 * NCLS + b); };
+  auto m_full = [&](uint32_t b) { return bar0 + 8u * (4 * NCLS + b); };
+  auto o_full = [&](uint32_t b) { return bar0 + 8u * (4 * NCLS + 4 + b); };
+  auto o_free = [&](uint32_t b) { return bar0 + 8u * (4 * NCLS + 6 + b); };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + MX_OFF + 2048);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
   if (tid == 0) {
-    for (uint32_t b = 0; b < NSB; ++b) {     // 4 = one arrival per lane quarter (the four warps that own a step)
+    for (uint32_t b = 0; b < NCLS; ++b) {     // 4 = one arrival per lane quarter (the four warps that own a step)
       mbar_init(s_full(b), 1); mbar_init(s_free(b), 4);
       mbar_init(p_full(b), 4); mbar_init(p_free(b), 1);
-      mbar_init(m_full(b), 4);
     }
-    for (uint32_t b = 0; b < 2; ++b) { mbar_init(o_full(b), 1); mbar_init(o_free(b), 4); }
+    for (uint32_t b = 0; b < 4; ++b) mbar_init(m_full(b), 4);
+    // o_full: one commit per class that owns a chunk of the query tile (its last P V of the tile)
+    for (uint32_t b = 0; b < 2; ++b) { mbar_init(o_full(b), (uint32_t)(nc < NCLS ? nc : NCLS)); mbar_init(o_free(b), 4); }
     mbar_fence_init();
   }
   if (warp == N_EXP) tmem_alloc<TMEM_COLS>(smem_u32(tmem_slot));
@@ -150,7 +157,7 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
   const int q_rel = (int)(q0 - k0);
   for (int j = tid; j < nc * KC; j += THREADS) {
     const uint32_t kd = sb + K_OFF + (j >> 3) * 256 + (j & 7) * 16;
-    const uint32_t vd = sb + V_OFF + (j >> 3) * 512 + (j & 7) * 16;
+    const uint32_t vd = sb + V_OFF + (j >> 3) * 256 + (j & 7) * 16;
     if (j < kl) {
       const int64_t row = order ? order[k0 + j] : k0 + j;
       const __nv_bfloat16* qp = qbase + row * rs;
@@ -160,7 +167,6 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
       cp_async16(kd + 128, kp + 8, 16u);
       cp_async16(vd, vp, 16u);
       cp_async16(vd + 128, vp + 8, 16u);
-      asm volatile("st.shared.v4.u32 [%0], {%1, %2, %2, %2};" ::"r"(vd + 256), "r"(0x00003f80u), "r"(0u) : "memory");
       const int qi = j - q_rel;      // this key row is query qi of the window (queries are a sub-range of the keys)
       if (qi >= 0 && qi < ql) {
         const uint32_t qd = sb + Q_OFF + (qi >> 3) * 256 + (qi & 7) * 16;
@@ -169,9 +175,12 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
       }
     } else {
       st_shared_zero16(kd); st_shared_zero16(kd + 128);
-      st_shared_zero16(vd); st_shared_zero16(vd + 128); st_shared_zero16(vd + 256);
+      st_shared_zero16(vd); st_shared_zero16(vd + 128);
     }
-    st_shared_zero16(vd + 384);
+  }
+  if (tid < 32) {     // the ones block: 16 keys x 16 columns, column 0 = 1.0 (bf16), same MN-major layout as V
+    const uint32_t od = sb + ONES_OFF + (tid >> 4) * 256 + ((tid >> 1) & 7) * 16 + (tid & 1) * 128;
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %2, %2};" ::"r"(od), "r"((tid & 1) ? 0u : 0x00003f80u), "r"(0u) : "memory");
   }
   for (int i = ql + tid; i < n_qt * QT; i += THREADS) {     // rows of the last query tile past the last query
     const uint32_t qd = sb + Q_OFF + (i >> 3) * 256 + (i & 7) * 16;
@@ -185,64 +194,84 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
   fence_after_sync();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == N_EXP) {
-    // ============ Q K^T issuer: refills an S tile as soon as its owner has read it.  Both issuers sleep between polls:
-    // they have the highest warp ids = the highest issue priority on their schedulers, a hot spin would steal issue
-    // slots from the exponential warps there ============
+  if (warp < 4) {     // O accumulators start at zero: the P V MMAs only ever accumulate (see the issuers)
+    uint32_t z[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) z[j] = 0u;
+    const uint32_t lb = (uint32_t)(warp * 32) << 16;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) tmem_st16(tmem + lb + O_COL + k * 16, z);
+    tmem_st_wait();
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+
+  if (warp >= N_EXP) {
+    // =========================== MMA issuer of step class cls = warp - N_EXP ===========================
     if (elect_one_sync()) {
-      constexpr uint32_t idesc_s = idesc_bf16_f32(QT, KC);                    // S: M128 N64, A and B K-major
-      int tq = 0, cq = 0;      // (query tile, chunk) of the next Q K^T
-      for (int g = 0; g < G; ++g) {
-        const uint32_t b = (uint32_t)g & 3u;
-        if (g >= NSB) {
-          mbar_wait_sleep(s_free(b), (((uint32_t)g >> 2) & 1u) ^ 1u, 64);      // step g - 4 has been read
-          fence_after_sync();
-        }
+      const int cls = warp - N_EXP;
+      constexpr uint32_t idesc_s = idesc_bf16_f32(QT, KC);                    // S: M128 N32, A and B K-major
+      constexpr uint32_t idesc_o = idesc_bf16_f32(QT, 16) | (1u << 16);       // M128 N16, B MN-major (V and the ones block)
+      const uint64_t ones_desc = desc_plain(sb + ONES_OFF, 256, 128);
+      const uint32_t b = (uint32_t)cls;
+      int tq = 0, cq = cls;    // (query tile, chunk) of this class's next Q K^T
+      while (cq >= nc) { cq -= nc; ++tq; }
+      int t = tq, c = cq;      // ... and of its next P V
+      auto issue_qk = [&]() {
         mma_bf16_ss(tmem + b * KC, desc_plain(sb + Q_OFF + tq * 4096, 128, 256),
-                    desc_plain(sb + K_OFF + cq * 2048, 128, 256), idesc_s, 0u);
+                    desc_plain(sb + K_OFF + cq * 1024, 128, 256), idesc_s, 0u);
         mma_commit(s_full(b));
-        if (++cq == nc) { cq = 0; ++tq; }
-      }
-    }
-  } else if (warp == N_EXP + 1) {
-    // =========================== P V issuer (its own thread: never blocks a refill of S) ===========================
-    if (elect_one_sync()) {
-      constexpr uint32_t idesc_o = idesc_bf16_f32(QT, 32) | (1u << 16);       // O: M128 N32, B (V) MN-major
-      int t = 0, c = 0;        // (query tile, chunk) of the next P V
-      for (int g = 0; g < G; ++g) {
-        const uint32_t b = (uint32_t)g & 3u, par = ((uint32_t)g >> 2) & 1u;
-        mbar_wait_sleep(p_full(b), par, 64);
+        cq += NCLS;
+        while (cq >= nc) { cq -= nc; ++tq; }
+      };
+      if (cls < G) issue_qk();
+      int t_seen = -1;
+      uint32_t use = 0;
+      for (int g = cls; g < G; g += NCLS, ++use) {
+        if (g + NCLS < G) {     // the owner has read S(g): refill the tile with step g + NCLS while it computes
+          mbar_wait(s_free(b), use & 1u);
+          fence_after_sync();
+          issue_qk();
+        }
+        mbar_wait(p_full(b), use & 1u);
         const uint32_t ob = (uint32_t)t & 1u;
-        if (c == 0) mbar_wait_sleep(o_free(ob), (((uint32_t)t >> 1) & 1u) ^ 1u, 64);   // O of tile t-2 has been read
+        if (t != t_seen) {      // my first P V of this query tile: the epilogue of tile t-2 has read and zeroed O
+          t_seen = t;
+          mbar_wait(o_free(ob), (((uint32_t)t >> 1) & 1u) ^ 1u);
+        }
         fence_after_sync();
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)     // 16 keys per MMA = 8 TMEM columns of P
-          mma_bf16_ts(tmem + O_COL + ob * 32, tmem + P_COL + b * 32 + kk * 8,
-                      desc_plain(sb + V_OFF + c * 4096 + kk * 1024, 512, 128), idesc_o, (c | kk) ? 1u : 0u);
+        for (int kk = 0; kk < 2; ++kk) {     // 16 keys per MMA = 8 TMEM columns of P; always accumulate
+          mma_bf16_ts(tmem + O_COL + ob * 32, tmem + P_COL + b * 16 + kk * 8,
+                      desc_plain(sb + V_OFF + c * 1024 + kk * 512, 256, 128), idesc_o, 1u);
+          mma_bf16_ts(tmem + O_COL + ob * 32 + 16, tmem + P_COL + b * 16 + kk * 8, ones_desc, idesc_o, 1u);
+        }
         mma_commit(p_free(b));
-        if (c == nc - 1) mma_commit(o_full(ob));
-        if (++c == nc) { c = 0; ++t; }
+        if (c + NCLS >= nc) mma_commit(o_full(ob));      // my last chunk of this tile
+        c += NCLS;
+        while (c >= nc) { c -= nc; ++t; }
       }
     }
   } else {
     // =========================== exponential warps ===========================
     // warp -> TMEM lane quarter q = warp % 4 (the hardware rule: a warp may only touch lanes 32*(warp%4)..+31) and
-    // step class i = warp / 4: the warp owns rows 32q..32q+31 of every step g = i (mod 4); thread = one query row.
+    // step class i = warp / 4: the warp owns rows 32q..32q+31 of every step g = i (mod NCLS); thread = one query row.
     const int q = warp & 3, i = warp >> 2;
     const int row = q * 32 + lane;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
     float* mx = reinterpret_cast<float*>(smem + MX_OFF);   // [tile & 3][row]: exponent reference of the row
-    const uint32_t s_addr = tmem + lane_base + (uint32_t)i * KC, p_addr = tmem + lane_base + P_COL + (uint32_t)i * 32;
+    const uint32_t s_addr = tmem + lane_base + (uint32_t)i * KC, p_addr = tmem + lane_base + P_COL + (uint32_t)i * 16;
     bool bad = false;
     float msc = 0.f;       // reference maximum of my row of the current query tile, times scale * log2(e)
     int t = 0, c = i, t_ref = -1;
     while (c >= nc) { c -= nc; ++t; }
     uint32_t par = 0;
-    for (int g = i; g < G; g += NSB, par ^= 1u) {
-      uint32_t v[64];
-      mbar_wait(s_full((uint32_t)i), par);
+    for (int g = i; g < G; g += NCLS, par ^= 1u) {
+      uint32_t v[32];
+      mbar_wait_park(s_full((uint32_t)i), par, 4000);
       fence_after_sync();
-      tmem_ld64(s_addr, v);
+      tmem_ld32(s_addr, v);
       tmem_ld_wait();
       fence_before_sync();
       __syncwarp();
@@ -271,27 +300,28 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
           __syncwarp();
           if (lane == 0) mbar_arrive(m_full(tb));      // default .release.cta: the stores above are visible to waiters
         } else {
-          mbar_wait(m_full(tb), ((uint32_t)t >> 2) & 1u);
+          mbar_wait_park(m_full(tb), ((uint32_t)t >> 2) & 1u, 4000);
           msc = mx[tb * 128 + row] * scale_log2;
         }
       }
-      mbar_wait(p_free((uint32_t)i), par ^ 1u);
-      fence_after_sync();
+      uint32_t pk[16];
 #pragma unroll
-      for (int hlf = 0; hlf < 2; ++hlf) {
-        uint32_t pk[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float x0 = fmaf(__uint_as_float(v[hlf * 32 + 2 * j]), scale_log2, -msc);
-          const float x1 = fmaf(__uint_as_float(v[hlf * 32 + 2 * j + 1]), scale_log2, -msc);
-          // the odd key of a pair goes to the polynomial when its slot in the 8-key group is 1 (POLYN >= 1), 5 (>= 2),
-          // 3 (>= 3): the two kinds of exponentials alternate evenly in the instruction stream
-          const int slot = (2 * j + 1) & 7;
-          const bool poly1 = (slot == 1 && POLYN >= 1) || (slot == 5 && POLYN >= 2) || (slot == 3 && POLYN >= 3);
-          pk[j] = pack2(ex2f(x0), poly1 ? ex2_poly(x1) : ex2f(x1));
+      for (int j = 0; j < 16; ++j) {
+        const float x0 = fmaf(__uint_as_float(v[2 * j]), scale_log2, -msc);
+        const float x1 = fmaf(__uint_as_float(v[2 * j + 1]), scale_log2, -msc);
+        // the odd key of a pair goes to the polynomial when its slot in the 8-key group is 1 (POLYN >= 1), 5 (>= 2),
+        // 3 (>= 3): the two kinds of exponentials alternate evenly in the instruction stream
+        const int slot = (2 * j + 1) & 7;
+        const bool poly1 = (slot == 1 && POLYN >= 1) || (slot == 5 && POLYN >= 2) || (slot == 3 && POLYN >= 3);
+        if (POLYN == 9) {   // TIMING ABLATION (wrong results): no exponentials at all
+          pk[j] = pack2(fmaf(x0, 0.001f, 1.f), fmaf(x1, 0.001f, 1.f));
+          continue;
         }
-        tmem_st16(p_addr + hlf * 16, pk);
+        pk[j] = pack2(ex2f(x0), poly1 ? ex2_poly(x1) : ex2f(x1));
       }
+      mbar_wait_park(p_free((uint32_t)i), par ^ 1u, 4000);
+      fence_after_sync();
+      tmem_st16(p_addr, pk);
       tmem_st_wait();
       fence_before_sync();
       __syncwarp();
@@ -299,12 +329,20 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
       // ---- epilogue (the owner of a tile's last chunk): O / denominator -> storage row ----
       if (c == nc - 1) {
         const uint32_t ob = (uint32_t)t & 1u;
-        mbar_wait(o_full(ob), ((uint32_t)t >> 1) & 1u);
+        mbar_wait_park(o_full(ob), ((uint32_t)t >> 1) & 1u, 4000);
         fence_after_sync();
         uint32_t o[16], lbits;
         tmem_ld16(tmem + lane_base + O_COL + ob * 32, o);
         asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(lbits) : "r"(tmem + lane_base + O_COL + ob * 32 + 16) : "memory");
         tmem_ld_wait();
+        {     // leave the accumulator zeroed for tile t + 2 (the issuers only accumulate)
+          uint32_t z[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) z[j] = 0u;
+          tmem_st16(tmem + lane_base + O_COL + ob * 32, z);
+          tmem_st16(tmem + lane_base + O_COL + ob * 32 + 16, z);
+          tmem_st_wait();
+        }
         fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(o_free(ob));
@@ -323,7 +361,7 @@ __global__ void __launch_bounds__(tm::THREADS, 1) attn_window_tm_kernel(
           dst[1] = make_uint4(ok[4], ok[5], ok[6], ok[7]);
         }
       }
-      c += NSB;
+      c += NCLS;
       while (c >= nc) { c -= nc; ++t; }
     }
     if (__any_sync(0xffffffffu, bad) && lane == 0) redo[blockIdx.x] = 1;
@@ -352,6 +390,8 @@ int attn_window_tm(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
         cudaFuncSetAttribute(attn_window_tm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tm::SMEM_BYTES) !=
             cudaSuccess ||
         cudaFuncSetAttribute(attn_window_tm_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, tm::SMEM_BYTES) !=
+            cudaSuccess ||
+        cudaFuncSetAttribute(attn_window_tm_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, tm::SMEM_BYTES) !=
             cudaSuccess)
       return PTV3_ELAUNCH;
     configured[dev] = true;
@@ -362,6 +402,7 @@ int attn_window_tm(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
     case 1: attn_window_tm_kernel<1><<<grid, tm::THREADS, tm::SMEM_BYTES, st>>>(qkv, order, windows, n_windows, h, sl2, out, redo); break;
     case 2: attn_window_tm_kernel<2><<<grid, tm::THREADS, tm::SMEM_BYTES, st>>>(qkv, order, windows, n_windows, h, sl2, out, redo); break;
     case 3: attn_window_tm_kernel<3><<<grid, tm::THREADS, tm::SMEM_BYTES, st>>>(qkv, order, windows, n_windows, h, sl2, out, redo); break;
+    case 9: attn_window_tm_kernel<9><<<grid, tm::THREADS, tm::SMEM_BYTES, st>>>(qkv, order, windows, n_windows, h, sl2, out, redo); break;
     default: attn_window_tm_kernel<0><<<grid, tm::THREADS, tm::SMEM_BYTES, st>>>(qkv, order, windows, n_windows, h, sl2, out, redo); break;
   }
   return check_launch();

@@ -47,6 +47,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// try_wait with a suspend-time hint (ns): the warp stays parked in hardware instead of re-polling every few dozen
+// clocks.  With two dozen waiting warps per CTA the plain poll loop issued 0.3 SYNCS / clk / SM and slowed every
+// arrive / commit the issuers depend on (profiles/r02_attention.md).
+__device__ __forceinline__ void mbar_wait_park(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity), "r"(hint_ns)
+        : "memory");
+  } while (!ok);
+}
 // long waits off the critical path (an epilogue waiting for a whole tile): back off between polls so the spinning
 // warp does not take issue slots from the MMA / gather warps on its scheduler
 __device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, unsigned ns) {

@@ -61,7 +61,7 @@ def main():
     except Exception as e:  # noqa: BLE001
         fa2 = None
         print("flash_attn unavailable:", e)
-    names = ["algo 2 (r01)"] + [f"algo 5 (tcgen05), poly {pn}/8" for pn in range(4)] + [(f"v{v}: {'pp' if v // 100 == 2 else 'rr'}, poly {(v // 10) % 10 - 1}/8, {['', '2 tiles/warp 64-key 2 CTAs', '2 tiles/warp 32-key 3 CTAs', '1 tile/warp 64-key 3 CTAs', '1 tile/warp 64-key 4 CTAs'][v % 10]}" if v < 1000 else
+    names = ["algo 2 (r01)"] + [f"algo 5 (tcgen05), poly {pn}/8" for pn in range(3)] + ["algo 5 ABLATION no exp"] + [(f"v{v}: {'pp' if v // 100 == 2 else 'rr'}, poly {(v // 10) % 10 - 1}/8, {['', '2 tiles/warp 64-key 2 CTAs', '2 tiles/warp 32-key 3 CTAs', '1 tile/warp 64-key 3 CTAs', '1 tile/warp 64-key 4 CTAs'][v % 10]}" if v < 1000 else
               "ABLATION without " + "+".join(n for b, n in ((1, "exp"), (2, "PV MMAs"), (4, "QK MMAs"), (8, "max")) if (v - 1000) & b))
              for v in variants] + \
             ["FA2 2.8 (pre-gathered)"]
@@ -77,7 +77,7 @@ def main():
         w, nw = ops.build_windows(offset, 1024, n)
         scores = float((w[: int(nw)][:, 1] * w[: int(nw)][:, 3]).sum()) * H
         ts = [timed(lambda: ops.attn_window(qkv, order, w, nw, H, 1024, algo=2))]
-        for pn in range(4):
+        for pn in (0, 1, 2, 9):
             ops.debug_set(9, pn)
             ts.append(timed(lambda: ops.attn_window(qkv, order, w, nw, H, 1024, algo=5)))
         ops.debug_set(9, 0)
@@ -101,7 +101,7 @@ def main():
         ts.append(tfa)
         tot = [a + b for a, b in zip(tot, ts)]
         if ref is not None:
-            for pn in (3, 2, 1, 0):
+            for pn in (9, 2, 1, 0):
                 ops.debug_set(9, pn)
                 got = ops.attn_window(qkv, order, w, nw, H, 1024, algo=5).float()
                 errs.insert(0, f"{((got - ref).norm() / ref.norm()).item():.1e}")

@@ -174,6 +174,55 @@ __global__ void mix(float* out, long long* cyc, float seed) {
   if (threadIdx.x == 0) cyc[blockIdx.x] = t1 - t0;
 }
 
+// tcgen05.mma issue rate for small tiles: one thread issues `reps` MMAs M128 x N x K16 (bf16, fp32 accumulate in TMEM) back
+// to back into the same accumulator, A from shared memory (SS) or from tensor memory (TS), then commits and waits.
+// Operands are whatever the shared / tensor memory holds (timing only).
+template <int N, bool TS>
+__global__ void tc_mma(long long* cyc, int reps) {
+  extern __shared__ __align__(1024) unsigned char sm[];
+  __shared__ uint32_t slot;
+  __shared__ __align__(8) unsigned long long bar;
+  const int warp = threadIdx.x >> 5;
+  const uint32_t sb = (uint32_t)__cvta_generic_to_shared(sm);
+  const uint32_t barp = (uint32_t)__cvta_generic_to_shared(&bar);
+  for (int i = threadIdx.x; i < 16384 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(sm)[i] = 0x3c003c00u;
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(barp));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"((uint32_t)__cvta_generic_to_shared(&slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = slot;
+  if (threadIdx.x == 0) {
+    // K-major no-swizzle descriptors (8-row core matrices, the two K halves 128 B apart, row groups 256 B apart)
+    const uint64_t adesc = (uint64_t)((sb >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
+    const uint64_t bdesc = (uint64_t)(((sb + 8192) >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    long long t0 = clock64();
+    for (int i = 0; i < reps; ++i) {
+      if (TS)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem), "r"(tmem + 256), "l"(bdesc), "r"(idesc), "r"(1u) : "memory");
+      else
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(1u) : "memory");
+    }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(barp) : "memory");
+    uint32_t ok = 0;
+    while (!ok)
+      asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(barp), "r"(0u) : "memory");
+    long long t1 = clock64();
+    cyc[blockIdx.x] = t1 - t0;
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+}
+
 static double mean_cycles(long long* d_cyc, int n) {
   static long long h[256];
   cudaMemcpy(h, d_cyc, n * sizeof(long long), cudaMemcpyDeviceToHost);
@@ -220,6 +269,16 @@ int main() {
   MIX(16, 8, 8, 0, "16 ex2 + 8 cvt + 8 max3")
   MIX(16, 8, 8, 10, "16 ex2 + 8 cvt + 8 max3 + 10 hmma (softmax mix)")
   MIX(16, 8, 8, 6, "16 ex2 + 8 cvt + 8 max3 + 6 hmma")
+#define TCMMA(N, TS)                                                                                             \
+  {                                                                                                              \
+    cudaFuncSetAttribute(tc_mma<N, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768);                     \
+    for (int rep = 0; rep < 2; ++rep) tc_mma<N, TS><<<G, 128, 32768>>>(cyc, 2000);                               \
+    CHECK(cudaDeviceSynchronize());                                                                              \
+    printf("tcgen05.mma M128 N%-3d K16 %s: %6.1f clk per MMA (ideal %5.1f at 8192 FLOP/clk/SM)\n", N,            \
+           TS ? "A in TMEM" : "A in smem", mean_cycles(cyc, G) / 2000.0, 128.0 * N * 16 * 2 / 8192.0);            \
+  }
+  TCMMA(16, false) TCMMA(32, false) TCMMA(64, false) TCMMA(128, false) TCMMA(256, false)
+  TCMMA(16, true) TCMMA(32, true) TCMMA(64, true) TCMMA(128, true)
   for (int threads : {128, 256, 512}) {
     for (int rep = 0; rep < 2; ++rep) ldtm<<<G, threads>>>((uint32_t*)out, cyc);
     CHECK(cudaDeviceSynchronize());
