@@ -356,17 +356,23 @@ def run_ours(args):
         cpu = cpu_baseline(args, seconds=20.0)
 
     if rank == 0:
+        seg = args.head == "segmentor"
+        head_name = "20-class segmentor head (DefaultSegmentorV2)" if seg else "offset-keypoint head"
+        result_name = ("per-voxel class ids (uint8 argmax of the logits, taken on the device)" if seg
+                       else "per-scene keypoints (scenes,6,3) fp32 after on-device aggregation")
         line = dict(metric=METRIC, value=round(value, 1), unit=UNIT, n_gpus=world, steps=args.steps,
                     warmup=max(args.warmup, 3), ms_per_step=round(ms / args.steps, 3), higher_is_better=True,
-                    scaling="weak", vs_baseline=None, dtype=args.dtype, data="synthetic",
-                    config=dict(workload=f"PTv3-v1m1 + offset-keypoint head forward, {args.scenes} scenes x "
-                                         f"{args.points} raw pts (scale {args.scale}, grid {GRID} m) per GPU",
-                                voxels_per_gpu=n_vox, scenes_per_gpu=args.scenes, raw_points_per_scene=args.points,
+                    scaling=args.scaling, vs_baseline=None, dtype=args.dtype, data="synthetic",
+                    config=dict(workload=f"PTv3-v1m1 + {head_name} forward, {args.scenes} scenes x "
+                                         f"{args.points} raw pts (scale {args.scale}, grid {GRID} m) "
+                                         f"{'in total, split over the ranks' if args.scaling == 'strong' else 'per GPU'}"
+                                         f" ({args.workload_name})",
+                                voxels_per_gpu=n_vox, scenes_per_gpu=len(ids), raw_points_per_scene=args.points,
                                 patch=1024, parallelism=f"scene-sharded x{world} (no collective in forward)",
                                 l2="per-step working set (qkv 224 MB at stage 0) exceeds the 126 MB L2"),
                     e2e=dict(value=round(e2e, 1), unit=UNIT, h2d_bytes_per_step=h2d_bytes,
                              d2h_bytes_per_step=d2h_bytes, ms_per_step=round(e2e_wall / args.steps, 3),
-                             result="per-scene keypoints (scenes,6,3) fp32 after on-device aggregation"),
+                             result=result_name),
                     gpu_launches=int(launches), clocks=clocks, roofline=roof, cpu_baseline=cpu, op_ms=ops_ms,
                     gridsample=gs_leg)
         print(json.dumps(line))
