@@ -114,6 +114,21 @@ int ptv3_gridsample_batch(const float* coord, int64_t r, const int64_t* offset, 
                           int64_t* voxel_offset, int64_t* n_voxels, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/* PT-v3m2 GridPooling integer front end (replaces point_transformer_v3m2_sonata.py:393-417: torch.unique(dim=0) over
+ * rows [x/stride | batch << 48, y/stride, z/stride], torch.sort(cluster), cumsum(counts)).  grid_coord (n,3) int32 or
+ * int64, non-negative; batch (n) int64; `bits` = bits per axis that hold every grid_coord / stride (the parent's
+ * serialization depth), `scene_bits` = bits that hold every batch id; 3*bits + scene_bits <= 63.  Outputs: cluster (n)
+ * = pooling_inverse, ids in ascending (batch, x, y, z) order like torch.unique; indices (n) = rows sorted by cluster
+ * (stable); idx_ptr (n+1 allocated, n_pooled+1 valid) CSR pointer; pooled_grid (n,3) / pooled_batch (n) / indices4
+ * (n,4) int32 [b,x,y,z] (first n_pooled rows valid); meta (4) int64 = {n_pooled, max x, max y, max z of the pooled grid}
+ * (the one host read of the level: row count + next serialization depth, structure.py:73).  A coordinate outside
+ * [0, 2^bits * stride) sets bit 4 of ptv3_device_error(). */
+size_t ptv3_grid_pool_workspace(int64_t n);
+int ptv3_grid_pool(const void* grid_coord, int grid_is_i64, const int64_t* batch, int64_t n, int stride, int bits,
+                   int scene_bits, int64_t* cluster, int64_t* indices, int64_t* idx_ptr, int64_t* pooled_grid,
+                   int64_t* pooled_batch, int32_t* indices4, int64_t* meta, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
 /* ---------------------------------------------------------------------------
  * A6  SerializedPooling integer front end.
  * Replaces point_transformer_v3m1_base.py:385-412: code >> 3*pool_depth,
@@ -160,7 +175,9 @@ int ptv3_segment_csr(const void* src, int dtype, const int64_t* gather /* NULL o
 
 /* A7  SerializedUnpooling gather-add (:471-482) with the two GELUs fused:
  * skip_act[i] = act(skip[i]); out[i] = skip_act[i] + act(up[inverse[i]]); act = GELU(erf) if gelu else identity.
- * skip (n,c), up (m,c), skip_act (n,c) or NULL in `dtype`; out (n,c) is always fp32 (the residual stream). */
+ * skip (n,c), up (m,c), skip_act (n,c) or NULL in `dtype`; out (n,c) is always fp32 (the residual stream).
+ * `gelu` bit 0: apply GELU to both operands; bit 1: the second output holds the SUM in `dtype` instead of act(skip)
+ * (PT-v3m2 GridUnpooling, point_transformer_v3m2_sonata.py:498-499, refreshes the sparse tensor with the sum). */
 int ptv3_unpool_add(const void* skip, const void* up, int dtype, const int64_t* inverse, int64_t n, int64_t c, int gelu,
                     void* out, void* skip_act, void* stream);
 

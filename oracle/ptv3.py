@@ -89,9 +89,14 @@ def _block(pt, W, p, H, K, order_index, nbr, enable_flash=True):
     if not enable_flash:      # dense branch :173-176: one patch size for the whole batch
         K = min(int(torch.diff(pt.offset, prepend=pt.offset.new_zeros(1)).min()), K)
     y = O.window_attention(qkv, pt.order[order_index], pt.inverse[order_index], pt.offset.numpy(), H, K)
-    x = x + _lin(y, W, p + ".attn.proj")
+    y = _lin(y, W, p + ".attn.proj")
+    if p + ".ls1.0.gamma" in W:      # PT-v3m2 LayerScale (point_transformer_v3m2_sonata.py:27-39, :349)
+        y = y * W[p + ".ls1.0.gamma"]
+    x = x + y
     y = _ln(x, W, p + ".norm2.0")
     y = _lin(F.gelu(_lin(y, W, p + ".mlp.0.fc1")), W, p + ".mlp.0.fc2")
+    if p + ".ls2.0.gamma" in W:
+        y = y * W[p + ".ls2.0.gamma"]
     pt.feat = x + y
     return pt
 

@@ -37,6 +37,9 @@ SIGNATURES = {
     "ptv3_gridsample_batch_workspace": (c_sz, [c_i64, c_i64]),
     "ptv3_gridsample_batch": (c_int, [c_vp, c_i64, c_vp, c_i64, c_f64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                       c_vp, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "ptv3_grid_pool_workspace": (c_sz, [c_i64]),
+    "ptv3_grid_pool": (c_int, [c_vp, c_int, c_vp, c_i64, c_int, c_int, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                               c_vp, c_sz, c_vp]),
     "ptv3_pool_front_workspace": (c_sz, [c_i64, c_i64]),
     "ptv3_pool_front": (c_int, [c_vp, c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                 c_vp, c_sz, c_vp]),

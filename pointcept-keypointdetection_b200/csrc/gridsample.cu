@@ -256,6 +256,62 @@ __global__ void gsb_voxel_offset_kernel(const int64_t* __restrict__ offset, int 
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// PT-v3m2 GridPooling front end (point_transformer_v3m2_sonata.py:393-417).  The reference runs
+// torch.unique(dim=0) over rows [x/stride | batch << 48, y/stride, z/stride]: clusters come out in ascending
+// (batch, x, y, z) order.  Here one 64-bit key (batch, x, y, z) with `bits` bits per axis is radix-sorted (stable) and
+// run-length encoded; the pooled grid / batch / spconv indices are decoded from the run heads and the per-axis maximum
+// of the pooled grid (the next serialization depth, structure.py:73) is reduced in the same pass.
+// ---------------------------------------------------------------------------------------------------------------
+template <typename TG>
+__global__ void __launch_bounds__(256) gp_key_kernel(const TG* __restrict__ grid, const int64_t* __restrict__ batch,
+                                                     int64_t n, int stride, int bits, uint64_t* __restrict__ key,
+                                                     long long* __restrict__ meta, int* __restrict__ err) {
+  if (blockIdx.x == 0 && threadIdx.x < 4) meta[threadIdx.x] = threadIdx.x == 0 ? 0 : -1;
+  const uint64_t lim = 1ull << bits;
+  bool bad = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const long long gx = (long long)grid[3 * i], gy = (long long)grid[3 * i + 1], gz = (long long)grid[3 * i + 2];
+    const uint64_t x = (uint64_t)(gx / stride), y = (uint64_t)(gy / stride), z = (uint64_t)(gz / stride);
+    bad |= gx < 0 || gy < 0 || gz < 0 || x >= lim || y >= lim || z >= lim;
+    key[i] = ((((uint64_t)batch[i] << bits | x) << bits | y) << bits) | z;
+  }
+  if (bad) atomicOr(err, 4);
+}
+
+__global__ void __launch_bounds__(256) gp_heads_kernel(const uint64_t* __restrict__ skey,
+                                                       const int64_t* __restrict__ seg_start,
+                                                       const int64_t* __restrict__ n_pooled, int bits,
+                                                       int64_t* __restrict__ grid, int64_t* __restrict__ batch,
+                                                       int32_t* __restrict__ indices4, long long* __restrict__ meta) {
+  const int64_t m = n_pooled[0];
+  const uint64_t msk = (1ull << bits) - 1ull;
+  long long mx[3] = {-1, -1, -1};
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < m; v += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t k = skey[seg_start[v]];
+    const long long z = (long long)(k & msk), y = (long long)((k >> bits) & msk), x = (long long)((k >> (2 * bits)) & msk);
+    const long long b = (long long)(k >> (3 * bits));
+    grid[3 * v] = x;
+    grid[3 * v + 1] = y;
+    grid[3 * v + 2] = z;
+    batch[v] = b;
+    *reinterpret_cast<int4*>(indices4 + 4 * v) = make_int4((int)b, (int)x, (int)y, (int)z);
+    mx[0] = x > mx[0] ? x : mx[0];
+    mx[1] = y > mx[1] ? y : mx[1];
+    mx[2] = z > mx[2] ? z : mx[2];
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      long long o = __shfl_xor_sync(0xffffffffu, mx[a], d);
+      mx[a] = o > mx[a] ? o : mx[a];
+    }
+    if ((threadIdx.x & 31) == 0 && mx[a] >= 0) atomicMax(&meta[1 + a], mx[a]);
+  }
+}
+
 }  // namespace ptv3
 
 using namespace ptv3;
@@ -374,6 +430,55 @@ int ptv3_gridsample_batch(const float* coord, int64_t r, const int64_t* offset, 
   gs_select_kernel<<<g, 256, 0, st>>>(idx_sort, seg_start, n_voxels, rnd, count, idx_unique);
   gsb_voxel_offset_kernel<<<1, 256, 0, st>>>(offset, b, ex, total, r, voxel_offset);
   return check_launch(3);
+}
+
+size_t ptv3_grid_pool_workspace(int64_t n) {
+  int64_t rr = n > 0 ? n : 1;
+  return radix_argsort_workspace(1, rr) + 2 * align_up((size_t)rr * 8) /* keys, sorted keys */ +
+         2 * align_up((size_t)rr * 4) /* flags, ex */ + align_up(scan_workspace_elems(1, rr) * 4) + 1024;
+}
+
+int ptv3_grid_pool(const void* grid_coord, int grid_is_i64, const int64_t* batch, int64_t n, int stride, int bits,
+                   int scene_bits, int64_t* cluster, int64_t* indices, int64_t* idx_ptr, int64_t* pooled_grid,
+                   int64_t* pooled_batch, int32_t* indices4, int64_t* meta, void* workspace, size_t workspace_bytes,
+                   void* stream) {
+  if (n < 0 || stride < 1 || bits < 1 || scene_bits < 0 || 3 * bits + scene_bits > 63 || !meta) return PTV3_EINVAL;
+  cudaStream_t st = as_stream(stream);
+  if (n == 0) {
+    cudaMemsetAsync(meta, 0, 8, st);
+    cudaMemsetAsync(meta + 1, 0xff, 24, st);
+    return PTV3_OK;
+  }
+  if (!grid_coord || !batch || !cluster || !indices || !idx_ptr || !pooled_grid || !pooled_batch || !indices4)
+    return PTV3_EINVAL;
+  Workspace ws(workspace, workspace_bytes);
+  size_t rs_bytes = radix_argsort_workspace(1, n);
+  char* rs_ws = ws.take<char>(rs_bytes);
+  uint64_t* key = ws.take<uint64_t>((size_t)n);
+  uint64_t* skey = ws.take<uint64_t>((size_t)n);
+  uint32_t* flags = ws.take<uint32_t>((size_t)n);
+  uint32_t* ex = ws.take<uint32_t>((size_t)n);
+  uint32_t* partials = ws.take<uint32_t>(scan_workspace_elems(1, n));
+  uint32_t* total = ws.take<uint32_t>(1);
+  if (!ws.ok()) return PTV3_EWORKSPACE;
+  const int g = grid_for(n, 256);
+  long long* m = reinterpret_cast<long long*>(meta);
+  if (grid_is_i64)
+    gp_key_kernel<int64_t><<<g, 256, 0, st>>>((const int64_t*)grid_coord, batch, n, stride, bits, key, m,
+                                              device_error_flag());
+  else
+    gp_key_kernel<int32_t><<<g, 256, 0, st>>>((const int32_t*)grid_coord, batch, n, stride, bits, key, m,
+                                              device_error_flag());
+  g_launch_count += 1;
+  int rc = radix_argsort_rows(key, 1, n, 3 * bits + scene_bits, indices, nullptr, skey, rs_ws, rs_bytes, st);
+  if (rc != PTV3_OK) return rc;
+  gs_flags_kernel<<<g, 256, 0, st>>>(skey, n, flags);
+  g_launch_count += 1;
+  rc = exclusive_scan_u32(flags, ex, 1, n, partials, total, st);
+  if (rc != PTV3_OK) return rc;
+  gs_segments_kernel<<<g, 256, 0, st>>>(indices, flags, ex, total, n, cluster, idx_ptr, meta);
+  gp_heads_kernel<<<g, 256, 0, st>>>(skey, idx_ptr, meta, bits, pooled_grid, pooled_batch, indices4, m);
+  return check_launch(2);
 }
 
 }  // extern "C"

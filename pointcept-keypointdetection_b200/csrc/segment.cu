@@ -137,7 +137,8 @@ __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + er
 template <typename T, bool GELU>
 __global__ void __launch_bounds__(256) unpool_add_kernel(const T* __restrict__ skip, const T* __restrict__ up,
                                                          const int64_t* __restrict__ inverse, int64_t n, int c4,
-                                                         float* __restrict__ out, T* __restrict__ skip_act) {
+                                                         float* __restrict__ out, T* __restrict__ skip_act,
+                                                         bool second_is_sum) {
   int64_t total = n * c4;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
     int64_t i = t / c4;
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(256) unpool_add_kernel(const T* __restrict__ s
       o[q] = a[q] + b[q];
     }
     store4<float>(out + t * 4, o);
-    if (skip_act) store4<T>(skip_act + t * 4, a);
+    if (skip_act) store4<T>(skip_act + t * 4, second_is_sum ? o : a);
   }
 }
 
@@ -410,22 +411,24 @@ int ptv3_unpool_add(const void* skip, const void* up, int dtype, const int64_t* 
   int c4 = (int)(c / 4);
   int g = grid_for(n * c4, 256);
   cudaStream_t st = as_stream(stream);
+  const bool sum2 = (gelu & 2) != 0;     // bit 1: the second output holds the sum (PT-v3m2) instead of act(skip) (PT-v3m1)
+  gelu &= 1;
   if (dtype == PTV3_F32) {
     if (gelu)
       unpool_add_kernel<float, true><<<g, 256, 0, st>>>((const float*)skip, (const float*)up, inverse, n, c4,
-                                                        (float*)out, (float*)skip_act);
+                                                        (float*)out, (float*)skip_act, sum2);
     else
       unpool_add_kernel<float, false><<<g, 256, 0, st>>>((const float*)skip, (const float*)up, inverse, n, c4,
-                                                         (float*)out, (float*)skip_act);
+                                                         (float*)out, (float*)skip_act, sum2);
   } else if (dtype == PTV3_BF16) {
     if (gelu)
       unpool_add_kernel<__nv_bfloat16, true><<<g, 256, 0, st>>>((const __nv_bfloat16*)skip, (const __nv_bfloat16*)up,
                                                                 inverse, n, c4, (float*)out,
-                                                                (__nv_bfloat16*)skip_act);
+                                                                (__nv_bfloat16*)skip_act, sum2);
     else
       unpool_add_kernel<__nv_bfloat16, false><<<g, 256, 0, st>>>((const __nv_bfloat16*)skip, (const __nv_bfloat16*)up,
                                                                  inverse, n, c4, (float*)out,
-                                                                 (__nv_bfloat16*)skip_act);
+                                                                 (__nv_bfloat16*)skip_act, sum2);
   } else {
     return PTV3_EINVAL;
   }

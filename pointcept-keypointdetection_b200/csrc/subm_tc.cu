@@ -29,8 +29,8 @@ static inline int n_kblocks(int c_in, int k3) { return (k3 * c_in + KBLK - 1) / 
 static inline int pick_nt(int c_out) { return c_out >= 256 ? 256 : c_out; }
 
 bool subm_conv_tc_supported(int c_in, int c_out, int k3) {
-  bool cin_ok = c_in == 32 || (c_in % 64 == 0 && c_in >= 64 && c_in <= 512);
-  bool cout_ok = c_out == 32 || c_out == 64 || c_out == 128 || c_out == 256 || c_out == 512;
+  bool cin_ok = c_in == 32 || (c_in % 64 == 0 && c_in >= 64 && c_in <= 1024);      // PTv3-large: 768
+  bool cout_ok = c_out == 32 || c_out == 64 || c_out == 128 || (c_out % 256 == 0 && c_out >= 256 && c_out <= 1024);
   return cin_ok && cout_ok && k3 >= 1 && k3 <= MAX_K3;
 }
 

@@ -1,0 +1,79 @@
+"""Criteria of the segmentation configs that train on this path (configs/concerto/semseg-ptv3-large-v1m1-waymo-6a-lin.py
+:38-41, configs/scannet/semseg-pt-v3m1-0-base.py): CrossEntropyLoss + LovaszLoss(mode="multiclass"), summed by
+`Criteria` (pointcept/models/losses/builder.py:13-30).  Plain torch on whatever device the logits live on; the
+Lovasz-Softmax surrogate (pointcept/models/losses/lovasz.py:20-32, :119-166: Berman et al., Alg. 1) is evaluated for
+all present classes at once -- ONE (C, P) sort instead of a Python loop of C sorts -- which matters at ~1 M points x 22
+classes per step.  Pinned on the reference's LovaszLoss value and gradient (tests/golden/sonata.npz).
+"""
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+def lovasz_softmax(logits, labels, ignore_index=None):
+    """LovaszLoss(mode="multiclass", per_image=False, class_seen=None): mean over the classes PRESENT in `labels` of
+    dot(sorted |fg - p_c|, lovasz_grad(sorted fg))."""
+    probas = logits.float().softmax(dim=1)
+    labels = labels.view(-1)
+    if ignore_index is not None:
+        valid = labels != ignore_index
+        probas, labels = probas[valid], labels[valid]
+    if probas.numel() == 0:
+        return probas.sum() * 0.0
+    c = probas.shape[1]
+    fg = F.one_hot(labels, c).to(probas.dtype).t()                    # (C, P)
+    present = fg.sum(1) > 0
+    errors = (fg - probas.t()).abs()
+    errors_sorted, perm = torch.sort(errors, dim=1, descending=True)
+    fg_sorted = torch.gather(fg, 1, perm)
+    gts = fg_sorted.sum(1, keepdim=True)
+    inter = gts - fg_sorted.cumsum(1)
+    union = gts + (1.0 - fg_sorted).cumsum(1)
+    jac = 1.0 - inter / union
+    jac = torch.cat([jac[:, :1], jac[:, 1:] - jac[:, :-1]], dim=1)
+    per_class = (errors_sorted * jac).sum(1)
+    return per_class[present].mean()
+
+
+class LovaszLoss(nn.Module):
+    def __init__(self, mode="multiclass", class_seen=None, per_image=False, ignore_index=None, loss_weight=1.0):
+        super().__init__()
+        if mode != "multiclass" or per_image or class_seen is not None:
+            raise NotImplementedError("only the multiclass / whole-batch form is used by the target configs")
+        self.ignore_index, self.loss_weight = ignore_index, loss_weight
+
+    def forward(self, y_pred, y_true):
+        return lovasz_softmax(y_pred, y_true, self.ignore_index) * self.loss_weight
+
+
+class CrossEntropyLoss(nn.Module):
+    """pointcept/models/losses/misc.py CrossEntropyLoss(loss_weight, ignore_index) over (P, C) logits."""
+
+    def __init__(self, weight=None, size_average=None, reduce=None, reduction="mean", label_smoothing=0.0,
+                 loss_weight=1.0, ignore_index=-1):
+        super().__init__()
+        self.loss_weight = loss_weight
+        self.loss = nn.CrossEntropyLoss(weight=torch.as_tensor(weight) if weight is not None else None,
+                                        ignore_index=ignore_index, reduction=reduction, label_smoothing=label_smoothing)
+
+    def forward(self, pred, target):
+        return self.loss(pred.float(), target) * self.loss_weight
+
+
+class Criteria:
+    """losses/builder.py:13-30: a list of loss configs (dicts with `type`) summed; empty -> returns the prediction."""
+
+    def __init__(self, cfg=None):
+        kinds = dict(CrossEntropyLoss=CrossEntropyLoss, LovaszLoss=LovaszLoss)
+        self.criteria = []
+        for c in cfg or []:
+            c = dict(c)
+            self.criteria.append(kinds[c.pop("type")](**c))
+
+    def __call__(self, pred, target):
+        if not self.criteria:
+            return pred
+        loss = 0
+        for c in self.criteria:
+            loss = loss + c(pred, target)
+        return loss

@@ -287,6 +287,19 @@ class MLP(nn.Module):
         return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
 
 
+class LayerScale(nn.Module):
+    """point_transformer_v3m2_sonata.py:27-39: per-channel scale of a residual branch.  In the inference path it never
+    runs as a kernel: gamma is folded into the weights of the Linear that ends the branch (attn.proj / mlp.fc2)."""
+
+    def __init__(self, dim, init_values=1e-5, inplace=False):
+        super().__init__()
+        self.inplace = inplace
+        self.gamma = nn.Parameter(init_values * torch.ones(dim))
+
+    def forward(self, x):
+        return x.mul_(self.gamma) if self.inplace else x * self.gamma
+
+
 class Block(PointModule):
     """:251-338.  xCPE (SubMConv3d -> Linear -> LN) + attention + MLP with pre-norm; three fused
     residual/LayerNorm kernels replace the six elementwise passes of the reference."""
@@ -294,11 +307,14 @@ class Block(PointModule):
     def __init__(self, channels, num_heads, patch_size=48, mlp_ratio=4.0, qkv_bias=True, qk_scale=None, attn_drop=0.0,
                  proj_drop=0.0, drop_path=0.0, norm_layer=nn.LayerNorm, act_layer=nn.GELU, pre_norm=True,
                  order_index=0, cpe_indice_key=None, enable_rpe=False, enable_flash=True, upcast_attention=True,
-                 upcast_softmax=True):
+                 upcast_softmax=True, layer_scale=None):
         super().__init__()
         if not pre_norm:
             raise NotImplementedError("pre_norm=False is not used by any target config")
         self.channels, self.pre_norm = channels, pre_norm
+        if layer_scale is not None:      # PT-v3m2 (point_transformer_v3m2_sonata.py:304-308, :325-329): state_dict ls1.0.gamma
+            self.ls1 = PointSequential(LayerScale(channels, init_values=layer_scale))
+            self.ls2 = PointSequential(LayerScale(channels, init_values=layer_scale))
         self.cpe = PointSequential(
             SubMConv3d(channels, channels, kernel_size=3, bias=True, indice_key=cpe_indice_key),
             nn.Linear(channels, channels), norm_layer(channels))
@@ -316,9 +332,18 @@ class Block(PointModule):
         self.compute_dtype = torch.bfloat16
         self.conv_algo = 0
 
-    def _lin(self, lin, dtype):
-        return _cached(self, (id(lin), dtype), [lin.weight, lin.bias],
-                       lambda: (lin.weight.to(dtype), lin.bias.to(dtype) if lin.bias is not None else None))
+    def _lin(self, lin, dtype, ls=None):
+        """Weights of a Linear in the compute dtype; `ls` (a LayerScale gamma) is folded in: gamma * (W x + b)."""
+        if ls is None:
+            return _cached(self, (id(lin), dtype), [lin.weight, lin.bias],
+                           lambda: (lin.weight.to(dtype), lin.bias.to(dtype) if lin.bias is not None else None))
+        return _cached(self, (id(lin), dtype, "ls"), [lin.weight, lin.bias, ls],
+                       lambda: ((lin.weight.float() * ls.float()[:, None]).to(dtype).contiguous(),
+                                (lin.bias.float() * ls.float()).to(dtype) if lin.bias is not None else None))
+
+    def _gammas(self):
+        ls1, ls2 = self._modules.get("ls1"), self._modules.get("ls2")
+        return (ls1[0].gamma if ls1 is not None else None), (ls2[0].gamma if ls2 is not None else None)
 
     @staticmethod
     def _ln(ln):
@@ -333,27 +358,29 @@ class Block(PointModule):
         cd = torch.bfloat16
         lins = [self.cpe[1], attn.qkv, attn.proj, mlp.fc1, mlp.fc2]
         lns = [self.cpe[2], self.norm1[0], self.norm2[0]]
+        g1, g2 = self._gammas()
         params = [conv.weight, conv.bias] + [q for l in lins for q in (l.weight, l.bias)] + \
-                 [q for l in lns for q in (l.weight, l.bias)]
+                 [q for l in lns for q in (l.weight, l.bias)] + [g1, g2]
 
         def build():
             fused = ops.mlp_fused_supported(c, hidden) and mlp.fc2.out_features == c
             dev = conv.weight.device
             zeros = lambda n, dt: torch.zeros(n, dtype=dt, device=dev)
-            lw = lambda l: l.weight.to(cd).contiguous()
-            lb = lambda l: l.bias.to(cd).contiguous() if l.bias is not None else zeros(l.out_features, cd)
+            sc = lambda t, g: t.float() if g is None else t.float() * (g.float()[:, None] if t.dim() == 2 else g.float())
+            lw = lambda l, g=None: sc(l.weight, g).to(cd).contiguous()
+            lb = lambda l, g=None: sc(l.bias, g).to(cd).contiguous() if l.bias is not None else zeros(l.out_features, cd)
             w, b = conv._weights(cd)
             t = dict(conv_w_packed=ops.subm_pack_weight(w), conv_bias=b if b is not None else zeros(c, torch.float32),
                      cpe_lin_w=lw(self.cpe[1]), cpe_lin_b=lb(self.cpe[1]),
                      cpe_ln_g=self.cpe[2].weight.float().contiguous(), cpe_ln_b=self.cpe[2].bias.float().contiguous(),
                      norm1_g=self.norm1[0].weight.float().contiguous(), norm1_b=self.norm1[0].bias.float().contiguous(),
                      norm2_g=self.norm2[0].weight.float().contiguous(), norm2_b=self.norm2[0].bias.float().contiguous(),
-                     qkv_w=lw(attn.qkv), qkv_b=lb(attn.qkv), proj_w=lw(attn.proj), proj_b=lb(attn.proj))
+                     qkv_w=lw(attn.qkv), qkv_b=lb(attn.qkv), proj_w=lw(attn.proj, g1), proj_b=lb(attn.proj, g1))
             if fused:
                 t.update(fc1_w=ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), fc1_b=mlp.fc1.bias.float().contiguous(),
-                         fc2_w=ops.pack_kmajor(mlp.fc2.weight.to(cd), c), fc2_b=mlp.fc2.bias.float().contiguous())
+                         fc2_w=ops.pack_kmajor(lw(mlp.fc2, g2), c), fc2_b=sc(mlp.fc2.bias, g2).contiguous())
             else:
-                t.update(fc1_w=lw(mlp.fc1), fc1_b=lb(mlp.fc1), fc2_w=lw(mlp.fc2), fc2_b=lb(mlp.fc2))
+                t.update(fc1_w=lw(mlp.fc1), fc1_b=lb(mlp.fc1), fc2_w=lw(mlp.fc2, g2), fc2_b=lb(mlp.fc2, g2))
             return ops.block_params(c=c, heads=attn.num_heads, hidden=hidden, k3=conv.kernel_size ** 3,
                                     patch=attn.patch_size, mlp_fused=int(fused), attn_algo=attn.algo,
                                     scale=float(attn.scale), eps_cpe=float(self.cpe[2].eps),
@@ -407,7 +434,8 @@ class Block(PointModule):
         # attention
         qkv = F.linear(h, *self.attn._w(self.attn.qkv, cd))
         a = self.attn.attend(point, qkv)
-        p = F.linear(a, *self.attn._w(self.attn.proj, cd))
+        ls1, ls2 = self._gammas()
+        p = F.linear(a, *self._lin(self.attn.proj, cd, ls1))
         gn2, bn2, eps2 = self._ln(self.norm2[0])
         x, h = ops.ln_residual(p, None, None, eps2, residual=x, gamma2=gn2, beta2=bn2, out2_dtype=cd)
         # mlp
@@ -417,13 +445,14 @@ class Block(PointModule):
                 and ops.mlp_fused_supported(self.channels, hidden) and mlp.fc2.out_features == self.channels):
             # fc1 -> GELU -> fc2 -> + residual in one tcgen05 kernel: the (N, 4C) hidden activation stays on the SM
             w1p, b1, w2p, b2 = _cached(
-                self, "mlp_packed", [mlp.fc1.weight, mlp.fc1.bias, mlp.fc2.weight, mlp.fc2.bias],
+                self, "mlp_packed", [mlp.fc1.weight, mlp.fc1.bias, mlp.fc2.weight, mlp.fc2.bias, ls2],
                 lambda: (ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), mlp.fc1.bias.float().contiguous(),
-                         ops.pack_kmajor(mlp.fc2.weight.to(cd), self.channels), mlp.fc2.bias.float().contiguous()))
+                         ops.pack_kmajor(self._lin(mlp.fc2, cd, ls2)[0], self.channels),
+                         (mlp.fc2.bias.float() * (ls2.float() if ls2 is not None else 1.0)).contiguous()))
             x, xcd = ops.mlp_fused(h, w1p, b1, w2p, b2, hidden, residual=x)
         else:
             f = F.gelu(F.linear(h, *self._lin(mlp.fc1, cd)))
-            f = F.linear(f, *self._lin(mlp.fc2, cd))
+            f = F.linear(f, *self._lin(mlp.fc2, cd, ls2))
             x, xcd = ops.ln_residual(f, None, None, 1e-5, residual=x, out2_dtype=None if cd == torch.float32 else cd)
         point.feat = x
         point["_feat_cd"] = xcd if xcd is not None else x
@@ -852,12 +881,18 @@ class DefaultSegmentorV2(nn.Module):
 
     def __init__(self, num_classes, backbone_out_channels, backbone=None, criteria=None, freeze_backbone=False):
         super().__init__()
-        if isinstance(backbone, dict):
-            conf = dict(backbone)
-            conf.pop("type", None)
-            backbone = PointTransformerV3(**conf)
-        self.backbone = backbone
         self.seg_head = nn.Linear(backbone_out_channels, num_classes) if num_classes > 0 else nn.Identity()
+        if isinstance(backbone, dict):
+            backbone = build_backbone(backbone)
+        self.backbone = backbone
+        if criteria is not None and not callable(criteria):     # the reference's list-of-dicts config (losses/builder.py)
+            from .losses import Criteria
+            criteria = Criteria(criteria)
+        self.criteria = criteria
+        self.freeze_backbone = freeze_backbone
+        if freeze_backbone:                                  # default.py:58-60
+            for p in self.backbone.parameters():
+                p.requires_grad = False
 
     def forward(self, input_dict, return_point=False):
         if self.training:
@@ -865,9 +900,38 @@ class DefaultSegmentorV2(nn.Module):
             return train.segmentor_forward(self, input_dict)
         return self._forward_eval(input_dict, return_point)
 
+    def upcast_logits(self, point):
+        """seg_head(cat(feat_0, feat_1[inv_1], feat_2[inv_2][inv_1], ...)) of default.py:70-84 WITHOUT materialising
+        the concatenation: the head is linear, so each level's slice of the weight is applied at that level's own
+        (2x / 4x / ... fewer) rows and the partial logits are gathered down the pooling_inverse chain:
+            acc_L = feat_L W_L^T ;  acc_l = feat_l W_l^T + acc_{l+1}[inv_{l+1}] ;  logits = acc_0 + bias.
+        For the PTv3-large lin config this replaces an (N, 1728) fp32 tensor by (N, 22) ones."""
+        levels, invs = [point], []
+        while "pooling_parent" in levels[-1]:
+            invs.append(levels[-1]["pooling_inverse"])
+            levels.append(levels[-1]["pooling_parent"])
+        w, b = self.seg_head.weight.float(), self.seg_head.bias
+        lo = sum(lv.feat.shape[1] for lv in levels)
+        assert lo == w.shape[1], "backbone_out_channels must equal the sum of the level widths"
+        acc = None
+        for lv, inv in zip(levels, invs + [None]):           # coarsest first; its columns are the LAST slice
+            c = lv.feat.shape[1]
+            part = F.linear(lv.feat.float(), w[:, lo - c:lo])
+            lo -= c
+            acc = part if acc is None else part + acc
+            if inv is not None:
+                acc = acc.index_select(0, inv)
+        if acc.shape[0] != levels[-1].feat.shape[0]:
+            raise RuntimeError("upcast_logits: broken pooling chain")
+        return (acc + b.float()) if b is not None else acc, levels[-1]
+
     @torch.no_grad()
     def _forward_eval(self, input_dict, return_point=False):
         point = self.backbone(Point(input_dict))
+        if (isinstance(point, Point) and "pooling_parent" in point and isinstance(self.seg_head, nn.Linear)
+                and not return_point):
+            logits, _ = self.upcast_logits(point)
+            return dict(seg_logits=logits)
         while isinstance(point, Point) and "pooling_parent" in point:     # enc_mode backbones (:74-82)
             parent = point.pop("pooling_parent")
             inverse = point.pop("pooling_inverse")
@@ -878,6 +942,18 @@ class DefaultSegmentorV2(nn.Module):
         if return_point:
             out["point"] = point
         return out
+
+
+def build_backbone(conf):
+    """builder.MODELS.build for the two registered PTv3 variants: type "PT-v3m1" (default) or "PT-v3m2"."""
+    conf = dict(conf)
+    kind = conf.pop("type", "PT-v3m1")
+    if kind == "PT-v3m2":
+        from .sonata import PointTransformerV3 as M2
+        return M2(**conf)
+    if kind not in ("PT-v3m1", "PointTransformerV3"):
+        raise NotImplementedError(f"backbone type {kind!r}")
+    return PointTransformerV3(**conf)
 
 
 def aggregate_keypoints(coord, pred, offset, mode="argmax", mask_thresh=0.5):

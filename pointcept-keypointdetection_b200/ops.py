@@ -199,6 +199,35 @@ def gridsample_batch(coord, offset, grid_size, hash_type="fnv", rand=None, quoti
 
 
 # ------------------------------------------------------------------ A6 pooling front end
+def grid_pool(grid_coord, batch, stride, bits, n_scenes):
+    """Integer front end of PT-v3m2's GridPooling (point_transformer_v3m2_sonata.py:393-417) in one launch chain and ONE
+    host read (pooled row count + the pooled grid's per-axis maximum).  Returns dict(cluster, indices, idx_ptr,
+    grid_coord (M,3) int64, batch (M), indices4 (M,4) int32, n_pooled, grid_max (3 ints))."""
+    _need_cuda(grid_coord, batch)
+    lib = _lib.load()
+    g = grid_coord.contiguous()
+    if g.dtype not in (torch.int32, torch.int64):
+        g = g.long()
+    b = batch.contiguous().long()
+    n, dev = g.shape[0], g.device
+    scene_bits = max(1, (int(n_scenes) - 1).bit_length())
+    cluster = torch.empty(n, dtype=torch.int64, device=dev)
+    indices = torch.empty(n, dtype=torch.int64, device=dev)
+    idx_ptr = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    pg = torch.empty((n, 3), dtype=torch.int64, device=dev)
+    pb = torch.empty(n, dtype=torch.int64, device=dev)
+    i4 = torch.empty((n, 4), dtype=torch.int32, device=dev)
+    meta = torch.empty(4, dtype=torch.int64, device=dev)
+    nbytes = lib.ptv3_grid_pool_workspace(n)
+    ws = _ws(nbytes, dev)
+    _lib.check(lib.ptv3_grid_pool(_p(g), int(g.dtype == torch.int64), _p(b), n, int(stride), int(bits), scene_bits,
+                                  _p(cluster), _p(indices), _p(idx_ptr), _p(pg), _p(pb), _p(i4), _p(meta), _p(ws), nbytes,
+                                  _stream()), "ptv3_grid_pool")
+    m, mx, my, mz = (int(v) for v in meta.tolist())      # the level's one host read
+    return dict(cluster=cluster, indices=indices, idx_ptr=idx_ptr[:m + 1], grid_coord=pg[:m], batch=pb[:m],
+                indices4=i4[:m], n_pooled=m, grid_max=(mx, my, mz))
+
+
 def pool_front(code, order, pool_depth):
     """SerializedPooling integer front end (:385-412).  One host sync (pooled count)."""
     _need_cuda(code, order)
@@ -273,8 +302,10 @@ def segment_csr(src, indptr, reduce="sum", gather=None, long_segments=False):
     return out.view((m,) + tuple(shape[1:]))
 
 
-def unpool_add(skip, up, inverse, gelu=True, want_skip_act=True):
-    """out = act(skip) + act(up)[inverse]; also returns act(skip) (SerializedUnpooling :471-482)."""
+def unpool_add(skip, up, inverse, gelu=True, want_skip_act=True, second="skip"):
+    """out = act(skip) + act(up)[inverse] (fp32); the second output, in the input dtype, is act(skip) (PT-v3m1's
+    SerializedUnpooling :471-482, where the sparse tensor keeps the skip branch) or, with second="sum", the sum again
+    (PT-v3m2's GridUnpooling :498-499: the compute-dtype copy for the next conv)."""
     _need_cuda(skip, up, inverse)
     lib = _lib.load()
     skip, up = skip.contiguous(), up.contiguous()
@@ -282,8 +313,9 @@ def unpool_add(skip, up, inverse, gelu=True, want_skip_act=True):
     n, c = skip.shape
     out = torch.empty((n, c), dtype=torch.float32, device=skip.device)
     act = torch.empty_like(skip) if want_skip_act else None
-    _lib.check(lib.ptv3_unpool_add(_p(skip), _p(up), _dt(skip), _p(inverse.contiguous().long()), n, c, int(gelu),
-                                   _p(out), _p(act), _stream()), "ptv3_unpool_add")
+    _lib.check(lib.ptv3_unpool_add(_p(skip), _p(up), _dt(skip), _p(inverse.contiguous().long()), n, c,
+                                   int(bool(gelu)) | (2 if second == "sum" else 0), _p(out), _p(act), _stream()),
+               "ptv3_unpool_add")
     return out, act
 
 

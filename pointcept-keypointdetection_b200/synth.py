@@ -48,6 +48,8 @@ def make_weights(shapes, seed=0):
             w = rng.normal(0.0, 0.1, shape)
         elif leaf == "running_var":
             w = rng.uniform(0.5, 1.5, shape)
+        elif leaf == "gamma":                            # PT-v3m2 LayerScale
+            w = rng.uniform(0.5, 1.5, shape)
         elif len(shape) == 1 and leaf == "weight":      # LN / BN gamma
             w = rng.uniform(0.8, 1.2, shape)
         elif len(shape) == 1:                             # biases, beta

@@ -71,10 +71,12 @@ def block_forward(mod, point):
     windows, nwin = att.get_windows(point)
     a = A.attn_window(qkv, point.serialized_order[att.order_index], windows, nwin, att.num_heads, att.patch_size,
                       att.scale, att.algo)
-    x = _residual(x, _lin(a, att.proj, cd), mod.drop_path_rate, mod.training)
+    g1, g2 = mod._gammas()                    # PT-v3m2 LayerScale (None for PT-v3m1)
+    p = _lin(a, att.proj, cd)
+    x = _residual(x, p if g1 is None else p * g1, mod.drop_path_rate, mod.training)
     mlp = mod.mlp[0]
     f = _lin(mlp.act(_lin(_ln(x, mod.norm2[0], cd), mlp.fc1, cd)), mlp.fc2, cd)
-    x = _residual(x, f, mod.drop_path_rate, mod.training)
+    x = _residual(x, f if g2 is None else f * g2, mod.drop_path_rate, mod.training)
     point.feat = x
     point["_feat_cd"] = None
     point.sparse_conv_feat = sp.replace_feature(x)
@@ -137,6 +139,109 @@ def unpooling_forward(mod, point):
     if mod.traceable:
         parent["unpooling_parent"] = point
     return parent
+
+
+def _seq_tail(x, mods):
+    """norm / activation modules after a Linear, on fp32 rows (torch: LayerNorm / BatchNorm / GELU)."""
+    for m in mods:
+        x = _bn(x, m) if isinstance(m, nn.BatchNorm1d) else m(x.float())
+    return x
+
+
+def embedding_forward_m2(mod, point):
+    """point_transformer_v3m2_sonata.py:532-540."""
+    mods = list(mod.stem._modules.values())
+    y = _seq_tail(F.linear(point.feat.float(), mods[0].weight, mods[0].bias), mods[1:])
+    if "mask" in point:
+        y = torch.where(point.mask.unsqueeze(-1), mod.mask_token.to(y.dtype), y)
+    point.feat = y
+    point["_feat_cd"] = None
+    if "sparse_conv_feat" in point:
+        point.sparse_conv_feat = point.sparse_conv_feat.replace_feature(y)
+    return point
+
+
+def grid_pooling_forward(mod, point):
+    """GridPooling :393-463 with autograd through the projection and the segment reduction."""
+    cd = mod.compute_dtype
+    n_scenes = len(point.offset)
+    with torch.no_grad():
+        plans = point.pop("_pool_plans", None)
+        plan = plans.pop(0) if plans else mod.plan(point.grid_coord, point.batch, mod._depth_of(point), n_scenes,
+                                                   point.order)
+        coord = ops.segment_csr(point.coord.float(), plan["idx_ptr"], "mean", gather=plan["indices"])
+    feat = A.segment_csr(_lin(point.feat, mod.proj, cd), plan["idx_ptr"], mod.reduce, plan["indices"]).float()
+    if hasattr(mod, "norm"):
+        feat = _seq_tail(feat, [mod.norm[0]])
+    if hasattr(mod, "act"):
+        feat = mod.act[0](feat)
+    new = Point(feat=feat, coord=coord, grid_coord=plan["grid_coord"], batch=plan["batch"], offset=plan["offset"],
+                serialized_depth=plan["depth"], serialized_code=plan["code"], serialized_order=plan["order"],
+                serialized_inverse=plan["inverse"], order=point.order)
+    for k in ("condition", "context", "name", "split"):
+        if k in point:
+            new[k] = point[k]
+    if "grid_size" in point:
+        new["grid_size"] = point.grid_size * mod.stride
+    if plans:
+        new["_pool_plans"] = plans
+    new["pooling_inverse"] = plan["cluster"]
+    new["pooling_parent"] = point
+    new["idx_ptr"] = plan["idx_ptr"]
+    new["_pooling_csr"] = (plan["indices"], plan["idx_ptr"])
+    new["sparse_shape"] = [(1 << max(int(plan["depth"]), 0)) + 96] * 3
+    new["sparse_conv_feat"] = SparseConvTensor(feat, plan["indices4"], new["sparse_shape"], n_scenes)
+    return new
+
+
+def grid_unpooling_forward(mod, point):
+    """GridUnpooling :491-504: parent.feat = proj_skip(parent) + proj(point)[inverse]; the sparse tensor is refreshed."""
+    cd = mod.compute_dtype
+    parent = point.pop("pooling_parent")
+    inverse = point.pooling_inverse
+    indices, idx_ptr = point["_pooling_csr"]
+    feat = point.feat
+
+    def branch(seq, x):
+        mods = list(seq._modules.values())
+        return _seq_tail(_lin(x, mods[0], cd), mods[1:]).float()
+    up, skip = branch(mod.proj, point.feat), branch(mod.proj_skip, parent.feat)
+    parent.feat = skip + A.gather_rows(up, inverse, indices, idx_ptr)
+    parent["_feat_cd"] = None
+    parent.sparse_conv_feat = parent.sparse_conv_feat.replace_feature(parent.feat)
+    if mod.traceable:
+        point.feat = feat
+        parent["unpooling_parent"] = point
+    return parent
+
+
+def backbone_forward_m2(bb, data_dict):
+    """PT-v3m2 forward in train() mode (point_transformer_v3m2_sonata.py:720-732).  A backbone without any trainable
+    parameter (DefaultSegmentorV2(freeze_backbone=True), the "lin" configs) runs without building a graph; DropPath
+    stays active like in the reference, which leaves the frozen backbone in train() mode."""
+    from . import model as M
+    from . import sonata as S2
+    point = Point(data_dict)
+    if not hasattr(bb, "_param_cast"):
+        bb._param_cast = A.ParamCast()
+    A.set_param_cast(bb._param_cast.refresh(bb, bb.compute_dtype))
+    frozen = not any(p.requires_grad for p in bb.parameters()) and not point.feat.requires_grad
+    with torch.no_grad():
+        point = bb.plan_levels(point)
+    with torch.set_grad_enabled(not frozen and torch.is_grad_enabled()):
+        point = embedding_forward_m2(bb.embedding, point)
+        for seq in [bb.enc] + ([] if bb.enc_mode else [bb.dec]):
+            for stage in seq._modules.values():
+                for m in stage._modules.values():
+                    if isinstance(m, M.Block):
+                        point = block_forward(m, point)
+                    elif isinstance(m, S2.GridPooling):
+                        point = grid_pooling_forward(m, point)
+                    elif isinstance(m, S2.GridUnpooling):
+                        point = grid_unpooling_forward(m, point)
+                    else:
+                        raise NotImplementedError(type(m))
+    return point
 
 
 def backbone_forward(bb, data_dict):
@@ -220,8 +325,11 @@ def keypoint_forward(model, data_dict):
 
 def segmentor_forward(model, input_dict, criterion=None):
     """default.py:63-95 with a decoder backbone: logits = seg_head(feat); loss = criterion(logits, segment)."""
-    point = backbone_forward(model.backbone, Point(input_dict))
-    logits = model.seg_head(point.feat.float())
+    point = model.backbone(Point(input_dict))           # train() mode: backbone_forward / backbone_forward_m2
+    if "pooling_parent" in point and isinstance(model.seg_head, nn.Linear):
+        logits, _ = model.upcast_logits(point)          # enc_mode: default.py:70-84 without the (N, sum C) concatenation
+    else:
+        logits = model.seg_head(point.feat.float())
     out = dict(seg_logits=logits)
     if "segment" in input_dict:
         crit = criterion or getattr(model, "criteria", None) or nn.CrossEntropyLoss(ignore_index=-1)

@@ -27,12 +27,20 @@ Fixtures (all inputs are seeded; the script is the provenance):
   dense_batch.npz    reference OffsetKeypointPTv3 with enable_flash=False on a TWO-scene batch of unequal sizes (the dense
                      branch's batch-wide patch size K = min(smallest scene, patch), :173-176): eval prediction and a
                      training step (loss, gradient norms, six gradient tensors)
+  sonata.npz         reference DefaultSegmentorV2 over PT-v3m2 (point_transformer_v3m2_sonata.py: GridPooling, LayerScale,
+                     Linear stem, LayerNorm) on a TWO-scene batch: (a) encoder-decoder, 13 classes, C_in 6; (b) enc_mode with
+                     layer_scale, a 768-channel last stage and the segmentor's feature up-cast (22 classes, C_in 9, the
+                     shape family of configs/concerto/semseg-ptv3-large-v1m1-waymo-6a-lin.py); eval logits + intermediate
+                     features, and for (b) a training step (cross-entropy on the logits, drop_path 0): loss and gradients.
+                     Plus the reference LovaszLoss (multiclass, ignore_index) value and gradient on seeded logits.
   heads.npz          reference KeypointPTv3 (scatter_mean + regression MLP, C_in = 4) and
                      DefaultSegmentorV2 (20 classes, C_in = 6, BASELINE configs[2] shape)
                      forwards, one scene each, same deterministic weights
 """
 import os
 import sys
+
+import importlib
 
 import numpy as np
 import torch
@@ -236,6 +244,88 @@ def gold_heads(R):
     np.savez_compressed(os.path.join(HERE, "heads.npz"), **out)
 
 
+import sonata_common  # noqa: E402  (tests/sonata_common.py: the two configurations and the seeded input batch)
+
+SONATA_CFGS, sonata_inputs = sonata_common.CFGS, sonata_common.inputs
+
+
+def gold_sonata(R):
+    import json
+    assert R.ptv3m2 is not None and R.DefaultSegmentorV2 is not None
+    out, shapes_all = {}, {}
+    for tag, cfg in SONATA_CFGS.items():
+        bbc = dict(type="PT-v3m2", enable_flash=False, upcast_attention=False, upcast_softmax=False, drop_path=0.0,
+                   **cfg["backbone"])
+        m = R.DefaultSegmentorV2(num_classes=cfg["num_classes"], backbone_out_channels=cfg["out_channels"],
+                                 backbone=bbc).eval()
+        shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+        W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
+        m.load_state_dict(W, strict=False)
+        shapes_all[tag] = {k: list(v) for k, v in shapes.items() if not k.endswith("num_batches_tracked")}
+        c, g, f, off = sonata_inputs(cfg["backbone"]["in_channels"])
+        feats = {}
+
+        def hook(name):
+            def h(mod, inp, o):
+                feats[name] = o.feat.detach().clone()
+            return h
+        bb = m.backbone
+        hs = [bb.embedding.register_forward_hook(hook("stem")), bb.enc.enc0.register_forward_hook(hook("enc0")),
+              bb.enc.enc1.down.register_forward_hook(hook("pool1")), bb.enc.enc4.register_forward_hook(hook("enc4"))]
+        if not cfg["backbone"]["enc_mode"]:
+            hs.append(bb.dec.dec3.register_forward_hook(hook("dec3")))
+        data = lambda: dict(coord=torch.from_numpy(c), grid_coord=torch.from_numpy(g), feat=torch.from_numpy(f),
+                            offset=torch.from_numpy(off), grid_size=0.02)
+        torch.manual_seed(400)
+        out[f"perms_{tag}"] = np.stack([torch.randperm(4).numpy() for _ in range(5)])
+        torch.manual_seed(400)
+        with torch.no_grad():
+            r = m(data())
+        out[f"logits_{tag}"] = r["seg_logits"].numpy()
+        for k, v in feats.items():
+            out[f"{k}_{tag}"] = v.numpy()
+        for h in hs:
+            h.remove()
+        print("sonata", tag, "rows", len(c), "offset", off.tolist(), "logits", r["seg_logits"].shape)
+        if tag == "enc":      # one training step: train() mode, drop_path 0, cross-entropy on the returned logits
+            rng = np.random.default_rng(5)
+            seg = rng.integers(0, cfg["num_classes"], len(c)).astype(np.int64)
+            seg[rng.random(len(c)) < 0.05] = -1
+            out["segment_enc"] = seg
+            m.train()
+            torch.manual_seed(400)
+            d = data()
+            d["segment"] = torch.from_numpy(seg)
+            logits = m(d)["loss"]          # Criteria() without a config returns the logits (losses/builder.py:21-23)
+            loss = torch.nn.functional.cross_entropy(logits, d["segment"], ignore_index=-1)
+            loss.backward()
+            out["loss_enc"] = np.float64(loss.item())
+            names = [k for k, p in m.named_parameters() if p.grad is not None]
+            out["grad_names_enc"] = np.array(names)
+            out["grad_norms_enc"] = np.array([float(dict(m.named_parameters())[k].grad.norm()) for k in names])
+            for k in SONATA_GRADS:
+                out["grad_enc::" + k] = dict(m.named_parameters())[k].grad.numpy()
+    # LovaszLoss (criteria of the waymo lin config) on seeded logits
+    lov = importlib.import_module("pointcept.models.losses.lovasz")
+    rng = np.random.default_rng(9)
+    lg = torch.from_numpy(rng.normal(size=(700, 7)).astype(np.float32)).requires_grad_(True)
+    lab = rng.integers(0, 6, 700).astype(np.int64)      # class 6 absent
+    lab[rng.random(700) < 0.1] = -1
+    crit = lov.LovaszLoss(mode="multiclass", loss_weight=1.0, ignore_index=-1)
+    val = crit(lg, torch.from_numpy(lab))
+    val.backward()
+    out["lovasz_logits"], out["lovasz_labels"] = lg.detach().numpy(), lab
+    out["lovasz_value"], out["lovasz_grad"] = np.float64(val.item()), lg.grad.numpy()
+    with open(os.path.join(HERE, "param_shapes_sonata.json"), "w") as fh:
+        json.dump(shapes_all, fh, indent=0)
+    np.savez_compressed(os.path.join(HERE, "sonata.npz"), **out)
+
+
+SONATA_GRADS = ["backbone.embedding.stem.linear.weight", "backbone.enc.enc0.block0.cpe.0.weight",
+                "backbone.enc.enc0.block0.ls1.0.gamma", "backbone.enc.enc1.down.proj.weight",
+                "backbone.enc.enc3.block1.attn.qkv.weight", "backbone.enc.enc4.block0.ls2.0.gamma", "seg_head.weight"]
+
+
 from make_golden_names import TRAIN_GRADS, make_target  # noqa: E402  (tests/make_golden_names.py)
 
 
@@ -419,6 +509,9 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["gridsample"]:
         gold_gridsample(R)
         sys.exit(0)
+    if sys.argv[1:] == ["sonata"]:
+        gold_sonata(R)
+        sys.exit(0)
     if sys.argv[1:] == ["dense_batch"]:
         gold_dense_batch(R)
         sys.exit(0)
@@ -433,6 +526,7 @@ if __name__ == "__main__":
     gold_spunet(R)
     gold_eval(R)
     gold_dense_batch(R)
+    gold_sonata(R)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)))

@@ -237,6 +237,11 @@ def load():
     ppt.PDNorm = importlib.import_module(
         "pointcept.models.point_prompt_training.prompt_driven_normalization").PDNorm
     ptv3 = importlib.import_module("pointcept.models.point_transformer_v3.point_transformer_v3m1_base")
+    try:       # PT-v3m2 ("Sonata" PTv3: GridPooling / LayerScale / Linear stem), registered as "PT-v3m2"
+        ptv3m2 = importlib.import_module("pointcept.models.point_transformer_v3.point_transformer_v3m2_sonata")
+    except Exception as e:                                 # noqa: BLE001
+        print("PT-v3m2 not importable:", repr(e))
+        ptv3m2 = None
     okp = importlib.import_module("pointcept.models.offset_keypoint_ptv3")
     kp = importlib.import_module("pointcept.models.keypoint_ptv3")
     # default.py (DefaultSegmentorV2) imports torch_cluster and peft at module level without using them on this path
@@ -277,6 +282,6 @@ def load():
     _loaded.update(ptv3=ptv3, PointTransformerV3=ptv3.PointTransformerV3, SerializedAttention=ptv3.SerializedAttention,
                    OffsetKeypointPTv3=okp.OffsetKeypointPTv3, KeypointPTv3=kp.KeypointPTv3,
                    DefaultSegmentorV2=getattr(seg, "DefaultSegmentorV2", None),
-                   SpUNetBase=getattr(spunet, "SpUNetBase", None),
+                   SpUNetBase=getattr(spunet, "SpUNetBase", None), ptv3m2=ptv3m2,
                    Point=structure.Point, encode=ser.encode, GridSample=tr.GridSample, builder=builder)
     return types.SimpleNamespace(**_loaded)

@@ -107,7 +107,7 @@ def test_subm_conv_vs_oracle(k, cin, cout):
 
 
 @pytest.mark.parametrize("cin,cout", [(32, 32), (64, 64), (128, 128), (256, 256), (512, 512), (32, 64), (64, 32),
-                                      (128, 256), (256, 128)])
+                                      (128, 256), (256, 128), (768, 768), (192, 1024), (768, 256)])
 def test_subm_conv_tcgen05_vs_oracle(cin, cout):
     """bf16 tcgen05 implicit-GEMM kernel (algo 2 and the packed-weight entry) against the fp32 oracle evaluated on
     the bf16-rounded operands: only the final bf16 rounding of the output differs (rel-L2 <= 4e-3)."""

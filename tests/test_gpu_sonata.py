@@ -1,0 +1,211 @@
+"""GPU parity of the PT-v3m2 path (BASELINE configs[4] family): GridPooling's integer front end
+bit-exact against torch.unique(dim=0), the whole DefaultSegmentorV2(PT-v3m2) forward and one training step against the
+UNMODIFIED reference frozen in tests/golden/sonata.npz (encoder-decoder and enc_mode + LayerScale + 768-channel stage +
+feature up-cast).  Tolerances: fp32 rel-L2 <= 1e-4 everywhere.  bf16: <= 1e-2 (north_star) down to the third level and for
+the full-size scene of test_sonata_fullsize_scene_vs_oracle; <= 1.5e-2 for the 56- and 10-row levels and the logits of
+this tiny two-scene fixture: every GridPooling ends in max -> LayerNorm, whose mean removal amplifies the error the bf16
+Blocks already put into the fp32 residual stream by ~1.2e-3 per level (measured per module with tools/sonata_dbg.py;
+PT-v3m1's BatchNorm does not do that), and the coarse levels of the fixture hold too few rows to average it out.
+Gradients that went through the whole network: <= 1e-3 (fp32) / 0.3 (bf16, like test_gpu_train.py)."""
+import numpy as np
+import pytest
+import torch
+
+import sonata_common as SC
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_l2(a, b):
+    a, b = torch.as_tensor(a).detach().float().cpu(), torch.as_tensor(b).detach().float().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+@pytest.mark.parametrize("n,scenes,stride,span", [(20000, 3, 2, 200), (5000, 1, 2, 64), (30000, 7, 4, 1000), (1, 1, 2, 4),
+                                                  (4000, 2, 3, 90)])
+def test_grid_pool_matches_torch_unique(n, scenes, stride, span):
+    from ptv3_b200 import ops
+    g = torch.Generator().manual_seed(n + stride)
+    grid = torch.randint(0, span, (n, 3), generator=g, dtype=torch.int32)
+    grid[: n // 3] = grid[n // 3: n // 3 + n // 3] | 1 if n >= 3 else grid[: n // 3]      # plenty of shared cells
+    batch = torch.sort(torch.randint(0, scenes, (n,), generator=g))[0]
+    # reference statement (point_transformer_v3m2_sonata.py:405-417)
+    rows = torch.div(grid.long(), stride, rounding_mode="trunc")
+    rows[:, 0] |= batch << 48
+    uniq, cluster, counts = torch.unique(rows, sorted=True, return_inverse=True, return_counts=True, dim=0)
+    uniq = uniq & ((1 << 48) - 1)
+    depth = int(int(grid.max()) + 1).bit_length()
+    for gdev in (grid.cuda(), grid.long().cuda()):
+        r = ops.grid_pool(gdev, batch.cuda(), stride, depth, scenes)
+        assert r["n_pooled"] == uniq.shape[0]
+        assert torch.equal(r["cluster"].cpu(), cluster)
+        assert torch.equal(r["grid_coord"].cpu(), uniq)
+        assert torch.equal(r["idx_ptr"].cpu(), torch.cat([counts.new_zeros(1), counts.cumsum(0)]))
+        ind = r["indices"].cpu()
+        assert torch.equal(cluster[ind], torch.sort(cluster)[0]) and torch.equal(torch.sort(ind)[0], torch.arange(n))
+        head = ind[r["idx_ptr"].cpu()[:-1]]
+        assert torch.equal(r["batch"].cpu(), batch[head])
+        assert torch.equal(r["indices4"].cpu(), torch.cat([batch[head][:, None], uniq], 1).int())
+        assert list(r["grid_max"]) == uniq.max(0).values.tolist()
+    assert ops.device_error() == 0
+
+
+def test_grid_pool_flags_out_of_range_coordinates():
+    from ptv3_b200 import ops
+    grid = torch.tensor([[1, 2, 3], [40, 2, 3]], dtype=torch.int32).cuda()
+    ops.grid_pool(grid, torch.zeros(2, dtype=torch.long).cuda(), 2, 4, 1)       # 40 / 2 does not fit 4 bits
+    assert ops.device_error() & 4
+    assert ops.device_error() == 0
+
+
+def _model(tag, dtype):
+    from ptv3_b200 import model as M
+    cfg = SC.CFGS[tag]
+    m = M.DefaultSegmentorV2(cfg["num_classes"], cfg["out_channels"],
+                             backbone=dict(type="PT-v3m2", enable_flash=False, drop_path=0.0, **cfg["backbone"]))
+    missing, unexpected = m.load_state_dict(SC.weights(tag), strict=False)
+    assert not missing and not unexpected
+    m.backbone.set_compute_dtype(dtype)
+    return m.cuda()
+
+
+def _data(tag):
+    c, g, f, off = SC.inputs(SC.CFGS[tag]["backbone"]["in_channels"])
+    return dict(coord=torch.from_numpy(c).cuda(), grid_coord=torch.from_numpy(g).cuda(), feat=torch.from_numpy(f).cuda(),
+                offset=torch.from_numpy(off).cuda(), grid_size=0.02)
+
+
+@pytest.mark.parametrize("dtype,tol,tol_deep", [(torch.float32, 1e-4, 1e-4), (torch.bfloat16, 1e-2, 1.5e-2)])
+@pytest.mark.parametrize("tag", ["dec", "enc"])
+def test_sonata_forward_golden(tag, dtype, tol, tol_deep):
+    G = SC.golden()
+    m = _model(tag, dtype).eval()
+    feats = {}
+
+    def hook(name):
+        def h(mod, inp, o):
+            feats[name] = o.feat.detach().float().clone()
+        return h
+    bb = m.backbone
+    bb.embedding.register_forward_hook(hook("stem"))
+    bb.enc.enc0.register_forward_hook(hook("enc0"))
+    bb.enc.enc1.down.register_forward_hook(hook("pool1"))
+    bb.enc.enc4.register_forward_hook(hook("enc4"))
+    if tag == "dec":
+        bb.dec.dec3.register_forward_hook(hook("dec3"))
+    torch.manual_seed(400)
+    out = m(_data(tag))
+    errs = {k: rel_l2(v, G[f"{k}_{tag}"]) for k, v in feats.items()}
+    errs["logits"] = rel_l2(out["seg_logits"], G[f"logits_{tag}"])
+    print(f"PT-v3m2 {tag} {dtype}: " + ", ".join(f"{k} {v:.2e}" for k, v in errs.items()))
+    from ptv3_b200 import ops
+    assert ops.device_error() == 0
+    assert max(errs[k] for k in ("stem", "enc0", "pool1")) <= tol, errs
+    assert max(errs.values()) <= tol_deep, errs
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])
+def test_sonata_fullsize_scene_vs_oracle(dtype, tol):
+    """One config-2-sized scene (100 k raw points -> ~73 k voxels) through PT-v3m2 (encoder-decoder, LayerScale on) against
+    the oracle (pinned exactly on the reference by test_oracle.py::test_sonata_oracle_vs_reference)."""
+    from oracle import gridsample as G
+    from oracle import sonata as SO
+    from ptv3_b200 import model as M, synth
+    cfg = dict(SC.CFGS["dec"]["backbone"], layer_scale=0.5, enc_depths=(2, 2, 2, 6, 2))
+    m = M.DefaultSegmentorV2(13, 64, backbone=dict(type="PT-v3m2", drop_path=0.0, **cfg))
+    shapes = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    W = {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=3).items()}
+    m.load_state_dict(W, strict=False)
+    m.backbone.set_compute_dtype(dtype)
+    m = m.cuda().eval()
+    coord, feat = synth.pig_scan(100000, scale=4.1, seed=5, in_channels=6)
+    gs = G.grid_sample(coord, 0.02)
+    iu = gs["idx_unique"]
+    c, g, f = coord[iu], gs["grid_coord"][iu], feat[iu]
+    torch.manual_seed(77)
+    perms = [torch.randperm(4).numpy() for _ in range(5)]
+    pt = SO.backbone_forward(W, c, g, f, [len(iu)], cfg=cfg, perms=perms)
+    ref = SO.seg_head(W, pt.feat)
+    torch.manual_seed(77)
+    out = m(dict(coord=torch.from_numpy(c).cuda(), grid_coord=torch.from_numpy(g).cuda(), feat=torch.from_numpy(f).cuda(),
+                 offset=torch.tensor([len(iu)]).cuda(), grid_size=0.02))
+    e_logits = rel_l2(out["seg_logits"], ref)
+    print(f"PT-v3m2 full-size scene ({len(iu)} voxels) {dtype}: logits rel-L2 {e_logits:.2e}")
+    assert e_logits <= tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_sonata_native_block_equals_op_by_op(dtype):
+    """LayerScale folded into the one-call Block path and into the op-by-op path give the same features."""
+    from ptv3_b200 import ops
+    m = _model("enc", dtype).eval()
+    torch.manual_seed(400)
+    a = m(_data("enc"))["seg_logits"]
+    ops.NATIVE_BLOCK = False
+    try:
+        torch.manual_seed(400)
+        b = m(_data("enc"))["seg_logits"]
+    finally:
+        ops.NATIVE_BLOCK = True
+    assert rel_l2(a, b) <= (1e-6 if dtype == torch.float32 else 2e-3)
+
+
+def test_upcast_logits_equal_the_concatenation():
+    m = _model("enc", torch.float32).eval()
+    torch.manual_seed(400)
+    fused = m(_data("enc"))["seg_logits"]
+    torch.manual_seed(400)
+    plain = m(_data("enc"), return_point=True)["seg_logits"]           # materialises the (N, 1248) concatenation
+    assert plain.shape == fused.shape and rel_l2(fused, plain) <= 1e-5
+
+
+@pytest.mark.parametrize("dtype,tol_loss,tol_grad", [(torch.float32, 1e-5, 1e-3), (torch.bfloat16, 1e-2, 0.3)])
+def test_sonata_training_step_golden(dtype, tol_loss, tol_grad):
+    G = SC.golden()
+    m = _model("enc", dtype).train()
+    d = _data("enc")
+    d["segment"] = torch.from_numpy(G["segment_enc"]).cuda()
+    torch.manual_seed(400)
+    out = m(d)
+    loss = out["loss"]
+    loss.backward()
+    assert abs(loss.item() - float(G["loss_enc"])) <= tol_loss * max(1.0, abs(float(G["loss_enc"])))
+    params = dict(m.named_parameters())
+    names, norms = [str(s) for s in G["grad_names_enc"]], G["grad_norms_enc"]
+    assert set(names) == {k for k, p in params.items() if p.grad is not None}
+    worst = 0.0
+    for k, ref in zip(names, norms):
+        got = float(params[k].grad.float().norm())
+        worst = max(worst, abs(got - ref) / max(ref, 1e-12))
+    full = {k[len("grad_enc::"):]: rel_l2(params[k[len("grad_enc::"):]].grad, G[k]) for k in G.files
+            if k.startswith("grad_enc::")}
+    print(f"PT-v3m2 train {dtype}: loss {loss.item():.6f} vs {float(G['loss_enc']):.6f}, worst grad-norm error "
+          f"{worst:.2e}, full tensors " + ", ".join(f"{k.split('.', 1)[1]} {v:.2e}" for k, v in full.items()))
+    assert worst <= tol_grad and max(full.values()) <= tol_grad
+
+
+def test_frozen_backbone_trains_the_head_only():
+    """DefaultSegmentorV2(freeze_backbone=True) (the waymo "lin" config): no graph through the backbone, gradients
+    for the head only, and the same loss as the unfrozen model (drop_path 0)."""
+    from ptv3_b200 import model as M
+    cfg = SC.CFGS["enc"]
+    G = SC.golden()
+    m = M.DefaultSegmentorV2(cfg["num_classes"], cfg["out_channels"], freeze_backbone=True,
+                             criteria=[dict(type="CrossEntropyLoss", loss_weight=1.0, ignore_index=-1),
+                                       dict(type="LovaszLoss", mode="multiclass", loss_weight=1.0, ignore_index=-1)],
+                             backbone=dict(type="PT-v3m2", enable_flash=False, drop_path=0.0, **cfg["backbone"]))
+    m.load_state_dict(SC.weights("enc"), strict=False)
+    m.backbone.set_compute_dtype(torch.float32)
+    m = m.cuda().train()
+    d = _data("enc")
+    d["segment"] = torch.from_numpy(G["segment_enc"]).cuda()
+    torch.manual_seed(400)
+    out = m(d)
+    out["loss"].backward()
+    grads = {k for k, p in m.named_parameters() if p.grad is not None}
+    assert grads == {"seg_head.weight", "seg_head.bias"}
+    from ptv3_b200 import losses
+    logits = torch.from_numpy(G["logits_enc"])       # eval logits = train logits here (no BatchNorm, drop_path 0)
+    seg = torch.from_numpy(G["segment_enc"])
+    ref = torch.nn.functional.cross_entropy(logits, seg, ignore_index=-1) + losses.lovasz_softmax(logits, seg, -1)
+    assert abs(out["loss"].item() - ref.item()) <= 1e-4 * max(1.0, abs(ref.item()))

@@ -236,3 +236,17 @@ def test_shim_trace_covers_every_third_party_call_site():
     assert kinds == {"encode": 4, "SubMConv3d.forward": 23, "flash_attn_varlen_qkvpacked_func": 22, "segment_csr": 8}
     assert callable(shims.segment_csr) and callable(shims.flash_attn_varlen_qkvpacked_func)
     assert hasattr(shims.SubMConv3d, "forward")
+
+
+def test_sonata_state_dict_matches_reference():
+    """PT-v3m2 modules carry the reference's state_dict names and shapes (tests/golden/param_shapes_sonata.json, written
+    from the unmodified reference by make_golden.py sonata), so its checkpoints load unchanged."""
+    import json
+    import sonata_common as SC
+    from ptv3_b200 import model as M
+    with open(os.path.join(REPO, "tests", "golden", "param_shapes_sonata.json")) as f:
+        shapes = json.load(f)
+    for tag, cfg in SC.CFGS.items():
+        m = M.DefaultSegmentorV2(cfg["num_classes"], cfg["out_channels"], backbone=dict(type="PT-v3m2", **cfg["backbone"]))
+        got = {k: list(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
+        assert got == shapes[tag], (tag, set(got) ^ set(shapes[tag]))

@@ -290,3 +290,43 @@ def test_offset_keypoint_eval_vs_reference(golden):
     assert mean_dist == float(g["mean_dist"])                         # same arithmetic in the same order: exact
     assert np.array_equal(np.array(per_kp), g["per_kp"])
     assert acc[1] == 4 and acc[2 + 6 + 2] == 3                        # scene 1 of batch 0 not a sample; keypoint 2 skipped once
+
+
+@pytest.mark.parametrize("tag", ["dec", "enc"])
+def test_sonata_oracle_vs_reference(tag):
+    """oracle/sonata.py (PT-v3m2: GridPooling, LayerScale, Linear stem, LayerNorm, enc_mode feature up-cast) pinned on the
+    UNMODIFIED reference's DefaultSegmentorV2(PT-v3m2) run on a two-scene batch (tests/golden/sonata.npz)."""
+    import sonata_common as SC
+    from oracle import sonata as SO
+    G = SC.golden()
+    cfg = dict(SC.CFGS[tag]["backbone"], enable_flash=False)
+    W = SC.weights(tag)
+    c, g, f, off = SC.inputs(cfg["in_channels"])
+    trace = {}
+    pt = SO.backbone_forward(W, c, g, f, off, cfg=cfg, perms=list(G[f"perms_{tag}"]), trace=trace)
+    feat = SO.upcast_features(pt) if cfg["enc_mode"] else pt.feat
+    assert feat.shape[1] == SC.CFGS[tag]["out_channels"]
+    logits = SO.seg_head(W, feat)
+    ref = torch.from_numpy(G[f"logits_{tag}"])
+    assert logits.shape == ref.shape and ((logits - ref).norm() / ref.norm()).item() < 1e-5
+    for k in ("stem", "enc0", "pool1", "enc4", "dec3"):
+        if f"{k}_{tag}" in G.files:
+            r = torch.from_numpy(G[f"{k}_{tag}"])
+            assert ((trace[k] - r).norm() / r.norm()).item() < 1e-5, k
+
+
+def test_lovasz_softmax_vs_reference():
+    """ptv3_b200.losses.LovaszLoss (one batched sort over all classes) against the reference's class-by-class
+    LovaszLoss(mode="multiclass", ignore_index=-1): value and gradient (tests/golden/sonata.npz)."""
+    import sonata_common as SC
+    from ptv3_b200 import losses
+    G = SC.golden()
+    lg = torch.from_numpy(G["lovasz_logits"]).requires_grad_(True)
+    crit = losses.Criteria([dict(type="LovaszLoss", mode="multiclass", loss_weight=1.0, ignore_index=-1)])
+    v = crit(lg, torch.from_numpy(G["lovasz_labels"]))
+    v.backward()
+    assert abs(v.item() - float(G["lovasz_value"])) < 1e-6
+    assert (lg.grad - torch.from_numpy(G["lovasz_grad"])).abs().max().item() < 1e-6
+    # all labels ignored: zero loss with a graph (lovasz.py:127-129)
+    z = losses.lovasz_softmax(lg, torch.full((lg.shape[0],), -1), ignore_index=-1)
+    assert z.item() == 0.0 and z.requires_grad
