@@ -39,7 +39,19 @@ WORKLOADS = {
             name="configs[1]: 16 x 100k-pt pig scans, keypoint-offset head"),
     3: dict(scenes=8, points=150000, scale=5.0, in_channels=6, head="segmentor",
             name="configs[2]: semseg-pt-v3m1-0-base shape, 8 ScanNet-sized scenes (150k pts, C_in 6, 20 classes)"),
+    # configs[4]: configs/concerto/semseg-ptv3-large-v1m1-waymo-6a-lin.py -- PT-v3m2 encoder (3,3,3,12,3) x
+    # (64,128,256,512,768), frozen, + Linear(1728, 22) head trained with CE + Lovasz; batch 64 over 8 GPUs = 8 sweeps per
+    # GPU; Waymo-shaped 64-beam sweeps of ~180 k returns, scaled by 0.2 and voxelised at 0.01 (the config's RandomScale /
+    # GridSample: 5 cm cells of the original sweep).  --mode train only.
+    5: dict(scenes=8, points=180000, scale=0.2, in_channels=9, head="lin", grid=0.01,
+            name="configs[4]: PTv3-large (PT-v3m2) linear-probe TRAINING step, 8 Waymo-shaped 180k-pt sweeps per GPU"),
 }
+
+LARGE_M2 = dict(type="PT-v3m2", in_channels=9, order=("z", "z-trans", "hilbert", "hilbert-trans"), stride=(2, 2, 2, 2),
+                enc_depths=(3, 3, 3, 12, 3), enc_channels=(64, 128, 256, 512, 768), enc_num_head=(4, 8, 16, 32, 48),
+                enc_patch_size=(1024,) * 5, mlp_ratio=4, qkv_bias=True, drop_path=0.3, shuffle_orders=True,
+                pre_norm=True, enable_rpe=False, enable_flash=True, traceable=False, mask_token=False, enc_mode=True,
+                freeze_encoder=False)
 
 
 def peaks():
@@ -141,13 +153,13 @@ def shard_scenes(n_scenes, rank, world, scaling):
     return [1000 * rank + i for i in range(n_scenes)]
 
 
-def voxelize_on_device(raw, device):
+def voxelize_on_device(raw, device, grid=GRID):
     """GridSample (our CUDA kernel, first point per voxel) per scene -> host numpy batch dict."""
     from ptv3_b200 import ops
     coords, feats, grids, counts = [], [], [], []
     for coord, feat in raw:
         c = torch.from_numpy(coord).to(device)
-        r = ops.gridsample(c, GRID, "fnv")
+        r = ops.gridsample(c, grid, "fnv")
         iu = r["idx_unique"]
         coords.append(c[iu].cpu())
         feats.append(torch.from_numpy(feat).to(device)[iu].cpu())
@@ -391,6 +403,12 @@ def cpu_sample_scene(args, seconds, steps=1):
     full = 72900.0 * (args.scale / 4.1) ** 2 * min(1.0, args.points / 100000.0) ** 0.5     # voxels of one full scene
     target = min(full, target)
     scale = args.scale * (target / full) ** 0.5
+    if getattr(args, "head", "") == "lin":       # a bounded part of one Waymo-shaped sweep: fewer rays, same geometry
+        target = max(3000.0, min(150000.0, 1500.0 * max(1.0, (cores / 8.0) ** 0.5) * seconds / steps))
+        coord, feat = synth.lidar_sweep(int(target * 1.25), seed=0, in_channels=9, beams=64, max_range=75.0)
+        gs = G.grid_sample((coord * args.scale).astype(np.float32), WORKLOADS[5]["grid"])
+        iu = gs["idx_unique"]
+        return (coord * args.scale).astype(np.float32)[iu], feat[iu], gs["grid_coord"][iu], args.scale
     coord, feat = synth.pig_scan(args.points, scale=scale, seed=0, in_channels=getattr(args, "in_channels", 4))
     gs = G.grid_sample(coord, GRID)
     iu = gs["idx_unique"]
@@ -401,6 +419,18 @@ def cpu_forward(W, scene, head="offset"):
     from oracle import ptv3 as P
     c, f, g, _ = scene
     perms = [torch.randperm(4).numpy() for _ in range(5)]
+    if head == "lin":      # configs[4]: frozen PT-v3m2 encoder (no graph), up-cast, Linear head with CE loss + head grads
+        from oracle import sonata as SO
+        cfg = {k: v for k, v in LARGE_M2.items() if k != "type"}
+        pt = SO.backbone_forward(W, c, g, f, [len(c)], cfg=cfg, perms=perms)
+        feat = SO.upcast_features(pt)
+        w = W["seg_head.weight"].clone().requires_grad_(True)
+        b = W["seg_head.bias"].clone().requires_grad_(True)
+        with torch.enable_grad():
+            loss = torch.nn.functional.cross_entropy(torch.nn.functional.linear(feat, w, b),
+                                                     torch.zeros(len(c), dtype=torch.long))
+            loss.backward()
+        return loss.detach()
     pt = P.backbone_forward(W, c, g, f, [len(c)], cfg=dict(CFG, in_channels=f.shape[1]), perms=perms)
     return P.seg_head(W, pt.feat) if head == "segmentor" else P.offset_head(W, pt.feat)
 
@@ -408,8 +438,11 @@ def cpu_forward(W, scene, head="offset"):
 def cpu_weights(args):
     from ptv3_b200 import model as M, synth
     conf = dict(CFG, in_channels=args.in_channels)
-    m = (M.DefaultSegmentorV2(num_classes=20, backbone_out_channels=64, backbone=conf) if args.head == "segmentor"
-         else M.OffsetKeypointPTv3(backbone_conf=conf))
+    if args.head == "lin":
+        m = M.DefaultSegmentorV2(num_classes=22, backbone_out_channels=1728, backbone=dict(LARGE_M2))
+    else:
+        m = (M.DefaultSegmentorV2(num_classes=20, backbone_out_channels=64, backbone=conf) if args.head == "segmentor"
+             else M.OffsetKeypointPTv3(backbone_conf=conf))
     shapes = {k: tuple(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
     return {k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()}
 
@@ -455,12 +488,15 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     v = n * args.steps / dt
     sample = f"1 scene per step at scale {scene[3]:.2f} -> {n} voxels (of the {args.scenes}-scene batch), fp32"
-    line = dict(impl="reference", metric=METRIC, value=round(v, 1), unit=UNIT, n_gpus=int(os.environ.get("WORLD_SIZE", "1")),
+    lin = args.head == "lin"
+    line = dict(impl="reference", metric="ptv3_train_step_voxels_per_sec" if lin else METRIC, value=round(v, 1), unit=UNIT, n_gpus=int(os.environ.get("WORLD_SIZE", "1")),
                 steps=args.steps, warmup=args.warmup, ms_per_step=round(dt / args.steps * 1e3, 3),
                 higher_is_better=True, scaling=args.scaling, vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=f"PTv3-v1m1 + {'20-class segmentor' if args.head == 'segmentor' else 'offset-keypoint'} "
-                                     f"head forward on the host CPU ({args.workload_name}; oracle port of the "
-                                     f"reference, enable_flash=False semantics one scene per forward, restated spconv), {sample}"),
+                config=dict(workload=(f"PTv3-large (PT-v3m2) frozen-encoder forward + Linear(1728, 22) head loss / gradient on "
+                                      f"the host CPU ({args.workload_name}; oracle port, restated spconv), {sample}") if lin
+                            else f"PTv3-v1m1 + {'20-class segmentor' if args.head == 'segmentor' else 'offset-keypoint'} "
+                                 f"head forward on the host CPU ({args.workload_name}; oracle port of the "
+                                 f"reference, enable_flash=False semantics one scene per forward, restated spconv), {sample}"),
                 cpu_baseline=dict(value=round(v, 1), unit=UNIT, cores=cores, kind="port", sample=sample),
                 e2e=dict(value=round(v, 1), unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
                 gpu_launches=0)
@@ -485,17 +521,46 @@ def run_train(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
-    model, _ = build_model(dtype, device)
+    lin = args.head == "lin"
+    if lin:       # BASELINE configs[4]
+        from ptv3_b200 import model as M, synth
+        model = M.DefaultSegmentorV2(
+            num_classes=22, backbone_out_channels=1728, backbone=dict(LARGE_M2, compute_dtype=dtype), freeze_backbone=True,
+            criteria=[dict(type="CrossEntropyLoss", loss_weight=1.0, ignore_index=-1),
+                      dict(type="LovaszLoss", mode="multiclass", loss_weight=1.0, ignore_index=-1)])
+        shapes = {k: tuple(v.shape) for k, v in model.state_dict().items()}
+        model.load_state_dict({k: torch.from_numpy(v) for k, v in synth.make_weights(shapes, seed=0).items()},
+                              strict=False)
+        model = model.to(device)
+        raw = []
+        for i in range(args.scenes):      # rays without a return (sky) are dropped by the generator: oversample, keep `points`
+            c, f = synth.lidar_sweep(int(args.points * 2.2), seed=1000 * rank + i, in_channels=9, beams=64, max_range=75.0)
+            keep = np.random.default_rng(i).permutation(len(c))[: args.points]
+            raw.append(((c[keep] * args.scale).astype(np.float32), f[keep]))
+        grid = WORKLOADS[5]["grid"]
+    else:
+        model, _ = build_model(dtype, device)
+        raw = make_raw_scenes(args.scenes, args.points, args.scale, seed0=1000 * rank)
+        grid = GRID
     model.train()
-    raw = make_raw_scenes(args.scenes, args.points, args.scale, seed0=1000 * rank)
-    host, counts = voxelize_on_device(raw, device)
+    host, counts = voxelize_on_device(raw, device, grid)
     n_vox = int(sum(counts))
-    host["target"] = torch.from_numpy(make_target(n_vox, 7 + rank))
+    if lin:
+        rng = np.random.default_rng(7 + rank)
+        seg = rng.integers(0, 22, n_vox).astype(np.int64)
+        seg[rng.random(n_vox) < 0.05] = -1
+        host["segment"] = torch.from_numpy(seg)
+    else:
+        host["target"] = torch.from_numpy(make_target(n_vox, 7 + rank))
     pinned = {k: v.pin_memory() for k, v in host.items()}
     resident = {k: v.to(device) for k, v in host.items()}
     h2d_bytes = int(sum(v.numel() * v.element_size() for v in pinned.values()))
-    opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=0.05, fused=True)
-    sync = GradSync(model.parameters()) if world > 1 else None
+    trainable = [p for p in model.parameters() if p.requires_grad]
+    if lin:       # the config's optimizer: AdamW(lr 0.002, weight_decay 0.005) over what is not frozen (the head)
+        opt = torch.optim.AdamW(trainable, lr=0.002, weight_decay=0.005, fused=True)
+    else:
+        opt = torch.optim.AdamW(trainable, lr=1e-4, weight_decay=0.05, fused=True)
+    sync = GradSync(trainable) if world > 1 else None
 
     def step(batch):
         if sync is not None:
@@ -551,14 +616,20 @@ def run_train(args):
         dist.all_reduce(total_vox)
     total_vox = float(total_vox.item())
     n_params = sum(p.numel() for p in model.parameters())
+    if lin:
+        what = (f"PTv3-large (PT-v3m2 encoder 3-3-3-12-3 x 64-128-256-512-768, frozen, train() mode with DropPath 0.3) + "
+                f"Linear(1728, 22) head TRAINING step (fwd + CE + Lovasz + head bwd + AdamW), {args.scenes} Waymo-shaped "
+                f"sweeps x {args.points} returns (x {args.scale}, grid {grid} m) per GPU ({args.workload_name})")
+    else:
+        what = (f"PTv3-v1m1 + offset-keypoint head TRAINING step (fwd + loss + bwd + AdamW), {args.scenes} scenes x "
+                f"{args.points} raw pts (scale {args.scale}, grid {GRID} m) per GPU")
     if rank == 0:
         print(json.dumps(dict(
             metric="ptv3_train_step_voxels_per_sec", value=round(total_vox * args.steps / (ms * 1e-3), 1), unit=UNIT,
             n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=round(ms / args.steps, 3),
             higher_is_better=True, scaling="weak", vs_baseline=None, dtype=args.dtype, data="synthetic", mode="train",
-            config=dict(workload=f"PTv3-v1m1 + offset-keypoint head TRAINING step (fwd + loss + bwd + AdamW), "
-                                 f"{args.scenes} scenes x {args.points} raw pts (scale {args.scale}, grid {GRID} m) "
-                                 f"per GPU", voxels_per_gpu=n_vox, params=n_params,
+            config=dict(workload=what, voxels_per_gpu=n_vox, params=n_params,
+                        trainable_params=sum(p.numel() for p in trainable),
                         parallelism=f"replicas x{world}, scenes sharded per rank, bucketed gradient all-reduce "
                                     f"({'NCCL AVG, overlapped with backward' if world > 1 else 'none at N=1'})"),
             e2e=dict(value=round(total_vox * args.steps / (e2e_wall * 1e-3), 1), unit=UNIT, h2d_bytes_per_step=h2d_bytes,
@@ -576,9 +647,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
-    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3],
+    ap.add_argument("--config", type=int, default=2, choices=[1, 2, 3, 5],
                     help="BASELINE.json workload: 1 = configs[0] (one 40k-pt scan), 2 = configs[1] (16 x 100k-pt scans, the "
-                         "headline), 3 = configs[2] (8 ScanNet-sized scenes, C_in 6, 20-class segmentor)")
+                         "headline), 3 = configs[2] (8 ScanNet-sized scenes, C_in 6, 20-class segmentor), 5 = configs[4] (PTv3-large "
+                         "linear-probe training step on Waymo-shaped sweeps; implies --mode train)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: --scenes per GPU (default); strong: --scenes in total, dealt over the ranks")
     ap.add_argument("--scenes", type=int, default=None)
@@ -593,6 +665,8 @@ def main():
         if getattr(args, k) is None:
             setattr(args, k, wl[k])
     args.in_channels, args.head, args.workload_name = wl["in_channels"], wl["head"], wl["name"]
+    if args.config == 5:
+        args.mode = "train"
     if args.impl == "reference":
         run_reference(args)
     elif args.mode == "train":

@@ -309,6 +309,12 @@ int ptv3_device_error(void);
 int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float* beta, float eps,
                      const float* residual, float* res_out, const float* gamma2, const float* beta2, void* out2,
                      int dtype_out2, int64_t n, int c, void* stream);
+/* The same with DropPath on the branch (timm.layers.DropPath as used by Block, point_transformer_v3m1_base.py:329-335):
+ * t *= row_scale[row] (fp32 (n): 0 or 1 / keep_prob, NULL = none) before the residual add.  Used when a frozen backbone
+ * runs in train() mode (DefaultSegmentorV2(freeze_backbone=True), default.py:58-60) through the fused kernels. */
+int ptv3_ln_residual_rs(const void* x, int dtype_x, const float* gamma, const float* beta, float eps,
+                        const float* row_scale, const float* residual, float* res_out, const float* gamma2,
+                        const float* beta2, void* out2, int dtype_out2, int64_t n, int c, void* stream);
 
 /* ---------------------------------------------------------------------------
  * A6 glue: y = act(x * scale[c] + shift[c]) in one pass (eval BatchNorm + GELU after the pooled segment-max,

@@ -73,6 +73,8 @@ SIGNATURES = {
     "ptv3_device_error": (c_int, []),
     "ptv3_ln_residual": (c_int, [c_vp, c_int, c_vp, c_vp, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_i64, c_int,
                                  c_vp]),
+    "ptv3_ln_residual_rs": (c_int, [c_vp, c_int, c_vp, c_vp, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_i64,
+                                    c_int, c_vp]),
     "ptv3_affine_act": (c_int, [c_vp, c_int, c_vp, c_vp, c_int, c_i64, c_int, c_vp, c_vp, c_vp]),
     "ptv3_subm_wgrad": (c_int, [c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_attn_window_bwd_workspace": (c_sz, [c_i64, c_int]),

@@ -160,7 +160,7 @@ __global__ void __launch_bounds__(256) unpool_add_kernel(const T* __restrict__ s
 }
 
 // One warp per row, MAXV channels per lane (c <= 32*MAXV).
-//   t = gamma ? LayerNorm(x; gamma, beta) : x ;  r = residual ? residual + t : t
+//   t = gamma ? LayerNorm(x; gamma, beta) : x ;  t *= row_scale[row] (optional) ;  r = residual ? residual + t : t
 //   res_out = r (fp32, optional) ;  out2 = LayerNorm(r; gamma2, beta2) (optional)
 template <typename TX, typename TO, int MAXV>
 __global__ void __launch_bounds__(256) ln_residual_kernel(const TX* __restrict__ x, const float* __restrict__ gamma,
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(256) ln_residual_kernel(const TX* __restrict__
                                                           const float* __restrict__ residual,
                                                           float* __restrict__ res_out, const float* __restrict__ gamma2,
                                                           const float* __restrict__ beta2, TO* __restrict__ out2,
-                                                          int64_t n, int c) {
+                                                          int64_t n, int c, const float* __restrict__ row_scale) {
   const int lane = threadIdx.x & 31;
   int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -195,6 +195,7 @@ __global__ void __launch_bounds__(256) ln_residual_kernel(const TX* __restrict__
     for (int d = 16; d > 0; d >>= 1) q += __shfl_xor_sync(0xffffffffu, q, d);
     float rstd = rsqrtf(q * inv_c + eps);
     if (gamma == nullptr) { mean = 0.f; rstd = 1.f; }
+    const float rs = row_scale ? row_scale[row] : 1.f;     // DropPath: 0 or 1 / keep for the whole row of the branch
     float s2 = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
@@ -202,6 +203,7 @@ __global__ void __launch_bounds__(256) ln_residual_kernel(const TX* __restrict__
       if (ch < c) {
         float y = (v[i] - mean) * rstd;
         if (gamma) y = y * gamma[ch] + beta[ch];
+        y *= rs;
         if (residual) y += residual[row * c + ch];
         v[i] = y;
         if (res_out) res_out[row * c + ch] = y;
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(256) ln_residual_vec_kernel(const TX* __restri
                                                               float* __restrict__ res_out,
                                                               const float* __restrict__ gamma2,
                                                               const float* __restrict__ beta2, TO* __restrict__ out2,
-                                                              int64_t n) {
+                                                              int64_t n, const float* __restrict__ row_scale) {
   constexpr int C = L * 8 * VPT;
   constexpr int ROWS_PER_WARP = 32 / L;
   const int lane = threadIdx.x & 31, sub = lane % L;
@@ -320,6 +322,13 @@ __global__ void __launch_bounds__(256) ln_residual_vec_kernel(const TX* __restri
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[p][i] = (v[p][i] - mean) * rstd * g[i] + b[i];
       }
+    }
+    if (row_scale) {
+      const float rs = row_scale[row];
+#pragma unroll
+      for (int p = 0; p < VPT; ++p)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[p][i] *= rs;
     }
     float s2 = 0.f;
 #pragma unroll
@@ -438,6 +447,13 @@ int ptv3_unpool_add(const void* skip, const void* up, int dtype, const int64_t* 
 int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float* beta, float eps,
                      const float* residual, float* res_out, const float* gamma2, const float* beta2, void* out2,
                      int dtype_out2, int64_t n, int c, void* stream) {
+  return ptv3_ln_residual_rs(x, dtype_x, gamma, beta, eps, nullptr, residual, res_out, gamma2, beta2, out2, dtype_out2,
+                             n, c, stream);
+}
+
+int ptv3_ln_residual_rs(const void* x, int dtype_x, const float* gamma, const float* beta, float eps,
+                        const float* row_scale, const float* residual, float* res_out, const float* gamma2,
+                        const float* beta2, void* out2, int dtype_out2, int64_t n, int c, void* stream) {
   if (n < 0 || c < 1 || c > 1024 || (gamma && !beta)) return PTV3_EINVAL;
   if (gamma2 && !beta2) return PTV3_EINVAL;
   if (n == 0) return PTV3_OK;
@@ -455,7 +471,7 @@ int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float
     if (gv > capv) gv = capv;
 #define LAUNCHVEC(TX, TO, L, VPT)                                                                                  \
   ln_residual_vec_kernel<TX, TO, L, VPT><<<gv, 256, 0, st>>>((const TX*)x, gamma, beta, eps, residual, res_out, \
-                                                            gamma2, beta2, (TO*)out2, n)
+                                                            gamma2, beta2, (TO*)out2, n, row_scale)
 #define LAUNCHC(TX, TO)                          \
   do {                                           \
     if (c == 32) LAUNCHVEC(TX, TO, 4, 1);        \
@@ -475,7 +491,7 @@ int ptv3_ln_residual(const void* x, int dtype_x, const float* gamma, const float
   }
 #define LAUNCHV(TX, TO, V)                                                                                   \
   ln_residual_kernel<TX, TO, V><<<g, 256, 0, st>>>((const TX*)x, gamma, beta, eps, residual, res_out, gamma2, \
-                                                   beta2, (TO*)out2, n, c)
+                                                   beta2, (TO*)out2, n, c, row_scale)
 #define LAUNCH(TX, TO)                                                                   \
   do {                                                                                   \
     if (c <= 32) LAUNCHV(TX, TO, 1);                                                     \

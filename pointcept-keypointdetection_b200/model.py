@@ -405,15 +405,32 @@ class Block(PointModule):
         return (self.native and ops.NATIVE_BLOCK and cd == torch.bfloat16 and self.conv_algo != 1
                 and self._fast()["static_ok"])
 
-    @torch.no_grad()
+    def _drop_scale(self, n, device):
+        """timm DropPath in train() mode: one Bernoulli(keep) draw per row, kept rows scaled by 1 / keep (the same draw,
+        in the same order, as train._residual); None in eval() or with rate 0."""
+        if not self.training or self.drop_path_rate == 0.0:
+            return None
+        keep = 1.0 - self.drop_path_rate
+        return torch.empty((n, 1), dtype=torch.float32, device=device).bernoulli_(keep).div_(keep)
+
     def forward(self, point):
-        if self.training:
-            raise NotImplementedError("ptv3_b200 Block: inference only (call .eval())")
+        """Fused forward WITHOUT a graph.  eval(): the inference path.  train() under torch.no_grad(): a frozen backbone
+        in a training step (DefaultSegmentorV2(freeze_backbone=True) leaves it in train() mode, default.py:58-60), i.e.
+        the same kernels with DropPath applied inside the residual kernels; anything that needs gradients goes
+        through train.block_forward."""
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError("ptv3_b200 Block.forward builds no graph: use train.block_forward (the model's "
+                                      "forward dispatches to it in train() mode) or call .eval()")
+        with torch.no_grad():
+            return self._forward(point)
+
+    def _forward(self, point):
         cd = self.compute_dtype
         x = point.feat if point.feat.dtype == torch.float32 else point.feat.float()
         sp = point.sparse_conv_feat
         conv_in = sp.features if sp.features.dtype == cd else sp.features.to(cd)
-        if self._native_ok(cd):
+        dropping = self.training and self.drop_path_rate > 0.0
+        if self._native_ok(cd) and not dropping:
             f = self._fast()
             attn = f["attn"]
             bp, _keep = self._native_params()
@@ -437,11 +454,12 @@ class Block(PointModule):
         ls1, ls2 = self._gammas()
         p = F.linear(a, *self._lin(self.attn.proj, cd, ls1))
         gn2, bn2, eps2 = self._ln(self.norm2[0])
-        x, h = ops.ln_residual(p, None, None, eps2, residual=x, gamma2=gn2, beta2=bn2, out2_dtype=cd)
+        x, h = ops.ln_residual(p, None, None, eps2, residual=x, gamma2=gn2, beta2=bn2, out2_dtype=cd,
+                               row_scale=self._drop_scale(x.shape[0], x.device))
         # mlp
         mlp = self.mlp[0]
         hidden = mlp.fc1.out_features
-        if (cd == torch.bfloat16 and isinstance(mlp.act, nn.GELU) and mlp.act.approximate == "none"
+        if (cd == torch.bfloat16 and isinstance(mlp.act, nn.GELU) and mlp.act.approximate == "none" and not dropping
                 and ops.mlp_fused_supported(self.channels, hidden) and mlp.fc2.out_features == self.channels):
             # fc1 -> GELU -> fc2 -> + residual in one tcgen05 kernel: the (N, 4C) hidden activation stays on the SM
             w1p, b1, w2p, b2 = _cached(
@@ -453,7 +471,8 @@ class Block(PointModule):
         else:
             f = F.gelu(F.linear(h, *self._lin(mlp.fc1, cd)))
             f = F.linear(f, *self._lin(mlp.fc2, cd, ls2))
-            x, xcd = ops.ln_residual(f, None, None, 1e-5, residual=x, out2_dtype=None if cd == torch.float32 else cd)
+            x, xcd = ops.ln_residual(f, None, None, 1e-5, residual=x, out2_dtype=None if cd == torch.float32 else cd,
+                                     row_scale=self._drop_scale(x.shape[0], x.device))
         point.feat = x
         point["_feat_cd"] = xcd if xcd is not None else x
         point.sparse_conv_feat = sp.replace_feature(point["_feat_cd"])

@@ -320,9 +320,10 @@ def unpool_add(skip, up, inverse, gelu=True, want_skip_act=True, second="skip"):
 
 
 def ln_residual(x, gamma=None, beta=None, eps=1e-5, residual=None, want_res=True, gamma2=None, beta2=None,
-                out2_dtype=None):
-    """t = LN(x) if gamma is given else x; r = residual + t (or t).  Returns (r fp32 or None, out2 or None) with
-    out2 = LN2(r) if gamma2 is given, else r cast to out2_dtype (when out2_dtype is given)."""
+                out2_dtype=None, row_scale=None):
+    """t = LN(x) if gamma is given else x; t *= row_scale[:, None] if given (DropPath: fp32 (n), 0 or 1 / keep);
+    r = residual + t (or t).  Returns (r fp32 or None, out2 or None) with out2 = LN2(r) if gamma2 is given, else r cast
+    to out2_dtype (when out2_dtype is given)."""
     _need_cuda(x)
     lib = _lib.load()
     x = x.contiguous()
@@ -334,9 +335,12 @@ def ln_residual(x, gamma=None, beta=None, eps=1e-5, residual=None, want_res=True
     if residual is not None:
         residual = residual.contiguous()
         assert residual.dtype == torch.float32
-    _lib.check(lib.ptv3_ln_residual(_p(x), _dt(x), _p(gamma), _p(beta), float(eps), _p(residual), _p(res_out),
-                                    _p(gamma2), _p(beta2), _p(out2), _dt(out2) if out2 is not None else 0, n, c,
-                                    _stream()), "ptv3_ln_residual")
+    if row_scale is not None:
+        row_scale = row_scale.contiguous().view(-1)
+        assert row_scale.dtype == torch.float32 and row_scale.numel() == n
+    _lib.check(lib.ptv3_ln_residual_rs(_p(x), _dt(x), _p(gamma), _p(beta), float(eps), _p(row_scale), _p(residual),
+                                       _p(res_out), _p(gamma2), _p(beta2), _p(out2),
+                                       _dt(out2) if out2 is not None else 0, n, c, _stream()), "ptv3_ln_residual_rs")
     return res_out, out2
 
 

@@ -320,6 +320,7 @@ class PointTransformerV3(PointModule):
                 p.requires_grad = False
         self.apply(self._init_weights)
         self.plan_ahead = True
+        self.fused_when_frozen = True      # A/B switch: frozen backbone in train() runs the fused kernels (train.py)
         self.set_compute_dtype(compute_dtype)
 
     @staticmethod

@@ -228,6 +228,11 @@ def backbone_forward_m2(bb, data_dict):
     frozen = not any(p.requires_grad for p in bb.parameters()) and not point.feat.requires_grad
     with torch.no_grad():
         point = bb.plan_levels(point)
+        if frozen and bb.fused_when_frozen:
+            # no graph needed and no BatchNorm anywhere in PT-v3m2: the fused inference modules ARE the train() forward,
+            # with DropPath applied inside the residual kernels (model.Block.forward)
+            point = bb.enc(bb.embedding(point))
+            return point if bb.enc_mode else bb.dec(point)
     with torch.set_grad_enabled(not frozen and torch.is_grad_enabled()):
         point = embedding_forward_m2(bb.embedding, point)
         for seq in [bb.enc] + ([] if bb.enc_mode else [bb.dec]):

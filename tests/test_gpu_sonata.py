@@ -209,3 +209,27 @@ def test_frozen_backbone_trains_the_head_only():
     seg = torch.from_numpy(G["segment_enc"])
     ref = torch.nn.functional.cross_entropy(logits, seg, ignore_index=-1) + losses.lovasz_softmax(logits, seg, -1)
     assert abs(out["loss"].item() - ref.item()) <= 1e-4 * max(1.0, abs(ref.item()))
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 3e-2)])     # bf16: two differently rounded paths
+def test_frozen_fused_forward_with_drop_path_equals_train_path(dtype, tol):
+    """A frozen backbone in train() mode runs the fused kernels with DropPath inside the residual kernels; the op-by-op
+    training forward (train.block_forward) with the same device seed must give the same logits (same Bernoulli draws)."""
+    from ptv3_b200 import model as M
+    cfg = SC.CFGS["enc"]
+    m = M.DefaultSegmentorV2(cfg["num_classes"], cfg["out_channels"], freeze_backbone=True,
+                             backbone=dict(type="PT-v3m2", enable_flash=False, drop_path=0.3, **cfg["backbone"]))
+    m.load_state_dict(SC.weights("enc"), strict=False)
+    m.backbone.set_compute_dtype(dtype)
+    m = m.cuda().train()
+    outs = []
+    for fused in (True, False):
+        m.backbone.fused_when_frozen = fused
+        torch.manual_seed(400)
+        torch.cuda.manual_seed(123)
+        outs.append(m(_data("enc"))["seg_logits"].detach())
+    m.eval()
+    torch.manual_seed(400)
+    ev = m(_data("enc"))["seg_logits"]
+    assert rel_l2(outs[0], outs[1]) <= tol
+    assert rel_l2(outs[0], ev) > 5e-2          # DropPath did something
