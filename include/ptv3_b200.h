@@ -260,6 +260,10 @@ int ptv3_mlp_fused_supported(int c, int hidden);
 int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
                    const float* residual /* NULL ok */, int64_t n, int c, int hidden, float* res_out /* NULL ok */,
                    void* out_bf16 /* NULL ok */, void* stream);
+/* The same with DropPath on the MLP branch: (fc2 out + b2) * row_scale[row] before the residual add (NULL = none). */
+int ptv3_mlp_fused_rs(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
+                      const float* residual, const float* row_scale, int64_t n, int c, int hidden, float* res_out,
+                      void* out_bf16, void* stream);
 
 /* ---------------------------------------------------------------------------
  * A8  one call per Block (inference, bf16 operands): the whole launch chain of Block.forward
@@ -283,6 +287,9 @@ typedef struct ptv3_block_params {
   const float *cpe_ln_g, *cpe_ln_b, *norm1_g, *norm1_b, *norm2_g, *norm2_b;
   const void *qkv_w, *qkv_b, *proj_w, *proj_b;
   const void *fc1_w, *fc1_b, *fc2_w, *fc2_b;
+  /* DropPath of the two residual branches for THIS call (timm DropPath in train() mode, :329-335): fp32 (n) row scales,
+   * 0 or 1 / keep_prob; NULL = none (eval).  Used by a frozen backbone inside a training step. */
+  const float *drop_attn, *drop_mlp;
 } ptv3_block_params;
 size_t ptv3_block_workspace(const ptv3_block_params* p, int64_t n, int64_t n_windows_max);
 int ptv3_block_fwd(const ptv3_block_params* p, const float* x, const void* conv_in, const int32_t* nbr,

@@ -200,18 +200,19 @@ int ptv3_block_fwd(const ptv3_block_params* p, const float* x, const void* conv_
   PTV3_TRY(ptv3_attn_window_fwd(qkv, PTV3_BF16, order, windows, n_windows, n_windows_max, p->patch, n, p->heads, 16,
                                 p->scale, p->attn_algo, a, attn_ws, attn_ws_bytes, stream));
   PTV3_TRY(linear_bf16(a, p->proj_w, p->proj_b, pr, n, c, c, lt_ws, st));
-  PTV3_TRY(ptv3_ln_residual(pr, PTV3_BF16, nullptr, nullptr, p->eps_norm2, x1, x2, p->norm2_g, p->norm2_b, h2,
-                            PTV3_BF16, n, c, stream));
+  PTV3_TRY(ptv3_ln_residual_rs(pr, PTV3_BF16, nullptr, nullptr, p->eps_norm2, p->drop_attn, x1, x2, p->norm2_g,
+                               p->norm2_b, h2, PTV3_BF16, n, c, stream));
   // MLP + shortcut (:332-337)
   if (p->mlp_fused) {
-    PTV3_TRY(ptv3_mlp_fused(h2, p->fc1_w, static_cast<const float*>(p->fc1_b), p->fc2_w,
-                            static_cast<const float*>(p->fc2_b), x2, n, c, p->hidden, x_out, x_out_bf16, stream));
+    PTV3_TRY(ptv3_mlp_fused_rs(h2, p->fc1_w, static_cast<const float*>(p->fc1_b), p->fc2_w,
+                               static_cast<const float*>(p->fc2_b), x2, p->drop_mlp, n, c, p->hidden, x_out, x_out_bf16,
+                               stream));
   } else {
     PTV3_TRY(linear_bf16(h2, p->fc1_w, p->fc1_b, f1, n, c, p->hidden, lt_ws, st));
     PTV3_TRY(ptv3_affine_act(f1, PTV3_BF16, nullptr, nullptr, 1, n, p->hidden, nullptr, f1, stream));   // exact GELU
     PTV3_TRY(linear_bf16(f1, p->fc2_w, p->fc2_b, f2, n, p->hidden, c, lt_ws, st));
-    PTV3_TRY(ptv3_ln_residual(f2, PTV3_BF16, nullptr, nullptr, 1e-5f, x2, x_out, nullptr, nullptr, x_out_bf16,
-                              PTV3_BF16, n, c, stream));
+    PTV3_TRY(ptv3_ln_residual_rs(f2, PTV3_BF16, nullptr, nullptr, 1e-5f, p->drop_mlp, x2, x_out, nullptr, nullptr,
+                                 x_out_bf16, PTV3_BF16, n, c, stream));
   }
 #undef PTV3_TRY
   return PTV3_OK;

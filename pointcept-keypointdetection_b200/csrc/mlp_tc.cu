@@ -90,7 +90,8 @@ __global__ void __launch_bounds__(256) pack_kmajor_kernel(const __nv_bfloat16* _
 template <int C>
 __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w1p, const float* __restrict__ b1,
-    const __nv_bfloat16* __restrict__ w2p, const float* __restrict__ b2, const float* __restrict__ residual, int64_t n,
+    const __nv_bfloat16* __restrict__ w2p, const float* __restrict__ b2, const float* __restrict__ residual,
+    const float* __restrict__ row_scale, int64_t n,
     int n_tiles, float* __restrict__ res_out, __nv_bfloat16* __restrict__ out_bf16) {
   using namespace mlp;
   using L = Smem<C>;
@@ -259,11 +260,13 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
       float4 rres[NC / 4];
 #pragma unroll
       for (int j = 0; j < NC / 4; ++j) rres[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      float rs = 1.f;      // DropPath on the branch: 0 or 1 / keep for the whole row (NULL = none)
       if (residual && grow < n) {
         const float4* rp = reinterpret_cast<const float4*>(residual + grow * C + col0);
 #pragma unroll
         for (int j = 0; j < NC / 4; ++j) rres[j] = __ldcs(rp + j);
       }
+      if (row_scale && grow < n) rs = row_scale[grow];
       mbar_wait(bar(13 + ab), tph);
       fence_after_sync();
       uint32_t v[NC];
@@ -276,7 +279,7 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
         float f[NC];
         const float* b2s = reinterpret_cast<const float*>(smem + L::BIAS_OFF) + L::HID;
 #pragma unroll
-        for (int j = 0; j < NC; ++j) f[j] = __uint_as_float(v[j]) + b2s[col0 + j];
+        for (int j = 0; j < NC; ++j) f[j] = (__uint_as_float(v[j]) + b2s[col0 + j]) * rs;
 #pragma unroll
         for (int j = 0; j < NC / 4; ++j) {
           f[4 * j] += rres[j].x; f[4 * j + 1] += rres[j].y; f[4 * j + 2] += rres[j].z; f[4 * j + 3] += rres[j].w;
@@ -317,8 +320,8 @@ bool mlp_fused_supported(int c, int hidden) { return (c == 32 || c == 64) && hid
 
 template <int C>
 static int launch_mlp(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const float* b1, const __nv_bfloat16* w2p,
-                      const float* b2, const float* residual, int64_t n, float* res_out, __nv_bfloat16* out_bf16,
-                      cudaStream_t st) {
+                      const float* b2, const float* residual, const float* row_scale, int64_t n, float* res_out,
+                      __nv_bfloat16* out_bf16, cudaStream_t st) {
   using L = mlp::Smem<C>;
   static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
   static bool configured = false;
@@ -328,8 +331,8 @@ static int launch_mlp(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const fl
   }
   const int n_tiles = (int)cdiv(n, mlp::TM);
   const int g = n_tiles < kNumSMs ? n_tiles : kNumSMs;
-  mlp_fused_kernel<C><<<g, mlp::THREADS, L::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, n, n_tiles, res_out,
-                                                              out_bf16);
+  mlp_fused_kernel<C><<<g, mlp::THREADS, L::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, row_scale, n, n_tiles,
+                                                              res_out, out_bf16);
   return check_launch();
 }
 
@@ -355,15 +358,21 @@ int ptv3_mlp_fused_supported(int c, int hidden) { return mlp_fused_supported(c, 
 
 int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
                    const float* residual, int64_t n, int c, int hidden, float* res_out, void* out_bf16, void* stream) {
+  return ptv3_mlp_fused_rs(x, w1_packed, b1, w2_packed, b2, residual, nullptr, n, c, hidden, res_out, out_bf16, stream);
+}
+
+int ptv3_mlp_fused_rs(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
+                      const float* residual, const float* row_scale, int64_t n, int c, int hidden, float* res_out,
+                      void* out_bf16, void* stream) {
   if (n < 0 || !mlp_fused_supported(c, hidden)) return n < 0 ? PTV3_EINVAL : PTV3_EUNSUPPORTED;
   if (n == 0) return PTV3_OK;
   if (!x || !w1_packed || !b1 || !w2_packed || !b2 || (!res_out && !out_bf16)) return PTV3_EINVAL;
   cudaStream_t st = as_stream(stream);
   if (c == 32)
     return launch_mlp<32>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed,
-                          b2, residual, n, res_out, (__nv_bfloat16*)out_bf16, st);
+                          b2, residual, row_scale, n, res_out, (__nv_bfloat16*)out_bf16, st);
   return launch_mlp<64>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed,
-                        b2, residual, n, res_out, (__nv_bfloat16*)out_bf16, st);
+                        b2, residual, row_scale, n, res_out, (__nv_bfloat16*)out_bf16, st);
 }
 
 }  // extern "C"

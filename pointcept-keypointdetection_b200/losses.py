@@ -27,8 +27,10 @@ def lovasz_softmax(logits, labels, ignore_index=None):
     errors_sorted, perm = torch.sort(errors, dim=1, descending=True)
     fg_sorted = torch.gather(fg, 1, perm)
     gts = fg_sorted.sum(1, keepdim=True)
-    inter = gts - fg_sorted.cumsum(1)
-    union = gts + (1.0 - fg_sorted).cumsum(1)
+    cum = fg_sorted.cumsum(1)                         # the only scan: cumsum(1 - fg) = position - cumsum(fg)
+    pos = torch.arange(1, cum.shape[1] + 1, device=cum.device, dtype=cum.dtype)
+    inter = gts - cum
+    union = gts + (pos - cum)
     jac = 1.0 - inter / union
     jac = torch.cat([jac[:, :1], jac[:, 1:] - jac[:, :-1]], dim=1)
     per_class = (errors_sorted * jac).sum(1)

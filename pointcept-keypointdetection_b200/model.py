@@ -429,13 +429,16 @@ class Block(PointModule):
         x = point.feat if point.feat.dtype == torch.float32 else point.feat.float()
         sp = point.sparse_conv_feat
         conv_in = sp.features if sp.features.dtype == cd else sp.features.to(cd)
-        dropping = self.training and self.drop_path_rate > 0.0
-        if self._native_ok(cd) and not dropping:
+        if self._native_ok(cd):
             f = self._fast()
             attn = f["attn"]
             bp, _keep = self._native_params()
             windows, nwin = attn.get_windows(point)
             bp.patch, bp.attn_algo = int(attn.patch_size), int(attn.algo)
+            d1 = self._drop_scale(x.shape[0], x.device)         # train() + no graph: DropPath inside the residual kernels
+            d2 = self._drop_scale(x.shape[0], x.device)
+            bp.drop_attn, bp.drop_mlp = (d1.data_ptr() if d1 is not None else None), \
+                (d2.data_ptr() if d2 is not None else None)
             x, xcd = ops.block_fwd(bp, x.contiguous(), conv_in.contiguous(), f["conv"].neighbor_map(sp),
                                    point.serialized_order[attn.order_index], windows, nwin)
             point.feat = x
@@ -459,7 +462,7 @@ class Block(PointModule):
         # mlp
         mlp = self.mlp[0]
         hidden = mlp.fc1.out_features
-        if (cd == torch.bfloat16 and isinstance(mlp.act, nn.GELU) and mlp.act.approximate == "none" and not dropping
+        if (cd == torch.bfloat16 and isinstance(mlp.act, nn.GELU) and mlp.act.approximate == "none"
                 and ops.mlp_fused_supported(self.channels, hidden) and mlp.fc2.out_features == self.channels):
             # fc1 -> GELU -> fc2 -> + residual in one tcgen05 kernel: the (N, 4C) hidden activation stays on the SM
             w1p, b1, w2p, b2 = _cached(
@@ -467,9 +470,14 @@ class Block(PointModule):
                 lambda: (ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), mlp.fc1.bias.float().contiguous(),
                          ops.pack_kmajor(self._lin(mlp.fc2, cd, ls2)[0], self.channels),
                          (mlp.fc2.bias.float() * (ls2.float() if ls2 is not None else 1.0)).contiguous()))
-            x, xcd = ops.mlp_fused(h, w1p, b1, w2p, b2, hidden, residual=x)
+            x, xcd = ops.mlp_fused(h, w1p, b1, w2p, b2, hidden, residual=x,
+                                   row_scale=self._drop_scale(x.shape[0], x.device))
         else:
-            f = F.gelu(F.linear(h, *self._lin(mlp.fc1, cd)))
+            f = F.linear(h, *self._lin(mlp.fc1, cd))
+            if cd == torch.bfloat16 and isinstance(mlp.act, nn.GELU) and mlp.act.approximate == "none":
+                _, f = ops.affine_act(f, None, None, "gelu", want_f32=False, want_bf16=True)    # 16-byte vectorised GELU
+            else:
+                f = mlp.act(f)
             f = F.linear(f, *self._lin(mlp.fc2, cd, ls2))
             x, xcd = ops.ln_residual(f, None, None, 1e-5, residual=x, out2_dtype=None if cd == torch.float32 else cd,
                                      row_scale=self._drop_scale(x.shape[0], x.device))
@@ -933,13 +941,21 @@ class DefaultSegmentorV2(nn.Module):
         lo = sum(lv.feat.shape[1] for lv in levels)
         assert lo == w.shape[1], "backbone_out_channels must equal the sum of the level widths"
         acc = None
-        for lv, inv in zip(levels, invs + [None]):           # coarsest first; its columns are the LAST slice
-            c = lv.feat.shape[1]
-            part = F.linear(lv.feat.float(), w[:, lo - c:lo])
-            lo -= c
-            acc = part if acc is None else part + acc
-            if inv is not None:
-                acc = acc.index_select(0, inv)
+        # fp32 parity mode keeps strict fp32 GEMMs; with a bf16 backbone (the reference runs this Linear under autocast
+        # in bf16) the slices use TF32 tensor-core products with fp32 accumulation, like the offset head
+        tf32 = getattr(self.backbone, "compute_dtype", torch.float32) != torch.float32
+        prev = torch.backends.cuda.matmul.allow_tf32
+        torch.backends.cuda.matmul.allow_tf32 = bool(tf32)
+        try:
+            for lv, inv in zip(levels, invs + [None]):           # coarsest first; its columns are the LAST slice
+                c = lv.feat.shape[1]
+                part = F.linear(lv.feat.float(), w[:, lo - c:lo])
+                lo -= c
+                acc = part if acc is None else part + acc
+                if inv is not None:
+                    acc = acc.index_select(0, inv)
+        finally:
+            torch.backends.cuda.matmul.allow_tf32 = prev
         if acc.shape[0] != levels[-1].feat.shape[0]:
             raise RuntimeError("upcast_logits: broken pooling chain")
         return (acc + b.float()) if b is not None else acc, levels[-1]

@@ -361,8 +361,9 @@ def mlp_fused_supported(c, hidden):
     return bool(_lib.load().ptv3_mlp_fused_supported(int(c), int(hidden)))
 
 
-def mlp_fused(x, w1_packed, b1, w2_packed, b2, hidden, residual=None, want_res=True, want_bf16=True):
-    """r = (residual +) fc2(GELU(fc1(x))) in one kernel.  x (N,C) bf16.  Returns (r fp32 or None, r bf16 or None)."""
+def mlp_fused(x, w1_packed, b1, w2_packed, b2, hidden, residual=None, want_res=True, want_bf16=True, row_scale=None):
+    """r = (residual +) row_scale[:, None] * fc2(GELU(fc1(x))) in one kernel (row_scale: DropPath, fp32 (N) or None).
+    x (N,C) bf16.  Returns (r fp32 or None, r bf16 or None)."""
     _need_cuda(x, w1_packed, w2_packed)
     lib = _lib.load()
     x = x.contiguous()
@@ -374,8 +375,12 @@ def mlp_fused(x, w1_packed, b1, w2_packed, b2, hidden, residual=None, want_res=T
         residual = residual.contiguous()
         assert residual.dtype == torch.float32 and residual.shape == x.shape
     with _timed("mlp_fused", n=n, c=c, hidden=int(hidden)):
-        _lib.check(lib.ptv3_mlp_fused(_p(x), _p(w1_packed), _p(b1), _p(w2_packed), _p(b2), _p(residual), n, c,
-                                      int(hidden), _p(res_out), _p(out16), _stream()), "ptv3_mlp_fused")
+        if row_scale is not None:
+            row_scale = row_scale.contiguous().view(-1)
+            assert row_scale.dtype == torch.float32 and row_scale.numel() == n
+        _lib.check(lib.ptv3_mlp_fused_rs(_p(x), _p(w1_packed), _p(b1), _p(w2_packed), _p(b2), _p(residual),
+                                         _p(row_scale), n, c, int(hidden), _p(res_out), _p(out16), _stream()),
+                   "ptv3_mlp_fused_rs")
     return res_out, out16
 
 
