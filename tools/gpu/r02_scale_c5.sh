@@ -1,0 +1,10 @@
+#!/bin/bash
+# BASELINE configs[4] at its own scale: batch 64 = 8 sweeps per GPU x 8 GPUs, NCCL all-reduce of the head gradients.
+set -x
+mkdir -p gpurun_out
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29531 \
+  bench.py --gpus 8 --config 5 --steps 10 --warmup 3 > gpurun_out/r2_scale_c5_n8.json 2> gpurun_out/r2_scale_c5_n8.err
+tail -c 600 gpurun_out/r2_scale_c5_n8.err; cut -c 1-1500 gpurun_out/r2_scale_c5_n8.json
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29532 \
+  bench.py --gpus 8 --mode train --steps 10 --warmup 3 > gpurun_out/r2_scale_train_n8.json 2> gpurun_out/r2_scale_train_n8.err
+tail -c 600 gpurun_out/r2_scale_train_n8.err; cut -c 1-1500 gpurun_out/r2_scale_train_n8.json
