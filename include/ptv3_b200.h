@@ -33,6 +33,7 @@ extern "C" {
 #define PTV3_EWORKSPACE (-2) /* workspace too small */
 #define PTV3_ELAUNCH (-3)    /* cudaGetLastError() != cudaSuccess after a launch */
 #define PTV3_EUNSUPPORTED (-4)
+#define PTV3_ETOOLARGE (-5)   /* size beyond the fixed capacity of an allocation-free (`_static`) entry point */
 
 /* element types of floating point feature buffers */
 #define PTV3_F32 0
@@ -74,6 +75,23 @@ int ptv3_grid_max(const void* grid_coord, int grid_is_i64, int64_t n, int64_t* o
 size_t ptv3_argsort_rows_workspace(int64_t rows, int64_t n);
 int ptv3_argsort_rows(const int64_t* code, int64_t rows, int64_t n, int key_bits, int64_t* order,
                       int64_t* inverse /* may be NULL */, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ptv3_argsort_rows without a workspace argument and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same inputs, outputs and result (bit-identical) as ptv3_argsort_rows; the
+ * scratch is a file-scope `static __device__` array of PTV3_ARGSORT_STATIC_SCRATCH_BYTES (8 MiB) inside the library,
+ * held by every GPU that loads it until the process exits.  Limit: rows * n <= PTV3_ARGSORT_STATIC_MAX_ELEMS (262 144
+ * codes per call, e.g. the 4 orders of a 65 536-voxel scene) AND ptv3_argsort_rows_workspace(rows, n) <= the array size
+ * (only violated by thousands of very short rows, whose per-row histograms dominate); otherwise the call returns
+ * PTV3_ETOOLARGE and enqueues nothing.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine), only enqueues on `stream`.
+ * All calls on a device share the one array (it keeps the previous call's contents; nothing in it has to start at
+ * zero): calls that OVERLAP on the GPU -- different streams, concurrent graph branches -- race; serialise them. */
+#define PTV3_ARGSORT_STATIC_SCRATCH_BYTES (8u << 20)
+#define PTV3_ARGSORT_STATIC_MAX_ELEMS 262144
+int64_t ptv3_argsort_rows_static_max_elems(void);
+int ptv3_argsort_rows_static(const int64_t* code, int64_t rows, int64_t n, int key_bits, int64_t* order,
+                             int64_t* inverse /* may be NULL */, void* stream);
 
 /* ---------------------------------------------------------------------------
  * A0  GridSample voxel hashing / unique / representative selection.

@@ -32,6 +32,8 @@ SIGNATURES = {
     "ptv3_grid_max": (c_int, [c_vp, c_int, c_i64, c_vp, c_vp]),
     "ptv3_argsort_rows_workspace": (c_sz, [c_i64, c_i64]),
     "ptv3_argsort_rows": (c_int, [c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp, c_sz, c_vp]),
+    "ptv3_argsort_rows_static_max_elems": (c_i64, []),
+    "ptv3_argsort_rows_static": (c_int, [c_vp, c_i64, c_i64, c_int, c_vp, c_vp, c_vp]),
     "ptv3_gridsample_workspace": (c_sz, [c_i64]),
     "ptv3_gridsample": (c_int, [c_vp, c_i64, c_f64, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                 c_vp, c_sz, c_vp]),

@@ -112,6 +112,7 @@ const char* ptv3_error_string(int code) {
     case PTV3_EWORKSPACE: return "workspace too small";
     case PTV3_ELAUNCH: return "CUDA launch failure";
     case PTV3_EUNSUPPORTED: return "unsupported configuration";
+    case PTV3_ETOOLARGE: return "size beyond the fixed capacity of this allocation-free entry point";
     default: return "unknown error";
   }
 }

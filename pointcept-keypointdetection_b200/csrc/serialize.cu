@@ -1,6 +1,7 @@
 // A2: Morton / Hilbert codes + row-wise LSD radix argsort with fused inverse.
 // Integer work, bit-exact against oracle/serialization.py (pinned on the
 // reference's encode(), tests/golden/serialization.npz).
+#include <mutex>
 #include "common.cuh"
 
 namespace ptv3 {
@@ -311,6 +312,68 @@ int ptv3_argsort_rows(const int64_t* code, int64_t rows, int64_t n, int key_bits
   if (!order || !code) return PTV3_EINVAL;
   return radix_argsort_rows((const uint64_t*)code, rows, n, key_bits, order, inverse, nullptr, workspace,
                             workspace_bytes, as_stream(stream));
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// ptv3_argsort_rows_static: ptv3_argsort_rows without a caller workspace and without ANY allocation (no counterpart in
+// the reference; added for callers that cannot call cudaMalloc: CUDA graph
+// capture, tight serving loops, harnesses that forbid it).  The radix sort's scratch (two key buffers, two index
+// buffers, the per-tile histograms and the scan partials) lives in the file-scope device array below: 8 MiB that every
+// GPU which loads the library holds until exit.  In host code `g_argsort_static_scratch` is only a host-side stand-in
+// for the symbol -- never a device address -- so the device address is resolved ONCE PER DEVICE, with that device
+// current, by cudaGetSymbolAddress, and that pointer is what the kernels receive.
+// Every call on a device shares the array and finds the previous call's contents in it.  Nothing needs to start at
+// zero: each pass writes every histogram slot, scan partial, key and index it later reads (rs_hist_kernel stores all
+// 256 x nblk counters of a row; the scatter of pass p writes the buffers pass p + 1 reads).  Calls that overlap on
+// the GPU (different streams, or graph branches that run concurrently) RACE on the array: serialise them.
+// ---------------------------------------------------------------------------------------------------------------
+namespace ptv3 {
+constexpr size_t kArgsortStaticBytes = (size_t)PTV3_ARGSORT_STATIC_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_argsort_static_scratch[kArgsortStaticBytes];
+
+constexpr int kMaxStaticDevices = 64;
+static void* g_argsort_static_ptr[kMaxStaticDevices] = {};
+static std::mutex g_argsort_static_mutex;
+
+// Device address of the scratch array on the CURRENT device (resolved at the first call on that device).
+static int argsort_static_scratch_ptr(void** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxStaticDevices) return PTV3_ELAUNCH;
+  std::lock_guard<std::mutex> lock(g_argsort_static_mutex);
+  if (g_argsort_static_ptr[dev] == nullptr) {
+    void* ptr = nullptr;
+    if (cudaGetSymbolAddress((void**)&ptr, g_argsort_static_scratch) != cudaSuccess || ptr == nullptr) {
+      cudaGetLastError();   // leave no sticky error behind
+      return PTV3_ELAUNCH;
+    }
+    g_argsort_static_ptr[dev] = ptr;
+  }
+  *out = g_argsort_static_ptr[dev];
+  return PTV3_OK;
+}
+}  // namespace ptv3
+
+extern "C" {
+
+int64_t ptv3_argsort_rows_static_max_elems(void) { return (int64_t)PTV3_ARGSORT_STATIC_MAX_ELEMS; }
+
+int ptv3_argsort_rows_static(const int64_t* code, int64_t rows, int64_t n, int key_bits, int64_t* order,
+                             int64_t* inverse, void* stream) {
+  if (rows < 0 || n < 0) return PTV3_EINVAL;
+  if (rows == 0 || n == 0) return PTV3_OK;
+  if (!order || !code) return PTV3_EINVAL;
+  // the stated limit first (a clear error, independent of how the scratch is laid out), then the exact byte check
+  if (rows > PTV3_ARGSORT_STATIC_MAX_ELEMS || n > PTV3_ARGSORT_STATIC_MAX_ELEMS ||
+      rows * n > (int64_t)PTV3_ARGSORT_STATIC_MAX_ELEMS)
+    return PTV3_ETOOLARGE;
+  if (radix_argsort_workspace(rows, n) > kArgsortStaticBytes) return PTV3_ETOOLARGE;
+  void* scratch = nullptr;
+  int rc = argsort_static_scratch_ptr(&scratch);
+  if (rc != PTV3_OK) return rc;
+  return radix_argsort_rows((const uint64_t*)code, rows, n, key_bits, order, inverse, nullptr, scratch,
+                            kArgsortStaticBytes, as_stream(stream));
 }
 
 }  // extern "C"
