@@ -346,7 +346,8 @@ int attn_window_bwd_tc(const __nv_bfloat16* qkv, const __nv_bfloat16* out, const
   int kpad = (int)(cdiv(max_len, 64) * 64);
   size_t smem = (size_t)kpad * 128 + (size_t)kpad * 12;
   if (smem > 220 * 1024) return PTV3_EUNSUPPORTED;
-  static size_t configured = 0;
+  static size_t configured_dev[kMaxDeviceSlots] = {};
+  size_t& configured = configured_dev[device_slot()];
   if (smem > configured) {
     if (cudaFuncSetAttribute(attn_bwd_mma_kernel<8, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
             cudaSuccess ||

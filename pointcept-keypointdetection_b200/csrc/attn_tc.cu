@@ -236,7 +236,8 @@ int attn_window_tc(const __nv_bfloat16* qkv, const int64_t* order, const int64_t
   int kpad = (int)(cdiv(max_len, kChunk) * kChunk);
   size_t smem = (size_t)kpad * kD * 2 * 2 + (size_t)kpad * 4;
   if (smem > 200 * 1024) return PTV3_EUNSUPPORTED;  // patch > 3200
-  static size_t configured = 0;
+  static size_t configured_dev[kMaxDeviceSlots] = {};
+  size_t& configured = configured_dev[device_slot()];
   if (smem > configured) {
     if (cudaFuncSetAttribute(attn_window_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
             cudaSuccess ||

@@ -285,7 +285,8 @@ int attn_window_tc05(const __nv_bfloat16* qkv, const int64_t* order, const int64
                      const int64_t* n_windows, int64_t n_windows_max, int64_t max_len, int h, float scale,
                      __nv_bfloat16* out, cudaStream_t st) {
   if (max_len > a5::MAXKC * a5::KC) return PTV3_EUNSUPPORTED;
-  static bool configured = false;
+  static bool configured_dev[kMaxDeviceSlots] = {};
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     if (cudaFuncSetAttribute(attn_window_tc05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, a5::SMEM_BYTES) !=
         cudaSuccess)

@@ -11,6 +11,13 @@ namespace ptv3 {
 
 extern int64_t g_launch_count;  // host-side count of kernel launches (abi.cu)
 
+// Index of the current device for per-device one-time set-up flags (cudaFuncSetAttribute applies to the current device only).
+constexpr int kMaxDeviceSlots = 64;
+inline int device_slot() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < kMaxDeviceSlots ? dev : 0;
+}
 int* device_error_flag();   // abi.cu: device address of the sticky error word (bit mask, see ptv3_device_error)
 
 inline int check_launch(int n_kernels = 1) {

@@ -324,7 +324,8 @@ static int launch_mlp(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const fl
                       __nv_bfloat16* out_bf16, cudaStream_t st) {
   using L = mlp::Smem<C>;
   static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
-  static bool configured = false;
+  static bool configured_dev[kMaxDeviceSlots] = {};
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     cudaFuncSetAttribute(mlp_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::DYN_BYTES);
     configured = true;

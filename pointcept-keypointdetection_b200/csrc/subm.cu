@@ -443,7 +443,8 @@ int ptv3_subm_stem_fused(const int32_t* indices, int64_t n, int ksize, const flo
   cudaMemsetAsync(vals, 0x7f, (size_t)cap * 4, st);
   subm_insert_kernel<<<grid_for(n, 256), 256, 0, st>>>(indices, n, keys, vals, cap - 1, device_error_flag());
   const size_t smem = (size_t)k3 * 32 * sizeof(float4);
-  static bool configured = false;
+  static bool configured_dev[kMaxDeviceSlots] = {};
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     if (cudaFuncSetAttribute(subm_stem_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 125 * 32 * 16) !=
         cudaSuccess)

@@ -366,7 +366,8 @@ static int launch_conv(const __nv_bfloat16* in, const __nv_bfloat16* packed, con
   using L = ConvSmem<NT, STAGES>;
   static_assert(STAGES <= 8, "ring");
   static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
-  static bool configured = false;
+  static bool configured_dev[kMaxDeviceSlots] = {};
+  bool& configured = configured_dev[device_slot()];
   if (!configured) {
     if (const char* e = getenv("PTV3_CONV_ASYNC")) g_conv_async = atoi(e);
     cudaFuncSetAttribute(subm_conv_tc_kernel<NT, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,

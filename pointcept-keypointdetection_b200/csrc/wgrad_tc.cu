@@ -191,7 +191,8 @@ int subm_wgrad_fast(const void* in, const void* dout, const int32_t* nbr, int64_
     dim3 grid((unsigned)k3, (unsigned)chunks, (unsigned)tiles);
     const size_t smem = (size_t)kWgRows * 8 + (size_t)4 * kWgGroup * (T * 2 + 16);
     if (T == 64) {
-      static bool configured = false;
+      static bool configured_dev[kMaxDeviceSlots] = {};
+      bool& configured = configured_dev[device_slot()];
       if (!configured) {
         if (cudaFuncSetAttribute(subm_wgrad_mma_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
             cudaSuccess)
@@ -209,7 +210,8 @@ int subm_wgrad_fast(const void* in, const void* dout, const int32_t* nbr, int64_
   if (dtype == PTV3_F32 && c_out == 32 && c_in <= 8) {
     const size_t smem = (size_t)k3 * c_in * 32 * 4;
     if (smem > 200 * 1024) return PTV3_EUNSUPPORTED;
-    static size_t configured = 0;
+    static size_t configured_dev2[kMaxDeviceSlots] = {};
+    size_t& configured = configured_dev2[device_slot()];
     if (smem > configured) {
       if (cudaFuncSetAttribute(subm_wgrad_stem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) !=
           cudaSuccess)

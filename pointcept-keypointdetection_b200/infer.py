@@ -24,7 +24,6 @@ def collate(scenes):
     for s in scenes:
         rows = next(s[k] for k in ("coord", "grid_coord", "feat") if k in s)
         counts.append(int(rows.shape[0]))
-    n_set = set(counts)
     for k in scenes[0]:
         v0 = scenes[0][k]
         if k == "offset":
@@ -36,7 +35,6 @@ def collate(scenes):
             out[k] = v0
     dev = next(v.device for v in out.values() if torch.is_tensor(v))
     out["offset"] = torch.cumsum(torch.tensor(counts, dtype=torch.int64), 0).to(dev)
-    del n_set
     return out
 
 

@@ -869,8 +869,13 @@ class OffsetKeypointPTv3(nn.Module):
         finally:
             torch.backends.cuda.matmul.allow_tf32 = prev
         pred = pred.view(-1, self.num_keypoints, 4)
+        out = {}
+        if "target" in data_dict:        # validation: the reference returns the loss next to the prediction (:50-86)
+            from .train import offset_keypoint_loss
+            out["loss"] = offset_keypoint_loss(pred, data_dict["target"])[0]
         pred[..., 3] = torch.sigmoid(pred[..., 3])
-        return dict(pred=pred)
+        out["pred"] = pred
+        return out
 
 
 class KeypointPTv3(nn.Module):

@@ -286,6 +286,16 @@ def backbone_forward(bb, data_dict):
     return point
 
 
+def offset_keypoint_loss(pred, target):
+    """offset_keypoint_ptv3.py:50-86 on (N, K, 4) LOGITS: BCE-with-logits on the mask channel of every point + 2 x L1 on
+    the offsets of the points whose target mask is set.  Returns (loss, cls_loss, reg_loss)."""
+    offset_gt, mask_gt = target[..., :3], target[..., 3]
+    cls_loss = F.binary_cross_entropy_with_logits(pred[..., 3], mask_gt, reduction="none").mean()
+    valid = (mask_gt > 0.5).float().unsqueeze(-1)
+    reg_loss = (F.l1_loss(pred[..., :3], offset_gt, reduction="none") * valid).sum() / (valid.sum() * 3 + 1e-6)
+    return cls_loss + reg_loss * 2.0, cls_loss, reg_loss
+
+
 def offset_keypoint_forward(model, data_dict):
     """offset_keypoint_ptv3.py:37-107: per-point (dx,dy,dz,mask logit); BCE on every point + L1 on the points whose
     target mask is set (weight 2)."""
@@ -293,12 +303,7 @@ def offset_keypoint_forward(model, data_dict):
     pred = model.head(point.feat.float()).view(-1, model.num_keypoints, 4)
     out = {}
     if "target" in data_dict:
-        target = data_dict["target"]
-        offset_gt, mask_gt = target[..., :3], target[..., 3]
-        cls_loss = F.binary_cross_entropy_with_logits(pred[..., 3], mask_gt, reduction="none").mean()
-        valid = (mask_gt > 0.5).float().unsqueeze(-1)
-        reg_loss = (F.l1_loss(pred[..., :3], offset_gt, reduction="none") * valid).sum() / (valid.sum() * 3 + 1e-6)
-        out["loss"] = cls_loss + reg_loss * 2.0
+        out["loss"], cls_loss, reg_loss = offset_keypoint_loss(pred, data_dict["target"])
         out["train/cls_loss"] = cls_loss.detach()
         out["train/reg_loss"] = reg_loss.detach()
     if not model.training:

@@ -7,6 +7,7 @@ import numpy as np
 import pytest
 import torch
 
+from oracle import ops as O
 from oracle import spunet as U
 
 pytestmark = pytest.mark.gpu
@@ -70,7 +71,8 @@ def test_strided_and_inverse_conv_vs_oracle(golden):
 @pytest.mark.parametrize("cin,cout,k3", [(192, 128, 27), (384, 256, 27), (256, 128, 8), (320, 64, 8)])
 def test_tc_conv_channel_counts_of_the_decoder(golden, cin, cout, k3):
     """The tcgen05 conv with 3 / 5 / 6 K-blocks per kernel offset (concatenated skip channels) and 8-column pair
-    tables, against the CUDA-core kernel on the same bf16 operands."""
+    tables, against the CPU oracle (fp32 math on the same bf16-rounded operands; only the bf16 rounding of the output
+    differs) and, as a cross-check, the CUDA-core kernel."""
     from ptv3_b200 import ops
     g = golden("spunet")
     _, idx = _batch_indices(g)
@@ -84,8 +86,10 @@ def test_tc_conv_channel_counts_of_the_decoder(golden, cin, cout, k3):
     b = torch.randn(cout, generator=gen).cuda()
     assert ops.subm_conv_tc_supported(cin, cout, k3)
     got = ops.subm_conv_packed(x, ops.subm_pack_weight(w), b, nbr, cout)
-    ref = ops.subm_conv(x, w, b, nbr, algo=1)
+    wo = w.float().cpu().permute(1, 0, 2).reshape(cout, k3, 1, 1, cin)          # oracle layout (out, k..., in)
+    ref = O.subm_conv(x.float().cpu(), nbr.cpu().long(), wo, b.cpu())
     assert rel_l2(got, ref) < 4e-3
+    assert rel_l2(ops.subm_conv(x, w, b, nbr, algo=1), ref) < 4e-3
 
 
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])

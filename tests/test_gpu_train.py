@@ -432,3 +432,24 @@ def test_training_other_heads_vs_oracle(golden):
     params = dict(m.named_parameters())
     for k in ("seg_head.weight", "backbone.embedding.stem.conv.weight", "backbone.enc.enc3.block2.mlp.0.fc1.weight"):
         assert rel_l2(params[k].grad, ref[k]) < 1e-3, k
+
+
+def test_eval_returns_loss_when_target_is_present(golden):
+    """Validation batches carry `target`: the reference returns the loss next to the sigmoid prediction in eval() mode
+    (offset_keypoint_ptv3.py:50-105).  Checked against the oracle's loss on the oracle's features."""
+    from make_golden_names import make_target
+    g = golden("forward")
+    c, f, gc, perms = g["coord_0"], g["feat_0"], g["grid_coord_0"], g["perms_0"]
+    W = _weights()
+    target = torch.from_numpy(make_target(len(c), 11))
+    pt = P.backbone_forward(W, c, gc, f, [len(c)], perms=list(perms))
+    ref = P.offset_keypoint_loss(W, pt.feat, target)
+    m = _train_model(torch.float32).eval()
+    torch.manual_seed(100)
+    out = m(dict(coord=torch.from_numpy(c).cuda(), grid_coord=torch.from_numpy(gc).cuda(), feat=torch.from_numpy(f).cuda(),
+                 offset=torch.tensor([len(c)]).cuda(), target=target.cuda()))
+    assert abs(out["loss"].item() - ref.item()) <= 1e-5 * max(1.0, abs(ref.item()))
+    assert rel_l2(out["pred"], torch.from_numpy(g["pred_0"])) < 1e-4
+    out2 = m(dict(coord=torch.from_numpy(c).cuda(), grid_coord=torch.from_numpy(gc).cuda(), feat=torch.from_numpy(f).cuda(),
+                  offset=torch.tensor([len(c)]).cuda()))
+    assert "loss" not in out2
