@@ -227,6 +227,17 @@ int ptv3_subm_stem_fused(const int32_t* indices, int64_t n, int ksize, const flo
                          const float* bias, int act, float* out32, void* out16, void* workspace, size_t workspace_bytes,
                          void* stream);
 
+/* The same result (bit-identical) with a block-occupancy neighbour search instead of 125 hash probes per voxel.  Uses
+ * what Point.serialization() (structure.py:52-109) has already computed: code_z (n) = the "z" codes of the rows
+ * (batch << 3*depth | Morton), order_z (n) = their argsort, depth = the serialization depth (>= 2).  Every 4x4x4 block
+ * of cells is one run of the sorted order; a 5^3 window touches at most 8 blocks, so a row costs 8 hash probes of
+ * (block -> run start, 64-bit occupancy mask) + one 4-byte load per PRESENT neighbour.  Sites must be unique (bit 8 of
+ * ptv3_device_error() otherwise).  workspace: ptv3_subm_stem_z_workspace(n). */
+size_t ptv3_subm_stem_z_workspace(int64_t n);
+int ptv3_subm_stem_fused_z(const int32_t* indices, int64_t n, int ksize, const int64_t* code_z, const int64_t* order_z,
+                           int depth, const float* in, const float* weight, const float* bias, int act, float* out32,
+                           void* out16, void* workspace, size_t workspace_bytes, void* stream);
+
 /* bf16 tensor-core path with the weight packed once (eval: weights are constants).  `packed` is the
  * shared-memory image of the K-blocked, 128-byte-swizzled weight (ptv3_subm_pack_weight_bytes() bytes, 1024-byte
  * aligned); supported shapes: c_in == 32 or a multiple of 64 (<= 512), c_out in {32,64,128,256,512}, k3 <= 27. */
@@ -321,6 +332,7 @@ int ptv3_debug_set(int key, int value);
 /* Reads AND clears the library's sticky device-side error word, a bit mask (0 = none): 1 = an attention window record
  * violated the ptv3_build_windows contract (its CTA wrote nothing); 2 = a sparse-conv site lies outside the packed
  * key range (batch id >= 1024 or a coordinate outside [0, 262128)) and was left out of the neighbour map.
+ * 4 = ptv3_grid_pool saw a coordinate outside [0, 2^bits * stride); 8 = ptv3_subm_stem_fused_z found duplicate sites.
  * Synchronises the device (one 4-byte copy): meant for tests and for shims that forward caller-built inputs. */
 int ptv3_device_error(void);
 

@@ -355,6 +355,155 @@ __global__ void __launch_bounds__(512, 2) subm_stem_fused_kernel(const float* __
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Stem with a BLOCK-OCCUPANCY neighbour search (round 2).  subm_stem_fused_kernel spends its time on 125 random hash
+// probes per voxel (one 32-byte sector each: ~5 KB of L2 -> L1 traffic per row).  The z-order serialization that
+// Point.serialization() has already computed groups every 4 x 4 x 4 block of cells into one contiguous run of the
+// sorted order (code >> 6 is the block, code & 63 the Morton cell inside it), so:
+//   stem_blocks_kernel   one pass over the sorted codes: per run head -> hash insert of (block key -> run start, 64-bit
+//                        occupancy mask); also writes the sorted rows as int32
+//   subm_stem_z_kernel   a 5^3 window touches at most 2 x 2 x 2 blocks: lanes 0-7 probe one block each (8 probes per
+//                        row instead of 125); a neighbour cell is present iff its mask bit is set and its row is
+//                        rows_sorted[start + popcount(mask below the cell)] -- one dependent 4-byte load, only for
+//                        the ~16 present neighbours.  Same walking order of the present offsets as the kernel above:
+//                        bit-identical sums.
+// Requires unique sites (GridSample / pooling guarantee it; a block whose run holds the same cell twice sets bit 8 of
+// the device error word) and depth >= 2.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) stem_blocks_kernel(const int64_t* __restrict__ code, const int64_t* __restrict__ order,
+                                                          int64_t n, unsigned long long* __restrict__ keys,
+                                                          uint4* __restrict__ payload, uint32_t mask,
+                                                          int32_t* __restrict__ rows_sorted, int* __restrict__ err) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = order[j];
+    rows_sorted[j] = (int32_t)row;
+    const uint64_t c = (uint64_t)code[row];
+    const uint64_t kb = c >> 6;
+    if (j > 0 && ((uint64_t)code[order[j - 1]] >> 6) == kb) continue;      // not a run head
+    uint64_t m = 1ull << (c & 63);
+    int cnt = 1;
+    for (int64_t t = j + 1; t < n; ++t) {
+      const uint64_t ct = (uint64_t)code[order[t]];
+      if ((ct >> 6) != kb) break;
+      m |= 1ull << (ct & 63);
+      ++cnt;
+    }
+    if (cnt != __popcll(m) && err) atomicOr(err, 8);                        // duplicate sites: ranks would be wrong
+    uint32_t slot = hash_site(kb) & mask;
+    while (true) {
+      const unsigned long long prev = atomicCAS(&keys[slot], (unsigned long long)kEmptyKey, (unsigned long long)kb);
+      if (prev == kEmptyKey) break;      // block keys are unique among run heads (the codes are sorted)
+      slot = (slot + 1) & mask;
+    }
+    payload[slot] = make_uint4((uint32_t)m, (uint32_t)(m >> 32), (uint32_t)j, (uint32_t)cnt);
+  }
+}
+
+__device__ __forceinline__ uint64_t spread3_u64(uint64_t v) {
+  v &= 0xffffull;
+  v = (v | (v << 32)) & 0x001f00000000ffffull;
+  v = (v | (v << 16)) & 0x001f0000ff0000ffull;
+  v = (v | (v << 8)) & 0x100f00f00f00f00full;
+  v = (v | (v << 4)) & 0x10c30c30c30c30c3ull;
+  v = (v | (v << 2)) & 0x1249249249249249ull;
+  return v;
+}
+
+__global__ void __launch_bounds__(512, 2) subm_stem_z_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                                          const float* __restrict__ bias,
+                                                          const int32_t* __restrict__ indices,
+                                                          const unsigned long long* __restrict__ keys,
+                                                          const uint4* __restrict__ payload, uint32_t mask,
+                                                          const int32_t* __restrict__ rows_sorted, int depth, int64_t n,
+                                                          int ksize, int act, float* __restrict__ out32,
+                                                          __nv_bfloat16* __restrict__ out16) {
+  extern __shared__ float4 ws4[];  // [k3][32] weights, then [warps][128] gathered input rows of the row in flight
+  const int k3 = ksize * ksize * ksize, r = ksize / 2;
+  float4* xs = ws4 + k3 * 32 + (threadIdx.x >> 5) * 128;
+  for (int idx = threadIdx.x; idx < k3 * 32; idx += blockDim.x) {
+    const int co = idx & 31, k = idx >> 5;
+    const float* p = w + ((int64_t)k * 32 + co) * 4;
+    ws4[idx] = make_float4(p[0], p[1], p[2], p[3]);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int64_t stride = (int64_t)gridDim.x * (blockDim.x >> 5);
+  const float b = bias ? bias[lane] : 0.f;
+  const int nblk_axis = 1 << (depth - 2);          // blocks per axis
+  const int bshift = 3 * depth - 6;                // batch id sits above the block Morton code
+  int dxs[4], dys[4], dzs[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int k = q * 32 + lane;
+    dzs[q] = k % ksize - r;
+    dys[q] = (k / ksize) % ksize - r;
+    dxs[q] = k / (ksize * ksize) - r;
+  }
+  for (; row < n; row += stride) {
+    const int4 s = reinterpret_cast<const int4*>(indices)[row];
+    const int bx0 = (s.y - r) >> 2, by0 = (s.z - r) >> 2, bz0 = (s.w - r) >> 2;      // arithmetic shifts: -1 below the grid
+    // lanes 0-7: one candidate block each
+    uint32_t m_lo = 0, m_hi = 0, start = 0;
+    if (lane < 8) {
+      const int bx = (lane & 4) ? (s.y + r) >> 2 : bx0, by = (lane & 2) ? (s.z + r) >> 2 : by0,
+                bz = (lane & 1) ? (s.w + r) >> 2 : bz0;
+      if (bx >= 0 && by >= 0 && bz >= 0 && bx < nblk_axis && by < nblk_axis && bz < nblk_axis) {
+        const uint64_t kb = ((uint64_t)(uint32_t)s.x << bshift) | (spread3_u64((uint32_t)bx) << 2) |
+                            (spread3_u64((uint32_t)by) << 1) | spread3_u64((uint32_t)bz);
+        uint32_t slot = hash_site(kb) & mask;
+        unsigned long long cur = keys[slot];
+        while (cur != kb && cur != kEmptyKey) {
+          slot = (slot + 1) & mask;
+          cur = keys[slot];
+        }
+        if (cur == kb) {
+          const uint4 pl = payload[slot];
+          m_lo = pl.x; m_hi = pl.y; start = pl.z;
+        }
+      }
+    }
+    int mine[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int x = s.y + dxs[q], y = s.z + dys[q], z = s.w + dzs[q];
+      const int sel = (((x >> 2) != bx0) ? 4 : 0) | (((y >> 2) != by0) ? 2 : 0) | (((z >> 2) != bz0) ? 1 : 0);
+      const uint32_t lo = __shfl_sync(0xffffffffu, m_lo, sel), hi = __shfl_sync(0xffffffffu, m_hi, sel);
+      const uint32_t st = __shfl_sync(0xffffffffu, start, sel);
+      const uint64_t m = ((uint64_t)hi << 32) | lo;
+      const int cell = ((x & 2) << 4) | ((y & 2) << 3) | ((z & 2) << 2) | ((x & 1) << 2) | ((y & 1) << 1) | (z & 1);
+      const bool present = q * 32 + lane < k3 && ((m >> cell) & 1ull);
+      mine[q] = present ? rows_sorted[st + __popcll(m & ((1ull << cell) - 1ull))] : -1;
+    }
+    // the gathered input rows go through shared memory: one broadcast 16-byte load per present neighbour instead of
+    // four shuffles (the walk below was shuffle-issue bound)
+    __syncwarp();
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (mine[q] >= 0) xs[q * 32 + lane] = *reinterpret_cast<const float4*>(in + (int64_t)mine[q] * 4);
+    __syncwarp();
+    float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t present = __ballot_sync(0xffffffffu, mine[q] >= 0);
+      while (present) {
+        const int j = __ffs(present) - 1;
+        present &= present - 1;
+        const float4 wv = ws4[(q * 32 + j) * 32 + lane];
+        const float4 xv = xs[q * 32 + j];
+        acc0 = fmaf(xv.x, wv.x, acc0);
+        acc1 = fmaf(xv.y, wv.y, acc1);
+        acc0 = fmaf(xv.z, wv.z, acc0);
+        acc1 = fmaf(xv.w, wv.w, acc1);
+      }
+    }
+    float y = acc0 + acc1 + b;
+    if (act == 1) y = 0.5f * y * (1.f + erff(y * 0.70710678118654752f));
+    if (out32) out32[row * 32 + lane] = y;
+    if (out16) out16[row * 32 + lane] = __float2bfloat16_rn(y);
+  }
+}
+
 template <typename T>
 static int conv_cuda_core(const T* in, const T* w, const float* bias, const int32_t* nbr, int64_t n, int cin, int cout,
                           int k3, T* out, cudaStream_t st) {
@@ -455,6 +604,45 @@ int ptv3_subm_stem_fused(const int32_t* indices, int64_t n, int ksize, const flo
   if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
   subm_stem_fused_kernel<<<(unsigned)blocks, 512, smem, st>>>(in, weight, bias, indices, keys, vals, cap - 1, n, ksize,
                                                                act, out32, (__nv_bfloat16*)out16);
+  return check_launch(2);
+}
+
+size_t ptv3_subm_stem_z_workspace(int64_t n) {
+  uint32_t cap = table_capacity(n > 0 ? n : 1);
+  return align_up((size_t)cap * 8) + align_up((size_t)cap * 16) + align_up((size_t)(n > 0 ? n : 1) * 4) + 1024;
+}
+
+int ptv3_subm_stem_fused_z(const int32_t* indices, int64_t n, int ksize, const int64_t* code_z, const int64_t* order_z,
+                           int depth, const float* in, const float* weight, const float* bias, int act, float* out32,
+                           void* out16, void* workspace, size_t workspace_bytes, void* stream) {
+  if (n < 0 || ksize < 1 || ksize > 5 || (ksize & 1) == 0 || act < 0 || act > 1 || depth < 2 || depth > 16)
+    return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!indices || !in || !weight || !code_z || !order_z || (!out32 && !out16) || n >= (1ll << 30)) return PTV3_EINVAL;
+  const int k3 = ksize * ksize * ksize;
+  uint32_t cap = table_capacity(n);
+  Workspace ws(workspace, workspace_bytes);
+  unsigned long long* keys = ws.take<unsigned long long>(cap);
+  uint4* payload = ws.take<uint4>(cap);
+  int32_t* rows_sorted = ws.take<int32_t>((size_t)n);
+  if (!ws.ok()) return PTV3_EWORKSPACE;
+  cudaStream_t st = as_stream(stream);
+  cudaMemsetAsync(keys, 0xff, (size_t)cap * 8, st);
+  stem_blocks_kernel<<<grid_for(n, 256), 256, 0, st>>>(code_z, order_z, n, keys, payload, cap - 1, rows_sorted,
+                                                       device_error_flag());
+  const size_t smem = (size_t)k3 * 32 * sizeof(float4);
+  static bool configured_dev[kMaxDeviceSlots] = {};
+  bool& configured = configured_dev[device_slot()];
+  if (!configured) {
+    if (cudaFuncSetAttribute(subm_stem_z_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (125 * 32 + 16 * 128) * 16) != cudaSuccess)
+      return PTV3_ELAUNCH;
+    configured = true;
+  }
+  int64_t blocks = cdiv(n, 16);
+  if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
+  subm_stem_z_kernel<<<(unsigned)blocks, 512, smem + 16 * 128 * sizeof(float4), st>>>(in, weight, bias, indices, keys, payload, cap - 1, rows_sorted,
+                                                          depth, n, ksize, act, out32, (__nv_bfloat16*)out16);
   return check_launch(2);
 }
 

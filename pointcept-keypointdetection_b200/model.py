@@ -641,6 +641,7 @@ class Embedding(PointModule):
             self.stem.add(act_layer(), name="act")
         self.compute_dtype = torch.bfloat16
         self.fuse_lookup = True        # A/B switch for the fused stem kernel (tests compare both paths)
+        self.block_search = True       # A/B switch: block-occupancy neighbour search over the z-order serialization
 
     @torch.no_grad()
     def forward(self, point):
@@ -657,8 +658,13 @@ class Embedding(PointModule):
             s, t = (None, None) if bn is None else _cached(
                 self, "bn", [bn.weight, bn.bias, bn.running_mean, bn.running_var], lambda: _bn_scale_shift(bn))
             w, b = conv._weights(torch.float32, s, t)
+            z = None
+            zr = point.get("_z_row") if self.block_search else None
+            if zr is not None and "serialized_code" in point and point.serialized_code.shape[1] == feat_in.shape[0]:
+                # the z-order serialization is already there: 4^3-block occupancy search instead of 125 hash probes
+                z = (point.serialized_code[zr], point.serialized_order[zr], int(point.serialized_depth))
             y, ycd = ops.subm_stem_fused(sp.indices, feat_in, w, b, conv.kernel_size, gelu=gelu, want_f32=True,
-                                         want_bf16=cd == torch.bfloat16)
+                                         want_bf16=cd == torch.bfloat16, z=z)
             point.feat = y
             point["_feat_cd"] = ycd if ycd is not None else y
             point.sparse_conv_feat = sp.replace_feature(point["_feat_cd"])

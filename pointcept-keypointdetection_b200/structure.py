@@ -116,11 +116,15 @@ class Point(dict):
         code = ops.encode_orders(self.grid_coord, self.batch, depth, order)
         key_bits = depth * 3 + max(1, (len(self.offset) - 1).bit_length())
         order_, inverse = ops.argsort_rows(code, key_bits=key_bits)
+        z_row = order.index("z") if "z" in order else None       # row of the plain Morton codes (stem block search)
         if shuffle_orders:
             perm = torch.randperm(code.shape[0])
+            if z_row is not None:
+                z_row = perm.tolist().index(z_row)
             if not torch.equal(perm, torch.arange(code.shape[0])):
                 perm = device_perm(perm, code.device)
                 code, order_, inverse = code[perm], order_[perm], inverse[perm]
+        self["_z_row"] = z_row
         self["serialized_code"] = code
         self["serialized_order"] = order_
         self["serialized_inverse"] = inverse

@@ -597,8 +597,10 @@ def test_serving_paths_on_device(golden):
 
 
 def test_fused_stem_equals_table_path():
-    """Embedding with the neighbour search fused into the stem conv (no (N,125) table) against the table path:
-    same present offsets in the same order, so the fp32 outputs are bit-identical; plus the oracle."""
+    """Embedding with the neighbour search fused into the stem conv (no (N,125) table) -- by block-occupancy search over
+    the z-order serialization (8 probes per row) and by 125 hash probes per row -- against the table path: same present
+    offsets in the same order, so the fp32 outputs are bit-identical; plus the oracle."""
+    from ptv3_b200 import ops
     m = _model(torch.bfloat16)
     emb = m.backbone.embedding
     from ptv3_b200.structure import Point
@@ -606,15 +608,20 @@ def test_fused_stem_equals_table_path():
     cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
     offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
     outs = []
-    for fuse in (True, False):
-        emb.fuse_lookup = fuse
+    torch.manual_seed(5)
+    for fuse, block, order, shuffle in ((True, True, ["hilbert", "z-trans", "z", "hilbert-trans"], True),
+                                        (True, True, "z", False), (True, False, "z", False), (False, False, "z", False)):
+        emb.fuse_lookup, emb.block_search = fuse, block
         p = Point(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset)
-        p.serialization(order="z")
+        p.serialization(order=order, shuffle_orders=shuffle)
+        assert p["_z_row"] is not None
         p.sparsify()
         p = emb(p)
         outs.append((p.feat.clone(), p["_feat_cd"].clone()))
-    emb.fuse_lookup = True
-    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    emb.fuse_lookup = emb.block_search = True
+    assert ops.device_error() == 0
+    for o in outs[1:]:
+        assert torch.equal(outs[0][0], o[0]) and torch.equal(outs[0][1], o[1])
     assert outs[0][1].dtype == torch.bfloat16 and outs[0][0].dtype == torch.float32
     W = {k[len("backbone."):]: v for k, v in _weights().items() if k.startswith("backbone.")}
     idx = torch.cat([torch.repeat_interleave(torch.arange(2), torch.tensor([len(s[0]) for s in scenes]))[:, None],
