@@ -293,6 +293,17 @@ int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const 
 int ptv3_mlp_fused_rs(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
                       const float* residual, const float* row_scale, int64_t n, int c, int hidden, float* res_out,
                       void* out_bf16, void* stream);
+/* The second half of Block.forward (:329-337) in one tcgen05 kernel (c in {32, 64}, hidden = 4c, bf16 operands):
+ *   x2 = x1 + rs_attn * (a Wproj^T + bproj);  h = LayerNorm(x2; ln_gamma, ln_beta, eps);
+ *   res_out = x2 + rs_mlp * (GELU_erf(h W1^T + b1) W2^T + b2);  out_bf16 = bf16(res_out) (optional)
+ * a (n,c) bf16 = attention output, x1 (n,c) fp32 = residual stream after the xCPE branch, rs_* fp32 (n) DropPath row
+ * scales or NULL; wproj_packed = ptv3_pack_kmajor of (c,c) with tile_rows = c, bproj / LayerNorm parameters fp32.
+ * res_out (n,c) fp32 is required and must not alias x1 (x2 is parked in it between the two epilogues). */
+int ptv3_proj_mlp_fused(const void* a, const void* wproj_packed, const float* bproj, const float* x1,
+                        const float* rs_attn, const float* ln_gamma, const float* ln_beta, float eps,
+                        const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
+                        const float* rs_mlp, int64_t n, int c, int hidden, float* res_out, void* out_bf16,
+                        void* stream);
 
 /* ---------------------------------------------------------------------------
  * A8  one call per Block (inference, bf16 operands): the whole launch chain of Block.forward
@@ -319,6 +330,11 @@ typedef struct ptv3_block_params {
   /* DropPath of the two residual branches for THIS call (timm DropPath in train() mode, :329-335): fp32 (n) row scales,
    * 0 or 1 / keep_prob; NULL = none (eval).  Used by a frozen backbone inside a training step. */
   const float *drop_attn, *drop_mlp;
+  /* with mlp_fused = 1: ptv3_pack_kmajor image of the (c,c) projection weight (tile_rows = c) and its fp32 bias; when both
+   * are set, proj + shortcut + LayerNorm + MLP + shortcut run as ONE kernel (ptv3_proj_mlp_fused).  NULL = separate
+   * launches (cuBLASLt proj, ptv3_ln_residual, ptv3_mlp_fused). */
+  const void* proj_w_packed;
+  const float* proj_b_f32;
 } ptv3_block_params;
 size_t ptv3_block_workspace(const ptv3_block_params* p, int64_t n, int64_t n_windows_max);
 int ptv3_block_fwd(const ptv3_block_params* p, const float* x, const void* conv_in, const int32_t* nbr,

@@ -20,7 +20,7 @@ class BlockParams(ctypes.Structure):
                [(k, ctypes.c_void_p) for k in ("conv_w_packed", "conv_bias", "cpe_lin_w", "cpe_lin_b", "cpe_ln_g",
                                                "cpe_ln_b", "norm1_g", "norm1_b", "norm2_g", "norm2_b", "qkv_w", "qkv_b",
                                                "proj_w", "proj_b", "fc1_w", "fc1_b", "fc2_w", "fc2_b", "drop_attn",
-                                               "drop_mlp")]
+                                               "drop_mlp", "proj_w_packed", "proj_b_f32")]
 
 
 # name -> (restype, argtypes); order mirrors include/ptv3_b200.h
@@ -73,6 +73,8 @@ SIGNATURES = {
     "ptv3_mlp_fused_supported": (c_int, [c_int, c_int]),
     "ptv3_mlp_fused": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
     "ptv3_mlp_fused_rs": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
+    "ptv3_proj_mlp_fused": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64,
+                                    c_int, c_int, c_vp, c_vp, c_vp]),
     "ptv3_block_workspace": (c_sz, [ctypes.POINTER(BlockParams), c_i64, c_i64]),
     "ptv3_block_fwd": (c_int, [ctypes.POINTER(BlockParams), c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i64, c_vp, c_vp,
                                c_vp, c_sz, c_vp]),

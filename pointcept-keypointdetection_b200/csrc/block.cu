@@ -199,6 +199,14 @@ int ptv3_block_fwd(const ptv3_block_params* p, const float* x, const void* conv_
   PTV3_TRY(linear_bf16(h, p->qkv_w, p->qkv_b, qkv, n, c, 3 * c, lt_ws, st));
   PTV3_TRY(ptv3_attn_window_fwd(qkv, PTV3_BF16, order, windows, n_windows, n_windows_max, p->patch, n, p->heads, 16,
                                 p->scale, p->attn_algo, a, attn_ws, attn_ws_bytes, stream));
+  if (p->mlp_fused && p->proj_w_packed && p->proj_b_f32) {
+    // proj -> + shortcut -> LayerNorm -> MLP -> + shortcut in ONE kernel (:329-337), C = 32 / 64
+    PTV3_TRY(ptv3_proj_mlp_fused(a, p->proj_w_packed, p->proj_b_f32, x1, p->drop_attn, p->norm2_g, p->norm2_b,
+                                 p->eps_norm2, p->fc1_w, static_cast<const float*>(p->fc1_b), p->fc2_w,
+                                 static_cast<const float*>(p->fc2_b), p->drop_mlp, n, c, p->hidden, x_out, x_out_bf16,
+                                 stream));
+    return PTV3_OK;
+  }
   PTV3_TRY(linear_bf16(a, p->proj_w, p->proj_b, pr, n, c, c, lt_ws, st));
   PTV3_TRY(ptv3_ln_residual_rs(pr, PTV3_BF16, nullptr, nullptr, p->eps_norm2, p->drop_attn, x1, x2, p->norm2_g,
                                p->norm2_b, h2, PTV3_BF16, n, c, stream));

@@ -316,6 +316,381 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
   if (warp == 2) tmem_dealloc<512>(tmem);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// proj + LayerNorm + MLP (round 2): the second half of Block.forward (:329-337) as ONE kernel for C = 32 / 64
+//   x2 = x1 + rs_a * (a Wp^T + bp)            attention projection + DropPath + shortcut
+//   h  = LayerNorm(x2; g2, be2)                pre-norm of the MLP
+//   out = x2 + rs_m * (GELU(h W1^T + b1) W2^T + b2)
+// = mlp_fused_kernel with one more GEMM in front: the loaders bring the attention output tile `a` (A0), the issuer runs
+// GEMM0 (D0 = A0 . Wp^T, two tiles ahead), and the epilogue warps turn D0 into the A operand of GEMM1 themselves:
+// + bp, x rs_a, + x1 (read from HBM), the row statistics of the 4 column quarters exchanged through shared memory,
+// normalised, bf16 into the swizzled A1 stage.  x2 is parked in `res_out` (same thread writes it, reads it back in
+// epilogue 2 and overwrites it with the final value), so it costs no registers across the tile.
+// Against the separate launches (cuBLASLt proj, ln_residual, mlp_fused) this removes the write + read of proj's
+// output, of x2 and of h: 28 C -> 16 C bytes per row (12 C from HBM: the x2 round trip stays in L2), and two launches.
+// ---------------------------------------------------------------------------------------------------------------
+namespace mlp {
+template <int C>
+struct PSmem {
+  static constexpr int HID = 4 * C;
+  static constexpr int NHB = HID / HB;
+  static constexpr int W1_BYTES = NHB * HB * 128;
+  static constexpr int W2_TILE = C * 128;
+  static constexpr int W2_BYTES = (HID / 64) * W2_TILE;
+  static constexpr int WP_BYTES = C * 128;                   // [C rows][64] one K-block
+  static constexpr int A1_BYTES = TM * 128;
+  static constexpr int A2_BYTES = 2 * TM * 128;
+  static constexpr int W1_OFF = 0;
+  static constexpr int W2_OFF = W1_OFF + W1_BYTES;
+  static constexpr int WP_OFF = W2_OFF + W2_BYTES;
+  static constexpr int A0_OFF = WP_OFF + WP_BYTES;
+  static constexpr int A1_OFF = A0_OFF + 2 * A1_BYTES;
+  static constexpr int A2_OFF = A1_OFF + 2 * A1_BYTES;
+  static constexpr int BIAS_OFF = A2_OFF + 2 * A2_BYTES;      // b1 (HID) | b2 (C) | bp (C) | g2 (C) | be2 (C)
+  static constexpr int STAT_OFF = BIAS_OFF + (HID + 4 * C) * 4;   // [2 parities][128 rows][4 quarters] float2
+  static constexpr int BAR_OFF = STAT_OFF + 2 * TM * 4 * 8;
+  static constexpr int DYN_BYTES = BAR_OFF + 256 + 1024;
+  static constexpr int D2_COL = 256, D0_COL = 256 + 2 * C;    // TMEM columns: D1 2 x 128 | D2 2 x C | D0 2 x C
+};
+__device__ __forceinline__ void epi_sync() { asm volatile("bar.sync 2, %0;" ::"n"(EPI) : "memory"); }
+}  // namespace mlp
+
+template <int C>
+__global__ void __launch_bounds__(mlp::THREADS, 1) proj_mlp_fused_kernel(
+    const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ wpp, const float* __restrict__ bp,
+    const float* __restrict__ x1, const float* __restrict__ rs_attn, const float* __restrict__ g2,
+    const float* __restrict__ be2, float eps, const __nv_bfloat16* __restrict__ w1p, const float* __restrict__ b1,
+    const __nv_bfloat16* __restrict__ w2p, const float* __restrict__ b2, const float* __restrict__ rs_mlp, int64_t n,
+    int n_tiles, float* __restrict__ res_out, __nv_bfloat16* __restrict__ out_bf16) {
+  using namespace mlp;
+  using L = PSmem<C>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t sb = smem_u32(smem);
+  auto bar = [&](int id) { return sb + L::BAR_OFF + 8u * (uint32_t)id; };
+  // 0 w_full | 1,2 a1_full | 3,4 a1_free | 5,6 d1_full | 7,8 d1_free | 9,10 a2_full | 11,12 a2_free | 13,14 d2_full
+  // | 15,16 d2_free | 17,18 a0_full | 19,20 a0_free | 21,22 d0_full | 23,24 d0_free
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::BAR_OFF + 240);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (tid == 0) {
+    mbar_init(bar(0), 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(bar(1 + b), EPI);     mbar_init(bar(3 + b), 1);
+      mbar_init(bar(5 + b), 1);       mbar_init(bar(7 + b), EPI);
+      mbar_init(bar(9 + b), EPI);     mbar_init(bar(11 + b), 1);
+      mbar_init(bar(13 + b), 1);      mbar_init(bar(15 + b), EPI);
+      mbar_init(bar(17 + b), LOADERS); mbar_init(bar(19 + b), 1);
+      mbar_init(bar(21 + b), 1);      mbar_init(bar(23 + b), EPI);
+    }
+    mbar_fence_init();
+  }
+  {
+    float* bs = reinterpret_cast<float*>(smem + L::BIAS_OFF);
+    for (int j = tid; j < L::HID + 4 * C; j += THREADS) {
+      const int k = j - L::HID;
+      bs[j] = j < L::HID ? b1[j] : k < C ? b2[k] : k < 2 * C ? bp[k - C] : k < 3 * C ? g2[k - 2 * C] : be2[k - 3 * C];
+    }
+  }
+  if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 2) {
+    // =========================== loaders: attention output tiles -> A0 ===========================
+    if (tid == 0) {
+      mbar_arrive_expect_tx(bar(0), L::W1_BYTES + L::W2_BYTES + L::WP_BYTES);
+      bulk_g2s(sb + L::W1_OFF, w1p, L::W1_BYTES, bar(0));
+      bulk_g2s(sb + L::W2_OFF, w2p, L::W2_BYTES, bar(0));
+      bulk_g2s(sb + L::WP_OFF, wpp, L::WP_BYTES, bar(0));
+    }
+    if (C == 32) {   // K padded to 64: the upper four 16-byte chunks of every A0 / A1 row stay zero
+      for (int idx = tid; idx < 4 * TM * 4; idx += LOADERS) {
+        const int buf = idx / (TM * 4), r = (idx / 4) % TM, c = 4 + (idx & 3);
+        st_shared_zero16(sb + L::A0_OFF + buf * L::A1_BYTES + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4));
+      }
+    }
+    const int c = tid & 7, r0 = tid >> 3;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int ab = i & 1;
+      const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
+      mbar_wait(bar(19 + ab), ((uint32_t)(i >> 1) & 1u) ^ 1u);
+      if (c < C / 8) {
+        const uint32_t a0 = sb + L::A0_OFF + ab * L::A1_BYTES;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) {
+          const int r = r0 + 8 * q;
+          const uint32_t dst = a0 + (r >> 3) * 1024 + (r & 7) * 128 + ((c ^ (r & 7)) << 4);
+          if (row0 + r < n) cp_async16(dst, a + (row0 + r) * C + c * 8, 16u);
+          else st_shared_zero16(dst);
+        }
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      fence_proxy_async();
+      mbar_arrive(bar(17 + ab));
+    }
+  } else if (warp == 2) {
+    // =========================== MMA issuer ===========================
+    // mlp_fused_kernel's flat schedule (GEMM1 two hidden-block steps ahead of GEMM2) with GEMM0 of tile it + 2 issued
+    // right after the first GEMM1 of tile it: by then the epilogue warps have long consumed D0 of tile it.
+    {
+      constexpr uint32_t idesc0 = idesc_bf16_f32(TM, C), idesc1 = idesc_bf16_f32(TM, HB), idesc2 = idesc_bf16_f32(TM, C);
+      constexpr int NHB = L::NHB;
+      mbar_wait(bar(0), 0);
+      const int T = my_tiles * NHB;
+      auto proj = [&](int it) {
+        const uint32_t ab = (uint32_t)it & 1u, ph = (uint32_t)(it >> 1) & 1u;
+        mbar_wait(bar(17 + ab), ph);            // attention-output tile landed
+        mbar_wait(bar(23 + ab), ph ^ 1u);       // D0[ab] drained by E0 of tile it - 2
+        fence_after_sync();
+        const uint64_t a_desc = smem_desc_sw128(sb + L::A0_OFF + ab * L::A1_BYTES);
+        const uint64_t b_desc = smem_desc_sw128(sb + L::WP_OFF);
+#pragma unroll
+        for (int kk = 0; kk < C / 16; ++kk)
+          mma_bf16_ss(tmem + L::D0_COL + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc0, kk ? 1u : 0u);
+        mma_commit(bar(21 + ab));
+        mma_commit(bar(19 + ab));               // A0[ab] may be refilled
+      };
+      auto fc1 = [&](int t) {
+        const int it = t / NHB, hb = t - it * NHB;
+        const uint32_t ab = (uint32_t)it & 1u, bb = (uint32_t)t & 1u;
+        if (hb == 0) mbar_wait(bar(1 + ab), (uint32_t)(it >> 1) & 1u);   // LayerNorm'd tile written by the epilogue warps
+        mbar_wait(bar(7 + bb), (((uint32_t)t >> 1) & 1u) ^ 1u);
+        fence_after_sync();
+        const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + ab * L::A1_BYTES);
+        const uint64_t b_desc = smem_desc_sw128(sb + L::W1_OFF + hb * HB * 128);
+#pragma unroll
+        for (int kk = 0; kk < C / 16 && kk < 4; ++kk)
+          mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc1, kk ? 1u : 0u);
+        mma_commit(bar(5 + bb));
+        if (hb == NHB - 1) mma_commit(bar(3 + ab));
+        if (hb == 0 && it + 2 < my_tiles) proj(it + 2);
+      };
+      auto fc2 = [&](int t) {
+        const int it = t / NHB, h2 = t - it * NHB;
+        const uint32_t ab = (uint32_t)it & 1u, bb = (uint32_t)t & 1u;
+        mbar_wait(bar(9 + bb), ((uint32_t)t >> 1) & 1u);
+        if (h2 == 0) mbar_wait(bar(15 + ab), ((uint32_t)(it >> 1) & 1u) ^ 1u);
+        fence_after_sync();
+#pragma unroll
+        for (int kb = 0; kb < 2; ++kb) {
+          const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
+          const uint64_t b_desc = smem_desc_sw128(sb + L::W2_OFF + (2 * h2 + kb) * L::W2_TILE);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            mma_bf16_ss(tmem + L::D2_COL + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc2, (h2 | kb | kk) ? 1u : 0u);
+        }
+        mma_commit(bar(11 + bb));
+        if (h2 == NHB - 1) mma_commit(bar(13 + ab));
+      };
+      if (elect_one_sync()) {
+        if (my_tiles > 0) proj(0);
+        if (my_tiles > 1) proj(1);
+        if (T > 0) fc1(0);
+        if (T > 1) fc1(1);
+        for (int t = 0; t < T; ++t) {
+          if (t + 2 < T) fc1(t + 2);
+          fc2(t);
+        }
+      }
+      __syncwarp();
+    }
+  } else if (warp >= 4) {
+    // =========================== epilogue warps ===========================
+    const int q4 = warp & 3, quarter = (warp - 4) >> 2;   // TMEM lane quarter, column quarter
+    const int row = q4 * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
+    constexpr int NC = C / 4;                               // columns of a row this thread owns in E0 / E2
+    const int col0 = quarter * NC;
+    const float* bs = reinterpret_cast<const float*>(smem + L::BIAS_OFF);
+    float2* stats = reinterpret_cast<float2*>(smem + L::STAT_OFF);
+
+    // ---- E0: D0 -> + bp, x rs_a, + x1 -> x2 (parked in res_out) -> LayerNorm -> bf16 A operand of GEMM1 ----
+    auto e0_step = [&](int i) {
+      const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
+      const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
+      float4 xr[NC / 4];
+#pragma unroll
+      for (int j = 0; j < NC / 4; ++j) xr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      float rs = 1.f;
+      if (grow < n) {
+        const float4* xp = reinterpret_cast<const float4*>(x1 + grow * C + col0);
+#pragma unroll
+        for (int j = 0; j < NC / 4; ++j) xr[j] = __ldcs(xp + j);
+        if (rs_attn) rs = rs_attn[grow];
+      }
+      mbar_wait(bar(21 + ab), tph);
+      fence_after_sync();
+      uint32_t v[NC];
+      if constexpr (NC == 16) tmem_ld16(tmem + lane_base + L::D0_COL + ab * C + col0, v);
+      else tmem_ld8(tmem + lane_base + L::D0_COL + ab * C + col0, v);
+      tmem_ld_wait();
+      fence_before_sync();
+      mbar_arrive(bar(23 + ab));
+      float f[NC];
+      const float* bps = bs + L::HID + C;
+#pragma unroll
+      for (int j = 0; j < NC; ++j) f[j] = (__uint_as_float(v[j]) + bps[col0 + j]) * rs;
+#pragma unroll
+      for (int j = 0; j < NC / 4; ++j) {
+        f[4 * j] += xr[j].x; f[4 * j + 1] += xr[j].y; f[4 * j + 2] += xr[j].z; f[4 * j + 3] += xr[j].w;
+      }
+      if (grow < n) {
+        float4* op = reinterpret_cast<float4*>(res_out + grow * C + col0);
+#pragma unroll
+        for (int j = 0; j < NC / 4; ++j) op[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+      }
+      float sum = 0.f, sq = 0.f;
+#pragma unroll
+      for (int j = 0; j < NC; ++j) {
+        sum += f[j];
+        sq = fmaf(f[j], f[j], sq);
+      }
+      float2* st = stats + ((int)ab * TM + row) * 4;
+      st[quarter] = make_float2(sum, sq);
+      epi_sync();
+      const float4 s01 = reinterpret_cast<const float4*>(st)[0], s23 = reinterpret_cast<const float4*>(st)[1];
+      const float mean = (s01.x + s01.z + s23.x + s23.z) * (1.f / C);
+      const float var = fmaxf((s01.y + s01.w + s23.y + s23.w) * (1.f / C) - mean * mean, 0.f);
+      const float rstd = rsqrtf(var + eps);
+      const float* gs = bs + L::HID + 2 * C;
+      const float* bes = bs + L::HID + 3 * C;
+      uint32_t pk[NC / 2];
+#pragma unroll
+      for (int j = 0; j < NC / 2; ++j)
+        pk[j] = pack2((f[2 * j] - mean) * rstd * gs[col0 + 2 * j] + bes[col0 + 2 * j],
+                      (f[2 * j + 1] - mean) * rstd * gs[col0 + 2 * j + 1] + bes[col0 + 2 * j + 1]);
+      mbar_wait(bar(3 + ab), tph ^ 1u);       // GEMM1 of tile i - 2 no longer reads A1[ab]
+      const uint32_t prow = sb + L::A1_OFF + ab * L::A1_BYTES + (row >> 3) * 1024 + (row & 7) * 128;
+#pragma unroll
+      for (int c4 = 0; c4 < NC / 8; ++c4)
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (((col0 / 8 + c4) ^ (row & 7)) << 4)),
+                     "r"(pk[4 * c4]), "r"(pk[4 * c4 + 1]), "r"(pk[4 * c4 + 2]), "r"(pk[4 * c4 + 3])
+                     : "memory");
+      fence_proxy_async();
+      mbar_arrive(bar(1 + ab));
+    };
+
+    auto gelu_step = [&](int hb, uint32_t e1) {   // D1 -> + b1 -> GELU -> bf16 A operand of GEMM2
+      const uint32_t bb = e1 & 1u;
+      mbar_wait(bar(5 + bb), (e1 >> 1) & 1u);
+      fence_after_sync();
+      uint32_t v[32], pk[16];
+      const int gc0 = quarter * 32;
+      tmem_ld32(tmem + lane_base + bb * HB + gc0, v);
+      tmem_ld_wait();
+      fence_before_sync();
+      mbar_arrive(bar(7 + bb));
+      const float4* bp4 = reinterpret_cast<const float4*>(smem + L::BIAS_OFF) + (hb * HB + gc0) / 4;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 bv = bp4[j];
+        pk[2 * j] = pack2(gelu_erf(__uint_as_float(v[4 * j]) + bv.x), gelu_erf(__uint_as_float(v[4 * j + 1]) + bv.y));
+        pk[2 * j + 1] =
+            pack2(gelu_erf(__uint_as_float(v[4 * j + 2]) + bv.z), gelu_erf(__uint_as_float(v[4 * j + 3]) + bv.w));
+      }
+      mbar_wait(bar(11 + bb), ((e1 >> 1) & 1u) ^ 1u);
+      const uint32_t prow = sb + L::A2_OFF + bb * L::A2_BYTES + (quarter >> 1) * 16384 + (row >> 3) * 1024 +
+                            (row & 7) * 128;
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4)
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(
+                         prow + ((((quarter & 1) * 4 + c4) ^ (row & 7)) << 4)),
+                     "r"(pk[4 * c4]), "r"(pk[4 * c4 + 1]), "r"(pk[4 * c4 + 2]), "r"(pk[4 * c4 + 3])
+                     : "memory");
+      fence_proxy_async();
+      mbar_arrive(bar(9 + bb));
+    };
+
+    auto epilogue2 = [&](int i) {   // D2 -> + b2, x rs_m, + x2 (read back from res_out) -> fp32 stream + bf16 copy
+      const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
+      const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
+      float4 rres[NC / 4];
+#pragma unroll
+      for (int j = 0; j < NC / 4; ++j) rres[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      float rs = 1.f;
+      if (grow < n) {
+        const float4* rp = reinterpret_cast<const float4*>(res_out + grow * C + col0);   // this thread's own E0 store
+#pragma unroll
+        for (int j = 0; j < NC / 4; ++j) rres[j] = rp[j];
+        if (rs_mlp) rs = rs_mlp[grow];
+      }
+      mbar_wait(bar(13 + ab), tph);
+      fence_after_sync();
+      uint32_t v[NC];
+      if constexpr (NC == 16) tmem_ld16(tmem + lane_base + L::D2_COL + ab * C + col0, v);
+      else tmem_ld8(tmem + lane_base + L::D2_COL + ab * C + col0, v);
+      tmem_ld_wait();
+      fence_before_sync();
+      mbar_arrive(bar(15 + ab));
+      if (grow < n) {
+        float f[NC];
+        const float* b2s = bs + L::HID;
+#pragma unroll
+        for (int j = 0; j < NC; ++j) f[j] = (__uint_as_float(v[j]) + b2s[col0 + j]) * rs;
+#pragma unroll
+        for (int j = 0; j < NC / 4; ++j) {
+          f[4 * j] += rres[j].x; f[4 * j + 1] += rres[j].y; f[4 * j + 2] += rres[j].z; f[4 * j + 3] += rres[j].w;
+        }
+        float4* op = reinterpret_cast<float4*>(res_out + grow * C + col0);
+#pragma unroll
+        for (int j = 0; j < NC / 4; ++j) op[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        if (out_bf16) {
+          uint4* ob = reinterpret_cast<uint4*>(out_bf16 + grow * C + col0);
+#pragma unroll
+          for (int j = 0; j < NC / 8; ++j)
+            ob[j] = make_uint4(pack2(f[8 * j], f[8 * j + 1]), pack2(f[8 * j + 2], f[8 * j + 3]),
+                               pack2(f[8 * j + 4], f[8 * j + 5]), pack2(f[8 * j + 6], f[8 * j + 7]));
+        }
+      }
+    };
+    // order per tile i: G(i,0)  E0(i+1)  E2(i-1)  G(i,1..)  -- the LayerNorm of the NEXT tile is ready before its first
+    // GEMM1 is due, and the wait for GEMM2 of tile i-1 hides behind the first GELU block of tile i.  E0(i+1) must come
+    // BEFORE E2(i-1): the issuer queues GEMM1 of tile i+1 (which waits for E0(i+1)) ahead of the last GEMM2 of tile i-1
+    // when a tile has a single hidden block (C = 32), so the other order deadlocks.
+    uint32_t e1 = 0;
+    if (my_tiles > 0) e0_step(0);
+    for (int i = 0; i <= my_tiles; ++i) {
+      if (i < my_tiles) gelu_step(0, e1++);
+      if (i + 1 < my_tiles) e0_step(i + 1);
+      if (i >= 1) epilogue2(i - 1);
+      if (i < my_tiles)
+        for (int hb = 1; hb < L::NHB; ++hb) gelu_step(hb, e1++);
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<512>(tmem);
+}
+
+template <int C>
+static int launch_proj_mlp(const __nv_bfloat16* a, const __nv_bfloat16* wpp, const float* bp, const float* x1,
+                           const float* rs_attn, const float* g2, const float* be2, float eps, const __nv_bfloat16* w1p,
+                           const float* b1, const __nv_bfloat16* w2p, const float* b2, const float* rs_mlp, int64_t n,
+                           float* res_out, __nv_bfloat16* out_bf16, cudaStream_t st) {
+  using L = mlp::PSmem<C>;
+  static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
+  static_assert(L::D0_COL + 2 * C <= 512, "TMEM columns");
+  static bool configured_dev[kMaxDeviceSlots] = {};
+  bool& configured = configured_dev[device_slot()];
+  if (!configured) {
+    if (cudaFuncSetAttribute(proj_mlp_fused_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::DYN_BYTES) !=
+        cudaSuccess)
+      return PTV3_ELAUNCH;
+    configured = true;
+  }
+  const int n_tiles = (int)cdiv(n, mlp::TM);
+  const int g = n_tiles < kNumSMs ? n_tiles : kNumSMs;
+  proj_mlp_fused_kernel<C><<<g, mlp::THREADS, L::DYN_BYTES, st>>>(a, wpp, bp, x1, rs_attn, g2, be2, eps, w1p, b1, w2p,
+                                                                   b2, rs_mlp, n, n_tiles, res_out, out_bf16);
+  return check_launch();
+}
+
 bool mlp_fused_supported(int c, int hidden) { return (c == 32 || c == 64) && hidden == 4 * c; }
 
 template <int C>
@@ -374,6 +749,26 @@ int ptv3_mlp_fused_rs(const void* x, const void* w1_packed, const float* b1, con
                           b2, residual, row_scale, n, res_out, (__nv_bfloat16*)out_bf16, st);
   return launch_mlp<64>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed,
                         b2, residual, row_scale, n, res_out, (__nv_bfloat16*)out_bf16, st);
+}
+
+int ptv3_proj_mlp_fused(const void* a, const void* wproj_packed, const float* bproj, const float* x1,
+                        const float* rs_attn, const float* ln_gamma, const float* ln_beta, float eps,
+                        const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
+                        const float* rs_mlp, int64_t n, int c, int hidden, float* res_out, void* out_bf16,
+                        void* stream) {
+  if (n < 0 || !mlp_fused_supported(c, hidden)) return n < 0 ? PTV3_EINVAL : PTV3_EUNSUPPORTED;
+  if (n == 0) return PTV3_OK;
+  if (!a || !wproj_packed || !bproj || !x1 || !ln_gamma || !ln_beta || !w1_packed || !b1 || !w2_packed || !b2 ||
+      !res_out || res_out == x1)
+    return PTV3_EINVAL;
+  cudaStream_t st = as_stream(stream);
+#define PTV3_PM(CC)                                                                                              \
+  launch_proj_mlp<CC>((const __nv_bfloat16*)a, (const __nv_bfloat16*)wproj_packed, bproj, x1, rs_attn, ln_gamma, \
+                      ln_beta, eps, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed, b2,     \
+                      rs_mlp, n, res_out, (__nv_bfloat16*)out_bf16, st)
+  const int rc = c == 32 ? PTV3_PM(32) : PTV3_PM(64);
+#undef PTV3_PM
+  return rc;
 }
 
 }  // extern "C"

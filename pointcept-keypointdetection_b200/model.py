@@ -350,6 +350,7 @@ class Block(PointModule):
         return ln.weight, ln.bias, ln.eps
 
     native = True      # one C-ABI call per Block (ops.block_fwd) when the shapes allow; False = the op-by-op path
+    fuse_proj = True   # A/B switch: attn.proj + LayerNorm + MLP in one kernel (C = 32 / 64) inside the native call
 
     def _native_params(self):
         """ptv3_block_params of this Block (bf16 inference), rebuilt when a parameter changes."""
@@ -379,13 +380,19 @@ class Block(PointModule):
             if fused:
                 t.update(fc1_w=ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), fc1_b=mlp.fc1.bias.float().contiguous(),
                          fc2_w=ops.pack_kmajor(lw(mlp.fc2, g2), c), fc2_b=sc(mlp.fc2.bias, g2).contiguous())
+                # proj + LN + MLP as one kernel.  Measured (profiles/r02_fusions.md): a win at C = 32 (0.64 vs 0.79 ms for
+                # the two stage-0 blocks), a loss at C = 64 (2.64 vs 2.37 ms over six blocks): the MLP's epilogue warps
+                # are GELU-issue bound there and the LayerNorm work lands on the same warps.  fuse_proj = "all" forces it.
+                if ((self.fuse_proj == "all" or (self.fuse_proj and c == 32)) and attn.proj.bias is not None):
+                    t.update(proj_w_packed=ops.pack_kmajor(lw(attn.proj, g1), c),
+                             proj_b_f32=sc(attn.proj.bias, g1).contiguous())
             else:
                 t.update(fc1_w=lw(mlp.fc1), fc1_b=lb(mlp.fc1), fc2_w=lw(mlp.fc2, g2), fc2_b=lb(mlp.fc2, g2))
             return ops.block_params(c=c, heads=attn.num_heads, hidden=hidden, k3=conv.kernel_size ** 3,
                                     patch=attn.patch_size, mlp_fused=int(fused), attn_algo=attn.algo,
                                     scale=float(attn.scale), eps_cpe=float(self.cpe[2].eps),
                                     eps_norm2=float(self.norm2[0].eps), **t)
-        return _cached(self, "native", params, build)
+        return _cached(self, ("native", self.fuse_proj), params, build)
 
     def _fast(self):
         """Sub-module references and the static half of the native-path test, resolved once (nn.Module attribute

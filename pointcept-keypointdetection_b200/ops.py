@@ -384,6 +384,27 @@ def mlp_fused(x, w1_packed, b1, w2_packed, b2, hidden, residual=None, want_res=T
     return res_out, out16
 
 
+def proj_mlp_fused(a, wproj_packed, bproj, x1, ln_gamma, ln_beta, eps, w1_packed, b1, w2_packed, b2, hidden,
+                   rs_attn=None, rs_mlp=None, want_bf16=True):
+    """Second half of Block.forward in one kernel (C = 32 / 64): x2 = x1 + rs_attn * proj(a); out = x2 + rs_mlp *
+    MLP(LayerNorm(x2)).  a (N,C) bf16, x1 (N,C) fp32.  Returns (out fp32, out bf16 or None)."""
+    _need_cuda(a, x1, wproj_packed, w1_packed, w2_packed)
+    lib = _lib.load()
+    a, x1 = a.contiguous(), x1.contiguous()
+    assert a.dtype == torch.bfloat16 and x1.dtype == torch.float32 and a.shape == x1.shape
+    n, c = a.shape
+    out = torch.empty((n, c), dtype=torch.float32, device=a.device)
+    out16 = torch.empty((n, c), dtype=torch.bfloat16, device=a.device) if want_bf16 else None
+    for r in (rs_attn, rs_mlp):
+        assert r is None or (r.dtype == torch.float32 and r.numel() == n and r.is_contiguous())
+    with _timed("proj_mlp_fused", n=n, c=c, hidden=int(hidden)):
+        _lib.check(lib.ptv3_proj_mlp_fused(_p(a), _p(wproj_packed), _p(bproj), _p(x1), _p(rs_attn), _p(ln_gamma),
+                                           _p(ln_beta), float(eps), _p(w1_packed), _p(b1), _p(w2_packed), _p(b2),
+                                           _p(rs_mlp), n, c, int(hidden), _p(out), _p(out16), _stream()),
+                   "ptv3_proj_mlp_fused")
+    return out, out16
+
+
 # ------------------------------------------------------------------ A8 one native call per Block
 NATIVE_BLOCK = True      # bench.py's per-op timing leg and A/B tests switch this off (op-by-op path, same kernels)
 

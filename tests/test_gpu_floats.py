@@ -183,6 +183,47 @@ def test_mlp_fused_tcgen05(c, n):
     assert r2 is None and rel_l2(r216, ref) < 6e-3
 
 
+@pytest.mark.parametrize("c,n", [(32, 1), (64, 127), (32, 5000), (64, 40001), (32, 148 * 128 * 4 + 3),
+                                 (64, 148 * 128 * 5 + 77)])
+@pytest.mark.parametrize("drop", [False, True])
+def test_proj_mlp_fused_tcgen05(c, n, drop):
+    """attn.proj -> (+ DropPath) + shortcut -> LayerNorm -> fc1 -> GELU(erf) -> fc2 -> (+ DropPath) + shortcut in one
+    tcgen05 kernel against the torch fp32 reference on the same bf16-rounded operands (LayerNorm output and hidden
+    activation rounded to bf16 like the reference under autocast): rel-L2 <= 4e-3 on the two branches."""
+    import torch.nn.functional as F
+    from ptv3_b200 import ops
+    torch.manual_seed(c * 3 + n)
+    h = 4 * c
+    a = torch.randn(n, c).bfloat16()
+    wp = (torch.randn(c, c) / c ** 0.5).bfloat16()
+    w1 = (torch.randn(h, c) / c ** 0.5).bfloat16()
+    w2 = (torch.randn(c, h) / h ** 0.5).bfloat16()
+    bp, b1, b2 = torch.randn(c) * 0.5, torch.randn(h) * 0.5, torch.randn(c) * 0.5
+    g, be = torch.rand(c) + 0.5, torch.randn(c) * 0.2
+    x1 = torch.randn(n, c) * 2.0 + 0.7
+    ra = (torch.rand(n) > 0.3).float() / 0.7 if drop else None
+    rm = (torch.rand(n) > 0.2).float() / 0.8 if drop else None
+    br1 = a.float() @ wp.float().t() + bp
+    x2 = x1 + (br1 * ra[:, None] if drop else br1)
+    hn = F.layer_norm(x2, (c,), g, be, 1e-5).bfloat16().float()
+    hid = F.gelu(hn @ w1.float().t() + b1).bfloat16().float()
+    br2 = hid @ w2.float().t() + b2
+    ref = x2 + (br2 * rm[:, None] if drop else br2)
+    cu = lambda t: t.cuda() if t is not None else None
+    out, out16 = ops.proj_mlp_fused(a.cuda(), ops.pack_kmajor(wp.cuda(), c), bp.cuda(), x1.cuda(), g.cuda(), be.cuda(),
+                                    1e-5, ops.pack_kmajor(w1.cuda(), 128), b1.cuda(), ops.pack_kmajor(w2.cuda(), c),
+                                    b2.cuda(), h, rs_attn=cu(ra), rs_mlp=cu(rm))
+    assert rel_l2(out - x1.cuda(), ref - x1) < 4e-3, rel_l2(out - x1.cuda(), ref - x1)
+    assert torch.equal(out16, out.bfloat16())
+    # and against the separate launches it replaces (proj output rounded to bf16 there)
+    p16 = F.linear(a.cuda(), wp.cuda(), bp.bfloat16().cuda())
+    x2k, hk = ops.ln_residual(p16, None, None, 1e-5, residual=x1.cuda(), gamma2=g.cuda(), beta2=be.cuda(),
+                              out2_dtype=torch.bfloat16, row_scale=cu(ra))
+    chain, _ = ops.mlp_fused(hk, ops.pack_kmajor(w1.cuda(), 128), b1.cuda(), ops.pack_kmajor(w2.cuda(), c), b2.cuda(),
+                             h, residual=x2k, row_scale=cu(rm))
+    assert rel_l2(out - x1.cuda(), chain - x1.cuda()) < 8e-3
+
+
 def test_attention_golden(golden):
     """Reference SerializedAttention.forward (dense branch, one scene) frozen in tests/golden/attention.npz."""
     from ptv3_b200 import ops
@@ -318,24 +359,29 @@ def test_block_native_call_equals_op_by_op():
     scenes = [_scene(71, 6000, 0.6), _scene(72, 2500, 0.35)]
     cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
     offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
+    from ptv3_b200.model import Block
     feats = {}
-    for native in (True, False):
-        ops.NATIVE_BLOCK = native
+    for native, fuse in ((True, False), (True, True), (False, False)):
+        ops.NATIVE_BLOCK, Block.fuse_proj = native, fuse
         try:
             hooks = []
             for name, mod in (("enc0", m.backbone.enc.enc0), ("enc2", m.backbone.enc.enc2)):
                 hooks.append(mod.register_forward_hook(
-                    lambda _m, _i, o, name=name, native=native: feats.__setitem__((name, native), o.feat.clone())))
+                    lambda _m, _i, o, name=name, key=(native, fuse): feats.__setitem__((name, key), o.feat.clone())))
             torch.manual_seed(9)
             pred = m(dict(coord=cat(0), feat=cat(1), grid_coord=cat(2), offset=offset))["pred"]
-            feats[("pred", native)] = pred.clone()
+            feats[("pred", (native, fuse))] = pred.clone()
             for h in hooks:
                 h.remove()
         finally:
-            ops.NATIVE_BLOCK = True
+            ops.NATIVE_BLOCK, Block.fuse_proj = True, True
     for k in ("enc0", "enc2", "pred"):
-        e = rel_l2(feats[(k, True)], feats[(k, False)])
+        e = rel_l2(feats[(k, (True, False))], feats[(k, (False, False))])
         assert e < 2e-3, (k, e)       # same kernels; the GEMMs may pick another cuBLASLt algorithm (bf16 rounding)
+        # proj + LayerNorm + MLP in one kernel (C = 32): attn.proj's output is no longer rounded to bf16 on the way, so
+        # these are two differently rounded bf16 paths (each is held to the oracle by the golden / full-size tests)
+        e = rel_l2(feats[(k, (True, True))], feats[(k, (False, False))])
+        assert e < 1e-2, (k, e)
 
 
 def test_subm_map_site_range_flag():

@@ -147,7 +147,8 @@ def test_sonata_native_block_equals_op_by_op(dtype):
         b = m(_data("enc"))["seg_logits"]
     finally:
         ops.NATIVE_BLOCK = True
-    assert rel_l2(a, b) <= (1e-6 if dtype == torch.float32 else 2e-3)
+    # bf16: the native call also fuses attn.proj + LayerNorm + MLP at C = 32 (proj output not rounded to bf16)
+    assert rel_l2(a, b) <= (1e-6 if dtype == torch.float32 else 1e-2)
 
 
 def test_upcast_logits_equal_the_concatenation():
