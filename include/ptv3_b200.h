@@ -234,6 +234,10 @@ int ptv3_subm_stem_fused(const int32_t* indices, int64_t n, int ksize, const flo
  * (block -> run start, 64-bit occupancy mask) + one 4-byte load per PRESENT neighbour.  Sites must be unique (bit 8 of
  * ptv3_device_error() otherwise).  workspace: ptv3_subm_stem_z_workspace(n). */
 size_t ptv3_subm_stem_z_workspace(int64_t n);
+/* ptv3_subm_build_map (k = 3 or 5) through the same block table: identical (n, k^3) table, 8 hash probes per row
+ * instead of k^3.  workspace: ptv3_subm_stem_z_workspace(n). */
+int ptv3_subm_build_map_z(const int32_t* indices, int64_t n, int ksize, const int64_t* code_z, const int64_t* order_z,
+                          int depth, int32_t* nbr, void* workspace, size_t workspace_bytes, void* stream);
 int ptv3_subm_stem_fused_z(const int32_t* indices, int64_t n, int ksize, const int64_t* code_z, const int64_t* order_z,
                            int depth, const float* in, const float* weight, const float* bias, int act, float* out32,
                            void* out16, void* workspace, size_t workspace_bytes, void* stream);

@@ -93,7 +93,9 @@ def window_attention(qkv, order, inverse, offset, H, K, scale=None):
 # ----------------------------------------------------------------------------
 # A5: submanifold convolution (spconv 2.x SubMConv3d semantics, restated)
 # ----------------------------------------------------------------------------
-def _pack_key(b, xyz, shift=21):
+def _pack_key(b, xyz, shift=18):
+    # 18-bit coordinate fields (bias included) + the batch id above bit 54: exact for batch < 512, coordinates < 2^18 - 1024
+    # (with 21-bit fields the batch id sat at bit 63 and batch ids >= 2 wrapped around: fixed in round 2)
     return (b.to(torch.int64) << (3 * shift)) | (xyz[:, 0].to(torch.int64) << (2 * shift)) | \
            (xyz[:, 1].to(torch.int64) << shift) | xyz[:, 2].to(torch.int64)
 
@@ -112,7 +114,8 @@ def subm_neighbor_table(indices, ksize):
     skey, sidx = torch.sort(key)
     rng = torch.arange(-r, r + 1)
     delta = torch.stack(torch.meshgrid(rng, rng, rng, indexing="ij"), -1).reshape(-1, 3)      # (k^3, 3), dz fastest
-    dkey = (delta[:, 0].to(torch.int64) << (2 * 21)) + (delta[:, 1].to(torch.int64) << 21) + delta[:, 2].to(torch.int64)
+    assert int(idx[:, 0].max()) < 512 and int(idx[:, 1:].max()) < (1 << 18) - 2 * OFF and int(idx[:, 1:].min()) >= 0
+    dkey = (delta[:, 0].to(torch.int64) << (2 * 18)) + (delta[:, 1].to(torch.int64) << 18) + delta[:, 2].to(torch.int64)
     q = (key[:, None] + dkey[None, :]).reshape(-1)          # packed keys add component-wise (bias keeps fields >= 0)
     pos = torch.searchsorted(skey, q).clamp_(max=N - 1)
     hit = skey[pos] == q

@@ -55,6 +55,7 @@ SIGNATURES = {
     "ptv3_subm_build_map": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, c_sz, c_vp]),
     "ptv3_subm_stem_fused": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_sz, c_vp]),
     "ptv3_subm_stem_z_workspace": (c_sz, [c_i64]),
+    "ptv3_subm_build_map_z": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, c_int, c_vp, c_vp, c_sz, c_vp]),
     "ptv3_subm_stem_fused_z": (c_int, [c_vp, c_i64, c_int, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp,
                                        c_sz, c_vp]),
     "ptv3_subm_conv_workspace": (c_sz, [c_i64, c_int, c_int, c_int, c_int, c_int]),

@@ -504,6 +504,57 @@ __global__ void __launch_bounds__(512, 2) subm_stem_z_kernel(const float* __rest
   }
 }
 
+// (N, k^3) neighbour table through the same block table (k = 3 or 5): 8 lanes per row probe one candidate block each,
+// then share the k^3 offsets (lane l takes k = l, l + 8, ...).  Same table as subm_lookup_kernel, bit for bit.
+__global__ void __launch_bounds__(256) subm_lookup_z_kernel(const int32_t* __restrict__ indices, int64_t n, int ksize,
+                                                            const unsigned long long* __restrict__ keys,
+                                                            const uint4* __restrict__ payload, uint32_t mask,
+                                                            const int32_t* __restrict__ rows_sorted, int depth,
+                                                            int32_t* __restrict__ nbr) {
+  const int k3 = ksize * ksize * ksize, r = ksize / 2;
+  const int l8 = threadIdx.x & 7;
+  const int nblk_axis = 1 << (depth - 2), bshift = 3 * depth - 6;
+  const int64_t groups = ((int64_t)gridDim.x * blockDim.x) >> 3;
+  const int64_t n_pad = (n + 3) & ~3ll;      // whole warps stay in the loop: the shuffles below need all 32 lanes
+  for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; row < n_pad; row += groups) {
+    const bool live = row < n;
+    const int4 s = live ? reinterpret_cast<const int4*>(indices)[row] : make_int4(0, 0, 0, 0);
+    const int bx0 = (s.y - r) >> 2, by0 = (s.z - r) >> 2, bz0 = (s.w - r) >> 2;
+    uint32_t m_lo = 0, m_hi = 0, start = 0;
+    {
+      const int bx = (l8 & 4) ? (s.y + r) >> 2 : bx0, by = (l8 & 2) ? (s.z + r) >> 2 : by0,
+                bz = (l8 & 1) ? (s.w + r) >> 2 : bz0;
+      if (live && bx >= 0 && by >= 0 && bz >= 0 && bx < nblk_axis && by < nblk_axis && bz < nblk_axis) {
+        const uint64_t kb = ((uint64_t)(uint32_t)s.x << bshift) | (spread3_u64((uint32_t)bx) << 2) |
+                            (spread3_u64((uint32_t)by) << 1) | spread3_u64((uint32_t)bz);
+        uint32_t slot = hash_site(kb) & mask;
+        unsigned long long cur = keys[slot];
+        while (cur != kb && cur != kEmptyKey) {
+          slot = (slot + 1) & mask;
+          cur = keys[slot];
+        }
+        if (cur == kb) {
+          const uint4 pl = payload[slot];
+          m_lo = pl.x; m_hi = pl.y; start = pl.z;
+        }
+      }
+    }
+    for (int k0 = 0; k0 < k3; k0 += 8) {
+      const int k = k0 + l8;
+      const int dz = k % ksize - r, dy = (k / ksize) % ksize - r, dx = k / (ksize * ksize) - r;
+      const int x = s.y + dx, y = s.z + dy, z = s.w + dz;
+      const int sel = (((x >> 2) != bx0) ? 4 : 0) | (((y >> 2) != by0) ? 2 : 0) | (((z >> 2) != bz0) ? 1 : 0);
+      const uint32_t lo = __shfl_sync(0xffffffffu, m_lo, sel, 8), hi = __shfl_sync(0xffffffffu, m_hi, sel, 8);
+      const uint32_t st = __shfl_sync(0xffffffffu, start, sel, 8);
+      if (k < k3 && live) {
+        const uint64_t m = ((uint64_t)hi << 32) | lo;
+        const int cell = ((x & 2) << 4) | ((y & 2) << 3) | ((z & 2) << 2) | ((x & 1) << 2) | ((y & 1) << 1) | (z & 1);
+        nbr[row * k3 + k] = ((m >> cell) & 1ull) ? rows_sorted[st + __popcll(m & ((1ull << cell) - 1ull))] : -1;
+      }
+    }
+  }
+}
+
 template <typename T>
 static int conv_cuda_core(const T* in, const T* w, const float* bias, const int32_t* nbr, int64_t n, int cin, int cout,
                           int k3, T* out, cudaStream_t st) {
@@ -643,6 +694,26 @@ int ptv3_subm_stem_fused_z(const int32_t* indices, int64_t n, int ksize, const i
   if (blocks > kNumSMs * 2) blocks = kNumSMs * 2;
   subm_stem_z_kernel<<<(unsigned)blocks, 512, smem + 16 * 128 * sizeof(float4), st>>>(in, weight, bias, indices, keys, payload, cap - 1, rows_sorted,
                                                           depth, n, ksize, act, out32, (__nv_bfloat16*)out16);
+  return check_launch(2);
+}
+
+int ptv3_subm_build_map_z(const int32_t* indices, int64_t n, int ksize, const int64_t* code_z, const int64_t* order_z,
+                          int depth, int32_t* nbr, void* workspace, size_t workspace_bytes, void* stream) {
+  if (n < 0 || (ksize != 3 && ksize != 5) || depth < 2 || depth > 16) return PTV3_EINVAL;
+  if (n == 0) return PTV3_OK;
+  if (!indices || !nbr || !code_z || !order_z || n >= (1ll << 30)) return PTV3_EINVAL;
+  uint32_t cap = table_capacity(n);
+  Workspace ws(workspace, workspace_bytes);
+  unsigned long long* keys = ws.take<unsigned long long>(cap);
+  uint4* payload = ws.take<uint4>(cap);
+  int32_t* rows_sorted = ws.take<int32_t>((size_t)n);
+  if (!ws.ok()) return PTV3_EWORKSPACE;
+  cudaStream_t st = as_stream(stream);
+  cudaMemsetAsync(keys, 0xff, (size_t)cap * 8, st);
+  stem_blocks_kernel<<<grid_for(n, 256), 256, 0, st>>>(code_z, order_z, n, keys, payload, cap - 1, rows_sorted,
+                                                       device_error_flag());
+  subm_lookup_z_kernel<<<grid_for(n * 8, 256, 16), 256, 0, st>>>(indices, n, ksize, keys, payload, cap - 1, rows_sorted,
+                                                                 depth, nbr);
   return check_launch(2);
 }
 

@@ -29,7 +29,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from . import ops
-from .structure import Point, SparseConvTensor, device_perm, offset2batch  # noqa: F401
+from .structure import Point, SparseConvTensor, device_perm, offset2batch, z_info  # noqa: F401
 
 
 def _cached(module, slot, params, builder):
@@ -158,7 +158,7 @@ class SubMConv3d(SparseModule):
         key = (self.indice_key, self.kernel_size)
         nbr = x.indice_dict.get(key) if self.indice_key is not None else None
         if nbr is None:
-            nbr = ops.subm_build_map(x.indices, self.kernel_size)
+            nbr = ops.subm_build_map(x.indices, self.kernel_size, z=x.indice_dict.get("_z") if self.block_search else None)
             if self.indice_key is not None:
                 x.indice_dict[key] = nbr
         return nbr
@@ -182,6 +182,10 @@ class SubMConv3d(SparseModule):
         return _cached(self, ("w", dtype, scale is not None, cin_p, cout_p), [self.weight, self.bias, scale, shift],
                        build)
 
+    # A/B switch: (N, k^3) neighbour tables through 4^3-block occupancy masks when the level is serialized
+    # (ops.subm_build_map(z=...)).  Off by default: measured equal to the hash-probe kernel for k = 3 (0.44 ms per step
+    # either way -- 27 probes per row were never the bound there, unlike the stem's 125; profiles/r02_fusions.md)
+    block_search = False
     pad_channels = False     # SpUNet sets this: 96-channel levels run as 128-wide tensors whose last columns are zero
 
     def conv(self, features, x, scale=None, shift=None, algo=0):
@@ -516,7 +520,7 @@ class SerializedPooling(PointModule):
         return 0 if d > serialized_depth else d
 
     @torch.no_grad()
-    def plan(self, code, order, grid_coord, batch, pooling_depth, n_scenes):
+    def plan(self, code, order, grid_coord, batch, pooling_depth, n_scenes, z_row=None):
         """The integer half of the pooling (:385-412, :426-433): clusters, CSR, heads, pooled codes / orders / grid /
         batch / offset.  It depends on the serialization only, so PointTransformerV3.forward runs it for ALL levels
         before the first feature kernel: the one host read per level (pooled row count) then waits for a few tiny
@@ -526,11 +530,13 @@ class SerializedPooling(PointModule):
         c, o, inv = pf["code"], pf["order"], pf["inverse"]
         if self.shuffle_orders:
             perm = torch.randperm(c.shape[0])
+            if z_row is not None:
+                z_row = perm.tolist().index(z_row)
             if not torch.equal(perm, torch.arange(c.shape[0])):
                 perm = device_perm(perm, c.device)
                 c, o, inv = c[perm], o[perm], inv[perm]
         return dict(pf=pf, grid_coord=g, batch=b, indices4=indices4, code=c, order=o, inverse=inv,
-                    offset=ops.batch_to_offset(b, n_scenes))
+                    offset=ops.batch_to_offset(b, n_scenes), z_row=z_row)
 
     @torch.no_grad()
     def forward(self, point):
@@ -540,7 +546,7 @@ class SerializedPooling(PointModule):
             point.keys()), "Run point.serialization() point cloud before SerializedPooling"
         plans = point.pop("_pool_plans", None)
         plan = plans.pop(0) if plans else self.plan(point.serialized_code, point.serialized_order, point.grid_coord,
-                                                    point.batch, pooling_depth, len(point.offset))
+                                                    point.batch, pooling_depth, len(point.offset), point.get("_z_row"))
         pf, grid_coord, batch, indices4 = plan["pf"], plan["grid_coord"], plan["batch"], plan["indices4"]
         code, order, inverse = plan["code"], plan["order"], plan["inverse"]
         w, b = _cached(self, ("proj", cd), [self.proj.weight, self.proj.bias],
@@ -580,6 +586,10 @@ class SerializedPooling(PointModule):
         new["_feat_cd"] = feat_cd if feat_cd is not None else (feat if cd == torch.float32 else feat.to(cd))
         new["sparse_shape"] = [(1 << max(int(new.serialized_depth), 0)) + 96] * 3
         new["sparse_conv_feat"] = SparseConvTensor(new["_feat_cd"], indices4, new["sparse_shape"], n_scenes)
+        new["_z_row"] = plan.get("z_row")
+        z = z_info(new)
+        if z is not None:
+            new["sparse_conv_feat"].indice_dict["_z"] = z
         return new
 
 
@@ -809,6 +819,7 @@ class PointTransformerV3(PointModule):
             ready.record(main)                                   # codes / orders / grid / batch are final here
             code, order = point.serialized_code, point.serialized_order
             grid, batch, depth, n_scenes = point.grid_coord, point.batch, point.serialized_depth, len(point.offset)
+            z_row = point.get("_z_row")
             if self.plan_overlap and "down" not in stages[0]._modules:
                 point = stages[0](self.embedding(point))
                 first_done = True
@@ -820,8 +831,8 @@ class PointTransformerV3(PointModule):
                     if down is None:
                         continue
                     pd = down.pooling_depth(depth)
-                    plans.append(down.plan(code, order, grid, batch, pd, n_scenes))
-                    code, order, grid, batch = (plans[-1][k] for k in ("code", "order", "grid_coord", "batch"))
+                    plans.append(down.plan(code, order, grid, batch, pd, n_scenes, z_row))
+                    code, order, grid, batch, z_row = (plans[-1][k] for k in ("code", "order", "grid_coord", "batch", "z_row"))
                     depth -= pd
             main.wait_stream(side)
             for plan in plans:                                   # allocated on the side stream, consumed on the main one

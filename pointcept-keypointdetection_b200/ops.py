@@ -453,13 +453,20 @@ def block_fwd(bp, x, conv_in, nbr, order, windows, n_windows):
 
 
 # ------------------------------------------------------------------ A5 submanifold conv
-def subm_build_map(indices, ksize):
-    """indices (N,4) int32 [b,x,y,z] -> nbr (N, ksize^3) int32 (-1 = absent)."""
+def subm_build_map(indices, ksize, z=None):
+    """indices (N,4) int32 [b,x,y,z] -> nbr (N, ksize^3) int32 (-1 = absent).  z = (code_z, order_z, depth) from the
+    level's serialization selects the block-occupancy search (same table, 8 probes per row instead of ksize^3)."""
     _need_cuda(indices)
     lib = _lib.load()
     indices = indices.contiguous().int()
     n = indices.shape[0]
     nbr = torch.empty((n, ksize ** 3), dtype=torch.int32, device=indices.device)
+    if z is not None and ksize in (3, 5) and int(z[2]) >= 2 and z[0].numel() == n:
+        nbytes = lib.ptv3_subm_stem_z_workspace(n)
+        ws = _ws(nbytes, indices.device)
+        _lib.check(lib.ptv3_subm_build_map_z(_p(indices), n, int(ksize), _p(z[0].contiguous()), _p(z[1].contiguous()),
+                                             int(z[2]), _p(nbr), _p(ws), nbytes, _stream()), "ptv3_subm_build_map_z")
+        return nbr
     ws = _ws(lib.ptv3_subm_map_workspace(n), indices.device)
     _lib.check(lib.ptv3_subm_build_map(_p(indices), n, int(ksize), _p(nbr), _p(ws), ws.numel(), _stream()),
                "ptv3_subm_build_map")

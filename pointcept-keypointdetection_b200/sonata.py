@@ -26,7 +26,7 @@ import torch.nn.functional as F
 from . import ops
 from .model import (Block, LayerScale, PointModule, PointSequential, SubMConv3d, _cached,  # noqa: F401
                     _feat_cd)
-from .structure import Point, SparseConvTensor, device_perm
+from .structure import Point, SparseConvTensor, device_perm, z_info
 
 
 def _linear_f32_out(x, w, b):
@@ -46,7 +46,8 @@ def _ln_gelu(x, ln, cd):
 
 @torch.no_grad()
 def serialize_level(grid_coord, batch, n_scenes, orders, shuffle, grid_max=None):
-    """Point.serialization (structure.py:52-109) of one level as plain tensors: (depth, code, order, inverse).
+    """Point.serialization (structure.py:52-109) of one level as plain tensors: (depth, code, order, inverse, row of
+    the plain Morton codes or None).
     `grid_max`: per-axis maximum already on the host (saves the sync of :73)."""
     if grid_max is None:
         grid_max = [int(v) for v in ops.grid_max(grid_coord).tolist()]
@@ -55,12 +56,15 @@ def serialize_level(grid_coord, batch, n_scenes, orders, shuffle, grid_max=None)
     code = ops.encode_orders(grid_coord, batch, depth, orders)
     key_bits = depth * 3 + max(1, (int(n_scenes) - 1).bit_length())
     order, inverse = ops.argsort_rows(code, key_bits=key_bits)
+    z_row = list(orders).index("z") if "z" in orders else None
     if shuffle:
         perm = torch.randperm(code.shape[0])
+        if z_row is not None:
+            z_row = perm.tolist().index(z_row)
         if not torch.equal(perm, torch.arange(code.shape[0])):
             perm = device_perm(perm, code.device)
             code, order, inverse = code[perm], order[perm], inverse[perm]
-    return depth, code, order, inverse
+    return depth, code, order, inverse, z_row
 
 
 class GridPooling(PointModule):
@@ -84,9 +88,10 @@ class GridPooling(PointModule):
         """The integer half (:393-417 + the re-serialization of :460): clusters, CSR, pooled grid / batch / spconv
         indices, and the pooled level's codes / orders.  Depends on the grid only."""
         gp = ops.grid_pool(grid_coord, batch, self.stride, depth, n_scenes)
-        d, code, order, inverse = serialize_level(gp["grid_coord"], gp["batch"], n_scenes, orders, self.shuffle_orders,
-                                                  grid_max=gp["grid_max"])
-        gp.update(depth=d, code=code, order=order, inverse=inverse, offset=ops.batch_to_offset(gp["batch"], n_scenes))
+        d, code, order, inverse, z_row = serialize_level(gp["grid_coord"], gp["batch"], n_scenes, orders,
+                                                         self.shuffle_orders, grid_max=gp["grid_max"])
+        gp.update(depth=d, code=code, order=order, inverse=inverse, offset=ops.batch_to_offset(gp["batch"], n_scenes),
+                  z_row=z_row)
         return gp
 
     @torch.no_grad()
@@ -148,6 +153,10 @@ class GridPooling(PointModule):
         new["_feat_cd"] = feat_cd if feat_cd is not None else (feat if cd == torch.float32 else feat.to(cd))
         new["sparse_shape"] = [(1 << max(int(plan["depth"]), 0)) + 96] * 3
         new["sparse_conv_feat"] = SparseConvTensor(new["_feat_cd"], plan["indices4"], new["sparse_shape"], n_scenes)
+        new["_z_row"] = plan.get("z_row")
+        z = z_info(new)
+        if z is not None:
+            new["sparse_conv_feat"].indice_dict["_z"] = z
         return new
 
     @staticmethod

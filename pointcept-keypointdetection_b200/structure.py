@@ -49,6 +49,14 @@ def device_perm(perm, device):
     return t
 
 
+def z_info(point):
+    """(code_z, order_z, depth) of a serialized Point -- the row of plain Morton codes and its argsort -- or None."""
+    zr = point.get("_z_row")
+    if zr is None or "serialized_code" not in point or int(point["serialized_depth"]) < 2:
+        return None
+    return point["serialized_code"][zr], point["serialized_order"][zr], int(point["serialized_depth"])
+
+
 class SparseConvTensor:
     """features (N,C), indices (N,4) int32 [b,x,y,z]; `indice_dict` is the spconv-style cache shared by every
     tensor derived through replace_feature (holds the neighbour maps keyed by (indice_key, ksize))."""
@@ -147,3 +155,6 @@ class Point(dict):
         _, _, indices = ops.pool_gather_ints(self.grid_coord, self.batch, None, 0, want_grid=False, want_batch=False)
         self["sparse_shape"] = sparse_shape
         self["sparse_conv_feat"] = SparseConvTensor(self.feat, indices, sparse_shape, len(self.offset))
+        z = z_info(self)
+        if z is not None:       # lets the neighbour search of this level use 4^3-block occupancy masks (ops.subm_build_map)
+            self["sparse_conv_feat"].indice_dict["_z"] = z

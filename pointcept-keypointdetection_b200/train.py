@@ -20,7 +20,7 @@ import torch.nn.functional as F
 
 from . import autograd as A
 from . import ops
-from .structure import Point, SparseConvTensor
+from .structure import Point, SparseConvTensor, z_info
 
 
 def _lin(x, lin, cd):
@@ -90,7 +90,7 @@ def pooling_forward(mod, point):
     with torch.no_grad():
         plans = point.pop("_pool_plans", None)
         plan = plans.pop(0) if plans else mod.plan(point.serialized_code, point.serialized_order, point.grid_coord,
-                                                   point.batch, depth, n_scenes)
+                                                   point.batch, depth, n_scenes, point.get("_z_row"))
         pf, grid_coord, batch, indices4 = plan["pf"], plan["grid_coord"], plan["batch"], plan["indices4"]
         code, order, inverse, offset = plan["code"], plan["order"], plan["inverse"], plan["offset"]
         coord = ops.segment_csr(point.coord.float(), pf["idx_ptr"], "mean", gather=pf["indices"])
@@ -111,6 +111,10 @@ def pooling_forward(mod, point):
     new["_pooling_csr"] = (pf["indices"], pf["idx_ptr"])
     new["sparse_shape"] = [(1 << max(int(new.serialized_depth), 0)) + 96] * 3
     new["sparse_conv_feat"] = SparseConvTensor(feat, indices4, new["sparse_shape"], n_scenes)
+    new["_z_row"] = plan.get("z_row")
+    z = z_info(new)
+    if z is not None:
+        new["sparse_conv_feat"].indice_dict["_z"] = z
     return new
 
 
@@ -191,6 +195,10 @@ def grid_pooling_forward(mod, point):
     new["_pooling_csr"] = (plan["indices"], plan["idx_ptr"])
     new["sparse_shape"] = [(1 << max(int(plan["depth"]), 0)) + 96] * 3
     new["sparse_conv_feat"] = SparseConvTensor(feat, plan["indices4"], new["sparse_shape"], n_scenes)
+    new["_z_row"] = plan.get("z_row")
+    z = z_info(new)
+    if z is not None:
+        new["sparse_conv_feat"].indice_dict["_z"] = z
     return new
 
 
@@ -261,13 +269,15 @@ def backbone_forward(bb, data_dict):
         if bb.plan_ahead:        # integer front ends of all pooling levels first (see model.SerializedPooling.plan)
             plans, code, order = [], point.serialized_code, point.serialized_order
             grid, batch, depth = point.grid_coord, point.batch, point.serialized_depth
+            z_row = point.get("_z_row")
             for stage in bb.enc._modules.values():
                 down = stage._modules.get("down")
                 if down is None:
                     continue
                 pd = down.pooling_depth(depth)
-                plans.append(down.plan(code, order, grid, batch, pd, len(point.offset)))
+                plans.append(down.plan(code, order, grid, batch, pd, len(point.offset), z_row))
                 code, order, grid, batch = plans[-1]["code"], plans[-1]["order"], plans[-1]["grid_coord"], plans[-1]["batch"]
+                z_row = plans[-1]["z_row"]
                 depth -= pd
             point["_pool_plans"] = plans
     point = embedding_forward(bb.embedding, point)

@@ -303,6 +303,29 @@ def test_subm_map_vs_oracle():
     assert np.array_equal(one[:, 0], np.arange(len(idx)))
 
 
+@pytest.mark.parametrize("n_scenes,seed", [(1, 3), (2, 11), (5, 12)])
+def test_subm_map_block_search_vs_oracle(n_scenes, seed):
+    """ptv3_subm_build_map_z (4^3-block occupancy masks over the z-order serialization, 8 probes per row) gives the same
+    table as the oracle for k = 3 and k = 5, at the original depth and with spare depth (sites at the grid border, rows
+    in scrambled storage order)."""
+    ops = _ops()
+    grid, counts = _scene_grid(seed, n_scenes=n_scenes)
+    batch = np.repeat(np.arange(len(counts)), counts)
+    rng = np.random.default_rng(seed)
+    perm = np.concatenate([o + rng.permutation(c) for o, c in zip(np.cumsum([0] + list(counts[:-1])), counts)])
+    grid = grid[perm]                                           # storage order != any spatial order
+    idx = np.concatenate([batch[:, None], grid], 1).astype(np.int32)
+    depth0 = int(int(grid.max()) + 1).bit_length()
+    for depth in (depth0, depth0 + 2):
+        code = ops.encode_orders(dev(grid), dev(batch), depth, ["z"])
+        order, _ = ops.argsort_rows(code, key_bits=3 * depth + max(1, (n_scenes - 1).bit_length()))
+        for k in (3, 5):
+            ref = O.subm_neighbor_table(torch.from_numpy(idx), k).numpy()
+            got = ops.subm_build_map(dev(idx), k, z=(code[0], order[0], depth)).cpu().numpy()
+            assert np.array_equal(got, ref), (depth, k)
+    assert ops.device_error() == 0
+
+
 def test_voxelize_first_matches_reference(golden):
     """A0': first point per voxel with numpy's float32 quotient, both index orders, bit-exact against the reference's
     `voxelize_points` (frozen) and the oracle on a fresh scan; normalisation to the unit sphere."""

@@ -330,3 +330,21 @@ def test_lovasz_softmax_vs_reference():
     # all labels ignored: zero loss with a graph (lovasz.py:127-129)
     z = losses.lovasz_softmax(lg, torch.full((lg.shape[0],), -1), ignore_index=-1)
     assert z.item() == 0.0 and z.requires_grad
+
+
+def test_neighbor_table_many_scenes_brute_force():
+    """oracle.ops.subm_neighbor_table against a dictionary lookup on a batch of 5 scenes (the 64-bit key used to put the
+    batch id at bit 63, so batch ids >= 2 wrapped around; every earlier fixture had at most two scenes)."""
+    g = torch.Generator().manual_seed(0)
+    idx = torch.unique(torch.cat([torch.randint(0, 5, (600, 1), generator=g), torch.randint(0, 7, (600, 3), generator=g)], 1), dim=0)
+    for k in (3, 5):
+        nbr = O.subm_neighbor_table(idx, k)
+        where = {tuple(r): i for i, r in enumerate(idx.tolist())}
+        r = k // 2
+        for i, (b, x, y, z) in enumerate(idx.tolist()):
+            col = 0
+            for dx in range(-r, r + 1):
+                for dy in range(-r, r + 1):
+                    for dz in range(-r, r + 1):
+                        assert int(nbr[i, col]) == where.get((b, x + dx, y + dy, z + dz), -1)
+                        col += 1
