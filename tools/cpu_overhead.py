@@ -11,7 +11,7 @@ import bench  # noqa: E402
 
 dev = torch.device("cuda", 0)
 model, _ = bench.build_model(torch.bfloat16, dev)
-raw = bench.make_raw_scenes(16, 100000, 4.1, seed0=0)
+raw = bench.make_raw_scenes(int(sys.argv[1]) if len(sys.argv) > 1 else 16, 100000, 4.1, seed0=0)
 host, counts = bench.voxelize_on_device(raw, dev)
 res = {k: v.to(dev) for k, v in host.items()}
 for _ in range(3):
