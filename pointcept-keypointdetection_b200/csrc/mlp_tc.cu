@@ -10,6 +10,7 @@
 // Both weight matrices (pre-packed into shared-memory images by pack_kmajor_kernel) stay resident in shared memory
 // for the CTA's lifetime (one bulk copy each); X tiles are double-buffered by two loader warps with 16-byte cp.async.
 // HBM traffic per row: read C x 2 B (+ C x 4 B residual), write C x (4 + 2) B  -- the hidden activation costs nothing.
+#include <cstdlib>
 #include "common.cuh"
 #include "tc05.cuh"
 
@@ -257,14 +258,15 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
       const int col0 = quarter * NC;
       const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
       // the residual row segment is requested BEFORE waiting for GEMM2: its HBM latency hides behind that wait
-      float4 rres[NC / 4];
+      float rres[NC / 8][8];      // 256-bit accesses: one whole 32-byte sector per lane and instruction
 #pragma unroll
-      for (int j = 0; j < NC / 4; ++j) rres[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < NC / 8; ++j)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) rres[j][q] = 0.f;
       float rs = 1.f;      // DropPath on the branch: 0 or 1 / keep for the whole row (NULL = none)
       if (residual && grow < n) {
-        const float4* rp = reinterpret_cast<const float4*>(residual + grow * C + col0);
 #pragma unroll
-        for (int j = 0; j < NC / 4; ++j) rres[j] = __ldcs(rp + j);
+        for (int j = 0; j < NC / 8; ++j) ldg256_cs(residual + grow * C + col0 + 8 * j, rres[j]);
       }
       if (row_scale && grow < n) rs = row_scale[grow];
       mbar_wait(bar(13 + ab), tph);
@@ -281,20 +283,28 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
 #pragma unroll
         for (int j = 0; j < NC; ++j) f[j] = (__uint_as_float(v[j]) + b2s[col0 + j]) * rs;
 #pragma unroll
-        for (int j = 0; j < NC / 4; ++j) {
-          f[4 * j] += rres[j].x; f[4 * j + 1] += rres[j].y; f[4 * j + 2] += rres[j].z; f[4 * j + 3] += rres[j].w;
-        }
-        if (res_out) {
-          float4* op = reinterpret_cast<float4*>(res_out + grow * C + col0);
+        for (int j = 0; j < NC / 8; ++j)
 #pragma unroll
-          for (int j = 0; j < NC / 4; ++j) op[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+          for (int q = 0; q < 8; ++q) f[8 * j + q] += rres[j][q];
+        if (res_out) {
+#pragma unroll
+          for (int j = 0; j < NC / 8; ++j) {
+            float o8[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) o8[q] = f[8 * j + q];
+            stg256(res_out + grow * C + col0 + 8 * j, o8);
+          }
         }
         if (out_bf16) {
-          uint4* op = reinterpret_cast<uint4*>(out_bf16 + grow * C + col0);
+          if constexpr (NC == 16) {
+            uint32_t pk8[8];
 #pragma unroll
-          for (int j = 0; j < NC / 8; ++j)
-            op[j] = make_uint4(pack2(f[8 * j], f[8 * j + 1]), pack2(f[8 * j + 2], f[8 * j + 3]),
-                               pack2(f[8 * j + 4], f[8 * j + 5]), pack2(f[8 * j + 6], f[8 * j + 7]));
+            for (int q = 0; q < 8; ++q) pk8[q] = pack2(f[2 * q], f[2 * q + 1]);
+            stg256_u32(out_bf16 + grow * C + col0, pk8);
+          } else {
+            *reinterpret_cast<uint4*>(out_bf16 + grow * C + col0) =
+                make_uint4(pack2(f[0], f[1]), pack2(f[2], f[3]), pack2(f[4], f[5]), pack2(f[6], f[7]));
+          }
         }
       }
     };
@@ -514,14 +524,15 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) proj_mlp_fused_kernel(
     auto e0_step = [&](int i) {
       const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
       const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
-      float4 xr[NC / 4];
+      float xr[NC / 8][8];
 #pragma unroll
-      for (int j = 0; j < NC / 4; ++j) xr[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < NC / 8; ++j)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) xr[j][q] = 0.f;
       float rs = 1.f;
       if (grow < n) {
-        const float4* xp = reinterpret_cast<const float4*>(x1 + grow * C + col0);
 #pragma unroll
-        for (int j = 0; j < NC / 4; ++j) xr[j] = __ldcs(xp + j);
+        for (int j = 0; j < NC / 8; ++j) ldg256_cs(x1 + grow * C + col0 + 8 * j, xr[j]);
         if (rs_attn) rs = rs_attn[grow];
       }
       mbar_wait(bar(21 + ab), tph);
@@ -537,13 +548,17 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) proj_mlp_fused_kernel(
 #pragma unroll
       for (int j = 0; j < NC; ++j) f[j] = (__uint_as_float(v[j]) + bps[col0 + j]) * rs;
 #pragma unroll
-      for (int j = 0; j < NC / 4; ++j) {
-        f[4 * j] += xr[j].x; f[4 * j + 1] += xr[j].y; f[4 * j + 2] += xr[j].z; f[4 * j + 3] += xr[j].w;
-      }
-      if (grow < n) {
-        float4* op = reinterpret_cast<float4*>(res_out + grow * C + col0);
+      for (int j = 0; j < NC / 8; ++j)
 #pragma unroll
-        for (int j = 0; j < NC / 4; ++j) op[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        for (int q = 0; q < 8; ++q) f[8 * j + q] += xr[j][q];
+      if (grow < n) {
+#pragma unroll
+        for (int j = 0; j < NC / 8; ++j) {
+          float o8[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) o8[q] = f[8 * j + q];
+          stg256(res_out + grow * C + col0 + 8 * j, o8);
+        }
       }
       float sum = 0.f, sq = 0.f;
 #pragma unroll
@@ -610,14 +625,15 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) proj_mlp_fused_kernel(
     auto epilogue2 = [&](int i) {   // D2 -> + b2, x rs_m, + x2 (read back from res_out) -> fp32 stream + bf16 copy
       const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
       const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
-      float4 rres[NC / 4];
+      float rres[NC / 8][8];
 #pragma unroll
-      for (int j = 0; j < NC / 4; ++j) rres[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j = 0; j < NC / 8; ++j)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) rres[j][q] = 0.f;
       float rs = 1.f;
       if (grow < n) {
-        const float4* rp = reinterpret_cast<const float4*>(res_out + grow * C + col0);   // this thread's own E0 store
 #pragma unroll
-        for (int j = 0; j < NC / 4; ++j) rres[j] = rp[j];
+        for (int j = 0; j < NC / 8; ++j) ldg256_cs(res_out + grow * C + col0 + 8 * j, rres[j]);   // this thread's own E0 store
         if (rs_mlp) rs = rs_mlp[grow];
       }
       mbar_wait(bar(13 + ab), tph);
@@ -634,18 +650,22 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) proj_mlp_fused_kernel(
 #pragma unroll
         for (int j = 0; j < NC; ++j) f[j] = (__uint_as_float(v[j]) + b2s[col0 + j]) * rs;
 #pragma unroll
-        for (int j = 0; j < NC / 4; ++j) {
-          f[4 * j] += rres[j].x; f[4 * j + 1] += rres[j].y; f[4 * j + 2] += rres[j].z; f[4 * j + 3] += rres[j].w;
+        for (int j = 0; j < NC / 8; ++j) {
+          float o8[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) o8[q] = f[8 * j + q] += rres[j][q];
+          stg256(res_out + grow * C + col0 + 8 * j, o8);
         }
-        float4* op = reinterpret_cast<float4*>(res_out + grow * C + col0);
-#pragma unroll
-        for (int j = 0; j < NC / 4; ++j) op[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
         if (out_bf16) {
-          uint4* ob = reinterpret_cast<uint4*>(out_bf16 + grow * C + col0);
+          if constexpr (NC == 16) {
+            uint32_t pk8[8];
 #pragma unroll
-          for (int j = 0; j < NC / 8; ++j)
-            ob[j] = make_uint4(pack2(f[8 * j], f[8 * j + 1]), pack2(f[8 * j + 2], f[8 * j + 3]),
-                               pack2(f[8 * j + 4], f[8 * j + 5]), pack2(f[8 * j + 6], f[8 * j + 7]));
+            for (int q = 0; q < 8; ++q) pk8[q] = pack2(f[2 * q], f[2 * q + 1]);
+            stg256_u32(out_bf16 + grow * C + col0, pk8);
+          } else {
+            *reinterpret_cast<uint4*>(out_bf16 + grow * C + col0) =
+                make_uint4(pack2(f[0], f[1]), pack2(f[2], f[3]), pack2(f[4], f[5]), pack2(f[6], f[7]));
+          }
         }
       }
     };
@@ -691,7 +711,283 @@ static int launch_proj_mlp(const __nv_bfloat16* a, const __nv_bfloat16* wpp, con
   return check_launch();
 }
 
-bool mlp_fused_supported(int c, int hidden) { return (c == 32 || c == 64) && hidden == 4 * c; }
+// ---------------------------------------------------------------------------------------------------------------
+// The same MLP for C = 128 (hidden 512), round 2: the two weight matrices (2 x 128 KB) do not fit in shared memory, so
+// they are STREAMED: per hidden block hb the 32 KB images W1[hb] (128 hidden rows x K = 128) and W2[:, hb] (128 output
+// rows x K = 128) travel through a 3-slot ring, fetched from L2 by one bulk copy each in exactly the order the issuer
+// consumes them (fc1(0) fc1(1) | fc1(t+2) fc2(t) ...).  X tile single-buffered (2 K-blocks), GELU tile double-buffered,
+// D1 2 x 128 + D2 2 x 128 = all 512 TMEM columns.  Replaces cuBLASLt fc1 + gelu_bf16_kernel + cuBLASLt fc2 +
+// ln_residual (40 C bytes per row through HBM) by 12 C.
+// ---------------------------------------------------------------------------------------------------------------
+namespace mlps {
+constexpr int C = 128, HID = 512, HB = 128, NHB = HID / HB, TM = 128;
+constexpr int THREADS = 640, LOADERS = 64, EPI = 512;
+constexpr int WBLK = 32768, NSLOT = 3;
+constexpr int RING_OFF = 0;
+constexpr int A1_OFF = RING_OFF + NSLOT * WBLK;        // [2 K-blocks][128 rows][64]
+constexpr int A2_OFF = A1_OFF + 32768;                 // 2 x [2 K-blocks][128 rows][64]
+constexpr int BIAS_OFF = A2_OFF + 2 * 32768;           // b1 (512) | b2 (128)
+constexpr int BAR_OFF = BIAS_OFF + (HID + C) * 4;
+constexpr int DYN_BYTES = BAR_OFF + 256;               // no alignment slack: the dynamic array is declared __align__(1024)
+// barriers: 0-3 w_full | 4-7 w_free | 8 a1_full | 9 a1_free | 10,11 d1_full | 12,13 d1_free | 14,15 a2_full | 16,17 a2_free
+//           | 18,19 d2_full | 20,21 d2_free
+}  // namespace mlps
+
+__global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
+    const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w1p, const float* __restrict__ b1,
+    const __nv_bfloat16* __restrict__ w2p, const float* __restrict__ b2, const float* __restrict__ residual,
+    const float* __restrict__ row_scale, int64_t n, int n_tiles, float* __restrict__ res_out,
+    __nv_bfloat16* __restrict__ out_bf16, int dbg) {
+  using namespace mlps;
+  using mlp::gelu_erf;
+  using mlp::pack2;
+  extern __shared__ __align__(1024) uint8_t smem_aligned[];
+  uint8_t* smem = smem_aligned;
+  const uint32_t sb = smem_u32(smem);
+  if (sb & 1023u) __trap();      // the swizzled operand layouts need the 1024-byte alignment the declaration asks for
+  auto bar = [&](int id) { return sb + BAR_OFF + 8u * (uint32_t)id; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_OFF + 240);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int T = my_tiles * NHB;
+
+  if (tid == 0) {
+    for (int s = 0; s < NSLOT; ++s) { mbar_init(bar(s), 1); mbar_init(bar(4 + s), 1); }
+    mbar_init(bar(8), LOADERS); mbar_init(bar(9), 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(bar(10 + b), 1);   mbar_init(bar(12 + b), EPI);
+      mbar_init(bar(14 + b), EPI); mbar_init(bar(16 + b), 1);
+      mbar_init(bar(18 + b), 1);  mbar_init(bar(20 + b), EPI);
+    }
+    mbar_fence_init();
+  }
+  for (int j = tid; j < HID + C; j += THREADS)
+    reinterpret_cast<float*>(smem + BIAS_OFF)[j] = j < HID ? b1[j] : b2[j - HID];
+  if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp < 2) {
+    // =========================== X tile loaders ===========================
+    const int c = tid & 15, r0 = tid >> 4;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
+      mbar_wait(bar(9), ((uint32_t)i & 1u) ^ 1u);
+      const uint32_t a1 = sb + A1_OFF + (c >> 3) * 16384;
+#pragma unroll 8
+      for (int q = 0; q < 32; ++q) {
+        const int r = r0 + 4 * q;
+        const uint32_t dst = a1 + (r >> 3) * 1024 + (r & 7) * 128 + (((c & 7) ^ (r & 7)) << 4);
+        if (dbg & 4) continue;
+        if (row0 + r < n) cp_async16(dst, x + (row0 + r) * C + c * 8, 16u);
+        else st_shared_zero16(dst);
+      }
+      cp_async_commit();
+      cp_async_wait<0>();
+      fence_proxy_async();
+      mbar_arrive(bar(8));
+    }
+  } else if (warp == 3) {
+    // =========================== weight streamer (one thread) ===========================
+    // same sequence as the issuer: fc1(0) fc1(1) | fc1(t+2) fc2(t) ...
+    if (lane == 0) {
+      uint32_t gi = 0;
+      auto fetch = [&](const __nv_bfloat16* base, int hb) {
+        const uint32_t slot = gi % NSLOT, ph = (gi / NSLOT) & 1u;
+        mbar_wait(bar(4 + slot), ph ^ 1u);
+        const uint32_t bytes = (dbg & 2) ? 16u : (uint32_t)WBLK;
+        mbar_arrive_expect_tx(bar(slot), bytes);
+        bulk_g2s(sb + RING_OFF + slot * WBLK, reinterpret_cast<const char*>(base) + (size_t)hb * WBLK, bytes, bar(slot));
+        ++gi;
+      };
+      if (T > 0) fetch(w1p, 0);
+      if (T > 1) fetch(w1p, 1 % NHB);
+      for (int t = 0; t < T; ++t) {
+        if (t + 2 < T) fetch(w1p, (t + 2) % NHB);
+        fetch(w2p, t % NHB);
+      }
+    }
+  } else if (warp == 2) {
+    // =========================== MMA issuer ===========================
+    constexpr uint32_t idesc = idesc_bf16_f32(TM, 128);
+    uint32_t gi = 0;
+    auto fc1 = [&](int t) {
+      const int it = t / NHB, hb = t - it * NHB;
+      const uint32_t bb = (uint32_t)t & 1u;
+      const uint32_t slot = gi % NSLOT, ph = (gi / NSLOT) & 1u;
+      ++gi;
+      if (hb == 0) mbar_wait(bar(8), (uint32_t)it & 1u);
+      mbar_wait(bar(12 + bb), (((uint32_t)t >> 1) & 1u) ^ 1u);
+      mbar_wait(bar(slot), ph);
+      fence_after_sync();
+#pragma unroll
+      for (int kb = 0; kb < 2; ++kb) {
+        const uint64_t a_desc = smem_desc_sw128(sb + A1_OFF + kb * 16384);
+        const uint64_t b_desc = smem_desc_sw128(sb + RING_OFF + slot * WBLK + kb * 16384);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (kb | kk) ? 1u : 0u);
+      }
+      mma_commit(bar(10 + bb));
+      mma_commit(bar(4 + slot));
+      if (hb == NHB - 1) mma_commit(bar(9));
+    };
+    auto fc2 = [&](int t) {
+      const int it = t / NHB, h2 = t - it * NHB;
+      const uint32_t ab = (uint32_t)it & 1u, bb = (uint32_t)t & 1u;
+      const uint32_t slot = gi % NSLOT, ph = (gi / NSLOT) & 1u;
+      ++gi;
+      mbar_wait(bar(14 + bb), ((uint32_t)t >> 1) & 1u);
+      if (h2 == 0) mbar_wait(bar(20 + ab), ((uint32_t)(it >> 1) & 1u) ^ 1u);
+      mbar_wait(bar(slot), ph);
+      fence_after_sync();
+#pragma unroll
+      for (int kb = 0; kb < 2; ++kb) {
+        const uint64_t a_desc = smem_desc_sw128(sb + A2_OFF + bb * 32768 + kb * 16384);
+        const uint64_t b_desc = smem_desc_sw128(sb + RING_OFF + slot * WBLK + kb * 16384);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (h2 | kb | kk) ? 1u : 0u);
+      }
+      mma_commit(bar(16 + bb));
+      mma_commit(bar(4 + slot));
+      if (h2 == NHB - 1) mma_commit(bar(18 + ab));
+    };
+    if (elect_one_sync()) {
+      if (T > 0) fc1(0);
+      if (T > 1) fc1(1);
+      for (int t = 0; t < T; ++t) {
+        if (t + 2 < T) fc1(t + 2);
+        fc2(t);
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // =========================== epilogue warps ===========================
+    const int q4 = warp & 3, quarter = (warp - 4) >> 2;
+    const int row = q4 * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
+    auto gelu_step = [&](int hb, uint32_t e1) {
+      const uint32_t bb = e1 & 1u;
+      mbar_wait(bar(10 + bb), (e1 >> 1) & 1u);
+      fence_after_sync();
+      uint32_t v[32], pk[16];
+      const int col0 = quarter * 32;
+      tmem_ld32(tmem + lane_base + bb * HB + col0, v);
+      tmem_ld_wait();
+      fence_before_sync();
+      mbar_arrive(bar(12 + bb));
+      const float4* bp = reinterpret_cast<const float4*>(smem + BIAS_OFF) + (hb * HB + col0) / 4;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 bv = bp[j];
+        if (dbg & 1) {
+          pk[2 * j] = pack2(__uint_as_float(v[4 * j]) + bv.x, __uint_as_float(v[4 * j + 1]) + bv.y);
+          pk[2 * j + 1] = pack2(__uint_as_float(v[4 * j + 2]) + bv.z, __uint_as_float(v[4 * j + 3]) + bv.w);
+          continue;
+        }
+        pk[2 * j] = pack2(gelu_erf(__uint_as_float(v[4 * j]) + bv.x), gelu_erf(__uint_as_float(v[4 * j + 1]) + bv.y));
+        pk[2 * j + 1] =
+            pack2(gelu_erf(__uint_as_float(v[4 * j + 2]) + bv.z), gelu_erf(__uint_as_float(v[4 * j + 3]) + bv.w));
+      }
+      mbar_wait(bar(16 + bb), ((e1 >> 1) & 1u) ^ 1u);
+      const uint32_t prow = sb + A2_OFF + bb * 32768 + (quarter >> 1) * 16384 + (row >> 3) * 1024 + (row & 7) * 128;
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4)
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(
+                         prow + ((((quarter & 1) * 4 + c4) ^ (row & 7)) << 4)),
+                     "r"(pk[4 * c4]), "r"(pk[4 * c4 + 1]), "r"(pk[4 * c4 + 2]), "r"(pk[4 * c4 + 3])
+                     : "memory");
+      fence_proxy_async();
+      mbar_arrive(bar(14 + bb));
+    };
+    auto epilogue2 = [&](int i) {   // this thread: row `row`, columns quarter * 32 .. + 31, in two halves of 16
+      const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
+      const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
+      const int colq = quarter * 32;
+      // the residual row segment is requested BEFORE waiting for GEMM2: its HBM latency hides behind that wait
+      float rres[4][8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) rres[j][q] = 0.f;
+      float rs = 1.f;
+      if (grow < n) {
+        if (residual) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + colq + 8 * j, rres[j]);
+        }
+        if (row_scale) rs = row_scale[grow];
+      }
+      mbar_wait(bar(18 + ab), tph);
+      fence_after_sync();
+      uint32_t v[32];
+      tmem_ld32(tmem + lane_base + 256 + ab * C + colq, v);
+      tmem_ld_wait();
+      fence_before_sync();
+      mbar_arrive(bar(20 + ab));
+      if (grow < n) {
+        const float* b2s = reinterpret_cast<const float*>(smem + BIAS_OFF) + HID + colq;
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float f[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) f[q] = fmaf(__uint_as_float(v[8 * j + q]) + b2s[8 * j + q], rs, rres[j][q]);
+          if (res_out) stg256(res_out + grow * C + colq + 8 * j, f);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) pk[4 * j + q] = pack2(f[2 * q], f[2 * q + 1]);
+        }
+        if (out_bf16) {
+          uint32_t lo[8], hi[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) { lo[q] = pk[q]; hi[q] = pk[8 + q]; }
+          stg256_u32(out_bf16 + grow * C + colq, lo);
+          stg256_u32(out_bf16 + grow * C + colq + 16, hi);
+        }
+      }
+    };
+    uint32_t e1 = 0;
+    for (int i = 0; i <= my_tiles; ++i) {
+      if (i < my_tiles) gelu_step(0, e1++);
+      if (i >= 1) epilogue2(i - 1);
+      if (i < my_tiles)
+        for (int hb = 1; hb < NHB; ++hb) gelu_step(hb, e1++);
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<512>(tmem);
+}
+
+static int launch_mlp_stream(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const float* b1, const __nv_bfloat16* w2p,
+                             const float* b2, const float* residual, const float* row_scale, int64_t n, float* res_out,
+                             __nv_bfloat16* out_bf16, cudaStream_t st) {
+  static_assert(mlps::DYN_BYTES <= 232448, "shared memory budget");
+  static bool configured_dev[kMaxDeviceSlots] = {};
+  bool& configured = configured_dev[device_slot()];
+  if (!configured) {
+    if (cudaFuncSetAttribute(mlp_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mlps::DYN_BYTES) !=
+        cudaSuccess)
+      return PTV3_ELAUNCH;
+    configured = true;
+  }
+  const int n_tiles = (int)cdiv(n, mlps::TM);
+  const int g = n_tiles < kNumSMs ? n_tiles : kNumSMs;
+  static int dbg = -1;      // PTV3_MLP_STREAM_DBG: timing ablations (results wrong by design): 1 no GELU, 2 16-byte weight
+  if (dbg < 0) {            // fetches, 4 no X loads
+    const char* e = getenv("PTV3_MLP_STREAM_DBG");
+    dbg = e ? atoi(e) : 0;
+  }
+  mlp_stream_kernel<<<g, mlps::THREADS, mlps::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, row_scale, n, n_tiles,
+                                                               res_out, out_bf16, dbg);
+  return check_launch();
+}
+
+bool mlp_fused_supported(int c, int hidden) { return (c == 32 || c == 64 || c == 128) && hidden == 4 * c; }
 
 template <int C>
 static int launch_mlp(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const float* b1, const __nv_bfloat16* w2p,
@@ -744,6 +1040,10 @@ int ptv3_mlp_fused_rs(const void* x, const void* w1_packed, const float* b1, con
   if (n == 0) return PTV3_OK;
   if (!x || !w1_packed || !b1 || !w2_packed || !b2 || (!res_out && !out_bf16)) return PTV3_EINVAL;
   cudaStream_t st = as_stream(stream);
+  if (c == 128)
+    return launch_mlp_stream((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1,
+                             (const __nv_bfloat16*)w2_packed, b2, residual, row_scale, n, res_out,
+                             (__nv_bfloat16*)out_bf16, st);
   if (c == 32)
     return launch_mlp<32>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed,
                           b2, residual, row_scale, n, res_out, (__nv_bfloat16*)out_bf16, st);
@@ -756,7 +1056,7 @@ int ptv3_proj_mlp_fused(const void* a, const void* wproj_packed, const float* bp
                         const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
                         const float* rs_mlp, int64_t n, int c, int hidden, float* res_out, void* out_bf16,
                         void* stream) {
-  if (n < 0 || !mlp_fused_supported(c, hidden)) return n < 0 ? PTV3_EINVAL : PTV3_EUNSUPPORTED;
+  if (n < 0 || !mlp_fused_supported(c, hidden) || c > 64) return n < 0 ? PTV3_EINVAL : PTV3_EUNSUPPORTED;
   if (n == 0) return PTV3_OK;
   if (!a || !wproj_packed || !bproj || !x1 || !ln_gamma || !ln_beta || !w1_packed || !b1 || !w2_packed || !b2 ||
       !res_out || res_out == x1)

@@ -8,7 +8,10 @@ from ptv3_b200 import ops  # noqa: E402
 
 dev = torch.device("cuda", 0)
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 10
-for n, c in ((1165350, 32), (1165350, 64), (588256, 64)):
+shapes = ((1165350, 32), (1165350, 64), (588256, 64), (181696, 128), (588256, 128))
+if len(sys.argv) > 2:
+    shapes = ((int(sys.argv[2]), int(sys.argv[3])),)
+for n, c in shapes:
     x = torch.randn(n, c, device=dev).bfloat16()
     res = torch.randn(n, c, device=dev)
     w1 = (torch.randn(4 * c, c, device=dev) / c ** 0.5).bfloat16()

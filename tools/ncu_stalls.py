@@ -40,7 +40,7 @@ def main():
     byop = collections.defaultdict(collections.Counter)
     nexec = collections.Counter()
     for r in rows[hi + 1:]:
-        if len(r) < len(head):
+        if len(r) < len(head) or r[col["Source"]] == "Source":      # second kernel instance: header repeated
             continue
         s = r[col["Source"]].split()
         if not s:
