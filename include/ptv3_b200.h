@@ -283,13 +283,16 @@ int ptv3_attn_window_fwd(const void* qkv, int dtype, const int64_t* order /* NUL
 /* ---------------------------------------------------------------------------
  * A8  fused MLP of Block.forward (MLP.forward :225-248 + the residual add :337): one tcgen05 kernel for
  *   h = GELU_erf(x W1^T + b1);  f = h W2^T + b2;  r = residual ? residual + f : f
- *   res_out = r (fp32, optional), out_bf16 = bf16(r) (optional).  x (n,c) bf16; c in {32, 64}, hidden = 4c.
+ *   res_out = r (fp32, optional), out_bf16 = bf16(r) (optional).  x (n,c) bf16; c in {32, 64, 128, 256}, hidden = 4c
+ *   (c <= 64: both weights resident in shared memory; c >= 128: 32 KB weight blocks streamed through a 3-slot ring).
  * Weights are packed once with ptv3_pack_kmajor into K-blocked, 128-byte-swizzled shared-memory images:
- *   w1 (hidden, c) with tile_rows = 128;  w2 (c, hidden) with tile_rows = c.
+ *   w1 (hidden, c) with tile_rows = ptv3_mlp_fc1_tile_rows(c);  w2 (c, hidden) with tile_rows = c.
  * ------------------------------------------------------------------------- */
 size_t ptv3_pack_kmajor_bytes(int rows, int k);
 int ptv3_pack_kmajor(const void* w /* (rows,k) bf16 */, int rows, int k, int tile_rows, void* packed, void* stream);
 int ptv3_mlp_fused_supported(int c, int hidden);
+/* tile_rows to pack fc1's weight with (ptv3_pack_kmajor): the hidden-block width of the kernel for this c (128; 64 at c = 256) */
+int ptv3_mlp_fc1_tile_rows(int c);
 int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
                    const float* residual /* NULL ok */, int64_t n, int c, int hidden, float* res_out /* NULL ok */,
                    void* out_bf16 /* NULL ok */, void* stream);

@@ -72,6 +72,7 @@ SIGNATURES = {
     "ptv3_pack_kmajor_bytes": (c_sz, [c_int, c_int]),
     "ptv3_pack_kmajor": (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_vp]),
     "ptv3_mlp_fused_supported": (c_int, [c_int, c_int]),
+    "ptv3_mlp_fc1_tile_rows": (c_int, [c_int]),
     "ptv3_mlp_fused": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
     "ptv3_mlp_fused_rs": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_int, c_int, c_vp, c_vp, c_vp]),
     "ptv3_proj_mlp_fused": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_f32, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64,

@@ -720,37 +720,57 @@ static int launch_proj_mlp(const __nv_bfloat16* a, const __nv_bfloat16* wpp, con
 // ln_residual (40 C bytes per row through HBM) by 12 C.
 // ---------------------------------------------------------------------------------------------------------------
 namespace mlps {
-constexpr int C = 128, HID = 512, HB = 128, NHB = HID / HB, TM = 128;
-constexpr int THREADS = 640, LOADERS = 64, EPI = 512;
-constexpr int WBLK = 32768, NSLOT = 3;
-constexpr int RING_OFF = 0;
-constexpr int A1_OFF = RING_OFF + NSLOT * WBLK;        // [2 K-blocks][128 rows][64]
-constexpr int A2_OFF = A1_OFF + 32768;                 // 2 x [2 K-blocks][128 rows][64]
-constexpr int BIAS_OFF = A2_OFF + 2 * 32768;           // b1 (512) | b2 (128)
-constexpr int BAR_OFF = BIAS_OFF + (HID + C) * 4;
-constexpr int DYN_BYTES = BAR_OFF + 256;               // no alignment slack: the dynamic array is declared __align__(1024)
+constexpr int TM = 128, THREADS = 640, LOADERS = 64, EPI = 512, WBLK = 32768, NSLOT = 3;
+// C = 128: hidden blocks of 128 (GEMM1 N = 128, K = 128; GEMM2 N = 128, K = 128), D1 2 x 128 + D2 2 x 128 TMEM columns.
+// C = 256: hidden blocks of  64 (GEMM1 N =  64, K = 256; GEMM2 N = 256, K =  64), D1 2 x 64 + ONE D2 of 256 columns.
+// Either way a weight block is 32 KB and the ring holds three.
+template <int C>
+struct Cfg {
+  static constexpr int HID = 4 * C;
+  static constexpr int HB = C == 128 ? 128 : 64;
+  static constexpr int NHB = HID / HB;
+  static constexpr int KB1 = C / 64;                       // K-blocks of the X tile
+  static constexpr int KB2 = HB / 64;                      // K-blocks of the GELU tile
+  static constexpr bool D2_DOUBLE = C == 128;
+  static constexpr int A1_BYTES = TM * C * 2;
+  static constexpr int A2_BYTES = TM * HB * 2;
+  static constexpr int RING_OFF = 0;
+  static constexpr int A1_OFF = RING_OFF + NSLOT * WBLK;
+  static constexpr int A2_OFF = A1_OFF + A1_BYTES;
+  static constexpr int BIAS_OFF = A2_OFF + 2 * A2_BYTES;   // b1 (HID) | b2 (C)
+  static constexpr int BAR_OFF = BIAS_OFF + (HID + C) * 4;
+  static constexpr int DYN_BYTES = BAR_OFF + 256;          // no alignment slack: the dynamic array is declared __align__(1024)
+  static constexpr int GC = HB / 4;                        // hidden columns a thread handles per GELU step (32 / 16)
+  static_assert(HB * C * 2 == WBLK, "weight block size");
+};
 // barriers: 0-3 w_full | 4-7 w_free | 8 a1_full | 9 a1_free | 10,11 d1_full | 12,13 d1_free | 14,15 a2_full | 16,17 a2_free
 //           | 18,19 d2_full | 20,21 d2_free
 }  // namespace mlps
 
+template <int C>
 __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w1p, const float* __restrict__ b1,
     const __nv_bfloat16* __restrict__ w2p, const float* __restrict__ b2, const float* __restrict__ residual,
     const float* __restrict__ row_scale, int64_t n, int n_tiles, float* __restrict__ res_out,
     __nv_bfloat16* __restrict__ out_bf16, int dbg) {
   using namespace mlps;
+  using L = Cfg<C>;
   using mlp::gelu_erf;
   using mlp::pack2;
+  constexpr int HB = L::HB, NHB = L::NHB;
   extern __shared__ __align__(1024) uint8_t smem_aligned[];
   uint8_t* smem = smem_aligned;
   const uint32_t sb = smem_u32(smem);
   if (sb & 1023u) __trap();      // the swizzled operand layouts need the 1024-byte alignment the declaration asks for
-  auto bar = [&](int id) { return sb + BAR_OFF + 8u * (uint32_t)id; };
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_OFF + 240);
+  auto bar = [&](int id) { return sb + L::BAR_OFF + 8u * (uint32_t)id; };
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::BAR_OFF + 240);
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int my_tiles = (n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int T = my_tiles * NHB;
+  // D2 buffer / phase of tile `it`
+  auto d2_buf = [](int it) -> uint32_t { return L::D2_DOUBLE ? (uint32_t)it & 1u : 0u; };
+  auto d2_phase = [](int it) -> uint32_t { return L::D2_DOUBLE ? (uint32_t)(it >> 1) & 1u : (uint32_t)it & 1u; };
 
   if (tid == 0) {
     for (int s = 0; s < NSLOT; ++s) { mbar_init(bar(s), 1); mbar_init(bar(4 + s), 1); }
@@ -758,12 +778,12 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
     for (int b = 0; b < 2; ++b) {
       mbar_init(bar(10 + b), 1);   mbar_init(bar(12 + b), EPI);
       mbar_init(bar(14 + b), EPI); mbar_init(bar(16 + b), 1);
-      mbar_init(bar(18 + b), 1);  mbar_init(bar(20 + b), EPI);
+      mbar_init(bar(18 + b), 1);   mbar_init(bar(20 + b), EPI);
     }
     mbar_fence_init();
   }
-  for (int j = tid; j < HID + C; j += THREADS)
-    reinterpret_cast<float*>(smem + BIAS_OFF)[j] = j < HID ? b1[j] : b2[j - HID];
+  for (int j = tid; j < L::HID + C; j += THREADS)
+    reinterpret_cast<float*>(smem + L::BIAS_OFF)[j] = j < L::HID ? b1[j] : b2[j - L::HID];
   if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
   fence_before_sync();
   __syncthreads();
@@ -772,14 +792,16 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
 
   if (warp < 2) {
     // =========================== X tile loaders ===========================
-    const int c = tid & 15, r0 = tid >> 4;
+    constexpr int CH = C / 8;                       // 16-byte chunks per row
+    constexpr int RSTEP = LOADERS / CH;             // rows covered per pass
+    const int c = tid % CH, r0 = tid / CH;
     for (int i = 0; i < my_tiles; ++i) {
       const int64_t row0 = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM;
       mbar_wait(bar(9), ((uint32_t)i & 1u) ^ 1u);
-      const uint32_t a1 = sb + A1_OFF + (c >> 3) * 16384;
+      const uint32_t a1 = sb + L::A1_OFF + (c >> 3) * 16384;
 #pragma unroll 8
-      for (int q = 0; q < 32; ++q) {
-        const int r = r0 + 4 * q;
+      for (int q = 0; q < TM / RSTEP; ++q) {
+        const int r = r0 + RSTEP * q;
         const uint32_t dst = a1 + (r >> 3) * 1024 + (r & 7) * 128 + (((c & 7) ^ (r & 7)) << 4);
         if (dbg & 4) continue;
         if (row0 + r < n) cp_async16(dst, x + (row0 + r) * C + c * 8, 16u);
@@ -800,7 +822,7 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
         mbar_wait(bar(4 + slot), ph ^ 1u);
         const uint32_t bytes = (dbg & 2) ? 16u : (uint32_t)WBLK;
         mbar_arrive_expect_tx(bar(slot), bytes);
-        bulk_g2s(sb + RING_OFF + slot * WBLK, reinterpret_cast<const char*>(base) + (size_t)hb * WBLK, bytes, bar(slot));
+        bulk_g2s(sb + L::RING_OFF + slot * WBLK, reinterpret_cast<const char*>(base) + (size_t)hb * WBLK, bytes, bar(slot));
         ++gi;
       };
       if (T > 0) fetch(w1p, 0);
@@ -812,7 +834,7 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
     }
   } else if (warp == 2) {
     // =========================== MMA issuer ===========================
-    constexpr uint32_t idesc = idesc_bf16_f32(TM, 128);
+    constexpr uint32_t idesc1 = idesc_bf16_f32(TM, HB), idesc2 = idesc_bf16_f32(TM, C);
     uint32_t gi = 0;
     auto fc1 = [&](int t) {
       const int it = t / NHB, hb = t - it * NHB;
@@ -824,12 +846,12 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
       mbar_wait(bar(slot), ph);
       fence_after_sync();
 #pragma unroll
-      for (int kb = 0; kb < 2; ++kb) {
-        const uint64_t a_desc = smem_desc_sw128(sb + A1_OFF + kb * 16384);
-        const uint64_t b_desc = smem_desc_sw128(sb + RING_OFF + slot * WBLK + kb * 16384);
+      for (int kb = 0; kb < L::KB1; ++kb) {      // W1 block: [KB1 K-blocks][HB rows][64]
+        const uint64_t a_desc = smem_desc_sw128(sb + L::A1_OFF + kb * 16384);
+        const uint64_t b_desc = smem_desc_sw128(sb + L::RING_OFF + slot * WBLK + kb * (HB * 128));
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (kb | kk) ? 1u : 0u);
+          mma_bf16_ss(tmem + bb * HB, a_desc + 2 * kk, b_desc + 2 * kk, idesc1, (kb | kk) ? 1u : 0u);
       }
       mma_commit(bar(10 + bb));
       mma_commit(bar(4 + slot));
@@ -837,20 +859,20 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
     };
     auto fc2 = [&](int t) {
       const int it = t / NHB, h2 = t - it * NHB;
-      const uint32_t ab = (uint32_t)it & 1u, bb = (uint32_t)t & 1u;
+      const uint32_t ab = d2_buf(it), bb = (uint32_t)t & 1u;
       const uint32_t slot = gi % NSLOT, ph = (gi / NSLOT) & 1u;
       ++gi;
       mbar_wait(bar(14 + bb), ((uint32_t)t >> 1) & 1u);
-      if (h2 == 0) mbar_wait(bar(20 + ab), ((uint32_t)(it >> 1) & 1u) ^ 1u);
+      if (h2 == 0) mbar_wait(bar(20 + ab), d2_phase(it) ^ 1u);
       mbar_wait(bar(slot), ph);
       fence_after_sync();
 #pragma unroll
-      for (int kb = 0; kb < 2; ++kb) {
-        const uint64_t a_desc = smem_desc_sw128(sb + A2_OFF + bb * 32768 + kb * 16384);
-        const uint64_t b_desc = smem_desc_sw128(sb + RING_OFF + slot * WBLK + kb * 16384);
+      for (int kb = 0; kb < L::KB2; ++kb) {      // W2 block: [KB2 K-blocks][C rows][64]
+        const uint64_t a_desc = smem_desc_sw128(sb + L::A2_OFF + bb * L::A2_BYTES + kb * 16384);
+        const uint64_t b_desc = smem_desc_sw128(sb + L::RING_OFF + slot * WBLK + kb * (C * 128));
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc, (h2 | kb | kk) ? 1u : 0u);
+          mma_bf16_ss(tmem + 256 + ab * C, a_desc + 2 * kk, b_desc + 2 * kk, idesc2, (h2 | kb | kk) ? 1u : 0u);
       }
       mma_commit(bar(16 + bb));
       mma_commit(bar(4 + slot));
@@ -871,18 +893,20 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
     const int row = q4 * 32 + lane;
     const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
     auto gelu_step = [&](int hb, uint32_t e1) {
+      constexpr int GC = L::GC;
       const uint32_t bb = e1 & 1u;
       mbar_wait(bar(10 + bb), (e1 >> 1) & 1u);
       fence_after_sync();
-      uint32_t v[32], pk[16];
-      const int col0 = quarter * 32;
-      tmem_ld32(tmem + lane_base + bb * HB + col0, v);
+      uint32_t v[GC], pk[GC / 2];
+      const int col0 = quarter * GC;
+      if constexpr (GC == 32) tmem_ld32(tmem + lane_base + bb * HB + col0, v);
+      else tmem_ld16(tmem + lane_base + bb * HB + col0, v);
       tmem_ld_wait();
       fence_before_sync();
       mbar_arrive(bar(12 + bb));
-      const float4* bp = reinterpret_cast<const float4*>(smem + BIAS_OFF) + (hb * HB + col0) / 4;
+      const float4* bp = reinterpret_cast<const float4*>(smem + L::BIAS_OFF) + (hb * HB + col0) / 4;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
+      for (int j = 0; j < GC / 4; ++j) {
         const float4 bv = bp[j];
         if (dbg & 1) {
           pk[2 * j] = pack2(__uint_as_float(v[4 * j]) + bv.x, __uint_as_float(v[4 * j + 1]) + bv.y);
@@ -894,21 +918,25 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
             pack2(gelu_erf(__uint_as_float(v[4 * j + 2]) + bv.z), gelu_erf(__uint_as_float(v[4 * j + 3]) + bv.w));
       }
       mbar_wait(bar(16 + bb), ((e1 >> 1) & 1u) ^ 1u);
-      const uint32_t prow = sb + A2_OFF + bb * 32768 + (quarter >> 1) * 16384 + (row >> 3) * 1024 + (row & 7) * 128;
+      // my GC hidden columns = GC / 8 16-byte chunks, chunk index col0 / 8 + c4 inside the 64-column K-blocks of the tile
+      const uint32_t prow = sb + L::A2_OFF + bb * L::A2_BYTES + (row >> 3) * 1024 + (row & 7) * 128;
 #pragma unroll
-      for (int c4 = 0; c4 < 4; ++c4)
-        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(
-                         prow + ((((quarter & 1) * 4 + c4) ^ (row & 7)) << 4)),
+      for (int c4 = 0; c4 < GC / 8; ++c4) {
+        const int chunk = col0 / 8 + c4;
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (chunk >> 3) * 16384 +
+                                                                     (((chunk & 7) ^ (row & 7)) << 4)),
                      "r"(pk[4 * c4]), "r"(pk[4 * c4 + 1]), "r"(pk[4 * c4 + 2]), "r"(pk[4 * c4 + 3])
                      : "memory");
+      }
       fence_proxy_async();
       mbar_arrive(bar(14 + bb));
     };
-    auto epilogue2 = [&](int i) {   // this thread: row `row`, columns quarter * 32 .. + 31, in two halves of 16
-      const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
+    auto epilogue2 = [&](int i) {   // this thread: row `row`, columns quarter * (C / 4) .., in pieces of 32
+      constexpr int PIECES = C / 128;
+      const uint32_t ab = d2_buf(i), tph = d2_phase(i);
       const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
-      const int colq = quarter * 32;
-      // the residual row segment is requested BEFORE waiting for GEMM2: its HBM latency hides behind that wait
+      const int colq = quarter * (C / 4);
+      // the first piece of the residual row segment is requested BEFORE waiting for GEMM2 (latency hides behind the wait)
       float rres[4][8];
 #pragma unroll
       for (int j = 0; j < 4; ++j)
@@ -924,29 +952,45 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
       }
       mbar_wait(bar(18 + ab), tph);
       fence_after_sync();
-      uint32_t v[32];
-      tmem_ld32(tmem + lane_base + 256 + ab * C + colq, v);
-      tmem_ld_wait();
-      fence_before_sync();
-      mbar_arrive(bar(20 + ab));
-      if (grow < n) {
-        const float* b2s = reinterpret_cast<const float*>(smem + BIAS_OFF) + HID + colq;
-        uint32_t pk[16];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          float f[8];
+      for (int pc = 0; pc < PIECES; ++pc) {
+        const int col0 = colq + 32 * pc;
+        if (pc > 0) {
 #pragma unroll
-          for (int q = 0; q < 8; ++q) f[q] = fmaf(__uint_as_float(v[8 * j + q]) + b2s[8 * j + q], rs, rres[j][q]);
-          if (res_out) stg256(res_out + grow * C + colq + 8 * j, f);
+          for (int j = 0; j < 4; ++j)
 #pragma unroll
-          for (int q = 0; q < 4; ++q) pk[4 * j + q] = pack2(f[2 * q], f[2 * q + 1]);
+            for (int q = 0; q < 8; ++q) rres[j][q] = 0.f;
+          if (residual && grow < n) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + col0 + 8 * j, rres[j]);
+          }
         }
-        if (out_bf16) {
-          uint32_t lo[8], hi[8];
+        uint32_t v[32];
+        tmem_ld32(tmem + lane_base + 256 + ab * C + col0, v);
+        tmem_ld_wait();
+        if (pc == PIECES - 1) {
+          fence_before_sync();
+          mbar_arrive(bar(20 + ab));
+        }
+        if (grow < n) {
+          const float* b2s = reinterpret_cast<const float*>(smem + L::BIAS_OFF) + L::HID + col0;
+          uint32_t pk[16];
 #pragma unroll
-          for (int q = 0; q < 8; ++q) { lo[q] = pk[q]; hi[q] = pk[8 + q]; }
-          stg256_u32(out_bf16 + grow * C + colq, lo);
-          stg256_u32(out_bf16 + grow * C + colq + 16, hi);
+          for (int j = 0; j < 4; ++j) {
+            float f[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) f[q] = fmaf(__uint_as_float(v[8 * j + q]) + b2s[8 * j + q], rs, rres[j][q]);
+            if (res_out) stg256(res_out + grow * C + col0 + 8 * j, f);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) pk[4 * j + q] = pack2(f[2 * q], f[2 * q + 1]);
+          }
+          if (out_bf16) {
+            uint32_t lo[8], hi[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) { lo[q] = pk[q]; hi[q] = pk[8 + q]; }
+            stg256_u32(out_bf16 + grow * C + col0, lo);
+            stg256_u32(out_bf16 + grow * C + col0 + 16, hi);
+          }
         }
       }
     };
@@ -963,14 +1007,16 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
   if (warp == 2) tmem_dealloc<512>(tmem);
 }
 
+template <int C>
 static int launch_mlp_stream(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const float* b1, const __nv_bfloat16* w2p,
                              const float* b2, const float* residual, const float* row_scale, int64_t n, float* res_out,
                              __nv_bfloat16* out_bf16, cudaStream_t st) {
-  static_assert(mlps::DYN_BYTES <= 232448, "shared memory budget");
+  using L = mlps::Cfg<C>;
+  static_assert(L::DYN_BYTES <= 232448, "shared memory budget");
   static bool configured_dev[kMaxDeviceSlots] = {};
   bool& configured = configured_dev[device_slot()];
   if (!configured) {
-    if (cudaFuncSetAttribute(mlp_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mlps::DYN_BYTES) !=
+    if (cudaFuncSetAttribute(mlp_stream_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::DYN_BYTES) !=
         cudaSuccess)
       return PTV3_ELAUNCH;
     configured = true;
@@ -982,12 +1028,15 @@ static int launch_mlp_stream(const __nv_bfloat16* x, const __nv_bfloat16* w1p, c
     const char* e = getenv("PTV3_MLP_STREAM_DBG");
     dbg = e ? atoi(e) : 0;
   }
-  mlp_stream_kernel<<<g, mlps::THREADS, mlps::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, row_scale, n, n_tiles,
-                                                               res_out, out_bf16, dbg);
+  mlp_stream_kernel<C><<<g, mlps::THREADS, L::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, row_scale, n, n_tiles,
+                                                                 res_out, out_bf16, dbg);
   return check_launch();
 }
 
-bool mlp_fused_supported(int c, int hidden) { return (c == 32 || c == 64 || c == 128) && hidden == 4 * c; }
+// rows per packing tile of fc1's weight (ptv3_pack_kmajor tile_rows): the hidden-block width of the kernel that will read it
+int mlp_fc1_tile_rows(int c) { return c == 256 ? 64 : 128; }
+
+bool mlp_fused_supported(int c, int hidden) { return (c == 32 || c == 64 || c == 128 || c == 256) && hidden == 4 * c; }
 
 template <int C>
 static int launch_mlp(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const float* b1, const __nv_bfloat16* w2p,
@@ -1028,6 +1077,8 @@ int ptv3_pack_kmajor(const void* w, int rows, int k, int tile_rows, void* packed
 
 int ptv3_mlp_fused_supported(int c, int hidden) { return mlp_fused_supported(c, hidden) ? 1 : 0; }
 
+int ptv3_mlp_fc1_tile_rows(int c) { return mlp_fc1_tile_rows(c); }
+
 int ptv3_mlp_fused(const void* x, const void* w1_packed, const float* b1, const void* w2_packed, const float* b2,
                    const float* residual, int64_t n, int c, int hidden, float* res_out, void* out_bf16, void* stream) {
   return ptv3_mlp_fused_rs(x, w1_packed, b1, w2_packed, b2, residual, nullptr, n, c, hidden, res_out, out_bf16, stream);
@@ -1041,9 +1092,13 @@ int ptv3_mlp_fused_rs(const void* x, const void* w1_packed, const float* b1, con
   if (!x || !w1_packed || !b1 || !w2_packed || !b2 || (!res_out && !out_bf16)) return PTV3_EINVAL;
   cudaStream_t st = as_stream(stream);
   if (c == 128)
-    return launch_mlp_stream((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1,
-                             (const __nv_bfloat16*)w2_packed, b2, residual, row_scale, n, res_out,
-                             (__nv_bfloat16*)out_bf16, st);
+    return launch_mlp_stream<128>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1,
+                                  (const __nv_bfloat16*)w2_packed, b2, residual, row_scale, n, res_out,
+                                  (__nv_bfloat16*)out_bf16, st);
+  if (c == 256)
+    return launch_mlp_stream<256>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1,
+                                  (const __nv_bfloat16*)w2_packed, b2, residual, row_scale, n, res_out,
+                                  (__nv_bfloat16*)out_bf16, st);
   if (c == 32)
     return launch_mlp<32>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w1_packed, b1, (const __nv_bfloat16*)w2_packed,
                           b2, residual, row_scale, n, res_out, (__nv_bfloat16*)out_bf16, st);

@@ -348,9 +348,12 @@ __global__ void __launch_bounds__(kConvThreads, 1) subm_conv_tc_kernel(const __n
             __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
             pk[q] = *reinterpret_cast<uint32_t*>(&h);
           }
-          uint4* dst = reinterpret_cast<uint4*>(out + row * c_out + co0);
+          // two 256-bit stores: a whole 32-byte sector per lane and instruction (16-byte stores touch every sector twice)
+          uint32_t lo[8], hi[8];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) dst[q] = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+          for (int q = 0; q < 8; ++q) { lo[q] = pk[q]; hi[q] = pk[8 + q]; }
+          stg256_u32(out + row * c_out + co0, lo);
+          stg256_u32(out + row * c_out + co0 + 16, hi);
         }
       }
     }

@@ -382,7 +382,7 @@ class Block(PointModule):
                      norm2_g=self.norm2[0].weight.float().contiguous(), norm2_b=self.norm2[0].bias.float().contiguous(),
                      qkv_w=lw(attn.qkv), qkv_b=lb(attn.qkv), proj_w=lw(attn.proj, g1), proj_b=lb(attn.proj, g1))
             if fused:
-                t.update(fc1_w=ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), fc1_b=mlp.fc1.bias.float().contiguous(),
+                t.update(fc1_w=ops.pack_kmajor(mlp.fc1.weight.to(cd), ops.mlp_fc1_tile_rows(c)), fc1_b=mlp.fc1.bias.float().contiguous(),
                          fc2_w=ops.pack_kmajor(lw(mlp.fc2, g2), c), fc2_b=sc(mlp.fc2.bias, g2).contiguous())
                 # proj + LN + MLP as one kernel.  Measured (profiles/r02_fusions.md): a win at C = 32 (0.64 vs 0.79 ms for
                 # the two stage-0 blocks), a loss at C = 64 (2.64 vs 2.37 ms over six blocks): the MLP's epilogue warps
@@ -478,7 +478,7 @@ class Block(PointModule):
             # fc1 -> GELU -> fc2 -> + residual in one tcgen05 kernel: the (N, 4C) hidden activation stays on the SM
             w1p, b1, w2p, b2 = _cached(
                 self, "mlp_packed", [mlp.fc1.weight, mlp.fc1.bias, mlp.fc2.weight, mlp.fc2.bias, ls2],
-                lambda: (ops.pack_kmajor(mlp.fc1.weight.to(cd), 128), mlp.fc1.bias.float().contiguous(),
+                lambda: (ops.pack_kmajor(mlp.fc1.weight.to(cd), ops.mlp_fc1_tile_rows(self.channels)), mlp.fc1.bias.float().contiguous(),
                          ops.pack_kmajor(self._lin(mlp.fc2, cd, ls2)[0], self.channels),
                          (mlp.fc2.bias.float() * (ls2.float() if ls2 is not None else 1.0)).contiguous()))
             x, xcd = ops.mlp_fused(h, w1p, b1, w2p, b2, hidden, residual=x,

@@ -357,6 +357,11 @@ def pack_kmajor(w, tile_rows):
     return packed
 
 
+def mlp_fc1_tile_rows(c):
+    """tile_rows for pack_kmajor of fc1's weight (the hidden-block width of the fused-MLP kernel for this width)."""
+    return int(_lib.load().ptv3_mlp_fc1_tile_rows(int(c)))
+
+
 def mlp_fused_supported(c, hidden):
     return bool(_lib.load().ptv3_mlp_fused_supported(int(c), int(hidden)))
 

@@ -160,7 +160,8 @@ def test_subm_conv_tcgen05_many_tiles(cin, cout):
 
 
 @pytest.mark.parametrize("c,n", [(32, 1000), (64, 777), (32, 148 * 128 * 2 + 5), (64, 148 * 128 * 3 + 129), (128, 1),
-                                 (128, 1000), (128, 148 * 128 * 3 + 129), (128, 148 * 128 + 1)])
+                                 (128, 1000), (128, 148 * 128 * 3 + 129), (128, 148 * 128 + 1), (256, 1), (256, 3000),
+                                 (256, 148 * 128 * 3 + 129)])
 def test_mlp_fused_tcgen05(c, n):
     """fc1 -> GELU(erf) -> fc2 (+ residual) in one tcgen05 kernel against the torch fp32 reference on the same
     bf16-rounded operands (hidden activation rounded to bf16 like the reference under autocast): rel-L2 <= 4e-3."""
@@ -175,8 +176,8 @@ def test_mlp_fused_tcgen05(c, n):
     res = torch.randn(n, c)
     hid = F.gelu(x.float() @ w1.float().t() + b1).bfloat16().float()
     ref = hid @ w2.float().t() + b2
-    assert ops.mlp_fused_supported(c, h) and not ops.mlp_fused_supported(256, 1024)
-    w1p, w2p = ops.pack_kmajor(w1.cuda(), 128), ops.pack_kmajor(w2.cuda(), c)
+    assert ops.mlp_fused_supported(c, h) and not ops.mlp_fused_supported(512, 2048)
+    w1p, w2p = ops.pack_kmajor(w1.cuda(), ops.mlp_fc1_tile_rows(c)), ops.pack_kmajor(w2.cuda(), c)
     r, r16 = ops.mlp_fused(x.cuda(), w1p, b1.cuda(), w2p, b2.cuda(), h, residual=res.cuda())
     assert rel_l2(r - res.cuda(), ref) < 4e-3, rel_l2(r - res.cuda(), ref)
     assert torch.equal(r16, r.bfloat16())

@@ -8,7 +8,7 @@ from ptv3_b200 import ops  # noqa: E402
 
 dev = torch.device("cuda", 0)
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 10
-shapes = ((1165350, 32), (1165350, 64), (588256, 64), (181696, 128), (588256, 128))
+shapes = ((1165350, 32), (1165350, 64), (588256, 64), (181696, 128), (588256, 128), (47616, 256), (181696, 256))
 if len(sys.argv) > 2:
     shapes = ((int(sys.argv[2]), int(sys.argv[3])),)
 for n, c in shapes:
@@ -17,7 +17,7 @@ for n, c in shapes:
     w1 = (torch.randn(4 * c, c, device=dev) / c ** 0.5).bfloat16()
     w2 = (torch.randn(c, 4 * c, device=dev) / (4 * c) ** 0.5).bfloat16()
     b1, b2 = torch.randn(4 * c, device=dev) * 0.1, torch.randn(c, device=dev) * 0.1
-    w1p, w2p = ops.pack_kmajor(w1, 128), ops.pack_kmajor(w2, c)
+    w1p, w2p = ops.pack_kmajor(w1, ops.mlp_fc1_tile_rows(c)), ops.pack_kmajor(w2, c)
     for _ in range(3):
         r, o = ops.mlp_fused(x, w1p, b1, w2p, b2, 4 * c, residual=res)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
