@@ -720,7 +720,8 @@ static int launch_proj_mlp(const __nv_bfloat16* a, const __nv_bfloat16* wpp, con
 // ln_residual (40 C bytes per row through HBM) by 12 C.
 // ---------------------------------------------------------------------------------------------------------------
 namespace mlps {
-constexpr int TM = 128, THREADS = 640, LOADERS = 64, EPI = 512, WBLK = 32768, NSLOT = 3;
+constexpr int TM = 128, THREADS = 768, LOADERS = 64, EPI = 512, OUTW = 128, WBLK = 32768, NSLOT = 3;
+// warps: 0-1 X loaders | 2 MMA issuer (+ TMEM alloc) | 3 weight streamer | 4-19 GELU epilogue | 20-23 output epilogue
 // C = 128: hidden blocks of 128 (GEMM1 N = 128, K = 128; GEMM2 N = 128, K = 128), D1 2 x 128 + D2 2 x 128 TMEM columns.
 // C = 256: hidden blocks of  64 (GEMM1 N =  64, K = 256; GEMM2 N = 256, K =  64), D1 2 x 64 + ONE D2 of 256 columns.
 // Either way a weight block is 32 KB and the ring holds three.
@@ -778,7 +779,7 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
     for (int b = 0; b < 2; ++b) {
       mbar_init(bar(10 + b), 1);   mbar_init(bar(12 + b), EPI);
       mbar_init(bar(14 + b), EPI); mbar_init(bar(16 + b), 1);
-      mbar_init(bar(18 + b), 1);   mbar_init(bar(20 + b), EPI);
+      mbar_init(bar(18 + b), 1);   mbar_init(bar(20 + b), OUTW);
     }
     mbar_fence_init();
   }
@@ -887,8 +888,10 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
       }
     }
     __syncwarp();
-  } else if (warp >= 4) {
+  } else {
     // =========================== epilogue warps ===========================
+    // 16 GELU warps (D1 -> A2) and 4 OUTPUT warps (D2 -> HBM).  On the same warps the output epilogue's HBM round trip
+    // (residual read, stores) stalled the GELU steps of the next tile: 36 % of the kernel (timing ablation 8).
     const int q4 = warp & 3, quarter = (warp - 4) >> 2;
     const int row = q4 * 32 + lane;
     const uint32_t lane_base = (uint32_t)(q4 * 32) << 16;
@@ -931,40 +934,34 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
       fence_proxy_async();
       mbar_arrive(bar(14 + bb));
     };
-    auto epilogue2 = [&](int i) {   // this thread: row `row`, columns quarter * (C / 4) .., in pieces of 32
-      constexpr int PIECES = C / 128;
+    auto epilogue2 = [&](int i) {   // output warps: this thread owns row `row` and walks all C columns in pieces of 32
+      constexpr int PIECES = C / 32;
       const uint32_t ab = d2_buf(i), tph = d2_phase(i);
       const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
-      const int colq = quarter * (C / 4);
-      // the first piece of the residual row segment is requested BEFORE waiting for GEMM2 (latency hides behind the wait)
+      // the first piece of the residual row is requested BEFORE waiting for GEMM2 (its latency hides behind the wait)
       float rres[4][8];
 #pragma unroll
       for (int j = 0; j < 4; ++j)
 #pragma unroll
         for (int q = 0; q < 8; ++q) rres[j][q] = 0.f;
       float rs = 1.f;
-      if (grow < n) {
+      if (grow < n && !(dbg & 8)) {
         if (residual) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + colq + 8 * j, rres[j]);
+          for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + 8 * j, rres[j]);
         }
         if (row_scale) rs = row_scale[grow];
       }
       mbar_wait(bar(18 + ab), tph);
       fence_after_sync();
-#pragma unroll
+      if (dbg & 8) {      // timing ablation: no output epilogue at all
+        fence_before_sync();
+        mbar_arrive(bar(20 + ab));
+        return;
+      }
+#pragma unroll 1
       for (int pc = 0; pc < PIECES; ++pc) {
-        const int col0 = colq + 32 * pc;
-        if (pc > 0) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-#pragma unroll
-            for (int q = 0; q < 8; ++q) rres[j][q] = 0.f;
-          if (residual && grow < n) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + col0 + 8 * j, rres[j]);
-          }
-        }
+        const int col0 = 32 * pc;
         uint32_t v[32];
         tmem_ld32(tmem + lane_base + 256 + ab * C + col0, v);
         tmem_ld_wait();
@@ -972,9 +969,9 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
           fence_before_sync();
           mbar_arrive(bar(20 + ab));
         }
+        uint32_t pk[16];
         if (grow < n) {
           const float* b2s = reinterpret_cast<const float*>(smem + L::BIAS_OFF) + L::HID + col0;
-          uint32_t pk[16];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             float f[8];
@@ -983,6 +980,11 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
             if (res_out) stg256(res_out + grow * C + col0 + 8 * j, f);
 #pragma unroll
             for (int q = 0; q < 4; ++q) pk[4 * j + q] = pack2(f[2 * q], f[2 * q + 1]);
+          }
+          // next piece of the residual row: in flight while this piece's bf16 copy is stored and the next tcgen05.ld runs
+          if (residual && pc + 1 < PIECES) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + col0 + 32 + 8 * j, rres[j]);
           }
           if (out_bf16) {
             uint32_t lo[8], hi[8];
@@ -994,12 +996,12 @@ __global__ void __launch_bounds__(mlps::THREADS, 1) mlp_stream_kernel(
         }
       }
     };
-    uint32_t e1 = 0;
-    for (int i = 0; i <= my_tiles; ++i) {
-      if (i < my_tiles) gelu_step(0, e1++);
-      if (i >= 1) epilogue2(i - 1);
-      if (i < my_tiles)
-        for (int hb = 1; hb < NHB; ++hb) gelu_step(hb, e1++);
+    if (warp < 20) {
+      uint32_t e1 = 0;
+      for (int i = 0; i < my_tiles; ++i)
+        for (int hb = 0; hb < NHB; ++hb) gelu_step(hb, e1++);
+    } else {
+      for (int i = 0; i < my_tiles; ++i) epilogue2(i);
     }
   }
   fence_before_sync();
