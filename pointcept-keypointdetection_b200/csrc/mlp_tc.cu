@@ -24,6 +24,7 @@ constexpr int HB = 128;            // hidden columns per GEMM1 / K extent per GE
 constexpr int THREADS = 640;       // warps 0-1 loaders, 2 MMA issuer (+TMEM alloc), 3 spare, 4-19 epilogue
 constexpr int LOADERS = 64;
 constexpr int EPI = 512;
+constexpr int OUTW = 128;         // mlp_fused_kernel: four more warps (20-23) for the output epilogue
 
 template <int C>
 struct Smem {
@@ -89,11 +90,11 @@ __global__ void __launch_bounds__(256) pack_kmajor_kernel(const __nv_bfloat16* _
 }
 
 template <int C>
-__global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
+__global__ void __launch_bounds__(mlp::THREADS + mlp::OUTW, 1) mlp_fused_kernel(
     const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w1p, const float* __restrict__ b1,
     const __nv_bfloat16* __restrict__ w2p, const float* __restrict__ b2, const float* __restrict__ residual,
     const float* __restrict__ row_scale, int64_t n,
-    int n_tiles, float* __restrict__ res_out, __nv_bfloat16* __restrict__ out_bf16) {
+    int n_tiles, float* __restrict__ res_out, __nv_bfloat16* __restrict__ out_bf16, int dbg) {
   using namespace mlp;
   using L = Smem<C>;
   extern __shared__ uint8_t smem_raw[];
@@ -113,11 +114,11 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
       mbar_init(bar(1 + b), LOADERS); mbar_init(bar(3 + b), 1);
       mbar_init(bar(5 + b), 1);       mbar_init(bar(7 + b), EPI);
       mbar_init(bar(9 + b), EPI);     mbar_init(bar(11 + b), 1);
-      mbar_init(bar(13 + b), 1);      mbar_init(bar(15 + b), EPI);
+      mbar_init(bar(13 + b), 1);      mbar_init(bar(15 + b), OUTW);
     }
     mbar_fence_init();
   }
-  for (int j = tid; j < L::HID + C; j += THREADS)
+  for (int j = tid; j < L::HID + C; j += THREADS + OUTW)
     reinterpret_cast<float*>(smem + L::BIAS_OFF)[j] = j < L::HID ? b1[j] : b2[j - L::HID];
   if (warp == 2) tmem_alloc<512>(smem_u32(tmem_slot));
   fence_before_sync();
@@ -251,74 +252,75 @@ __global__ void __launch_bounds__(mlp::THREADS, 1) mlp_fused_kernel(
       fence_proxy_async();
       mbar_arrive(bar(9 + bb));
     };
+    // ---- output epilogue (4 separate warps, 20-23): D2 -> + b2 (+ residual) -> fp32 stream and bf16 copy.  On the GELU warps
+    // its HBM round trip stalled the GELU steps of the next tile (timing ablation: 0.301 -> 0.218 ms without it at C = 64).
+    // This thread owns row `row` and all C columns, in pieces of 32.
     auto epilogue2 = [&](int i) {
+      constexpr int PW = C < 32 ? C : 32, PIECES = C / PW;
       const uint32_t ab = (uint32_t)i & 1u, tph = (uint32_t)(i >> 1) & 1u;
-      // ---- epilogue 2: D2 -> + b2 (+ residual) -> fp32 stream and bf16 copy; this thread owns C/4 columns ----
-      constexpr int NC = C / 4;
-      const int col0 = quarter * NC;
       const int64_t grow = (int64_t)(blockIdx.x + (int64_t)i * gridDim.x) * TM + row;
-      // the residual row segment is requested BEFORE waiting for GEMM2: its HBM latency hides behind that wait
-      float rres[NC / 8][8];      // 256-bit accesses: one whole 32-byte sector per lane and instruction
-#pragma unroll
-      for (int j = 0; j < NC / 8; ++j)
+      float rres[4][8];      // one 32-column piece of the residual row (256-bit accesses); the first piece is requested
+#pragma unroll            // BEFORE waiting for GEMM2, the next one while the current piece is being stored
+      for (int j = 0; j < 4; ++j)
 #pragma unroll
         for (int q = 0; q < 8; ++q) rres[j][q] = 0.f;
       float rs = 1.f;      // DropPath on the branch: 0 or 1 / keep for the whole row (NULL = none)
-      if (residual && grow < n) {
+      if (grow < n && !(dbg & 8)) {
+        if (residual) {
 #pragma unroll
-        for (int j = 0; j < NC / 8; ++j) ldg256_cs(residual + grow * C + col0 + 8 * j, rres[j]);
+          for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + 8 * j, rres[j]);
+        }
+        if (row_scale) rs = row_scale[grow];
       }
-      if (row_scale && grow < n) rs = row_scale[grow];
       mbar_wait(bar(13 + ab), tph);
       fence_after_sync();
-      uint32_t v[NC];
-      if constexpr (NC == 16) tmem_ld16(tmem + lane_base + 256 + ab * C + col0, v);
-      else tmem_ld8(tmem + lane_base + 256 + ab * C + col0, v);
-      tmem_ld_wait();
-      fence_before_sync();
-      mbar_arrive(bar(15 + ab));
-      if (grow < n) {
-        float f[NC];
-        const float* b2s = reinterpret_cast<const float*>(smem + L::BIAS_OFF) + L::HID;
-#pragma unroll
-        for (int j = 0; j < NC; ++j) f[j] = (__uint_as_float(v[j]) + b2s[col0 + j]) * rs;
-#pragma unroll
-        for (int j = 0; j < NC / 8; ++j)
-#pragma unroll
-          for (int q = 0; q < 8; ++q) f[8 * j + q] += rres[j][q];
-        if (res_out) {
-#pragma unroll
-          for (int j = 0; j < NC / 8; ++j) {
-            float o8[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) o8[q] = f[8 * j + q];
-            stg256(res_out + grow * C + col0 + 8 * j, o8);
-          }
+      if (dbg & 8) {      // timing ablation: no output epilogue
+        fence_before_sync();
+        mbar_arrive(bar(15 + ab));
+        return;
+      }
+#pragma unroll 1
+      for (int pc = 0; pc < PIECES; ++pc) {
+        const int col0 = 32 * pc;
+        uint32_t v[32];
+        tmem_ld32(tmem + lane_base + 256 + ab * C + col0, v);
+        tmem_ld_wait();
+        if (pc == PIECES - 1) {
+          fence_before_sync();
+          mbar_arrive(bar(15 + ab));
         }
-        if (out_bf16) {
-          if constexpr (NC == 16) {
-            uint32_t pk8[8];
+        if (grow < n) {
+          const float* b2s = reinterpret_cast<const float*>(smem + L::BIAS_OFF) + L::HID + col0;
+          uint32_t pk[16];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) pk8[q] = pack2(f[2 * q], f[2 * q + 1]);
-            stg256_u32(out_bf16 + grow * C + col0, pk8);
-          } else {
-            *reinterpret_cast<uint4*>(out_bf16 + grow * C + col0) =
-                make_uint4(pack2(f[0], f[1]), pack2(f[2], f[3]), pack2(f[4], f[5]), pack2(f[6], f[7]));
+          for (int j = 0; j < 4; ++j) {
+            float f[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) f[q] = fmaf(__uint_as_float(v[8 * j + q]) + b2s[8 * j + q], rs, rres[j][q]);
+            if (res_out) stg256(res_out + grow * C + col0 + 8 * j, f);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) pk[4 * j + q] = pack2(f[2 * q], f[2 * q + 1]);
+          }
+          if (residual && pc + 1 < PIECES) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ldg256_cs(residual + grow * C + col0 + 32 + 8 * j, rres[j]);
+          }
+          if (out_bf16) {
+            uint32_t lo[8], hi[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) { lo[q] = pk[q]; hi[q] = pk[8 + q]; }
+            stg256_u32(out_bf16 + grow * C + col0, lo);
+            stg256_u32(out_bf16 + grow * C + col0 + 16, hi);
           }
         }
       }
     };
-    // order: G(i,0) E2(i-1) G(i,1) ... : the wait for GEMM2 of tile i-1 hides behind the first GELU block of tile i
-    uint32_t e1 = 0;
-    for (int i = 0; i <= my_tiles; ++i) {
-      if (residual && i >= 1) {   // pull tile i-1's residual segment into L2 while the GELU block below runs
-        const int64_t grow = (int64_t)(blockIdx.x + (int64_t)(i - 1) * gridDim.x) * TM + row;
-        if (grow < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(residual + grow * C + quarter * (C / 4)));
-      }
-      if (i < my_tiles) gelu_step(i, 0, e1++);
-      if (i >= 1) epilogue2(i - 1);
-      if (i < my_tiles)
-        for (int hb = 1; hb < L::NHB; ++hb) gelu_step(i, hb, e1++);
+    if (warp < 20) {
+      uint32_t e1 = 0;
+      for (int i = 0; i < my_tiles; ++i)
+        for (int hb = 0; hb < L::NHB; ++hb) gelu_step(i, hb, e1++);
+    } else {
+      for (int i = 0; i < my_tiles; ++i) epilogue2(i);
     }
   }
   fence_before_sync();
@@ -1054,8 +1056,13 @@ static int launch_mlp(const __nv_bfloat16* x, const __nv_bfloat16* w1p, const fl
   }
   const int n_tiles = (int)cdiv(n, mlp::TM);
   const int g = n_tiles < kNumSMs ? n_tiles : kNumSMs;
-  mlp_fused_kernel<C><<<g, mlp::THREADS, L::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, row_scale, n, n_tiles,
-                                                              res_out, out_bf16);
+  static int dbg = -1;      // PTV3_MLP_STREAM_DBG bit 8: timing ablation without the output epilogue (results wrong)
+  if (dbg < 0) {
+    const char* e = getenv("PTV3_MLP_STREAM_DBG");
+    dbg = e ? atoi(e) : 0;
+  }
+  mlp_fused_kernel<C><<<g, mlp::THREADS + mlp::OUTW, L::DYN_BYTES, st>>>(x, w1p, b1, w2p, b2, residual, row_scale, n, n_tiles,
+                                                              res_out, out_bf16, dbg);
   return check_launch();
 }
 

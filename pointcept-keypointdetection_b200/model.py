@@ -354,7 +354,11 @@ class Block(PointModule):
         return ln.weight, ln.bias, ln.eps
 
     native = True      # one C-ABI call per Block (ops.block_fwd) when the shapes allow; False = the op-by-op path
-    fuse_proj = True   # A/B switch: attn.proj + LayerNorm + MLP in one kernel (C = 32 / 64) inside the native call
+    # A/B switch: attn.proj + LayerNorm + MLP in one kernel (ptv3_proj_mlp_fused, C = 32 / 64) inside the native call.
+    # OFF by default: once the fused MLP got its own output warps and 256-bit accesses, the separate launches (cuBLASLt proj,
+    # ln_residual, mlp_fused) became faster than the one kernel at both widths (27.45 vs 27.70 ms per step with it on at
+    # C = 32; profiles/r02_fusions.md).  True = at C = 32, "all" = at C = 32 and 64; PTV3_FUSE_PROJ=1 / all sets it.
+    fuse_proj = {"1": True, "all": "all"}.get(__import__("os").environ.get("PTV3_FUSE_PROJ", "0"), False)
 
     def _native_params(self):
         """ptv3_block_params of this Block (bf16 inference), rebuilt when a parameter changes."""
@@ -384,9 +388,7 @@ class Block(PointModule):
             if fused:
                 t.update(fc1_w=ops.pack_kmajor(mlp.fc1.weight.to(cd), ops.mlp_fc1_tile_rows(c)), fc1_b=mlp.fc1.bias.float().contiguous(),
                          fc2_w=ops.pack_kmajor(lw(mlp.fc2, g2), c), fc2_b=sc(mlp.fc2.bias, g2).contiguous())
-                # proj + LN + MLP as one kernel.  Measured (profiles/r02_fusions.md): a win at C = 32 (0.64 vs 0.79 ms for
-                # the two stage-0 blocks), a loss at C = 64 (2.64 vs 2.37 ms over six blocks): the MLP's epilogue warps
-                # are GELU-issue bound there and the LayerNorm work lands on the same warps.  fuse_proj = "all" forces it.
+                # proj + LN + MLP as one kernel (see fuse_proj above)
                 if ((self.fuse_proj == "all" or (self.fuse_proj and c == 32)) and attn.proj.bias is not None):
                     t.update(proj_w_packed=ops.pack_kmajor(lw(attn.proj, g1), c),
                              proj_b_f32=sc(attn.proj.bias, g1).contiguous())

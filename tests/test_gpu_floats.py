@@ -362,7 +362,7 @@ def test_block_native_call_equals_op_by_op():
     cat = lambda j: torch.from_numpy(np.concatenate([s[j] for s in scenes])).cuda()
     offset = torch.tensor(np.cumsum([len(s[0]) for s in scenes])).cuda()
     from ptv3_b200.model import Block
-    feats = {}
+    feats, fuse_default = {}, Block.fuse_proj
     for native, fuse in ((True, False), (True, True), (False, False)):
         ops.NATIVE_BLOCK, Block.fuse_proj = native, fuse
         try:
@@ -376,7 +376,7 @@ def test_block_native_call_equals_op_by_op():
             for h in hooks:
                 h.remove()
         finally:
-            ops.NATIVE_BLOCK, Block.fuse_proj = True, True
+            ops.NATIVE_BLOCK, Block.fuse_proj = True, fuse_default
     for k in ("enc0", "enc2", "pred"):
         e = rel_l2(feats[(k, (True, False))], feats[(k, (False, False))])
         assert e < 2e-3, (k, e)       # same kernels; the GEMMs may pick another cuBLASLt algorithm (bf16 rounding)
