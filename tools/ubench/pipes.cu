@@ -177,7 +177,7 @@ __global__ void mix(float* out, long long* cyc, float seed) {
 // tcgen05.mma issue rate for small tiles: one thread issues `reps` MMAs M128 x N x K16 (bf16, fp32 accumulate in TMEM) back
 // to back into the same accumulator, A from shared memory (SS) or from tensor memory (TS), then commits and waits.
 // Operands are whatever the shared / tensor memory holds (timing only).
-template <int N, bool TS>
+template <int N, bool TS, int M = 128>
 __global__ void tc_mma(long long* cyc, int reps) {
   extern __shared__ __align__(1024) unsigned char sm[];
   __shared__ uint32_t slot;
@@ -203,7 +203,7 @@ __global__ void tc_mma(long long* cyc, int reps) {
     // K-major no-swizzle descriptors (8-row core matrices, the two K halves 128 B apart, row groups 256 B apart)
     const uint64_t adesc = (uint64_t)((sb >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
     const uint64_t bdesc = (uint64_t)(((sb + 8192) >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | ((uint64_t)1 << 46);
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
     long long t0 = clock64();
     for (int i = 0; i < reps; ++i) {
       if (TS)
@@ -279,6 +279,15 @@ int main() {
   }
   TCMMA(16, false) TCMMA(32, false) TCMMA(64, false) TCMMA(128, false) TCMMA(256, false)
   TCMMA(16, true) TCMMA(32, true) TCMMA(64, true) TCMMA(128, true)
+#define TCMMA64(N)                                                                                               \
+  {                                                                                                              \
+    cudaFuncSetAttribute(tc_mma<N, false, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768);              \
+    for (int rep = 0; rep < 2; ++rep) tc_mma<N, false, 64><<<G, 128, 32768>>>(cyc, 2000);                        \
+    CHECK(cudaDeviceSynchronize());                                                                              \
+    printf("tcgen05.mma M64  N%-3d K16 A in smem: %6.1f clk per MMA (ideal %5.1f at 8192 FLOP/clk/SM)\n", N,      \
+           mean_cycles(cyc, G) / 2000.0, 64.0 * N * 16 * 2 / 8192.0);                                            \
+  }
+  TCMMA64(64) TCMMA64(128) TCMMA64(256)
   for (int threads : {128, 256, 512}) {
     for (int rep = 0; rep < 2; ++rep) ldtm<<<G, threads>>>((uint32_t*)out, cyc);
     CHECK(cudaDeviceSynchronize());
