@@ -462,9 +462,9 @@ int ptv3_ln_residual_rs(const void* x, int dtype_x, const float* gamma, const fl
   int cap = kNumSMs * 8 * 4;
   if (g > cap) g = cap;
   cudaStream_t st = as_stream(stream);
-  if (c == 32 || c == 64 || c == 128 || c == 256 || c == 512) {
+  if (c == 32 || c == 64 || c == 128 || c == 256 || c == 512 || c == 768) {
     // rows are spread over c/8 lanes; enough CTAs for ~8 resident warps of loads per SM sub-partition
-    const int l = c == 512 ? 32 : c / 8;
+    const int l = c >= 512 ? 32 : c / 8;
     const int64_t rows_per_cta_v = 8 * (32 / l);
     int gv = (int)cdiv(n, rows_per_cta_v);
     const int capv = kNumSMs * 8 * 8;
@@ -478,7 +478,8 @@ int ptv3_ln_residual_rs(const void* x, int dtype_x, const float* gamma, const fl
     else if (c == 64) LAUNCHVEC(TX, TO, 8, 1);   \
     else if (c == 128) LAUNCHVEC(TX, TO, 16, 1); \
     else if (c == 256) LAUNCHVEC(TX, TO, 32, 1); \
-    else LAUNCHVEC(TX, TO, 32, 2);               \
+    else if (c == 512) LAUNCHVEC(TX, TO, 32, 2); \
+    else LAUNCHVEC(TX, TO, 32, 3);               \
   } while (0)
     if (dtype_x == PTV3_F32 && dtype_out2 == PTV3_F32) LAUNCHC(float, float);
     else if (dtype_x == PTV3_F32 && dtype_out2 == PTV3_BF16) LAUNCHC(float, __nv_bfloat16);

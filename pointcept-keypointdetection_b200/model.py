@@ -978,9 +978,16 @@ class DefaultSegmentorV2(nn.Module):
         prev = torch.backends.cuda.matmul.allow_tf32
         torch.backends.cuda.matmul.allow_tf32 = bool(tf32)
         try:
+            # training with a bf16 backbone: bf16 operands like torch.autocast gives the reference's nn.Linear, so that
+            # the weight-gradient GEMMs of the backward run on the tensor cores too (the TF32 switch above only covers
+            # the forward; fp32 SIMT GEMMs cost 1.5 ms per step of the PTv3-large linear probe)
+            amp = tf32 and self.training and torch.is_grad_enabled()
             for lv, inv in zip(levels, invs + [None]):           # coarsest first; its columns are the LAST slice
                 c = lv.feat.shape[1]
-                part = F.linear(lv.feat.float(), w[:, lo - c:lo])
+                if amp:
+                    part = F.linear(lv.feat.to(torch.bfloat16), w[:, lo - c:lo].to(torch.bfloat16)).float()
+                else:
+                    part = F.linear(lv.feat.float(), w[:, lo - c:lo])
                 lo -= c
                 acc = part if acc is None else part + acc
                 if inv is not None:

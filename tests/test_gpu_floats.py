@@ -69,7 +69,7 @@ def test_unpool_add_and_ln_residual():
     out, act = ops.unpool_add(skip.bfloat16().cuda(), up.bfloat16().cuda(), inv.cuda(), gelu=True)
     assert out.dtype == torch.float32 and act.dtype == torch.bfloat16
     assert rel_l2(out, F.gelu(skip.bfloat16().float()) + F.gelu(up.bfloat16().float())[inv]) < 1e-5
-    for c in (32, 64, 128, 256, 512, 96):
+    for c in (32, 64, 128, 256, 512, 768, 96):
         x, res = torch.randn(777, c) * 3 + 1, torch.randn(777, c)
         g1, b1, g2, b2 = (torch.randn(c) for _ in range(4))
         r_ref = res + F.layer_norm(x, (c,), g1, b1, 1e-5)
