@@ -47,20 +47,29 @@ __global__ void __launch_bounds__(256) affine_act_kernel(const TX* __restrict__ 
   }
 }
 
-// exact GELU of a bf16 matrix, bf16 out (may be in place): the hidden activation of the MLP at C >= 128 between the two
-// library GEMMs (MLP.forward :237-247).  16-byte accesses, 8 elements per thread: one read + one write of the matrix.
-__global__ void __launch_bounds__(256) gelu_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int64_t n8) {
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n8; t += (int64_t)gridDim.x * blockDim.x) {
-    uint4 u = x[t];
-    uint32_t w[4] = {u.x, u.y, u.z, u.w};
+// exact GELU of a bf16 matrix, bf16 out (may be in place): the hidden activation of the MLP at C >= 512 between the two
+// library GEMMs (MLP.forward :237-247).  16-byte accesses, two independent vectors per thread and iteration, and the
+// 15-instruction erf of common.cuh (|error| 1.5e-7, invisible after the bf16 rounding) instead of erff(): with erff the
+// kernel was instruction-bound at 0.45 of the HBM rate.
+__device__ __forceinline__ uint4 gelu8(uint4 u) {
+  uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float lo = gelu_exact(__uint_as_float(w[j] << 16)), hi = gelu_exact(__uint_as_float(w[j] & 0xffff0000u));
-      const __nv_bfloat162 r = __floats2bfloat162_rn(lo, hi);
-      w[j] = *reinterpret_cast<const uint32_t*>(&r);
-    }
-    y[t] = make_uint4(w[0], w[1], w[2], w[3]);
+  for (int j = 0; j < 4; ++j) {
+    const float lo = gelu_erf(__uint_as_float(w[j] << 16)), hi = gelu_erf(__uint_as_float(w[j] & 0xffff0000u));
+    const __nv_bfloat162 r = __floats2bfloat162_rn(lo, hi);
+    w[j] = *reinterpret_cast<const uint32_t*>(&r);
   }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__global__ void __launch_bounds__(256) gelu_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int64_t n8) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; t + stride < n8; t += 2 * stride) {
+    const uint4 a = x[t], b = x[t + stride];
+    y[t] = gelu8(a);
+    y[t + stride] = gelu8(b);
+  }
+  if (t < n8) y[t] = gelu8(x[t]);
 }
 
 }  // namespace ptv3
@@ -78,7 +87,7 @@ extern "C" int ptv3_affine_act(const void* x, int dtype_x, const float* scale, c
   if (dtype_x == PTV3_BF16 && act == 1 && !scale && !shift && !out32 && (c & 7) == 0 &&
       (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(out16) & 15) == 0) {
     const int64_t n8 = n * (int64_t)(c >> 3);
-    gelu_bf16_kernel<<<(unsigned)grid_for(n8, 256), 256, 0, st>>>((const uint4*)x, (uint4*)out16, n8);
+    gelu_bf16_kernel<<<(unsigned)grid_for((n8 + 1) / 2, 256), 256, 0, st>>>((const uint4*)x, (uint4*)out16, n8);
     return check_launch();
   }
   if (dtype_x == PTV3_F32)

@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) seg_block_kernel(const T* __restrict__ sr
   }
 }
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
+__device__ __forceinline__ float gelu_libm(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
 
 template <typename T, bool GELU>
 __global__ void __launch_bounds__(256) unpool_add_kernel(const T* __restrict__ skip, const T* __restrict__ up,
@@ -149,8 +149,8 @@ __global__ void __launch_bounds__(256) unpool_add_kernel(const T* __restrict__ s
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       if (GELU) {
-        a[q] = gelu_erf(a[q]);
-        b[q] = gelu_erf(b[q]);
+        a[q] = gelu_libm(a[q]);
+        b[q] = gelu_libm(b[q]);
       }
       o[q] = a[q] + b[q];
     }

@@ -533,6 +533,23 @@ def test_affine_act(dtype, act):
     assert torch.equal(o16.cpu(), o32.cpu().bfloat16())
 
 
+@pytest.mark.parametrize("n,c", [(1, 8), (777, 512), (1003, 2048), (4097, 3072)])
+def test_gelu_bf16_plain(n, c):
+    """The stand-alone bf16 GELU between the library GEMMs of the wide MLPs (MLP.forward :237-247): exact-erf GELU of the
+    bf16 input in fp32, rounded once to bf16 (two vectors per thread + tail; in place as the model calls it)."""
+    from ptv3_b200 import ops
+    g = torch.Generator().manual_seed(n + c)
+    x = (torch.randn(n, c, generator=g) * 2.5).bfloat16()
+    ref = torch.nn.functional.gelu(x.float()).bfloat16()
+    _, o16 = ops.affine_act(x.cuda(), None, None, "gelu", want_f32=False, want_bf16=True)
+    o = o16.cpu()
+    # the 15-instruction erf is within 1.5e-7 ABSOLUTE of erf: at most one bf16 ulp everywhere, rounding flips only on a
+    # handful of ties where the value is not tiny (deep in the negative tail, |gelu| < 1e-3, 4e-7 is a visible fraction)
+    assert torch.allclose(o.float(), ref.float(), rtol=8e-3, atol=1e-6)
+    big = ref.float().abs() > 1e-3
+    assert (o != ref)[big].float().mean() < 1e-3
+
+
 def _head_weights(tag):
     from conftest import GOLDEN
     from ptv3_b200 import synth
