@@ -27,7 +27,13 @@ def lovasz_softmax(logits, labels, ignore_index=None):
     errors_sorted, perm = torch.sort(errors, dim=1, descending=True)
     fg_sorted = torch.gather(fg, 1, perm)
     gts = fg_sorted.sum(1, keepdim=True)
-    cum = fg_sorted.cumsum(1)                         # the only scan: cumsum(1 - fg) = position - cumsum(fg)
+    # the only scan: cumsum(1 - fg) = position - cumsum(fg).  Run over the FLAT (C * P) array -- torch's row-wise scan
+    # gives each of the C rows to one thread block (1.2 ms for 22 x 757 k on a B200), the 1-D form is a device-wide
+    # decoupled look-back scan -- and take each row's starting count off again; fg is 0 / 1, so every partial sum is an
+    # integer below 2^24 and the result is exact in fp32 whatever the order.
+    assert fg_sorted.numel() < (1 << 24) * c and fg_sorted.shape[1] < (1 << 24)
+    flat = fg_sorted.reshape(-1).cumsum(0).view_as(fg_sorted)
+    cum = flat - (flat[:, -1:] - gts)
     pos = torch.arange(1, cum.shape[1] + 1, device=cum.device, dtype=cum.dtype)
     inter = gts - cum
     union = gts + (pos - cum)
@@ -58,8 +64,20 @@ class CrossEntropyLoss(nn.Module):
         self.loss = nn.CrossEntropyLoss(weight=torch.as_tensor(weight) if weight is not None else None,
                                         ignore_index=ignore_index, reduction=reduction, label_smoothing=label_smoothing)
 
+        self.ignore_index = ignore_index
+        self.plain = weight is None and reduction == "mean" and label_smoothing == 0.0
+
     def forward(self, pred, target):
-        return self.loss(pred.float(), target) * self.loss_weight
+        pred = pred.float()
+        if self.plain and pred.dim() == 2:
+            # mean over the valid rows of -log_softmax(pred)[row, target]: same value as nn.CrossEntropyLoss, but the
+            # pick is a gather and the mean a device-wide reduction -- torch's nll_loss 2-D forward / backward reduce with
+            # ONE thread block (0.73 + 0.45 ms for 757 k rows on a B200)
+            valid = target != self.ignore_index
+            logp = F.log_softmax(pred, dim=1)
+            picked = logp.gather(1, target.clamp(min=0).unsqueeze(1)).squeeze(1)
+            return -(picked * valid).sum() / valid.sum() * self.loss_weight
+        return self.loss(pred, target) * self.loss_weight
 
 
 class Criteria:

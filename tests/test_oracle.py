@@ -332,6 +332,25 @@ def test_lovasz_softmax_vs_reference():
     assert z.item() == 0.0 and z.requires_grad
 
 
+def test_cross_entropy_gather_form_vs_torch():
+    """losses.CrossEntropyLoss (log_softmax + gather + device-wide mean instead of torch's one-block nll_loss reduction)
+    against torch.nn.functional.cross_entropy: value and gradient, with ignored rows; other options fall back to torch."""
+    from ptv3_b200 import losses
+    g = torch.Generator().manual_seed(3)
+    x = (torch.randn(5000, 22, generator=g) * 3).requires_grad_(True)
+    t = torch.randint(-1, 22, (5000,), generator=g)
+    ce = losses.CrossEntropyLoss(loss_weight=0.7, ignore_index=-1)
+    assert ce.plain
+    a = ce(x, t)
+    ga, = torch.autograd.grad(a, x)
+    b = torch.nn.functional.cross_entropy(x, t, ignore_index=-1) * 0.7
+    gb, = torch.autograd.grad(b, x)
+    assert abs(a.item() - b.item()) < 1e-6 and (ga - gb).abs().max().item() < 1e-9
+    sm = losses.CrossEntropyLoss(label_smoothing=0.1, ignore_index=-1)
+    assert not sm.plain
+    assert abs(sm(x, t).item() - torch.nn.functional.cross_entropy(x, t, ignore_index=-1, label_smoothing=0.1).item()) < 1e-6
+
+
 def test_neighbor_table_many_scenes_brute_force():
     """oracle.ops.subm_neighbor_table against a dictionary lookup on a batch of 5 scenes (the 64-bit key used to put the
     batch id at bit 63, so batch ids >= 2 wrapped around; every earlier fixture had at most two scenes)."""

@@ -13,7 +13,7 @@ raw = bench.make_raw_scenes(16, 100000, 4.1, seed0=0)
 host, counts = bench.voxelize_on_device(raw, dev)
 grid = host["grid_coord"].to(dev)
 batch = torch.repeat_interleave(torch.arange(16, device=dev), torch.tensor(counts, device=dev))
-_lib.load().ptv3_debug_set(3, int(os.environ.get('CONV_ASYNC', '0')))
+_lib.load().ptv3_debug_set(3, int(os.environ.get('CONV_ASYNC', '1')))   # 1 = gather copies arrive on the stage barrier themselves (default)
 stages = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 10
 for s in range(stages):

@@ -62,3 +62,5 @@ ks = sorted([e for e in prof.events() if e.device_type.name == "CUDA" and e.time
 span = ks[-1].time_range.end - ks[0].time_range.start
 idle = sum(max(0, b_.time_range.start - a_.time_range.end) for a_, b_ in zip(ks[:-1], ks[1:]))
 print(f"first-to-last kernel span {span / 1e3:.3f} ms, idle inside {idle / 1e3:.3f} ms")
+convs = [e for e in ks if "subm_conv_tc_kernel" in e.name]
+print("conv launches in order (us):", " ".join(f"{e.name.split('<')[1].split('>')[0].replace(' ', '')}:{e.time_range.end - e.time_range.start:.0f}" for e in convs))
