@@ -182,6 +182,46 @@ def conv_flops(rec_meta):
     return 2.0 * rec_meta["cin"] * rec_meta["cout"] * present, present
 
 
+def roofline_from_records(recs, step_ms, pk, clocks):
+    """recs = ops.profile_stop(): (op, ms, meta) per instrumented launch of one step -> (roofline dict of the op with
+    the largest share, per-op ms)."""
+    tot = {}
+    for name, t, meta in recs:
+        if name == "attn_window":
+            fl, units = attn_flops(meta)
+        elif name == "mlp_fused":      # fc1 + fc2: 2 * (2 * n * c * hidden)
+            fl, units = 4.0 * meta["n"] * meta["c"] * meta["hidden"], float(meta["n"])
+        elif name == "proj_mlp_fused":  # + the attention projection
+            fl, units = 4.0 * meta["n"] * meta["c"] * meta["hidden"] + 2.0 * meta["n"] * meta["c"] ** 2, float(meta["n"])
+        elif name == "subm_conv":
+            fl, units = conv_flops(meta)
+        else:
+            continue
+        e = tot.setdefault(name, dict(ms=0.0, flops=0.0, units=0.0, launches=0))
+        e["ms"] += t
+        e["flops"] += fl
+        e["units"] += units
+        e["launches"] += 1
+    ops_ms = {k: round(v["ms"], 3) for k, v in tot.items()}
+    ops_ms["step_instrumented"] = round(step_ms, 3)
+    top = max(tot, key=lambda k: tot[k]["ms"])
+    e = tot[top]
+    ach = e["flops"] / (e["ms"] * 1e-3) / 1e12
+    roof = dict(kernel=top, bound="tensor", achieved=round(ach, 2), peak=pk["tf_sust"], unit="TFLOP/s",
+                frac=round(ach / pk["tf_sust"], 4), traffic=None, peak_source=pk["src"] + " (sustained bf16 GEMM)",
+                launches_per_step=e["launches"], ms_per_step=round(e["ms"], 3),
+                share_of_step=round(e["ms"] / step_ms, 3))
+    roof["traffic"], roof["traffic_note"] = ncu_traffic({"attn_window": "attn_window_f16", "subm_conv": "subm_conv_tc",
+                                                         "mlp_fused": "mlp_fused"}.get(top, top))
+    if top == "attn_window":   # head_dim 16: the exp pipe, not the tensor pipe, bounds this kernel (SURVEY 8d)
+        roof["exp_per_s"] = round(e["units"] / (e["ms"] * 1e-3) / 1e12, 3)
+        roof["exp_peak_mufu_per_s"] = round(16 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 3)
+        roof["limiter"] = ("mufu: 16 ex2 / clk / SM measured (tools/ubench/pipes.cu; the packed f16x2 / bf16x2 forms "
+                           "are two MUFU ops each); frac_of_limiter = exp_per_s / exp_peak_mufu_per_s")
+        roof["frac_of_limiter"] = round(roof["exp_per_s"] / roof["exp_peak_mufu_per_s"], 4)
+    return roof, ops_ms
+
+
 def run_ours(args):
     from ptv3_b200 import _lib, ops
     from ptv3_b200.model import aggregate_keypoints
@@ -302,36 +342,7 @@ def run_ours(args):
         recs = ops.profile_stop()
         ops.NATIVE_BLOCK = True
         step_ms = a.elapsed_time(b)
-        tot = {}
-        for name, t, meta in recs:
-            if name == "attn_window":
-                fl, units = attn_flops(meta)
-            elif name == "mlp_fused":      # fc1 + fc2: 2 * (2 * n * c * hidden)
-                fl, units = 4.0 * meta["n"] * meta["c"] * meta["hidden"], float(meta["n"])
-            else:
-                fl, units = conv_flops(meta)
-            e = tot.setdefault(name, dict(ms=0.0, flops=0.0, units=0.0, launches=0))
-            e["ms"] += t
-            e["flops"] += fl
-            e["units"] += units
-            e["launches"] += 1
-        ops_ms = {k: round(v["ms"], 3) for k, v in tot.items()}
-        ops_ms["step_instrumented"] = round(step_ms, 3)
-        top = max(tot, key=lambda k: tot[k]["ms"])
-        e = tot[top]
-        ach = e["flops"] / (e["ms"] * 1e-3) / 1e12
-        roof = dict(kernel=top, bound="tensor", achieved=round(ach, 2), peak=pk["tf_sust"], unit="TFLOP/s",
-                    frac=round(ach / pk["tf_sust"], 4), traffic=None, peak_source=pk["src"] + " (sustained bf16 GEMM)",
-                    launches_per_step=e["launches"], ms_per_step=round(e["ms"], 3),
-                    share_of_step=round(e["ms"] / step_ms, 3))
-        roof["traffic"], roof["traffic_note"] = ncu_traffic({"attn_window": "attn_window_f16", "subm_conv": "subm_conv_tc",
-                                                             "mlp_fused": "mlp_fused"}.get(top, top))
-        if top == "attn_window":   # head_dim 16: the exp pipe, not the tensor pipe, bounds this kernel
-            roof["exp_per_s"] = round(e["units"] / (e["ms"] * 1e-3) / 1e12, 3)
-            roof["exp_peak_mufu_per_s"] = round(16 * 148 * (clocks.get("sm_mhz") or 1965.0) * 1e6 / 1e12, 3)
-            roof["limiter"] = ("mufu: 16 ex2 / clk / SM measured (tools/ubench/pipes.cu; the packed f16x2 / bf16x2 forms "
-                               "are two MUFU ops each); frac_of_limiter = exp_per_s / exp_peak_mufu_per_s")
-            roof["frac_of_limiter"] = round(roof["exp_per_s"] / roof["exp_peak_mufu_per_s"], 4)
+        roof, ops_ms = roofline_from_records(recs, step_ms, pk, clocks)
     # ---- GridSample leg (BASELINE metric: "GridSample reported separately in raw points/s"), raw scans resident ----
     gs_leg = None
     if rank == 0:
@@ -616,6 +627,21 @@ def run_train(args):
         dist.all_reduce(total_vox)
     total_vox = float(total_vox.item())
     n_params = sum(p.numel() for p in model.parameters())
+    roof, ops_ms = None, {}
+    if rank == 0 and lin:      # roofline leg, as in run_ours: one instrumented step on the op-by-op path (frozen backbone)
+        from ptv3_b200 import ops
+        ops.NATIVE_BLOCK = False
+        step(resident)
+        torch.cuda.synchronize()
+        ops.profile_start()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step(resident)
+        b.record()
+        recs = ops.profile_stop()
+        ops.NATIVE_BLOCK = True
+        if recs:
+            roof, ops_ms = roofline_from_records(recs, a.elapsed_time(b), peaks(), clocks)
     if lin:
         what = (f"PTv3-large (PT-v3m2 encoder 3-3-3-12-3 x 64-128-256-512-768, frozen, train() mode with DropPath 0.3) + "
                 f"Linear(1728, 22) head TRAINING step (fwd + CE + Lovasz + head bwd + AdamW), {args.scenes} Waymo-shaped "
@@ -634,7 +660,7 @@ def run_train(args):
                                     f"({'NCCL AVG, overlapped with backward' if world > 1 else 'none at N=1'})"),
             e2e=dict(value=round(total_vox * args.steps / (e2e_wall * 1e-3), 1), unit=UNIT, h2d_bytes_per_step=h2d_bytes,
                      d2h_bytes_per_step=4, ms_per_step=round(e2e_wall / args.steps, 3), result="loss (fp32 scalar)"),
-            gpu_launches=int(launches), clocks=clocks, loss=round(float(loss.item()), 5),
+            gpu_launches=int(launches), clocks=clocks, roofline=roof, op_ms=ops_ms, loss=round(float(loss.item()), 5),
             peak_mem_gib=round(torch.cuda.max_memory_allocated() / 2 ** 30, 2))))
     if world > 1:
         dist.destroy_process_group()

@@ -62,5 +62,9 @@ ks = sorted([e for e in prof.events() if e.device_type.name == "CUDA" and e.time
 span = ks[-1].time_range.end - ks[0].time_range.start
 idle = sum(max(0, b_.time_range.start - a_.time_range.end) for a_, b_ in zip(ks[:-1], ks[1:]))
 print(f"first-to-last kernel span {span / 1e3:.3f} ms, idle inside {idle / 1e3:.3f} ms")
+gc = res["grid_coord"].long()
+bt = torch.repeat_interleave(torch.arange(len(counts), device=dev), torch.tensor(counts, device=dev))
+print("rows per level:", [int(torch.unique((bt << 48) | ((gc[:, 0] >> s_) << 32) | ((gc[:, 1] >> s_) << 16) | (gc[:, 2] >> s_)).numel())
+                          for s_ in range(5)])
 convs = [e for e in ks if "subm_conv_tc_kernel" in e.name]
 print("conv launches in order (us):", " ".join(f"{e.name.split('<')[1].split('>')[0].replace(' ', '')}:{e.time_range.end - e.time_range.start:.0f}" for e in convs))
