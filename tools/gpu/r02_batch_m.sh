@@ -1,5 +1,6 @@
 #!/bin/bash
-# conv with two row tiles per CTA: parity, micro-bench per mode, config 2 / 5 effect
+# (historical) two-row-tile variant of the tcgen05 conv: parity, micro-bench per mode, config 2 / 5 effect.  The variant was
+# measured and reverted (profiles/r02_fusions.md); CONV_ASYNC bits 1-2 no longer select anything at HEAD.
 set -x
 mkdir -p gpurun_out
 timeout 300 python -m pytest tests/test_gpu_floats.py -x -q -k "subm_conv" 2>&1 | tail -4

@@ -1,5 +1,5 @@
 #!/bin/bash
-# conv with two row tiles per CTA, 3-stage ring filled by 3 groups: parity + effect (tight timeouts: a hang costs seconds)
+# (historical) two-row-tile conv variant on a 3-stage ring filled by 3 groups: parity + effect.  Reverted (profiles/r02_fusions.md).
 set -x
 mkdir -p gpurun_out
 timeout 150 python -m pytest tests/test_gpu_floats.py -x -q -k "two_row_tiles or many_tiles" 2>&1 | tail -4
