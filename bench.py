@@ -554,6 +554,9 @@ def run_train(args):
         raw = make_raw_scenes(args.scenes, args.points, args.scale, seed0=1000 * rank)
         grid = GRID
     model.train()
+    if getattr(args, "sync_bn", False) and world > 1:
+        from ptv3_b200.ddp import convert_sync_batchnorm
+        convert_sync_batchnorm(model)
     host, counts = voxelize_on_device(raw, device, grid)
     n_vox = int(sum(counts))
     if lin:
@@ -683,6 +686,8 @@ def main():
     ap.add_argument("--points", type=int, default=None)
     ap.add_argument("--scale", type=float, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sync-bn", action="store_true",
+                    help="--mode train: BatchNorm statistics over every rank's rows (the reference's cfg.sync_bn)")
     ap.add_argument("--mode", default="forward", choices=["forward", "train"],
                     help="forward = the headline metric (default); train = training step (SURVEY 8f rank 1)")
     args = ap.parse_args()

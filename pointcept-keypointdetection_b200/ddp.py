@@ -86,3 +86,90 @@ class GradSync:
     def remove(self):
         for h in self._hooks:
             h.remove()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# SyncBatchNorm (engines/train.py:256-257: `if cfg.sync_bn: model = nn.SyncBatchNorm.convert_sync_batchnorm(model)`).
+# PT-v3m1 has BatchNorm1d at the stem, the four poolings and the unpoolings; with scenes sharded per rank their batch
+# statistics must span every rank's rows to equal the single-process step.  The modules stay nn.BatchNorm1d (same
+# state_dict names, same eval-mode folding into the fused kernels); `convert_sync_batchnorm` only marks them, and the
+# training forward (train._bn) then routes through `sync_batch_norm`:
+#   forward : per rank (count, mean, M2) -> all_gather -> pooled mean / biased variance (Chan's parallel merge, the
+#             cancellation-free form torch's batch_norm_gather_stats_with_counts uses), running stats updated with the
+#             UNBIASED pooled variance like nn.BatchNorm1d;
+#   backward: all_reduce of (sum dy, sum dy * xhat); dx uses the pooled count; d weight / d bias stay per-rank sums and
+#             are averaged with every other parameter gradient by GradSync (what DDP does for nn.SyncBatchNorm).
+# Two small collectives per BatchNorm and direction ((2 C + 1) and 2 C floats), torch ops only: runs on NCCL and gloo.
+# ---------------------------------------------------------------------------------------------------------------
+def convert_sync_batchnorm(model, process_group=None):
+    """Marks every BatchNorm of `model` for cross-rank statistics in training; returns the model (same classes)."""
+    for m in model.modules():
+        if isinstance(m, torch.nn.modules.batchnorm._BatchNorm):
+            m.ptv3_sync = True
+            m.ptv3_sync_group = process_group
+    return model
+
+
+def _sync_active(bn):
+    return (bool(getattr(bn, "ptv3_sync", False)) and bn.training and dist.is_available() and dist.is_initialized()
+            and dist.get_world_size(getattr(bn, "ptv3_sync_group", None)) > 1)
+
+
+class _SyncBNFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps, group):
+        n, c = x.shape
+        cnt = x.new_tensor([float(n)])
+        if n > 0:
+            mean_l = x.mean(0)
+            m2_l = (x - mean_l).square().sum(0)
+        else:                                  # a rank without rows (ragged shard) still takes part in the collectives
+            mean_l, m2_l = x.new_zeros(c), x.new_zeros(c)
+        mine = torch.cat([cnt, mean_l, m2_l])
+        world = dist.get_world_size(group)
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine, group=group)
+        allp = torch.stack(parts)                                         # (world, 1 + 2 C)
+        counts, means, m2s = allp[:, :1], allp[:, 1:1 + c], allp[:, 1 + c:]
+        total = counts.sum()
+        mean = (counts * means).sum(0) / total
+        m2 = m2s.sum(0) + (counts * (means - mean).square()).sum(0)
+        var = m2 / total                                                  # biased: what normalises the batch
+        invstd = torch.rsqrt(var + eps)
+        xhat = (x - mean) * invstd
+        ctx.save_for_backward(xhat, weight, invstd)
+        ctx.total, ctx.group = total, group
+        ctx.mark_non_differentiable(mean, m2, total)
+        y = xhat * weight + bias if weight is not None else xhat
+        return y, mean, m2, total
+
+    @staticmethod
+    def backward(ctx, dy, _m, _v, _t):
+        xhat, weight, invstd = ctx.saved_tensors
+        c = xhat.shape[1]
+        dy = dy.float()
+        sum_dy, sum_dy_xhat = dy.sum(0), (dy * xhat).sum(0)
+        red = torch.cat([sum_dy, sum_dy_xhat])
+        dist.all_reduce(red, group=ctx.group)
+        g_dy, g_dyx = red[:c] / ctx.total, red[c:] / ctx.total
+        scale = invstd * weight if weight is not None else invstd
+        dx = (dy - g_dy - xhat * g_dyx) * scale
+        dw = sum_dy_xhat if weight is not None else None
+        db = sum_dy if weight is not None else None
+        return dx, dw, db, None, None
+
+
+def sync_batch_norm(x, bn):
+    """Training-mode BatchNorm1d over the rows of EVERY rank (x: (n_local, C) fp32).  Updates bn.running_mean /
+    running_var / num_batches_tracked exactly as nn.BatchNorm1d would on the concatenated batch."""
+    group = getattr(bn, "ptv3_sync_group", None)
+    w, b = (bn.weight, bn.bias) if bn.affine else (None, None)
+    y, mean, m2, total = _SyncBNFn.apply(x, w, b, bn.eps, group)
+    if bn.track_running_stats:
+        with torch.no_grad():
+            bn.num_batches_tracked += 1
+            mom = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+            unbiased = m2 / torch.clamp(total - 1.0, min=1.0)
+            bn.running_mean.mul_(1.0 - mom).add_(mean.to(bn.running_mean.dtype), alpha=mom)
+            bn.running_var.mul_(1.0 - mom).add_(unbiased.to(bn.running_var.dtype), alpha=mom)
+    return y

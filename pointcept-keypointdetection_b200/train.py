@@ -32,6 +32,9 @@ def _ln(x, ln, out_dtype=torch.float32):
 
 
 def _bn(x, bn):
+    from . import ddp
+    if ddp._sync_active(bn):        # cfg.sync_bn (engines/train.py:256-257): statistics over every rank's rows
+        return ddp.sync_batch_norm(x.float(), bn)
     return bn(x.float())            # nn.BatchNorm1d: batch statistics in train(), running ones in eval()
 
 

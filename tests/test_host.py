@@ -168,6 +168,89 @@ def test_grad_sync_world_size_2_gloo():
     assert all((r[2] == 0).all() for r in res)
 
 
+_SBN_ROWS = [[5, 9], [7, 0], [1, 1]]          # rows per rank for three consecutive steps (one rank empty, two single rows)
+
+
+def _sbn_data(step, rank, c=6):
+    g = torch.Generator().manual_seed(100 * step + rank)
+    n = _SBN_ROWS[step][rank]
+    return torch.randn(n, c, generator=g) * (1.0 + rank) + 3.0 * step, torch.randn(n, c, generator=g)
+
+
+def _syncbn_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from ptv3_b200 import ddp, train
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        bn = torch.nn.BatchNorm1d(6, eps=1e-3, momentum=0.01)
+        with torch.no_grad():
+            bn.weight.copy_(torch.linspace(0.5, 1.5, 6))
+            bn.bias.copy_(torch.linspace(-1, 1, 6))
+        holder = torch.nn.Sequential(bn)
+        assert ddp.convert_sync_batchnorm(holder) is holder and type(bn) is torch.nn.BatchNorm1d and bn.ptv3_sync
+        out = []
+        for step in range(len(_SBN_ROWS)):
+            x, gy = _sbn_data(step, rank)
+            x.requires_grad_(True)
+            bn.zero_grad()
+            y = train._bn(x, bn)                       # the call site of the training forward
+            (y * gy).sum().backward()
+            out.append([t.detach().numpy().copy() for t in (y, x.grad, bn.weight.grad, bn.bias.grad)])
+        stats = [bn.running_mean.numpy().copy(), bn.running_var.numpy().copy(), int(bn.num_batches_tracked)]
+        bn.eval()                                      # eval(): plain running statistics, no collective
+        x, _ = _sbn_data(0, rank)
+        ev = train._bn(x, bn).detach().numpy().copy()
+        q.put((rank, out, stats, ev))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sync_batchnorm_world_size_2_gloo():
+    """cfg.sync_bn (engines/train.py:256-257): BatchNorm statistics over the rows of every rank.  Two gloo ranks with
+    unequal (and empty) shards must reproduce nn.BatchNorm1d on the concatenated batch: outputs, input gradients,
+    parameter gradients (per-rank sums; GradSync averages them like DDP) and the running statistics."""
+    import torch.multiprocessing as mp
+    world, port = 2, 29500 + (os.getpid() % 2000) + 23
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_syncbn_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    bn = torch.nn.BatchNorm1d(6, eps=1e-3, momentum=0.01)
+    with torch.no_grad():
+        bn.weight.copy_(torch.linspace(0.5, 1.5, 6))
+        bn.bias.copy_(torch.linspace(-1, 1, 6))
+    for step in range(len(_SBN_ROWS)):
+        xs, gs = zip(*[_sbn_data(step, r) for r in range(world)])
+        x = torch.cat(xs).requires_grad_(True)
+        bn.zero_grad()
+        y = bn(x)
+        (y * torch.cat(gs)).sum().backward()
+        o = 0
+        for r in range(world):
+            n = _SBN_ROWS[step][r]
+            yr, dxr, _, _ = res[r][1][step]
+            assert torch.allclose(torch.from_numpy(yr), y[o:o + n].detach(), atol=2e-5), (step, r)
+            assert torch.allclose(torch.from_numpy(dxr), x.grad[o:o + n], atol=2e-5), (step, r)
+            o += n
+        dw = sum(torch.from_numpy(res[r][1][step][2]) for r in range(world))
+        db = sum(torch.from_numpy(res[r][1][step][3]) for r in range(world))
+        assert torch.allclose(dw, bn.weight.grad, atol=2e-5) and torch.allclose(db, bn.bias.grad, atol=2e-5)
+    for r in range(world):
+        rm, rv, nb = res[r][2]
+        assert torch.allclose(torch.from_numpy(rm), bn.running_mean, atol=1e-6)
+        assert torch.allclose(torch.from_numpy(rv), bn.running_var, atol=1e-6) and nb == len(_SBN_ROWS)
+        bn.eval()
+        assert torch.allclose(torch.from_numpy(res[r][3]), bn(_sbn_data(0, r)[0]).detach(), atol=1e-6)
+        bn.train()
+
+
 def _eval_reduce_worker(rank, world, port, q):
     import torch.distributed as dist
     from ptv3_b200.evaluator import reduce_sums, summarize
