@@ -358,3 +358,73 @@ def segmentor_forward(model, input_dict, criterion=None):
         crit = criterion or getattr(model, "criteria", None) or nn.CrossEntropyLoss(ignore_index=-1)
         out["loss"] = crit(logits, input_dict["segment"])
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# The trainer's step (engines/train.py:184-245 `Trainer.run_step`, :346-354 `build_scaler`): gradient accumulation,
+# GradScaler when AMP is on, gradient clipping after unscale_, and the scheduler advanced only when the scaler did not
+# skip the optimizer step.  `torch.autocast` has no role here: mixed precision is the model's `compute_dtype` (bf16
+# operands, fp32 residual stream / norms / loss), so `amp_dtype` only selects it.  The kernels compute in bf16 or fp32;
+# an fp16 request is refused instead of silently computing in another type.  The reference builds its GradScaler for
+# bf16 as well (enable_amp alone decides), so it is kept: with bf16 it never finds an overflow and is a pass-through.
+# ---------------------------------------------------------------------------------------------------------------
+class TrainStep:
+    def __init__(self, model, optimizer, scheduler=None, enable_amp=False, amp_dtype="bfloat16", clip_grad=None,
+                 gradient_accumulation_steps=1, grad_sync=None, scaler=None):
+        if enable_amp and amp_dtype not in ("bfloat16", torch.bfloat16):
+            raise NotImplementedError("ptv3_b200 kernels compute in bf16 (or fp32); amp_dtype='float16' is not built -- "
+                                      "bf16 has fp32's exponent range and needs no loss scaling")
+        self.model, self.optimizer, self.scheduler = model, optimizer, scheduler
+        self.enable_amp, self.clip_grad = bool(enable_amp), clip_grad
+        self.accum = int(gradient_accumulation_steps)
+        self.sync = grad_sync                      # ddp.GradSync or None (one process)
+        if scaler is None and self.enable_amp:     # build_scaler (:346-354)
+            dev = next(model.parameters()).device.type
+            scaler = torch.amp.GradScaler(device=dev)
+        self.scaler = scaler if self.enable_amp else None
+        self._count = 0
+        backbone = getattr(model, "backbone", model)
+        if hasattr(backbone, "set_compute_dtype"):
+            backbone.set_compute_dtype(torch.bfloat16 if self.enable_amp else torch.float32)
+
+    def _zero(self):
+        if self.sync is not None:
+            self.sync.zero_grad()
+        else:
+            self.optimizer.zero_grad()
+
+    def __call__(self, input_dict):
+        """One run_step: returns the model's output dict; `stepped` says whether the optimizer advanced."""
+        if self._count == 0:
+            self._zero()
+        out = self.model(input_dict)
+        loss = out["loss"] / self.accum
+        if self.scaler is not None:
+            self.scaler.scale(loss).backward()
+        else:
+            loss.backward()
+        self._count += 1
+        self.stepped = False
+        if self._count >= self.accum:
+            if self.sync is not None:
+                self.sync.finish()                 # the averaged gradients are in place before unscale / clip
+            params = list(self.model.parameters())          # clip_grad_norm_(self.model.parameters(), ...) (:220, :234)
+            if self.scaler is not None:
+                self.scaler.unscale_(self.optimizer)
+                if self.clip_grad is not None:
+                    torch.nn.utils.clip_grad_norm_(params, self.clip_grad)
+                self.scaler.step(self.optimizer)
+                scale = self.scaler.get_scale()
+                self.scaler.update()
+                self.stepped = scale <= self.scaler.get_scale()      # skipped steps shrink the scale (:226-231)
+                if self.stepped and self.scheduler is not None:
+                    self.scheduler.step()
+            else:
+                if self.clip_grad is not None:
+                    torch.nn.utils.clip_grad_norm_(params, self.clip_grad)
+                self.optimizer.step()
+                self.stepped = True
+                if self.scheduler is not None:
+                    self.scheduler.step()
+            self._count = 0
+        return out

@@ -333,3 +333,82 @@ def test_sonata_state_dict_matches_reference():
         m = M.DefaultSegmentorV2(cfg["num_classes"], cfg["out_channels"], backbone=dict(type="PT-v3m2", **cfg["backbone"]))
         got = {k: list(v.shape) for k, v in m.state_dict().items() if not k.endswith("num_batches_tracked")}
         assert got == shapes[tag], (tag, set(got) ^ set(shapes[tag]))
+
+
+class _Toy(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        torch.manual_seed(0)
+        self.net = torch.nn.Sequential(torch.nn.Linear(4, 8), torch.nn.GELU(), torch.nn.Linear(8, 1))
+
+    def forward(self, d):
+        return dict(loss=(self.net(d["x"]) * d["w"]).square().mean())
+
+
+def _ref_run_step(model, opt, sched, scaler, batches, accum, clip):
+    """The reference sequence, engines/train.py:196-239, written out literally."""
+    count, stepped = 0, []
+    for b in batches:
+        if count == 0:
+            opt.zero_grad()
+        loss = model(b)["loss"] / accum
+        if scaler is not None:
+            scaler.scale(loss).backward()
+        else:
+            loss.backward()
+        count += 1
+        if count >= accum:
+            if scaler is not None:
+                scaler.unscale_(opt)
+                if clip is not None:
+                    torch.nn.utils.clip_grad_norm_(model.parameters(), clip)
+                scaler.step(opt)
+                scale = scaler.get_scale()
+                scaler.update()
+                if scale <= scaler.get_scale():
+                    sched.step()
+                    stepped.append(True)
+                else:
+                    stepped.append(False)
+            else:
+                if clip is not None:
+                    torch.nn.utils.clip_grad_norm_(model.parameters(), clip)
+                opt.step()
+                sched.step()
+                stepped.append(True)
+            count = 0
+    return stepped
+
+
+@pytest.mark.parametrize("amp", [False, True])
+def test_train_step_follows_reference_run_step(amp):
+    """train.TrainStep against the reference's Trainer.run_step order of operations (engines/train.py:184-245) on a toy
+    model: gradient accumulation, clipping after unscale_, GradScaler skip (a non-finite batch) holding the scheduler
+    back.  CPU: torch.amp.GradScaler('cpu'); the model-side mixed precision (compute_dtype) is covered by the GPU tests."""
+    from ptv3_b200 import train
+    g = torch.Generator().manual_seed(5)
+    batches = [dict(x=torch.randn(6, 4, generator=g), w=torch.ones(6, 1)) for _ in range(8)]
+    if amp:
+        batches[4]["w"] = torch.full((6, 1), float("inf"))       # the third optimizer step overflows -> skipped
+    out = []
+    for mine in (False, True):
+        m = _Toy()
+        opt = torch.optim.AdamW(m.parameters(), lr=1e-2, weight_decay=0.05)
+        sched = torch.optim.lr_scheduler.StepLR(opt, step_size=1, gamma=0.5)
+        scaler = torch.amp.GradScaler(device="cpu", init_scale=1024.0) if amp else None
+        if mine:
+            ts = train.TrainStep(m, opt, sched, enable_amp=amp, clip_grad=0.5, gradient_accumulation_steps=2, scaler=scaler)
+            stepped = []
+            for i, b in enumerate(batches):
+                ts(b)
+                if i % 2 == 1:
+                    stepped.append(ts.stepped)
+        else:
+            stepped = _ref_run_step(m, opt, sched, scaler, batches, 2, 0.5)
+        out.append((stepped, [p.detach().clone() for p in m.parameters()], sched.get_last_lr(),
+                    scaler.get_scale() if amp else None))
+    assert out[0][0] == out[1][0] == ([True, True, False, True] if amp else [True] * 4)
+    assert all(torch.equal(a, b) for a, b in zip(out[0][1], out[1][1]))
+    assert out[0][2] == out[1][2] and out[0][3] == out[1][3]
+    with pytest.raises(NotImplementedError):
+        train.TrainStep(_Toy(), None, enable_amp=True, amp_dtype="float16")
